@@ -1,0 +1,187 @@
+/*
+ * ugu_b200_raster.h — C-ABI of the B200-native (sm_100a) software mesh rasterizer.
+ *
+ * This is the drop-in boundary for ONE path of unclearness/ugu: ugu::Rasterizer behind the
+ * ugu::RendererCpu interface (reference include/ugu/renderer/cpu/renderer.h:42-76,
+ * include/ugu/renderer/cpu/rasterizer.h:14-53, src/renderer/cpu/rasterizer.cc:105-307).
+ * The reference has no FFI; the host-side C++ class that a maintainer adds to the reference tree
+ * (ugu::RasterizerCuda : ugu::RendererCpu, ugu_b200/cpp/rasterizer_cuda.{h,cc}) binds exactly
+ * these entry points.  See INTEGRATION.md.
+ *
+ * Conventions: plain C, POD descriptors, opaque handle, int status (0 = ok, see UGU_B200_E_*),
+ * no exceptions, no C++/torch types.  All matrices are ROW-MAJOR.  All images are contiguous,
+ * row-major, channels interleaved — the layout of ugu::ImageBase (reference
+ * include/ugu/image.h:374-382,410-413).  There is NO CPU fallback: every entry point that computes
+ * fails with UGU_B200_E_CUDA when no sm_100 device / driver is available.
+ */
+#ifndef UGU_B200_RASTER_H_
+#define UGU_B200_RASTER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UGU_B200_ABI_VERSION 1
+
+enum {
+  UGU_B200_OK = 0,
+  UGU_B200_E_INVALID = 1,   /* failed validation (mirrors util_private.cc:19-67 returning false) */
+  UGU_B200_E_CUDA = 2,      /* CUDA runtime/driver error, or no usable device */
+  UGU_B200_E_NOMEM = 3,
+  UGU_B200_E_STATE = 4      /* call order violated (mesh not prepared, ...) */
+};
+
+/* Enumerators mirror the reference enums value for value. */
+enum { UGU_B200_COLOR_NONE = 0, UGU_B200_COLOR_TEXTURE = 1, UGU_B200_COLOR_VERTEX = 2 }; /* renderer/base.h:11-15 */
+enum { UGU_B200_INTERP_NN = 0, UGU_B200_INTERP_BILINEAR = 1 };                           /* common.h:50-53 */
+enum { UGU_B200_NORMAL_FACE = 0, UGU_B200_NORMAL_VERTEX = 1 };                           /* renderer/base.h:19-22 */
+enum { UGU_B200_SHADING_NONE = 0, UGU_B200_SHADING_LAMBERTIAN = 1, UGU_B200_SHADING_OREN_NAYAR = 2 }; /* base.h:26-32 */
+
+/* Replaces ugu::RendererCpuOption (renderer/cpu/renderer.h:17-38). */
+typedef struct ugu_b200_option {
+  int32_t diffuse_color;
+  int32_t interp;
+  int32_t shading_normal;
+  int32_t diffuse_shading;
+  int32_t backface_culling;
+  float depth_scale;       /* accepted and ignored, as the reference Rasterizer does */
+  float oren_nayar_sigma;  /* the reference's CopyTo never copies it; hosts pass 0.3f (renderer.h:30-37) */
+} ugu_b200_option;
+
+/* Replaces the read side of ugu::Mesh (mesh.h:137-148): AoS host arrays exactly as
+ * std::vector<Eigen::Vector3f/3i/2f>::data() lays them out.  Repacked to device SoA on upload. */
+typedef struct ugu_b200_mesh_desc {
+  int32_t num_vertices;
+  int32_t num_normals;
+  int32_t num_colors;        /* 0 or num_vertices */
+  int32_t num_faces;
+  int32_t num_face_normals;  /* 0 or num_faces */
+  int32_t num_uv;
+  int32_t num_materials;
+  int32_t reserved;
+  const float* vertices;          /* num_vertices * 3 */
+  const float* normals;           /* num_normals * 3 */
+  const float* vertex_colors;     /* num_colors * 3, RGB as float 0..255 */
+  const int32_t* vertex_indices;  /* num_faces * 3 */
+  const int32_t* normal_indices;  /* num_faces * 3, or NULL */
+  const float* face_normals;      /* num_face_normals * 3 */
+  const float* uv;                /* num_uv * 2 */
+  const int32_t* uv_indices;      /* num_faces * 3, or NULL */
+  const int32_t* material_ids;    /* num_faces, or NULL */
+  const uint8_t* const* tex_data; /* num_materials pointers to RGB8 (Image3b) texels, NULL = empty */
+  const int32_t* tex_w;
+  const int32_t* tex_h;
+} ugu_b200_mesh_desc;
+
+/* Replaces what Render reads from ugu::PinholeCamera each call: size, intrinsics
+ * (camera.h:341-347) and the float pose constants derived as rasterizer.cc:118-119
+ * (w2c().rotation().cast<float>(), w2c().translation().cast<float>()) and camera.h:321
+ * (c2w().matrix().block<3,3>(0,0).cast<float>()). */
+typedef struct ugu_b200_camera {
+  int32_t width, height;
+  float fx, fy, cx, cy;
+  float w2c_R[9];
+  float w2c_t[3];
+  float c2w_R[9];
+} ugu_b200_camera;
+
+/* The five outputs of RendererCpu::Render (renderer.h:60-61).  Any pointer may be NULL; all NULL is
+ * an error (util_private.cc:63-67).  Sizes: color W*H*3 u8 (RGB), depth W*H f32, normal W*H*3 f32
+ * (camera space), mask W*H u8 (0/255), face_id W*H i32 (-1 = none). */
+typedef struct ugu_b200_outputs {
+  uint8_t* color;
+  float* depth;
+  float* normal;
+  uint8_t* mask;
+  int32_t* face_id;
+} ugu_b200_outputs;
+
+/* Per-stage device timings (CUDA events on the rendering stream) and counters, accumulated since
+ * the last ugu_b200_rasterizer_reset_stats(). */
+enum {
+  UGU_B200_STAGE_VERTEX = 0,   /* vertex transform + projection              (rasterizer.cc:125-136) */
+  UGU_B200_STAGE_RASTER = 1,   /* triangle setup, small-triangle raster, large-triangle enqueue (:162-241) */
+  UGU_B200_STAGE_BINNED = 2,   /* large-triangle tile-job raster              (:194-241) */
+  UGU_B200_STAGE_RESOLVE = 3,  /* resolve + attributes + shading + packing    (:244-301) */
+  UGU_B200_NUM_STAGES = 4
+};
+typedef struct ugu_b200_stats {
+  double stage_ms[UGU_B200_NUM_STAGES]; /* summed event time of each stage over timed views */
+  uint64_t timed_views;                 /* views that contributed to stage_ms */
+  uint64_t views;                       /* views rendered */
+  uint64_t kernel_launches;             /* kernels launched by this library */
+  uint64_t h2d_bytes;                   /* per-view host->device bytes (camera constants) */
+  uint64_t d2h_bytes;                   /* device->host bytes of outputs */
+  uint64_t large_triangles;             /* last synchronous view: triangles sent to the tile-job path */
+  uint64_t tile_jobs;                   /* last synchronous view: 8x4-pixel tile jobs */
+  uint64_t hazard_fragments;            /* last synchronous view: fragments with z < FLT_MIN or NaN */
+} ugu_b200_stats;
+
+typedef struct ugu_b200_rasterizer ugu_b200_rasterizer;
+
+int ugu_b200_abi_version(void);
+
+/* Number of usable sm_100 devices (0 if none / no driver).  Never fails. */
+int ugu_b200_device_count(void);
+
+/* ctor of ugu::Rasterizer (rasterizer.cc:351-357).  `device` is a CUDA ordinal. */
+int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out);
+void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r);
+
+/* Rasterizer::set_option (rasterizer.cc:73-75). */
+int ugu_b200_rasterizer_set_option(ugu_b200_rasterizer* r, const ugu_b200_option* opt);
+
+/* Rasterizer::set_mesh + PrepareMesh (rasterizer.cc:77-99): the one-time H2D upload + SoA repack.
+ * The host arrays are not referenced after the call returns. */
+int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_desc* mesh);
+
+/* Rasterizer::Render (rasterizer.cc:105-307) into HOST buffers: validates, renders, copies the
+ * requested outputs device->host and returns when they are complete.  Pinned buffers (from
+ * ugu_b200_host_alloc or cudaHostRegister) are written by DMA directly; pageable ones through an
+ * internal pinned staging ring. */
+int ugu_b200_rasterizer_render(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                               const ugu_b200_outputs* host_out);
+
+/* Same, outputs left in DEVICE memory (16-byte aligned device pointers), asynchronous on `stream`
+ * (a cudaStream_t passed as void*; NULL = the rasterizer's own stream). */
+int ugu_b200_rasterizer_render_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                      const ugu_b200_outputs* dev_out, void* stream);
+
+/* Multi-view batch (the ex09 orbit loop, examples/ex09_renderer_realtime.cc:125-182): view i writes
+ * at element offset i*W*H of every non-NULL output.  All cameras must share width/height.
+ * `outputs_on_device` selects device-resident (async on `stream`) or host (synchronous) outputs. */
+int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
+                                     const ugu_b200_camera* cams, const ugu_b200_outputs* out,
+                                     int32_t outputs_on_device, void* stream);
+
+/* Block until everything queued by this rasterizer has finished; returns the first deferred error. */
+int ugu_b200_rasterizer_sync(ugu_b200_rasterizer* r);
+
+/* Rasterizer::RenderW's depth conversion (rasterizer.cc:329-344 + ConvertTo, image_proc.h:453-460):
+ * truncating f32 -> u16 cast of a host depth image. */
+int ugu_b200_depth_to_u16(const float* depth, uint16_t* depth_w, size_t count);
+
+/* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
+int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);
+int ugu_b200_rasterizer_get_stats(ugu_b200_rasterizer* r, ugu_b200_stats* out);
+int ugu_b200_rasterizer_reset_stats(ugu_b200_rasterizer* r);
+
+/* Host-side camera constants from a row-major 4x4 double c2w, as PinholeCamera::set_c2w
+ * (camera.h:317-331) and rasterizer.cc:118-119 derive them.  Pure host code, needs no GPU. */
+int ugu_b200_camera_from_c2w(const double* c2w16, int32_t width, int32_t height, float fx, float fy,
+                             float cx, float cy, ugu_b200_camera* out);
+
+/* Pinned host memory for outputs (so Render's D2H is a single DMA). */
+void* ugu_b200_host_alloc(size_t bytes);
+void ugu_b200_host_free(void* p);
+
+/* Message of the last error on this rasterizer (or of the last handle-less call when r == NULL). */
+const char* ugu_b200_last_error(const ugu_b200_rasterizer* r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UGU_B200_RASTER_H_ */

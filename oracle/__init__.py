@@ -1,0 +1,243 @@
+"""TEST INFRASTRUCTURE — python loaders for the two checkers.
+
+  OraclePort     oracle/liboracle.so        plain-C restatement (oracle/raster_oracle.c)
+  OracleRef      oracle/_ref/libugu_ref.so  the unmodified reference Rasterizer + oracle/ref_shim.cc
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this
+package.  Nothing under ugu_b200/ does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+PORT_LIB = HERE / "liboracle.so"
+REF_LIB = HERE / "_ref" / "libugu_ref.so"
+
+
+def build_port(force: bool = False) -> Path:
+    src = HERE / "raster_oracle.c"
+    if force or not PORT_LIB.exists() or PORT_LIB.stat().st_mtime < src.stat().st_mtime:
+        subprocess.run(["make", "-C", str(HERE), "oracle"], check=True, capture_output=True)
+    return PORT_LIB
+
+
+def build_ref() -> Path:
+    """Compile the reference from /root/reference (only possible where that tree exists)."""
+    subprocess.run(["make", "-C", str(HERE), "-j8", "ref"], check=True, capture_output=True)
+    return REF_LIB
+
+
+def ref_available() -> bool:
+    return REF_LIB.exists()
+
+
+class _MeshDesc(C.Structure):
+    _fields_ = [("num_vertices", C.c_int32), ("num_normals", C.c_int32), ("num_colors", C.c_int32),
+                ("num_faces", C.c_int32), ("num_face_normals", C.c_int32), ("num_uv", C.c_int32),
+                ("num_materials", C.c_int32), ("pad_", C.c_int32),
+                ("vertices", C.c_void_p), ("normals", C.c_void_p), ("vertex_colors", C.c_void_p),
+                ("vertex_indices", C.c_void_p), ("normal_indices", C.c_void_p),
+                ("face_normals", C.c_void_p), ("uv", C.c_void_p), ("uv_indices", C.c_void_p),
+                ("material_ids", C.c_void_p), ("tex_data", C.POINTER(C.c_void_p)),
+                ("tex_w", C.POINTER(C.c_int32)), ("tex_h", C.POINTER(C.c_int32))]
+
+
+class _PortCamera(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("w2c_R", C.c_float * 9),
+                ("w2c_t", C.c_float * 3), ("c2w_R", C.c_float * 9)]
+
+
+class _PortOption(C.Structure):
+    _fields_ = [("diffuse_color", C.c_int32), ("interp", C.c_int32), ("shading_normal", C.c_int32),
+                ("diffuse_shading", C.c_int32), ("backface_culling", C.c_int32),
+                ("depth_scale", C.c_float), ("oren_nayar_sigma", C.c_float)]
+
+
+class _RefCamera(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("c2w", C.c_double * 16)]
+
+
+class _RefOption(C.Structure):
+    _fields_ = [("diffuse_color", C.c_int32), ("interp", C.c_int32), ("shading_normal", C.c_int32),
+                ("diffuse_shading", C.c_int32), ("backface_culling", C.c_int32),
+                ("depth_scale", C.c_float)]
+
+
+class _MeshHolder:
+    """Keeps the numpy arrays alive and exposes the flat descriptor both checkers share."""
+
+    def __init__(self, mesh):
+        f32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1, w))
+        i32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.int32).reshape(-1, w))
+        self.v, self.n, self.c = f32(mesh.vertices, 3), f32(mesh.normals, 3), f32(mesh.vertex_colors, 3)
+        self.vi, self.ni, self.ui = (i32(mesh.vertex_indices, 3), i32(mesh.normal_indices, 3),
+                                     i32(mesh.uv_indices, 3))
+        self.fn, self.uv = f32(mesh.face_normals, 3), f32(mesh.uv, 2)
+        self.mid = np.ascontiguousarray(np.asarray(mesh.material_ids, np.int32).reshape(-1))
+        self.texs = [None if (t.diffuse_tex is None or t.diffuse_tex.size == 0)
+                     else np.ascontiguousarray(t.diffuse_tex, np.uint8) for t in mesh.materials]
+        F, M = len(self.vi), len(self.texs)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        d = _MeshDesc()
+        d.num_vertices, d.num_normals, d.num_colors = len(self.v), len(self.n), len(self.c)
+        d.num_faces, d.num_face_normals, d.num_uv, d.num_materials = F, len(self.fn), len(self.uv), M
+        d.vertices, d.normals, d.vertex_colors = p(self.v), p(self.n), p(self.c)
+        d.vertex_indices = p(self.vi)
+        d.normal_indices = p(self.ni) if len(self.ni) == F and F > 0 else None
+        d.face_normals, d.uv = p(self.fn), p(self.uv)
+        d.uv_indices = p(self.ui) if len(self.ui) == F and F > 0 else None
+        d.material_ids = p(self.mid) if len(self.mid) == F and F > 0 else None
+        self._tp = (C.c_void_p * max(M, 1))(*[None if t is None else t.ctypes.data for t in self.texs])
+        self._tw = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[1] for t in self.texs])
+        self._th = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[0] for t in self.texs])
+        d.tex_data = C.cast(self._tp, C.POINTER(C.c_void_p))
+        d.tex_w = C.cast(self._tw, C.POINTER(C.c_int32))
+        d.tex_h = C.cast(self._th, C.POINTER(C.c_int32))
+        self.desc = d
+
+
+def _alloc_outputs(W, H, want):
+    out = {}
+    if "color" in want:
+        out["color"] = np.empty((H, W, 3), np.uint8)
+    if "depth" in want:
+        out["depth"] = np.empty((H, W), np.float32)
+    if "normal" in want:
+        out["normal"] = np.empty((H, W, 3), np.float32)
+    if "mask" in want:
+        out["mask"] = np.empty((H, W), np.uint8)
+    if "face_id" in want:
+        out["face_id"] = np.empty((H, W), np.int32)
+    return out
+
+
+ALL_OUTPUTS = ("color", "depth", "normal", "mask", "face_id")
+
+
+def _optr(out, k):
+    return out[k].ctypes.data_as(C.c_void_p) if k in out else None
+
+
+class OraclePort:
+    """The plain-C restatement.  Takes the float camera constants (a ugu_b200 `Camera` POD or any
+    object with the same fields) so that it and the CUDA path see identical inputs."""
+
+    def __init__(self, mesh):
+        build_port()
+        self.lib = C.CDLL(str(PORT_LIB))
+        self.lib.oracle_render.restype = C.c_int
+        self.lib.oracle_render.argtypes = [C.POINTER(_MeshDesc), C.POINTER(_PortCamera),
+                                           C.POINTER(_PortOption)] + [C.c_void_p] * 5
+        self.holder = _MeshHolder(mesh)
+
+    def render(self, cam_pod, option, want=ALL_OUTPUTS):
+        cam = _PortCamera()
+        for name, _ in _PortCamera._fields_:
+            setattr(cam, name, getattr(cam_pod, name))
+        opt = _PortOption(int(option.diffuse_color), int(option.interp), int(option.shading_normal),
+                          int(option.diffuse_shading), 1 if option.backface_culling else 0,
+                          float(option.depth_scale), 0.3)  # CopyTo never copies sigma
+        out = _alloc_outputs(cam.width, cam.height, want)
+        rc = self.lib.oracle_render(C.byref(self.holder.desc), C.byref(cam), C.byref(opt),
+                                    *[_optr(out, k) for k in ALL_OUTPUTS])
+        if rc != 0:
+            return None
+        return out
+
+
+class OracleRef:
+    """The compiled, unmodified reference ugu::Rasterizer (present only where oracle/_ref was built)."""
+
+    def __init__(self, mesh=None):
+        if not REF_LIB.exists():
+            raise FileNotFoundError(f"{REF_LIB} not built (needs /root/reference: make -C oracle ref)")
+        lib = C.CDLL(str(REF_LIB))
+        lib.ugu_ref_create.restype = C.c_void_p
+        lib.ugu_ref_create.argtypes = [C.POINTER(_MeshDesc)]
+        lib.ugu_ref_destroy.argtypes = [C.c_void_p]
+        lib.ugu_ref_render.restype = C.c_int
+        lib.ugu_ref_render.argtypes = [C.c_void_p, C.POINTER(_RefCamera), C.POINTER(_RefOption)] + \
+            [C.c_void_p] * 5 + [C.c_int, C.POINTER(C.c_double)]
+        lib.ugu_ref_camera_constants.argtypes = [C.POINTER(C.c_double)] + [C.POINTER(C.c_float)] * 3
+        lib.ugu_ref_lookat_c2w.argtypes = [C.POINTER(C.c_float)] * 3 + [C.POINTER(C.c_double)]
+        lib.ugu_ref_mesh_load_obj.restype = C.c_void_p
+        lib.ugu_ref_mesh_load_obj.argtypes = [C.c_char_p, C.c_char_p]
+        lib.ugu_ref_mesh_free.argtypes = [C.c_void_p]
+        lib.ugu_ref_mesh_sizes.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        lib.ugu_ref_mesh_copy.argtypes = [C.c_void_p] * 11
+        self.lib = lib
+        self.h = None
+        self.holder = None
+        self.last_timing_ms = (0.0, 0.0)
+        if mesh is not None:
+            self.holder = _MeshHolder(mesh)
+            self.h = lib.ugu_ref_create(C.byref(self.holder.desc))
+            if not self.h:
+                raise RuntimeError("ugu_ref_create failed")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.ugu_ref_destroy(self.h)
+            self.h = None
+
+    def render(self, camera, option, want=ALL_OUTPUTS, repeat_warm=False):
+        """`camera` is a ugu_b200.PinholeCamera-like object (width(), height(), c2w(),
+        principal_point(), focal_length())."""
+        cam = _RefCamera()
+        cam.width, cam.height = camera.width(), camera.height()
+        cam.fx, cam.fy = float(camera.focal_length()[0]), float(camera.focal_length()[1])
+        cam.cx, cam.cy = float(camera.principal_point()[0]), float(camera.principal_point()[1])
+        cam.c2w = (C.c_double * 16)(*np.asarray(camera.c2w(), np.float64).reshape(-1))
+        opt = _RefOption(int(option.diffuse_color), int(option.interp), int(option.shading_normal),
+                         int(option.diffuse_shading), 1 if option.backface_culling else 0,
+                         float(option.depth_scale))
+        out = _alloc_outputs(cam.width, cam.height, want)
+        timing = (C.c_double * 2)()
+        rc = self.lib.ugu_ref_render(self.h, C.byref(cam), C.byref(opt),
+                                     *[_optr(out, k) for k in ALL_OUTPUTS],
+                                     1 if repeat_warm else 0, timing)
+        self.last_timing_ms = (timing[0], timing[1])
+        if rc != 0:
+            return None
+        return out
+
+    def camera_constants(self, c2w):
+        m = (C.c_double * 16)(*np.asarray(c2w, np.float64).reshape(-1))
+        R, t, Cm = (C.c_float * 9)(), (C.c_float * 3)(), (C.c_float * 9)()
+        self.lib.ugu_ref_camera_constants(m, R, t, Cm)
+        return (np.array(R, np.float32), np.array(t, np.float32), np.array(Cm, np.float32))
+
+    def lookat_c2w(self, eye, center, up):
+        f3 = lambda a: (C.c_float * 3)(*[float(x) for x in a])
+        m = (C.c_double * 16)()
+        self.lib.ugu_ref_lookat_c2w(f3(eye), f3(center), f3(up), m)
+        return np.array(m, np.float64).reshape(4, 4)
+
+    def load_obj(self, obj_path: str, mtl_dir: str):
+        """Load an OBJ through the reference's own loader; returns a dict of numpy arrays."""
+        h = self.lib.ugu_ref_mesh_load_obj(obj_path.encode(), mtl_dir.encode())
+        if not h:
+            raise RuntimeError(f"reference LoadObj failed for {obj_path}")
+        sz = (C.c_int32 * 9)()
+        self.lib.ugu_ref_mesh_sizes(h, sz)
+        V, Nn, Nc, F, Nfn, Nuv, M, tw, th = list(sz)
+        a = dict(vertices=np.zeros((V, 3), np.float32), normals=np.zeros((Nn, 3), np.float32),
+                 vertex_colors=np.zeros((Nc, 3), np.float32),
+                 vertex_indices=np.zeros((F, 3), np.int32), normal_indices=np.zeros((F, 3), np.int32),
+                 face_normals=np.zeros((Nfn, 3), np.float32), uv=np.zeros((Nuv, 2), np.float32),
+                 uv_indices=np.zeros((F, 3), np.int32), material_ids=np.zeros((F,), np.int32),
+                 tex0=np.zeros((th, tw, 3), np.uint8))
+        p = lambda k: a[k].ctypes.data_as(C.c_void_p) if a[k].size else None
+        self.lib.ugu_ref_mesh_copy(h, p("vertices"), p("normals"), p("vertex_colors"),
+                                   p("vertex_indices"), p("normal_indices"), p("face_normals"),
+                                   p("uv"), p("uv_indices"), p("material_ids"), p("tex0"))
+        self.lib.ugu_ref_mesh_free(h)
+        a["num_materials"] = M
+        return a

@@ -1,0 +1,364 @@
+/*
+ * TEST INFRASTRUCTURE — NOT PART OF THE PRODUCT.
+ *
+ * Plain-C, dependency-free CPU restatement ("port") of the reference software rasterizer
+ * ugu::Rasterizer::Impl::Render (src/renderer/cpu/rasterizer.cc:105-307) together with the pieces of
+ * ugu::PinholeCamera (include/ugu/camera.h:380-387,438-448,482-513) and the pixel shaders
+ * (include/ugu/renderer/cpu/pixel_shader.h:143-148,222-422) that it calls.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
+ * this library, and only as the checker.  Nothing under ugu_b200/ links, imports or executes it.
+ *
+ * Parity status: PINNED.  The reference ships no tests or golden vectors, so this
+ * restatement is pinned differentially: tests/test_oracle_vs_reference.py compares it bit-for-bit
+ * with the compiled, unmodified reference (oracle/_ref/libugu_ref.so, built by oracle/Makefile from
+ * /root/reference) whenever that library is present, and tests/golden/ holds outputs of the compiled
+ * reference that this file must reproduce bit-for-bit everywhere (CPU suite).
+ *
+ * Float discipline: every expression below is evaluated in IEEE binary32 with round-to-nearest
+ * single operations in exactly the association order of the compiled reference (Eigen 3.4.0
+ * fixed-size reductions associate a0*b0 + (a1*b1 + a2*b2), third_party/eigen/Eigen/src/Core/
+ * Redux.h:99-113).  Compile with -ffp-contract=off and without -ffast-math (oracle/Makefile).
+ */
+
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct OracleMesh {
+  int32_t num_vertices;
+  int32_t num_normals;
+  int32_t num_colors;
+  int32_t num_faces;
+  int32_t num_face_normals;
+  int32_t num_uv;
+  int32_t num_materials;
+  int32_t pad_;
+  const float* vertices;          /* num_vertices * 3 */
+  const float* normals;           /* num_normals * 3 */
+  const float* vertex_colors;     /* num_colors * 3, 0..255 as float */
+  const int32_t* vertex_indices;  /* num_faces * 3 */
+  const int32_t* normal_indices;  /* num_faces * 3 or NULL */
+  const float* face_normals;      /* num_face_normals * 3 */
+  const float* uv;                /* num_uv * 2 */
+  const int32_t* uv_indices;      /* num_faces * 3 or NULL */
+  const int32_t* material_ids;    /* num_faces or NULL */
+  const uint8_t* const* tex_data; /* per material RGB8 row-major */
+  const int32_t* tex_w;
+  const int32_t* tex_h;
+} OracleMesh;
+
+/* Float camera constants, derived on the host exactly as rasterizer.cc:118-119 and
+ * camera.h:317-331 do (row-major 3x3). */
+typedef struct OracleCamera {
+  int32_t width, height;
+  float fx, fy, cx, cy;
+  float w2c_R[9];
+  float w2c_t[3];
+  float c2w_R[9];
+} OracleCamera;
+
+typedef struct OracleOption {
+  int32_t diffuse_color;    /* 0 none, 1 texture, 2 vertex     (renderer/base.h:11-15) */
+  int32_t interp;           /* 0 nearest, 1 bilinear           (common.h:50-53) */
+  int32_t shading_normal;   /* 0 face, 1 vertex                (renderer/base.h:19-22) */
+  int32_t diffuse_shading;  /* 0 none, 1 Lambertian, 2 Oren-Nayar (renderer/base.h:26-32) */
+  int32_t backface_culling;
+  float depth_scale;        /* ignored by the Rasterizer */
+  float oren_nayar_sigma;   /* the reference never copies it, so callers pass 0.3f (renderer.h:30-37) */
+} OracleOption;
+
+/* Eigen fixed-size 3-vector reduction order. */
+static inline float dot3(const float* a, const float* b) {
+  return a[0] * b[0] + (a[1] * b[1] + a[2] * b[2]);
+}
+
+/* Row-major 3x3 times vector, each row reduced like dot3. */
+static inline void mat3_mul(const float* M, const float* v, float* out) {
+  float r0 = M[0] * v[0] + (M[1] * v[1] + M[2] * v[2]);
+  float r1 = M[3] * v[0] + (M[4] * v[1] + M[5] * v[2]);
+  float r2 = M[6] * v[0] + (M[7] * v[1] + M[8] * v[2]);
+  out[0] = r0;
+  out[1] = r1;
+  out[2] = r2;
+}
+
+/* rasterizer.cc:25-28 */
+static inline float edge_function(const float* a, const float* b, const float* c) {
+  return (c[0] - a[0]) * (b[1] - a[1]) - (c[1] - a[1]) * (b[0] - a[0]);
+}
+
+/* camera.h:438-448 (ray_c then rotation by c2w_R_f_), evaluated per pixel instead of through the
+ * lazily built table of camera.h:482-513 — the table entries are these very values. */
+static inline void ray_w(const OracleCamera* cam, int x, int y, float* out) {
+  float d[3];
+  d[0] = ((float)x - cam->cx) / cam->fx;
+  d[1] = ((float)y - cam->cy) / cam->fy;
+  d[2] = 1.0f;
+  float n2 = d[0] * d[0] + (d[1] * d[1] + d[2] * d[2]);
+  if (n2 > 0.0f) {
+    float s = sqrtf(n2);
+    d[0] = d[0] / s;
+    d[1] = d[1] / s;
+    d[2] = d[2] / s;
+  }
+  mat3_mul(cam->c2w_R, d, out);
+}
+
+/* static_cast<unsigned char>(float) as x86-64 gcc compiles it: cvttss2si to int32 (0x80000000 when
+ * out of range or NaN), then the low byte. */
+static inline uint8_t f2u8(float f) {
+  if (!(f > -2147483904.0f && f < 2147483648.0f)) return 0;
+  return (uint8_t)(int32_t)f;
+}
+
+/* Image3b::at<Vec3b>(y, x) without bounds checks (image.h:415-427): a linear address.  Reads that
+ * fall outside the buffer are undefined behaviour in the reference; here they return 0, which is
+ * what the reference effectively uses whenever the tap's weight is 0 (uv on the last row/col). */
+static inline void texel(const uint8_t* tex, int w, int h, int x, int y, float* rgb) {
+  int64_t off = ((int64_t)y * w + x) * 3;
+  int64_t last = (int64_t)w * h * 3 - 3;
+  if (off < 0 || off > last) {
+    rgb[0] = rgb[1] = rgb[2] = 0.0f;
+    return;
+  }
+  rgb[0] = (float)tex[off];
+  rgb[1] = (float)tex[off + 1];
+  rgb[2] = (float)tex[off + 2];
+}
+
+static inline int32_t sat_i32(float f) {
+  /* (int32_t)float with the out-of-range cases pinned (UB in the reference; unreachable for
+   * on-contract geometry). */
+  if (!(f > -2147483904.0f)) return INT32_MIN;
+  if (!(f < 2147483648.0f)) return INT32_MAX;
+  return (int32_t)f;
+}
+
+int oracle_render(const OracleMesh* mesh, const OracleCamera* cam, const OracleOption* opt,
+                  uint8_t* color, float* depth, float* normal, uint8_t* mask, int32_t* face_id) {
+  const int W = cam->width, H = cam->height;
+  const size_t P = (size_t)W * (size_t)H;
+  const int V = mesh->num_vertices, F = mesh->num_faces;
+  if (W <= 0 || H <= 0) return 2;
+
+  /* util_private.cc:19-67 — the validations that depend on mesh/option content. */
+  if (opt->backface_culling && mesh->num_face_normals == 0) return 1;
+  if (opt->diffuse_color == 1 && mesh->num_materials == 0) return 1;
+  if (opt->diffuse_color == 1) {
+    for (int i = 0; i < mesh->num_materials; i++)
+      if (mesh->tex_data[i] == NULL || mesh->tex_w[i] < 1 || mesh->tex_h[i] < 1) return 1;
+  }
+  if (opt->diffuse_color == 2 && mesh->num_colors == 0) return 1;
+  if (opt->shading_normal == 0 && mesh->num_face_normals == 0) return 1;
+  if (opt->shading_normal == 1 && mesh->num_normals == 0) return 1;
+  if (!color && !depth && !normal && !mask && !face_id) return 1;
+
+  /* util_private.cc:72-87 */
+  if (color) memset(color, 0, P * 3);
+  if (normal) memset(normal, 0, P * 12);
+  if (mask) memset(mask, 0, P);
+
+  /* pixel_shader.h:143-148 */
+  const float sigma = opt->oren_nayar_sigma;
+  const float sigma_2 = sigma * sigma;
+  const float on_A = 1.0f - (0.5f * sigma_2 / (sigma_2 + 0.33f));
+  const float on_B = 0.45f * sigma_2 / (sigma_2 + 0.09f);
+
+  /* rasterizer.cc:125-136 + camera.h:380-387 */
+  float* img = (float*)malloc((size_t)(V > 0 ? V : 1) * 3 * sizeof(float));
+  float* depth_ = depth ? depth : (float*)malloc(P * sizeof(float));
+  int32_t* fid_ = face_id ? face_id : (int32_t*)malloc(P * sizeof(int32_t));
+  uint8_t* backface = (uint8_t*)calloc(P, 1);
+  float* weight = (float*)calloc(P * 3, sizeof(float));
+  if (!img || !depth_ || !fid_ || !backface || !weight) return 3;
+  for (int i = 0; i < V; i++) {
+    float p[3];
+    mat3_mul(cam->w2c_R, &mesh->vertices[(size_t)i * 3], p);
+    p[0] = p[0] + cam->w2c_t[0];
+    p[1] = p[1] + cam->w2c_t[1];
+    p[2] = p[2] + cam->w2c_t[2];
+    img[(size_t)i * 3 + 0] = cam->fx / p[2] * p[0] + cam->cx;
+    img[(size_t)i * 3 + 1] = cam->fy / p[2] * p[1] + cam->cy;
+    img[(size_t)i * 3 + 2] = p[2];
+  }
+
+  /* rasterizer.cc:138-159 */
+  for (size_t i = 0; i < P; i++) {
+    depth_[i] = 0.0f;
+    fid_[i] = -1;
+  }
+
+  /* rasterizer.cc:162-241 — z-buffer in ascending face order */
+  for (int i = 0; i < F; i++) {
+    const int32_t* face = &mesh->vertex_indices[(size_t)i * 3];
+    const float* v0 = &img[(size_t)face[0] * 3];
+    const float* v1 = &img[(size_t)face[1] * 3];
+    const float* v2 = &img[(size_t)face[2] * 3];
+    if (v0[2] < 0.0f || v1[2] < 0.0f || v2[2] < 0.0f) continue;
+
+    float xmin = fminf(fminf(v0[0], v1[0]), v2[0]);
+    float ymin = fminf(fminf(v0[1], v1[1]), v2[1]);
+    float xmax = fmaxf(fmaxf(v0[0], v1[0]), v2[0]);
+    float ymax = fmaxf(fmaxf(v0[1], v1[1]), v2[1]);
+    if (xmin > (float)(W - 1) || xmax < 0.0f || ymin > (float)(H - 1) || ymax < 0.0f) continue;
+
+    int32_t x0 = sat_i32(ceilf(xmin));
+    if (x0 < 0) x0 = 0;
+    int32_t x1 = sat_i32(floorf(xmax));
+    if (x1 > W - 1) x1 = W - 1;
+    int32_t y0 = sat_i32(ceilf(ymin));
+    if (y0 < 0) y0 = 0;
+    int32_t y1 = sat_i32(floorf(ymax));
+    if (y1 > H - 1) y1 = H - 1;
+
+    float area = edge_function(v0, v1, v2);
+    if (fabsf(area) < FLT_MIN) continue;
+
+    const float* fn = mesh->num_face_normals > i ? &mesh->face_normals[(size_t)i * 3] : NULL;
+    for (int32_t y = y0; y <= y1; ++y) {
+      for (int32_t x = x0; x <= x1; ++x) {
+        float ray[3];
+        ray_w(cam, x, y, ray);
+        int bf = fn ? (dot3(fn, ray) > 0.0f) : 0;
+        float ps[3] = {(float)x, (float)y, 0.0f};
+        float w0 = edge_function(v1, v2, ps);
+        float w1 = edge_function(v2, v0, ps);
+        float w2 = edge_function(v0, v1, ps);
+        if ((!bf && (w0 >= 0 && w1 >= 0 && w2 >= 0)) || (bf && (w0 <= 0 && w1 <= 0 && w2 <= 0))) {
+          w0 /= area;
+          w1 /= area;
+          w2 /= area;
+          w0 /= v0[2];
+          w1 /= v1[2];
+          w2 /= v2[2];
+          float z = 1.0f / (w0 + w1 + w2);
+          w0 = w0 * z;
+          w1 = w1 * z;
+          w2 = w2 * z;
+          size_t pi = (size_t)y * W + x;
+          float d = depth_[pi];
+          if (d < FLT_MIN || z < d) {
+            depth_[pi] = z;
+            fid_[pi] = i;
+            weight[pi * 3 + 0] = w0;
+            weight[pi * 3 + 1] = w1;
+            weight[pi * 3 + 2] = w2;
+            backface[pi] = bf ? 255 : 0;
+          }
+        }
+      }
+    }
+  }
+
+  /* rasterizer.cc:244-301 */
+  for (int y = 0; y < H; y++) {
+    for (int x = 0; x < W; x++) {
+      size_t pi = (size_t)y * W + x;
+      if (opt->backface_culling && backface[pi] == 255) {
+        depth_[pi] = 0.0f;
+        fid_[pi] = -1;
+        continue;
+      }
+      int32_t fid = fid_[pi];
+      if (fid > 0) { /* sic: face 0 is never shaded */
+        float ray[3];
+        ray_w(cam, x, y, ray);
+        float w0 = weight[pi * 3 + 0], w1 = weight[pi * 3 + 1], w2 = weight[pi * 3 + 2];
+        if (mask) mask[pi] = 255;
+
+        float n_w[3] = {0.0f, 0.0f, 0.0f};
+        if (opt->shading_normal == 0) {
+          memcpy(n_w, &mesh->face_normals[(size_t)fid * 3], 12);
+        } else if (opt->shading_normal == 1) {
+          const int32_t* ni = &mesh->normal_indices[(size_t)fid * 3];
+          const float* n0 = &mesh->normals[(size_t)ni[0] * 3];
+          const float* n1 = &mesh->normals[(size_t)ni[1] * 3];
+          const float* n2 = &mesh->normals[(size_t)ni[2] * 3];
+          for (int k = 0; k < 3; k++) n_w[k] = (w0 * n0[k] + w1 * n1[k]) + w2 * n2[k];
+        }
+        if (normal) mat3_mul(cam->w2c_R, n_w, &normal[pi * 3]);
+
+        if (color) {
+          const float u = w1, v = w2;
+          uint8_t* c = &color[pi * 3];
+          /* colourizer: pixel_shader.h:222-359 */
+          if (opt->diffuse_color == 2) {
+            const int32_t* f = &mesh->vertex_indices[(size_t)fid * 3];
+            const float* c0 = &mesh->vertex_colors[(size_t)f[0] * 3];
+            const float* c1 = &mesh->vertex_colors[(size_t)f[1] * 3];
+            const float* c2 = &mesh->vertex_colors[(size_t)f[2] * 3];
+            const float k0 = 1.0f - u - v;
+            for (int k = 0; k < 3; k++) c[k] = f2u8((k0 * c0[k] + u * c1[k]) + v * c2[k]);
+          } else if (opt->diffuse_color == 1) {
+            const int32_t* ui = &mesh->uv_indices[(size_t)fid * 3];
+            const float* t0 = &mesh->uv[(size_t)ui[0] * 2];
+            const float* t1 = &mesh->uv[(size_t)ui[1] * 2];
+            const float* t2 = &mesh->uv[(size_t)ui[2] * 2];
+            const int mat = mesh->material_ids[fid];
+            const uint8_t* tex = mesh->tex_data[mat];
+            const int tw = mesh->tex_w[mat], th = mesh->tex_h[mat];
+            const float k0 = 1.0f - u - v;
+            const float iu = (k0 * t0[0] + u * t1[0]) + v * t2[0];
+            const float iv = (k0 * t0[1] + u * t1[1]) + v * t2[1];
+            const float tx = iu * (float)(tw - 1);
+            const float ty = (1.0f - iv) * (float)(th - 1);
+            if (opt->interp == 0) {
+              float rgb[3];
+              texel(tex, tw, th, sat_i32(roundf(tx)), sat_i32(roundf(ty)), rgb);
+              for (int k = 0; k < 3; k++) c[k] = f2u8(rgb[k]);
+            } else {
+              const int xm = sat_i32(floorf(tx)), ym = sat_i32(floorf(ty));
+              const float lu = tx - (float)xm, lv = ty - (float)ym;
+              float a[3], b[3], cc[3], dd[3];
+              texel(tex, tw, th, xm, ym, a);
+              texel(tex, tw, th, xm + 1, ym, b);
+              texel(tex, tw, th, xm, ym + 1, cc);
+              texel(tex, tw, th, xm + 1, ym + 1, dd);
+              for (int k = 0; k < 3; k++) {
+                float val = (1.0f - lu) * (1.0f - lv) * a[k] + lu * (1.0f - lv) * b[k] +
+                            (1.0f - lu) * lv * cc[k] + lu * lv * dd[k];
+                c[k] = f2u8(val);
+              }
+            }
+          } else {
+            c[0] = c[1] = c[2] = 255;
+          }
+          /* shader: pixel_shader.h:363-422; light_dir == ray_w (rasterizer.cc:293) */
+          if (opt->diffuse_shading == 1) {
+            float coeff = -dot3(ray, n_w);
+            if (coeff < 0.0f) coeff = 0.0f;
+            for (int k = 0; k < 3; k++) c[k] = f2u8(coeff * (float)c[k]);
+          } else if (opt->diffuse_shading == 2) {
+            float dot_light = -dot3(ray, n_w);
+            float theta_i = acosf(dot_light);
+            float dot_ray = -dot3(ray, n_w);
+            float theta_r = acosf(dot_ray);
+            float bl[3], br[3];
+            for (int k = 0; k < 3; k++) {
+              bl[k] = (-n_w[k]) * dot_light - ray[k];
+              br[k] = (-n_w[k]) * dot_light - ray[k];
+            }
+            float phi_diff_cos = fmaxf(0.0f, dot3(bl, br));
+            float alpha = (theta_i < theta_r) ? theta_r : theta_i; /* std::max(theta_i, theta_r) */
+            float beta = (theta_r < theta_i) ? theta_r : theta_i;  /* std::min(theta_i, theta_r) */
+            float coeff = (dot_light > 0.0f ? dot_light : 0.0f) *
+                          (on_A + (on_B * phi_diff_cos * sinf(alpha) * tanf(beta)));
+            for (int k = 0; k < 3; k++) c[k] = f2u8(coeff * (float)c[k]);
+          }
+        }
+      }
+    }
+  }
+
+  free(img);
+  free(backface);
+  free(weight);
+  if (!depth) free(depth_);
+  if (!face_id) free(fid_);
+  return 0;
+}
+
+int oracle_abi_version(void) { return 1; }

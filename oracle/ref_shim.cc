@@ -1,0 +1,292 @@
+// TEST INFRASTRUCTURE — NOT PART OF THE PRODUCT.
+//
+// A thin extern "C" shim around the UNMODIFIED reference ugu::Rasterizer, compiled from the
+// sources where they lie under /root/reference by oracle/Makefile into oracle/_ref/libugu_ref.so.
+// It exists so that tests/ and bench.py's cpu_baseline / `--impl reference` legs can drive the
+// real reference implementation (include/ugu/renderer/cpu/rasterizer.h:14-53,
+// src/renderer/cpu/rasterizer.cc:105-307) from plain arrays.  Nothing under ugu_b200/ may load it.
+//
+// The shim only converts flat arrays <-> ugu::Mesh / ugu::PinholeCamera / ugu::Image and calls the
+// reference's public API in the call order of examples/ex02_renderer.cc:245-278,142-143.
+
+#include <chrono>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+#include "ugu/camera.h"
+#include "ugu/log.h"
+#include "ugu/mesh.h"
+#include "ugu/renderer/cpu/rasterizer.h"
+
+extern "C" {
+
+struct UguRefMeshDesc {
+  int32_t num_vertices;
+  int32_t num_normals;
+  int32_t num_colors;
+  int32_t num_faces;
+  int32_t num_face_normals;
+  int32_t num_uv;
+  int32_t num_materials;
+  int32_t pad_;
+  const float* vertices;          // num_vertices * 3
+  const float* normals;           // num_normals * 3
+  const float* vertex_colors;     // num_colors * 3 (0..255 as float)
+  const int32_t* vertex_indices;  // num_faces * 3
+  const int32_t* normal_indices;  // num_faces * 3 or null
+  const float* face_normals;      // num_face_normals * 3
+  const float* uv;                // num_uv * 2
+  const int32_t* uv_indices;      // num_faces * 3 or null
+  const int32_t* material_ids;    // num_faces or null
+  const uint8_t* const* tex_data; // num_materials pointers, RGB8 row-major
+  const int32_t* tex_w;
+  const int32_t* tex_h;
+};
+
+struct UguRefCamera {
+  int32_t width, height;
+  float fx, fy, cx, cy;
+  double c2w[16];  // row-major 4x4
+};
+
+struct UguRefOption {
+  int32_t diffuse_color;    // ugu::DiffuseColor
+  int32_t interp;           // ugu::ColorInterpolation
+  int32_t shading_normal;   // ugu::ShadingNormal
+  int32_t diffuse_shading;  // ugu::DiffuseShading
+  int32_t backface_culling;
+  float depth_scale;
+};
+
+}  // extern "C"
+
+namespace {
+
+struct RefHandle {
+  std::shared_ptr<ugu::Mesh> mesh;
+  std::shared_ptr<ugu::PinholeCamera> camera;
+  std::unique_ptr<ugu::Rasterizer> renderer;
+  ugu::Image3b color;
+  ugu::Image1f depth;
+  ugu::Image3f normal;
+  ugu::Image1b mask;
+  ugu::Image1i face_id;
+};
+
+template <typename V>
+std::vector<V> ToVec(const typename V::Scalar* p, int n) {
+  std::vector<V> out(static_cast<size_t>(n));
+  constexpr int D = V::RowsAtCompileTime;
+  for (int i = 0; i < n; i++) {
+    for (int k = 0; k < D; k++) out[i][k] = p[static_cast<size_t>(i) * D + k];
+  }
+  return out;
+}
+
+Eigen::Affine3d ToAffine(const double* m) {
+  Eigen::Affine3d a = Eigen::Affine3d::Identity();
+  for (int r = 0; r < 4; r++)
+    for (int c = 0; c < 4; c++) a.matrix()(r, c) = m[r * 4 + c];
+  return a;
+}
+
+double NowMs() {
+  return std::chrono::duration<double, std::milli>(
+             std::chrono::steady_clock::now().time_since_epoch())
+      .count();
+}
+
+}  // namespace
+
+extern "C" {
+
+void* ugu_ref_create(const UguRefMeshDesc* d) {
+  ugu::set_log_level(ugu::LogLevel::kError);
+  auto h = new RefHandle;
+  h->mesh = std::make_shared<ugu::Mesh>();
+  ugu::Mesh& m = *h->mesh;
+  m.set_vertices(ToVec<Eigen::Vector3f>(d->vertices, d->num_vertices));
+  if (d->num_normals > 0) m.set_normals(ToVec<Eigen::Vector3f>(d->normals, d->num_normals));
+  if (d->num_colors > 0)
+    m.set_vertex_colors(ToVec<Eigen::Vector3f>(d->vertex_colors, d->num_colors));
+  m.set_vertex_indices(ToVec<Eigen::Vector3i>(d->vertex_indices, d->num_faces));
+  if (d->normal_indices)
+    m.set_normal_indices(ToVec<Eigen::Vector3i>(d->normal_indices, d->num_faces));
+  if (d->num_face_normals > 0)
+    m.set_face_normals(ToVec<Eigen::Vector3f>(d->face_normals, d->num_face_normals));
+  if (d->num_uv > 0) m.set_uv(ToVec<Eigen::Vector2f>(d->uv, d->num_uv));
+  if (d->uv_indices) m.set_uv_indices(ToVec<Eigen::Vector3i>(d->uv_indices, d->num_faces));
+  if (d->num_materials > 0) {
+    std::vector<ugu::ObjMaterial> mats(d->num_materials);
+    for (int i = 0; i < d->num_materials; i++) {
+      mats[i].name = "mat" + std::to_string(i);
+      if (d->tex_data[i] != nullptr && d->tex_w[i] > 0 && d->tex_h[i] > 0) {
+        mats[i].diffuse_tex = ugu::Image3b::zeros(d->tex_h[i], d->tex_w[i]);
+        std::memcpy(mats[i].diffuse_tex.data, d->tex_data[i],
+                    static_cast<size_t>(d->tex_w[i]) * d->tex_h[i] * 3);
+      }
+    }
+    m.set_materials(mats);
+  }
+  if (d->material_ids) {
+    m.set_material_ids(std::vector<int>(d->material_ids, d->material_ids + d->num_faces));
+  }
+  h->renderer = std::make_unique<ugu::Rasterizer>();
+  h->renderer->set_mesh(h->mesh);
+  if (!h->renderer->PrepareMesh()) {
+    delete h;
+    return nullptr;
+  }
+  return h;
+}
+
+void ugu_ref_destroy(void* handle) { delete static_cast<RefHandle*>(handle); }
+
+// Renders one view.  Any output pointer may be null.  `timing_ms` (optional, 2 doubles) receives
+// [0] wall ms of the whole caller-visible step (set_c2w + Render, i.e. including the lazy ray-table
+// rebuild of include/ugu/camera.h:474-513) and [1] the same again for an immediately repeated Render
+// with the camera untouched (steady state, ray table warm) when `repeat_warm` != 0.
+int ugu_ref_render(void* handle, const UguRefCamera* cam, const UguRefOption* opt, uint8_t* color,
+                   float* depth, float* normal, uint8_t* mask, int32_t* face_id, int repeat_warm,
+                   double* timing_ms) {
+  RefHandle* h = static_cast<RefHandle*>(handle);
+  if (h == nullptr) return -1;
+  ugu::RendererCpuOption o;
+  o.diffuse_color = static_cast<ugu::DiffuseColor>(opt->diffuse_color);
+  o.interp = static_cast<ugu::ColorInterpolation>(opt->interp);
+  o.shading_normal = static_cast<ugu::ShadingNormal>(opt->shading_normal);
+  o.diffuse_shading = static_cast<ugu::DiffuseShading>(opt->diffuse_shading);
+  o.backface_culling = opt->backface_culling != 0;
+  o.depth_scale = opt->depth_scale;
+  h->renderer->set_option(o);
+
+  if (!h->camera || h->camera->width() != cam->width || h->camera->height() != cam->height) {
+    h->camera = std::make_shared<ugu::PinholeCamera>(
+        cam->width, cam->height, Eigen::Affine3d::Identity(), Eigen::Vector2f(cam->cx, cam->cy),
+        Eigen::Vector2f(cam->fx, cam->fy));
+    h->renderer->set_camera(h->camera);
+  }
+  h->camera->set_principal_point(Eigen::Vector2f(cam->cx, cam->cy));
+  h->camera->set_focal_length(Eigen::Vector2f(cam->fx, cam->fy));
+
+  ugu::Image3b* pc = color ? &h->color : nullptr;
+  ugu::Image1f* pd = depth ? &h->depth : nullptr;
+  ugu::Image3f* pn = normal ? &h->normal : nullptr;
+  ugu::Image1b* pm = mask ? &h->mask : nullptr;
+  ugu::Image1i* pf = face_id ? &h->face_id : nullptr;
+
+  double t0 = NowMs();
+  h->camera->set_c2w(ToAffine(cam->c2w));
+  bool ok = h->renderer->Render(pc, pd, pn, pm, pf);
+  double t1 = NowMs();
+  if (timing_ms) timing_ms[0] = t1 - t0;
+  if (ok && repeat_warm) {
+    double t2 = NowMs();
+    ok = h->renderer->Render(pc, pd, pn, pm, pf);
+    double t3 = NowMs();
+    if (timing_ms) timing_ms[1] = t3 - t2;
+  } else if (timing_ms) {
+    timing_ms[1] = 0.0;
+  }
+  if (!ok) return 1;
+  const size_t P = static_cast<size_t>(cam->width) * cam->height;
+  if (color) std::memcpy(color, h->color.data, P * 3);
+  if (depth) std::memcpy(depth, h->depth.data, P * 4);
+  if (normal) std::memcpy(normal, h->normal.data, P * 12);
+  if (mask) std::memcpy(mask, h->mask.data, P);
+  if (face_id) std::memcpy(face_id, h->face_id.data, P * 4);
+  return 0;
+}
+
+// The float camera constants exactly as the reference derives them
+// (src/renderer/cpu/rasterizer.cc:118-119, include/ugu/camera.h:317-331).  Row-major 3x3.
+int ugu_ref_camera_constants(const double* c2w16, float* w2c_R, float* w2c_t, float* c2w_R) {
+  ugu::PinholeCamera cam(4, 4, ToAffine(c2w16), 45.0f);
+  const Eigen::Matrix3f R = cam.w2c().rotation().cast<float>();
+  const Eigen::Vector3f t = cam.w2c().translation().cast<float>();
+  const Eigen::Matrix3f C = cam.c2w().matrix().block<3, 3>(0, 0).cast<float>();
+  for (int r = 0; r < 3; r++) {
+    for (int c = 0; c < 3; c++) {
+      w2c_R[r * 3 + c] = R(r, c);
+      c2w_R[r * 3 + c] = C(r, c);
+    }
+    w2c_t[r] = t[r];
+  }
+  return 0;
+}
+
+// ugu::c2w look-at (include/ugu/util/camera_util.h:26-34) so fixtures can use the very poses of
+// examples/ex02_renderer.cc:49-102 and ex09_renderer_realtime.cc:137-142.  Row-major 4x4 out.
+int ugu_ref_lookat_c2w(const float* eye, const float* center, const float* up, double* c2w16) {
+  Eigen::Matrix4f m;
+  ugu::c2w(Eigen::Vector3f(eye[0], eye[1], eye[2]), Eigen::Vector3f(center[0], center[1], center[2]),
+           Eigen::Vector3f(up[0], up[1], up[2]), &m);
+  for (int r = 0; r < 4; r++)
+    for (int c = 0; c < 4; c++) c2w16[r * 4 + c] = static_cast<double>(m(r, c));
+  return 0;
+}
+
+// --- OBJ loading through the reference (fixture generation only) -------------------------------
+void* ugu_ref_mesh_load_obj(const char* obj_path, const char* mtl_dir) {
+  ugu::set_log_level(ugu::LogLevel::kError);
+  auto m = new ugu::Mesh;
+  if (!m->LoadObj(obj_path, mtl_dir)) {
+    delete m;
+    return nullptr;
+  }
+  return m;
+}
+
+void ugu_ref_mesh_free(void* mesh) { delete static_cast<ugu::Mesh*>(mesh); }
+
+// out[0..8] = V, Nn, Nc, F, Nfn, Nuv, M, tex_w(0), tex_h(0)
+void ugu_ref_mesh_sizes(void* mesh, int32_t* out) {
+  const ugu::Mesh& m = *static_cast<ugu::Mesh*>(mesh);
+  out[0] = static_cast<int32_t>(m.vertices().size());
+  out[1] = static_cast<int32_t>(m.normals().size());
+  out[2] = static_cast<int32_t>(m.vertex_colors().size());
+  out[3] = static_cast<int32_t>(m.vertex_indices().size());
+  out[4] = static_cast<int32_t>(m.face_normals().size());
+  out[5] = static_cast<int32_t>(m.uv().size());
+  out[6] = static_cast<int32_t>(m.materials().size());
+  out[7] = m.materials().empty() ? 0 : m.materials()[0].diffuse_tex.cols;
+  out[8] = m.materials().empty() ? 0 : m.materials()[0].diffuse_tex.rows;
+}
+
+void ugu_ref_mesh_copy(void* mesh, float* vertices, float* normals, float* colors,
+                       int32_t* vertex_indices, int32_t* normal_indices, float* face_normals,
+                       float* uv, int32_t* uv_indices, int32_t* material_ids, uint8_t* tex0) {
+  const ugu::Mesh& m = *static_cast<ugu::Mesh*>(mesh);
+  auto cp3f = [](const std::vector<Eigen::Vector3f>& v, float* o) {
+    if (!o) return;
+    for (size_t i = 0; i < v.size(); i++)
+      for (int k = 0; k < 3; k++) o[i * 3 + k] = v[i][k];
+  };
+  auto cp3i = [](const std::vector<Eigen::Vector3i>& v, int32_t* o) {
+    if (!o) return;
+    for (size_t i = 0; i < v.size(); i++)
+      for (int k = 0; k < 3; k++) o[i * 3 + k] = v[i][k];
+  };
+  cp3f(m.vertices(), vertices);
+  cp3f(m.normals(), normals);
+  cp3f(m.vertex_colors(), colors);
+  cp3i(m.vertex_indices(), vertex_indices);
+  cp3i(m.normal_indices(), normal_indices);
+  cp3f(m.face_normals(), face_normals);
+  if (uv)
+    for (size_t i = 0; i < m.uv().size(); i++) {
+      uv[i * 2] = m.uv()[i][0];
+      uv[i * 2 + 1] = m.uv()[i][1];
+    }
+  cp3i(m.uv_indices(), uv_indices);
+  if (material_ids)
+    for (size_t i = 0; i < m.material_ids().size(); i++) material_ids[i] = m.material_ids()[i];
+  if (tex0 && !m.materials().empty()) {
+    const ugu::Image3b& t = m.materials()[0].diffuse_tex;
+    std::memcpy(tex0, t.data, static_cast<size_t>(t.rows) * t.cols * 3);
+  }
+}
+
+}  // extern "C"

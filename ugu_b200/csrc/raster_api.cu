@@ -1,0 +1,912 @@
+// C-ABI implementation (include/ugu_b200_raster.h) over the kernels in raster_kernels.cuh.
+// One rasterizer handle = one CUDA device + one stream + the device-resident SoA mesh + per-view
+// scratch (projected vertices, visibility buffer, large-triangle queue).  No CPU fallback anywhere:
+// without a usable sm_100 device every computing entry point returns UGU_B200_E_CUDA.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "raster_kernels.cuh"
+#include "ugu_b200_raster.h"
+
+using namespace ugu_b200;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+constexpr int kEventPool = 512;           // timed (stage, view) slots before a drain
+constexpr size_t kStageChunk = 4u << 20;  // pinned staging chunk for pageable destinations
+
+}  // namespace
+
+struct ugu_b200_rasterizer {
+  int device = 0;
+  cudaStream_t stream = nullptr;       // compute stream (own)
+  cudaStream_t copy_stream = nullptr;  // D2H stream for batch overlap
+  std::string error;
+  int deferred_status = UGU_B200_OK;
+
+  ugu_b200_option opt{};
+  bool mesh_ready = false;
+  MeshDev mesh{};
+  bool has_nidx = false, has_uvidx = false, has_matids = false;
+  std::vector<bool> tex_present;
+  std::vector<void*> mesh_allocs;  // everything owned by the current mesh
+
+  // per-view scratch
+  DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
+  size_t vis_pixels = 0;
+
+  // internal device outputs for the host-destination paths (two sets for batch overlap)
+  DevBuf out_color[2], out_depth[2], out_normal[2], out_mask[2], out_fid[2];
+  cudaEvent_t ev_render[2] = {nullptr, nullptr};
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr};
+  bool copied_pending[2] = {false, false};
+
+  // pinned staging for pageable destinations
+  void* staging = nullptr;
+  size_t staging_bytes = 0;
+  std::vector<cudaEvent_t> chunk_events;
+  unsigned long long* counters_host = nullptr;  // pinned snapshot of the device counters
+
+  // profiling
+  bool profiling = false;
+  uint32_t stage_mask = 0;
+  std::vector<cudaEvent_t> ev_pool;  // 2 per slot
+  std::vector<int> ev_stage;         // stage of each used slot
+  int ev_used = 0;
+  ugu_b200_stats stats{};
+};
+
+namespace {
+
+int Fail(ugu_b200_rasterizer* r, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (r) r->error = buf;
+  g_last_error = buf;
+  return code;
+}
+
+#define CU_TRY(r, expr)                                                                     \
+  do {                                                                                      \
+    cudaError_t e__ = (expr);                                                               \
+    if (e__ != cudaSuccess)                                                                 \
+      return Fail((r), e__ == cudaErrorMemoryAllocation ? UGU_B200_E_NOMEM : UGU_B200_E_CUDA, \
+                  "%s failed: %s", #expr, cudaGetErrorString(e__));                         \
+  } while (0)
+
+int Grow(ugu_b200_rasterizer* r, DevBuf* b, size_t bytes) {
+  if (bytes <= b->bytes) return UGU_B200_OK;
+  if (b->p) CU_TRY(r, cudaFree(b->p));
+  b->p = nullptr;
+  b->bytes = 0;
+  CU_TRY(r, cudaMalloc(&b->p, bytes));
+  b->bytes = bytes;
+  return UGU_B200_OK;
+}
+
+void FreeBuf(DevBuf* b) {
+  if (b->p) cudaFree(b->p);
+  b->p = nullptr;
+  b->bytes = 0;
+}
+
+void FreeMesh(ugu_b200_rasterizer* r) {
+  for (void* p : r->mesh_allocs) cudaFree(p);
+  r->mesh_allocs.clear();
+  r->mesh = MeshDev{};
+  r->mesh_ready = false;
+  r->has_nidx = r->has_uvidx = r->has_matids = false;
+  r->tex_present.clear();
+}
+
+template <typename T>
+int MeshAlloc(ugu_b200_rasterizer* r, T** out, size_t count) {
+  void* p = nullptr;
+  CU_TRY(r, cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+  r->mesh_allocs.push_back(p);
+  *out = static_cast<T*>(p);
+  return UGU_B200_OK;
+}
+
+inline unsigned Blocks(size_t n, unsigned threads) { return (unsigned)((n + threads - 1) / threads); }
+
+bool IndicesInRange(const int32_t* idx, size_t count, int32_t limit) {
+  int32_t lo = 0, hi = -1;
+  for (size_t i = 0; i < count; i++) {
+    lo = std::min(lo, idx[i]);
+    hi = std::max(hi, idx[i]);
+  }
+  return lo >= 0 && hi < limit;
+}
+
+// ---- profiling ---------------------------------------------------------------------------------
+int DrainEvents(ugu_b200_rasterizer* r) {
+  for (int s = 0; s < r->ev_used; s++) {
+    CU_TRY(r, cudaEventSynchronize(r->ev_pool[2 * s + 1]));
+    float ms = 0.f;
+    CU_TRY(r, cudaEventElapsedTime(&ms, r->ev_pool[2 * s], r->ev_pool[2 * s + 1]));
+    r->stats.stage_ms[r->ev_stage[s]] += ms;
+  }
+  r->ev_used = 0;
+  return UGU_B200_OK;
+}
+
+struct StageTimer {
+  ugu_b200_rasterizer* r;
+  cudaStream_t st;
+  int slot = -1;
+  StageTimer(ugu_b200_rasterizer* r_, cudaStream_t st_, int stage) : r(r_), st(st_) {
+    if (!r->profiling || !(r->stage_mask & (1u << stage))) return;
+    if (r->ev_used >= kEventPool) DrainEvents(r);
+    slot = r->ev_used++;
+    r->ev_stage[slot] = stage;
+    cudaEventRecord(r->ev_pool[2 * slot], st);
+  }
+  ~StageTimer() {
+    if (slot >= 0) cudaEventRecord(r->ev_pool[2 * slot + 1], st);
+  }
+};
+
+// ---- validation (mirrors ValidateAndInitBeforeRender, util_private.cc:12-67) --------------------
+int Validate(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* out) {
+  if (cam == nullptr) return Fail(r, UGU_B200_E_INVALID, "camera has not been set");
+  if (!r->mesh_ready) return Fail(r, UGU_B200_E_STATE, "mesh has not been initialized");
+  const ugu_b200_option& o = r->opt;
+  const MeshDev& m = r->mesh;
+  if (o.backface_culling && m.num_face_normals == 0)
+    return Fail(r, UGU_B200_E_INVALID, "specified back-face culling but face normal is empty.");
+  if (o.diffuse_color == UGU_B200_COLOR_TEXTURE && m.num_materials == 0)
+    return Fail(r, UGU_B200_E_INVALID, "specified texture as diffuse color but texture is empty.");
+  if (o.diffuse_color == UGU_B200_COLOR_TEXTURE) {
+    for (int i = 0; i < m.num_materials; i++)
+      if (!r->tex_present[i])
+        return Fail(r, UGU_B200_E_INVALID,
+                    "specified texture as diffuse color but %d th texture is empty.", i);
+    if (m.num_uv == 0 || !r->has_uvidx || !r->has_matids)
+      return Fail(r, UGU_B200_E_INVALID,
+                  "specified texture as diffuse color but uv / uv_indices / material_ids are empty.");
+  }
+  if (o.diffuse_color == UGU_B200_COLOR_VERTEX && m.num_colors == 0)
+    return Fail(r, UGU_B200_E_INVALID,
+                "specified vertex color as diffuse color but vertex color is empty.");
+  if (o.shading_normal == UGU_B200_NORMAL_FACE && m.num_face_normals == 0)
+    return Fail(r, UGU_B200_E_INVALID,
+                "specified face normal as shading normal but face normal is empty.");
+  if (o.shading_normal == UGU_B200_NORMAL_VERTEX && (m.num_normals == 0 || !r->has_nidx))
+    return Fail(r, UGU_B200_E_INVALID,
+                "specified vertex normal as shading normal but vertex normal is empty.");
+  if (out == nullptr ||
+      (!out->color && !out->depth && !out->normal && !out->mask && !out->face_id))
+    return Fail(r, UGU_B200_E_INVALID, "all arguments are nullptr. nothing to do");
+  if (cam->width <= 0 || cam->height <= 0)
+    return Fail(r, UGU_B200_E_INVALID, "camera size %dx%d is invalid", cam->width, cam->height);
+  if (o.diffuse_color < 0 || o.diffuse_color > 2 || o.interp < 0 || o.interp > 1 ||
+      o.shading_normal < 0 || o.shading_normal > 1 || o.diffuse_shading < 0 || o.diffuse_shading > 2)
+    return Fail(r, UGU_B200_E_INVALID, "option enumerator out of range");
+  return UGU_B200_OK;
+}
+
+// ---- per-view scratch --------------------------------------------------------------------------
+int EnsureFrame(ugu_b200_rasterizer* r, int W, int H, cudaStream_t st) {
+  const size_t P = (size_t)W * H;
+  int rc;
+  if ((rc = Grow(r, &r->ray_dx, (size_t)W * 4))) return rc;
+  if ((rc = Grow(r, &r->ray_dy, (size_t)H * 4))) return rc;
+  if (P != r->vis_pixels || r->vis.bytes < P * 8) {
+    // (re)size + fill with EMPTY; afterwards resolve_kernel leaves it EMPTY after every view
+    if ((rc = Grow(r, &r->vis, P * 8))) return rc;
+    fill_u64<<<Blocks(P, 256), 256, 0, st>>>((unsigned long long*)r->vis.p, P, kVisEmpty);
+    r->stats.kernel_launches++;
+    CU_TRY(r, cudaGetLastError());
+    r->vis_pixels = P;
+  }
+  return UGU_B200_OK;
+}
+
+void MakeViewParams(const ugu_b200_camera* cam, ViewParams* vp) {
+  vp->W = cam->width;
+  vp->H = cam->height;
+  vp->fx = cam->fx;
+  vp->fy = cam->fy;
+  vp->cx = cam->cx;
+  vp->cy = cam->cy;
+  vp->wm1 = (float)(cam->width - 1);
+  vp->hm1 = (float)(cam->height - 1);
+  memcpy(vp->w2c_R, cam->w2c_R, sizeof(vp->w2c_R));
+  memcpy(vp->w2c_t, cam->w2c_t, sizeof(vp->w2c_t));
+  memcpy(vp->c2w_R, cam->c2w_R, sizeof(vp->c2w_R));
+}
+
+int g_num_sms = 148;
+
+// Launch the four kernels of one view into device outputs `dout` on stream `st`.
+int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
+               cudaStream_t st) {
+  int rc = EnsureFrame(r, cam->width, cam->height, st);
+  if (rc) return rc;
+  ViewParams vp;
+  MakeViewParams(cam, &vp);
+  FrameDev fr;
+  fr.proj = (float4*)r->proj.p;
+  fr.ray_dx = (float*)r->ray_dx.p;
+  fr.ray_dy = (float*)r->ray_dy.p;
+  fr.vis = (unsigned long long*)r->vis.p;
+  fr.counters = (unsigned long long*)r->counters.p;
+  fr.q_face = (int*)r->q_face.p;
+  fr.q_job = (unsigned long long*)r->q_job.p;
+  const MeshDev& m = r->mesh;
+
+  ShadeParams sp;
+  sp.diffuse_color = r->opt.diffuse_color;
+  sp.interp = r->opt.interp;
+  sp.shading_normal = r->opt.shading_normal;
+  sp.diffuse_shading = r->opt.diffuse_shading;
+  sp.backface_culling = r->opt.backface_culling;
+  {  // OrenNayarParam (pixel_shader.h:143-148)
+    const float sigma = r->opt.oren_nayar_sigma;
+    const float s2 = sigma * sigma;
+    sp.on_A = 1.0f - (0.5f * s2 / (s2 + 0.33f));
+    sp.on_B = 0.45f * s2 / (s2 + 0.09f);
+  }
+  sp.color = dout->color;
+  sp.depth = dout->depth;
+  sp.normal = dout->normal;
+  sp.mask = dout->mask;
+  sp.face_id = dout->face_id;
+
+  const size_t P = (size_t)vp.W * vp.H;
+  {
+    StageTimer t(r, st, UGU_B200_STAGE_VERTEX);
+    const size_t threads = std::max<size_t>((size_t)(m.V + 3) / 4, (size_t)vp.W + vp.H);
+    vertex_kernel<<<Blocks(threads, 256), 256, 0, st>>>(vp, m, fr);
+  }
+  if (m.F > 0) {
+    StageTimer t(r, st, UGU_B200_STAGE_RASTER);
+    raster_kernel<<<Blocks((size_t)m.F, 256), 256, 0, st>>>(vp, m, fr);
+  }
+  if (m.F > 0) {
+    StageTimer t(r, st, UGU_B200_STAGE_BINNED);
+    binned_kernel<<<g_num_sms * 8, 128, 0, st>>>(vp, m, fr);
+  }
+  {
+    StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
+    resolve_kernel<<<Blocks((P + 3) / 4, 256), 256, 0, st>>>(vp, m, fr, sp);
+  }
+  CU_TRY(r, cudaGetLastError());
+  r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
+  r->stats.views++;
+  if (r->profiling) r->stats.timed_views++;
+  r->stats.h2d_bytes += sizeof(ViewParams);
+  return UGU_B200_OK;
+}
+
+bool IsPinnedHost(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+int EnsureInternalOutputs(ugu_b200_rasterizer* r, int set, const ugu_b200_outputs* want, size_t P,
+                          ugu_b200_outputs* dout) {
+  int rc;
+  memset(dout, 0, sizeof(*dout));
+  if (want->color) {
+    if ((rc = Grow(r, &r->out_color[set], (P * 3 + 15) & ~size_t(15)))) return rc;
+    dout->color = (uint8_t*)r->out_color[set].p;
+  }
+  if (want->depth) {
+    if ((rc = Grow(r, &r->out_depth[set], P * 4 + 16))) return rc;
+    dout->depth = (float*)r->out_depth[set].p;
+  }
+  if (want->normal) {
+    if ((rc = Grow(r, &r->out_normal[set], P * 12 + 16))) return rc;
+    dout->normal = (float*)r->out_normal[set].p;
+  }
+  if (want->mask) {
+    if ((rc = Grow(r, &r->out_mask[set], P + 16))) return rc;
+    dout->mask = (uint8_t*)r->out_mask[set].p;
+  }
+  if (want->face_id) {
+    if ((rc = Grow(r, &r->out_fid[set], P * 4 + 16))) return rc;
+    dout->face_id = (int32_t*)r->out_fid[set].p;
+  }
+  return UGU_B200_OK;
+}
+
+struct CopySeg {
+  void* dst;
+  const void* src;
+  size_t bytes;
+};
+
+int CollectSegs(const ugu_b200_outputs* host, const ugu_b200_outputs* dev, size_t P, size_t view,
+                std::vector<CopySeg>* segs) {
+  if (host->color) segs->push_back({host->color + view * P * 3, dev->color, P * 3});
+  if (host->depth) segs->push_back({host->depth + view * P, dev->depth, P * 4});
+  if (host->normal) segs->push_back({host->normal + view * P * 3, dev->normal, P * 12});
+  if (host->mask) segs->push_back({host->mask + view * P, dev->mask, P});
+  if (host->face_id) segs->push_back({host->face_id + view * P, dev->face_id, P * 4});
+  return UGU_B200_OK;
+}
+
+// Device -> host copy of the segments on `st`.  Pinned destinations: one async DMA each.
+// Pageable destinations: chunked through the pinned staging buffer, the host memcpy of chunk k
+// overlapping the DMA of chunk k+1.  Returns after everything has landed in the destinations.
+int CopyOut(ugu_b200_rasterizer* r, const std::vector<CopySeg>& segs, cudaStream_t st) {
+  std::vector<CopySeg> pageable;
+  size_t pageable_bytes = 0;
+  for (const CopySeg& s : segs) {
+    r->stats.d2h_bytes += s.bytes;
+    if (IsPinnedHost(s.dst)) {
+      CU_TRY(r, cudaMemcpyAsync(s.dst, s.src, s.bytes, cudaMemcpyDeviceToHost, st));
+    } else {
+      pageable.push_back(s);
+      pageable_bytes += s.bytes;
+    }
+  }
+  if (!pageable.empty()) {
+    if (r->staging_bytes < pageable_bytes) {
+      if (r->staging) cudaFreeHost(r->staging);
+      r->staging = nullptr;
+      r->staging_bytes = 0;
+      CU_TRY(r, cudaHostAlloc(&r->staging, pageable_bytes, cudaHostAllocDefault));
+      r->staging_bytes = pageable_bytes;
+    }
+    struct Chunk {
+      void* dst;
+      const void* stage;
+      size_t bytes;
+    };
+    std::vector<Chunk> chunks;
+    size_t off = 0;
+    for (const CopySeg& s : pageable) {
+      for (size_t o = 0; o < s.bytes; o += kStageChunk) {
+        const size_t n = std::min(kStageChunk, s.bytes - o);
+        char* stage = (char*)r->staging + off;
+        CU_TRY(r, cudaMemcpyAsync(stage, (const char*)s.src + o, n, cudaMemcpyDeviceToHost, st));
+        if (chunks.size() >= r->chunk_events.size()) {
+          cudaEvent_t e;
+          CU_TRY(r, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+          r->chunk_events.push_back(e);
+        }
+        CU_TRY(r, cudaEventRecord(r->chunk_events[chunks.size()], st));
+        chunks.push_back({(char*)s.dst + o, stage, n});
+        off += n;
+      }
+    }
+    for (size_t i = 0; i < chunks.size(); i++) {
+      CU_TRY(r, cudaEventSynchronize(r->chunk_events[i]));
+      memcpy(chunks[i].dst, chunks[i].stage, chunks[i].bytes);
+    }
+  }
+  CU_TRY(r, cudaStreamSynchronize(st));
+  return UGU_B200_OK;
+}
+
+int SnapshotCounters(ugu_b200_rasterizer* r) {
+  // counters[4..6] hold the previous view's (queue, hazards, -) as saved by resolve_kernel
+  const unsigned long long packed = r->counters_host[0];
+  r->stats.large_triangles = packed >> kQueueJobBits;
+  r->stats.tile_jobs = packed & kQueueJobMask;
+  r->stats.hazard_fragments = r->counters_host[1];
+  return UGU_B200_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+extern "C" {
+
+int ugu_b200_abi_version(void) { return UGU_B200_ABI_VERSION; }
+
+int ugu_b200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  int usable = 0;
+  for (int i = 0; i < n; i++) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, i) == cudaSuccess && p.major == 10) usable++;
+  }
+  return usable;
+}
+
+const char* ugu_b200_last_error(const ugu_b200_rasterizer* r) {
+  return r ? r->error.c_str() : g_last_error.c_str();
+}
+
+int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
+  if (out == nullptr) return Fail(nullptr, UGU_B200_E_INVALID, "out is NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return Fail(nullptr, UGU_B200_E_CUDA,
+                "no CUDA device available (%s); ugu_b200 has no CPU fallback",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  }
+  if (device < 0 || device >= n) return Fail(nullptr, UGU_B200_E_INVALID, "device %d out of range", device);
+  cudaDeviceProp prop;
+  CU_TRY(nullptr, cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return Fail(nullptr, UGU_B200_E_CUDA,
+                "device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major,
+                prop.minor);
+  CU_TRY(nullptr, cudaSetDevice(device));
+  g_num_sms = prop.multiProcessorCount;
+  ugu_b200_rasterizer* r = new ugu_b200_rasterizer;
+  r->device = device;
+  r->opt.diffuse_color = UGU_B200_COLOR_NONE;
+  r->opt.interp = UGU_B200_INTERP_BILINEAR;
+  r->opt.shading_normal = UGU_B200_NORMAL_VERTEX;
+  r->opt.diffuse_shading = UGU_B200_SHADING_NONE;
+  r->opt.backface_culling = 1;
+  r->opt.depth_scale = 1.0f;
+  r->opt.oren_nayar_sigma = 0.3f;
+  auto fail = [&](cudaError_t err, const char* what) {
+    int rc = Fail(nullptr, UGU_B200_E_CUDA, "%s failed: %s", what, cudaGetErrorString(err));
+    ugu_b200_rasterizer_destroy(r);
+    return rc;
+  };
+  if ((e = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking)) != cudaSuccess)
+    return fail(e, "cudaStreamCreate");
+  if ((e = cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking)) != cudaSuccess)
+    return fail(e, "cudaStreamCreate");
+  for (int i = 0; i < 2; i++) {
+    if ((e = cudaEventCreateWithFlags(&r->ev_render[i], cudaEventDisableTiming)) != cudaSuccess)
+      return fail(e, "cudaEventCreate");
+    if ((e = cudaEventCreateWithFlags(&r->ev_copied[i], cudaEventDisableTiming)) != cudaSuccess)
+      return fail(e, "cudaEventCreate");
+  }
+  r->ev_pool.resize(2 * kEventPool, nullptr);
+  r->ev_stage.resize(kEventPool, 0);
+  for (auto& ev : r->ev_pool)
+    if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e, "cudaEventCreate");
+  if ((e = cudaMalloc(&r->counters.p, 64)) != cudaSuccess) return fail(e, "cudaMalloc");
+  r->counters.bytes = 64;
+  if ((e = cudaMemset(r->counters.p, 0, 64)) != cudaSuccess) return fail(e, "cudaMemset");
+  if ((e = cudaHostAlloc((void**)&r->counters_host, 64, cudaHostAllocDefault)) != cudaSuccess)
+    return fail(e, "cudaHostAlloc");
+  memset(r->counters_host, 0, 64);
+  *out = r;
+  return UGU_B200_OK;
+}
+
+void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
+  if (!r) return;
+  cudaSetDevice(r->device);
+  if (r->stream) cudaStreamSynchronize(r->stream);
+  if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
+  FreeMesh(r);
+  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters};
+  for (DevBuf* b : bufs) FreeBuf(b);
+  for (int i = 0; i < 2; i++) {
+    FreeBuf(&r->out_color[i]);
+    FreeBuf(&r->out_depth[i]);
+    FreeBuf(&r->out_normal[i]);
+    FreeBuf(&r->out_mask[i]);
+    FreeBuf(&r->out_fid[i]);
+    if (r->ev_render[i]) cudaEventDestroy(r->ev_render[i]);
+    if (r->ev_copied[i]) cudaEventDestroy(r->ev_copied[i]);
+  }
+  for (auto ev : r->ev_pool)
+    if (ev) cudaEventDestroy(ev);
+  for (auto ev : r->chunk_events) cudaEventDestroy(ev);
+  if (r->staging) cudaFreeHost(r->staging);
+  if (r->counters_host) cudaFreeHost(r->counters_host);
+  if (r->stream) cudaStreamDestroy(r->stream);
+  if (r->copy_stream) cudaStreamDestroy(r->copy_stream);
+  delete r;
+}
+
+int ugu_b200_rasterizer_set_option(ugu_b200_rasterizer* r, const ugu_b200_option* opt) {
+  if (!r || !opt) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  r->opt = *opt;
+  return UGU_B200_OK;
+}
+
+int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_desc* d) {
+  if (!r || !d) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  CU_TRY(r, cudaSetDevice(r->device));
+  CU_TRY(r, cudaStreamSynchronize(r->stream));
+  FreeMesh(r);
+  const int V = d->num_vertices, F = d->num_faces;
+  if (V < 0 || F < 0 || d->num_normals < 0 || d->num_colors < 0 || d->num_face_normals < 0 ||
+      d->num_uv < 0 || d->num_materials < 0)
+    return Fail(r, UGU_B200_E_INVALID, "negative element count");
+  if ((unsigned long long)F >= (1ull << (64 - kQueueJobBits)))
+    return Fail(r, UGU_B200_E_INVALID, "more than %llu faces are not supported",
+                (1ull << (64 - kQueueJobBits)) - 1);
+  if ((V > 0 && !d->vertices) || (F > 0 && !d->vertex_indices))
+    return Fail(r, UGU_B200_E_INVALID, "vertices / vertex_indices are NULL");
+  if (F > 0 && !IndicesInRange(d->vertex_indices, (size_t)F * 3, V))
+    return Fail(r, UGU_B200_E_INVALID, "vertex_indices reference a vertex outside [0, %d)", V);
+  if (d->num_face_normals > 0 && d->num_face_normals < F)
+    return Fail(r, UGU_B200_E_INVALID, "face_normals has %d entries for %d faces", d->num_face_normals, F);
+  if (d->num_colors > 0 && d->num_colors < V)
+    return Fail(r, UGU_B200_E_INVALID, "vertex_colors has %d entries for %d vertices", d->num_colors, V);
+  if (d->normal_indices && F > 0 && !IndicesInRange(d->normal_indices, (size_t)F * 3, d->num_normals))
+    return Fail(r, UGU_B200_E_INVALID, "normal_indices reference a normal outside [0, %d)", d->num_normals);
+  if (d->uv_indices && F > 0 && !IndicesInRange(d->uv_indices, (size_t)F * 3, d->num_uv))
+    return Fail(r, UGU_B200_E_INVALID, "uv_indices reference a uv outside [0, %d)", d->num_uv);
+  if (d->material_ids && F > 0 && d->num_materials > 0 &&
+      !IndicesInRange(d->material_ids, (size_t)F, d->num_materials))
+    return Fail(r, UGU_B200_E_INVALID, "material_ids reference a material outside [0, %d)", d->num_materials);
+
+  MeshDev m{};
+  m.V = V;
+  m.F = F;
+  m.num_normals = d->num_normals;
+  m.num_colors = d->num_colors;
+  m.num_face_normals = d->num_face_normals > 0 ? F : 0;
+  m.num_uv = d->num_uv;
+  m.num_materials = d->num_materials;
+  cudaStream_t st = r->stream;
+  int rc;
+
+  // staging area on the device for the AoS host arrays (freed at the end)
+  std::vector<void*> temps;
+  auto upload = [&](const void* host, size_t bytes, void** dev) -> int {
+    CU_TRY(r, cudaMalloc(dev, std::max<size_t>(bytes, 16)));
+    temps.push_back(*dev);
+    CU_TRY(r, cudaMemcpyAsync(*dev, host, bytes, cudaMemcpyHostToDevice, st));
+    return UGU_B200_OK;
+  };
+  auto cleanup = [&](int code) {
+    cudaStreamSynchronize(st);
+    for (void* p : temps) cudaFree(p);
+    if (code != UGU_B200_OK) FreeMesh(r);
+    return code;
+  };
+#define UP_TRY(expr)                   \
+  do {                                 \
+    if ((rc = (expr))) return cleanup(rc); \
+  } while (0)
+
+  float *px = nullptr, *py = nullptr, *pz = nullptr;
+  // planes padded to a multiple of 4 so the float4 loads of vertex_kernel stay in bounds
+  const size_t Vpad = ((size_t)V + 3) & ~size_t(3);
+  UP_TRY(MeshAlloc(r, &px, Vpad));
+  UP_TRY(MeshAlloc(r, &py, Vpad));
+  UP_TRY(MeshAlloc(r, &pz, Vpad));
+  if (V > 0) {
+    void* t;
+    UP_TRY(upload(d->vertices, (size_t)V * 12, &t));
+    repack_vec3_to_planes<<<Blocks(V, 256), 256, 0, st>>>((const float*)t, V, px, py, pz);
+    r->stats.kernel_launches++;
+  }
+  m.pos_x = px; m.pos_y = py; m.pos_z = pz;
+
+  int *i0 = nullptr, *i1 = nullptr, *i2 = nullptr;
+  UP_TRY(MeshAlloc(r, &i0, F));
+  UP_TRY(MeshAlloc(r, &i1, F));
+  UP_TRY(MeshAlloc(r, &i2, F));
+  if (F > 0) {
+    void* t;
+    UP_TRY(upload(d->vertex_indices, (size_t)F * 12, &t));
+    repack_ivec3_to_planes<<<Blocks(F, 256), 256, 0, st>>>((const int*)t, F, i0, i1, i2);
+    r->stats.kernel_launches++;
+  }
+  m.idx0 = i0; m.idx1 = i1; m.idx2 = i2;
+
+  if (m.num_face_normals > 0) {
+    float *fx = nullptr, *fy = nullptr, *fz = nullptr;
+    UP_TRY(MeshAlloc(r, &fx, F));
+    UP_TRY(MeshAlloc(r, &fy, F));
+    UP_TRY(MeshAlloc(r, &fz, F));
+    void* t;
+    UP_TRY(upload(d->face_normals, (size_t)F * 12, &t));
+    repack_vec3_to_planes<<<Blocks(F, 256), 256, 0, st>>>((const float*)t, F, fx, fy, fz);
+    r->stats.kernel_launches++;
+    m.fn_x = fx; m.fn_y = fy; m.fn_z = fz;
+  }
+  if (d->num_normals > 0 && d->normals) {
+    float4* n4 = nullptr;
+    UP_TRY(MeshAlloc(r, &n4, d->num_normals));
+    void* t;
+    UP_TRY(upload(d->normals, (size_t)d->num_normals * 12, &t));
+    repack_vec3_to_float4<<<Blocks(d->num_normals, 256), 256, 0, st>>>((const float*)t, d->num_normals, n4);
+    r->stats.kernel_launches++;
+    m.nrm4 = n4;
+  } else {
+    m.num_normals = 0;
+  }
+  if (d->num_colors > 0 && d->vertex_colors) {
+    float4* c4 = nullptr;
+    UP_TRY(MeshAlloc(r, &c4, d->num_colors));
+    void* t;
+    UP_TRY(upload(d->vertex_colors, (size_t)d->num_colors * 12, &t));
+    repack_vec3_to_float4<<<Blocks(d->num_colors, 256), 256, 0, st>>>((const float*)t, d->num_colors, c4);
+    r->stats.kernel_launches++;
+    m.col4 = c4;
+  } else {
+    m.num_colors = 0;
+  }
+  if (d->normal_indices && F > 0) {
+    int4* n = nullptr;
+    UP_TRY(MeshAlloc(r, &n, F));
+    void* t;
+    UP_TRY(upload(d->normal_indices, (size_t)F * 12, &t));
+    repack_ivec3_to_int4<<<Blocks(F, 256), 256, 0, st>>>((const int*)t, F, n);
+    r->stats.kernel_launches++;
+    m.nidx = n;
+    r->has_nidx = true;
+  }
+  if (d->uv_indices && F > 0) {
+    int4* n = nullptr;
+    UP_TRY(MeshAlloc(r, &n, F));
+    void* t;
+    UP_TRY(upload(d->uv_indices, (size_t)F * 12, &t));
+    repack_ivec3_to_int4<<<Blocks(F, 256), 256, 0, st>>>((const int*)t, F, n);
+    r->stats.kernel_launches++;
+    m.uvidx = n;
+    r->has_uvidx = true;
+  }
+  if (d->num_uv > 0 && d->uv) {
+    float2* u = nullptr;
+    UP_TRY(MeshAlloc(r, &u, d->num_uv));
+    if ((rc = [&]() -> int {
+          CU_TRY(r, cudaMemcpyAsync(u, d->uv, (size_t)d->num_uv * 8, cudaMemcpyHostToDevice, st));
+          return UGU_B200_OK;
+        }()))
+      return cleanup(rc);
+    m.uv2 = u;
+  } else {
+    m.num_uv = 0;
+  }
+  if (d->material_ids && F > 0) {
+    int* ids = nullptr;
+    UP_TRY(MeshAlloc(r, &ids, F));
+    if ((rc = [&]() -> int {
+          CU_TRY(r, cudaMemcpyAsync(ids, d->material_ids, (size_t)F * 4, cudaMemcpyHostToDevice, st));
+          return UGU_B200_OK;
+        }()))
+      return cleanup(rc);
+    m.material_ids = ids;
+    r->has_matids = true;
+  }
+  r->tex_present.assign(d->num_materials, false);
+  if (d->num_materials > 0) {
+    std::vector<const uchar4*> tex_ptrs(d->num_materials, nullptr);
+    std::vector<int2> tex_sizes(d->num_materials, make_int2(0, 0));
+    for (int i = 0; i < d->num_materials; i++) {
+      const bool present = d->tex_data && d->tex_data[i] && d->tex_w[i] > 0 && d->tex_h[i] > 0;
+      r->tex_present[i] = present;
+      if (!present) continue;
+      const size_t n = (size_t)d->tex_w[i] * d->tex_h[i];
+      uchar4* t4 = nullptr;
+      UP_TRY(MeshAlloc(r, &t4, n));
+      void* t;
+      UP_TRY(upload(d->tex_data[i], n * 3, &t));
+      repack_rgb_to_rgba<<<Blocks(n, 256), 256, 0, st>>>((const uint8_t*)t, n, t4);
+      r->stats.kernel_launches++;
+      tex_ptrs[i] = t4;
+      tex_sizes[i] = make_int2(d->tex_w[i], d->tex_h[i]);
+    }
+    const uchar4** dev_ptrs = nullptr;
+    int2* dev_sizes = nullptr;
+    UP_TRY(MeshAlloc(r, &dev_ptrs, d->num_materials));
+    UP_TRY(MeshAlloc(r, &dev_sizes, d->num_materials));
+    if ((rc = [&]() -> int {
+          CU_TRY(r, cudaMemcpyAsync(dev_ptrs, tex_ptrs.data(), sizeof(void*) * d->num_materials,
+                                    cudaMemcpyHostToDevice, st));
+          CU_TRY(r, cudaMemcpyAsync(dev_sizes, tex_sizes.data(), sizeof(int2) * d->num_materials,
+                                    cudaMemcpyHostToDevice, st));
+          CU_TRY(r, cudaStreamSynchronize(st));  // tex_ptrs / tex_sizes are stack-owned
+          return UGU_B200_OK;
+        }()))
+      return cleanup(rc);
+    m.tex = dev_ptrs;
+    m.tex_size = dev_sizes;
+  }
+#undef UP_TRY
+  if ((rc = [&]() -> int {
+        CU_TRY(r, cudaGetLastError());
+        CU_TRY(r, cudaStreamSynchronize(st));
+        return UGU_B200_OK;
+      }()))
+    return cleanup(rc);
+  // per-view scratch that depends on the mesh size
+  if ((rc = Grow(r, &r->proj, std::max<size_t>(Vpad, 4) * sizeof(float4)))) return cleanup(rc);
+  if ((rc = Grow(r, &r->q_face, std::max<size_t>(F, 1) * 4))) return cleanup(rc);
+  if ((rc = Grow(r, &r->q_job, std::max<size_t>(F, 1) * 8))) return cleanup(rc);
+  r->mesh = m;
+  r->mesh_ready = true;
+  return cleanup(UGU_B200_OK);
+}
+
+int ugu_b200_rasterizer_render_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                      const ugu_b200_outputs* dev_out, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  int rc = Validate(r, cam, dev_out);
+  if (rc) return rc;
+  const uintptr_t align = (uintptr_t)dev_out->color | (uintptr_t)dev_out->depth |
+                          (uintptr_t)dev_out->normal | (uintptr_t)dev_out->mask |
+                          (uintptr_t)dev_out->face_id;
+  if (align & 15u) return Fail(r, UGU_B200_E_INVALID, "device outputs must be 16-byte aligned");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  return RenderView(r, cam, dev_out, st);
+}
+
+int ugu_b200_rasterizer_render(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                               const ugu_b200_outputs* host_out) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  int rc = Validate(r, cam, host_out);
+  if (rc) return rc;
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t P = (size_t)cam->width * cam->height;
+  ugu_b200_outputs dout;
+  if ((rc = EnsureInternalOutputs(r, 0, host_out, P, &dout))) return rc;
+  if ((rc = RenderView(r, cam, &dout, r->stream))) return rc;
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+                            r->stream));
+  std::vector<CopySeg> segs;
+  CollectSegs(host_out, &dout, P, 0, &segs);
+  if ((rc = CopyOut(r, segs, r->stream))) return rc;
+  SnapshotCounters(r);
+  return UGU_B200_OK;
+}
+
+int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
+                                     const ugu_b200_camera* cams, const ugu_b200_outputs* out,
+                                     int32_t outputs_on_device, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (num_views <= 0 || !cams) return Fail(r, UGU_B200_E_INVALID, "no views");
+  int rc;
+  for (int i = 0; i < num_views; i++) {
+    if ((rc = Validate(r, &cams[i], out))) return rc;
+    if (cams[i].width != cams[0].width || cams[i].height != cams[0].height)
+      return Fail(r, UGU_B200_E_INVALID, "all views of a batch must share one image size");
+  }
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t P = (size_t)cams[0].width * cams[0].height;
+  if (outputs_on_device) {
+    if ((P % 16) != 0) {
+      // per-view offsets keep every pointer 16-byte aligned only when P*1 (mask) is a multiple of 16
+      if (out->mask || out->color)
+        return Fail(r, UGU_B200_E_INVALID,
+                    "device batch with color/mask needs W*H to be a multiple of 16");
+    }
+    cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+    for (int i = 0; i < num_views; i++) {
+      ugu_b200_outputs o;
+      o.color = out->color ? out->color + (size_t)i * P * 3 : nullptr;
+      o.depth = out->depth ? out->depth + (size_t)i * P : nullptr;
+      o.normal = out->normal ? out->normal + (size_t)i * P * 3 : nullptr;
+      o.mask = out->mask ? out->mask + (size_t)i * P : nullptr;
+      o.face_id = out->face_id ? out->face_id + (size_t)i * P : nullptr;
+      const uintptr_t align = (uintptr_t)o.color | (uintptr_t)o.depth | (uintptr_t)o.normal |
+                              (uintptr_t)o.mask | (uintptr_t)o.face_id;
+      if (align & 15u) return Fail(r, UGU_B200_E_INVALID, "device outputs must be 16-byte aligned");
+      if ((rc = RenderView(r, &cams[i], &o, st))) return rc;
+    }
+    return UGU_B200_OK;
+  }
+  // Host destinations.  Pinned: render view i into output set i%2 on the compute stream while the
+  // copy stream drains view i-1 by DMA.  Pageable: staged, one view at a time.
+  bool all_pinned = true;
+  {
+    std::vector<CopySeg> probe;
+    ugu_b200_outputs none{};
+    CollectSegs(out, &none, P, 0, &probe);
+    for (const CopySeg& s : probe) all_pinned = all_pinned && IsPinnedHost(s.dst);
+  }
+  for (int i = 0; i < num_views; i++) {
+    const int set = all_pinned ? (i & 1) : 0;
+    ugu_b200_outputs dout;
+    if ((rc = EnsureInternalOutputs(r, set, out, P, &dout))) return rc;
+    if (all_pinned) {
+      if (r->copied_pending[set]) CU_TRY(r, cudaStreamWaitEvent(r->stream, r->ev_copied[set], 0));
+      if ((rc = RenderView(r, &cams[i], &dout, r->stream))) return rc;
+      CU_TRY(r, cudaEventRecord(r->ev_render[set], r->stream));
+      CU_TRY(r, cudaStreamWaitEvent(r->copy_stream, r->ev_render[set], 0));
+      std::vector<CopySeg> segs;
+      CollectSegs(out, &dout, P, (size_t)i, &segs);
+      for (const CopySeg& s : segs) {
+        r->stats.d2h_bytes += s.bytes;
+        CU_TRY(r, cudaMemcpyAsync(s.dst, s.src, s.bytes, cudaMemcpyDeviceToHost, r->copy_stream));
+      }
+      CU_TRY(r, cudaEventRecord(r->ev_copied[set], r->copy_stream));
+      r->copied_pending[set] = true;
+    } else {
+      if ((rc = RenderView(r, &cams[i], &dout, r->stream))) return rc;
+      std::vector<CopySeg> segs;
+      CollectSegs(out, &dout, P, (size_t)i, &segs);
+      if ((rc = CopyOut(r, segs, r->stream))) return rc;
+    }
+  }
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+                            r->stream));
+  CU_TRY(r, cudaStreamSynchronize(r->stream));
+  CU_TRY(r, cudaStreamSynchronize(r->copy_stream));
+  r->copied_pending[0] = r->copied_pending[1] = false;
+  SnapshotCounters(r);
+  return UGU_B200_OK;
+}
+
+int ugu_b200_rasterizer_sync(ugu_b200_rasterizer* r) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  CU_TRY(r, cudaSetDevice(r->device));
+  CU_TRY(r, cudaStreamSynchronize(r->stream));
+  CU_TRY(r, cudaStreamSynchronize(r->copy_stream));
+  return UGU_B200_OK;
+}
+
+int ugu_b200_depth_to_u16(const float* depth, uint16_t* depth_w, size_t count) {
+  if (!depth || !depth_w) return Fail(nullptr, UGU_B200_E_INVALID, "NULL argument");
+  // ConvertTo(f_depth, depth) with scale 1 (image_proc.h:453-460): static_cast<uint16_t>(float),
+  // compiled on x86-64 as cvttss2si + low 16 bits.
+  for (size_t i = 0; i < count; i++) {
+    const float f = depth[i];
+    int32_t v = (f > -2147483904.0f && f < 2147483648.0f) ? (int32_t)f : INT32_MIN;
+    depth_w[i] = (uint16_t)(uint32_t)v;
+  }
+  return UGU_B200_OK;
+}
+
+int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  CU_TRY(r, cudaSetDevice(r->device));
+  int rc = DrainEvents(r);
+  if (rc) return rc;
+  r->profiling = enable != 0;
+  r->stage_mask = stage_mask;
+  return UGU_B200_OK;
+}
+
+int ugu_b200_rasterizer_get_stats(ugu_b200_rasterizer* r, ugu_b200_stats* out) {
+  if (!r || !out) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  CU_TRY(r, cudaSetDevice(r->device));
+  int rc = DrainEvents(r);
+  if (rc) return rc;
+  *out = r->stats;
+  return UGU_B200_OK;
+}
+
+int ugu_b200_rasterizer_reset_stats(ugu_b200_rasterizer* r) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  CU_TRY(r, cudaSetDevice(r->device));
+  int rc = DrainEvents(r);
+  if (rc) return rc;
+  r->stats = ugu_b200_stats{};
+  return UGU_B200_OK;
+}
+
+void* ugu_b200_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, std::max<size_t>(bytes, 1), cudaHostAllocPortable) != cudaSuccess) {
+    Fail(nullptr, UGU_B200_E_NOMEM, "cudaHostAlloc(%zu) failed: %s", bytes,
+         cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  return p;
+}
+
+void ugu_b200_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"

@@ -1,0 +1,685 @@
+// Hand-written sm_100a kernels of the B200-native mesh rasterizer.
+//
+// Every float expression is evaluated with single round-to-nearest IEEE operations in the
+// association order of the compiled reference (SURVEY.md §8a "verified float op-order"), so the file
+// MUST be compiled with --fmad=false and without -use_fast_math (see ugu_b200/build.py).  The
+// visibility test is a 64-bit atomicMin on (float_bits(z) << 32 | face_id), which is
+// order-isomorphic to the reference's sequential `z < d` rule with its lowest-face-index tie-break
+// (src/renderer/cpu/rasterizer.cc:228-237) for every fragment with z >= FLT_MIN.
+//
+// Data layout in HBM (built once by upload, ugu_b200/csrc/raster_api.cu):
+//   pos_x/pos_y/pos_z   V floats each (SoA planes, float4-vectorised coalesced loads)
+//   idx0/idx1/idx2      F int32 each (SoA planes)
+//   fn_x/fn_y/fn_z      F floats each (face normals, SoA planes)
+//   nrm4 / col4         float4 per normal / per vertex colour (one LDG.128 per gather)
+//   nidx / uvidx        int4 per face (3 indices + pad) — one LDG.128 per winning fragment
+//   uv2                 float2 per uv
+//   tex (per material)  uchar4 RGBA8 texels, linear index = y * w + x like Image3b::at
+//   proj                float4 per vertex (image x, image y, camera z, 0), rewritten every view
+//   vis                 uint64 per pixel, the packed (z, face) visibility buffer; EMPTY = ~0
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ugu_b200 {
+
+constexpr unsigned long long kVisEmpty = 0xFFFFFFFFFFFFFFFFull;
+constexpr int kSmallMaxSamples = 16;  // bbox with <= this many pixel samples: rasterised in-thread
+constexpr int kJobW = 8;              // large-triangle tile job: 8 x 4 pixels = one warp
+constexpr int kJobH = 4;
+constexpr int kQueueJobBits = 38;     // packed queue counter: [63:38] entries, [37:0] tile jobs
+constexpr unsigned long long kQueueJobMask = (1ull << kQueueJobBits) - 1ull;
+constexpr int kJobsPerChunk = 16;     // tile jobs a warp claims at a time in the binned kernel
+
+struct ViewParams {
+  int W, H;
+  float fx, fy, cx, cy;
+  float wm1, hm1;  // (float)(W - 1), (float)(H - 1)
+  float w2c_R[9];
+  float w2c_t[3];
+  float c2w_R[9];
+};
+
+struct MeshDev {
+  int V, F;
+  int num_normals, num_colors, num_face_normals, num_uv, num_materials;
+  const float* pos_x;
+  const float* pos_y;
+  const float* pos_z;
+  const int* idx0;
+  const int* idx1;
+  const int* idx2;
+  const float* fn_x;
+  const float* fn_y;
+  const float* fn_z;
+  const float4* nrm4;
+  const float4* col4;
+  const int4* nidx;
+  const int4* uvidx;
+  const float2* uv2;
+  const int* material_ids;
+  const uchar4* const* tex;  // device array of per-material texel pointers
+  const int2* tex_size;      // (w, h) per material
+};
+
+struct FrameDev {
+  float4* proj;                  // V
+  float* ray_dx;                 // W: ((float)x - cx) / fx
+  float* ray_dy;                 // H: ((float)y - cy) / fy
+  unsigned long long* vis;       // W*H
+  unsigned long long* counters;  // [0] packed large queue counter, [1] hazard fragments, [2] chunk cursor
+  int* q_face;                   // F
+  unsigned long long* q_job;     // F : first tile job of each queued triangle
+};
+
+struct ShadeParams {
+  int diffuse_color, interp, shading_normal, diffuse_shading, backface_culling;
+  float on_A, on_B;
+  uint8_t* color;
+  float* depth;
+  float* normal;
+  uint8_t* mask;
+  int* face_id;
+};
+
+// ---------------------------------------------------------------------------------------------
+// Exact-order float helpers (Eigen fixed-size reduction order: a0*b0 + (a1*b1 + a2*b2)).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float dot3(float a0, float a1, float a2, float b0, float b1, float b2) {
+  return a0 * b0 + (a1 * b1 + a2 * b2);
+}
+
+struct Tri {
+  float v0x, v0y, v0z, v1x, v1y, v1z, v2x, v2y, v2z;
+  float e0x, e0y;  // v2 - v1
+  float e1x, e1y;  // v0 - v2
+  float e2x, e2y;  // v1 - v0
+  float area;
+};
+
+__device__ __forceinline__ void tri_setup(Tri& t, const float4& a, const float4& b, const float4& c) {
+  t.v0x = a.x; t.v0y = a.y; t.v0z = a.z;
+  t.v1x = b.x; t.v1y = b.y; t.v1z = b.z;
+  t.v2x = c.x; t.v2y = c.y; t.v2z = c.z;
+  t.e0x = c.x - b.x; t.e0y = c.y - b.y;
+  t.e1x = a.x - c.x; t.e1y = a.y - c.y;
+  t.e2x = b.x - a.x; t.e2y = b.y - a.y;
+  // EdgeFunction(v0, v1, v2) = (v2.x - v0.x)*(v1.y - v0.y) - (v2.y - v0.y)*(v1.x - v0.x)
+  t.area = (c.x - a.x) * t.e2y - (c.y - a.y) * t.e2x;
+}
+
+// EdgeFunction(a, b, p) with (b - a) precomputed: (p.x - a.x)*(b.y - a.y) - (p.y - a.y)*(b.x - a.x)
+__device__ __forceinline__ void tri_edges(const Tri& t, float px, float py, float& w0, float& w1,
+                                          float& w2) {
+  w0 = (px - t.v1x) * t.e0y - (py - t.v1y) * t.e0x;
+  w1 = (px - t.v2x) * t.e1y - (py - t.v2y) * t.e1x;
+  w2 = (px - t.v0x) * t.e2y - (py - t.v0y) * t.e2x;
+}
+
+// PinholeCamera::ray_w (camera.h:438-448): normalised camera ray rotated to world.
+__device__ __forceinline__ void ray_world(const ViewParams& vp, float d0, float d1, float& r0,
+                                          float& r1, float& r2) {
+  float c0 = d0, c1 = d1, c2 = 1.0f;
+  const float n2 = d0 * d0 + (d1 * d1 + 1.0f);  // d2*d2 == 1.0f exactly
+  if (n2 > 0.0f) {
+    const float s = sqrtf(n2);
+    c0 = d0 / s;
+    c1 = d1 / s;
+    c2 = 1.0f / s;
+  }
+  r0 = dot3(vp.c2w_R[0], vp.c2w_R[1], vp.c2w_R[2], c0, c1, c2);
+  r1 = dot3(vp.c2w_R[3], vp.c2w_R[4], vp.c2w_R[5], c0, c1, c2);
+  r2 = dot3(vp.c2w_R[6], vp.c2w_R[7], vp.c2w_R[8], c0, c1, c2);
+}
+
+// rasterizer.cc:208-224 — perspective-correct depth and weights of a covered sample.
+__device__ __forceinline__ float tri_depth(const Tri& t, float& w0, float& w1, float& w2) {
+  w0 = w0 / t.area;
+  w1 = w1 / t.area;
+  w2 = w2 / t.area;
+  w0 = w0 / t.v0z;
+  w1 = w1 / t.v1z;
+  w2 = w2 / t.v2z;
+  const float z = 1.0f / ((w0 + w1) + w2);
+  w0 = w0 * z;
+  w1 = w1 * z;
+  w2 = w2 * z;
+  return z;
+}
+
+// One pixel sample of one triangle (rasterizer.cc:196-237 minus the store): coverage with the
+// per-pixel facing rule, then depth.  Returns true when covered.
+__device__ __forceinline__ bool sample_triangle(const Tri& t, const ViewParams& vp, bool has_fn,
+                                                float fnx, float fny, float fnz, int x, int y,
+                                                const float* __restrict__ ray_dx,
+                                                const float* __restrict__ ray_dy, float& z,
+                                                float& w0, float& w1, float& w2, bool& backface) {
+  tri_edges(t, (float)x, (float)y, w0, w1, w2);
+  const bool pos = (w0 >= 0.0f) && (w1 >= 0.0f) && (w2 >= 0.0f);
+  const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
+  if (!pos && !neg) return false;
+  backface = false;
+  if (has_fn) {
+    float r0, r1, r2;
+    ray_world(vp, __ldg(ray_dx + x), __ldg(ray_dy + y), r0, r1, r2);
+    backface = dot3(fnx, fny, fnz, r0, r1, r2) > 0.0f;
+  }
+  if (backface ? !neg : !pos) return false;
+  z = tri_depth(t, w0, w1, w2);
+  return true;
+}
+
+__device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis, size_t pix,
+                                           float z, int face, unsigned long long* hazard) {
+  // Fragments with z < FLT_MIN (zero, negative, denormal) or NaN make the reference's sequential
+  // rule order dependent (rasterizer.cc:229, `d < FLT_MIN || z < d`); count them so the host can
+  // report the view as off-contract instead of silently diverging.
+  if (!(z >= 1.17549435e-38f)) {
+    atomicAdd(hazard, 1ull);
+    return;
+  }
+  const unsigned long long key =
+      ((unsigned long long)__float_as_uint(z) << 32) | (unsigned long long)(unsigned int)face;
+  // Early read: most occluded fragments never issue the atomic.
+  if (key < vis[pix]) atomicMin(vis + pix, key);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: vertex transform + projection (rasterizer.cc:125-136, camera.h:380-387) and the per-view ray
+// numerator tables.  4 vertices per thread, float4 SoA loads, float4 AoS stores.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 project_vertex(const ViewParams& vp, float x, float y, float z) {
+  float px = dot3(vp.w2c_R[0], vp.w2c_R[1], vp.w2c_R[2], x, y, z);
+  float py = dot3(vp.w2c_R[3], vp.w2c_R[4], vp.w2c_R[5], x, y, z);
+  float pz = dot3(vp.w2c_R[6], vp.w2c_R[7], vp.w2c_R[8], x, y, z);
+  px = px + vp.w2c_t[0];
+  py = py + vp.w2c_t[1];
+  pz = pz + vp.w2c_t[2];
+  float4 o;
+  o.x = vp.fx / pz * px + vp.cx;
+  o.y = vp.fy / pz * py + vp.cy;
+  o.z = pz;
+  o.w = 0.0f;
+  return o;
+}
+
+__global__ void __launch_bounds__(256) vertex_kernel(const ViewParams vp, const MeshDev m,
+                                                     const FrameDev fr) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  // ray tables: the first W + H threads
+  if (t < vp.W) fr.ray_dx[t] = ((float)t - vp.cx) / vp.fx;
+  else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
+
+  const int v = t * 4;
+  if (v + 3 < m.V) {
+    const float4 x = __ldg(reinterpret_cast<const float4*>(m.pos_x + v));
+    const float4 y = __ldg(reinterpret_cast<const float4*>(m.pos_y + v));
+    const float4 z = __ldg(reinterpret_cast<const float4*>(m.pos_z + v));
+    fr.proj[v + 0] = project_vertex(vp, x.x, y.x, z.x);
+    fr.proj[v + 1] = project_vertex(vp, x.y, y.y, z.y);
+    fr.proj[v + 2] = project_vertex(vp, x.z, y.z, z.z);
+    fr.proj[v + 3] = project_vertex(vp, x.w, y.w, z.w);
+  } else {
+    for (int k = v; k < m.V; k++)
+      fr.proj[k] = project_vertex(vp, __ldg(m.pos_x + k), __ldg(m.pos_y + k), __ldg(m.pos_z + k));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Triangle setup shared by K2 and K3: rejects + clamped bbox (rasterizer.cc:168-193).
+// Returns false when the triangle is rejected or has no pixel sample inside its bbox.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int sat_int(float f) {
+  // cvt.rzi.s32.f32 saturates and maps NaN to 0; the clamps below make the result identical to the
+  // reference for every on-contract (finite, in-int-range) coordinate.
+  return __float2int_rz(f);
+}
+
+__device__ __forceinline__ bool tri_bounds(const Tri& t, const ViewParams& vp, int& x0, int& y0,
+                                           int& x1, int& y1) {
+  if (t.v0z < 0.0f || t.v1z < 0.0f || t.v2z < 0.0f) return false;
+  const float xmin = fminf(fminf(t.v0x, t.v1x), t.v2x);
+  const float ymin = fminf(fminf(t.v0y, t.v1y), t.v2y);
+  const float xmax = fmaxf(fmaxf(t.v0x, t.v1x), t.v2x);
+  const float ymax = fmaxf(fmaxf(t.v0y, t.v1y), t.v2y);
+  if (xmin > vp.wm1 || xmax < 0.0f || ymin > vp.hm1 || ymax < 0.0f) return false;
+  x0 = max(0, sat_int(ceilf(xmin)));
+  x1 = min(vp.W - 1, sat_int(floorf(xmax)));
+  y0 = max(0, sat_int(ceilf(ymin)));
+  y1 = min(vp.H - 1, sat_int(floorf(ymax)));
+  if (fabsf(t.area) < 1.17549435e-38f) return false;
+  return x1 >= x0 && y1 >= y0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: one thread per face.  Gathers the three projected vertices, applies the reference's rejects,
+// rasterises triangles whose clamped bbox holds <= kSmallMaxSamples samples directly (the
+// micro-triangle regime of configs 2/4/5), and appends the others to the large-triangle queue with
+// a warp-level prefix sum over a packed (entries, tile jobs) counter — one atomicAdd per warp.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) raster_kernel(const ViewParams vp, const MeshDev m,
+                                                     const FrameDev fr) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31u;
+  unsigned long long my = 0ull;  // packed (1 entry, njobs) when this face goes to the queue
+  if (f < m.F) {
+    const int i0 = __ldg(m.idx0 + f), i1 = __ldg(m.idx1 + f), i2 = __ldg(m.idx2 + f);
+    const float4 a = __ldg(fr.proj + i0);
+    const float4 b = __ldg(fr.proj + i1);
+    const float4 c = __ldg(fr.proj + i2);
+    Tri t;
+    tri_setup(t, a, b, c);
+    int x0, y0, x1, y1;
+    if (tri_bounds(t, vp, x0, y0, x1, y1)) {
+      const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
+      if ((long long)nx * ny <= kSmallMaxSamples) {
+        const bool has_fn = m.num_face_normals > 0;
+        float fnx = 0.f, fny = 0.f, fnz = 0.f;
+        if (has_fn) {
+          fnx = __ldg(m.fn_x + f);
+          fny = __ldg(m.fn_y + f);
+          fnz = __ldg(m.fn_z + f);
+        }
+        for (int y = y0; y <= y1; ++y) {
+          for (int x = x0; x <= x1; ++x) {
+            float z, w0, w1, w2;
+            bool bf;
+            if (sample_triangle(t, vp, has_fn, fnx, fny, fnz, x, y, fr.ray_dx, fr.ray_dy, z, w0,
+                                w1, w2, bf)) {
+              vis_update(fr.vis, (size_t)y * vp.W + x, z, f, fr.counters + 1);
+            }
+          }
+        }
+      } else {
+        const unsigned long long njobs = (unsigned long long)((nx + kJobW - 1) / kJobW) *
+                                         (unsigned long long)((ny + kJobH - 1) / kJobH);
+        my = (1ull << kQueueJobBits) | njobs;
+      }
+    }
+  }
+  // warp-level inclusive prefix sum of the packed counter
+  unsigned long long incl = my;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (unsigned)d) incl += o;
+  }
+  const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
+  if (total != 0ull) {
+    unsigned long long base = 0ull;
+    if (lane == 31u) base = atomicAdd(fr.counters, total);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    if (my != 0ull) {
+      const unsigned long long excl = base + incl - my;
+      const unsigned slot = (unsigned)(excl >> kQueueJobBits);
+      fr.q_face[slot] = f;
+      fr.q_job[slot] = excl & kQueueJobMask;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3: large triangles.  The queue orders triangles by their first tile job, so the global job
+// space [0, T) is load-balanced regardless of triangle size: each warp claims chunks of
+// kJobsPerChunk jobs, finds the owning queue entry with a warp-cooperative 32-ary search, then
+// walks entries; a job is an 8x4 pixel block of the triangle's bbox, one lane per pixel.
+// Persistent grid (multiple of the SM count); exits at once when the queue is empty.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const MeshDev m,
+                                                     const FrameDev fr) {
+  const unsigned long long packed = fr.counters[0];
+  const unsigned long long T = packed & kQueueJobMask;
+  const unsigned n = (unsigned)(packed >> kQueueJobBits);
+  if (T == 0ull) return;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+  const unsigned long long gw = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const unsigned long long nchunks = (T + kJobsPerChunk - 1) / kJobsPerChunk;
+  const bool has_fn = m.num_face_normals > 0;
+  const int lx = (int)(lane & (kJobW - 1)), ly = (int)(lane >> 3);
+
+  for (unsigned long long chunk = gw; chunk < nchunks; chunk += nwarps) {
+    const unsigned long long jb = chunk * kJobsPerChunk;
+    const unsigned long long je = (jb + kJobsPerChunk < T) ? jb + kJobsPerChunk : T;
+    // 32-ary search: largest e with q_job[e] <= jb (q_job[0] == 0).
+    unsigned lo = 0, hi = n;
+    while (hi - lo > 1u) {
+      const unsigned span = hi - lo;
+      const unsigned step = (span + 31u) / 32u;
+      const unsigned idx = lo + lane * step;
+      const bool pred = (idx < hi) && (__ldg(fr.q_job + idx) <= jb);
+      const unsigned bal = __ballot_sync(0xffffffffu, pred);
+      const unsigned cnt = (unsigned)__popc(bal);  // >= 1: lane 0 probes lo
+      const unsigned nlo = lo + (cnt - 1u) * step;
+      const unsigned nhi = lo + cnt * step;
+      lo = nlo;
+      hi = (nhi < hi) ? nhi : hi;
+    }
+    unsigned e = lo;
+    unsigned long long j = jb;
+    while (j < je) {
+      const int f = __ldg(fr.q_face + e);
+      const unsigned long long js = __ldg(fr.q_job + e);
+      const unsigned long long jn = (e + 1u < n) ? __ldg(fr.q_job + e + 1u) : T;
+      const unsigned long long jend = (jn < je) ? jn : je;
+      const int i0 = __ldg(m.idx0 + f), i1 = __ldg(m.idx1 + f), i2 = __ldg(m.idx2 + f);
+      Tri t;
+      tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
+      int x0, y0, x1, y1;
+      tri_bounds(t, vp, x0, y0, x1, y1);  // queued triangles always pass
+      float fnx = 0.f, fny = 0.f, fnz = 0.f;
+      if (has_fn) {
+        fnx = __ldg(m.fn_x + f);
+        fny = __ldg(m.fn_y + f);
+        fnz = __ldg(m.fn_z + f);
+      }
+      const unsigned ntx = (unsigned)((x1 - x0 + kJobW) / kJobW);
+      for (unsigned long long jj = j; jj < jend; ++jj) {
+        const unsigned local = (unsigned)(jj - js);
+        const unsigned ty = local / ntx, tx = local - ty * ntx;
+        const int x = x0 + (int)tx * kJobW + lx;
+        const int y = y0 + (int)ty * kJobH + ly;
+        if (x <= x1 && y <= y1) {
+          float z, w0, w1, w2;
+          bool bf;
+          if (sample_triangle(t, vp, has_fn, fnx, fny, fnz, x, y, fr.ray_dx, fr.ray_dy, z, w0, w1,
+                              w2, bf)) {
+            vis_update(fr.vis, (size_t)y * vp.W + x, z, f, fr.counters + 1);
+          }
+        }
+      }
+      j = jend;
+      ++e;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4: resolve + attributes + shading + packing (rasterizer.cc:244-301, pixel_shader.h:222-422),
+// fused with the clear of every requested output (util_private.cc:72-87) and with the reset of the
+// visibility buffer and queue counters for the next view.  4 consecutive pixels per thread so every
+// store is a 32/128-bit vector store.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned f2u8(float f) {
+  // static_cast<unsigned char>(float) as the x86-64 reference compiles it: cvttss2si, low byte;
+  // out-of-int-range and NaN give 0x80000000 -> 0.
+  if (!(f > -2147483904.0f && f < 2147483648.0f)) return 0u;
+  return (unsigned)__float2int_rz(f) & 0xFFu;
+}
+
+__device__ __forceinline__ float3 fetch_texel(const uchar4* __restrict__ tex, int w, int h, int x,
+                                              int y) {
+  const long long idx = (long long)y * w + x;  // linear, like Image3b::at without bounds checks
+  if (idx < 0 || idx >= (long long)w * h) return make_float3(0.f, 0.f, 0.f);
+  const uchar4 t = __ldg(tex + idx);
+  return make_float3((float)t.x, (float)t.y, (float)t.z);
+}
+
+struct PixelOut {
+  unsigned color;  // r | g << 8 | b << 16
+  float depth;
+  float nx, ny, nz;
+  unsigned mask;
+  int face_id;
+};
+
+__device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDev& m,
+                                              const FrameDev& fr, const ShadeParams& sp,
+                                              unsigned long long key, int x, int y, PixelOut& o) {
+  o.color = 0u;
+  o.depth = 0.0f;
+  o.nx = o.ny = o.nz = 0.0f;
+  o.mask = 0u;
+  o.face_id = -1;
+  if (key == kVisEmpty) return;
+  const int fid = (int)(unsigned)(key & 0xFFFFFFFFull);
+  const float z = __uint_as_float((unsigned)(key >> 32));
+
+  const bool need_color = sp.color != nullptr;
+  const bool need_normal = sp.normal != nullptr;
+  const bool has_fn = m.num_face_normals > 0;
+  const bool shade = need_color && sp.diffuse_shading != 0;
+  const bool need_ray = (has_fn && sp.backface_culling) || shade;
+
+  float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+  if (need_ray) ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
+  float fnx = 0.f, fny = 0.f, fnz = 0.f;
+  if (has_fn && (sp.backface_culling || sp.shading_normal == 0)) {
+    fnx = __ldg(m.fn_x + fid);
+    fny = __ldg(m.fn_y + fid);
+    fnz = __ldg(m.fn_z + fid);
+  }
+  if (sp.backface_culling && has_fn) {
+    // the winner's backface flag (rasterizer.cc:200,235) recomputed bit-identically
+    if (dot3(fnx, fny, fnz, r0, r1, r2) > 0.0f) return;  // depth = 0, face_id = -1
+  }
+  o.depth = z;
+  o.face_id = fid;
+  if (fid <= 0) return;  // sic: face 0 is never shaded (rasterizer.cc:254)
+  o.mask = 255u;
+
+  const bool need_weights =
+      (sp.shading_normal == 1 && (need_normal || shade)) || (need_color && sp.diffuse_color != 0);
+  float w0 = 0.f, w1 = 0.f, w2 = 0.f;
+  int i0 = 0, i1 = 0, i2 = 0;
+  if (need_weights) {
+    i0 = __ldg(m.idx0 + fid);
+    i1 = __ldg(m.idx1 + fid);
+    i2 = __ldg(m.idx2 + fid);
+    Tri t;
+    tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
+    tri_edges(t, (float)x, (float)y, w0, w1, w2);
+    (void)tri_depth(t, w0, w1, w2);
+  }
+
+  // shading normal (rasterizer.cc:268-279)
+  float nwx = 0.f, nwy = 0.f, nwz = 0.f;
+  if (need_normal || shade) {
+    if (sp.shading_normal == 0) {
+      nwx = fnx; nwy = fny; nwz = fnz;
+    } else if (sp.shading_normal == 1) {
+      const int4 ni = __ldg(m.nidx + fid);
+      const float4 n0 = __ldg(m.nrm4 + ni.x);
+      const float4 n1 = __ldg(m.nrm4 + ni.y);
+      const float4 n2 = __ldg(m.nrm4 + ni.z);
+      nwx = (w0 * n0.x + w1 * n1.x) + w2 * n2.x;
+      nwy = (w0 * n0.y + w1 * n1.y) + w2 * n2.y;
+      nwz = (w0 * n0.z + w1 * n1.z) + w2 * n2.z;
+    }
+  }
+  if (need_normal) {  // rasterizer.cc:281-289
+    o.nx = dot3(vp.w2c_R[0], vp.w2c_R[1], vp.w2c_R[2], nwx, nwy, nwz);
+    o.ny = dot3(vp.w2c_R[3], vp.w2c_R[4], vp.w2c_R[5], nwx, nwy, nwz);
+    o.nz = dot3(vp.w2c_R[6], vp.w2c_R[7], vp.w2c_R[8], nwx, nwy, nwz);
+  }
+  if (!need_color) return;
+
+  unsigned cr = 255u, cg = 255u, cb = 255u;  // DiffuseDefaultColorizer
+  const float u = w1, v = w2;
+  if (sp.diffuse_color == 2) {  // DiffuseVertexColorColorizer (pixel_shader.h:234-256)
+    const float4 c0 = __ldg(m.col4 + i0);
+    const float4 c1 = __ldg(m.col4 + i1);
+    const float4 c2 = __ldg(m.col4 + i2);
+    const float k0 = 1.0f - u - v;
+    cr = f2u8((k0 * c0.x + u * c1.x) + v * c2.x);
+    cg = f2u8((k0 * c0.y + u * c1.y) + v * c2.y);
+    cb = f2u8((k0 * c0.z + u * c1.z) + v * c2.z);
+  } else if (sp.diffuse_color == 1) {  // texture colourizers (pixel_shader.h:260-359)
+    const int4 ui = __ldg(m.uvidx + fid);
+    const float2 t0 = __ldg(m.uv2 + ui.x);
+    const float2 t1 = __ldg(m.uv2 + ui.y);
+    const float2 t2 = __ldg(m.uv2 + ui.z);
+    const int mat = __ldg(m.material_ids + fid);
+    const uchar4* tex = m.tex[mat];
+    const int2 ts = m.tex_size[mat];
+    const float k0 = 1.0f - u - v;
+    const float iu = (k0 * t0.x + u * t1.x) + v * t2.x;
+    const float iv = (k0 * t0.y + u * t1.y) + v * t2.y;
+    const float tx = iu * (float)(ts.x - 1);
+    const float ty = (1.0f - iv) * (float)(ts.y - 1);
+    if (sp.interp == 0) {
+      const float3 c = fetch_texel(tex, ts.x, ts.y, sat_int(roundf(tx)), sat_int(roundf(ty)));
+      cr = f2u8(c.x); cg = f2u8(c.y); cb = f2u8(c.z);
+    } else {
+      const int xm = sat_int(floorf(tx)), ym = sat_int(floorf(ty));
+      const float lu = tx - (float)xm, lv = ty - (float)ym;
+      const float3 a = fetch_texel(tex, ts.x, ts.y, xm, ym);
+      const float3 b = fetch_texel(tex, ts.x, ts.y, xm + 1, ym);
+      const float3 c = fetch_texel(tex, ts.x, ts.y, xm, ym + 1);
+      const float3 d = fetch_texel(tex, ts.x, ts.y, xm + 1, ym + 1);
+      const float k00 = (1.0f - lu) * (1.0f - lv), k10 = lu * (1.0f - lv);
+      const float k01 = (1.0f - lu) * lv, k11 = lu * lv;
+      cr = f2u8(((k00 * a.x + k10 * b.x) + k01 * c.x) + k11 * d.x);
+      cg = f2u8(((k00 * a.y + k10 * b.y) + k01 * c.y) + k11 * d.y);
+      cb = f2u8(((k00 * a.z + k10 * b.z) + k01 * c.z) + k11 * d.z);
+    }
+  }
+  if (sp.diffuse_shading == 1) {  // DiffuseLambertianShader (pixel_shader.h:367-386); light == ray
+    float coeff = -dot3(r0, r1, r2, nwx, nwy, nwz);
+    if (coeff < 0.0f) coeff = 0.0f;
+    cr = f2u8(coeff * (float)cr);
+    cg = f2u8(coeff * (float)cg);
+    cb = f2u8(coeff * (float)cb);
+  } else if (sp.diffuse_shading == 2) {  // DiffuseOrenNayarShader (pixel_shader.h:390-422)
+    const float dot_light = -dot3(r0, r1, r2, nwx, nwy, nwz);
+    const float theta_i = acosf(dot_light);
+    const float theta_r = theta_i;  // dot_ray is the same expression: light_dir == ray_w
+    const float blx = (-nwx) * dot_light - r0;
+    const float bly = (-nwy) * dot_light - r1;
+    const float blz = (-nwz) * dot_light - r2;
+    const float phi = fmaxf(0.0f, dot3(blx, bly, blz, blx, bly, blz));
+    const float alpha = theta_i, beta = theta_r;
+    const float coeff =
+        fmaxf(0.0f, dot_light) * (sp.on_A + (sp.on_B * phi * sinf(alpha) * tanf(beta)));
+    cr = f2u8(coeff * (float)cr);
+    cg = f2u8(coeff * (float)cg);
+    cb = f2u8(coeff * (float)cb);
+  }
+  o.color = cr | (cg << 8) | (cb << 16);
+}
+
+__global__ void __launch_bounds__(256) resolve_kernel(const ViewParams vp, const MeshDev m,
+                                                      const FrameDev fr, const ShadeParams sp) {
+  const size_t P = (size_t)vp.W * (size_t)vp.H;
+  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // group of 4 pixels
+  if (g == 0) {
+    // the queue / hazard counters are consumed: snapshot them for the host (counters[4..5]) and
+    // reset them for the next view
+    fr.counters[4] = fr.counters[0];
+    fr.counters[5] = fr.counters[1];
+    fr.counters[0] = 0ull;
+    fr.counters[1] = 0ull;
+    fr.counters[2] = 0ull;
+  }
+  const size_t p0 = g * 4;
+  if (p0 >= P) return;
+  PixelOut o[4];
+  if (p0 + 3 < P) {
+    // 2 x 128-bit loads of the packed keys, then clear them for the next view
+    ulonglong2* vp2 = reinterpret_cast<ulonglong2*>(fr.vis + p0);
+    const ulonglong2 k01 = vp2[0], k23 = vp2[1];
+    vp2[0] = make_ulonglong2(kVisEmpty, kVisEmpty);
+    vp2[1] = make_ulonglong2(kVisEmpty, kVisEmpty);
+    const unsigned long long keys[4] = {k01.x, k01.y, k23.x, k23.y};
+    int y = (int)(p0 / (size_t)vp.W);
+    int x = (int)(p0 - (size_t)y * vp.W);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      resolve_pixel(vp, m, fr, sp, keys[k], x, y, o[k]);
+      if (++x == vp.W) { x = 0; ++y; }
+    }
+    if (sp.color) {
+      // 4 RGB pixels = 12 bytes = 3 aligned 32-bit words
+      const unsigned c0 = o[0].color, c1 = o[1].color, c2 = o[2].color, c3 = o[3].color;
+      unsigned* dst = reinterpret_cast<unsigned*>(sp.color + p0 * 3);
+      dst[0] = c0 | (c1 << 24);
+      dst[1] = (c1 >> 8) | (c2 << 16);
+      dst[2] = (c2 >> 16) | (c3 << 8);
+    }
+    if (sp.depth)
+      *reinterpret_cast<float4*>(sp.depth + p0) =
+          make_float4(o[0].depth, o[1].depth, o[2].depth, o[3].depth);
+    if (sp.normal) {
+      float4* dst = reinterpret_cast<float4*>(sp.normal + p0 * 3);
+      dst[0] = make_float4(o[0].nx, o[0].ny, o[0].nz, o[1].nx);
+      dst[1] = make_float4(o[1].ny, o[1].nz, o[2].nx, o[2].ny);
+      dst[2] = make_float4(o[2].nz, o[3].nx, o[3].ny, o[3].nz);
+    }
+    if (sp.mask)
+      *reinterpret_cast<unsigned*>(sp.mask + p0) =
+          o[0].mask | (o[1].mask << 8) | (o[2].mask << 16) | (o[3].mask << 24);
+    if (sp.face_id)
+      *reinterpret_cast<int4*>(sp.face_id + p0) =
+          make_int4(o[0].face_id, o[1].face_id, o[2].face_id, o[3].face_id);
+  } else {
+    for (size_t p = p0; p < P; p++) {
+      const unsigned long long key = fr.vis[p];
+      fr.vis[p] = kVisEmpty;
+      const int y = (int)(p / (size_t)vp.W);
+      const int x = (int)(p - (size_t)y * vp.W);
+      PixelOut q;
+      resolve_pixel(vp, m, fr, sp, key, x, y, q);
+      if (sp.color) {
+        sp.color[p * 3 + 0] = (uint8_t)(q.color & 0xFFu);
+        sp.color[p * 3 + 1] = (uint8_t)((q.color >> 8) & 0xFFu);
+        sp.color[p * 3 + 2] = (uint8_t)((q.color >> 16) & 0xFFu);
+      }
+      if (sp.depth) sp.depth[p] = q.depth;
+      if (sp.normal) {
+        sp.normal[p * 3 + 0] = q.nx;
+        sp.normal[p * 3 + 1] = q.ny;
+        sp.normal[p * 3 + 2] = q.nz;
+      }
+      if (sp.mask) sp.mask[p] = (uint8_t)q.mask;
+      if (sp.face_id) sp.face_id[p] = q.face_id;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Upload-time repack kernels (AoS host layout -> device SoA / padded vectors).  Run once per mesh.
+// ---------------------------------------------------------------------------------------------
+__global__ void repack_vec3_to_planes(const float* __restrict__ aos, int n, float* __restrict__ px,
+                                      float* __restrict__ py, float* __restrict__ pz) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    px[i] = aos[(size_t)i * 3 + 0];
+    py[i] = aos[(size_t)i * 3 + 1];
+    pz[i] = aos[(size_t)i * 3 + 2];
+  }
+}
+
+__global__ void repack_ivec3_to_planes(const int* __restrict__ aos, int n, int* __restrict__ p0,
+                                       int* __restrict__ p1, int* __restrict__ p2) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    p0[i] = aos[(size_t)i * 3 + 0];
+    p1[i] = aos[(size_t)i * 3 + 1];
+    p2[i] = aos[(size_t)i * 3 + 2];
+  }
+}
+
+__global__ void repack_vec3_to_float4(const float* __restrict__ aos, int n, float4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    out[i] = make_float4(aos[(size_t)i * 3 + 0], aos[(size_t)i * 3 + 1], aos[(size_t)i * 3 + 2], 0.f);
+}
+
+__global__ void repack_ivec3_to_int4(const int* __restrict__ aos, int n, int4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n)
+    out[i] = make_int4(aos[(size_t)i * 3 + 0], aos[(size_t)i * 3 + 1], aos[(size_t)i * 3 + 2], 0);
+}
+
+__global__ void repack_rgb_to_rgba(const uint8_t* __restrict__ rgb, size_t n, uchar4* __restrict__ out) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = make_uchar4(rgb[i * 3 + 0], rgb[i * 3 + 1], rgb[i * 3 + 2], 255);
+}
+
+__global__ void fill_u64(unsigned long long* __restrict__ p, size_t n, unsigned long long v) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+}  // namespace ugu_b200

@@ -1,0 +1,449 @@
+"""Host-side mirror of the reference renderer interface, on top of the C-ABI.
+
+Same names, argument meaning, call order and error behaviour as the reference's
+`ugu::RendererCpu` / `ugu::Rasterizer` (include/ugu/renderer/cpu/renderer.h:17-76,
+src/renderer/cpu/rasterizer.cc:73-103,309-348), `ugu::PinholeCamera`
+(include/ugu/camera.h:257-331,341-387) and the read side of `ugu::Mesh` (include/ugu/mesh.h:137-148):
+
+    renderer = Rasterizer(option)      # ctor(option)
+    renderer.set_mesh(mesh)            # set_mesh
+    renderer.PrepareMesh()             # PrepareMesh -> the one-time H2D upload
+    renderer.set_camera(camera)        # set_camera
+    camera.set_c2w(c2w)                # callers mutate the camera the renderer holds
+    ok = renderer.Render(color, depth, normal, mask, face_id)   # bool + logged message
+
+The C++ flavour of the same thing, compiled against the reference headers, is
+ugu_b200/cpp/rasterizer_cuda.{h,cc}.  Everything computed here runs in the CUDA library; without
+it (or without a B200) construction fails loudly — there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import enum
+import math
+import sys
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _native as N
+
+
+class DiffuseColor(enum.IntEnum):      # renderer/base.h:11-15
+    kNone = 0
+    kTexture = 1
+    kVertex = 2
+
+
+class ColorInterpolation(enum.IntEnum):  # common.h:50-53
+    kNn = 0
+    kBilinear = 1
+
+
+class ShadingNormal(enum.IntEnum):     # renderer/base.h:19-22
+    kFace = 0
+    kVertex = 1
+
+
+class DiffuseShading(enum.IntEnum):    # renderer/base.h:26-32
+    kNone = 0
+    kLambertian = 1
+    kOrenNayar = 2
+
+
+@dataclass
+class RendererCpuOption:
+    """renderer/cpu/renderer.h:17-38 (same defaults)."""
+    diffuse_color: DiffuseColor = DiffuseColor.kNone
+    interp: ColorInterpolation = ColorInterpolation.kBilinear
+    shading_normal: ShadingNormal = ShadingNormal.kVertex
+    diffuse_shading: DiffuseShading = DiffuseShading.kNone
+    depth_scale: float = 1.0
+    backface_culling: bool = True
+    oren_nayar_sigma: float = 0.3
+
+    def CopyTo(self, dst: "RendererCpuOption") -> None:
+        # renderer.h:30-37 — oren_nayar_sigma is NOT copied (stays at the destination's 0.3).
+        dst.diffuse_color = self.diffuse_color
+        dst.depth_scale = self.depth_scale
+        dst.interp = self.interp
+        dst.shading_normal = self.shading_normal
+        dst.diffuse_shading = self.diffuse_shading
+        dst.backface_culling = self.backface_culling
+
+
+def LOGE(msg: str) -> None:
+    """The reference reports failures with LOGE(...) + `return false` (util_private.cc:19-67)."""
+    sys.stderr.write("[ugu_b200 E] " + msg.rstrip("\n") + "\n")
+
+
+def LOGW(msg: str) -> None:
+    sys.stderr.write("[ugu_b200 W] " + msg.rstrip("\n") + "\n")
+
+
+@dataclass
+class Material:
+    """The part of ugu::ObjMaterial the renderer reads: diffuse_tex (Image3b, H x W x 3 u8)."""
+    diffuse_tex: Optional[np.ndarray] = None
+
+
+@dataclass
+class Mesh:
+    """Read side of ugu::Mesh (mesh.h:83-98,137-148): the same AoS arrays, as numpy."""
+    vertices: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.float32))
+    vertex_colors: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.float32))
+    vertex_indices: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.int32))
+    normals: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.float32))
+    face_normals: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.float32))
+    normal_indices: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.int32))
+    uv: np.ndarray = field(default_factory=lambda: np.zeros((0, 2), np.float32))
+    uv_indices: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.int32))
+    material_ids: np.ndarray = field(default_factory=lambda: np.zeros((0,), np.int32))
+    materials: List[Material] = field(default_factory=list)
+
+
+class PinholeCamera:
+    """ugu::PinholeCamera (camera.h:79-183): size, c2w pose (4x4 double), pixel-scale principal
+    point and focal length.  The float constants Render needs are derived by the C-ABI
+    (ugu_b200_camera_from_c2w) exactly when the renderer reads the camera."""
+
+    def __init__(self, width: int, height: int, c2w: Optional[np.ndarray] = None,
+                 principal_point: Optional[Sequence[float]] = None,
+                 focal_length: Optional[Sequence[float]] = None,
+                 fov_y_deg: Optional[float] = None):
+        self._width, self._height = int(width), int(height)
+        self.set_c2w(np.eye(4) if c2w is None else c2w)
+        if principal_point is None:  # camera.h:276-277
+            principal_point = (np.float32(self._width) * np.float32(0.5) - np.float32(0.5),
+                               np.float32(self._height) * np.float32(0.5) - np.float32(0.5))
+        self._pp = (np.float32(principal_point[0]), np.float32(principal_point[1]))
+        if focal_length is not None:
+            self._f = (np.float32(focal_length[0]), np.float32(focal_length[1]))
+        else:
+            self.set_fov_y(45.0 if fov_y_deg is None else fov_y_deg)
+
+    def width(self) -> int:
+        return self._width
+
+    def height(self) -> int:
+        return self._height
+
+    def c2w(self) -> np.ndarray:
+        return self._c2w
+
+    def set_size(self, width: int, height: int) -> None:
+        self._width, self._height = int(width), int(height)
+
+    def set_c2w(self, c2w: np.ndarray) -> None:
+        c2w = np.asarray(c2w, dtype=np.float64)
+        if c2w.shape != (4, 4):
+            raise ValueError("c2w must be 4x4")
+        self._c2w = np.ascontiguousarray(c2w)
+
+    def principal_point(self):
+        return self._pp
+
+    def focal_length(self):
+        return self._f
+
+    def set_principal_point(self, pp) -> None:
+        self._pp = (np.float32(pp[0]), np.float32(pp[1]))
+
+    def set_focal_length(self, f) -> None:
+        self._f = (np.float32(f[0]), np.float32(f[1]))
+
+    def set_fov_y(self, fov_y_deg: float) -> None:
+        # camera.h:372-378: height * 0.5f / static_cast<float>(std::tan(radians(fov) * 0.5))
+        rad = np.float32(np.float32(fov_y_deg) * np.float32(math.pi / 180.0))  # radians(float)
+        t = np.float32(math.tan(float(rad) * 0.5))
+        fy = np.float32(np.float32(self._height) * np.float32(0.5)) / t
+        self._f = (np.float32(fy), np.float32(fy))
+
+    def to_native(self) -> N.Camera:
+        cam = N.Camera()
+        c2w = (C.c_double * 16)(*self._c2w.reshape(-1))
+        rc = N.load().ugu_b200_camera_from_c2w(c2w, self._width, self._height, float(self._f[0]),
+                                               float(self._f[1]), float(self._pp[0]),
+                                               float(self._pp[1]), C.byref(cam))
+        if rc != N.OK:
+            raise ValueError("c2w is not invertible")
+        return cam
+
+
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """A numpy array over pinned host memory from the C-ABI (so Render's D2H is one DMA)."""
+    lib = N.load()
+    dtype = np.dtype(dtype)
+    nbytes = int(np.prod(shape)) * dtype.itemsize
+    ptr = lib.ugu_b200_host_alloc(max(nbytes, 1))
+    if not ptr:
+        raise MemoryError(N.last_error())
+    buf = (C.c_uint8 * max(nbytes, 1)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    class _Owner:
+        def __init__(self, p):
+            self.p = p
+
+        def __del__(self):
+            try:
+                lib.ugu_b200_host_free(self.p)
+            except Exception:
+                pass
+
+    _PINNED_OWNERS[ptr] = _Owner(ptr)
+    return arr
+
+
+_PINNED_OWNERS: dict = {}
+
+
+def free_pinned(arr: np.ndarray) -> None:
+    ptr = arr.ctypes.data
+    _PINNED_OWNERS.pop(ptr, None)
+
+
+class Image:
+    """Minimal ugu::Image<T> stand-in: `.data` is a contiguous numpy array (rows, cols[, ch]) that
+    Render (re)allocates only when the size differs, like ugu::Init (image.h:963-985)."""
+
+    dtype = np.uint8
+    channels = 1
+
+    def __init__(self, pinned: bool = True):
+        self.rows, self.cols = 0, 0
+        self.pinned = pinned
+        self.data = np.zeros((0, 0) if self.channels == 1 else (0, 0, self.channels), self.dtype)
+
+    def empty(self) -> bool:
+        return self.rows < 1 or self.cols < 1
+
+    def _init(self, width: int, height: int) -> None:
+        if self.cols != width or self.rows != height:
+            shape = (height, width) if self.channels == 1 else (height, width, self.channels)
+            if self.pinned and self.data.size:
+                free_pinned(self.data)
+            self.data = pinned_empty(shape, self.dtype) if self.pinned else np.empty(shape, self.dtype)
+            self.rows, self.cols = height, width
+
+
+class Image3b(Image):
+    dtype, channels = np.uint8, 3
+
+
+class Image1f(Image):
+    dtype, channels = np.float32, 1
+
+
+class Image3f(Image):
+    dtype, channels = np.float32, 3
+
+
+class Image1b(Image):
+    dtype, channels = np.uint8, 1
+
+
+class Image1i(Image):
+    dtype, channels = np.int32, 1
+
+
+class Image1w(Image):
+    dtype, channels = np.uint16, 1
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Rasterizer:
+    """The CUDA-backed drop-in for ugu::Rasterizer (rasterizer.h:14-53)."""
+
+    def __init__(self, option: Optional[RendererCpuOption] = None, device: int = 0):
+        self._lib = N.load()
+        self._h = C.c_void_p()
+        rc = self._lib.ugu_b200_rasterizer_create(int(device), C.byref(self._h))
+        if rc != N.OK:
+            raise RuntimeError(f"ugu_b200: cannot create the CUDA rasterizer: {N.last_error()}")
+        self._option = RendererCpuOption()
+        self._mesh: Optional[Mesh] = None
+        self._mesh_initialized = False
+        self._camera: Optional[PinholeCamera] = None
+        self._keep = None
+        if option is not None:
+            self.set_option(option)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self._lib.ugu_b200_rasterizer_destroy(h)
+            self._h = None
+
+    # -- RendererCpu interface -------------------------------------------------------------------
+    def set_option(self, option: RendererCpuOption) -> None:
+        option.CopyTo(self._option)  # rasterizer.cc:73-75
+
+    def set_mesh(self, mesh: Mesh) -> None:
+        self._mesh_initialized = False  # rasterizer.cc:78
+        self._mesh = mesh
+        if len(mesh.face_normals) == 0:
+            LOGW("face normal is empty. culling and shading may not work")
+        if len(mesh.normals) == 0:
+            LOGW("vertex normal is empty. shading may not work")
+
+    def PrepareMesh(self) -> bool:
+        if self._mesh is None:
+            LOGE("mesh has not been set")
+            return False
+        m = self._mesh
+        f32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1, w))
+        i32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.int32).reshape(-1, w))
+        v, n, c = f32(m.vertices, 3), f32(m.normals, 3), f32(m.vertex_colors, 3)
+        vi, ni, ui = i32(m.vertex_indices, 3), i32(m.normal_indices, 3), i32(m.uv_indices, 3)
+        fn, uv = f32(m.face_normals, 3), f32(m.uv, 2)
+        mid = np.ascontiguousarray(np.asarray(m.material_ids, np.int32).reshape(-1))
+        F = len(vi)
+        texs = [None if (t.diffuse_tex is None or t.diffuse_tex.size == 0)
+                else np.ascontiguousarray(t.diffuse_tex, np.uint8) for t in m.materials]
+        M = len(texs)
+        d = N.MeshDesc()
+        d.num_vertices, d.num_normals, d.num_colors = len(v), len(n), len(c)
+        d.num_faces, d.num_face_normals, d.num_uv, d.num_materials = F, len(fn), len(uv), M
+        d.vertices, d.normals, d.vertex_colors = _ptr(v), _ptr(n), _ptr(c)
+        d.vertex_indices = _ptr(vi)
+        d.normal_indices = _ptr(ni) if len(ni) == F and F > 0 else None
+        d.face_normals, d.uv = _ptr(fn), _ptr(uv)
+        d.uv_indices = _ptr(ui) if len(ui) == F and F > 0 else None
+        d.material_ids = _ptr(mid) if len(mid) == F and F > 0 else None
+        tex_ptrs = (C.c_void_p * max(M, 1))(*[None if t is None else t.ctypes.data for t in texs])
+        tex_w = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[1] for t in texs])
+        tex_h = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[0] for t in texs])
+        d.tex_data = C.cast(tex_ptrs, C.POINTER(C.c_void_p))
+        d.tex_w = C.cast(tex_w, C.POINTER(C.c_int32))
+        d.tex_h = C.cast(tex_h, C.POINTER(C.c_int32))
+        rc = self._lib.ugu_b200_rasterizer_upload_mesh(self._h, C.byref(d))
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        self._mesh_initialized = True
+        return True
+
+    def set_camera(self, camera: PinholeCamera) -> None:
+        self._camera = camera
+
+    def _native_option(self) -> N.Option:
+        o = self._option
+        return N.Option(int(o.diffuse_color), int(o.interp), int(o.shading_normal),
+                        int(o.diffuse_shading), 1 if o.backface_culling else 0,
+                        float(o.depth_scale), float(o.oren_nayar_sigma))
+
+    def Render(self, color: Optional[Image3b] = None, depth: Optional[Image1f] = None,
+               normal: Optional[Image3f] = None, mask: Optional[Image1b] = None,
+               face_id: Optional[Image1i] = None) -> bool:
+        if self._camera is None:
+            LOGE("camera has not been set")
+            return False
+        if not self._mesh_initialized:
+            LOGE("mesh has not been initialized")
+            return False
+        if not isinstance(self._camera, PinholeCamera):
+            LOGE("only PinholeCamera is supported by the CUDA rasterizer")
+            return False
+        opt = self._native_option()
+        self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+        cam = self._camera.to_native()
+        imgs = (color, depth, normal, mask, face_id)
+        if all(i is None for i in imgs):
+            LOGE("all arguments are nullptr. nothing to do")
+            return False
+        for im in imgs:  # ugu::Init: (re)allocate only when the size differs (image.h:970-985)
+            if im is not None:
+                im._init(cam.width, cam.height)
+        out = N.Outputs(*[None if im is None else im.data.ctypes.data for im in imgs])
+        rc = self._lib.ugu_b200_rasterizer_render(self._h, C.byref(cam), C.byref(out))
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        return True
+
+    def RenderColor(self, color: Image3b) -> bool:
+        return self.Render(color, None, None, None, None)
+
+    def RenderDepth(self, depth: Image1f) -> bool:
+        return self.Render(None, depth, None, None, None)
+
+    def RenderNormal(self, normal: Image3f) -> bool:
+        return self.Render(None, None, normal, None, None)
+
+    def RenderMask(self, mask: Image1b) -> bool:
+        return self.Render(None, None, None, mask, None)
+
+    def RenderFaceId(self, face_id: Image1i) -> bool:
+        return self.Render(None, None, None, None, face_id)
+
+    def RenderW(self, color: Optional[Image3b], depth: Optional[Image1w], normal: Optional[Image3f],
+                mask: Optional[Image1b], face_id: Optional[Image1i]) -> bool:
+        if depth is None:  # rasterizer.cc:331-334
+            LOGE("depth is nullptr")
+            return False
+        f_depth = Image1f()
+        ok = self.Render(color, f_depth, normal, mask, face_id)
+        if ok:
+            depth._init(f_depth.cols, f_depth.rows)
+            self._lib.ugu_b200_depth_to_u16(f_depth.data.ctypes.data, depth.data.ctypes.data,
+                                            f_depth.data.size)
+        return ok
+
+    def RenderDepthW(self, depth: Image1w) -> bool:
+        return self.RenderW(None, depth, None, None, None)
+
+    # -- device-resident / batch extensions (no reference counterpart) --------
+    def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
+                      face_id=None, stream: int = 0) -> None:
+        """Render into DEVICE buffers given as raw device pointers (ints), asynchronously on the
+        cudaStream_t `stream` (0 = the rasterizer's own stream)."""
+        opt = self._native_option()
+        self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+        cam = camera.to_native() if isinstance(camera, PinholeCamera) else camera
+        out = N.Outputs(color, depth, normal, mask, face_id)
+        rc = self._lib.ugu_b200_rasterizer_render_device(self._h, C.byref(cam), C.byref(out),
+                                                         C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
+    def render_batch(self, cameras: Sequence, color=None, depth=None, normal=None, mask=None,
+                     face_id=None, on_device: bool = False, stream: int = 0) -> None:
+        """Render len(cameras) views; view i lands at element offset i*W*H of each output.  Outputs
+        are raw pointers (ints): device pointers when on_device, else host pointers."""
+        opt = self._native_option()
+        self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+        n = len(cameras)
+        cams = (N.Camera * n)(*[c.to_native() if isinstance(c, PinholeCamera) else c for c in cameras])
+        out = N.Outputs(color, depth, normal, mask, face_id)
+        rc = self._lib.ugu_b200_rasterizer_render_batch(self._h, n, cams, C.byref(out),
+                                                        1 if on_device else 0, C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
+    def sync(self) -> None:
+        if self._lib.ugu_b200_rasterizer_sync(self._h) != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
+    def set_profiling(self, enable: bool, stages: Sequence[int] = (0, 1, 2, 3)) -> None:
+        mask = 0
+        for s in stages:
+            mask |= 1 << s
+        self._lib.ugu_b200_rasterizer_set_profiling(self._h, 1 if enable else 0, mask)
+
+    def stats(self) -> dict:
+        st = N.Stats()
+        if self._lib.ugu_b200_rasterizer_get_stats(self._h, C.byref(st)) != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+        d = {k: int(getattr(st, k)) for k in ("timed_views", "views", "kernel_launches", "h2d_bytes",
+                                              "d2h_bytes", "large_triangles", "tile_jobs",
+                                              "hazard_fragments")}
+        d["stage_ms"] = {N.STAGE_NAMES[i]: float(st.stage_ms[i]) for i in range(N.NUM_STAGES)}
+        return d
+
+    def reset_stats(self) -> None:
+        self._lib.ugu_b200_rasterizer_reset_stats(self._h)
