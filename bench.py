@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py — the headline benchmark of the rasterizer hot path (BASELINE.json metric).
+
+Workload (N = 1): BASELINE.json config 2 — synthetic 1 310 720-triangle subdivided icosphere with
+vertex colours, one pinhole view at 1920x1080 per step, all five outputs (colour + depth + normal +
+mask + face_id), back-face culling on.  A "step" is one Render of one view per GPU; the camera
+orbits the mesh so every step has a different pose (callers mutate the camera between frames,
+examples/ex09_renderer_realtime.cc:137-145).  With N > 1 the views shard across ranks with no
+data-path collective (weak scaling: one view per rank per step).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Prints ONE JSON line (see the keys at the end of main()).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parent
+for p in (str(REPO), str(REPO / "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+W, H = 1920, 1080
+ICO_LEVEL = 8
+N_POSES = 36
+L2_FLUSH_BYTES = 512 << 20
+WORKLOAD = "config2: icosphere L8 (V=655362, F=1310720) vertex colours, 1920x1080, 5 outputs"
+
+
+def measured_peak_gbs():
+    p = REPO / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def make_inputs(level=ICO_LEVEL):
+    from ugu_b200 import DiffuseColor, PinholeCamera, RendererCpuOption, meshgen
+    mesh = meshgen.icosphere(level)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex)
+    poses = meshgen.orbit_poses((0.0, 0.0, 0.0), 2.7, N_POSES)
+    cams = [PinholeCamera(W, H, p, fov_y_deg=45.0) for p in poses]
+    return mesh, opt, cams
+
+
+def algorithmic_bytes(mesh, P):
+    """Per-view and per-kernel ALGORITHMIC bytes (SURVEY.md §8d for the view)."""
+    V, F = len(mesh.vertices), len(mesh.vertex_indices)
+    Nn = len(mesh.normals)
+    out = P * (3 + 4 + 12 + 1 + 4)
+    view = 12 * V + 12 * F + 12 * F + (12 * Nn + 12 * F) + 12 * V + out
+    per_kernel = {
+        "vertex": 12 * V + 16 * V,                 # positions in, projected float4 out
+        "raster": 12 * F + 12 * F + 16 * V,        # indices + face normals + projected vertices once
+        "binned": 0,                               # empty queue at config 2
+        "resolve": 8 * P + 8 * P + out,            # visibility read + clear, outputs written once
+    }
+    return view, per_kernel
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons with NVML while the timed regions run."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def start(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+        return {"sm_mhz": (statistics.median(self.samples) if self.samples else None),
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def time_reference(mesh, opt, cams, steps, warmup, budget_s=None):
+    """The reference's own CPU implementation: oracle/_ref (compiled reference) when it travelled,
+    else the plain-C oracle port.  One step = camera->set_c2w + Render, as callers do."""
+    import oracle
+    if oracle.ref_available():
+        kind = "reference"
+        runner = oracle.OracleRef(mesh)
+        render = lambda cam: runner.render(cam, opt)
+        cores = os.cpu_count() or 1
+        note = ("unmodified ugu::Rasterizer; its Render loop is single-threaded, only the per-pose "
+                "ray-table rebuild (camera.h:482-513) uses OpenMP on all cores")
+    else:
+        kind = "port"
+        runner = oracle.OraclePort(mesh)
+        render = lambda cam: runner.render(cam.to_native(), opt)
+        cores = 1
+        note = "plain-C scalar restatement (oracle/raster_oracle.c), one thread"
+    for i in range(warmup):
+        render(cams[i % len(cams)])
+    t0 = time.perf_counter()
+    done = 0
+    for i in range(steps):
+        render(cams[(warmup + i) % len(cams)])
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return dict(kind=kind, cores=cores, steps=done, seconds=dt, note=note)
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    mesh, opt, cams = make_inputs()
+    steps = max(1, args.steps)
+    r = time_reference(mesh, opt, cams, steps, max(0, min(args.warmup, 2)), budget_s=240.0)
+    P = W * H
+    F = len(mesh.vertex_indices)
+    ms = r["seconds"] / r["steps"] * 1e3
+    value = P * r["steps"] / r["seconds"] / 1e6
+    line = {
+        "impl": "reference", "metric": "Mpix/s (color+depth+normal+mask+face_id)", "value": value,
+        "unit": "Mpix/s", "mtri_per_s": F * r["steps"] / r["seconds"] / 1e6, "n_gpus": args.gpus,
+        "steps": r["steps"], "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "views_per_step": 1, "culling": True},
+        "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": r["cores"], "kind": r["kind"],
+                         "sample": f"{r['steps']} full views of the workload (set_c2w + Render each)",
+                         "note": r["note"]},
+        "e2e": {"value": value, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ugu_b200", choices=["ugu_b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: ugu_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    warmup = max(3, args.warmup)
+    K = max(1, args.steps)
+
+    from ugu_b200 import Image1b, Image1f, Image1i, Image3b, Image3f, Rasterizer
+    from ugu_b200 import _native as N
+
+    mesh, opt, cams = make_inputs()
+    P = W * H
+    V, F = len(mesh.vertices), len(mesh.vertex_indices)
+    r = Rasterizer(opt, device=local)
+    r.set_mesh(mesh)
+    assert r.PrepareMesh()
+    natives = [c.to_native() for c in cams]
+
+    dev = dict(color=torch.empty(P * 3, dtype=torch.uint8, device="cuda"),
+               depth=torch.empty(P, dtype=torch.float32, device="cuda"),
+               normal=torch.empty(P * 3, dtype=torch.float32, device="cuda"),
+               mask=torch.empty(P, dtype=torch.uint8, device="cuda"),
+               face_id=torch.empty(P, dtype=torch.int32, device="cuda"))
+    ptrs = {k: v.data_ptr() for k, v in dev.items()}
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def device_step(i):
+        # each rank takes its own view of the step (views shard across ranks, no collective)
+        r.render_device(natives[(i * world + rank) % N_POSES], stream=stream, **ptrs)
+
+    # ---- device-resident loop: inputs already in HBM, outputs left in HBM ------------------------
+    for i in range(warmup):
+        flush.zero_()
+        device_step(i)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    r.reset_stats()
+    r.set_profiling(True, (0, 1, 2, 3))
+    ev0 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    barrier()
+    wall0 = time.perf_counter()
+    for i in range(K):
+        flush.zero_()          # L2 flush between timed iterations (outside the per-step events)
+        ev0[i].record()
+        device_step(warmup + i)
+        ev1[i].record()
+    barrier()
+    wall_dev = time.perf_counter() - wall0
+    dev_ms = sum(a.elapsed_time(b) for a, b in zip(ev0, ev1))
+    st = r.stats()
+    r.set_profiling(False, ())
+    launches = st["kernel_launches"]
+
+    # ---- end-to-end loop: the public Render call with HOST (pinned) images ------------------------
+    imgs = (Image3b(), Image1f(), Image3f(), Image1b(), Image1i())
+    r.set_camera(cams[0])
+    for i in range(min(warmup, 5)):
+        assert r.Render(*imgs)
+    barrier()
+    r.reset_stats()
+    e2e_t = 0.0
+    Ke = max(1, min(K, 200))
+    for i in range(Ke):
+        flush.zero_()
+        torch.cuda.synchronize()
+        cam = cams[((warmup + i) * world + rank) % N_POSES]
+        t0 = time.perf_counter()
+        r.set_camera(cam)         # the per-step input: the camera pose -> H2D as kernel constants
+        ok = r.Render(*imgs)      # validates, renders, D2H of all five outputs, returns when landed
+        e2e_t += time.perf_counter() - t0
+        assert ok
+    st_e = r.stats()
+    barrier()
+    clocks = sampler.stop()
+
+    # ---- max over ranks ---------------------------------------------------------------------------
+    t = torch.tensor([dev_ms, e2e_t * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms_max, e2e_ms_max = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        view_bytes, kbytes = algorithmic_bytes(mesh, P)
+        stage_ms = {k: v / max(1, st["timed_views"]) for k, v in st["stage_ms"].items()}
+        dom = max(stage_ms, key=lambda k: stage_ms[k])
+        achieved = kbytes[dom] / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
+        ms_per_step = dev_ms_max / K
+        value = world * P * K / (dev_ms_max * 1e-3) / 1e6
+        e2e_value = world * P * Ke / (e2e_ms_max * 1e-3) / 1e6
+        line = {
+            "metric": "Mpix/s (color+depth+normal+mask+face_id)", "value": value, "unit": "Mpix/s",
+            "mtri_per_s": world * F * K / (dev_ms_max * 1e-3) / 1e6,
+            "n_gpus": world, "steps": K, "warmup": warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "views_per_step_per_gpu": 1, "culling": True,
+                       "l2": f"flushed between timed iterations ({L2_FLUSH_BYTES >> 20} MiB write)",
+                       "timing": "sum of per-step CUDA-event pairs on the launching stream, max over ranks",
+                       "parallelism": f"views sharded over {world} GPU(s), no collective"},
+            "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": e2e_ms_max / Ke, "steps": Ke,
+                    "h2d_bytes_per_step": int(st_e["h2d_bytes"] // max(1, st_e["views"])),
+                    "d2h_bytes_per_step": int(st_e["d2h_bytes"] // max(1, st_e["views"])),
+                    "api": "ugu_b200.Rasterizer.Render -> ugu_b200_rasterizer_render, pinned host images"},
+            "gpu_launches": int(launches),
+            "stage_us": {k: round(v * 1e3, 2) for k, v in stage_ms.items()},
+            "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "algorithmic_bytes_per_launch": kbytes[dom], "peak_source": peak_src,
+                         "view": {"algorithmic_bytes": view_bytes,
+                                  "achieved": view_bytes / (ms_per_step * 1e-3) / 1e9,
+                                  "frac": view_bytes / (ms_per_step * 1e-3) / 1e9 / peak}},
+            "clocks": clocks,
+            "wall_s_device_loop": wall_dev,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cb = time_reference(mesh, opt, cams, steps=24, warmup=1, budget_s=20.0)
+            line["cpu_baseline"] = {
+                "value": P * cb["steps"] / cb["seconds"] / 1e6, "unit": "Mpix/s", "cores": cb["cores"],
+                "kind": cb["kind"], "ms_per_step": cb["seconds"] / cb["steps"] * 1e3,
+                "sample": f"{cb['steps']} full views of the same workload (set_c2w + Render each)",
+                "note": cb["note"]}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
