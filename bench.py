@@ -217,7 +217,13 @@ def main():
                face_id=torch.empty(P, dtype=torch.int32, device="cuda"))
     ptrs = {k: v.data_ptr() for k, v in dev.items()}
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
-    stream = torch.cuda.current_stream().cuda_stream
+    # A real (non-default) stream: the kernels, the L2 flush and the timing events must all be on
+    # ONE stream.  (Handle 0 would mean "the rasterizer's own stream" to the C-ABI, and torch events
+    # recorded on the default stream would then not bracket the kernels at all.)
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
 
     def barrier():
         torch.cuda.synchronize()
