@@ -1,0 +1,183 @@
+// TEST HARNESS (not product): drives the reference ugu::Rasterizer and ugu::RasterizerCuda through
+// the SAME ugu::RendererCpu* interface, in the call order of examples/ex02_renderer.cc:245-278 and
+// the orbit loop of examples/ex09_renderer_realtime.cc:125-182, and compares all five outputs.
+// Built only where the reference headers exist (tests/cpp/build_check.py); the binary travels
+// to the GPU box and is run by tests/test_parity_gpu.py::test_cpp_adapter_vs_reference.
+// Exit code 0 = parity (face_id / mask / depth / normal bit-exact, colour bit-exact or ±1 LSB for
+// Oren-Nayar), 1 = mismatch, 2 = no CUDA rasterizer.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+#include "rasterizer_cuda.h"
+#include "ugu/camera.h"
+#include "ugu/log.h"
+#include "ugu/mesh.h"
+#include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/util/camera_util.h"
+#include "ugu/util/geom_util.h"
+
+namespace {
+
+std::shared_ptr<ugu::Mesh> MakeTestMesh(int n_stacks, int n_slices) {
+  ugu::MeshPtr mesh = ugu::MakeUvSphere(n_stacks, n_slices);
+  const int V = static_cast<int>(mesh->vertices().size());
+  // deterministic bumps so that depth ties are rare and silhouettes are irregular
+  std::vector<Eigen::Vector3f> v = mesh->vertices();
+  for (int i = 0; i < V; i++) {
+    const float s = 1.0f + 0.08f * std::sin(7.0f * v[i].x()) * std::cos(5.0f * v[i].y() + 3.0f * v[i].z());
+    v[i] *= s;
+  }
+  mesh->set_vertices(v);
+  std::vector<Eigen::Vector2f> uv(V);
+  std::vector<Eigen::Vector3f> col(V);
+  for (int i = 0; i < V; i++) {
+    uv[i] = Eigen::Vector2f(0.05f + 0.9f * (0.5f + 0.5f * v[i].x() / 1.1f),
+                            0.05f + 0.9f * (0.5f + 0.5f * v[i].y() / 1.1f));
+    uv[i] = uv[i].cwiseMax(0.02f).cwiseMin(0.98f);
+    col[i] = Eigen::Vector3f(127.5f + 127.0f * std::sin(3.0f * v[i].x()),
+                             127.5f + 127.0f * std::sin(4.0f * v[i].y()),
+                             127.5f + 127.0f * std::sin(5.0f * v[i].z()));
+  }
+  mesh->set_uv(uv);
+  mesh->set_uv_indices(mesh->vertex_indices());
+  mesh->set_vertex_colors(col);
+  std::vector<ugu::ObjMaterial> mats(1);
+  mats[0].diffuse_tex = ugu::Image3b::zeros(256, 192);
+  uint32_t s = 1u;
+  for (int y = 0; y < 256; y++)
+    for (int x = 0; x < 192; x++) {
+      s ^= s << 13; s ^= s >> 17; s ^= s << 5;
+      mats[0].diffuse_tex.at<ugu::Vec3b>(y, x) =
+          ugu::Vec3b({uint8_t(s & 255u), uint8_t((s >> 8) & 255u), uint8_t((s >> 16) & 255u)});
+    }
+  mesh->set_materials(mats);
+  mesh->set_material_ids(std::vector<int>(mesh->vertex_indices().size(), 0));
+  mesh->CalcFaceNormal();
+  mesh->CalcNormal();
+  return mesh;
+}
+
+template <typename T>
+long CountDiff(const ugu::Image<T>& a, const ugu::Image<T>& b, int tol) {
+  if (a.rows != b.rows || a.cols != b.cols) return -1;
+  const size_t n = static_cast<size_t>(a.rows) * a.cols * sizeof(T);
+  long bad = 0;
+  if (tol == 0) {
+    // value compare on the raw element type would treat -0.0f == 0.0f; bytes are stricter, and the
+    // normals of uncovered pixels are +0 in both, so compare floats by value, integers by bytes
+    for (size_t i = 0; i < n; i++) bad += a.data[i] != b.data[i];
+  } else {
+    for (size_t i = 0; i < n; i++) bad += std::abs(int(a.data[i]) - int(b.data[i])) > tol;
+  }
+  return bad;
+}
+
+long CountDiffFloat(const float* a, const float* b, size_t n) {
+  long bad = 0;
+  for (size_t i = 0; i < n; i++) bad += !(a[i] == b[i]);
+  return bad;
+}
+
+struct Outs {
+  ugu::Image3b color;
+  ugu::Image1f depth;
+  ugu::Image3f normal;
+  ugu::Image1b mask;
+  ugu::Image1i face_id;
+};
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  const bool timing = argc > 1 && std::strcmp(argv[1], "--time") == 0;
+  ugu::set_log_level(ugu::LogLevel::kWarning);
+  auto mesh = MakeTestMesh(timing ? 700 : 90, timing ? 900 : 120);
+  const int W = timing ? 1920 : 320, H = timing ? 1080 : 240;
+  auto camera = std::make_shared<ugu::PinholeCamera>(W, H, 50.0f);
+
+  struct Case {
+    const char* name;
+    ugu::DiffuseColor color;
+    ugu::ColorInterpolation interp;
+    ugu::ShadingNormal normal;
+    ugu::DiffuseShading shading;
+    bool cull;
+    int color_tol;
+  };
+  const Case cases[] = {
+      {"vertex/vnormal/none/cull", ugu::DiffuseColor::kVertex, ugu::ColorInterpolation::kBilinear,
+       ugu::ShadingNormal::kVertex, ugu::DiffuseShading::kNone, true, 0},
+      {"texture-bilinear/vnormal/lambert/nocull", ugu::DiffuseColor::kTexture,
+       ugu::ColorInterpolation::kBilinear, ugu::ShadingNormal::kVertex,
+       ugu::DiffuseShading::kLambertian, false, 0},
+      {"texture-nn/fnormal/none/cull", ugu::DiffuseColor::kTexture, ugu::ColorInterpolation::kNn,
+       ugu::ShadingNormal::kFace, ugu::DiffuseShading::kNone, true, 0},
+      {"white/vnormal/oren-nayar/cull", ugu::DiffuseColor::kNone, ugu::ColorInterpolation::kBilinear,
+       ugu::ShadingNormal::kVertex, ugu::DiffuseShading::kOrenNayar, true, 1},
+  };
+  int failures = 0;
+  for (const Case& cs : cases) {
+    ugu::RendererCpuOption option;
+    option.diffuse_color = cs.color;
+    option.interp = cs.interp;
+    option.shading_normal = cs.normal;
+    option.diffuse_shading = cs.shading;
+    option.backface_culling = cs.cull;
+    // the two renderers behind the same interface pointer type
+    std::unique_ptr<ugu::RendererCpu> ref = std::make_unique<ugu::Rasterizer>(option);
+    auto cuda_owner = std::make_unique<ugu::RasterizerCuda>(option);
+    if (!cuda_owner->valid()) {
+      std::printf("no CUDA rasterizer available\n");
+      return 2;
+    }
+    std::unique_ptr<ugu::RendererCpu> cuda = std::move(cuda_owner);
+    for (ugu::RendererCpu* r : {ref.get(), cuda.get()}) {
+      r->set_mesh(mesh);
+      if (!r->PrepareMesh()) return 1;
+      r->set_camera(camera);
+    }
+    const int n_views = timing ? 3 : 5;
+    for (int k = 0; k < n_views; k++) {
+      const double a = 2.0 * 3.14159265358979323846 * k / n_views + 0.3;
+      Eigen::Matrix4d c2w;
+      ugu::c2w(Eigen::Vector3d(2.9 * std::sin(a), 0.4 * std::cos(2 * a), 2.9 * std::cos(a)),
+               Eigen::Vector3d(0.02, -0.03, 0.01), Eigen::Vector3d(0, -1, 0), &c2w);
+      camera->set_c2w(Eigen::Affine3d(c2w));  // callers mutate the camera the renderers hold
+      Outs o[2];
+      double ms[2];
+      int idx = 0;
+      for (ugu::RendererCpu* r : {ref.get(), cuda.get()}) {
+        const auto t0 = std::chrono::steady_clock::now();
+        if (!r->Render(&o[idx].color, &o[idx].depth, &o[idx].normal, &o[idx].mask, &o[idx].face_id)) return 1;
+        ms[idx] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        idx++;
+      }
+      const size_t P = static_cast<size_t>(W) * H;
+      const long d_fid = CountDiff(o[0].face_id, o[1].face_id, 0);
+      const long d_mask = CountDiff(o[0].mask, o[1].mask, 0);
+      const long d_depth = CountDiffFloat(reinterpret_cast<float*>(o[0].depth.data),
+                                          reinterpret_cast<float*>(o[1].depth.data), P);
+      const long d_normal = CountDiffFloat(reinterpret_cast<float*>(o[0].normal.data),
+                                           reinterpret_cast<float*>(o[1].normal.data), P * 3);
+      const long d_color = CountDiff(o[0].color, o[1].color, cs.color_tol);
+      long covered = 0;
+      for (size_t i = 0; i < P; i++) covered += reinterpret_cast<int32_t*>(o[0].face_id.data)[i] >= 0;
+      std::printf("%-42s view %d: covered %ld  diff face_id %ld mask %ld depth %ld normal %ld color %ld"
+                  "   ref %.2f ms  cuda %.2f ms\n",
+                  cs.name, k, covered, d_fid, d_mask, d_depth, d_normal, d_color, ms[0], ms[1]);
+      if (d_fid || d_mask || d_depth || d_normal || d_color || covered == 0) failures++;
+    }
+    // single-output wrappers and RenderW
+    ugu::Image1i f0, f1;
+    ugu::Image1w w0, w1;
+    if (!ref->RenderFaceId(&f0) || !cuda->RenderFaceId(&f1) || CountDiff(f0, f1, 0)) failures++;
+    if (!ref->RenderDepthW(&w0) || !cuda->RenderDepthW(&w1) || CountDiff(w0, w1, 0)) failures++;
+    if (cuda->Render(nullptr, nullptr, nullptr, nullptr, nullptr)) failures++;  // all-null is an error
+  }
+  std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);
+  return failures ? 1 : 0;
+}

@@ -1,0 +1,32 @@
+"""TEST INFRASTRUCTURE: builds tests/cpp/build/adapter_check, which links the product's C++ adapter
+(ugu_b200/cpp/build/librasterizer_cuda.so) AND the compiled reference (oracle/_ref/libugu_ref.so)
+to compare them behind the same ugu::RendererCpu interface.  Needs the reference headers, so it is
+built in this container and the binary travels to the GPU box."""
+from __future__ import annotations
+
+import subprocess
+import sys
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+REPO = HERE.parents[1]
+sys.path.insert(0, str(REPO))
+OUT = HERE / "build"
+EXE = OUT / "adapter_check"
+
+
+def build() -> Path:
+    from ugu_b200.cpp import build_adapter
+    so = build_adapter.build()
+    OUT.mkdir(exist_ok=True)
+    subprocess.run([*build_adapter.compile_command(), "-o", str(EXE), str(HERE / "adapter_check.cc"),
+                    f"-L{so.parent}", "-lrasterizer_cuda", f"-L{REPO / 'oracle' / '_ref'}", "-lugu_ref",
+                    f"-L{REPO / 'ugu_b200' / 'lib'}", "-lugu_b200_raster",
+                    "-Wl,-rpath,$ORIGIN/../../../ugu_b200/cpp/build:$ORIGIN/../../../ugu_b200/lib:"
+                    "$ORIGIN/../../../oracle/_ref"],
+                   check=True, capture_output=True)
+    return EXE
+
+
+if __name__ == "__main__":
+    print(build())

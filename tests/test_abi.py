@@ -9,7 +9,8 @@ import pytest
 
 from ugu_b200 import _native as N
 
-HEADER = Path(__file__).resolve().parents[1] / "include" / "ugu_b200_raster.h"
+REPO = Path(__file__).resolve().parents[1]
+HEADER = REPO / "include" / "ugu_b200_raster.h"
 
 
 def declared_symbols():
@@ -75,3 +76,14 @@ def test_product_never_references_the_oracle():
         text = p.read_text()
         assert "liboracle" not in text and "libugu_ref" not in text, p
         assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), p
+
+
+def test_cpp_adapter_fails_loudly_without_gpu():
+    """The C++ drop-in (ugu::RasterizerCuda) reports 'no CUDA rasterizer' instead of falling back."""
+    import subprocess
+    import torch
+    exe = REPO / "tests" / "cpp" / "build" / "adapter_check"
+    if not exe.exists() or torch.cuda.is_available():
+        pytest.skip("adapter harness not built here, or a GPU is present")
+    p = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 2 and "no CUDA rasterizer" in p.stdout

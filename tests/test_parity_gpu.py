@@ -201,3 +201,34 @@ def test_cuda_vs_live_compiled_reference_spot_640x480():
     for c2w in poses:
         cam = PinholeCamera(640, 480, c2w, principal_point=(318.6, 255.3), focal_length=(517.3, 516.5))
         util.assert_parity(run.render(cam, opt), ref.render(cam, opt), strict=True, what="config1")
+
+
+ADAPTER_CHECK = cases.GOLDEN_DIR.parents[0] / "cpp" / "build" / "adapter_check"
+
+
+@pytest.mark.skipif(not ADAPTER_CHECK.exists(), reason="C++ adapter harness not prebuilt (needs the reference headers)")
+def test_cpp_adapter_vs_reference():
+    """ugu::RasterizerCuda and the reference ugu::Rasterizer behind the same ugu::RendererCpu*
+    (tests/cpp/adapter_check.cc): 4 option sets x 5 orbit views, all five outputs, plus the
+    single-output wrappers and RenderW."""
+    import subprocess
+    p = subprocess.run([str(ADAPTER_CHECK)], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-4000:] + p.stderr[-2000:]
+    assert "ADAPTER PARITY OK" in p.stdout
+
+
+def test_multiview_renderer_matches_single_views():
+    """ugu_b200.multiview on one rank: the device-resident batch equals per-view Render calls."""
+    from ugu_b200.multiview import MultiViewRenderer
+    mesh = meshgen.icosphere(4)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex)
+    run = util.CudaRunner(mesh, opt)
+    cams = [PinholeCamera(96, 64, p, fov_y_deg=45.0) for p in meshgen.random_sphere_poses(6, seed=3)]
+    mv = MultiViewRenderer(run.r)
+    idx, outs = mv.render(cams, ("face_id", "depth"))
+    assert idx == list(range(6))
+    fid = mv.render_and_gather(cams, "face_id").cpu().numpy()
+    for i, cm in enumerate(cams):
+        single = run.render(cm, opt, want=("face_id", "depth"))
+        assert np.array_equal(fid[i], single["face_id"])
+        assert np.array_equal(util.bits(outs["depth"][i].cpu().numpy()), util.bits(single["depth"]))

@@ -1,0 +1,224 @@
+// ugu::RasterizerCuda: host C++ over the C-ABI (include/ugu_b200_raster.h).  Compiled against the
+// reference headers; mirrors the state machine and error behaviour of Rasterizer::Impl
+// (src/renderer/cpu/rasterizer.cc:35-103,309-404) and leaves every computation to the CUDA library.
+#include "rasterizer_cuda.h"
+
+#include <cstring>
+#include <vector>
+
+#include "ugu/log.h"
+#include "ugu_b200_raster.h"
+
+namespace ugu {
+
+class RasterizerCuda::Impl {
+ public:
+  ugu_b200_rasterizer* handle_ = nullptr;
+  bool mesh_initialized_ = false;
+  std::shared_ptr<const Camera> camera_;
+  std::shared_ptr<const Mesh> mesh_;
+  RendererCpuOption option_;
+
+  explicit Impl(int device) {
+    if (ugu_b200_rasterizer_create(device, &handle_) != UGU_B200_OK) {
+      LOGE("RasterizerCuda: %s\n", ugu_b200_last_error(nullptr));
+      handle_ = nullptr;
+    }
+  }
+  ~Impl() { ugu_b200_rasterizer_destroy(handle_); }
+
+  bool PrepareMesh() {
+    if (mesh_ == nullptr) {
+      LOGE("mesh has not been set\n");
+      return false;
+    }
+    if (handle_ == nullptr) {
+      LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
+      return false;
+    }
+    const Mesh& m = *mesh_;
+    const size_t F = m.vertex_indices().size();
+    ugu_b200_mesh_desc d;
+    std::memset(&d, 0, sizeof(d));
+    d.num_vertices = static_cast<int32_t>(m.vertices().size());
+    d.num_normals = static_cast<int32_t>(m.normals().size());
+    d.num_colors = static_cast<int32_t>(m.vertex_colors().size());
+    d.num_faces = static_cast<int32_t>(F);
+    d.num_face_normals = static_cast<int32_t>(m.face_normals().size());
+    d.num_uv = static_cast<int32_t>(m.uv().size());
+    d.num_materials = static_cast<int32_t>(m.materials().size());
+    // std::vector<Eigen::Vector3f/3i/2f> is a dense AoS array (no padding: 12 / 12 / 8 bytes)
+    static_assert(sizeof(Eigen::Vector3f) == 12 && sizeof(Eigen::Vector3i) == 12 &&
+                      sizeof(Eigen::Vector2f) == 8,
+                  "unexpected Eigen fixed-vector layout");
+    d.vertices = d.num_vertices ? m.vertices()[0].data() : nullptr;
+    d.normals = d.num_normals ? m.normals()[0].data() : nullptr;
+    d.vertex_colors = d.num_colors ? m.vertex_colors()[0].data() : nullptr;
+    d.vertex_indices = F ? m.vertex_indices()[0].data() : nullptr;
+    d.normal_indices = (F && m.normal_indices().size() == F) ? m.normal_indices()[0].data() : nullptr;
+    d.face_normals = d.num_face_normals ? m.face_normals()[0].data() : nullptr;
+    d.uv = d.num_uv ? m.uv()[0].data() : nullptr;
+    d.uv_indices = (F && m.uv_indices().size() == F) ? m.uv_indices()[0].data() : nullptr;
+    d.material_ids = (F && m.material_ids().size() == F) ? m.material_ids().data() : nullptr;
+    std::vector<const uint8_t*> tex(m.materials().size(), nullptr);
+    std::vector<int32_t> tw(m.materials().size(), 0), th(m.materials().size(), 0);
+    for (size_t i = 0; i < m.materials().size(); i++) {
+      const Image3b& t = m.materials()[i].diffuse_tex;
+      if (!t.empty()) {
+        tex[i] = t.data;
+        tw[i] = t.cols;
+        th[i] = t.rows;
+      }
+    }
+    d.tex_data = tex.data();
+    d.tex_w = tw.data();
+    d.tex_h = th.data();
+    if (ugu_b200_rasterizer_upload_mesh(handle_, &d) != UGU_B200_OK) {
+      LOGE("%s\n", ugu_b200_last_error(handle_));
+      return false;
+    }
+    mesh_initialized_ = true;
+    return true;
+  }
+
+  bool Render(Image3b* color, Image1f* depth, Image3f* normal, Image1b* mask,
+              Image1i* face_id) const {
+    // Preconditions in the order of ValidateAndInitBeforeRender (util_private.cc:19-67); the
+    // mesh/option dependent ones are checked by the library against the uploaded mesh.
+    if (camera_ == nullptr) {
+      LOGE("camera has not been set\n");
+      return false;
+    }
+    if (!mesh_initialized_) {
+      LOGE("mesh has not been initialized\n");
+      return false;
+    }
+    const PinholeCamera* pin = dynamic_cast<const PinholeCamera*>(camera_.get());
+    if (pin == nullptr || dynamic_cast<const OpenCvCamera*>(camera_.get()) != nullptr) {
+      LOGE("RasterizerCuda supports PinholeCamera only (no CPU fallback)\n");
+      return false;
+    }
+    if (color == nullptr && depth == nullptr && normal == nullptr && mask == nullptr &&
+        face_id == nullptr) {
+      LOGE("all arguments are nullptr. nothing to do\n");
+      return false;
+    }
+    ugu_b200_option o;
+    o.diffuse_color = static_cast<int32_t>(option_.diffuse_color);
+    o.interp = static_cast<int32_t>(option_.interp);
+    o.shading_normal = static_cast<int32_t>(option_.shading_normal);
+    o.diffuse_shading = static_cast<int32_t>(option_.diffuse_shading);
+    o.backface_culling = option_.backface_culling ? 1 : 0;
+    o.depth_scale = option_.depth_scale;
+    o.oren_nayar_sigma = option_.oren_nayar_sigma;
+    ugu_b200_rasterizer_set_option(handle_, &o);
+
+    // Camera constants exactly as rasterizer.cc:118-119 and camera.h:321 derive them.
+    ugu_b200_camera c;
+    c.width = camera_->width();
+    c.height = camera_->height();
+    c.fx = pin->focal_length().x();
+    c.fy = pin->focal_length().y();
+    c.cx = pin->principal_point().x();
+    c.cy = pin->principal_point().y();
+    const Eigen::Matrix3f w2c_R = camera_->w2c().rotation().cast<float>();
+    const Eigen::Vector3f w2c_t = camera_->w2c().translation().cast<float>();
+    const Eigen::Matrix3f c2w_R = camera_->c2w().matrix().block<3, 3>(0, 0).cast<float>();
+    for (int i = 0; i < 3; i++) {
+      for (int j = 0; j < 3; j++) {
+        c.w2c_R[i * 3 + j] = w2c_R(i, j);
+        c.c2w_R[i * 3 + j] = c2w_R(i, j);
+      }
+      c.w2c_t[i] = w2c_t[i];
+    }
+    // ugu::Init: (re)allocate only when the size differs (image.h:963-985).  The library writes
+    // every pixel of every requested image, so the clear is part of the kernel.
+    const int w = c.width, h = c.height;
+    if (color != nullptr && (color->cols != w || color->rows != h)) *color = Image3b::zeros(h, w);
+    if (depth != nullptr && (depth->cols != w || depth->rows != h)) *depth = Image1f::zeros(h, w);
+    if (normal != nullptr && (normal->cols != w || normal->rows != h)) *normal = Image3f::zeros(h, w);
+    if (mask != nullptr && (mask->cols != w || mask->rows != h)) *mask = Image1b::zeros(h, w);
+    if (face_id != nullptr && (face_id->cols != w || face_id->rows != h)) *face_id = Image1i::zeros(h, w);
+    ugu_b200_outputs out;
+    out.color = color ? color->data : nullptr;
+    out.depth = depth ? reinterpret_cast<float*>(depth->data) : nullptr;
+    out.normal = normal ? reinterpret_cast<float*>(normal->data) : nullptr;
+    out.mask = mask ? mask->data : nullptr;
+    out.face_id = face_id ? reinterpret_cast<int32_t*>(face_id->data) : nullptr;
+    if (ugu_b200_rasterizer_render(handle_, &c, &out) != UGU_B200_OK) {
+      LOGE("%s\n", ugu_b200_last_error(handle_));
+      return false;
+    }
+    return true;
+  }
+};
+
+RasterizerCuda::RasterizerCuda() : pimpl_(new Impl(0)) {}
+RasterizerCuda::~RasterizerCuda() {}
+RasterizerCuda::RasterizerCuda(const RendererCpuOption& option, int device)
+    : pimpl_(new Impl(device)) {
+  set_option(option);
+}
+bool RasterizerCuda::valid() const { return pimpl_->handle_ != nullptr; }
+
+void RasterizerCuda::set_option(const RendererCpuOption& option) {
+  option.CopyTo(&pimpl_->option_);  // rasterizer.cc:73-75 (oren_nayar_sigma is not copied)
+}
+
+void RasterizerCuda::set_mesh(std::shared_ptr<const Mesh> mesh) {
+  pimpl_->mesh_initialized_ = false;  // rasterizer.cc:78
+  pimpl_->mesh_ = mesh;
+  if (mesh->face_normals().empty()) {
+    LOGW("face normal is empty. culling and shading may not work\n");
+  }
+  if (mesh->normals().empty()) {
+    LOGW("vertex normal is empty. shading may not work\n");
+  }
+}
+
+bool RasterizerCuda::PrepareMesh() { return pimpl_->PrepareMesh(); }
+void RasterizerCuda::set_camera(std::shared_ptr<const Camera> camera) { pimpl_->camera_ = camera; }
+
+bool RasterizerCuda::Render(Image3b* color, Image1f* depth, Image3f* normal, Image1b* mask,
+                            Image1i* face_id) const {
+  return pimpl_->Render(color, depth, normal, mask, face_id);
+}
+bool RasterizerCuda::RenderColor(Image3b* color) const {
+  return Render(color, nullptr, nullptr, nullptr, nullptr);
+}
+bool RasterizerCuda::RenderDepth(Image1f* depth) const {
+  return Render(nullptr, depth, nullptr, nullptr, nullptr);
+}
+bool RasterizerCuda::RenderNormal(Image3f* normal) const {
+  return Render(nullptr, nullptr, normal, nullptr, nullptr);
+}
+bool RasterizerCuda::RenderMask(Image1b* mask) const {
+  return Render(nullptr, nullptr, nullptr, mask, nullptr);
+}
+bool RasterizerCuda::RenderFaceId(Image1i* face_id) const {
+  return Render(nullptr, nullptr, nullptr, nullptr, face_id);
+}
+
+bool RasterizerCuda::RenderW(Image3b* color, Image1w* depth, Image3f* normal, Image1b* mask,
+                             Image1i* face_id) const {
+  if (depth == nullptr) {  // rasterizer.cc:331-334
+    LOGE("depth is nullptr");
+    return false;
+  }
+  Image1f f_depth;
+  const bool ok = Render(color, &f_depth, normal, mask, face_id);
+  if (ok) {
+    if (depth->cols != f_depth.cols || depth->rows != f_depth.rows)
+      *depth = Image1w::zeros(f_depth.rows, f_depth.cols);
+    ugu_b200_depth_to_u16(reinterpret_cast<const float*>(f_depth.data),
+                          reinterpret_cast<uint16_t*>(depth->data),
+                          static_cast<size_t>(f_depth.rows) * f_depth.cols);
+  }
+  return ok;
+}
+
+bool RasterizerCuda::RenderDepthW(Image1w* depth) const {
+  return RenderW(nullptr, depth, nullptr, nullptr, nullptr);
+}
+
+}  // namespace ugu

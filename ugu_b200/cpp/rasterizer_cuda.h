@@ -1,0 +1,48 @@
+// ugu::RasterizerCuda — the drop-in a UGU maintainer adds next to ugu::Rasterizer.
+//
+// Same interface as the reference's CPU rasterizer (include/ugu/renderer/cpu/rasterizer.h:14-53):
+// it derives from ugu::RendererCpu (include/ugu/renderer/cpu/renderer.h:42-76), so the swap at a
+// construction site (examples/ex02_renderer.cc:249-254) is one line:
+//
+//     std::unique_ptr<ugu::RendererCpu> renderer = std::make_unique<ugu::RasterizerCuda>(option);
+//
+// All work happens in libugu_b200_raster.so through the C-ABI of include/ugu_b200_raster.h.  There
+// is no CPU fallback: if no sm_100 device is usable, PrepareMesh()/Render() return false and log.
+#pragma once
+
+#include <memory>
+
+#include "ugu/renderer/cpu/renderer.h"
+
+namespace ugu {
+
+class RasterizerCuda : public RendererCpu {
+  class Impl;
+  std::unique_ptr<Impl> pimpl_;
+
+ public:
+  RasterizerCuda();
+  ~RasterizerCuda() override;
+  explicit RasterizerCuda(const RendererCpuOption& option, int device = 0);
+
+  void set_option(const RendererCpuOption& option) override;
+  void set_mesh(std::shared_ptr<const Mesh> mesh) override;
+  bool PrepareMesh() override;
+  void set_camera(std::shared_ptr<const Camera> camera) override;
+
+  bool Render(Image3b* color, Image1f* depth, Image3f* normal, Image1b* mask,
+              Image1i* face_id) const override;
+  bool RenderColor(Image3b* color) const override;
+  bool RenderDepth(Image1f* depth) const override;
+  bool RenderNormal(Image3f* normal) const override;
+  bool RenderMask(Image1b* mask) const override;
+  bool RenderFaceId(Image1i* face_id) const override;
+  bool RenderW(Image3b* color, Image1w* depth, Image3f* normal, Image1b* mask,
+               Image1i* face_id) const override;
+  bool RenderDepthW(Image1w* depth) const override;
+
+  // false when the CUDA library could not create a rasterizer (no B200 / no driver).
+  bool valid() const;
+};
+
+}  // namespace ugu
