@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -47,6 +48,7 @@ struct ugu_b200_rasterizer {
   // per-view scratch
   DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
   size_t vis_pixels = 0;
+  int coop_max = 64;  // bbox samples up to which a triangle takes the warp-cooperative path
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
   DevBuf out_color[2], out_depth[2], out_normal[2], out_mask[2], out_fid[2];
@@ -194,7 +196,7 @@ int Validate(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_
   if (out == nullptr ||
       (!out->color && !out->depth && !out->normal && !out->mask && !out->face_id))
     return Fail(r, UGU_B200_E_INVALID, "all arguments are nullptr. nothing to do");
-  if (cam->width <= 0 || cam->height <= 0)
+  if (cam->width <= 0 || cam->height <= 0 || (long long)cam->width * cam->height >= (1ll << 31))
     return Fail(r, UGU_B200_E_INVALID, "camera size %dx%d is invalid", cam->width, cam->height);
   if (o.diffuse_color < 0 || o.diffuse_color > 2 || o.interp < 0 || o.interp > 1 ||
       o.shading_normal < 0 || o.shading_normal > 1 || o.diffuse_shading < 0 || o.diffuse_shading > 2)
@@ -250,6 +252,7 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   fr.counters = (unsigned long long*)r->counters.p;
   fr.q_face = (int*)r->q_face.p;
   fr.q_job = (unsigned long long*)r->q_job.p;
+  fr.coop_max = r->coop_max;
   const MeshDev& m = r->mesh;
 
   ShadeParams sp;
@@ -278,7 +281,7 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
-    raster_kernel<<<Blocks((size_t)m.F, 256), 256, 0, st>>>(vp, m, fr);
+    raster_kernel<<<Blocks((size_t)m.F, 8 * kGroupFaces), 256, 0, st>>>(vp, m, fr);
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
@@ -286,7 +289,7 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   }
   {
     StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
-    resolve_kernel<<<Blocks((P + 3) / 4, 256), 256, 0, st>>>(vp, m, fr, sp);
+    resolve_kernel<<<Blocks(P, 256), 256, 0, st>>>(vp, m, fr, sp);
   }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
@@ -465,6 +468,9 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   r->opt.backface_culling = 1;
   r->opt.depth_scale = 1.0f;
   r->opt.oren_nayar_sigma = 0.3f;
+  if (const char* e = getenv("UGU_B200_COOP_MAX")) {  // tuning knob, clamped to the kernel's limit
+    r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
+  }
   auto fail = [&](cudaError_t err, const char* what) {
     int rc = Fail(nullptr, UGU_B200_E_CUDA, "%s failed: %s", what, cudaGetErrorString(err));
     ugu_b200_rasterizer_destroy(r);
@@ -603,10 +609,10 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   UP_TRY(MeshAlloc(r, &i0, F));
   UP_TRY(MeshAlloc(r, &i1, F));
   UP_TRY(MeshAlloc(r, &i2, F));
+  void* vidx_aos = nullptr;
   if (F > 0) {
-    void* t;
-    UP_TRY(upload(d->vertex_indices, (size_t)F * 12, &t));
-    repack_ivec3_to_planes<<<Blocks(F, 256), 256, 0, st>>>((const int*)t, F, i0, i1, i2);
+    UP_TRY(upload(d->vertex_indices, (size_t)F * 12, &vidx_aos));
+    repack_ivec3_to_planes<<<Blocks(F, 256), 256, 0, st>>>((const int*)vidx_aos, F, i0, i1, i2);
     r->stats.kernel_launches++;
   }
   m.idx0 = i0; m.idx1 = i1; m.idx2 = i2;
@@ -644,15 +650,25 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   } else {
     m.num_colors = 0;
   }
-  if (d->normal_indices && F > 0) {
-    int4* n = nullptr;
-    UP_TRY(MeshAlloc(r, &n, F));
-    void* t;
-    UP_TRY(upload(d->normal_indices, (size_t)F * 12, &t));
-    repack_ivec3_to_int4<<<Blocks(F, 256), 256, 0, st>>>((const int*)t, F, n);
-    r->stats.kernel_launches++;
-    m.nidx = n;
-    r->has_nidx = true;
+  {  // per-face records for the resolve kernel: one 32-byte sector per winning fragment
+    int4* rec = nullptr;
+    UP_TRY(MeshAlloc(r, &rec, (size_t)std::max(F, 1) * 2));
+    if (F > 0) {
+      void* nidx_aos = nullptr;
+      void* mat_dev = nullptr;
+      if (d->normal_indices) {
+        UP_TRY(upload(d->normal_indices, (size_t)F * 12, &nidx_aos));
+        r->has_nidx = true;
+      }
+      if (d->material_ids) {
+        UP_TRY(upload(d->material_ids, (size_t)F * 4, &mat_dev));
+        r->has_matids = true;
+      }
+      build_face_records<<<Blocks(F, 256), 256, 0, st>>>((const int*)vidx_aos, (const int*)nidx_aos,
+                                                         (const int*)mat_dev, F, rec);
+      r->stats.kernel_launches++;
+    }
+    m.frec = rec;
   }
   if (d->uv_indices && F > 0) {
     int4* n = nullptr;
@@ -675,17 +691,6 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     m.uv2 = u;
   } else {
     m.num_uv = 0;
-  }
-  if (d->material_ids && F > 0) {
-    int* ids = nullptr;
-    UP_TRY(MeshAlloc(r, &ids, F));
-    if ((rc = [&]() -> int {
-          CU_TRY(r, cudaMemcpyAsync(ids, d->material_ids, (size_t)F * 4, cudaMemcpyHostToDevice, st));
-          return UGU_B200_OK;
-        }()))
-      return cleanup(rc);
-    m.material_ids = ids;
-    r->has_matids = true;
   }
   r->tex_present.assign(d->num_materials, false);
   if (d->num_materials > 0) {

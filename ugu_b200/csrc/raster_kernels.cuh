@@ -12,11 +12,14 @@
 //   idx0/idx1/idx2      F int32 each (SoA planes)
 //   fn_x/fn_y/fn_z      F floats each (face normals, SoA planes)
 //   nrm4 / col4         float4 per normal / per vertex colour (one LDG.128 per gather)
-//   nidx / uvidx        int4 per face (3 indices + pad) — one LDG.128 per winning fragment
+//   frec                2 x int4 per face = one 32-byte sector per winning fragment:
+//                       {vidx0, vidx1, vidx2, material_id}, {nidx0, nidx1, nidx2, 0}
+//   uvidx               int4 per face (3 indices + pad)
 //   uv2                 float2 per uv
 //   tex (per material)  uchar4 RGBA8 texels, linear index = y * w + x like Image3b::at
 //   proj                float4 per vertex (image x, image y, camera z, 0), rewritten every view
-//   vis                 uint64 per pixel, the packed (z, face) visibility buffer; EMPTY = ~0
+//   vis                 uint64 per pixel, the packed visibility buffer
+//                       float_bits(z) << 32 | face_id << 1 | backface; EMPTY = ~0
 #pragma once
 
 #include <cuda_runtime.h>
@@ -25,7 +28,8 @@
 namespace ugu_b200 {
 
 constexpr unsigned long long kVisEmpty = 0xFFFFFFFFFFFFFFFFull;
-constexpr int kSmallMaxSamples = 16;  // bbox with <= this many pixel samples: rasterised in-thread
+constexpr int kCoopMaxSamplesLimit = 256;  // hard limit of the warp-cooperative path (8-bit dx/dy)
+constexpr int kGroupFaces = 64;            // faces a warp sets up per group (2 per lane)
 constexpr int kJobW = 8;              // large-triangle tile job: 8 x 4 pixels = one warp
 constexpr int kJobH = 4;
 constexpr int kQueueJobBits = 38;     // packed queue counter: [63:38] entries, [37:0] tile jobs
@@ -55,10 +59,9 @@ struct MeshDev {
   const float* fn_z;
   const float4* nrm4;
   const float4* col4;
-  const int4* nidx;
+  const int4* frec;
   const int4* uvidx;
   const float2* uv2;
-  const int* material_ids;
   const uchar4* const* tex;  // device array of per-material texel pointers
   const int2* tex_size;      // (w, h) per material
 };
@@ -71,6 +74,7 @@ struct FrameDev {
   unsigned long long* counters;  // [0] packed large queue counter, [1] hazard fragments, [2] chunk cursor
   int* q_face;                   // F
   unsigned long long* q_job;     // F : first tile job of each queued triangle
+  int coop_max;                  // bbox sample count up to which a triangle takes the cooperative path
 };
 
 struct ShadeParams {
@@ -171,7 +175,8 @@ __device__ __forceinline__ bool sample_triangle(const Tri& t, const ViewParams& 
 }
 
 __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis, size_t pix,
-                                           float z, int face, unsigned long long* hazard) {
+                                           float z, int face, bool backface,
+                                           unsigned long long* hazard) {
   // Fragments with z < FLT_MIN (zero, negative, denormal) or NaN make the reference's sequential
   // rule order dependent (rasterizer.cc:229, `d < FLT_MIN || z < d`); count them so the host can
   // report the view as off-contract instead of silently diverging.
@@ -179,8 +184,12 @@ __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis,
     atomicAdd(hazard, 1ull);
     return;
   }
+  // (z, face) orders exactly like the reference's sequential rule; the fragment's backface flag
+  // (rasterizer.cc:200,235) rides in bit 0 — it is a function of (face, pixel), so it never
+  // decides a comparison.
   const unsigned long long key =
-      ((unsigned long long)__float_as_uint(z) << 32) | (unsigned long long)(unsigned int)face;
+      ((unsigned long long)__float_as_uint(z) << 32) |
+      (unsigned long long)(((unsigned int)face << 1) | (backface ? 1u : 0u));
   // Early read: most occluded fragments never issue the atomic.
   if (key < vis[pix]) atomicMin(vis + pix, key);
 }
@@ -253,69 +262,224 @@ __device__ __forceinline__ bool tri_bounds(const Tri& t, const ViewParams& vp, i
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: one thread per face.  Gathers the three projected vertices, applies the reference's rejects,
-// rasterises triangles whose clamped bbox holds <= kSmallMaxSamples samples directly (the
-// micro-triangle regime of configs 2/4/5), and appends the others to the large-triangle queue with
-// a warp-level prefix sum over a packed (entries, tile jobs) counter — one atomicAdd per warp.
+// K2: triangle setup + warp-cooperative fine raster.
+//
+// A warp takes a group of 64 consecutive faces.  Phase A (lane = face, 2 faces per lane): gather
+// the projected vertices, apply the reference's rejects, and either (a) compact the triangle into
+// the warp's shared-memory record table when its clamped bbox holds <= coop_max samples, or (b)
+// append it to the large-triangle queue (warp prefix sum over a packed (entries, tile jobs)
+// counter, one atomicAdd per warp).  Phase B (lane = bbox sample): the samples of all recorded
+// triangles form one index space [0, T) that the warp walks 32 at a time, so lanes stay busy
+// whatever the mix of triangle sizes; the owner of a sample is found from a REDUX.OR bitmask of the
+// triangle start offsets.  Samples that pass the (cheap) inclusive edge test are compacted into a
+// ring queue, and the expensive part — per-pixel world ray, facing, the seven IEEE divisions of the
+// perspective-correct depth, the 64-bit atomicMin — runs on full warps of queued fragments.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) raster_kernel(const ViewParams vp, const MeshDev m,
-                                                     const FrameDev fr) {
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+struct WarpTris {
+  float v[9][kGroupFaces];  // v0x v0y v0z v1x v1y v1z v2x v2y v2z
+  float area[kGroupFaces];
+  float fn[3][kGroupFaces];
+  int x0[kGroupFaces];
+  int y0[kGroupFaces];
+  int nxm[kGroupFaces];    // nx | ceil(65536 / nx) << 9
+  int start[kGroupFaces];  // first sample of the triangle in the group's sample space
+  int fid[kGroupFaces];
+  unsigned q_packed[64];  // fragment ring: slot | dx << 6 | dy << 14 | pos << 22 | neg << 23
+  float q_w0[64], q_w1[64], q_w2[64];
+};
+
+__device__ __forceinline__ void raster_fragments(const ViewParams& vp, const FrameDev& fr,
+                                                 WarpTris& S, bool has_fn, int qhead, int n,
+                                                 unsigned lane) {
+  if ((int)lane < n) {
+    const int qi = (qhead + (int)lane) & 63;
+    const unsigned packed = S.q_packed[qi];
+    float w0 = S.q_w0[qi], w1 = S.q_w1[qi], w2 = S.q_w2[qi];
+    const int slot = (int)(packed & 63u);
+    const int x = S.x0[slot] + (int)((packed >> 6) & 255u);
+    const int y = S.y0[slot] + (int)((packed >> 14) & 255u);
+    bool backface = false;
+    if (has_fn) {
+      float r0, r1, r2;
+      ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
+      backface = dot3(S.fn[0][slot], S.fn[1][slot], S.fn[2][slot], r0, r1, r2) > 0.0f;
+    }
+    const bool ok = backface ? ((packed >> 23) & 1u) : ((packed >> 22) & 1u);
+    if (ok) {
+      // rasterizer.cc:208-224
+      const float area = S.area[slot];
+      w0 = w0 / area;
+      w1 = w1 / area;
+      w2 = w2 / area;
+      w0 = w0 / S.v[2][slot];
+      w1 = w1 / S.v[5][slot];
+      w2 = w2 / S.v[8][slot];
+      const float z = 1.0f / ((w0 + w1) + w2);
+      vis_update(fr.vis, (size_t)y * vp.W + x, z, S.fid[slot], backface, fr.counters + 1);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, const MeshDev m,
+                                                        const FrameDev fr) {
+  __shared__ WarpTris sh[8];
+  WarpTris& S = sh[threadIdx.x >> 5];
   const unsigned lane = threadIdx.x & 31u;
-  unsigned long long my = 0ull;  // packed (1 entry, njobs) when this face goes to the queue
-  if (f < m.F) {
-    const int i0 = __ldg(m.idx0 + f), i1 = __ldg(m.idx1 + f), i2 = __ldg(m.idx2 + f);
-    const float4 a = __ldg(fr.proj + i0);
-    const float4 b = __ldg(fr.proj + i1);
-    const float4 c = __ldg(fr.proj + i2);
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const int base = (int)((blockIdx.x * 8u + (threadIdx.x >> 5)) * (unsigned)kGroupFaces);
+  if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
+  const bool has_fn = m.num_face_normals > 0;
+
+  // ---- Phase A ---------------------------------------------------------------------------------
+  int fidx[2];
+  float4 pa[2], pb[2], pc[2];
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    fidx[h] = base + h * 32 + (int)lane;
+    if (fidx[h] < m.F) {
+      const int i0 = __ldg(m.idx0 + fidx[h]), i1 = __ldg(m.idx1 + fidx[h]), i2 = __ldg(m.idx2 + fidx[h]);
+      pa[h] = __ldg(fr.proj + i0);
+      pb[h] = __ldg(fr.proj + i1);
+      pc[h] = __ldg(fr.proj + i2);
+    }
+  }
+  int nslots = 0, T = 0;
+  unsigned long long my[2] = {0ull, 0ull};  // packed (1 entry, njobs) when the face is queued
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const int f = fidx[h];
+    int cnt = 0;
+    int x0 = 0, y0 = 0, nx = 1;
     Tri t;
-    tri_setup(t, a, b, c);
-    int x0, y0, x1, y1;
-    if (tri_bounds(t, vp, x0, y0, x1, y1)) {
-      const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
-      if ((long long)nx * ny <= kSmallMaxSamples) {
-        const bool has_fn = m.num_face_normals > 0;
-        float fnx = 0.f, fny = 0.f, fnz = 0.f;
-        if (has_fn) {
-          fnx = __ldg(m.fn_x + f);
-          fny = __ldg(m.fn_y + f);
-          fnz = __ldg(m.fn_z + f);
+    if (f < m.F) {
+      tri_setup(t, pa[h], pb[h], pc[h]);
+      int x1, y1;
+      if (tri_bounds(t, vp, x0, y0, x1, y1)) {
+        nx = x1 - x0 + 1;
+        const int ny = y1 - y0 + 1;
+        const long long ns = (long long)nx * ny;
+        if (ns <= (long long)fr.coop_max) {
+          cnt = (int)ns;
+        } else {
+          const unsigned long long njobs = (unsigned long long)((nx + kJobW - 1) / kJobW) *
+                                           (unsigned long long)((ny + kJobH - 1) / kJobH);
+          my[h] = (1ull << kQueueJobBits) | njobs;
         }
-        for (int y = y0; y <= y1; ++y) {
-          for (int x = x0; x <= x1; ++x) {
-            float z, w0, w1, w2;
-            bool bf;
-            if (sample_triangle(t, vp, has_fn, fnx, fny, fnz, x, y, fr.ray_dx, fr.ray_dy, z, w0,
-                                w1, w2, bf)) {
-              vis_update(fr.vis, (size_t)y * vp.W + x, z, f, fr.counters + 1);
-            }
-          }
+      }
+    }
+    // slot = rank among the recorded triangles; start = exclusive prefix of the sample counts
+    const unsigned rec = __ballot_sync(0xffffffffu, cnt > 0);
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= (unsigned)d) incl += o;
+    }
+    if (cnt > 0) {
+      const int slot = nslots + __popc(rec & lt_mask);
+      S.v[0][slot] = t.v0x; S.v[1][slot] = t.v0y; S.v[2][slot] = t.v0z;
+      S.v[3][slot] = t.v1x; S.v[4][slot] = t.v1y; S.v[5][slot] = t.v1z;
+      S.v[6][slot] = t.v2x; S.v[7][slot] = t.v2y; S.v[8][slot] = t.v2z;
+      S.area[slot] = t.area;
+      if (has_fn) {
+        S.fn[0][slot] = __ldg(m.fn_x + f);
+        S.fn[1][slot] = __ldg(m.fn_y + f);
+        S.fn[2][slot] = __ldg(m.fn_z + f);
+      }
+      S.x0[slot] = x0;
+      S.y0[slot] = y0;
+      S.nxm[slot] = nx | (((65536 + nx - 1) / nx) << 9);
+      S.start[slot] = T + incl - cnt;
+      S.fid[slot] = f;
+    }
+    nslots += __popc(rec);
+    T += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  {  // large-triangle queue: warp-level prefix sum of the packed counter
+    const unsigned long long mine = my[0] + my[1];
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= (unsigned)d) incl += o;
+    }
+    const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total != 0ull) {
+      unsigned long long qbase = 0ull;
+      if (lane == 31u) qbase = atomicAdd(fr.counters, total);
+      qbase = __shfl_sync(0xffffffffu, qbase, 31);
+      unsigned long long excl = qbase + incl - mine;
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        if (my[h] != 0ull) {
+          const unsigned qslot = (unsigned)(excl >> kQueueJobBits);
+          fr.q_face[qslot] = fidx[h];
+          fr.q_job[qslot] = excl & kQueueJobMask;
+          excl += my[h];
         }
-      } else {
-        const unsigned long long njobs = (unsigned long long)((nx + kJobW - 1) / kJobW) *
-                                         (unsigned long long)((ny + kJobH - 1) / kJobH);
-        my = (1ull << kQueueJobBits) | njobs;
       }
     }
   }
-  // warp-level inclusive prefix sum of the packed counter
-  unsigned long long incl = my;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= (unsigned)d) incl += o;
-  }
-  const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
-  if (total != 0ull) {
-    unsigned long long base = 0ull;
-    if (lane == 31u) base = atomicAdd(fr.counters, total);
-    base = __shfl_sync(0xffffffffu, base, 31);
-    if (my != 0ull) {
-      const unsigned long long excl = base + incl - my;
-      const unsigned slot = (unsigned)(excl >> kQueueJobBits);
-      fr.q_face[slot] = f;
-      fr.q_job[slot] = excl & kQueueJobMask;
+  if (T == 0) return;
+  __syncwarp();
+
+  // ---- Phase B ---------------------------------------------------------------------------------
+  const int st0 = ((int)lane < nslots) ? S.start[lane] : 0x7fffffff;
+  const int st1 = ((int)lane + 32 < nslots) ? S.start[lane + 32] : 0x7fffffff;
+  const unsigned le_mask = lt_mask | (1u << lane);
+  int started = 0, qhead = 0, qcount = 0;
+  for (int sb = 0; sb < T; sb += 32) {
+    unsigned bits = 0u;
+    const unsigned r0 = (unsigned)(st0 - sb), r1 = (unsigned)(st1 - sb);
+    if (r0 < 32u) bits |= 1u << r0;
+    if (r1 < 32u) bits |= 1u << r1;
+    const unsigned starts = __reduce_or_sync(0xffffffffu, bits);
+    const int s = sb + (int)lane;
+    bool cand = false;
+    unsigned packed = 0u;
+    float w0 = 0.f, w1 = 0.f, w2 = 0.f;
+    if (s < T) {
+      const int slot = started + __popc(starts & le_mask) - 1;
+      const int k = s - S.start[slot];
+      const int nxm = S.nxm[slot];
+      const int nx = nxm & 511;
+      const int dy = (k * (nxm >> 9)) >> 16;  // k / nx, exact for k, nx <= 256
+      const int dx = k - dy * nx;
+      const float px = (float)(S.x0[slot] + dx), py = (float)(S.y0[slot] + dy);
+      const float v0x = S.v[0][slot], v0y = S.v[1][slot];
+      const float v1x = S.v[3][slot], v1y = S.v[4][slot];
+      const float v2x = S.v[6][slot], v2y = S.v[7][slot];
+      // EdgeFunction(v1,v2,p), (v2,v0,p), (v0,v1,p) — same expressions as tri_setup/tri_edges
+      w0 = (px - v1x) * (v2y - v1y) - (py - v1y) * (v2x - v1x);
+      w1 = (px - v2x) * (v0y - v2y) - (py - v2y) * (v0x - v2x);
+      w2 = (px - v0x) * (v1y - v0y) - (py - v0y) * (v1x - v0x);
+      const bool pos = (w0 >= 0.0f) && (w1 >= 0.0f) && (w2 >= 0.0f);
+      const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
+      cand = pos || neg;
+      packed = (unsigned)slot | ((unsigned)dx << 6) | ((unsigned)dy << 14) |
+               (pos ? (1u << 22) : 0u) | (neg ? (1u << 23) : 0u);
     }
+    started += __popc(starts);
+    const unsigned bal = __ballot_sync(0xffffffffu, cand);
+    if (cand) {
+      const int qi = (qhead + qcount + __popc(bal & lt_mask)) & 63;
+      S.q_packed[qi] = packed;
+      S.q_w0[qi] = w0;
+      S.q_w1[qi] = w1;
+      S.q_w2[qi] = w2;
+    }
+    qcount += __popc(bal);
+    if (qcount >= 32) {
+      __syncwarp();
+      raster_fragments(vp, fr, S, has_fn, qhead, 32, lane);
+      __syncwarp();
+      qhead = (qhead + 32) & 63;
+      qcount -= 32;
+    }
+  }
+  if (qcount > 0) {
+    __syncwarp();
+    raster_fragments(vp, fr, S, has_fn, qhead, qcount, lane);
   }
 }
 
@@ -385,7 +549,7 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
           bool bf;
           if (sample_triangle(t, vp, has_fn, fnx, fny, fnz, x, y, fr.ray_dx, fr.ray_dy, z, w0, w1,
                               w2, bf)) {
-            vis_update(fr.vis, (size_t)y * vp.W + x, z, f, fr.counters + 1);
+            vis_update(fr.vis, (size_t)y * vp.W + x, z, f, bf, fr.counters + 1);
           }
         }
       }
@@ -398,8 +562,10 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
 // ---------------------------------------------------------------------------------------------
 // K4: resolve + attributes + shading + packing (rasterizer.cc:244-301, pixel_shader.h:222-422),
 // fused with the clear of every requested output (util_private.cc:72-87) and with the reset of the
-// visibility buffer and queue counters for the next view.  4 consecutive pixels per thread so every
-// store is a 32/128-bit vector store.
+// visibility buffer and queue counters for the next view.  One pixel per thread (maximum number of
+// independent gather chains in flight); a warp owns 32 consecutive pixels and stages its colour /
+// normal / mask values through shared memory so that every global store is a full-width vector
+// store.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned f2u8(float f) {
   // static_cast<unsigned char>(float) as the x86-64 reference compiles it: cvttss2si, low byte;
@@ -420,7 +586,7 @@ struct PixelOut {
   unsigned color;  // r | g << 8 | b << 16
   float depth;
   float nx, ny, nz;
-  unsigned mask;
+  bool mask;
   int face_id;
 };
 
@@ -430,43 +596,31 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   o.color = 0u;
   o.depth = 0.0f;
   o.nx = o.ny = o.nz = 0.0f;
-  o.mask = 0u;
+  o.mask = false;
   o.face_id = -1;
   if (key == kVisEmpty) return;
-  const int fid = (int)(unsigned)(key & 0xFFFFFFFFull);
-  const float z = __uint_as_float((unsigned)(key >> 32));
+  const unsigned low = (unsigned)(key & 0xFFFFFFFFull);
+  const int fid = (int)(low >> 1);
+  // the winner's backface flag (rasterizer.cc:200,235), carried by the key
+  if (sp.backface_culling && (low & 1u)) return;  // depth = 0, face_id = -1 (rasterizer.cc:248-252)
+  o.depth = __uint_as_float((unsigned)(key >> 32));
+  o.face_id = fid;
+  if (fid <= 0) return;  // sic: face 0 is never shaded (rasterizer.cc:254, SURVEY.md Q1)
+  o.mask = true;
 
   const bool need_color = sp.color != nullptr;
   const bool need_normal = sp.normal != nullptr;
-  const bool has_fn = m.num_face_normals > 0;
   const bool shade = need_color && sp.diffuse_shading != 0;
-  const bool need_ray = (has_fn && sp.backface_culling) || shade;
-
-  float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-  if (need_ray) ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
-  float fnx = 0.f, fny = 0.f, fnz = 0.f;
-  if (has_fn && (sp.backface_culling || sp.shading_normal == 0)) {
-    fnx = __ldg(m.fn_x + fid);
-    fny = __ldg(m.fn_y + fid);
-    fnz = __ldg(m.fn_z + fid);
-  }
-  if (sp.backface_culling && has_fn) {
-    // the winner's backface flag (rasterizer.cc:200,235) recomputed bit-identically
-    if (dot3(fnx, fny, fnz, r0, r1, r2) > 0.0f) return;  // depth = 0, face_id = -1
-  }
-  o.depth = z;
-  o.face_id = fid;
-  if (fid <= 0) return;  // sic: face 0 is never shaded (rasterizer.cc:254, SURVEY.md Q1)
-  o.mask = 255u;
-
+  const bool need_nrm = need_normal || shade;
   const bool need_weights =
-      (sp.shading_normal == 1 && (need_normal || shade)) || (need_color && sp.diffuse_color != 0);
+      (sp.shading_normal == 1 && need_nrm) || (need_color && sp.diffuse_color != 0);
+  if (!need_nrm && !need_color) return;
+
   float w0 = 0.f, w1 = 0.f, w2 = 0.f;
-  int i0 = 0, i1 = 0, i2 = 0;
+  int i0 = 0, i1 = 0, i2 = 0, mat = 0;
   if (need_weights) {
-    i0 = __ldg(m.idx0 + fid);
-    i1 = __ldg(m.idx1 + fid);
-    i2 = __ldg(m.idx2 + fid);
+    const int4 vr = __ldg(m.frec + 2 * (size_t)fid);
+    i0 = vr.x; i1 = vr.y; i2 = vr.z; mat = vr.w;
     Tri t;
     tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
     tri_edges(t, (float)x, (float)y, w0, w1, w2);
@@ -475,11 +629,13 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
 
   // shading normal (rasterizer.cc:268-279)
   float nwx = 0.f, nwy = 0.f, nwz = 0.f;
-  if (need_normal || shade) {
+  if (need_nrm) {
     if (sp.shading_normal == 0) {
-      nwx = fnx; nwy = fny; nwz = fnz;
+      nwx = __ldg(m.fn_x + fid);
+      nwy = __ldg(m.fn_y + fid);
+      nwz = __ldg(m.fn_z + fid);
     } else if (sp.shading_normal == 1) {
-      const int4 ni = __ldg(m.nidx + fid);
+      const int4 ni = __ldg(m.frec + 2 * (size_t)fid + 1);
       const float4 n0 = __ldg(m.nrm4 + ni.x);
       const float4 n1 = __ldg(m.nrm4 + ni.y);
       const float4 n2 = __ldg(m.nrm4 + ni.z);
@@ -510,7 +666,6 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
     const float2 t0 = __ldg(m.uv2 + ui.x);
     const float2 t1 = __ldg(m.uv2 + ui.y);
     const float2 t2 = __ldg(m.uv2 + ui.z);
-    const int mat = __ldg(m.material_ids + fid);
     const uchar4* tex = m.tex[mat];
     const int2 ts = m.tex_size[mat];
     const float k0 = 1.0f - u - v;
@@ -535,23 +690,24 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
       cb = f2u8(((k00 * a.z + k10 * b.z) + k01 * c.z) + k11 * d.z);
     }
   }
-  if (sp.diffuse_shading == 1) {  // DiffuseLambertianShader (pixel_shader.h:367-386); light == ray
-    float coeff = -dot3(r0, r1, r2, nwx, nwy, nwz);
-    if (coeff < 0.0f) coeff = 0.0f;
-    cr = f2u8(coeff * (float)cr);
-    cg = f2u8(coeff * (float)cg);
-    cb = f2u8(coeff * (float)cb);
-  } else if (sp.diffuse_shading == 2) {  // DiffuseOrenNayarShader (pixel_shader.h:390-422)
-    const float dot_light = -dot3(r0, r1, r2, nwx, nwy, nwz);
-    const float theta_i = acosf(dot_light);
-    const float theta_r = theta_i;  // dot_ray is the same expression: light_dir == ray_w
-    const float blx = (-nwx) * dot_light - r0;
-    const float bly = (-nwy) * dot_light - r1;
-    const float blz = (-nwz) * dot_light - r2;
-    const float phi = fmaxf(0.0f, dot3(blx, bly, blz, blx, bly, blz));
-    const float alpha = theta_i, beta = theta_r;
-    const float coeff =
-        fmaxf(0.0f, dot_light) * (sp.on_A + (sp.on_B * phi * sinf(alpha) * tanf(beta)));
+  if (shade) {
+    float r0, r1, r2;  // light_dir == ray_w (rasterizer.cc:291-298)
+    ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
+    float coeff;
+    if (sp.diffuse_shading == 1) {  // DiffuseLambertianShader (pixel_shader.h:367-386)
+      coeff = -dot3(r0, r1, r2, nwx, nwy, nwz);
+      if (coeff < 0.0f) coeff = 0.0f;
+    } else {  // DiffuseOrenNayarShader (pixel_shader.h:390-422)
+      const float dot_light = -dot3(r0, r1, r2, nwx, nwy, nwz);
+      const float theta_i = acosf(dot_light);
+      const float theta_r = theta_i;  // dot_ray is the same expression: light_dir == ray_w
+      const float blx = (-nwx) * dot_light - r0;
+      const float bly = (-nwy) * dot_light - r1;
+      const float blz = (-nwz) * dot_light - r2;
+      const float phi = fmaxf(0.0f, dot3(blx, bly, blz, blx, bly, blz));
+      const float alpha = theta_i, beta = theta_r;
+      coeff = fmaxf(0.0f, dot_light) * (sp.on_A + (sp.on_B * phi * sinf(alpha) * tanf(beta)));
+    }
     cr = f2u8(coeff * (float)cr);
     cg = f2u8(coeff * (float)cg);
     cb = f2u8(coeff * (float)cb);
@@ -559,11 +715,14 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   o.color = cr | (cg << 8) | (cb << 16);
 }
 
-__global__ void __launch_bounds__(256) resolve_kernel(const ViewParams vp, const MeshDev m,
-                                                      const FrameDev fr, const ShadeParams sp) {
-  const size_t P = (size_t)vp.W * (size_t)vp.H;
-  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // group of 4 pixels
-  if (g == 0) {
+__global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, const MeshDev m,
+                                                         const FrameDev fr, const ShadeParams sp) {
+  __shared__ __align__(16) float s_n[8][96];
+  __shared__ __align__(16) unsigned char s_c[8][96];
+  const unsigned P = (unsigned)vp.W * (unsigned)vp.H;  // W*H < 2^31 is validated by the host
+  const unsigned p = blockIdx.x * 256u + threadIdx.x;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (p == 0u) {
     // the queue / hazard counters are consumed: snapshot them for the host (counters[4..5]) and
     // reset them for the next view
     fr.counters[4] = fr.counters[0];
@@ -572,68 +731,61 @@ __global__ void __launch_bounds__(256) resolve_kernel(const ViewParams vp, const
     fr.counters[1] = 0ull;
     fr.counters[2] = 0ull;
   }
-  const size_t p0 = g * 4;
-  if (p0 >= P) return;
-  PixelOut o[4];
-  if (p0 + 3 < P) {
-    // 2 x 128-bit loads of the packed keys, then clear them for the next view
-    ulonglong2* vp2 = reinterpret_cast<ulonglong2*>(fr.vis + p0);
-    const ulonglong2 k01 = vp2[0], k23 = vp2[1];
-    vp2[0] = make_ulonglong2(kVisEmpty, kVisEmpty);
-    vp2[1] = make_ulonglong2(kVisEmpty, kVisEmpty);
-    const unsigned long long keys[4] = {k01.x, k01.y, k23.x, k23.y};
-    int y = (int)(p0 / (size_t)vp.W);
-    int x = (int)(p0 - (size_t)y * vp.W);
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      resolve_pixel(vp, m, fr, sp, keys[k], x, y, o[k]);
-      if (++x == vp.W) { x = 0; ++y; }
+  unsigned long long key = kVisEmpty;
+  if (p < P) {
+    key = fr.vis[p];
+    if (key != kVisEmpty) fr.vis[p] = kVisEmpty;  // leave the buffer EMPTY for the next view
+  }
+  const unsigned y = p / (unsigned)vp.W;
+  const unsigned x = p - y * (unsigned)vp.W;
+  PixelOut o;
+  resolve_pixel(vp, m, fr, sp, key, (int)x, (int)y, o);
+
+  const unsigned wbase = p - lane;  // first pixel of this warp
+  if (wbase >= P) return;
+  if (wbase + 32u <= P) {
+    if (sp.depth) sp.depth[p] = o.depth;
+    if (sp.face_id) sp.face_id[p] = o.face_id;
+    if (sp.mask) {
+      const unsigned bal = __ballot_sync(0xffffffffu, o.mask);
+      if (lane < 8u) {
+        const unsigned b = bal >> (lane * 4u);
+        const unsigned word = ((b & 1u) ? 0x000000FFu : 0u) | ((b & 2u) ? 0x0000FF00u : 0u) |
+                              ((b & 4u) ? 0x00FF0000u : 0u) | ((b & 8u) ? 0xFF000000u : 0u);
+        *reinterpret_cast<unsigned*>(sp.mask + wbase + lane * 4u) = word;
+      }
+    }
+    if (sp.normal) {
+      s_n[warp][lane * 3u + 0u] = o.nx;
+      s_n[warp][lane * 3u + 1u] = o.ny;
+      s_n[warp][lane * 3u + 2u] = o.nz;
     }
     if (sp.color) {
-      // 4 RGB pixels = 12 bytes = 3 aligned 32-bit words
-      const unsigned c0 = o[0].color, c1 = o[1].color, c2 = o[2].color, c3 = o[3].color;
-      unsigned* dst = reinterpret_cast<unsigned*>(sp.color + p0 * 3);
-      dst[0] = c0 | (c1 << 24);
-      dst[1] = (c1 >> 8) | (c2 << 16);
-      dst[2] = (c2 >> 16) | (c3 << 8);
+      s_c[warp][lane * 3u + 0u] = (unsigned char)(o.color & 0xFFu);
+      s_c[warp][lane * 3u + 1u] = (unsigned char)((o.color >> 8) & 0xFFu);
+      s_c[warp][lane * 3u + 2u] = (unsigned char)((o.color >> 16) & 0xFFu);
     }
-    if (sp.depth)
-      *reinterpret_cast<float4*>(sp.depth + p0) =
-          make_float4(o[0].depth, o[1].depth, o[2].depth, o[3].depth);
+    __syncwarp();
+    if (sp.normal && lane < 24u)
+      reinterpret_cast<float4*>(sp.normal + (size_t)wbase * 3u)[lane] =
+          reinterpret_cast<const float4*>(s_n[warp])[lane];
+    if (sp.color && lane < 6u)
+      reinterpret_cast<uint4*>(sp.color + (size_t)wbase * 3u)[lane] =
+          reinterpret_cast<const uint4*>(s_c[warp])[lane];
+  } else if (p < P) {  // ragged last warp of the image
+    if (sp.color) {
+      sp.color[(size_t)p * 3 + 0] = (uint8_t)(o.color & 0xFFu);
+      sp.color[(size_t)p * 3 + 1] = (uint8_t)((o.color >> 8) & 0xFFu);
+      sp.color[(size_t)p * 3 + 2] = (uint8_t)((o.color >> 16) & 0xFFu);
+    }
+    if (sp.depth) sp.depth[p] = o.depth;
     if (sp.normal) {
-      float4* dst = reinterpret_cast<float4*>(sp.normal + p0 * 3);
-      dst[0] = make_float4(o[0].nx, o[0].ny, o[0].nz, o[1].nx);
-      dst[1] = make_float4(o[1].ny, o[1].nz, o[2].nx, o[2].ny);
-      dst[2] = make_float4(o[2].nz, o[3].nx, o[3].ny, o[3].nz);
+      sp.normal[(size_t)p * 3 + 0] = o.nx;
+      sp.normal[(size_t)p * 3 + 1] = o.ny;
+      sp.normal[(size_t)p * 3 + 2] = o.nz;
     }
-    if (sp.mask)
-      *reinterpret_cast<unsigned*>(sp.mask + p0) =
-          o[0].mask | (o[1].mask << 8) | (o[2].mask << 16) | (o[3].mask << 24);
-    if (sp.face_id)
-      *reinterpret_cast<int4*>(sp.face_id + p0) =
-          make_int4(o[0].face_id, o[1].face_id, o[2].face_id, o[3].face_id);
-  } else {
-    for (size_t p = p0; p < P; p++) {
-      const unsigned long long key = fr.vis[p];
-      fr.vis[p] = kVisEmpty;
-      const int y = (int)(p / (size_t)vp.W);
-      const int x = (int)(p - (size_t)y * vp.W);
-      PixelOut q;
-      resolve_pixel(vp, m, fr, sp, key, x, y, q);
-      if (sp.color) {
-        sp.color[p * 3 + 0] = (uint8_t)(q.color & 0xFFu);
-        sp.color[p * 3 + 1] = (uint8_t)((q.color >> 8) & 0xFFu);
-        sp.color[p * 3 + 2] = (uint8_t)((q.color >> 16) & 0xFFu);
-      }
-      if (sp.depth) sp.depth[p] = q.depth;
-      if (sp.normal) {
-        sp.normal[p * 3 + 0] = q.nx;
-        sp.normal[p * 3 + 1] = q.ny;
-        sp.normal[p * 3 + 2] = q.nz;
-      }
-      if (sp.mask) sp.mask[p] = (uint8_t)q.mask;
-      if (sp.face_id) sp.face_id[p] = q.face_id;
-    }
+    if (sp.mask) sp.mask[p] = o.mask ? 255 : 0;
+    if (sp.face_id) sp.face_id[p] = o.face_id;
   }
 }
 
@@ -670,6 +822,19 @@ __global__ void repack_ivec3_to_int4(const int* __restrict__ aos, int n, int4* _
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n)
     out[i] = make_int4(aos[(size_t)i * 3 + 0], aos[(size_t)i * 3 + 1], aos[(size_t)i * 3 + 2], 0);
+}
+
+// {vidx0, vidx1, vidx2, material_id}, {nidx0, nidx1, nidx2, 0}: one 32-byte sector per face
+__global__ void build_face_records(const int* __restrict__ vidx, const int* __restrict__ nidx,
+                                   const int* __restrict__ mat, int n, int4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    out[2 * (size_t)i] = make_int4(vidx[(size_t)i * 3 + 0], vidx[(size_t)i * 3 + 1],
+                                   vidx[(size_t)i * 3 + 2], mat ? mat[i] : 0);
+    out[2 * (size_t)i + 1] = nidx ? make_int4(nidx[(size_t)i * 3 + 0], nidx[(size_t)i * 3 + 1],
+                                              nidx[(size_t)i * 3 + 2], 0)
+                                  : make_int4(0, 0, 0, 0);
+  }
 }
 
 __global__ void repack_rgb_to_rgba(const uint8_t* __restrict__ rgb, size_t n, uchar4* __restrict__ out) {
