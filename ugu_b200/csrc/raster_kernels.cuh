@@ -175,8 +175,8 @@ __device__ __forceinline__ bool sample_triangle(const Tri& t, const ViewParams& 
 }
 
 __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis, size_t pix,
-                                           float z, int face, bool backface,
-                                           unsigned long long* hazard) {
+                                           unsigned long long seen, float z, int face,
+                                           bool backface, unsigned long long* hazard) {
   // Fragments with z < FLT_MIN (zero, negative, denormal) or NaN make the reference's sequential
   // rule order dependent (rasterizer.cc:229, `d < FLT_MIN || z < d`); count them so the host can
   // report the view as off-contract instead of silently diverging.
@@ -190,8 +190,9 @@ __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis,
   const unsigned long long key =
       ((unsigned long long)__float_as_uint(z) << 32) |
       (unsigned long long)(((unsigned int)face << 1) | (backface ? 1u : 0u));
-  // Early read: most occluded fragments never issue the atomic.
-  if (key < vis[pix]) atomicMin(vis + pix, key);
+  // `seen` is an earlier read of vis[pix] (values only ever decrease): most occluded fragments
+  // never issue the atomic.
+  if (key < seen) atomicMin(vis + pix, key);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -275,47 +276,54 @@ __device__ __forceinline__ bool tri_bounds(const Tri& t, const ViewParams& vp, i
 // ring queue, and the expensive part — per-pixel world ray, facing, the seven IEEE divisions of the
 // perspective-correct depth, the 64-bit atomicMin — runs on full warps of queued fragments.
 // ---------------------------------------------------------------------------------------------
-struct WarpTris {
-  float v[9][kGroupFaces];  // v0x v0y v0z v1x v1y v1z v2x v2y v2z
-  float area[kGroupFaces];
-  float fn[3][kGroupFaces];
-  int x0[kGroupFaces];
-  int y0[kGroupFaces];
-  int nxm[kGroupFaces];    // nx | ceil(65536 / nx) << 9
-  int start[kGroupFaces];  // first sample of the triangle in the group's sample space
-  int fid[kGroupFaces];
-  unsigned q_packed[64];  // fragment ring: slot | dx << 6 | dy << 14 | pos << 22 | neg << 23
-  float q_w0[64], q_w1[64], q_w2[64];
+struct __align__(16) WarpTris {
+  // per recorded triangle (slot), SoA of 16-byte fields -> one LDS.128 each
+  float4 a[kGroupFaces];  // v0x v0y v1x v1y
+  float4 b[kGroupFaces];  // v2x v2y (int)x0 (int)y0
+  float4 c[kGroupFaces];  // v0z v1z v2z area
+  float4 d[kGroupFaces];  // fnx fny fnz (int)face
+  int2 meta[kGroupFaces];  // first sample of the triangle in the group's sample space; nx | ceil(65536 / nx) << 9
+  uint4 q[64];  // fragment ring: {slot | dx << 6 | dy << 14 | pos << 22 | neg << 23, w0, w1, w2}
 };
+
+// exact int -> float for 0 <= v < 2^23 without the (quarter-rate) I2F
+__device__ __forceinline__ float small_int_to_float(int v) {
+  return __uint_as_float(0x4B000000u | (unsigned)v) - 8388608.0f;
+}
 
 __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const FrameDev& fr,
                                                  WarpTris& S, bool has_fn, int qhead, int n,
                                                  unsigned lane) {
   if ((int)lane < n) {
-    const int qi = (qhead + (int)lane) & 63;
-    const unsigned packed = S.q_packed[qi];
-    float w0 = S.q_w0[qi], w1 = S.q_w1[qi], w2 = S.q_w2[qi];
+    const uint4 e = S.q[(qhead + (int)lane) & 63];
+    const unsigned packed = e.x;
+    float w0 = __uint_as_float(e.y), w1 = __uint_as_float(e.z), w2 = __uint_as_float(e.w);
     const int slot = (int)(packed & 63u);
-    const int x = S.x0[slot] + (int)((packed >> 6) & 255u);
-    const int y = S.y0[slot] + (int)((packed >> 14) & 255u);
+    const float4 rb = S.b[slot];
+    const int x = __float_as_int(rb.z) + (int)((packed >> 6) & 255u);
+    const int y = __float_as_int(rb.w) + (int)((packed >> 14) & 255u);
+    const size_t pix = (size_t)y * vp.W + x;
+    // issued now, consumed after the divisions: a stale value only makes the early-out less sharp
+    const unsigned long long seen = fr.vis[pix];
+    const float4 rd = S.d[slot];
     bool backface = false;
     if (has_fn) {
       float r0, r1, r2;
       ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
-      backface = dot3(S.fn[0][slot], S.fn[1][slot], S.fn[2][slot], r0, r1, r2) > 0.0f;
+      backface = dot3(rd.x, rd.y, rd.z, r0, r1, r2) > 0.0f;
     }
     const bool ok = backface ? ((packed >> 23) & 1u) : ((packed >> 22) & 1u);
     if (ok) {
       // rasterizer.cc:208-224
-      const float area = S.area[slot];
-      w0 = w0 / area;
-      w1 = w1 / area;
-      w2 = w2 / area;
-      w0 = w0 / S.v[2][slot];
-      w1 = w1 / S.v[5][slot];
-      w2 = w2 / S.v[8][slot];
+      const float4 rc = S.c[slot];
+      w0 = w0 / rc.w;
+      w1 = w1 / rc.w;
+      w2 = w2 / rc.w;
+      w0 = w0 / rc.x;
+      w1 = w1 / rc.y;
+      w2 = w2 / rc.z;
       const float z = 1.0f / ((w0 + w1) + w2);
-      vis_update(fr.vis, (size_t)y * vp.W + x, z, S.fid[slot], backface, fr.counters + 1);
+      vis_update(fr.vis, pix, seen, z, __float_as_int(rd.w), backface, fr.counters + 1);
     }
   }
 }
@@ -333,11 +341,17 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
   // ---- Phase A ---------------------------------------------------------------------------------
   int fidx[2];
   float4 pa[2], pb[2], pc[2];
+  float fnx[2] = {0.f, 0.f}, fny[2] = {0.f, 0.f}, fnz[2] = {0.f, 0.f};
 #pragma unroll
   for (int h = 0; h < 2; h++) {
     fidx[h] = base + h * 32 + (int)lane;
     if (fidx[h] < m.F) {
       const int i0 = __ldg(m.idx0 + fidx[h]), i1 = __ldg(m.idx1 + fidx[h]), i2 = __ldg(m.idx2 + fidx[h]);
+      if (has_fn) {  // same round trip as the indices, not a third dependent one
+        fnx[h] = __ldg(m.fn_x + fidx[h]);
+        fny[h] = __ldg(m.fn_y + fidx[h]);
+        fnz[h] = __ldg(m.fn_z + fidx[h]);
+      }
       pa[h] = __ldg(fr.proj + i0);
       pb[h] = __ldg(fr.proj + i1);
       pc[h] = __ldg(fr.proj + i2);
@@ -377,34 +391,27 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
     }
     if (cnt > 0) {
       const int slot = nslots + __popc(rec & lt_mask);
-      S.v[0][slot] = t.v0x; S.v[1][slot] = t.v0y; S.v[2][slot] = t.v0z;
-      S.v[3][slot] = t.v1x; S.v[4][slot] = t.v1y; S.v[5][slot] = t.v1z;
-      S.v[6][slot] = t.v2x; S.v[7][slot] = t.v2y; S.v[8][slot] = t.v2z;
-      S.area[slot] = t.area;
-      if (has_fn) {
-        S.fn[0][slot] = __ldg(m.fn_x + f);
-        S.fn[1][slot] = __ldg(m.fn_y + f);
-        S.fn[2][slot] = __ldg(m.fn_z + f);
-      }
-      S.x0[slot] = x0;
-      S.y0[slot] = y0;
-      S.nxm[slot] = nx | (((65536 + nx - 1) / nx) << 9);
-      S.start[slot] = T + incl - cnt;
-      S.fid[slot] = f;
+      S.a[slot] = make_float4(t.v0x, t.v0y, t.v1x, t.v1y);
+      S.b[slot] = make_float4(t.v2x, t.v2y, __int_as_float(x0), __int_as_float(y0));
+      S.c[slot] = make_float4(t.v0z, t.v1z, t.v2z, t.area);
+      S.d[slot] = make_float4(fnx[h], fny[h], fnz[h], __int_as_float(f));
+      // ceil(65536 / nx) through an exact float division (nx <= 256): no integer-divide sequence
+      const int recip = (int)(65536.0f / small_int_to_float(nx));
+      S.meta[slot] = make_int2(T + incl - cnt, nx | ((recip + ((recip * nx) < 65536 ? 1 : 0)) << 9));
     }
     nslots += __popc(rec);
     T += __shfl_sync(0xffffffffu, incl, 31);
   }
   {  // large-triangle queue: warp-level prefix sum of the packed counter
     const unsigned long long mine = my[0] + my[1];
-    unsigned long long incl = mine;
+    if (__any_sync(0xffffffffu, mine != 0ull)) {
+      unsigned long long incl = mine;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= (unsigned)d) incl += o;
-    }
-    const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
-    if (total != 0ull) {
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (unsigned)d) incl += o;
+      }
+      const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
       unsigned long long qbase = 0ull;
       if (lane == 31u) qbase = atomicAdd(fr.counters, total);
       qbase = __shfl_sync(0xffffffffu, qbase, 31);
@@ -424,50 +431,44 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
   __syncwarp();
 
   // ---- Phase B ---------------------------------------------------------------------------------
-  const int st0 = ((int)lane < nslots) ? S.start[lane] : 0x7fffffff;
-  const int st1 = ((int)lane + 32 < nslots) ? S.start[lane + 32] : 0x7fffffff;
+  const int st0 = ((int)lane < nslots) ? S.meta[lane].x : 0x7fffffff;
+  const int st1 = ((int)lane + 32 < nslots) ? S.meta[lane + 32].x : 0x7fffffff;
   const unsigned le_mask = lt_mask | (1u << lane);
   int started = 0, qhead = 0, qcount = 0;
   for (int sb = 0; sb < T; sb += 32) {
     unsigned bits = 0u;
     const unsigned r0 = (unsigned)(st0 - sb), r1 = (unsigned)(st1 - sb);
-    if (r0 < 32u) bits |= 1u << r0;
+    if (r0 < 32u) bits = 1u << r0;
     if (r1 < 32u) bits |= 1u << r1;
     const unsigned starts = __reduce_or_sync(0xffffffffu, bits);
     const int s = sb + (int)lane;
     bool cand = false;
-    unsigned packed = 0u;
-    float w0 = 0.f, w1 = 0.f, w2 = 0.f;
+    uint4 e = make_uint4(0u, 0u, 0u, 0u);
     if (s < T) {
       const int slot = started + __popc(starts & le_mask) - 1;
-      const int k = s - S.start[slot];
-      const int nxm = S.nxm[slot];
-      const int nx = nxm & 511;
-      const int dy = (k * (nxm >> 9)) >> 16;  // k / nx, exact for k, nx <= 256
+      const int2 mt = S.meta[slot];
+      const float4 ra = S.a[slot];
+      const float4 rb = S.b[slot];
+      const int k = s - mt.x;
+      const int nx = mt.y & 511;
+      const int dy = (k * (mt.y >> 9)) >> 16;  // k / nx, exact for k, nx <= 256
       const int dx = k - dy * nx;
-      const float px = (float)(S.x0[slot] + dx), py = (float)(S.y0[slot] + dy);
-      const float v0x = S.v[0][slot], v0y = S.v[1][slot];
-      const float v1x = S.v[3][slot], v1y = S.v[4][slot];
-      const float v2x = S.v[6][slot], v2y = S.v[7][slot];
+      const float px = small_int_to_float(__float_as_int(rb.z) + dx);
+      const float py = small_int_to_float(__float_as_int(rb.w) + dy);
       // EdgeFunction(v1,v2,p), (v2,v0,p), (v0,v1,p) — same expressions as tri_setup/tri_edges
-      w0 = (px - v1x) * (v2y - v1y) - (py - v1y) * (v2x - v1x);
-      w1 = (px - v2x) * (v0y - v2y) - (py - v2y) * (v0x - v2x);
-      w2 = (px - v0x) * (v1y - v0y) - (py - v0y) * (v1x - v0x);
+      const float w0 = (px - ra.z) * (rb.y - ra.w) - (py - ra.w) * (rb.x - ra.z);
+      const float w1 = (px - rb.x) * (ra.y - rb.y) - (py - rb.y) * (ra.x - rb.x);
+      const float w2 = (px - ra.x) * (ra.w - ra.y) - (py - ra.y) * (ra.z - ra.x);
       const bool pos = (w0 >= 0.0f) && (w1 >= 0.0f) && (w2 >= 0.0f);
       const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
       cand = pos || neg;
-      packed = (unsigned)slot | ((unsigned)dx << 6) | ((unsigned)dy << 14) |
-               (pos ? (1u << 22) : 0u) | (neg ? (1u << 23) : 0u);
+      e = make_uint4((unsigned)slot | ((unsigned)dx << 6) | ((unsigned)dy << 14) |
+                         (pos ? (1u << 22) : 0u) | (neg ? (1u << 23) : 0u),
+                     __float_as_uint(w0), __float_as_uint(w1), __float_as_uint(w2));
     }
     started += __popc(starts);
     const unsigned bal = __ballot_sync(0xffffffffu, cand);
-    if (cand) {
-      const int qi = (qhead + qcount + __popc(bal & lt_mask)) & 63;
-      S.q_packed[qi] = packed;
-      S.q_w0[qi] = w0;
-      S.q_w1[qi] = w1;
-      S.q_w2[qi] = w2;
-    }
+    if (cand) S.q[(qhead + qcount + __popc(bal & lt_mask)) & 63] = e;
     qcount += __popc(bal);
     if (qcount >= 32) {
       __syncwarp();
@@ -549,7 +550,8 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
           bool bf;
           if (sample_triangle(t, vp, has_fn, fnx, fny, fnz, x, y, fr.ray_dx, fr.ray_dy, z, w0, w1,
                               w2, bf)) {
-            vis_update(fr.vis, (size_t)y * vp.W + x, z, f, bf, fr.counters + 1);
+            const size_t pix = (size_t)y * vp.W + x;
+            vis_update(fr.vis, pix, fr.vis[pix], z, f, bf, fr.counters + 1);
           }
         }
       }
