@@ -230,12 +230,24 @@ void MakeViewParams(const ugu_b200_camera* cam, ViewParams* vp) {
   vp->cy = cam->cy;
   vp->wm1 = (float)(cam->width - 1);
   vp->hm1 = (float)(cam->height - 1);
+  // p / W for p < 2^31 as a multiply-high (Granlund-Montgomery, N = 31): l = ceil(log2 W),
+  // magic = ceil(2^(31 + l) / W) < 2^32, quotient = umulhi(p, magic) >> (l - 1)
+  vp->w_magic = 0;
+  vp->w_shift = 0;
+  if (cam->width > 1) {
+    unsigned l = 0;
+    while ((1ull << l) < (unsigned long long)cam->width) l++;
+    const unsigned long long num = 1ull << (31 + l);
+    vp->w_magic = (unsigned)((num + (unsigned long long)cam->width - 1) / (unsigned long long)cam->width);
+    vp->w_shift = l - 1;
+  }
   memcpy(vp->w2c_R, cam->w2c_R, sizeof(vp->w2c_R));
   memcpy(vp->w2c_t, cam->w2c_t, sizeof(vp->w2c_t));
   memcpy(vp->c2w_R, cam->c2w_R, sizeof(vp->c2w_R));
 }
 
 int g_num_sms = 148;
+int g_resolve_ctas_per_sm = 4;
 
 // Launch the four kernels of one view into device outputs `dout` on stream `st`.
 int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
@@ -289,7 +301,10 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   }
   {
     StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
-    resolve_kernel<<<Blocks(P, 256), 256, 0, st>>>(vp, m, fr, sp);
+    // persistent: enough CTAs to fill the machine, never more than there are 32-pixel chunks
+    const unsigned chunks = (unsigned)((P + 31) / 32);
+    const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * g_resolve_ctas_per_sm), (chunks + 7) / 8));
+    resolve_kernel<<<grid, 256, 0, st>>>(vp, m, fr, sp);
   }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
@@ -459,6 +474,11 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
                 prop.minor);
   CU_TRY(nullptr, cudaSetDevice(device));
   g_num_sms = prop.multiProcessorCount;
+  {
+    int n_ctas = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n_ctas, resolve_kernel, 256, 0) == cudaSuccess && n_ctas > 0)
+      g_resolve_ctas_per_sm = n_ctas;
+  }
   ugu_b200_rasterizer* r = new ugu_b200_rasterizer;
   r->device = device;
   r->opt.diffuse_color = UGU_B200_COLOR_NONE;

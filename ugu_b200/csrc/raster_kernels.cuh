@@ -40,6 +40,7 @@ struct ViewParams {
   int W, H;
   float fx, fy, cx, cy;
   float wm1, hm1;  // (float)(W - 1), (float)(H - 1)
+  unsigned w_magic, w_shift;  // p / W == __umulhi(p, w_magic) >> w_shift for p < 2^31 (W > 1)
   float w2c_R[9];
   float w2c_t[3];
   float c2w_R[9];
@@ -592,9 +593,12 @@ struct PixelOut {
   int face_id;
 };
 
+// `vr` / `ni` are the winner's face record (frec[2 fid], frec[2 fid + 1]), prefetched by the
+// caller's software pipeline whenever resolve_prefetch() says they are needed.
 __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDev& m,
                                               const FrameDev& fr, const ShadeParams& sp,
-                                              unsigned long long key, int x, int y, PixelOut& o) {
+                                              unsigned long long key, const int4& vr, const int4& ni,
+                                              int x, int y, PixelOut& o) {
   o.color = 0u;
   o.depth = 0.0f;
   o.nx = o.ny = o.nz = 0.0f;
@@ -621,7 +625,6 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   float w0 = 0.f, w1 = 0.f, w2 = 0.f;
   int i0 = 0, i1 = 0, i2 = 0, mat = 0;
   if (need_weights) {
-    const int4 vr = __ldg(m.frec + 2 * (size_t)fid);
     i0 = vr.x; i1 = vr.y; i2 = vr.z; mat = vr.w;
     Tri t;
     tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
@@ -637,7 +640,6 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
       nwy = __ldg(m.fn_y + fid);
       nwz = __ldg(m.fn_z + fid);
     } else if (sp.shading_normal == 1) {
-      const int4 ni = __ldg(m.frec + 2 * (size_t)fid + 1);
       const float4 n0 = __ldg(m.nrm4 + ni.x);
       const float4 n1 = __ldg(m.nrm4 + ni.y);
       const float4 n2 = __ldg(m.nrm4 + ni.z);
@@ -717,14 +719,45 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   o.color = cr | (cg << 8) | (cb << 16);
 }
 
+// Pipeline stage 1: the packed key of pixel chunk*32 + lane (EMPTY outside the image).  The load is
+// only ISSUED here; nothing may consume the value before the next loop iteration.
+__device__ __forceinline__ unsigned long long resolve_load_key(const FrameDev& fr, unsigned chunk,
+                                                               unsigned nchunks, unsigned lane,
+                                                               unsigned P) {
+  unsigned long long key = kVisEmpty;
+  if (chunk < nchunks) {
+    const unsigned p = chunk * 32u + lane;
+    if (p < P) key = fr.vis[p];
+  }
+  return key;
+}
+
+// Pipeline stage 2: the winner's face record, when the pixel will be shaded and needs it.
+__device__ __forceinline__ void resolve_prefetch(const MeshDev& m, unsigned long long key, bool cull,
+                                                 bool need_vr, bool need_ni, int4& vr, int4& ni) {
+  vr = make_int4(0, 0, 0, 0);
+  ni = make_int4(0, 0, 0, 0);
+  if (key == kVisEmpty) return;
+  const unsigned low = (unsigned)(key & 0xFFFFFFFFull);
+  if ((cull && (low & 1u)) || (low >> 1) == 0u) return;
+  const int4* rec = m.frec + 2 * (size_t)(low >> 1);
+  if (need_vr) vr = __ldg(rec);
+  if (need_ni) ni = __ldg(rec + 1);
+}
+
+// Persistent grid: warp w resolves the 32-pixel chunks w, w + nwarps, ... with a two-deep software
+// pipeline (key of chunk i+2 and face record of chunk i+1 are in flight while chunk i gathers,
+// shades and stores), so the dependent-load chain key -> face record -> vertex attributes costs one
+// exposed round trip per chunk instead of three.
 __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, const MeshDev m,
                                                          const FrameDev fr, const ShadeParams sp) {
   __shared__ __align__(16) float s_n[8][96];
   __shared__ __align__(16) unsigned char s_c[8][96];
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;  // W*H < 2^31 is validated by the host
-  const unsigned p = blockIdx.x * 256u + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  if (p == 0u) {
+  const unsigned nchunks = (P + 31u) >> 5;
+  const unsigned nwarps = gridDim.x * 8u;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
     // the queue / hazard counters are consumed: snapshot them for the host (counters[4..5]) and
     // reset them for the next view
     fr.counters[4] = fr.counters[0];
@@ -733,61 +766,79 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
     fr.counters[1] = 0ull;
     fr.counters[2] = 0ull;
   }
-  unsigned long long key = kVisEmpty;
-  if (p < P) {
-    key = fr.vis[p];
-    if (key != kVisEmpty) fr.vis[p] = kVisEmpty;  // leave the buffer EMPTY for the next view
-  }
-  const unsigned y = p / (unsigned)vp.W;
-  const unsigned x = p - y * (unsigned)vp.W;
-  PixelOut o;
-  resolve_pixel(vp, m, fr, sp, key, (int)x, (int)y, o);
+  const bool cull = sp.backface_culling != 0;
+  const bool need_color = sp.color != nullptr;
+  const bool need_nrm = sp.normal != nullptr || (need_color && sp.diffuse_shading != 0);
+  const bool need_ni = sp.shading_normal == 1 && need_nrm;
+  const bool need_vr = need_ni || (need_color && sp.diffuse_color != 0);
 
-  const unsigned wbase = p - lane;  // first pixel of this warp
-  if (wbase >= P) return;
-  if (wbase + 32u <= P) {
-    if (sp.depth) sp.depth[p] = o.depth;
-    if (sp.face_id) sp.face_id[p] = o.face_id;
-    if (sp.mask) {
-      const unsigned bal = __ballot_sync(0xffffffffu, o.mask);
-      if (lane < 8u) {
-        const unsigned b = bal >> (lane * 4u);
-        const unsigned word = ((b & 1u) ? 0x000000FFu : 0u) | ((b & 2u) ? 0x0000FF00u : 0u) |
-                              ((b & 4u) ? 0x00FF0000u : 0u) | ((b & 8u) ? 0xFF000000u : 0u);
-        *reinterpret_cast<unsigned*>(sp.mask + wbase + lane * 4u) = word;
+  unsigned chunk = blockIdx.x * 8u + warp;
+  unsigned long long key_a = resolve_load_key(fr, chunk, nchunks, lane, P);
+  unsigned long long key_b = resolve_load_key(fr, chunk + nwarps, nchunks, lane, P);
+  int4 vr_a, ni_a;
+  resolve_prefetch(m, key_a, cull, need_vr, need_ni, vr_a, ni_a);
+  for (; chunk < nchunks; chunk += nwarps) {
+    const unsigned long long key_c = resolve_load_key(fr, chunk + 2u * nwarps, nchunks, lane, P);
+    int4 vr_b, ni_b;
+    resolve_prefetch(m, key_b, cull, need_vr, need_ni, vr_b, ni_b);
+
+    const unsigned wbase = chunk * 32u;  // first pixel of this chunk
+    const unsigned p = wbase + lane;
+    const unsigned y = (vp.W == 1) ? p : (__umulhi(p, vp.w_magic) >> vp.w_shift);
+    const unsigned x = p - y * (unsigned)vp.W;
+    if (key_a != kVisEmpty) fr.vis[p] = kVisEmpty;  // leave the buffer EMPTY for the next view
+    PixelOut o;
+    resolve_pixel(vp, m, fr, sp, key_a, vr_a, ni_a, (int)x, (int)y, o);
+
+    if (wbase + 32u <= P) {
+      if (sp.depth) sp.depth[p] = o.depth;
+      if (sp.face_id) sp.face_id[p] = o.face_id;
+      if (sp.mask) {
+        const unsigned bal = __ballot_sync(0xffffffffu, o.mask);
+        if (lane < 8u) {
+          // nibble -> 4 bytes of 0x00 / 0xFF
+          const unsigned b = (bal >> (lane * 4u)) & 15u;
+          const unsigned word = ((b * 0x00204081u) & 0x01010101u) * 0xFFu;
+          *reinterpret_cast<unsigned*>(sp.mask + wbase + lane * 4u) = word;
+        }
       }
+      if (sp.normal) {
+        s_n[warp][lane * 3u + 0u] = o.nx;
+        s_n[warp][lane * 3u + 1u] = o.ny;
+        s_n[warp][lane * 3u + 2u] = o.nz;
+      }
+      if (sp.color) {
+        s_c[warp][lane * 3u + 0u] = (unsigned char)(o.color & 0xFFu);
+        s_c[warp][lane * 3u + 1u] = (unsigned char)((o.color >> 8) & 0xFFu);
+        s_c[warp][lane * 3u + 2u] = (unsigned char)((o.color >> 16) & 0xFFu);
+      }
+      __syncwarp();
+      if (sp.normal && lane < 24u)
+        reinterpret_cast<float4*>(sp.normal + (size_t)wbase * 3u)[lane] =
+            reinterpret_cast<const float4*>(s_n[warp])[lane];
+      if (sp.color && lane < 6u)
+        reinterpret_cast<uint4*>(sp.color + (size_t)wbase * 3u)[lane] =
+            reinterpret_cast<const uint4*>(s_c[warp])[lane];
+      __syncwarp();  // the staging rows are rewritten by the next chunk
+    } else if (p < P) {  // ragged last chunk of the image
+      if (sp.color) {
+        sp.color[(size_t)p * 3 + 0] = (uint8_t)(o.color & 0xFFu);
+        sp.color[(size_t)p * 3 + 1] = (uint8_t)((o.color >> 8) & 0xFFu);
+        sp.color[(size_t)p * 3 + 2] = (uint8_t)((o.color >> 16) & 0xFFu);
+      }
+      if (sp.depth) sp.depth[p] = o.depth;
+      if (sp.normal) {
+        sp.normal[(size_t)p * 3 + 0] = o.nx;
+        sp.normal[(size_t)p * 3 + 1] = o.ny;
+        sp.normal[(size_t)p * 3 + 2] = o.nz;
+      }
+      if (sp.mask) sp.mask[p] = o.mask ? 255 : 0;
+      if (sp.face_id) sp.face_id[p] = o.face_id;
     }
-    if (sp.normal) {
-      s_n[warp][lane * 3u + 0u] = o.nx;
-      s_n[warp][lane * 3u + 1u] = o.ny;
-      s_n[warp][lane * 3u + 2u] = o.nz;
-    }
-    if (sp.color) {
-      s_c[warp][lane * 3u + 0u] = (unsigned char)(o.color & 0xFFu);
-      s_c[warp][lane * 3u + 1u] = (unsigned char)((o.color >> 8) & 0xFFu);
-      s_c[warp][lane * 3u + 2u] = (unsigned char)((o.color >> 16) & 0xFFu);
-    }
-    __syncwarp();
-    if (sp.normal && lane < 24u)
-      reinterpret_cast<float4*>(sp.normal + (size_t)wbase * 3u)[lane] =
-          reinterpret_cast<const float4*>(s_n[warp])[lane];
-    if (sp.color && lane < 6u)
-      reinterpret_cast<uint4*>(sp.color + (size_t)wbase * 3u)[lane] =
-          reinterpret_cast<const uint4*>(s_c[warp])[lane];
-  } else if (p < P) {  // ragged last warp of the image
-    if (sp.color) {
-      sp.color[(size_t)p * 3 + 0] = (uint8_t)(o.color & 0xFFu);
-      sp.color[(size_t)p * 3 + 1] = (uint8_t)((o.color >> 8) & 0xFFu);
-      sp.color[(size_t)p * 3 + 2] = (uint8_t)((o.color >> 16) & 0xFFu);
-    }
-    if (sp.depth) sp.depth[p] = o.depth;
-    if (sp.normal) {
-      sp.normal[(size_t)p * 3 + 0] = o.nx;
-      sp.normal[(size_t)p * 3 + 1] = o.ny;
-      sp.normal[(size_t)p * 3 + 2] = o.nz;
-    }
-    if (sp.mask) sp.mask[p] = o.mask ? 255 : 0;
-    if (sp.face_id) sp.face_id[p] = o.face_id;
+    key_a = key_b;
+    vr_a = vr_b;
+    ni_a = ni_b;
+    key_b = key_c;
   }
 }
 
