@@ -120,6 +120,9 @@ class ClockSampler:
 def time_reference(mesh, opt, cams, steps, warmup, budget_s=None):
     """The reference's own CPU implementation: oracle/_ref (compiled reference) when it travelled,
     else the plain-C oracle port.  One step = camera->set_c2w + Render, as callers do."""
+    # all the host threads the reference can use (torchrun exports OMP_NUM_THREADS=1 by default);
+    # must be set before libgomp is loaded with the reference library
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import oracle
     if oracle.ref_available():
         kind = "reference"
