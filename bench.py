@@ -251,8 +251,10 @@ def main():
     ev1 = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     barrier()
     wall0 = time.perf_counter()
+    no_flush = os.environ.get("UGU_BENCH_NOFLUSH") == "1"   # diagnostic only: warm-L2 numbers are NOT bench values
     for i in range(K):
-        flush.zero_()          # L2 flush between timed iterations (outside the per-step events)
+        if not no_flush:
+            flush.zero_()      # L2 flush between timed iterations (outside the per-step events)
         ev0[i].record()
         device_step(warmup + i)
         ev1[i].record()
@@ -307,7 +309,8 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "views_per_step_per_gpu": 1, "culling": True,
-                       "l2": f"flushed between timed iterations ({L2_FLUSH_BYTES >> 20} MiB write)",
+                       "l2": ("NOT FLUSHED (diagnostic run, not a bench value)" if no_flush else
+                              f"flushed between timed iterations ({L2_FLUSH_BYTES >> 20} MiB write)"),
                        "timing": "sum of per-step CUDA-event pairs on the launching stream, max over ranks",
                        "parallelism": f"views sharded over {world} GPU(s), no collective"},
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": e2e_ms_max / Ke, "steps": Ke,

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -49,6 +50,7 @@ struct ugu_b200_rasterizer {
   DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
   size_t vis_pixels = 0;
   int coop_max = 64;  // bbox samples up to which a triangle takes the warp-cooperative path
+  int raster_halves = 2;  // faces per lane in a raster group (1 or 2)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
   DevBuf out_color[2], out_depth[2], out_normal[2], out_mask[2], out_fid[2];
@@ -137,6 +139,39 @@ bool IndicesInRange(const int32_t* idx, size_t count, int32_t limit) {
   return lo >= 0 && hi < limit;
 }
 
+// First-use reordering of an indexed attribute stream (positions by vertex_indices, normals by
+// normal_indices, uvs by uv_indices): element k of the new array is the k-th distinct element the
+// face list references, unreferenced ones follow.  Faces keep their order (face ids are outputs);
+// vertex / normal / uv numbering is internal, so this is invisible in the results.  It turns the
+// per-face gathers of consecutive faces into near-contiguous accesses.
+struct Reorder {
+  std::vector<int32_t> new_of_old;  // old index -> new index
+  std::vector<int32_t> idx;         // remapped 3F indices
+  bool active = false;
+};
+
+void BuildReorder(const int32_t* idx, size_t n_idx, int count, Reorder* out) {
+  out->new_of_old.assign((size_t)count, -1);
+  out->idx.resize(n_idx);
+  int32_t next = 0;
+  for (size_t i = 0; i < n_idx; i++) {
+    int32_t& slot = out->new_of_old[(size_t)idx[i]];
+    if (slot < 0) slot = next++;
+    out->idx[i] = slot;
+  }
+  for (int v = 0; v < count; v++)
+    if (out->new_of_old[(size_t)v] < 0) out->new_of_old[(size_t)v] = next++;
+  out->active = true;
+}
+
+void PermuteRows(const float* src, int count, int width, const Reorder& ro, std::vector<float>* dst) {
+  dst->resize((size_t)count * width);
+  for (int v = 0; v < count; v++) {
+    const size_t to = (size_t)ro.new_of_old[(size_t)v] * width;
+    for (int k = 0; k < width; k++) (*dst)[to + k] = src[(size_t)v * width + k];
+  }
+}
+
 // ---- profiling ---------------------------------------------------------------------------------
 int DrainEvents(ugu_b200_rasterizer* r) {
   for (int s = 0; s < r->ev_used; s++) {
@@ -196,7 +231,8 @@ int Validate(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_
   if (out == nullptr ||
       (!out->color && !out->depth && !out->normal && !out->mask && !out->face_id))
     return Fail(r, UGU_B200_E_INVALID, "all arguments are nullptr. nothing to do");
-  if (cam->width <= 0 || cam->height <= 0 || (long long)cam->width * cam->height >= (1ll << 31))
+  if (cam->width <= 0 || cam->height <= 0 || cam->width > 65535 || cam->height > 65535 ||
+      (long long)cam->width * cam->height >= (1ll << 31))
     return Fail(r, UGU_B200_E_INVALID, "camera size %dx%d is invalid", cam->width, cam->height);
   if (o.diffuse_color < 0 || o.diffuse_color > 2 || o.interp < 0 || o.interp > 1 ||
       o.shading_normal < 0 || o.shading_normal > 1 || o.diffuse_shading < 0 || o.diffuse_shading > 2)
@@ -230,6 +266,15 @@ void MakeViewParams(const ugu_b200_camera* cam, ViewParams* vp) {
   vp->cy = cam->cy;
   vp->wm1 = (float)(cam->width - 1);
   vp->hm1 = (float)(cam->height - 1);
+  {  // facing_backface(): 64 u rho with rho = max row 1-norm of c2w_R (a hair of slack for its own rounding)
+    float rho = 0.f;
+    for (int i = 0; i < 3; i++)
+      rho = std::max(rho, std::fabs(cam->c2w_R[3 * i]) + std::fabs(cam->c2w_R[3 * i + 1]) +
+                              std::fabs(cam->c2w_R[3 * i + 2]));
+    vp->facing_eps = 64.0f * 5.9604645e-8f * rho * 1.0001f;
+    vp->inv_fx = 1.0f / cam->fx;
+    vp->inv_fy = 1.0f / cam->fy;
+  }
   // p / W for p < 2^31 as a multiply-high (Granlund-Montgomery, N = 31): l = ceil(log2 W),
   // magic = ceil(2^(31 + l) / W) < 2^32, quotient = umulhi(p, magic) >> (l - 1)
   vp->w_magic = 0;
@@ -293,7 +338,10 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
-    raster_kernel<<<Blocks((size_t)m.F, 8 * kGroupFaces), 256, 0, st>>>(vp, m, fr);
+    if (r->raster_halves == 1)
+      raster_kernel<1><<<Blocks((size_t)m.F, 8 * 32), 256, 0, st>>>(vp, m, fr);
+    else
+      raster_kernel<2><<<Blocks((size_t)m.F, 8 * 64), 256, 0, st>>>(vp, m, fr);
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
@@ -491,6 +539,11 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   if (const char* e = getenv("UGU_B200_COOP_MAX")) {  // tuning knob, clamped to the kernel's limit
     r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
   }
+  if (const char* e = getenv("UGU_B200_RASTER_HALVES")) r->raster_halves = atoi(e) == 1 ? 1 : 2;
+  if (const char* e = getenv("UGU_B200_RASTER_CARVEOUT")) {  // tuning knob: shared-memory carveout in percent
+    cudaFuncSetAttribute(raster_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+    cudaFuncSetAttribute(raster_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+  }
   auto fail = [&](cudaError_t err, const char* what) {
     int rc = Fail(nullptr, UGU_B200_E_CUDA, "%s failed: %s", what, cudaGetErrorString(err));
     ugu_b200_rasterizer_destroy(r);
@@ -581,6 +634,40 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
       !IndicesInRange(d->material_ids, (size_t)F, d->num_materials))
     return Fail(r, UGU_B200_E_INVALID, "material_ids reference a material outside [0, %d)", d->num_materials);
 
+  // host-side first-use reordering (UGU_B200_REORDER=0 disables it, for A/B measurements)
+  const bool reorder = !(getenv("UGU_B200_REORDER") && atoi(getenv("UGU_B200_REORDER")) == 0);
+  Reorder ro_v, ro_n, ro_uv;
+  std::vector<float> pos_p, col_p, nrm_p, uv_p;
+  const float* h_vertices = d->vertices;
+  const float* h_colors = d->vertex_colors;
+  const float* h_normals = d->normals;
+  const float* h_uv = d->uv;
+  const int32_t* h_vidx = d->vertex_indices;
+  const int32_t* h_nidx = d->normal_indices;
+  const int32_t* h_uvidx = d->uv_indices;
+  if (reorder && F > 0 && V > 0) {
+    BuildReorder(d->vertex_indices, (size_t)F * 3, V, &ro_v);
+    PermuteRows(d->vertices, V, 3, ro_v, &pos_p);
+    h_vertices = pos_p.data();
+    h_vidx = ro_v.idx.data();
+    if (d->num_colors > 0 && d->vertex_colors) {
+      PermuteRows(d->vertex_colors, V, 3, ro_v, &col_p);  // num_colors >= V was validated
+      h_colors = col_p.data();
+    }
+    if (d->normal_indices && d->num_normals > 0 && d->normals) {
+      BuildReorder(d->normal_indices, (size_t)F * 3, d->num_normals, &ro_n);
+      PermuteRows(d->normals, d->num_normals, 3, ro_n, &nrm_p);
+      h_normals = nrm_p.data();
+      h_nidx = ro_n.idx.data();
+    }
+    if (d->uv_indices && d->num_uv > 0 && d->uv) {
+      BuildReorder(d->uv_indices, (size_t)F * 3, d->num_uv, &ro_uv);
+      PermuteRows(d->uv, d->num_uv, 2, ro_uv, &uv_p);
+      h_uv = uv_p.data();
+      h_uvidx = ro_uv.idx.data();
+    }
+  }
+
   MeshDev m{};
   m.V = V;
   m.F = F;
@@ -619,7 +706,7 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   UP_TRY(MeshAlloc(r, &pz, Vpad));
   if (V > 0) {
     void* t;
-    UP_TRY(upload(d->vertices, (size_t)V * 12, &t));
+    UP_TRY(upload(h_vertices, (size_t)V * 12, &t));
     repack_vec3_to_planes<<<Blocks(V, 256), 256, 0, st>>>((const float*)t, V, px, py, pz);
     r->stats.kernel_launches++;
   }
@@ -631,7 +718,7 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   UP_TRY(MeshAlloc(r, &i2, F));
   void* vidx_aos = nullptr;
   if (F > 0) {
-    UP_TRY(upload(d->vertex_indices, (size_t)F * 12, &vidx_aos));
+    UP_TRY(upload(h_vidx, (size_t)F * 12, &vidx_aos));
     repack_ivec3_to_planes<<<Blocks(F, 256), 256, 0, st>>>((const int*)vidx_aos, F, i0, i1, i2);
     r->stats.kernel_launches++;
   }
@@ -648,11 +735,14 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     r->stats.kernel_launches++;
     m.fn_x = fx; m.fn_y = fy; m.fn_z = fz;
   }
+  void* nrm_aos = nullptr;
+  void* col_aos = nullptr;
   if (d->num_normals > 0 && d->normals) {
     float4* n4 = nullptr;
     UP_TRY(MeshAlloc(r, &n4, d->num_normals));
     void* t;
-    UP_TRY(upload(d->normals, (size_t)d->num_normals * 12, &t));
+    UP_TRY(upload(h_normals, (size_t)d->num_normals * 12, &t));
+    nrm_aos = t;
     repack_vec3_to_float4<<<Blocks(d->num_normals, 256), 256, 0, st>>>((const float*)t, d->num_normals, n4);
     r->stats.kernel_launches++;
     m.nrm4 = n4;
@@ -661,14 +751,27 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   }
   if (d->num_colors > 0 && d->vertex_colors) {
     float4* c4 = nullptr;
-    UP_TRY(MeshAlloc(r, &c4, d->num_colors));
+    const int nc = V;  // colours are indexed by vertex (validated: num_colors >= V)
+    UP_TRY(MeshAlloc(r, &c4, nc));
     void* t;
-    UP_TRY(upload(d->vertex_colors, (size_t)d->num_colors * 12, &t));
-    repack_vec3_to_float4<<<Blocks(d->num_colors, 256), 256, 0, st>>>((const float*)t, d->num_colors, c4);
+    UP_TRY(upload(h_colors, (size_t)nc * 12, &t));
+    col_aos = t;
+    repack_vec3_to_float4<<<Blocks(nc, 256), 256, 0, st>>>((const float*)t, nc, c4);
     r->stats.kernel_launches++;
     m.col4 = c4;
   } else {
     m.num_colors = 0;
+  }
+  // Merged per-vertex attribute records when normals are indexed exactly like vertices (meshes whose
+  // normals come from CalcNormal, mesh.cc): one 32-byte gather per corner instead of two.
+  if (nrm_aos && d->normal_indices && F > 0 && d->num_normals == V &&
+      !(getenv("UGU_B200_MERGE_VATTR") && atoi(getenv("UGU_B200_MERGE_VATTR")) == 0) &&
+      memcmp(d->normal_indices, d->vertex_indices, (size_t)F * 12) == 0) {
+    float4* va = nullptr;
+    UP_TRY(MeshAlloc(r, &va, (size_t)V * 2));
+    build_vertex_attr<<<Blocks(V, 256), 256, 0, st>>>((const float*)nrm_aos, (const float*)col_aos, V, va);
+    r->stats.kernel_launches++;
+    m.vattr = va;
   }
   {  // per-face records for the resolve kernel: one 32-byte sector per winning fragment
     int4* rec = nullptr;
@@ -677,7 +780,7 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
       void* nidx_aos = nullptr;
       void* mat_dev = nullptr;
       if (d->normal_indices) {
-        UP_TRY(upload(d->normal_indices, (size_t)F * 12, &nidx_aos));
+        UP_TRY(upload(h_nidx, (size_t)F * 12, &nidx_aos));
         r->has_nidx = true;
       }
       if (d->material_ids) {
@@ -694,7 +797,7 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     int4* n = nullptr;
     UP_TRY(MeshAlloc(r, &n, F));
     void* t;
-    UP_TRY(upload(d->uv_indices, (size_t)F * 12, &t));
+    UP_TRY(upload(h_uvidx, (size_t)F * 12, &t));
     repack_ivec3_to_int4<<<Blocks(F, 256), 256, 0, st>>>((const int*)t, F, n);
     r->stats.kernel_launches++;
     m.uvidx = n;
@@ -704,7 +807,7 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     float2* u = nullptr;
     UP_TRY(MeshAlloc(r, &u, d->num_uv));
     if ((rc = [&]() -> int {
-          CU_TRY(r, cudaMemcpyAsync(u, d->uv, (size_t)d->num_uv * 8, cudaMemcpyHostToDevice, st));
+          CU_TRY(r, cudaMemcpyAsync(u, h_uv, (size_t)d->num_uv * 8, cudaMemcpyHostToDevice, st));
           return UGU_B200_OK;
         }()))
       return cleanup(rc);

@@ -12,8 +12,10 @@
 //   idx0/idx1/idx2      F int32 each (SoA planes)
 //   fn_x/fn_y/fn_z      F floats each (face normals, SoA planes)
 //   nrm4 / col4         float4 per normal / per vertex colour (one LDG.128 per gather)
-//   frec                2 x int4 per face = one 32-byte sector per winning fragment:
+//   frec                2 x int4 per face = one 32-byte sector (one LDG.256) per winning fragment:
 //                       {vidx0, vidx1, vidx2, material_id}, {nidx0, nidx1, nidx2, 0}
+//   vattr               when normal_indices == vertex_indices: {nx ny nz 0, r g b 0} per vertex,
+//                       32 bytes = one LDG.256 instead of two gathers
 //   uvidx               int4 per face (3 indices + pad)
 //   uv2                 float2 per uv
 //   tex (per material)  uchar4 RGBA8 texels, linear index = y * w + x like Image3b::at
@@ -29,7 +31,6 @@ namespace ugu_b200 {
 
 constexpr unsigned long long kVisEmpty = 0xFFFFFFFFFFFFFFFFull;
 constexpr int kCoopMaxSamplesLimit = 256;  // hard limit of the warp-cooperative path (8-bit dx/dy)
-constexpr int kGroupFaces = 64;            // faces a warp sets up per group (2 per lane)
 constexpr int kJobW = 8;              // large-triangle tile job: 8 x 4 pixels = one warp
 constexpr int kJobH = 4;
 constexpr int kQueueJobBits = 38;     // packed queue counter: [63:38] entries, [37:0] tile jobs
@@ -41,6 +42,8 @@ struct ViewParams {
   float fx, fy, cx, cy;
   float wm1, hm1;  // (float)(W - 1), (float)(H - 1)
   unsigned w_magic, w_shift;  // p / W == __umulhi(p, w_magic) >> w_shift for p < 2^31 (W > 1)
+  float facing_eps;           // 64 * 2^-24 * max_i sum_j |c2w_R[i][j]|  (see facing_backface)
+  float inv_fx, inv_fy;       // 1 / fx, 1 / fy for the approximate ray numerators of facing_backface
   float w2c_R[9];
   float w2c_t[3];
   float c2w_R[9];
@@ -60,6 +63,7 @@ struct MeshDev {
   const float* fn_z;
   const float4* nrm4;
   const float4* col4;
+  const float4* vattr;  // optional merged per-vertex record {nx ny nz 0, r g b 0} (32 B), see upload
   const int4* frec;
   const int4* uvidx;
   const float2* uv2;
@@ -93,6 +97,14 @@ struct ShadeParams {
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float dot3(float a0, float a1, float a2, float b0, float b1, float b2) {
   return a0 * b0 + (a1 * b1 + a2 * b2);
+}
+
+// 256-bit read-only global load (sm_100: LDG.E.256): one request for a whole 32-byte sector
+__device__ __forceinline__ void ldg256(const void* p, float4& lo, float4& hi) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z),
+                 "=f"(hi.w)
+               : "l"(p));
 }
 
 struct Tri {
@@ -277,13 +289,15 @@ __device__ __forceinline__ bool tri_bounds(const Tri& t, const ViewParams& vp, i
 // ring queue, and the expensive part — per-pixel world ray, facing, the seven IEEE divisions of the
 // perspective-correct depth, the 64-bit atomicMin — runs on full warps of queued fragments.
 // ---------------------------------------------------------------------------------------------
+// HALVES = faces per lane in a group (group = 32 * HALVES faces per warp)
+template <int HALVES>
 struct __align__(16) WarpTris {
   // per recorded triangle (slot), SoA of 16-byte fields -> one LDS.128 each
-  float4 a[kGroupFaces];  // v0x v0y v1x v1y
-  float4 b[kGroupFaces];  // v2x v2y (int)x0 (int)y0
-  float4 c[kGroupFaces];  // v0z v1z v2z area
-  float4 d[kGroupFaces];  // fnx fny fnz (int)face
-  int2 meta[kGroupFaces];  // first sample of the triangle in the group's sample space; nx | ceil(65536 / nx) << 9
+  float4 a[32 * HALVES];  // v0x v0y v1x v1y
+  float4 b[32 * HALVES];  // v2x v2y (int)(x0 | y0 << 16) (int)face
+  float4 c[32 * HALVES];  // v0z v1z v2z area
+  float4 d[32 * HALVES];  // g = c2w_R^T * face_normal (3), facing threshold
+  int2 meta[32 * HALVES];  // first sample of the triangle in the group's sample space; nx | ceil(65536 / nx) << 9
   uint4 q[64];  // fragment ring: {slot | dx << 6 | dy << 14 | pos << 22 | neg << 23, w0, w1, w2}
 };
 
@@ -292,31 +306,66 @@ __device__ __forceinline__ float small_int_to_float(int v) {
   return __uint_as_float(0x4B000000u | (unsigned)v) - 8388608.0f;
 }
 
-__device__ __forceinline__ void raster_fragments(const ViewParams& vp, const FrameDev& fr,
-                                                 WarpTris& S, bool has_fn, int qhead, int n,
-                                                 unsigned lane) {
+// Per-pixel facing (rasterizer.cc:197-200): backface = face_normal . ray_w(x, y) > 0 with
+// ray_w = c2w_R * normalize(d), d = ((x - cx) / fx, (y - cy) / fy, 1).  Only the SIGN of that float
+// expression is needed, and it equals the sign of val = g . da with g = c2w_R^T * face_normal and
+// da = ((x - cx) * (1 / fx), (y - cy) * (1 / fy), 1) whenever |val| is clear of the rounding error
+// of both evaluations (u = 2^-24, rho = max row 1-norm of c2w_R, D = |d|, dm = max(|d0|, |d1|, 1)):
+//   reference    |t   - T|   <= 10.2 u rho |f|_1       t its float result, T the real value
+//   cheap path   |val - D T| <= (6.1 + 2.5) u rho |f|_1 dm   (2.5 u: da versus d), D <= sqrt(3) dm
+// so |val| > 26.3 u rho |f|_1 dm implies sign(t) == sign(val) and t != 0.  The stored threshold
+// uses 64 instead of 26.3 (and an absolute floor for the denormal range); anything closer to
+// edge-on, or NaN, evaluates the reference's expression verbatim (from the exact ray tables).
+__device__ __forceinline__ bool facing_backface(const ViewParams& vp, const MeshDev& m,
+                                                const FrameDev& fr, const float4& g, int face,
+                                                int x, int y) {
+  const float d0 = (small_int_to_float(x) - vp.cx) * vp.inv_fx;
+  const float d1 = (small_int_to_float(y) - vp.cy) * vp.inv_fy;
+  const float val = (g.x * d0 + g.y * d1) + g.z;
+  const float dm = fmaxf(fmaxf(fabsf(d0), fabsf(d1)), 1.0f);
+  if (fabsf(val) > g.w * dm) return val > 0.0f;
+  float r0, r1, r2;
+  ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
+  return dot3(__ldg(m.fn_x + face), __ldg(m.fn_y + face), __ldg(m.fn_z + face), r0, r1, r2) > 0.0f;
+}
+
+template <int HALVES>
+__device__ __forceinline__ void raster_fragments(const ViewParams& vp, const MeshDev& m,
+                                                 const FrameDev& fr, WarpTris<HALVES>& S, bool has_fn,
+                                                 int qhead, int n, unsigned lane) {
   if ((int)lane < n) {
     const uint4 e = S.q[(qhead + (int)lane) & 63];
     const unsigned packed = e.x;
     float w0 = __uint_as_float(e.y), w1 = __uint_as_float(e.z), w2 = __uint_as_float(e.w);
     const int slot = (int)(packed & 63u);
     const float4 rb = S.b[slot];
-    const int x = __float_as_int(rb.z) + (int)((packed >> 6) & 255u);
-    const int y = __float_as_int(rb.w) + (int)((packed >> 14) & 255u);
+    const unsigned xy = __float_as_uint(rb.z);
+    const int x = (int)(xy & 0xFFFFu) + (int)((packed >> 6) & 255u);
+    const int y = (int)(xy >> 16) + (int)((packed >> 14) & 255u);
+    const int face = __float_as_int(rb.w);
     const size_t pix = (size_t)y * vp.W + x;
-    // issued now, consumed after the divisions: a stale value only makes the early-out less sharp
+    // issued now, consumed after the divisions: a stale value only makes the early-outs less sharp
     const unsigned long long seen = fr.vis[pix];
-    const float4 rd = S.d[slot];
-    bool backface = false;
-    if (has_fn) {
-      float r0, r1, r2;
-      ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
-      backface = dot3(rd.x, rd.y, rd.z, r0, r1, r2) > 0.0f;
+    const float4 rc = S.c[slot];
+    const bool pos = (packed >> 22) & 1u, neg = (packed >> 23) & 1u;
+
+    // Conservative early-out.  For a one-orientation sample with |w0+w1+w2| <= 1.001 |area| (same
+    // sign), the reference's z = 1 / (sum_k (w_k / area) / z_k) is >= 0.998999 * min z_k (each
+    // correctly rounded op moves a bound by at most 2^-24), so a fragment whose 0.998 * zmin is
+    // already behind the stored depth cannot win — whatever its facing — and the stored depth only
+    // ever decreases.
+    {
+      const float zs = __uint_as_float((unsigned)(seen >> 32));  // NaN while the pixel is EMPTY
+      const float zmin = fminf(fminf(rc.x, rc.y), rc.z);
+      const float s3 = (w0 + w1) + w2;
+      const float sa = pos ? s3 : -s3, aa = pos ? rc.w : -rc.w;
+      if (pos != neg && aa > 0.0f && sa <= 1.001f * aa && zmin < 1e30f && 0.998f * zmin > zs) return;
     }
-    const bool ok = backface ? ((packed >> 23) & 1u) : ((packed >> 22) & 1u);
-    if (ok) {
+    bool backface = false;
+    if (has_fn)
+      backface = facing_backface(vp, m, fr, S.d[slot], face, x, y);
+    if (backface ? neg : pos) {
       // rasterizer.cc:208-224
-      const float4 rc = S.c[slot];
       w0 = w0 / rc.w;
       w1 = w1 / rc.w;
       w2 = w2 / rc.w;
@@ -324,27 +373,29 @@ __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const Fra
       w1 = w1 / rc.y;
       w2 = w2 / rc.z;
       const float z = 1.0f / ((w0 + w1) + w2);
-      vis_update(fr.vis, pix, seen, z, __float_as_int(rd.w), backface, fr.counters + 1);
+      vis_update(fr.vis, pix, seen, z, face, backface, fr.counters + 1);
     }
   }
 }
 
+template <int HALVES>
 __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, const MeshDev m,
                                                         const FrameDev fr) {
-  __shared__ WarpTris sh[8];
-  WarpTris& S = sh[threadIdx.x >> 5];
+  __shared__ WarpTris<HALVES> sh[8];
+  WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const int base = (int)((blockIdx.x * 8u + (threadIdx.x >> 5)) * (unsigned)kGroupFaces);
+  const int base = (int)((blockIdx.x * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
   if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
   const bool has_fn = m.num_face_normals > 0;
 
   // ---- Phase A ---------------------------------------------------------------------------------
-  int fidx[2];
-  float4 pa[2], pb[2], pc[2];
-  float fnx[2] = {0.f, 0.f}, fny[2] = {0.f, 0.f}, fnz[2] = {0.f, 0.f};
+  int fidx[HALVES];
+  float4 pa[HALVES], pb[HALVES], pc[HALVES];
+  float fnx[HALVES], fny[HALVES], fnz[HALVES];
 #pragma unroll
-  for (int h = 0; h < 2; h++) {
+  for (int h = 0; h < HALVES; h++) {
+    fnx[h] = fny[h] = fnz[h] = 0.f;
     fidx[h] = base + h * 32 + (int)lane;
     if (fidx[h] < m.F) {
       const int i0 = __ldg(m.idx0 + fidx[h]), i1 = __ldg(m.idx1 + fidx[h]), i2 = __ldg(m.idx2 + fidx[h]);
@@ -359,9 +410,10 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
     }
   }
   int nslots = 0, T = 0;
-  unsigned long long my[2] = {0ull, 0ull};  // packed (1 entry, njobs) when the face is queued
+  unsigned long long my[HALVES];  // packed (1 entry, njobs) when the face is queued
 #pragma unroll
-  for (int h = 0; h < 2; h++) {
+  for (int h = 0; h < HALVES; h++) {
+    my[h] = 0ull;
     const int f = fidx[h];
     int cnt = 0;
     int x0 = 0, y0 = 0, nx = 1;
@@ -393,9 +445,14 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
     if (cnt > 0) {
       const int slot = nslots + __popc(rec & lt_mask);
       S.a[slot] = make_float4(t.v0x, t.v0y, t.v1x, t.v1y);
-      S.b[slot] = make_float4(t.v2x, t.v2y, __int_as_float(x0), __int_as_float(y0));
+      S.b[slot] = make_float4(t.v2x, t.v2y, __int_as_float(x0 | (y0 << 16)), __int_as_float(f));
       S.c[slot] = make_float4(t.v0z, t.v1z, t.v2z, t.area);
-      S.d[slot] = make_float4(fnx[h], fny[h], fnz[h], __int_as_float(f));
+      // g = c2w_R^T * fn and the facing threshold (see facing_backface)
+      S.d[slot] = make_float4(
+          (vp.c2w_R[0] * fnx[h] + vp.c2w_R[3] * fny[h]) + vp.c2w_R[6] * fnz[h],
+          (vp.c2w_R[1] * fnx[h] + vp.c2w_R[4] * fny[h]) + vp.c2w_R[7] * fnz[h],
+          (vp.c2w_R[2] * fnx[h] + vp.c2w_R[5] * fny[h]) + vp.c2w_R[8] * fnz[h],
+          fmaxf(vp.facing_eps * ((fabsf(fnx[h]) + fabsf(fny[h])) + fabsf(fnz[h])), 1e-30f));
       // ceil(65536 / nx) through an exact float division (nx <= 256): no integer-divide sequence
       const int recip = (int)(65536.0f / small_int_to_float(nx));
       S.meta[slot] = make_int2(T + incl - cnt, nx | ((recip + ((recip * nx) < 65536 ? 1 : 0)) << 9));
@@ -404,7 +461,9 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
     T += __shfl_sync(0xffffffffu, incl, 31);
   }
   {  // large-triangle queue: warp-level prefix sum of the packed counter
-    const unsigned long long mine = my[0] + my[1];
+    unsigned long long mine = 0ull;
+#pragma unroll
+    for (int h = 0; h < HALVES; h++) mine += my[h];
     if (__any_sync(0xffffffffu, mine != 0ull)) {
       unsigned long long incl = mine;
 #pragma unroll
@@ -418,7 +477,7 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
       qbase = __shfl_sync(0xffffffffu, qbase, 31);
       unsigned long long excl = qbase + incl - mine;
 #pragma unroll
-      for (int h = 0; h < 2; h++) {
+      for (int h = 0; h < HALVES; h++) {
         if (my[h] != 0ull) {
           const unsigned qslot = (unsigned)(excl >> kQueueJobBits);
           fr.q_face[qslot] = fidx[h];
@@ -432,15 +491,19 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
   __syncwarp();
 
   // ---- Phase B ---------------------------------------------------------------------------------
-  const int st0 = ((int)lane < nslots) ? S.meta[lane].x : 0x7fffffff;
-  const int st1 = ((int)lane + 32 < nslots) ? S.meta[lane + 32].x : 0x7fffffff;
+  int st[HALVES];
+#pragma unroll
+  for (int h = 0; h < HALVES; h++)
+    st[h] = ((int)lane + 32 * h < nslots) ? S.meta[lane + 32 * h].x : 0x7fffffff;
   const unsigned le_mask = lt_mask | (1u << lane);
   int started = 0, qhead = 0, qcount = 0;
   for (int sb = 0; sb < T; sb += 32) {
     unsigned bits = 0u;
-    const unsigned r0 = (unsigned)(st0 - sb), r1 = (unsigned)(st1 - sb);
-    if (r0 < 32u) bits = 1u << r0;
-    if (r1 < 32u) bits |= 1u << r1;
+#pragma unroll
+    for (int h = 0; h < HALVES; h++) {
+      const unsigned rr = (unsigned)(st[h] - sb);
+      if (rr < 32u) bits |= 1u << rr;
+    }
     const unsigned starts = __reduce_or_sync(0xffffffffu, bits);
     const int s = sb + (int)lane;
     bool cand = false;
@@ -454,8 +517,9 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
       const int nx = mt.y & 511;
       const int dy = (k * (mt.y >> 9)) >> 16;  // k / nx, exact for k, nx <= 256
       const int dx = k - dy * nx;
-      const float px = small_int_to_float(__float_as_int(rb.z) + dx);
-      const float py = small_int_to_float(__float_as_int(rb.w) + dy);
+      const unsigned xy = __float_as_uint(rb.z);
+      const float px = small_int_to_float((int)(xy & 0xFFFFu) + dx);
+      const float py = small_int_to_float((int)(xy >> 16) + dy);
       // EdgeFunction(v1,v2,p), (v2,v0,p), (v0,v1,p) — same expressions as tri_setup/tri_edges
       const float w0 = (px - ra.z) * (rb.y - ra.w) - (py - ra.w) * (rb.x - ra.z);
       const float w1 = (px - rb.x) * (ra.y - rb.y) - (py - rb.y) * (ra.x - rb.x);
@@ -473,7 +537,7 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
     qcount += __popc(bal);
     if (qcount >= 32) {
       __syncwarp();
-      raster_fragments(vp, fr, S, has_fn, qhead, 32, lane);
+      raster_fragments(vp, m, fr, S, has_fn, qhead, 32, lane);
       __syncwarp();
       qhead = (qhead + 32) & 63;
       qcount -= 32;
@@ -481,7 +545,7 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
   }
   if (qcount > 0) {
     __syncwarp();
-    raster_fragments(vp, fr, S, has_fn, qhead, qcount, lane);
+    raster_fragments(vp, m, fr, S, has_fn, qhead, qcount, lane);
   }
 }
 
@@ -634,15 +698,25 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
 
   // shading normal (rasterizer.cc:268-279)
   float nwx = 0.f, nwy = 0.f, nwz = 0.f;
+  float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0, c2 = c0;
+  // merged vertex records deliver the colours together with the normals
+  const bool merged = m.vattr != nullptr && sp.shading_normal == 1 && need_nrm;
   if (need_nrm) {
     if (sp.shading_normal == 0) {
       nwx = __ldg(m.fn_x + fid);
       nwy = __ldg(m.fn_y + fid);
       nwz = __ldg(m.fn_z + fid);
     } else if (sp.shading_normal == 1) {
-      const float4 n0 = __ldg(m.nrm4 + ni.x);
-      const float4 n1 = __ldg(m.nrm4 + ni.y);
-      const float4 n2 = __ldg(m.nrm4 + ni.z);
+      float4 n0, n1, n2;
+      if (merged) {
+        ldg256(m.vattr + 2 * (size_t)i0, n0, c0);
+        ldg256(m.vattr + 2 * (size_t)i1, n1, c1);
+        ldg256(m.vattr + 2 * (size_t)i2, n2, c2);
+      } else {
+        n0 = __ldg(m.nrm4 + ni.x);
+        n1 = __ldg(m.nrm4 + ni.y);
+        n2 = __ldg(m.nrm4 + ni.z);
+      }
       nwx = (w0 * n0.x + w1 * n1.x) + w2 * n2.x;
       nwy = (w0 * n0.y + w1 * n1.y) + w2 * n2.y;
       nwz = (w0 * n0.z + w1 * n1.z) + w2 * n2.z;
@@ -658,9 +732,11 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   unsigned cr = 255u, cg = 255u, cb = 255u;  // DiffuseDefaultColorizer
   const float u = w1, v = w2;
   if (sp.diffuse_color == 2) {  // DiffuseVertexColorColorizer (pixel_shader.h:234-256)
-    const float4 c0 = __ldg(m.col4 + i0);
-    const float4 c1 = __ldg(m.col4 + i1);
-    const float4 c2 = __ldg(m.col4 + i2);
+    if (!merged) {
+      c0 = __ldg(m.col4 + i0);
+      c1 = __ldg(m.col4 + i1);
+      c2 = __ldg(m.col4 + i2);
+    }
     const float k0 = 1.0f - u - v;
     cr = f2u8((k0 * c0.x + u * c1.x) + v * c2.x);
     cg = f2u8((k0 * c0.y + u * c1.y) + v * c2.y);
@@ -741,8 +817,14 @@ __device__ __forceinline__ void resolve_prefetch(const MeshDev& m, unsigned long
   const unsigned low = (unsigned)(key & 0xFFFFFFFFull);
   if ((cull && (low & 1u)) || (low >> 1) == 0u) return;
   const int4* rec = m.frec + 2 * (size_t)(low >> 1);
-  if (need_vr) vr = __ldg(rec);
-  if (need_ni) ni = __ldg(rec + 1);
+  if (need_ni) {
+    float4 lo, hi;
+    ldg256(rec, lo, hi);
+    vr = make_int4(__float_as_int(lo.x), __float_as_int(lo.y), __float_as_int(lo.z), __float_as_int(lo.w));
+    ni = make_int4(__float_as_int(hi.x), __float_as_int(hi.y), __float_as_int(hi.z), __float_as_int(hi.w));
+  } else if (need_vr) {
+    vr = __ldg(rec);
+  }
 }
 
 // Persistent grid: warp w resolves the 32-pixel chunks w, w + nwarps, ... with a two-deep software
@@ -887,6 +969,18 @@ __global__ void build_face_records(const int* __restrict__ vidx, const int* __re
     out[2 * (size_t)i + 1] = nidx ? make_int4(nidx[(size_t)i * 3 + 0], nidx[(size_t)i * 3 + 1],
                                               nidx[(size_t)i * 3 + 2], 0)
                                   : make_int4(0, 0, 0, 0);
+  }
+}
+
+// {nx ny nz 0, r g b 0} per vertex (normals indexed like vertices); colours may be absent
+__global__ void build_vertex_attr(const float* __restrict__ nrm, const float* __restrict__ col, int n,
+                                  float4* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    out[2 * (size_t)i] = make_float4(nrm[(size_t)i * 3 + 0], nrm[(size_t)i * 3 + 1], nrm[(size_t)i * 3 + 2], 0.f);
+    out[2 * (size_t)i + 1] = col ? make_float4(col[(size_t)i * 3 + 0], col[(size_t)i * 3 + 1],
+                                               col[(size_t)i * 3 + 2], 0.f)
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
 
