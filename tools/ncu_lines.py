@@ -35,18 +35,24 @@ subprocess.run(["cuobjdump", "-xelf", "all", lib], cwd=tmp, capture_output=True)
 cubin = next(p for p in Path(tmp).glob("*.cubin") if "camera_host" not in p.name)
 dis = subprocess.run(["nvdisasm", "-g", "-c", str(cubin)], capture_output=True, text=True).stdout.splitlines()
 # locate the function
-start = next(i for i, l in enumerate(dis) if l.startswith(".text.") and re.search(kern, l))
-lines = []
-cur = 0
-for l in dis[start + 1:]:
-    if l.startswith("\t.section") or l.startswith(".text."):
-        break
-    m = re.search(r'//## File "([^"]+)", line (\d+)', l)
-    if m:
-        cur = int(m.group(2))
-        continue
-    if re.match(r"\s+/\*[0-9a-f]{4}\*/", l):
-        lines.append((cur, l.split("*/", 1)[1].strip().rstrip(";")))
+def parse(start):
+    out, cur = [], 0
+    for l in dis[start + 1:]:
+        if l.startswith("\t.section") or l.startswith(".text."):
+            break
+        m = re.search(r'//## File "([^"]+)", line (\d+)', l)
+        if m:
+            cur = int(m.group(2))
+            continue
+        if re.match(r"\s+/\*[0-9a-f]{4}\*/", l):
+            out.append((cur, l.split("*/", 1)[1].strip().rstrip(";")))
+    return out
+
+
+# several instantiations may match the regex: take the one whose instruction count fits the profile
+cands = [i for i, l in enumerate(dis) if l.startswith(".text.") and re.search(kern, l)]
+start = min(cands, key=lambda i: abs(len(parse(i)) - len(body)))
+lines = parse(start)
 if len(lines) != len(body):
     print(f"warning: {len(lines)} disassembled vs {len(body)} profiled instructions", file=sys.stderr)
 src = Path(re.search(r'//## File "([^"]+)"', "\n".join(dis[start:start + 50])).group(1)).read_text().splitlines()

@@ -50,7 +50,7 @@ struct ugu_b200_rasterizer {
   DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
   size_t vis_pixels = 0;
   int coop_max = 64;  // bbox samples up to which a triangle takes the warp-cooperative path
-  int raster_halves = 2;  // faces per lane in a raster group (1 or 2)
+  int raster_halves = 1;  // faces per lane in a raster group (1 or 2); 1 measured faster (more L1 left)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
   DevBuf out_color[2], out_depth[2], out_normal[2], out_mask[2], out_fid[2];
