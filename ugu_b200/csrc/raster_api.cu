@@ -49,7 +49,9 @@ struct ugu_b200_rasterizer {
   // per-view scratch
   DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
   size_t vis_pixels = 0;
-  int coop_max = 64;  // bbox samples up to which a triangle takes the warp-cooperative path
+  int coop_max = 16;  // bbox samples up to which a triangle takes the warp-cooperative path; larger
+                      // ones go to the globally load-balanced tile-job queue (measured: spot 640x480
+                      // 79 -> 64 us/view versus 64; no difference on the micro-triangle configs)
   int raster_halves = 1;  // faces per lane in a raster group (1 or 2); 1 measured faster (more L1 left)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)

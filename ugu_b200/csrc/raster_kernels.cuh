@@ -165,28 +165,6 @@ __device__ __forceinline__ float tri_depth(const Tri& t, float& w0, float& w1, f
   return z;
 }
 
-// One pixel sample of one triangle (rasterizer.cc:196-237 minus the store): coverage with the
-// per-pixel facing rule, then depth.  Returns true when covered.
-__device__ __forceinline__ bool sample_triangle(const Tri& t, const ViewParams& vp, bool has_fn,
-                                                float fnx, float fny, float fnz, int x, int y,
-                                                const float* __restrict__ ray_dx,
-                                                const float* __restrict__ ray_dy, float& z,
-                                                float& w0, float& w1, float& w2, bool& backface) {
-  tri_edges(t, (float)x, (float)y, w0, w1, w2);
-  const bool pos = (w0 >= 0.0f) && (w1 >= 0.0f) && (w2 >= 0.0f);
-  const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
-  if (!pos && !neg) return false;
-  backface = false;
-  if (has_fn) {
-    float r0, r1, r2;
-    ray_world(vp, __ldg(ray_dx + x), __ldg(ray_dy + y), r0, r1, r2);
-    backface = dot3(fnx, fny, fnz, r0, r1, r2) > 0.0f;
-  }
-  if (backface ? !neg : !pos) return false;
-  z = tri_depth(t, w0, w1, w2);
-  return true;
-}
-
 __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis, size_t pix,
                                            unsigned long long seen, float z, int face,
                                            bool backface, unsigned long long* hazard) {
@@ -551,10 +529,11 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
 
 // ---------------------------------------------------------------------------------------------
 // K3: large triangles.  The queue orders triangles by their first tile job, so the global job
-// space [0, T) is load-balanced regardless of triangle size: each warp claims chunks of
-// kJobsPerChunk jobs, finds the owning queue entry with a warp-cooperative 32-ary search, then
-// walks entries; a job is an 8x4 pixel block of the triangle's bbox, one lane per pixel.
-// Persistent grid (multiple of the SM count); exits at once when the queue is empty.
+// space [0, T) is load-balanced regardless of triangle size: each warp claims chunks of jobs (chunk
+// size adapted to T so that every resident warp gets work: small meshes of mid-size triangles would
+// otherwise leave most of the machine idle), finds the owning queue entry with a warp-cooperative
+// 32-ary search, then walks entries; a job is an 8x4 pixel block of the triangle's bbox, one lane
+// per pixel.  Persistent grid (multiple of the SM count); exits at once when the queue is empty.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const MeshDev m,
                                                      const FrameDev fr) {
@@ -565,13 +544,15 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
   const unsigned lane = threadIdx.x & 31u;
   const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
   const unsigned long long gw = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const unsigned long long nchunks = (T + kJobsPerChunk - 1) / kJobsPerChunk;
+  unsigned long long per = (T + nwarps - 1) / nwarps;  // jobs per chunk: 2 .. kJobsPerChunk
+  per = per < 2ull ? 2ull : (per > (unsigned long long)kJobsPerChunk ? (unsigned long long)kJobsPerChunk : per);
+  const unsigned long long nchunks = (T + per - 1) / per;
   const bool has_fn = m.num_face_normals > 0;
   const int lx = (int)(lane & (kJobW - 1)), ly = (int)(lane >> 3);
 
   for (unsigned long long chunk = gw; chunk < nchunks; chunk += nwarps) {
-    const unsigned long long jb = chunk * kJobsPerChunk;
-    const unsigned long long je = (jb + kJobsPerChunk < T) ? jb + kJobsPerChunk : T;
+    const unsigned long long jb = chunk * per;
+    const unsigned long long je = (jb + per < T) ? jb + per : T;
     // 32-ary search: largest e with q_job[e] <= jb (q_job[0] == 0).
     unsigned lo = 0, hi = n;
     while (hi - lo > 1u) {
@@ -594,16 +575,18 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
       const unsigned long long jn = (e + 1u < n) ? __ldg(fr.q_job + e + 1u) : T;
       const unsigned long long jend = (jn < je) ? jn : je;
       const int i0 = __ldg(m.idx0 + f), i1 = __ldg(m.idx1 + f), i2 = __ldg(m.idx2 + f);
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (has_fn) {  // g = c2w_R^T * fn and the facing threshold (see facing_backface)
+        const float fnx = __ldg(m.fn_x + f), fny = __ldg(m.fn_y + f), fnz = __ldg(m.fn_z + f);
+        g = make_float4((vp.c2w_R[0] * fnx + vp.c2w_R[3] * fny) + vp.c2w_R[6] * fnz,
+                        (vp.c2w_R[1] * fnx + vp.c2w_R[4] * fny) + vp.c2w_R[7] * fnz,
+                        (vp.c2w_R[2] * fnx + vp.c2w_R[5] * fny) + vp.c2w_R[8] * fnz,
+                        fmaxf(vp.facing_eps * ((fabsf(fnx) + fabsf(fny)) + fabsf(fnz)), 1e-30f));
+      }
       Tri t;
       tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
       int x0, y0, x1, y1;
       tri_bounds(t, vp, x0, y0, x1, y1);  // queued triangles always pass
-      float fnx = 0.f, fny = 0.f, fnz = 0.f;
-      if (has_fn) {
-        fnx = __ldg(m.fn_x + f);
-        fny = __ldg(m.fn_y + f);
-        fnz = __ldg(m.fn_z + f);
-      }
       const unsigned ntx = (unsigned)((x1 - x0 + kJobW) / kJobW);
       for (unsigned long long jj = j; jj < jend; ++jj) {
         const unsigned local = (unsigned)(jj - js);
@@ -611,12 +594,18 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
         const int x = x0 + (int)tx * kJobW + lx;
         const int y = y0 + (int)ty * kJobH + ly;
         if (x <= x1 && y <= y1) {
-          float z, w0, w1, w2;
-          bool bf;
-          if (sample_triangle(t, vp, has_fn, fnx, fny, fnz, x, y, fr.ray_dx, fr.ray_dy, z, w0, w1,
-                              w2, bf)) {
+          float w0, w1, w2;
+          tri_edges(t, small_int_to_float(x), small_int_to_float(y), w0, w1, w2);
+          const bool pos = (w0 >= 0.0f) && (w1 >= 0.0f) && (w2 >= 0.0f);
+          const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
+          if (pos || neg) {
             const size_t pix = (size_t)y * vp.W + x;
-            vis_update(fr.vis, pix, fr.vis[pix], z, f, bf, fr.counters + 1);
+            const unsigned long long seen = fr.vis[pix];  // consumed after the divisions
+            const bool bf = has_fn ? facing_backface(vp, m, fr, g, f, x, y) : false;
+            if (bf ? neg : pos) {
+              const float z = tri_depth(t, w0, w1, w2);
+              vis_update(fr.vis, pix, seen, z, f, bf, fr.counters + 1);
+            }
           }
         }
       }
