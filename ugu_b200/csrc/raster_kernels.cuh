@@ -857,6 +857,22 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
     const unsigned p = wbase + lane;
     const unsigned y = (vp.W == 1) ? p : (__umulhi(p, vp.w_magic) >> vp.w_shift);
     const unsigned x = p - y * (unsigned)vp.W;
+    if (wbase + 32u <= P && __all_sync(0xffffffffu, key_a == kVisEmpty)) {
+      // Nothing landed on these 32 pixels (most of a typical frame): write the cleared values
+      // (util_private.cc:72-87) with full-width stores and move on.
+      if (sp.depth) sp.depth[p] = 0.0f;
+      if (sp.face_id) sp.face_id[p] = -1;
+      if (sp.mask && lane < 8u) *reinterpret_cast<unsigned*>(sp.mask + wbase + lane * 4u) = 0u;
+      if (sp.normal && lane < 24u)
+        reinterpret_cast<float4*>(sp.normal + (size_t)wbase * 3u)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (sp.color && lane < 6u)
+        reinterpret_cast<uint4*>(sp.color + (size_t)wbase * 3u)[lane] = make_uint4(0u, 0u, 0u, 0u);
+      key_a = key_b;
+      vr_a = vr_b;
+      ni_a = ni_b;
+      key_b = key_c;
+      continue;
+    }
     if (key_a != kVisEmpty) fr.vis[p] = kVisEmpty;  // leave the buffer EMPTY for the next view
     PixelOut o;
     resolve_pixel(vp, m, fr, sp, key_a, vr_a, ni_a, (int)x, (int)y, o);
