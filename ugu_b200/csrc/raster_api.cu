@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "raster_kernels.cuh"
@@ -52,6 +53,7 @@ struct ugu_b200_rasterizer {
   int coop_max = 16;  // bbox samples up to which a triangle takes the warp-cooperative path; larger
                       // ones go to the globally load-balanced tile-job queue (measured: spot 640x480
                       // 79 -> 64 us/view versus 64; no difference on the micro-triangle configs)
+  bool use_pdl = true;  // programmatic dependent launch of the per-view kernels (UGU_B200_PDL=0 disables)
   int raster_halves = 1;  // faces per lane in a raster group (1 or 2); 1 measured faster (more L1 left)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
@@ -296,6 +298,24 @@ void MakeViewParams(const ugu_b200_camera* cam, ViewParams* vp) {
 int g_num_sms = 148;
 int g_resolve_ctas_per_sm = 4;
 
+// Launch with programmatic stream serialization (PDL): the kernel may be scheduled into the tail of
+// its predecessor on the stream; it synchronises on the predecessor's results itself (pdl_wait()).
+template <typename... KArgs, typename... Args>
+cudaError_t LaunchView(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, bool pdl,
+                       Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 // Launch the four kernels of one view into device outputs `dout` on stream `st`.
 int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
                cudaStream_t st) {
@@ -333,28 +353,29 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   sp.face_id = dout->face_id;
 
   const size_t P = (size_t)vp.W * vp.H;
+  const bool pdl = r->use_pdl;
   {
     StageTimer t(r, st, UGU_B200_STAGE_VERTEX);
     const size_t threads = std::max<size_t>((size_t)(m.V + 3) / 4, (size_t)vp.W + vp.H);
-    vertex_kernel<<<Blocks(threads, 256), 256, 0, st>>>(vp, m, fr);
+    CU_TRY(r, LaunchView(vertex_kernel, Blocks(threads, 256), 256, st, pdl, vp, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
     if (r->raster_halves == 1)
-      raster_kernel<1><<<Blocks((size_t)m.F, 8 * 32), 256, 0, st>>>(vp, m, fr);
+      CU_TRY(r, LaunchView(raster_kernel<1>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
     else
-      raster_kernel<2><<<Blocks((size_t)m.F, 8 * 64), 256, 0, st>>>(vp, m, fr);
+      CU_TRY(r, LaunchView(raster_kernel<2>, Blocks((size_t)m.F, 8 * 64), 256, st, pdl, vp, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
-    binned_kernel<<<g_num_sms * 8, 128, 0, st>>>(vp, m, fr);
+    CU_TRY(r, LaunchView(binned_kernel, (unsigned)g_num_sms * 8u, 128, st, pdl, vp, m, fr));
   }
   {
     StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
     // persistent: enough CTAs to fill the machine, never more than there are 32-pixel chunks
     const unsigned chunks = (unsigned)((P + 31) / 32);
     const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * g_resolve_ctas_per_sm), (chunks + 7) / 8));
-    resolve_kernel<<<grid, 256, 0, st>>>(vp, m, fr, sp);
+    CU_TRY(r, LaunchView(resolve_kernel, grid, 256, st, pdl, vp, m, fr, sp));
   }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
@@ -541,6 +562,7 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   if (const char* e = getenv("UGU_B200_COOP_MAX")) {  // tuning knob, clamped to the kernel's limit
     r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
   }
+  if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
   if (const char* e = getenv("UGU_B200_RASTER_HALVES")) r->raster_halves = atoi(e) == 1 ? 1 : 2;
   if (const char* e = getenv("UGU_B200_RASTER_CARVEOUT")) {  // tuning knob: shared-memory carveout in percent
     cudaFuncSetAttribute(raster_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));

@@ -107,6 +107,16 @@ __device__ __forceinline__ void ldg256(const void* p, float4& lo, float4& hi) {
                : "l"(p));
 }
 
+// Programmatic dependent launch (sm_90+): every per-view kernel is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, signals its dependents as soon as it starts
+// (they are scheduled once the LAST CTA of this grid has started, i.e. into this grid's tail) and
+// waits here for the complete, flushed results of its predecessors before touching per-view data.
+// Both are no-ops for a plain launch.
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 struct Tri {
   float v0x, v0y, v0z, v1x, v1y, v1z, v2x, v2y, v2z;
   float e0x, e0y;  // v2 - v1
@@ -207,24 +217,27 @@ __device__ __forceinline__ float4 project_vertex(const ViewParams& vp, float x, 
 
 __global__ void __launch_bounds__(256) vertex_kernel(const ViewParams vp, const MeshDev m,
                                                      const FrameDev fr) {
+  pdl_launch_dependents();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  // ray tables: the first W + H threads
-  if (t < vp.W) fr.ray_dx[t] = ((float)t - vp.cx) / vp.fx;
-  else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
-
   const int v = t * 4;
   if (v + 3 < m.V) {
+    // the mesh is immutable: its loads may precede the wait on the previous view's kernels
     const float4 x = __ldg(reinterpret_cast<const float4*>(m.pos_x + v));
     const float4 y = __ldg(reinterpret_cast<const float4*>(m.pos_y + v));
     const float4 z = __ldg(reinterpret_cast<const float4*>(m.pos_z + v));
+    pdl_wait();
     fr.proj[v + 0] = project_vertex(vp, x.x, y.x, z.x);
     fr.proj[v + 1] = project_vertex(vp, x.y, y.y, z.y);
     fr.proj[v + 2] = project_vertex(vp, x.z, y.z, z.z);
     fr.proj[v + 3] = project_vertex(vp, x.w, y.w, z.w);
   } else {
+    pdl_wait();
     for (int k = v; k < m.V; k++)
       fr.proj[k] = project_vertex(vp, __ldg(m.pos_x + k), __ldg(m.pos_y + k), __ldg(m.pos_z + k));
   }
+  // ray tables: the first W + H threads
+  if (t < vp.W) fr.ray_dx[t] = ((float)t - vp.cx) / vp.fx;
+  else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -303,7 +316,7 @@ __device__ __forceinline__ bool facing_backface(const ViewParams& vp, const Mesh
   const float dm = fmaxf(fmaxf(fabsf(d0), fabsf(d1)), 1.0f);
   if (fabsf(val) > g.w * dm) return val > 0.0f;
   float r0, r1, r2;
-  ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
+  ray_world(vp, fr.ray_dx[x], fr.ray_dy[y], r0, r1, r2);
   return dot3(__ldg(m.fn_x + face), __ldg(m.fn_y + face), __ldg(m.fn_z + face), r0, r1, r2) > 0.0f;
 }
 
@@ -364,27 +377,39 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
   const int base = (int)((blockIdx.x * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
+  pdl_launch_dependents();
   if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
   const bool has_fn = m.num_face_normals > 0;
 
   // ---- Phase A ---------------------------------------------------------------------------------
   int fidx[HALVES];
+  int i0[HALVES], i1[HALVES], i2[HALVES];
   float4 pa[HALVES], pb[HALVES], pc[HALVES];
   float fnx[HALVES], fny[HALVES], fnz[HALVES];
 #pragma unroll
   for (int h = 0; h < HALVES; h++) {
     fnx[h] = fny[h] = fnz[h] = 0.f;
+    i0[h] = i1[h] = i2[h] = 0;
     fidx[h] = base + h * 32 + (int)lane;
-    if (fidx[h] < m.F) {
-      const int i0 = __ldg(m.idx0 + fidx[h]), i1 = __ldg(m.idx1 + fidx[h]), i2 = __ldg(m.idx2 + fidx[h]);
+    if (fidx[h] < m.F) {  // immutable mesh data: may be read before the vertex kernel has finished
+      i0[h] = __ldg(m.idx0 + fidx[h]);
+      i1[h] = __ldg(m.idx1 + fidx[h]);
+      i2[h] = __ldg(m.idx2 + fidx[h]);
       if (has_fn) {  // same round trip as the indices, not a third dependent one
         fnx[h] = __ldg(m.fn_x + fidx[h]);
         fny[h] = __ldg(m.fn_y + fidx[h]);
         fnz[h] = __ldg(m.fn_z + fidx[h]);
       }
-      pa[h] = __ldg(fr.proj + i0);
-      pb[h] = __ldg(fr.proj + i1);
-      pc[h] = __ldg(fr.proj + i2);
+    }
+  }
+  pdl_wait();  // projected vertices of this view; visibility buffer / counters left clean by resolve
+#pragma unroll
+  for (int h = 0; h < HALVES; h++) {
+    if (fidx[h] < m.F) {
+      // plain (coherent) loads: proj is rewritten every view by the preceding kernel
+      pa[h] = fr.proj[i0[h]];
+      pb[h] = fr.proj[i1[h]];
+      pc[h] = fr.proj[i2[h]];
     }
   }
   int nslots = 0, T = 0;
@@ -537,6 +562,8 @@ __global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, con
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const MeshDev m,
                                                      const FrameDev fr) {
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned long long packed = fr.counters[0];
   const unsigned long long T = packed & kQueueJobMask;
   const unsigned n = (unsigned)(packed >> kQueueJobBits);
@@ -559,7 +586,7 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
       const unsigned span = hi - lo;
       const unsigned step = (span + 31u) / 32u;
       const unsigned idx = lo + lane * step;
-      const bool pred = (idx < hi) && (__ldg(fr.q_job + idx) <= jb);
+      const bool pred = (idx < hi) && (fr.q_job[idx] <= jb);
       const unsigned bal = __ballot_sync(0xffffffffu, pred);
       const unsigned cnt = (unsigned)__popc(bal);  // >= 1: lane 0 probes lo
       const unsigned nlo = lo + (cnt - 1u) * step;
@@ -570,9 +597,9 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
     unsigned e = lo;
     unsigned long long j = jb;
     while (j < je) {
-      const int f = __ldg(fr.q_face + e);
-      const unsigned long long js = __ldg(fr.q_job + e);
-      const unsigned long long jn = (e + 1u < n) ? __ldg(fr.q_job + e + 1u) : T;
+      const int f = fr.q_face[e];
+      const unsigned long long js = fr.q_job[e];
+      const unsigned long long jn = (e + 1u < n) ? fr.q_job[e + 1u] : T;
       const unsigned long long jend = (jn < je) ? jn : je;
       const int i0 = __ldg(m.idx0 + f), i1 = __ldg(m.idx1 + f), i2 = __ldg(m.idx2 + f);
       float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -584,7 +611,7 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
                         fmaxf(vp.facing_eps * ((fabsf(fnx) + fabsf(fny)) + fabsf(fnz)), 1e-30f));
       }
       Tri t;
-      tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
+      tri_setup(t, fr.proj[i0], fr.proj[i1], fr.proj[i2]);
       int x0, y0, x1, y1;
       tri_bounds(t, vp, x0, y0, x1, y1);  // queued triangles always pass
       const unsigned ntx = (unsigned)((x1 - x0 + kJobW) / kJobW);
@@ -680,7 +707,7 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   if (need_weights) {
     i0 = vr.x; i1 = vr.y; i2 = vr.z; mat = vr.w;
     Tri t;
-    tri_setup(t, __ldg(fr.proj + i0), __ldg(fr.proj + i1), __ldg(fr.proj + i2));
+    tri_setup(t, fr.proj[i0], fr.proj[i1], fr.proj[i2]);
     tri_edges(t, (float)x, (float)y, w0, w1, w2);
     (void)tri_depth(t, w0, w1, w2);
   }
@@ -761,7 +788,7 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   }
   if (shade) {
     float r0, r1, r2;  // light_dir == ray_w (rasterizer.cc:291-298)
-    ray_world(vp, __ldg(fr.ray_dx + x), __ldg(fr.ray_dy + y), r0, r1, r2);
+    ray_world(vp, fr.ray_dx[x], fr.ray_dy[y], r0, r1, r2);
     float coeff;
     if (sp.diffuse_shading == 1) {  // DiffuseLambertianShader (pixel_shader.h:367-386)
       coeff = -dot3(r0, r1, r2, nwx, nwy, nwz);
@@ -828,6 +855,8 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const unsigned nchunks = (P + 31u) >> 5;
   const unsigned nwarps = gridDim.x * 8u;
+  pdl_launch_dependents();
+  pdl_wait();
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // the queue / hazard counters are consumed: snapshot them for the host (counters[4..5]) and
     // reset them for the next view
