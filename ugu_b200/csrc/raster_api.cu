@@ -50,10 +50,11 @@ struct ugu_b200_rasterizer {
   // per-view scratch
   DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
   size_t vis_pixels = 0;
-  int coop_max = 16;  // bbox samples up to which a triangle takes the warp-cooperative path; larger
-                      // ones go to the globally load-balanced tile-job queue (measured: spot 640x480
-                      // 79 -> 64 us/view versus 64; no difference on the micro-triangle configs)
+  int coop_max = 0;  // bbox samples up to which a triangle is rasterised inside raster_kernel; larger
+                     // ones go to the tile-job queue.  0 = adaptive (see RenderView)
   bool use_pdl = true;  // programmatic dependent launch of the per-view kernels (UGU_B200_PDL=0 disables)
+  int vertex_vpt = 1;    // vertices per thread of the vertex kernel (4 or 1)
+  int raster_minb = 4;   // resident CTAs per SM the raster kernel is compiled for (4, 5, 6)
   int raster_halves = 1;  // faces per lane in a raster group (1 or 2); 1 measured faster (more L1 left)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
@@ -296,7 +297,6 @@ void MakeViewParams(const ugu_b200_camera* cam, ViewParams* vp) {
 }
 
 int g_num_sms = 148;
-int g_resolve_ctas_per_sm = 4;
 
 // Launch with programmatic stream serialization (PDL): the kernel may be scheduled into the tail of
 // its predecessor on the stream; it synchronises on the predecessor's results itself (pdl_wait()).
@@ -331,7 +331,12 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   fr.counters = (unsigned long long*)r->counters.p;
   fr.q_face = (int*)r->q_face.p;
   fr.q_job = (unsigned long long*)r->q_job.p;
-  fr.coop_max = r->coop_max;
+  // Triangles up to coop_max bbox samples are rasterised inside raster_kernel (one warp per 32
+  // faces); larger ones go to the globally load-balanced tile-job queue.  The in-kernel path is the
+  // cheaper one per triangle but only as parallel as the face count: with fewer raster warps than
+  // the machine holds (F < ~600k) mid-size triangles are better spread over the whole GPU by the
+  // queue (measured: config 4, 10M faces, 1.17 -> 0.93 ms with 32; spot, 5.9k faces, 33 -> 38 us).
+  fr.coop_max = r->coop_max > 0 ? r->coop_max : (r->mesh.F >= 4 * 32 * 32 * g_num_sms ? 32 : 16);
   const MeshDev& m = r->mesh;
 
   ShadeParams sp;
@@ -356,15 +361,24 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   const bool pdl = r->use_pdl;
   {
     StageTimer t(r, st, UGU_B200_STAGE_VERTEX);
-    const size_t threads = std::max<size_t>((size_t)(m.V + 3) / 4, (size_t)vp.W + vp.H);
-    CU_TRY(r, LaunchView(vertex_kernel, Blocks(threads, 256), 256, st, pdl, vp, m, fr));
+    if (r->vertex_vpt == 1) {
+      const size_t threads = std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H);
+      CU_TRY(r, LaunchView(vertex_kernel_1, Blocks(threads, 256), 256, st, pdl, vp, m, fr));
+    } else {
+      const size_t threads = std::max<size_t>((size_t)(m.V + 3) / 4, (size_t)vp.W + vp.H);
+      CU_TRY(r, LaunchView(vertex_kernel, Blocks(threads, 256), 256, st, pdl, vp, m, fr));
+    }
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
-    if (r->raster_halves == 1)
-      CU_TRY(r, LaunchView(raster_kernel<1>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
+    if (r->raster_halves == 2)
+      CU_TRY(r, LaunchView(raster_kernel<2, 4>, Blocks((size_t)m.F, 8 * 64), 256, st, pdl, vp, m, fr));
+    else if (r->raster_minb == 5)
+      CU_TRY(r, LaunchView(raster_kernel<1, 5>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
+    else if (r->raster_minb == 6)
+      CU_TRY(r, LaunchView(raster_kernel<1, 6>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
     else
-      CU_TRY(r, LaunchView(raster_kernel<2>, Blocks((size_t)m.F, 8 * 64), 256, st, pdl, vp, m, fr));
+      CU_TRY(r, LaunchView(raster_kernel<1, 4>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
@@ -374,8 +388,34 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
     StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
     // persistent: enough CTAs to fill the machine, never more than there are 32-pixel chunks
     const unsigned chunks = (unsigned)((P + 31) / 32);
-    const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * g_resolve_ctas_per_sm), (chunks + 7) / 8));
-    CU_TRY(r, LaunchView(resolve_kernel, grid, 256, st, pdl, vp, m, fr, sp));
+    const bool need_color = sp.color != nullptr;
+    const bool need_nrm = sp.normal != nullptr || (need_color && sp.diffuse_shading != 0);
+    const int color_mode = need_color ? sp.diffuse_color : 0;
+    const int nmode = !need_nrm ? 0 : (sp.shading_normal == 0 ? 1 : (m.vattr ? 3 : 2));
+    const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 4), (chunks + 7) / 8));
+    // (the one-chunk-deeper variant <.., true>, which also prefetches the projected vertices, measured
+    //  slower on every config: its extra live registers spill at 4 CTAs/SM — see DESIGN.md)
+#define UGU_RESOLVE_CASE(C, N)                                                                   \
+  case (C)*4 + (N):                                                                              \
+    CU_TRY(r, LaunchView(resolve_kernel<C, N, 4, false>, grid, 256, st, pdl, vp, m, fr, sp));    \
+    break;
+    switch (color_mode * 4 + nmode) {
+      UGU_RESOLVE_CASE(0, 0)
+      UGU_RESOLVE_CASE(0, 1)
+      UGU_RESOLVE_CASE(0, 2)
+      UGU_RESOLVE_CASE(0, 3)
+      UGU_RESOLVE_CASE(1, 0)
+      UGU_RESOLVE_CASE(1, 1)
+      UGU_RESOLVE_CASE(1, 2)
+      UGU_RESOLVE_CASE(1, 3)
+      UGU_RESOLVE_CASE(2, 0)
+      UGU_RESOLVE_CASE(2, 1)
+      UGU_RESOLVE_CASE(2, 2)
+      UGU_RESOLVE_CASE(2, 3)
+      default:
+        return Fail(r, UGU_B200_E_INVALID, "option enumerator out of range");
+    }
+#undef UGU_RESOLVE_CASE
   }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
@@ -545,11 +585,6 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
                 prop.minor);
   CU_TRY(nullptr, cudaSetDevice(device));
   g_num_sms = prop.multiProcessorCount;
-  {
-    int n_ctas = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n_ctas, resolve_kernel, 256, 0) == cudaSuccess && n_ctas > 0)
-      g_resolve_ctas_per_sm = n_ctas;
-  }
   ugu_b200_rasterizer* r = new ugu_b200_rasterizer;
   r->device = device;
   r->opt.diffuse_color = UGU_B200_COLOR_NONE;
@@ -563,11 +598,9 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
     r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
   }
   if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
+  if (const char* e = getenv("UGU_B200_VERTEX_VPT")) r->vertex_vpt = atoi(e) == 4 ? 4 : 1;
+  if (const char* e = getenv("UGU_B200_RASTER_MINB")) r->raster_minb = std::max(4, std::min(atoi(e), 6));
   if (const char* e = getenv("UGU_B200_RASTER_HALVES")) r->raster_halves = atoi(e) == 1 ? 1 : 2;
-  if (const char* e = getenv("UGU_B200_RASTER_CARVEOUT")) {  // tuning knob: shared-memory carveout in percent
-    cudaFuncSetAttribute(raster_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
-    cudaFuncSetAttribute(raster_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
-  }
   auto fail = [&](cudaError_t err, const char* what) {
     int rc = Fail(nullptr, UGU_B200_E_CUDA, "%s failed: %s", what, cudaGetErrorString(err));
     ugu_b200_rasterizer_destroy(r);

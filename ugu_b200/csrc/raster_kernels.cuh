@@ -240,6 +240,25 @@ __global__ void __launch_bounds__(256) vertex_kernel(const ViewParams vp, const 
   else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
 }
 
+// One vertex per thread: 4x the warps of vertex_kernel for the same bytes (the kernel is a few
+// microseconds of pure latency at mesh sizes that fit one wave), fully coalesced 4-byte loads and
+// 16-byte stores.
+__global__ void __launch_bounds__(256) vertex_kernel_1(const ViewParams vp, const MeshDev m,
+                                                       const FrameDev fr) {
+  pdl_launch_dependents();
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  float x = 0.f, y = 0.f, z = 0.f;
+  if (t < m.V) {
+    x = __ldg(m.pos_x + t);
+    y = __ldg(m.pos_y + t);
+    z = __ldg(m.pos_z + t);
+  }
+  pdl_wait();
+  if (t < m.V) fr.proj[t] = project_vertex(vp, x, y, z);
+  if (t < vp.W) fr.ray_dx[t] = ((float)t - vp.cx) / vp.fx;
+  else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Triangle setup shared by K2 and K3: rejects + clamped bbox (rasterizer.cc:168-193).
 // Returns false when the triangle is rejected or has no pixel sample inside its bbox.
@@ -369,8 +388,8 @@ __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const Mes
   }
 }
 
-template <int HALVES>
-__global__ void __launch_bounds__(256, 4) raster_kernel(const ViewParams vp, const MeshDev m,
+template <int HALVES, int MINB>
+__global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewParams vp, const MeshDev m,
                                                         const FrameDev fr) {
   __shared__ WarpTris<HALVES> sh[8];
   WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
@@ -673,17 +692,108 @@ struct PixelOut {
   int face_id;
 };
 
-// `vr` / `ni` are the winner's face record (frec[2 fid], frec[2 fid + 1]), prefetched by the
-// caller's software pipeline whenever resolve_prefetch() says they are needed.
+// Does the winner stored in `key` get shaded (mask = 255, rasterizer.cc:254-266)?  False for EMPTY
+// pixels, culled back-face winners (rasterizer.cc:248-252) and face 0 (sic).
+__device__ __forceinline__ bool key_shaded(unsigned long long key, bool cull) {
+  if (key == kVisEmpty) return false;
+  const unsigned low = (unsigned)(key & 0xFFFFFFFFull);
+  return !((cull && (low & 1u)) || (low >> 1) == 0u);
+}
+
+// The resolve kernel is compiled per (COLOR, NMODE) so that each instantiation carries only the
+// gathers and registers of its own attribute path:
+//   COLOR 0  no interpolated colour (white, or colour not requested)   pixel_shader.h:222-230
+//         1  texture (nearest / bilinear chosen at run time)           pixel_shader.h:260-359
+//         2  vertex colour                                              pixel_shader.h:234-256
+//   NMODE 0  no normal needed (no normal output, no shading)
+//         1  face normals                                               rasterizer.cc:268-270
+//         2  vertex normals through normal_indices                      rasterizer.cc:271-279
+//         3  vertex normals from the merged per-vertex records (normal_indices == vertex_indices)
+template <int COLOR, int NMODE>
+struct ResolveTraits {
+  static constexpr bool kWeights = (NMODE >= 2) || (COLOR != 0);  // needs the winner's barycentrics
+  static constexpr bool kNi = NMODE == 2;
+  static constexpr bool kUv = COLOR == 1;
+};
+
+// Per-lane state that travels down the software pipeline with a pixel chunk.
+template <int COLOR, int NMODE>
+struct ResolveStage {
+  unsigned long long key;
+  int4 vr;            // vertex indices + material id          (stage 2, from frec)
+  int4 ni;            // normal indices                         (stage 2, NMODE 2)
+  int4 ui;            // uv indices                             (stage 2, COLOR 1)
+  float4 p0, p1, p2;  // projected vertices of the winner       (stage 3)
+  float2 t0, t1, t2;  // uv of the winner's corners             (stage 3, COLOR 1)
+};
+
+// Stage 1: the packed key of pixel chunk*32 + lane (EMPTY outside the image).  Loads are only
+// ISSUED by the stage functions; nothing consumes the values before the next loop iteration.
+__device__ __forceinline__ unsigned long long resolve_load_key(const FrameDev& fr, unsigned chunk,
+                                                               unsigned nchunks, unsigned lane,
+                                                               unsigned P) {
+  unsigned long long key = kVisEmpty;
+  if (chunk < nchunks) {
+    const unsigned p = chunk * 32u + lane;
+    if (p < P) key = fr.vis[p];
+  }
+  return key;
+}
+
+// Stage 2: the winner's face record (and uv indices), indexed by the face id in the key.
+template <int COLOR, int NMODE>
+__device__ __forceinline__ void resolve_stage2(const MeshDev& m, bool cull, ResolveStage<COLOR, NMODE>& s) {
+  using T = ResolveTraits<COLOR, NMODE>;
+  if (!T::kWeights) return;
+  s.vr = make_int4(0, 0, 0, 0);
+  if (T::kNi) s.ni = make_int4(0, 0, 0, 0);
+  if (T::kUv) s.ui = make_int4(0, 0, 0, 0);
+  if (!key_shaded(s.key, cull)) return;
+  const unsigned fid = (unsigned)(s.key & 0xFFFFFFFFull) >> 1;
+  const int4* rec = m.frec + 2 * (size_t)fid;
+  if (T::kNi) {
+    float4 lo, hi;
+    ldg256(rec, lo, hi);
+    s.vr = make_int4(__float_as_int(lo.x), __float_as_int(lo.y), __float_as_int(lo.z), __float_as_int(lo.w));
+    s.ni = make_int4(__float_as_int(hi.x), __float_as_int(hi.y), __float_as_int(hi.z), __float_as_int(hi.w));
+  } else {
+    s.vr = __ldg(rec);
+  }
+  if (T::kUv) s.ui = __ldg(m.uvidx + fid);
+}
+
+// Stage 3: the winner's projected vertices (per-view data: plain loads) and corner uvs.
+template <int COLOR, int NMODE>
+__device__ __forceinline__ void resolve_stage3(const MeshDev& m, const FrameDev& fr, bool cull,
+                                               ResolveStage<COLOR, NMODE>& s) {
+  using T = ResolveTraits<COLOR, NMODE>;
+  if (!T::kWeights) return;
+  s.p0 = s.p1 = s.p2 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (T::kUv) s.t0 = s.t1 = s.t2 = make_float2(0.f, 0.f);
+  if (!key_shaded(s.key, cull)) return;
+  s.p0 = fr.proj[s.vr.x];
+  s.p1 = fr.proj[s.vr.y];
+  s.p2 = fr.proj[s.vr.z];
+  if (T::kUv) {
+    s.t0 = __ldg(m.uv2 + s.ui.x);
+    s.t1 = __ldg(m.uv2 + s.ui.y);
+    s.t2 = __ldg(m.uv2 + s.ui.z);
+  }
+}
+
+// Stage 4: everything else of rasterizer.cc:244-301 for one pixel.
+template <int COLOR, int NMODE>
 __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDev& m,
                                               const FrameDev& fr, const ShadeParams& sp,
-                                              unsigned long long key, const int4& vr, const int4& ni,
-                                              int x, int y, PixelOut& o) {
+                                              const ResolveStage<COLOR, NMODE>& s, int x, int y,
+                                              PixelOut& o) {
+  using T = ResolveTraits<COLOR, NMODE>;
   o.color = 0u;
   o.depth = 0.0f;
   o.nx = o.ny = o.nz = 0.0f;
   o.mask = false;
   o.face_id = -1;
+  const unsigned long long key = s.key;
   if (key == kVisEmpty) return;
   const unsigned low = (unsigned)(key & 0xFFFFFFFFull);
   const int fid = (int)(low >> 1);
@@ -697,48 +807,44 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   const bool need_color = sp.color != nullptr;
   const bool need_normal = sp.normal != nullptr;
   const bool shade = need_color && sp.diffuse_shading != 0;
-  const bool need_nrm = need_normal || shade;
-  const bool need_weights =
-      (sp.shading_normal == 1 && need_nrm) || (need_color && sp.diffuse_color != 0);
-  if (!need_nrm && !need_color) return;
+  if (NMODE == 0 && !need_color) return;
+
+  // attribute gathers first: they are in flight while the weights are recomputed
+  float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
+  float4 c0 = n0, c1 = n0, c2 = n0;
+  float nwx = 0.f, nwy = 0.f, nwz = 0.f;
+  if (NMODE == 1) {
+    nwx = __ldg(m.fn_x + fid);
+    nwy = __ldg(m.fn_y + fid);
+    nwz = __ldg(m.fn_z + fid);
+  } else if (NMODE == 2) {
+    n0 = __ldg(m.nrm4 + s.ni.x);
+    n1 = __ldg(m.nrm4 + s.ni.y);
+    n2 = __ldg(m.nrm4 + s.ni.z);
+  } else if (NMODE == 3) {  // merged vertex records deliver the colours together with the normals
+    ldg256(m.vattr + 2 * (size_t)s.vr.x, n0, c0);
+    ldg256(m.vattr + 2 * (size_t)s.vr.y, n1, c1);
+    ldg256(m.vattr + 2 * (size_t)s.vr.z, n2, c2);
+  }
+  if (COLOR == 2 && NMODE != 3 && need_color) {
+    c0 = __ldg(m.col4 + s.vr.x);
+    c1 = __ldg(m.col4 + s.vr.y);
+    c2 = __ldg(m.col4 + s.vr.z);
+  }
 
   float w0 = 0.f, w1 = 0.f, w2 = 0.f;
-  int i0 = 0, i1 = 0, i2 = 0, mat = 0;
-  if (need_weights) {
-    i0 = vr.x; i1 = vr.y; i2 = vr.z; mat = vr.w;
+  if (T::kWeights) {  // recomputed bit-identically to the raster kernels (no weight image)
     Tri t;
-    tri_setup(t, fr.proj[i0], fr.proj[i1], fr.proj[i2]);
+    tri_setup(t, s.p0, s.p1, s.p2);
     tri_edges(t, (float)x, (float)y, w0, w1, w2);
     (void)tri_depth(t, w0, w1, w2);
   }
-
-  // shading normal (rasterizer.cc:268-279)
-  float nwx = 0.f, nwy = 0.f, nwz = 0.f;
-  float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0, c2 = c0;
-  // merged vertex records deliver the colours together with the normals
-  const bool merged = m.vattr != nullptr && sp.shading_normal == 1 && need_nrm;
-  if (need_nrm) {
-    if (sp.shading_normal == 0) {
-      nwx = __ldg(m.fn_x + fid);
-      nwy = __ldg(m.fn_y + fid);
-      nwz = __ldg(m.fn_z + fid);
-    } else if (sp.shading_normal == 1) {
-      float4 n0, n1, n2;
-      if (merged) {
-        ldg256(m.vattr + 2 * (size_t)i0, n0, c0);
-        ldg256(m.vattr + 2 * (size_t)i1, n1, c1);
-        ldg256(m.vattr + 2 * (size_t)i2, n2, c2);
-      } else {
-        n0 = __ldg(m.nrm4 + ni.x);
-        n1 = __ldg(m.nrm4 + ni.y);
-        n2 = __ldg(m.nrm4 + ni.z);
-      }
-      nwx = (w0 * n0.x + w1 * n1.x) + w2 * n2.x;
-      nwy = (w0 * n0.y + w1 * n1.y) + w2 * n2.y;
-      nwz = (w0 * n0.z + w1 * n1.z) + w2 * n2.z;
-    }
+  if (NMODE >= 2) {  // rasterizer.cc:271-279
+    nwx = (w0 * n0.x + w1 * n1.x) + w2 * n2.x;
+    nwy = (w0 * n0.y + w1 * n1.y) + w2 * n2.y;
+    nwz = (w0 * n0.z + w1 * n1.z) + w2 * n2.z;
   }
-  if (need_normal) {  // rasterizer.cc:281-289
+  if (NMODE != 0 && need_normal) {  // rasterizer.cc:281-289
     o.nx = dot3(vp.w2c_R[0], vp.w2c_R[1], vp.w2c_R[2], nwx, nwy, nwz);
     o.ny = dot3(vp.w2c_R[3], vp.w2c_R[4], vp.w2c_R[5], nwx, nwy, nwz);
     o.nz = dot3(vp.w2c_R[6], vp.w2c_R[7], vp.w2c_R[8], nwx, nwy, nwz);
@@ -747,26 +853,18 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
 
   unsigned cr = 255u, cg = 255u, cb = 255u;  // DiffuseDefaultColorizer
   const float u = w1, v = w2;
-  if (sp.diffuse_color == 2) {  // DiffuseVertexColorColorizer (pixel_shader.h:234-256)
-    if (!merged) {
-      c0 = __ldg(m.col4 + i0);
-      c1 = __ldg(m.col4 + i1);
-      c2 = __ldg(m.col4 + i2);
-    }
+  if (COLOR == 2) {  // DiffuseVertexColorColorizer (pixel_shader.h:234-256)
     const float k0 = 1.0f - u - v;
     cr = f2u8((k0 * c0.x + u * c1.x) + v * c2.x);
     cg = f2u8((k0 * c0.y + u * c1.y) + v * c2.y);
     cb = f2u8((k0 * c0.z + u * c1.z) + v * c2.z);
-  } else if (sp.diffuse_color == 1) {  // texture colourizers (pixel_shader.h:260-359)
-    const int4 ui = __ldg(m.uvidx + fid);
-    const float2 t0 = __ldg(m.uv2 + ui.x);
-    const float2 t1 = __ldg(m.uv2 + ui.y);
-    const float2 t2 = __ldg(m.uv2 + ui.z);
+  } else if (COLOR == 1) {  // texture colourizers (pixel_shader.h:260-359)
+    const int mat = s.vr.w;
     const uchar4* tex = m.tex[mat];
     const int2 ts = m.tex_size[mat];
     const float k0 = 1.0f - u - v;
-    const float iu = (k0 * t0.x + u * t1.x) + v * t2.x;
-    const float iv = (k0 * t0.y + u * t1.y) + v * t2.y;
+    const float iu = (k0 * s.t0.x + u * s.t1.x) + v * s.t2.x;
+    const float iv = (k0 * s.t0.y + u * s.t1.y) + v * s.t2.y;
     const float tx = iu * (float)(ts.x - 1);
     const float ty = (1.0f - iv) * (float)(ts.y - 1);
     if (sp.interp == 0) {
@@ -786,7 +884,7 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
       cb = f2u8(((k00 * a.z + k10 * b.z) + k01 * c.z) + k11 * d.z);
     }
   }
-  if (shade) {
+  if (NMODE != 0 && shade) {
     float r0, r1, r2;  // light_dir == ray_w (rasterizer.cc:291-298)
     ray_world(vp, fr.ray_dx[x], fr.ray_dy[y], r0, r1, r2);
     float coeff;
@@ -811,44 +909,14 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   o.color = cr | (cg << 8) | (cb << 16);
 }
 
-// Pipeline stage 1: the packed key of pixel chunk*32 + lane (EMPTY outside the image).  The load is
-// only ISSUED here; nothing may consume the value before the next loop iteration.
-__device__ __forceinline__ unsigned long long resolve_load_key(const FrameDev& fr, unsigned chunk,
-                                                               unsigned nchunks, unsigned lane,
-                                                               unsigned P) {
-  unsigned long long key = kVisEmpty;
-  if (chunk < nchunks) {
-    const unsigned p = chunk * 32u + lane;
-    if (p < P) key = fr.vis[p];
-  }
-  return key;
-}
-
-// Pipeline stage 2: the winner's face record, when the pixel will be shaded and needs it.
-__device__ __forceinline__ void resolve_prefetch(const MeshDev& m, unsigned long long key, bool cull,
-                                                 bool need_vr, bool need_ni, int4& vr, int4& ni) {
-  vr = make_int4(0, 0, 0, 0);
-  ni = make_int4(0, 0, 0, 0);
-  if (key == kVisEmpty) return;
-  const unsigned low = (unsigned)(key & 0xFFFFFFFFull);
-  if ((cull && (low & 1u)) || (low >> 1) == 0u) return;
-  const int4* rec = m.frec + 2 * (size_t)(low >> 1);
-  if (need_ni) {
-    float4 lo, hi;
-    ldg256(rec, lo, hi);
-    vr = make_int4(__float_as_int(lo.x), __float_as_int(lo.y), __float_as_int(lo.z), __float_as_int(lo.w));
-    ni = make_int4(__float_as_int(hi.x), __float_as_int(hi.y), __float_as_int(hi.z), __float_as_int(hi.w));
-  } else if (need_vr) {
-    vr = __ldg(rec);
-  }
-}
-
-// Persistent grid: warp w resolves the 32-pixel chunks w, w + nwarps, ... with a two-deep software
-// pipeline (key of chunk i+2 and face record of chunk i+1 are in flight while chunk i gathers,
-// shades and stores), so the dependent-load chain key -> face record -> vertex attributes costs one
-// exposed round trip per chunk instead of three.
-__global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, const MeshDev m,
-                                                         const FrameDev fr, const ShadeParams sp) {
+// Persistent grid: warp w resolves the 32-pixel chunks w, w + nwarps, ... through a four-stage
+// software pipeline.  While chunk i gathers its vertex attributes, shades and stores, the projected
+// vertices (and uvs) of chunk i+1, the face record of chunk i+2 and the key of chunk i+3 are in
+// flight, so of the dependent chain key -> face record -> projected vertices / attributes -> texels
+// only the last links are exposed, and those overlap the weight arithmetic of the same chunk.
+template <int COLOR, int NMODE, int MINB, bool DEEP>
+__global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewParams vp, const MeshDev m,
+                                                            const FrameDev fr, const ShadeParams sp) {
   __shared__ __align__(16) float s_n[8][96];
   __shared__ __align__(16) unsigned char s_c[8][96];
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;  // W*H < 2^31 is validated by the host
@@ -867,26 +935,27 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
     fr.counters[2] = 0ull;
   }
   const bool cull = sp.backface_culling != 0;
-  const bool need_color = sp.color != nullptr;
-  const bool need_nrm = sp.normal != nullptr || (need_color && sp.diffuse_shading != 0);
-  const bool need_ni = sp.shading_normal == 1 && need_nrm;
-  const bool need_vr = need_ni || (need_color && sp.diffuse_color != 0);
+  using Stage = ResolveStage<COLOR, NMODE>;
 
   unsigned chunk = blockIdx.x * 8u + warp;
-  unsigned long long key_a = resolve_load_key(fr, chunk, nchunks, lane, P);
-  unsigned long long key_b = resolve_load_key(fr, chunk + nwarps, nchunks, lane, P);
-  int4 vr_a, ni_a;
-  resolve_prefetch(m, key_a, cull, need_vr, need_ni, vr_a, ni_a);
+  Stage a{}, b{}, c{};  // chunk, chunk + nwarps, chunk + 2 nwarps
+  a.key = resolve_load_key(fr, chunk, nchunks, lane, P);
+  b.key = resolve_load_key(fr, chunk + nwarps, nchunks, lane, P);
+  c.key = resolve_load_key(fr, chunk + 2u * nwarps, nchunks, lane, P);
+  resolve_stage2(m, cull, a);
+  resolve_stage2(m, cull, b);
+  if (DEEP) resolve_stage3(m, fr, cull, a);
   for (; chunk < nchunks; chunk += nwarps) {
-    const unsigned long long key_c = resolve_load_key(fr, chunk + 2u * nwarps, nchunks, lane, P);
-    int4 vr_b, ni_b;
-    resolve_prefetch(m, key_b, cull, need_vr, need_ni, vr_b, ni_b);
+    const unsigned long long key_d = resolve_load_key(fr, chunk + 3u * nwarps, nchunks, lane, P);
+    resolve_stage2(m, cull, c);
+    if (DEEP) resolve_stage3(m, fr, cull, b);
+    else resolve_stage3(m, fr, cull, a);
 
     const unsigned wbase = chunk * 32u;  // first pixel of this chunk
     const unsigned p = wbase + lane;
     const unsigned y = (vp.W == 1) ? p : (__umulhi(p, vp.w_magic) >> vp.w_shift);
     const unsigned x = p - y * (unsigned)vp.W;
-    if (wbase + 32u <= P && __all_sync(0xffffffffu, key_a == kVisEmpty)) {
+    if (wbase + 32u <= P && __all_sync(0xffffffffu, a.key == kVisEmpty)) {
       // Nothing landed on these 32 pixels (most of a typical frame): write the cleared values
       // (util_private.cc:72-87) with full-width stores and move on.
       if (sp.depth) sp.depth[p] = 0.0f;
@@ -896,15 +965,14 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
         reinterpret_cast<float4*>(sp.normal + (size_t)wbase * 3u)[lane] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (sp.color && lane < 6u)
         reinterpret_cast<uint4*>(sp.color + (size_t)wbase * 3u)[lane] = make_uint4(0u, 0u, 0u, 0u);
-      key_a = key_b;
-      vr_a = vr_b;
-      ni_a = ni_b;
-      key_b = key_c;
+      a = b;
+      b = c;
+      c.key = key_d;
       continue;
     }
-    if (key_a != kVisEmpty) fr.vis[p] = kVisEmpty;  // leave the buffer EMPTY for the next view
+    if (a.key != kVisEmpty) fr.vis[p] = kVisEmpty;  // leave the buffer EMPTY for the next view
     PixelOut o;
-    resolve_pixel(vp, m, fr, sp, key_a, vr_a, ni_a, (int)x, (int)y, o);
+    resolve_pixel<COLOR, NMODE>(vp, m, fr, sp, a, (int)x, (int)y, o);
 
     if (wbase + 32u <= P) {
       if (sp.depth) sp.depth[p] = o.depth;
@@ -913,8 +981,8 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
         const unsigned bal = __ballot_sync(0xffffffffu, o.mask);
         if (lane < 8u) {
           // nibble -> 4 bytes of 0x00 / 0xFF
-          const unsigned b = (bal >> (lane * 4u)) & 15u;
-          const unsigned word = ((b * 0x00204081u) & 0x01010101u) * 0xFFu;
+          const unsigned nb = (bal >> (lane * 4u)) & 15u;
+          const unsigned word = ((nb * 0x00204081u) & 0x01010101u) * 0xFFu;
           *reinterpret_cast<unsigned*>(sp.mask + wbase + lane * 4u) = word;
         }
       }
@@ -951,10 +1019,9 @@ __global__ void __launch_bounds__(256, 4) resolve_kernel(const ViewParams vp, co
       if (sp.mask) sp.mask[p] = o.mask ? 255 : 0;
       if (sp.face_id) sp.face_id[p] = o.face_id;
     }
-    key_a = key_b;
-    vr_a = vr_b;
-    ni_a = ni_b;
-    key_b = key_c;
+    a = b;
+    b = c;
+    c.key = key_d;
   }
 }
 
