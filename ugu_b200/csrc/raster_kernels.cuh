@@ -590,8 +590,14 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
   const unsigned lane = threadIdx.x & 31u;
   const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
   const unsigned long long gw = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  unsigned long long per = (T + nwarps - 1) / nwarps;  // jobs per chunk: 2 .. kJobsPerChunk
-  per = per < 2ull ? 2ull : (per > (unsigned long long)kJobsPerChunk ? (unsigned long long)kJobsPerChunk : per);
+  // Jobs per chunk: every warp makes `rounds` passes over interleaved chunks of at most
+  // kJobsPerChunk jobs, sized so that the chunk count is (just under) a multiple of the warp count
+  // — with a fixed chunk size a job count slightly above nwarps * kJobsPerChunk would hand a few
+  // warps twice the work of the others.
+  const unsigned long long rounds =
+      (T + nwarps * (unsigned long long)kJobsPerChunk - 1) / (nwarps * (unsigned long long)kJobsPerChunk);
+  unsigned long long per = (T + nwarps * rounds - 1) / (nwarps * rounds);
+  per = per < 2ull ? 2ull : per;
   const unsigned long long nchunks = (T + per - 1) / per;
   const bool has_fn = m.num_face_normals > 0;
   const int lx = (int)(lane & (kJobW - 1)), ly = (int)(lane >> 3);
@@ -634,9 +640,13 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const 
       int x0, y0, x1, y1;
       tri_bounds(t, vp, x0, y0, x1, y1);  // queued triangles always pass
       const unsigned ntx = (unsigned)((x1 - x0 + kJobW) / kJobW);
-      for (unsigned long long jj = j; jj < jend; ++jj) {
-        const unsigned local = (unsigned)(jj - js);
-        const unsigned ty = local / ntx, tx = local - ty * ntx;
+      // tile coordinates of the first job, then stepped (one integer division per triangle, not per job)
+      unsigned ty = (unsigned)(j - js) / ntx, tx = (unsigned)(j - js) - ty * ntx;
+      for (unsigned long long jj = j; jj < jend; ++jj, ++tx) {
+        if (tx == ntx) {
+          tx = 0u;
+          ++ty;
+        }
         const int x = x0 + (int)tx * kJobW + lx;
         const int y = y0 + (int)ty * kJobH + ly;
         if (x <= x1 && y <= y1) {
