@@ -308,6 +308,10 @@ def main():
         stage_ms = {k: v / max(1, st["timed_views"]) for k, v in st["stage_ms"].items()}
         dom = max(stage_ms, key=lambda k: stage_ms[k])
         achieved = kbytes[dom] / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
+        try:   # DRAM bytes per launch of each kernel from the committed ncu --set full capture
+            traffic = json.loads((REPO / "profiles" / "traffic.json").read_text())
+        except Exception:
+            traffic = {}
         ms_per_step = dev_ms_max / K
         value = world * P * K / (dev_ms_max * 1e-3) / 1e6
         e2e_value = world * P * Ke / (e2e_ms_max * 1e-3) / 1e6
@@ -330,7 +334,8 @@ def main():
             "stage_us": {k: round(v * 1e3, 2) for k, v in stage_ms.items()},
             "ms_per_step_stage_timed_pass": prof_ms / K,
             "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic.get(dom + "_kernel"),
+                         "traffic_source": traffic.get("source"),
                          "algorithmic_bytes_per_launch": kbytes[dom], "peak_source": peak_src,
                          "view": {"algorithmic_bytes": view_bytes,
                                   "achieved": view_bytes / (ms_per_step * 1e-3) / 1e9,
