@@ -295,6 +295,19 @@ def main():
     st_e = r.stats()
     barrier()
     clocks = sampler.stop()
+    # context for e2e: the host link.  One pinned D2H copy of the same number of bytes a view returns.
+    d2h_bytes = P * 24
+    link_src = torch.empty(d2h_bytes, dtype=torch.uint8, device="cuda")
+    link_dst = torch.empty(d2h_bytes, dtype=torch.uint8, pin_memory=True)
+    link_dst.copy_(link_src, non_blocking=True)
+    torch.cuda.synchronize()
+    le0, le1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    le0.record()
+    for _ in range(10):
+        link_dst.copy_(link_src, non_blocking=True)
+    le1.record()
+    torch.cuda.synchronize()
+    link_ms = le0.elapsed_time(le1) / 10
 
     # ---- max over ranks ---------------------------------------------------------------------------
     t = torch.tensor([dev_ms, e2e_t * 1e3], dtype=torch.float64, device="cuda")
@@ -329,7 +342,10 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": e2e_ms_max / Ke, "steps": Ke,
                     "h2d_bytes_per_step": int(st_e["h2d_bytes"] // max(1, st_e["views"])),
                     "d2h_bytes_per_step": int(st_e["d2h_bytes"] // max(1, st_e["views"])),
-                    "api": "ugu_b200.Rasterizer.Render -> ugu_b200_rasterizer_render, pinned host images"},
+                    "api": "ugu_b200.Rasterizer.Render -> ugu_b200_rasterizer_render, pinned host images",
+                    "host_link": {"pinned_d2h_gbs": d2h_bytes / (link_ms * 1e-3) / 1e9,
+                                  "ms_for_one_view_of_outputs": link_ms,
+                                  "note": "a view returns 24 B/pixel; e2e is bounded by this copy"}},
             "gpu_launches": int(launches),
             "stage_us": {k: round(v * 1e3, 2) for k, v in stage_ms.items()},
             "ms_per_step_stage_timed_pass": prof_ms / K,
