@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 1
+#define UGU_B200_ABI_VERSION 2
 
 enum {
   UGU_B200_OK = 0,
@@ -163,6 +163,23 @@ int ugu_b200_rasterizer_sync(ugu_b200_rasterizer* r);
 /* Rasterizer::RenderW's depth conversion (rasterizer.cc:329-344 + ConvertTo, image_proc.h:453-460):
  * truncating f32 -> u16 cast of a host depth image. */
 int ugu_b200_depth_to_u16(const float* depth, uint16_t* depth_w, size_t count);
+
+/* ugu::Depth2PointCloud(const Image1f& depth, const Camera&, Image3f* point_cloud, bool gl_coord)
+ * (src/util/rgbd_util.cc:472-513; PinholeCamera::Unproject, include/ugu/camera.h:406-413) — the step
+ * examples/ex02_renderer.cc:156-158 runs on the rendered depth.  point_cloud is W*H*3 f32 in
+ * ugu::Image3f layout, camera space.  The reference writes only pixels with depth >= FLT_MIN and
+ * leaves the others as they were: `zero_invalid` = 0 keeps that behaviour (the buffer is in/out),
+ * 1 writes zeros there (what a freshly Init()-ed image holds; saves the upload of the old image).
+ * Only size and intrinsics of `cam` are used.
+ * _device: depth / point_cloud are 16-byte aligned DEVICE pointers (e.g. the depth output of
+ * render_device), asynchronous on `stream`.  The host form copies in, runs, copies out, returns
+ * when the image is complete. */
+int ugu_b200_depth_to_point_cloud_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                         const float* depth_dev, float* point_cloud_dev,
+                                         int32_t gl_coord, int32_t zero_invalid, void* stream);
+int ugu_b200_depth_to_point_cloud(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                  const float* depth_host, float* point_cloud_host, int32_t gl_coord,
+                                  int32_t zero_invalid);
 
 /* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
 int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);

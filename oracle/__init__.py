@@ -152,6 +152,40 @@ class OraclePort:
         return out
 
 
+def port_depth2pointcloud(cam_pod, depth, point_cloud=None, gl_coord=False):
+    """Plain-C restatement of ugu::Depth2PointCloud (organized Image3f form, rgbd_util.cc:472-513).
+    `point_cloud` (H, W, 3) is the in/out image; None = a zero image."""
+    build_port()
+    lib = C.CDLL(str(PORT_LIB))
+    lib.oracle_depth2pointcloud.restype = C.c_int
+    lib.oracle_depth2pointcloud.argtypes = [C.POINTER(_PortCamera), C.c_void_p, C.c_void_p, C.c_int]
+    cam = _PortCamera()
+    for name, _ in _PortCamera._fields_:
+        setattr(cam, name, getattr(cam_pod, name))
+    d = np.ascontiguousarray(depth, np.float32)
+    pc = np.zeros((cam.height, cam.width, 3), np.float32) if point_cloud is None else \
+        np.array(point_cloud, np.float32, copy=True, order="C")
+    rc = lib.oracle_depth2pointcloud(C.byref(cam), d.ctypes.data, pc.ctypes.data, 1 if gl_coord else 0)
+    return pc if rc == 0 else None
+
+
+def ref_depth2pointcloud(camera, depth, point_cloud=None, gl_coord=False):
+    """The compiled reference's ugu::Depth2PointCloud through oracle/_ref."""
+    lib = C.CDLL(str(REF_LIB))
+    lib.ugu_ref_depth2pointcloud.restype = C.c_int
+    lib.ugu_ref_depth2pointcloud.argtypes = [C.POINTER(_RefCamera), C.c_void_p, C.c_void_p, C.c_int]
+    cam = _RefCamera()
+    cam.width, cam.height = camera.width(), camera.height()
+    cam.fx, cam.fy = float(camera.focal_length()[0]), float(camera.focal_length()[1])
+    cam.cx, cam.cy = float(camera.principal_point()[0]), float(camera.principal_point()[1])
+    cam.c2w = (C.c_double * 16)(*np.asarray(camera.c2w(), np.float64).reshape(-1))
+    d = np.ascontiguousarray(depth, np.float32)
+    pc = np.zeros((cam.height, cam.width, 3), np.float32) if point_cloud is None else \
+        np.array(point_cloud, np.float32, copy=True, order="C")
+    rc = lib.ugu_ref_depth2pointcloud(C.byref(cam), d.ctypes.data, pc.ctypes.data, 1 if gl_coord else 0)
+    return pc if rc == 0 else None
+
+
 class OracleRef:
     """The compiled, unmodified reference ugu::Rasterizer (present only where oracle/_ref was built)."""
 

@@ -361,4 +361,30 @@ int oracle_render(const OracleMesh* mesh, const OracleCamera* cam, const OracleO
   return 0;
 }
 
-int oracle_abi_version(void) { return 1; }
+/* ugu::Depth2PointCloud(const Image1f&, const Camera&, Image3f*, bool) — src/util/rgbd_util.cc:472-513
+ * with PinholeCamera::Unproject, include/ugu/camera.h:406-413:
+ *   camera_p = ((x - cx) * d / fx, (y - cy) * d / fy, d), y and z negated when gl_coord.
+ * Pixels with d < FLT_MIN are left untouched (pc is in/out), as the reference does. */
+int oracle_depth2pointcloud(const OracleCamera* cam, const float* depth, float* pc, int gl_coord) {
+  if (!cam || !depth || !pc) return 1;
+  for (int y = 0; y < cam->height; y++) {
+    for (int x = 0; x < cam->width; x++) {
+      const size_t p = (size_t)y * (size_t)cam->width + (size_t)x;
+      const float d = depth[p];
+      if (d < FLT_MIN) continue;
+      float cx_ = ((float)x - cam->cx) * d / cam->fx;
+      float cy_ = ((float)y - cam->cy) * d / cam->fy;
+      float cz_ = d;
+      if (gl_coord) {
+        cy_ = -cy_;
+        cz_ = -cz_;
+      }
+      pc[p * 3 + 0] = cx_;
+      pc[p * 3 + 1] = cy_;
+      pc[p * 3 + 2] = cz_;
+    }
+  }
+  return 0;
+}
+
+int oracle_abi_version(void) { return 2; }

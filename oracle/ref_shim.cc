@@ -19,6 +19,7 @@
 #include "ugu/log.h"
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/util/rgbd_util.h"
 
 extern "C" {
 
@@ -225,6 +226,25 @@ int ugu_ref_lookat_c2w(const float* eye, const float* center, const float* up, d
            Eigen::Vector3f(up[0], up[1], up[2]), &m);
   for (int r = 0; r < 4; r++)
     for (int c = 0; c < 4; c++) c2w16[r * 4 + c] = static_cast<double>(m(r, c));
+  return 0;
+}
+
+// ugu::Depth2PointCloud(const Image1f&, const Camera&, Image3f*, bool gl_coord)
+// (src/util/rgbd_util.cc:472-513), the step ex02 runs on the rendered depth
+// (examples/ex02_renderer.cc:156-158).  `pc` (W*H*3 floats) is IN/OUT: the reference only writes
+// pixels whose depth is >= FLT_MIN and leaves the others as they were.
+int ugu_ref_depth2pointcloud(const UguRefCamera* cam, const float* depth, float* pc, int gl_coord) {
+  ugu::PinholeCamera camera(cam->width, cam->height, ToAffine(cam->c2w),
+                            Eigen::Vector2f(cam->cx, cam->cy), Eigen::Vector2f(cam->fx, cam->fy));
+  const size_t P = static_cast<size_t>(cam->width) * cam->height;
+  ugu::Image1f d;
+  ugu::Image3f out;
+  ugu::Init(&d, cam->width, cam->height, 0.0f);
+  ugu::Init(&out, cam->width, cam->height, 0.0f);
+  std::memcpy(d.data, depth, P * 4);
+  std::memcpy(out.data, pc, P * 12);
+  if (!ugu::Depth2PointCloud(d, camera, &out, gl_coord != 0)) return 1;
+  std::memcpy(pc, out.data, P * 12);
   return 0;
 }
 

@@ -61,6 +61,13 @@ def camera_from_arrays(d) -> PinholeCamera:
                          principal_point=d["cam_pp"], focal_length=d["cam_f"])
 
 
+def pointcloud_prev(shape) -> np.ndarray:
+    """The deterministic non-zero "previous contents" of the in/out point-cloud image used by the
+    Depth2PointCloud fixtures (tests/golden/make_golden_pointcloud.py)."""
+    n = int(shape[0]) * int(shape[1]) * 3
+    return ((np.arange(n) % 7) + 1).astype(np.float32).reshape(int(shape[0]), int(shape[1]), 3)
+
+
 def load_spot() -> Mesh:
     """data/spot (2930 v / 5856 f / 1024^2 texture) as loaded by the reference's own
     Mesh::LoadObj, frozen into tests/golden/spot_mesh.npz by make_golden.py."""

@@ -65,6 +65,10 @@ SYMBOLS = {
                                                    C.POINTER(Outputs), C.c_int32, C.c_void_p]),
     "ugu_b200_rasterizer_sync": (C.c_int, [C.c_void_p]),
     "ugu_b200_depth_to_u16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "ugu_b200_depth_to_point_cloud_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p,
+                                                       C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "ugu_b200_depth_to_point_cloud": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p,
+                                                C.c_int32, C.c_int32]),
     "ugu_b200_rasterizer_set_profiling": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint32]),
     "ugu_b200_rasterizer_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "ugu_b200_rasterizer_reset_stats": (C.c_int, [C.c_void_p]),
@@ -92,7 +96,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 1:
+    if lib.ugu_b200_abi_version() != 2:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

@@ -1043,6 +1043,56 @@ int ugu_b200_rasterizer_sync(ugu_b200_rasterizer* r) {
   return UGU_B200_OK;
 }
 
+int ugu_b200_depth_to_point_cloud_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                         const float* depth_dev, float* point_cloud_dev,
+                                         int32_t gl_coord, int32_t zero_invalid, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!cam || !depth_dev || !point_cloud_dev) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (cam->width <= 0 || cam->height <= 0 || cam->width > 65535 || cam->height > 65535 ||
+      (long long)cam->width * cam->height >= (1ll << 31))
+    return Fail(r, UGU_B200_E_INVALID, "camera size %dx%d is invalid", cam->width, cam->height);
+  if (((uintptr_t)depth_dev | (uintptr_t)point_cloud_dev) & 15u)
+    return Fail(r, UGU_B200_E_INVALID, "device buffers must be 16-byte aligned");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  ViewParams vp;
+  MakeViewParams(cam, &vp);
+  const size_t P = (size_t)cam->width * cam->height;
+  depth_to_point_cloud_kernel<<<Blocks((P + 3) / 4, 256), 256, 0, st>>>(vp, depth_dev, point_cloud_dev,
+                                                                         gl_coord, zero_invalid);
+  CU_TRY(r, cudaGetLastError());
+  r->stats.kernel_launches++;
+  return UGU_B200_OK;
+}
+
+int ugu_b200_depth_to_point_cloud(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                  const float* depth_host, float* point_cloud_host, int32_t gl_coord,
+                                  int32_t zero_invalid) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!cam || !depth_host || !point_cloud_host) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (cam->width <= 0 || cam->height <= 0)
+    return Fail(r, UGU_B200_E_INVALID, "camera size %dx%d is invalid", cam->width, cam->height);
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t P = (size_t)cam->width * cam->height;
+  int rc;
+  // the depth / normal output buffers of set 1 double as scratch (set 0 belongs to Render)
+  if ((rc = Grow(r, &r->out_depth[1], P * 4 + 16))) return rc;
+  if ((rc = Grow(r, &r->out_normal[1], P * 12 + 16))) return rc;
+  float* d_dev = (float*)r->out_depth[1].p;
+  float* pc_dev = (float*)r->out_normal[1].p;
+  CU_TRY(r, cudaMemcpyAsync(d_dev, depth_host, P * 4, cudaMemcpyHostToDevice, r->stream));
+  r->stats.h2d_bytes += P * 4;
+  if (!zero_invalid) {  // in/out semantics: the kernel must see what the image held
+    CU_TRY(r, cudaMemcpyAsync(pc_dev, point_cloud_host, P * 12, cudaMemcpyHostToDevice, r->stream));
+    r->stats.h2d_bytes += P * 12;
+  }
+  if ((rc = ugu_b200_depth_to_point_cloud_device(r, cam, d_dev, pc_dev, gl_coord, zero_invalid, r->stream)))
+    return rc;
+  std::vector<CopySeg> segs;
+  segs.push_back({point_cloud_host, pc_dev, P * 12});
+  return CopyOut(r, segs, r->stream);
+}
+
 int ugu_b200_depth_to_u16(const float* depth, uint16_t* depth_w, size_t count) {
   if (!depth || !depth_w) return Fail(nullptr, UGU_B200_E_INVALID, "NULL argument");
   // ConvertTo(f_depth, depth) with scale 1 (image_proc.h:453-460): static_cast<uint16_t>(float),

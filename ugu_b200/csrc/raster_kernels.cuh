@@ -1036,6 +1036,87 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewParams vp,
 }
 
 // ---------------------------------------------------------------------------------------------
+// K5: depth image -> organized point cloud, ugu::Depth2PointCloud(const Image1f&, const Camera&,
+// Image3f*, bool gl_coord) (src/util/rgbd_util.cc:472-513) with PinholeCamera::Unproject
+// (include/ugu/camera.h:406-413): camera_p = ((x - cx) * d / fx, (y - cy) * d / fy, d), y and z
+// negated for gl_coord.  Pixels with d < FLT_MIN are skipped by the reference (the output keeps what
+// it held); `zero_invalid` writes zeros there instead, which is what a freshly Init()-ed image
+// holds.  Streaming: 4 pixels per thread, one 16-byte load and three 16-byte stores.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float3 unproject_pixel(const ViewParams& vp, unsigned p, float d, bool gl) {
+  const unsigned y = (vp.W == 1) ? p : (__umulhi(p, vp.w_magic) >> vp.w_shift);
+  const unsigned x = p - y * (unsigned)vp.W;
+  float3 c;
+  c.x = ((float)x - vp.cx) * d / vp.fx;
+  c.y = ((float)y - vp.cy) * d / vp.fy;
+  c.z = d;
+  if (gl) {
+    c.y = -c.y;
+    c.z = -c.z;
+  }
+  return c;
+}
+
+__global__ void __launch_bounds__(256) depth_to_point_cloud_kernel(const ViewParams vp,
+                                                                   const float* __restrict__ depth,
+                                                                   float* __restrict__ pc, int gl_coord,
+                                                                   int zero_invalid) {
+  const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
+  const unsigned p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+  if (p0 >= P) return;
+  const bool gl = gl_coord != 0;
+  if (p0 + 4u <= P) {
+    const float4 d4 = *reinterpret_cast<const float4*>(depth + p0);
+    const float d[4] = {d4.x, d4.y, d4.z, d4.w};
+    bool valid[4];
+    bool all = true;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      valid[k] = !(d[k] < 1.17549435e-38f);
+      all = all && valid[k];
+    }
+    if (all || zero_invalid) {
+      float o[12];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        float3 c = make_float3(0.f, 0.f, 0.f);
+        if (valid[k]) c = unproject_pixel(vp, p0 + k, d[k], gl);
+        o[3 * k + 0] = c.x;
+        o[3 * k + 1] = c.y;
+        o[3 * k + 2] = c.z;
+      }
+      float4* dst = reinterpret_cast<float4*>(pc + (size_t)p0 * 3);
+      dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+      dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+      dst[2] = make_float4(o[8], o[9], o[10], o[11]);
+      return;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (!valid[k]) continue;
+      const float3 c = unproject_pixel(vp, p0 + k, d[k], gl);
+      float* q = pc + (size_t)(p0 + k) * 3;
+      q[0] = c.x;
+      q[1] = c.y;
+      q[2] = c.z;
+    }
+    return;
+  }
+  for (unsigned p = p0; p < P; p++) {  // ragged tail
+    const float d = depth[p];
+    float* q = pc + (size_t)p * 3;
+    if (d < 1.17549435e-38f) {
+      if (zero_invalid) q[0] = q[1] = q[2] = 0.f;
+      continue;
+    }
+    const float3 c = unproject_pixel(vp, p, d, gl);
+    q[0] = c.x;
+    q[1] = c.y;
+    q[2] = c.z;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // Upload-time repack kernels (AoS host layout -> device SoA / padded vectors).  Run once per mesh.
 // ---------------------------------------------------------------------------------------------
 __global__ void repack_vec3_to_planes(const float* __restrict__ aos, int n, float* __restrict__ px,

@@ -397,6 +397,39 @@ class Rasterizer:
     def RenderDepthW(self, depth: Image1w) -> bool:
         return self.RenderW(None, depth, None, None, None)
 
+    # -- the step after Render in examples/ex02_renderer.cc:156-158 --------------------------------
+    def Depth2PointCloud(self, depth: Image1f, camera: PinholeCamera, point_cloud: Image3f,
+                         gl_coord: bool = False) -> bool:
+        """ugu::Depth2PointCloud(const Image1f&, const Camera&, Image3f*, bool gl_coord)
+        (src/util/rgbd_util.cc:472-513): organized camera-space point cloud of a depth image.  Like
+        the reference, a point_cloud of another size is re-initialised to 0 and pixels with depth <
+        FLT_MIN are left as they were."""
+        if depth.cols != camera.width() or depth.rows != camera.height():
+            LOGE(f"Depth2PointCloud depth size ({depth.cols}, {depth.rows}) and camera size "
+                 f"({camera.width()}, {camera.height()}) are different")
+            return False
+        fresh = point_cloud.cols != depth.cols or point_cloud.rows != depth.rows
+        point_cloud._init(depth.cols, depth.rows)
+        cam = camera.to_native()
+        rc = self._lib.ugu_b200_depth_to_point_cloud(self._h, C.byref(cam), depth.data.ctypes.data,
+                                                     point_cloud.data.ctypes.data,
+                                                     1 if gl_coord else 0, 1 if fresh else 0)
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        return True
+
+    def depth_to_point_cloud_device(self, camera: PinholeCamera, depth: int, point_cloud: int,
+                                    gl_coord: bool = False, zero_invalid: bool = True,
+                                    stream: int = 0) -> None:
+        """Device-resident form: `depth` / `point_cloud` are raw 16-byte aligned device pointers."""
+        cam = camera.to_native() if isinstance(camera, PinholeCamera) else camera
+        rc = self._lib.ugu_b200_depth_to_point_cloud_device(
+            self._h, C.byref(cam), C.c_void_p(depth), C.c_void_p(point_cloud), 1 if gl_coord else 0,
+            1 if zero_invalid else 0, C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
     # -- device-resident / batch extensions (no reference counterpart; see INTEGRATION.md) --------
     def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
                       face_id=None, stream: int = 0) -> None:
