@@ -17,6 +17,7 @@
 #include "ugu/log.h"
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/util/rgbd_util.h"
 #include "ugu/util/camera_util.h"
 #include "ugu/util/geom_util.h"
 
@@ -177,6 +178,21 @@ int main(int argc, char** argv) {
     if (!ref->RenderFaceId(&f0) || !cuda->RenderFaceId(&f1) || CountDiff(f0, f1, 0)) failures++;
     if (!ref->RenderDepthW(&w0) || !cuda->RenderDepthW(&w1) || CountDiff(w0, w1, 0)) failures++;
     if (cuda->Render(nullptr, nullptr, nullptr, nullptr, nullptr)) failures++;  // all-null is an error
+    {  // the step after Render in ex02: Depth2PointCloud, reference vs CUDA, fresh and in/out images
+      ugu::Image1f dref;
+      if (!ref->RenderDepth(&dref)) failures++;
+      for (int gl = 0; gl < 2; gl++) {
+        ugu::Image3f p0, p1;
+        if (!ugu::Depth2PointCloud(dref, *camera, &p0, gl != 0)) failures++;
+        if (!static_cast<ugu::RasterizerCuda*>(cuda.get())->Depth2PointCloud(dref, *camera, &p1, gl != 0)) failures++;
+        if (CountDiff(p0, p1, 0)) failures++;
+        p0.setTo(ugu::Vec3f({1.f, 2.f, 3.f}));
+        p1.setTo(ugu::Vec3f({1.f, 2.f, 3.f}));
+        if (!ugu::Depth2PointCloud(dref, *camera, &p0, gl != 0)) failures++;
+        if (!static_cast<ugu::RasterizerCuda*>(cuda.get())->Depth2PointCloud(dref, *camera, &p1, gl != 0)) failures++;
+        if (CountDiff(p0, p1, 0)) failures++;
+      }
+    }
   }
   std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);
   return failures ? 1 : 0;

@@ -161,6 +161,40 @@ RasterizerCuda::RasterizerCuda(const RendererCpuOption& option, int device)
 }
 bool RasterizerCuda::valid() const { return pimpl_->handle_ != nullptr; }
 
+bool RasterizerCuda::Depth2PointCloud(const Image1f& depth, const Camera& camera, Image3f* point_cloud,
+                                      bool gl_coord) const {
+  if (pimpl_->handle_ == nullptr) {
+    LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
+    return false;
+  }
+  if (depth.cols != camera.width() || depth.rows != camera.height()) {  // rgbd_util.cc:474-480
+    LOGE("Depth2PointCloud depth size (%d, %d) and camera size (%d, %d) are different\n", depth.cols,
+         depth.rows, camera.width(), camera.height());
+    return false;
+  }
+  const auto* pin = dynamic_cast<const PinholeCamera*>(&camera);
+  if (pin == nullptr || dynamic_cast<const OpenCvCamera*>(&camera) != nullptr || point_cloud == nullptr) {
+    LOGE("RasterizerCuda::Depth2PointCloud supports PinholeCamera only\n");
+    return false;
+  }
+  const bool fresh = point_cloud->cols != depth.cols || point_cloud->rows != depth.rows;
+  if (fresh) Init(point_cloud, depth.cols, depth.rows, 0.0f);  // rgbd_util.cc:482-484
+  ugu_b200_camera c{};
+  c.width = camera.width();
+  c.height = camera.height();
+  c.fx = pin->focal_length().x();
+  c.fy = pin->focal_length().y();
+  c.cx = pin->principal_point().x();
+  c.cy = pin->principal_point().y();
+  if (ugu_b200_depth_to_point_cloud(pimpl_->handle_, &c, reinterpret_cast<const float*>(depth.data),
+                                    reinterpret_cast<float*>(point_cloud->data), gl_coord ? 1 : 0,
+                                    fresh ? 1 : 0) != UGU_B200_OK) {
+    LOGE("%s\n", ugu_b200_last_error(pimpl_->handle_));
+    return false;
+  }
+  return true;
+}
+
 void RasterizerCuda::set_option(const RendererCpuOption& option) {
   option.CopyTo(&pimpl_->option_);  // rasterizer.cc:73-75 (oren_nayar_sigma is not copied)
 }

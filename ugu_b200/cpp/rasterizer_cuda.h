@@ -41,6 +41,13 @@ class RasterizerCuda : public RendererCpu {
                Image1i* face_id) const override;
   bool RenderDepthW(Image1w* depth) const override;
 
+  // ugu::Depth2PointCloud(depth, camera, &point_cloud, gl_coord) (include/ugu/util/rgbd_util.h:17-18,
+  // src/util/rgbd_util.cc:472-513) on this renderer's device — the step examples/ex02_renderer.cc
+  // runs on the rendered depth.  Same contract: false on a size mismatch, point_cloud re-initialised
+  // to 0 when its size differs, pixels with depth < FLT_MIN left as they were.  Pinhole cameras only.
+  bool Depth2PointCloud(const Image1f& depth, const Camera& camera, Image3f* point_cloud,
+                        bool gl_coord = false) const;
+
   // false when the CUDA library could not create a rasterizer (no B200 / no driver).
   bool valid() const;
 };
