@@ -186,6 +186,69 @@ def ref_depth2pointcloud(camera, depth, point_cloud=None, gl_coord=False):
     return pc if rc == 0 else None
 
 
+def _uv_raster_call(lib, fn_name, attrs, attr_indices, uv, uv_indices, width, height, texture_type,
+                    texture, mask):
+    fn = getattr(lib, fn_name)
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_int32] * 4 + [C.c_void_p] * 4 + [C.c_int32] * 4 + [C.c_void_p] * 2
+    a = np.ascontiguousarray(attrs, np.float32).reshape(-1, 3)
+    ui = np.ascontiguousarray(uv_indices, np.int32).reshape(-1, 3)
+    u = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+    per_face = attr_indices is None
+    ai = None if per_face else np.ascontiguousarray(attr_indices, np.int32).reshape(-1, 3)
+    if ai is not None and len(ai) != len(ui):
+        return None  # raster_util.h:148-151
+    dt = np.uint8 if texture_type == 0 else np.float32
+    keep = texture is not None
+    tex = np.array(texture, dt, copy=True, order="C").reshape(height, width, 3) if keep else \
+        np.zeros((height, width, 3), dt)
+    m = None if mask is None else np.array(mask, np.uint8, copy=True, order="C").reshape(height, width)
+    rc = fn(len(a), len(ui), len(u), 1 if per_face else 0, a.ctypes.data,
+            None if ai is None else ai.ctypes.data, u.ctypes.data, ui.ctypes.data, width, height,
+            texture_type, 1 if keep else 0, tex.ctypes.data, None if m is None else m.ctypes.data)
+    return (tex, m) if rc == 0 else None
+
+
+def port_uv_raster(attrs, attr_indices, uv, uv_indices, width, height, texture_type=0, texture=None,
+                   mask=None):
+    """Plain-C restatement of ugu::RasterizeVertexAttributeToTexture (attr_indices given) /
+    RasterizeFaceAttributeToTexture (attr_indices None) with num_threads = 1
+    (raster_util.h:139-268).  texture_type 0 = Image3b, 1 = Image3f; `texture` not None = rasterise
+    over its contents (the reference's width/height <= 0 form); `mask` = in/out Image1b or None.
+    Returns (texture, mask) or None when the reference returns false."""
+    build_port()
+    return _uv_raster_call(C.CDLL(str(PORT_LIB)), "oracle_uv_raster", attrs, attr_indices, uv,
+                           uv_indices, width, height, texture_type, texture, mask)
+
+
+def ref_uv_raster(attrs, attr_indices, uv, uv_indices, width, height, texture_type=0, texture=None,
+                  mask=None):
+    """The compiled reference's templates through oracle/_ref (num_threads = 1)."""
+    return _uv_raster_call(C.CDLL(str(REF_LIB)), "ugu_ref_uv_raster", attrs, attr_indices, uv,
+                           uv_indices, width, height, texture_type, texture, mask)
+
+
+def _uv_mask_call(lib, fn_name, uv, uv_indices, width, height, color):
+    fn = getattr(lib, fn_name)
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    ui = np.ascontiguousarray(uv_indices, np.int32).reshape(-1, 3)
+    u = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+    m = np.zeros((height, width), np.uint8)
+    rc = fn(len(ui), len(u), u.ctypes.data, ui.ctypes.data, width, height, int(color), m.ctypes.data)
+    return m if rc == 0 else None
+
+
+def port_uv_mask(uv, uv_indices, width, height, color=255):
+    """Plain-C restatement of ugu::GenerateUvMask (Image1b form, src/util/raster_util.cc:9-27)."""
+    build_port()
+    return _uv_mask_call(C.CDLL(str(PORT_LIB)), "oracle_uv_mask", uv, uv_indices, width, height, color)
+
+
+def ref_uv_mask(uv, uv_indices, width, height, color=255):
+    return _uv_mask_call(C.CDLL(str(REF_LIB)), "ugu_ref_uv_mask", uv, uv_indices, width, height, color)
+
+
 class OracleRef:
     """The compiled, unmodified reference ugu::Rasterizer (present only where oracle/_ref was built)."""
 

@@ -387,4 +387,117 @@ int oracle_depth2pointcloud(const OracleCamera* cam, const float* depth, float* 
   return 0;
 }
 
-int oracle_abi_version(void) { return 2; }
+/* static_cast<int>(float) as x86-64 compiles it (cvttss2si): truncation, 0x80000000 when out of range / NaN */
+static int32_t cvtt_x86(float f) {
+  if (!(f > -2147483904.0f && f < 2147483648.0f)) return INT32_MIN;
+  return (int32_t)f;
+}
+
+static float edge2(const float* a, const float* b, const float* c) {
+  /* EdgeFunction, include/ugu/util/raster_util.h:31-34 */
+  return (c[0] - a[0]) * (b[1] - a[1]) - (c[1] - a[1]) * (b[0] - a[0]);
+}
+
+static float min3f(float a, float b, float c) { /* std::min({a,b,c}): first smallest by operator< */
+  float m = a;
+  if (b < m) m = b;
+  if (c < m) m = c;
+  return m;
+}
+static float max3f(float a, float b, float c) { /* std::max({a,b,c}) */
+  float m = a;
+  if (m < b) m = b;
+  if (m < c) m = c;
+  return m;
+}
+static int clampi(int v, int hi) { /* std::max(0, std::min(v, hi)) */
+  int t = v < hi ? v : hi;
+  return t > 0 ? t : 0;
+}
+
+/* ugu::RasterizeVertexAttributeToTexture / RasterizeFaceAttributeToTexture with num_threads = 1
+ * (include/ugu/util/raster_util.h:139-268) and RasterizeTriangle (:78-137); U2X / V2Y (:18-21).
+ * Same argument meaning as ugu_ref_uv_raster in oracle/ref_shim.cc.  Faces in ascending index, the
+ * last writer of a pixel wins. */
+int oracle_uv_raster(int32_t num_attrs, int32_t num_faces, int32_t num_uv, int32_t per_face,
+                     const float* attrs, const int32_t* attr_indices, const float* uv,
+                     const int32_t* uv_indices, int32_t width, int32_t height, int32_t texture_type,
+                     int32_t keep_texture, void* texture, uint8_t* mask) {
+  (void)num_uv;
+  if (per_face) {
+    if (num_attrs == 0 || num_attrs != num_faces) return 1; /* raster_util.h:238-240 */
+  } else {
+    if (num_faces == 0) return 1; /* :148-151 (equal sizes are implied by the flat arguments) */
+  }
+  if (width <= 0 || height <= 0) return 1;
+  const size_t P = (size_t)width * (size_t)height;
+  uint8_t* tb = (uint8_t*)texture;
+  float* tf = (float*)texture;
+  if (!keep_texture) memset(texture, 0, texture_type == 0 ? P * 3 : P * 12);
+  for (int32_t f = 0; f < num_faces; f++) {
+    const int32_t* ui = uv_indices + (size_t)f * 3;
+    float tri[3][2];
+    const float* col[3];
+    for (int k = 0; k < 3; k++) {
+      const float* q = uv + (size_t)ui[k] * 2;
+      tri[k][0] = q[0] * (float)width - 0.5f;             /* U2X */
+      tri[k][1] = (1.f - q[1]) * (float)height - 0.5f;    /* V2Y, flip */
+      col[k] = per_face ? attrs + (size_t)f * 3 : attrs + (size_t)attr_indices[(size_t)f * 3 + k] * 3;
+    }
+    float area = edge2(tri[0], tri[1], tri[2]);
+    if (fabsf(area) < FLT_MIN) area = area > 0 ? FLT_MIN : -FLT_MIN;
+    const float inv_area = 1.0f / area;
+    const int xmin = clampi(cvtt_x86(min3f(tri[0][0], tri[1][0], tri[2][0]) - 1), width - 1);
+    const int xmax = clampi(cvtt_x86(max3f(tri[0][0], tri[1][0], tri[2][0]) + 1), width - 1);
+    const int ymin = clampi(cvtt_x86(min3f(tri[0][1], tri[1][1], tri[2][1]) - 1), height - 1);
+    const int ymax = clampi(cvtt_x86(max3f(tri[0][1], tri[1][1], tri[2][1]) + 1), height - 1);
+    for (int y = ymin; y <= ymax; y++) {
+      for (int x = xmin; x <= xmax; x++) {
+        const float p[2] = {(float)x, (float)y};
+        float w0 = edge2(tri[1], tri[2], p);
+        float w1 = edge2(tri[2], tri[0], p);
+        float w2 = edge2(tri[0], tri[1], p);
+        w0 *= inv_area;
+        w1 *= inv_area;
+        w2 *= inv_area;
+        if (w0 < 0 || w1 < 0 || w2 < 0) continue;
+        const size_t pix = (size_t)y * (size_t)width + (size_t)x;
+        for (int k = 0; k < 3; k++) {
+          const float c = (w0 * col[0][k] + w1 * col[1][k]) + w2 * col[2][k];
+          if (texture_type == 0)
+            tb[pix * 3 + k] = (uint8_t)(cvtt_x86(roundf(c)) & 0xFF); /* saturate_cast: std::round, then cast */
+          else
+            tf[pix * 3 + k] = c;
+        }
+        if (mask) mask[pix] = 255;
+      }
+    }
+  }
+  return 0;
+}
+
+/* ugu::GenerateUvMask(uvs, uv_indices, Image1b&, uint8_t color, ...) — src/util/raster_util.cc:9-27:
+ * one constant attribute rasterised into an Image3b, channel 0 copied out. */
+int oracle_uv_mask(int32_t num_faces, int32_t num_uv, const float* uv, const int32_t* uv_indices,
+                   int32_t width, int32_t height, int32_t color, uint8_t* mask) {
+  if (width <= 0 || height <= 0) return 1;
+  const size_t P = (size_t)width * (size_t)height;
+  const float c = (float)(uint8_t)color;
+  const float attr[3] = {c, c, c};
+  int32_t* zero_idx = (int32_t*)calloc((size_t)(num_faces > 0 ? num_faces : 1) * 3, sizeof(int32_t));
+  uint8_t* tex = (uint8_t*)malloc(P * 3);
+  if (!zero_idx || !tex) {
+    free(zero_idx);
+    free(tex);
+    return 1;
+  }
+  const int rc = oracle_uv_raster(1, num_faces, num_uv, 0, attr, zero_idx, uv, uv_indices, width, height,
+                                  0, 0, tex, NULL);
+  if (rc == 0)
+    for (size_t i = 0; i < P; i++) mask[i] = tex[i * 3];
+  free(zero_idx);
+  free(tex);
+  return rc;
+}
+
+int oracle_abi_version(void) { return 3; }

@@ -19,6 +19,7 @@
 #include "ugu/log.h"
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/util/raster_util.h"
 #include "ugu/util/rgbd_util.h"
 
 extern "C" {
@@ -245,6 +246,67 @@ int ugu_ref_depth2pointcloud(const UguRefCamera* cam, const float* depth, float*
   std::memcpy(out.data, pc, P * 12);
   if (!ugu::Depth2PointCloud(d, camera, &out, gl_coord != 0)) return 1;
   std::memcpy(pc, out.data, P * 12);
+  return 0;
+}
+
+// ugu::RasterizeVertexAttributeToTexture / RasterizeFaceAttributeToTexture
+// (include/ugu/util/raster_util.h:139-268) with num_threads = 1 — the reference's only deterministic
+// order (faces in ascending index, last writer wins; with more threads it is racy).
+//   per_face     0: attrs indexed through attr_indices (vertex attributes); 1: attrs[f] per face
+//   texture_type 0: Image3b, 1: Image3f
+//   keep_texture 1: the reference is called with width = height = -1 and rasterises over the
+//                existing contents of `texture` (raster_util.h:151-155); 0: zero-initialised
+//   mask         W*H u8 in/out (the reference never initialises it), or null
+int ugu_ref_uv_raster(int32_t num_attrs, int32_t num_faces, int32_t num_uv, int32_t per_face,
+                      const float* attrs, const int32_t* attr_indices, const float* uv,
+                      const int32_t* uv_indices, int32_t width, int32_t height, int32_t texture_type,
+                      int32_t keep_texture, void* texture, uint8_t* mask) {
+  std::vector<Eigen::Vector3f> a(num_attrs);
+  for (int i = 0; i < num_attrs; i++) a[i] = Eigen::Vector3f(attrs[i * 3], attrs[i * 3 + 1], attrs[i * 3 + 2]);
+  std::vector<Eigen::Vector3i> ai(per_face ? 0 : num_faces), ui(num_faces);
+  for (int i = 0; i < num_faces; i++) {
+    if (!per_face) ai[i] = Eigen::Vector3i(attr_indices[i * 3], attr_indices[i * 3 + 1], attr_indices[i * 3 + 2]);
+    ui[i] = Eigen::Vector3i(uv_indices[i * 3], uv_indices[i * 3 + 1], uv_indices[i * 3 + 2]);
+  }
+  std::vector<Eigen::Vector2f> u(num_uv);
+  for (int i = 0; i < num_uv; i++) u[i] = Eigen::Vector2f(uv[i * 2], uv[i * 2 + 1]);
+  const size_t P = static_cast<size_t>(width) * height;
+  ugu::Image1b m;
+  if (mask) {
+    ugu::Init(&m, width, height, static_cast<unsigned char>(0));
+    std::memcpy(m.data, mask, P);
+  }
+  const int w = keep_texture ? -1 : width, h = keep_texture ? -1 : height;
+  bool ok;
+  if (texture_type == 0) {
+    ugu::Image3b t = ugu::Image3b::zeros(height, width);
+    if (keep_texture) std::memcpy(t.data, texture, P * 3);
+    ok = per_face ? ugu::RasterizeFaceAttributeToTexture(a, u, ui, t, w, h, mask ? &m : nullptr, 1)
+                  : ugu::RasterizeVertexAttributeToTexture(a, ai, u, ui, t, w, h, mask ? &m : nullptr, 1);
+    if (ok) std::memcpy(texture, t.data, P * 3);
+  } else {
+    ugu::Image3f t = ugu::Image3f::zeros(height, width);
+    if (keep_texture) std::memcpy(t.data, texture, P * 12);
+    ok = per_face ? ugu::RasterizeFaceAttributeToTexture(a, u, ui, t, w, h, mask ? &m : nullptr, 1)
+                  : ugu::RasterizeVertexAttributeToTexture(a, ai, u, ui, t, w, h, mask ? &m : nullptr, 1);
+    if (ok) std::memcpy(texture, t.data, P * 12);
+  }
+  if (ok && mask) std::memcpy(mask, m.data, P);
+  return ok ? 0 : 1;
+}
+
+// ugu::GenerateUvMask(uvs, uv_indices, Image1b&, uint8_t color, w, h, num_threads)
+// (src/util/raster_util.cc:9-27)
+int ugu_ref_uv_mask(int32_t num_faces, int32_t num_uv, const float* uv, const int32_t* uv_indices,
+                    int32_t width, int32_t height, int32_t color, uint8_t* mask) {
+  std::vector<Eigen::Vector3i> ui(num_faces);
+  for (int i = 0; i < num_faces; i++)
+    ui[i] = Eigen::Vector3i(uv_indices[i * 3], uv_indices[i * 3 + 1], uv_indices[i * 3 + 2]);
+  std::vector<Eigen::Vector2f> u(num_uv);
+  for (int i = 0; i < num_uv; i++) u[i] = Eigen::Vector2f(uv[i * 2], uv[i * 2 + 1]);
+  ugu::Image1b m;
+  if (!ugu::GenerateUvMask(u, ui, m, static_cast<uint8_t>(color), width, height, 1)) return 1;
+  std::memcpy(mask, m.data, static_cast<size_t>(width) * height);
   return 0;
 }
 
