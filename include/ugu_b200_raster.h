@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 2
+#define UGU_B200_ABI_VERSION 3
 
 enum {
   UGU_B200_OK = 0,
@@ -180,6 +180,48 @@ int ugu_b200_depth_to_point_cloud_device(ugu_b200_rasterizer* r, const ugu_b200_
 int ugu_b200_depth_to_point_cloud(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
                                   const float* depth_host, float* point_cloud_host, int32_t gl_coord,
                                   int32_t zero_invalid);
+
+/* UV-space attribute rasterization: replaces
+ *   ugu::RasterizeVertexAttributeToTexture<T>  (include/ugu/util/raster_util.h:139-226)  per_face = 0
+ *   ugu::RasterizeFaceAttributeToTexture<T>    (raster_util.h:228-268)                   per_face = 1
+ * with T = Vec3b (texture_type 0, W*H*3 u8) or Vec3f (texture_type 1, W*H*3 f32), in the reference's
+ * SEQUENTIAL semantics (num_threads = 1: faces in ascending index, the last writer of a texel wins;
+ * with more threads the reference itself is racy).  Arrays are the AoS data() of the reference's
+ * std::vector<Eigen::Vector3f/3i/2f> arguments.  The texture is zero-initialised like
+ * Image<T>::zeros(height, width) unless keep_texture = 1, which is the reference's width/height <= 0
+ * form (rasterise over the existing contents, raster_util.h:151-155).  `mask` (W*H u8, may be NULL)
+ * gets 255 on covered texels; the reference never initialises it, so keep_mask = 1 leaves the other
+ * texels as they were (in/out) and keep_mask = 0 writes 0 there (a fresh zeros image).
+ * Returns UGU_B200_E_INVALID where the reference returns false (no faces / mismatched sizes,
+ * raster_util.h:148-151,238-240) and for out-of-range indices (undefined behaviour in the reference). */
+typedef struct ugu_b200_uv_raster_desc {
+  int32_t num_attrs;            /* per_face: must equal num_faces */
+  int32_t num_faces;
+  int32_t num_uv;
+  int32_t per_face;
+  const float* attrs;           /* num_attrs * 3 */
+  const int32_t* attr_indices;  /* num_faces * 3; ignored when per_face */
+  const float* uv;              /* num_uv * 2 */
+  const int32_t* uv_indices;    /* num_faces * 3 */
+  int32_t width, height;
+  int32_t texture_type;         /* 0 = Image3b, 1 = Image3f */
+  int32_t keep_texture;
+  int32_t keep_mask;
+  int32_t reserved;
+} ugu_b200_uv_raster_desc;
+
+/* Host form: arrays and images in host memory; uploads, runs, copies back, returns when complete. */
+int ugu_b200_uv_raster(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_desc* d, void* texture_host,
+                       uint8_t* mask_host);
+/* Device form: every pointer of `d`, `texture_dev` and `mask_dev` are 16-byte aligned DEVICE
+ * pointers (index ranges are NOT validated); asynchronous on `stream`. */
+int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_desc* d,
+                              void* texture_dev, uint8_t* mask_dev, void* stream);
+/* ugu::GenerateUvMask(uvs, uv_indices, Image1b& mask, uint8_t color, width, height)
+ * (src/util/raster_util.cc:9-27): `color` where any face covers the texel, else 0.  Host arrays. */
+int ugu_b200_uv_mask(ugu_b200_rasterizer* r, int32_t num_faces, int32_t num_uv, const float* uv,
+                     const int32_t* uv_indices, int32_t width, int32_t height, int32_t color,
+                     uint8_t* mask_host);
 
 /* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
 int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);

@@ -257,6 +257,11 @@ int ugu_ref_depth2pointcloud(const UguRefCamera* cam, const float* depth, float*
 //   keep_texture 1: the reference is called with width = height = -1 and rasterises over the
 //                existing contents of `texture` (raster_util.h:151-155); 0: zero-initialised
 //   mask         W*H u8 in/out (the reference never initialises it), or null
+static int g_uv_threads = 1;
+// threads the reference's parallel_for uses in the UV-raster calls below (1 = the deterministic
+// order the parity tests pin; -1 = the reference's default, all hardware threads, racy on overlaps)
+void ugu_ref_uv_set_threads(int n) { g_uv_threads = n; }
+
 int ugu_ref_uv_raster(int32_t num_attrs, int32_t num_faces, int32_t num_uv, int32_t per_face,
                       const float* attrs, const int32_t* attr_indices, const float* uv,
                       const int32_t* uv_indices, int32_t width, int32_t height, int32_t texture_type,
@@ -281,14 +286,14 @@ int ugu_ref_uv_raster(int32_t num_attrs, int32_t num_faces, int32_t num_uv, int3
   if (texture_type == 0) {
     ugu::Image3b t = ugu::Image3b::zeros(height, width);
     if (keep_texture) std::memcpy(t.data, texture, P * 3);
-    ok = per_face ? ugu::RasterizeFaceAttributeToTexture(a, u, ui, t, w, h, mask ? &m : nullptr, 1)
-                  : ugu::RasterizeVertexAttributeToTexture(a, ai, u, ui, t, w, h, mask ? &m : nullptr, 1);
+    ok = per_face ? ugu::RasterizeFaceAttributeToTexture(a, u, ui, t, w, h, mask ? &m : nullptr, g_uv_threads)
+                  : ugu::RasterizeVertexAttributeToTexture(a, ai, u, ui, t, w, h, mask ? &m : nullptr, g_uv_threads);
     if (ok) std::memcpy(texture, t.data, P * 3);
   } else {
     ugu::Image3f t = ugu::Image3f::zeros(height, width);
     if (keep_texture) std::memcpy(t.data, texture, P * 12);
-    ok = per_face ? ugu::RasterizeFaceAttributeToTexture(a, u, ui, t, w, h, mask ? &m : nullptr, 1)
-                  : ugu::RasterizeVertexAttributeToTexture(a, ai, u, ui, t, w, h, mask ? &m : nullptr, 1);
+    ok = per_face ? ugu::RasterizeFaceAttributeToTexture(a, u, ui, t, w, h, mask ? &m : nullptr, g_uv_threads)
+                  : ugu::RasterizeVertexAttributeToTexture(a, ai, u, ui, t, w, h, mask ? &m : nullptr, g_uv_threads);
     if (ok) std::memcpy(texture, t.data, P * 12);
   }
   if (ok && mask) std::memcpy(mask, m.data, P);

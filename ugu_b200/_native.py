@@ -43,6 +43,14 @@ class Outputs(C.Structure):
                 ("mask", C.c_void_p), ("face_id", C.c_void_p)]
 
 
+class UvRasterDesc(C.Structure):
+    _fields_ = [("num_attrs", C.c_int32), ("num_faces", C.c_int32), ("num_uv", C.c_int32),
+                ("per_face", C.c_int32), ("attrs", C.c_void_p), ("attr_indices", C.c_void_p),
+                ("uv", C.c_void_p), ("uv_indices", C.c_void_p), ("width", C.c_int32),
+                ("height", C.c_int32), ("texture_type", C.c_int32), ("keep_texture", C.c_int32),
+                ("keep_mask", C.c_int32), ("reserved", C.c_int32)]
+
+
 class Stats(C.Structure):
     _fields_ = [("stage_ms", C.c_double * NUM_STAGES), ("timed_views", C.c_uint64),
                 ("views", C.c_uint64), ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64),
@@ -69,6 +77,11 @@ SYMBOLS = {
                                                        C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "ugu_b200_depth_to_point_cloud": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p,
                                                 C.c_int32, C.c_int32]),
+    "ugu_b200_uv_raster": (C.c_int, [C.c_void_p, C.POINTER(UvRasterDesc), C.c_void_p, C.c_void_p]),
+    "ugu_b200_uv_raster_device": (C.c_int, [C.c_void_p, C.POINTER(UvRasterDesc), C.c_void_p, C.c_void_p,
+                                            C.c_void_p]),
+    "ugu_b200_uv_mask": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32,
+                                   C.c_int32, C.c_int32, C.c_void_p]),
     "ugu_b200_rasterizer_set_profiling": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint32]),
     "ugu_b200_rasterizer_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "ugu_b200_rasterizer_reset_stats": (C.c_int, [C.c_void_p]),
@@ -96,7 +109,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 2:
+    if lib.ugu_b200_abi_version() != 3:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "raster_kernels.cuh"
+#include "uv_raster_kernels.cuh"
 #include "ugu_b200_raster.h"
 
 using namespace ugu_b200;
@@ -61,6 +62,10 @@ struct ugu_b200_rasterizer {
   cudaEvent_t ev_render[2] = {nullptr, nullptr};
   cudaEvent_t ev_copied[2] = {nullptr, nullptr};
   bool copied_pending[2] = {false, false};
+
+  // UV-space rasterization scratch (uv_raster_kernels.cuh)
+  DevBuf uv_win, uv_counter, uv_q_face, uv_q_job, uv_in, uv_tex, uv_mask;
+  size_t uv_win_clean = 0;  // texels of uv_win known to hold -1
 
   // pinned staging for pageable destinations
   void* staging = nullptr;
@@ -639,7 +644,8 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   if (r->stream) cudaStreamSynchronize(r->stream);
   if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
   FreeMesh(r);
-  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters};
+  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters,
+                    &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_in, &r->uv_tex, &r->uv_mask};
   for (DevBuf* b : bufs) FreeBuf(b);
   for (int i = 0; i < 2; i++) {
     FreeBuf(&r->out_color[i]);
@@ -1091,6 +1097,155 @@ int ugu_b200_depth_to_point_cloud(ugu_b200_rasterizer* r, const ugu_b200_camera*
   std::vector<CopySeg> segs;
   segs.push_back({point_cloud_host, pc_dev, P * 12});
   return CopyOut(r, segs, r->stream);
+}
+
+int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_desc* d,
+                              void* texture_dev, uint8_t* mask_dev, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!d || !texture_dev) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  // raster_util.h:148-151,238-240: the reference returns false
+  if (d->num_faces <= 0) return Fail(r, UGU_B200_E_INVALID, "no faces");
+  if (d->per_face && d->num_attrs != d->num_faces)
+    return Fail(r, UGU_B200_E_INVALID, "face attribute count %d != face count %d", d->num_attrs, d->num_faces);
+  if (!d->attrs || !d->uv || !d->uv_indices || (!d->per_face && !d->attr_indices))
+    return Fail(r, UGU_B200_E_INVALID, "NULL array");
+  if (d->width <= 0 || d->height <= 0 || (long long)d->width * d->height >= (1ll << 31))
+    return Fail(r, UGU_B200_E_INVALID, "texture size %dx%d is invalid", d->width, d->height);
+  if (d->num_faces >= (1 << (64 - kQueueJobBits)))
+    return Fail(r, UGU_B200_E_INVALID, "more than 2^26 - 1 faces");
+  if (d->texture_type != 0 && d->texture_type != 1) return Fail(r, UGU_B200_E_INVALID, "bad texture_type");
+  if (((uintptr_t)texture_dev | (uintptr_t)mask_dev | (uintptr_t)d->attrs | (uintptr_t)d->uv |
+       (uintptr_t)d->uv_indices | (uintptr_t)d->attr_indices) & 15u)
+    return Fail(r, UGU_B200_E_INVALID, "device buffers must be 16-byte aligned");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  const size_t P = (size_t)d->width * d->height;
+  int rc;
+  if (r->uv_win.bytes < P * 4 + 16) r->uv_win_clean = 0;
+  if ((rc = Grow(r, &r->uv_win, P * 4 + 16))) return rc;
+  if ((rc = Grow(r, &r->uv_q_face, (size_t)d->num_faces * 4))) return rc;
+  if ((rc = Grow(r, &r->uv_q_job, (size_t)d->num_faces * 8))) return rc;
+  if (!r->uv_counter.p) {
+    if ((rc = Grow(r, &r->uv_counter, 16))) return rc;
+    CU_TRY(r, cudaMemsetAsync(r->uv_counter.p, 0, 16, st));
+  }
+  if (r->uv_win_clean < P) {  // the resolve kernel leaves [0, P) at -1 for the next call
+    fill_i32<<<Blocks(P, 256), 256, 0, st>>>((int*)r->uv_win.p, P, -1);
+    r->uv_win_clean = P;
+    r->stats.kernel_launches++;
+  }
+  UvRasterParams p;
+  p.W = d->width;
+  p.H = d->height;
+  p.F = d->num_faces;
+  p.per_face = d->per_face ? 1 : 0;
+  p.texture_f32 = d->texture_type;
+  p.keep_texture = d->keep_texture ? 1 : 0;
+  p.keep_mask = d->keep_mask ? 1 : 0;
+  p.attrs = d->attrs;
+  p.attr_idx = d->attr_indices;
+  p.uv = d->uv;
+  p.uv_idx = d->uv_indices;
+  p.win = (int*)r->uv_win.p;
+  p.counter = (unsigned long long*)r->uv_counter.p;
+  p.q_face = (int*)r->uv_q_face.p;
+  p.q_job = (unsigned long long*)r->uv_q_job.p;
+  p.texture = texture_dev;
+  p.mask = mask_dev;
+  uv_setup_kernel<<<Blocks((size_t)p.F, 256), 256, 0, st>>>(p);
+  uv_tile_kernel<<<(unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, 0, st>>>(p);
+  uv_resolve_kernel<<<Blocks((P + 3) / 4, 256), 256, 0, st>>>(p);
+  CU_TRY(r, cudaGetLastError());
+  r->stats.kernel_launches += 3;
+  return UGU_B200_OK;
+}
+
+int ugu_b200_uv_raster(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_desc* d, void* texture_host,
+                       uint8_t* mask_host) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!d || !texture_host) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (d->num_faces <= 0) return Fail(r, UGU_B200_E_INVALID, "no faces");
+  if (d->per_face && d->num_attrs != d->num_faces)
+    return Fail(r, UGU_B200_E_INVALID, "face attribute count %d != face count %d", d->num_attrs, d->num_faces);
+  if (d->num_attrs <= 0 || d->num_uv <= 0 || !d->attrs || !d->uv || !d->uv_indices ||
+      (!d->per_face && !d->attr_indices))
+    return Fail(r, UGU_B200_E_INVALID, "empty or NULL array");
+  if (d->width <= 0 || d->height <= 0 || (long long)d->width * d->height >= (1ll << 31))
+    return Fail(r, UGU_B200_E_INVALID, "texture size %dx%d is invalid", d->width, d->height);
+  const size_t nf3 = (size_t)d->num_faces * 3;
+  if (!IndicesInRange(d->uv_indices, nf3, d->num_uv))
+    return Fail(r, UGU_B200_E_INVALID, "uv index out of range");
+  if (!d->per_face && !IndicesInRange(d->attr_indices, nf3, d->num_attrs))
+    return Fail(r, UGU_B200_E_INVALID, "attribute index out of range");
+  CU_TRY(r, cudaSetDevice(r->device));
+  auto up16 = [](size_t b) { return (b + 15) & ~(size_t)15; };
+  const size_t b_attr = up16((size_t)d->num_attrs * 12), b_uv = up16((size_t)d->num_uv * 8);
+  const size_t b_idx = up16(nf3 * 4);
+  const size_t P = (size_t)d->width * d->height;
+  const size_t b_tex = P * (d->texture_type ? 12 : 3);
+  int rc;
+  if ((rc = Grow(r, &r->uv_in, b_attr + b_uv + 2 * b_idx))) return rc;
+  if ((rc = Grow(r, &r->uv_tex, up16(b_tex)))) return rc;
+  if (mask_host && (rc = Grow(r, &r->uv_mask, up16(P)))) return rc;
+  char* base = (char*)r->uv_in.p;
+  ugu_b200_uv_raster_desc dd = *d;
+  dd.attrs = (const float*)base;
+  dd.uv = (const float*)(base + b_attr);
+  dd.uv_indices = (const int32_t*)(base + b_attr + b_uv);
+  dd.attr_indices = d->per_face ? nullptr : (const int32_t*)(base + b_attr + b_uv + b_idx);
+  cudaStream_t st = r->stream;
+  CU_TRY(r, cudaMemcpyAsync((void*)dd.attrs, d->attrs, (size_t)d->num_attrs * 12, cudaMemcpyHostToDevice, st));
+  CU_TRY(r, cudaMemcpyAsync((void*)dd.uv, d->uv, (size_t)d->num_uv * 8, cudaMemcpyHostToDevice, st));
+  CU_TRY(r, cudaMemcpyAsync((void*)dd.uv_indices, d->uv_indices, nf3 * 4, cudaMemcpyHostToDevice, st));
+  r->stats.h2d_bytes += (size_t)d->num_attrs * 12 + (size_t)d->num_uv * 8 + nf3 * 4;
+  if (!d->per_face) {
+    CU_TRY(r, cudaMemcpyAsync((void*)dd.attr_indices, d->attr_indices, nf3 * 4, cudaMemcpyHostToDevice, st));
+    r->stats.h2d_bytes += nf3 * 4;
+  }
+  if (d->keep_texture) {
+    CU_TRY(r, cudaMemcpyAsync(r->uv_tex.p, texture_host, b_tex, cudaMemcpyHostToDevice, st));
+    r->stats.h2d_bytes += b_tex;
+  }
+  if (mask_host && d->keep_mask) {
+    CU_TRY(r, cudaMemcpyAsync(r->uv_mask.p, mask_host, P, cudaMemcpyHostToDevice, st));
+    r->stats.h2d_bytes += P;
+  }
+  if ((rc = ugu_b200_uv_raster_device(r, &dd, r->uv_tex.p, mask_host ? (uint8_t*)r->uv_mask.p : nullptr, st)))
+    return rc;
+  std::vector<CopySeg> segs;
+  segs.push_back({texture_host, r->uv_tex.p, b_tex});
+  if (mask_host) segs.push_back({mask_host, r->uv_mask.p, P});
+  return CopyOut(r, segs, st);
+}
+
+int ugu_b200_uv_mask(ugu_b200_rasterizer* r, int32_t num_faces, int32_t num_uv, const float* uv,
+                     const int32_t* uv_indices, int32_t width, int32_t height, int32_t color,
+                     uint8_t* mask_host) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!mask_host) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (width <= 0 || height <= 0) return Fail(r, UGU_B200_E_INVALID, "mask size %dx%d is invalid", width, height);
+  // raster_util.cc:13-26: one constant attribute {c, c, c} rasterised as Image3b; channel 0 is the
+  // mask.  (uint8_t)round((w0*c + w1*c) + w2*c) depends on the weights, so the texture path runs
+  // as it is and the first channel is extracted on the host.
+  const float c = (float)(uint8_t)color;
+  const float attr[3] = {c, c, c};
+  std::vector<int32_t> zero_idx((size_t)std::max(num_faces, 0) * 3, 0);
+  std::vector<uint8_t> tex((size_t)width * height * 3);
+  ugu_b200_uv_raster_desc d{};
+  d.num_attrs = 1;
+  d.num_faces = num_faces;
+  d.num_uv = num_uv;
+  d.attrs = attr;
+  d.attr_indices = zero_idx.data();
+  d.uv = uv;
+  d.uv_indices = uv_indices;
+  d.width = width;
+  d.height = height;
+  const int rc = ugu_b200_uv_raster(r, &d, tex.data(), nullptr);
+  if (rc) return rc;
+  const size_t P = (size_t)width * height;
+  for (size_t i = 0; i < P; i++) mask_host[i] = tex[i * 3];
+  return UGU_B200_OK;
 }
 
 int ugu_b200_depth_to_u16(const float* depth, uint16_t* depth_w, size_t count) {

@@ -430,6 +430,81 @@ class Rasterizer:
         if rc != N.OK:
             raise RuntimeError(N.last_error(self._h))
 
+    # -- UV-space attribute rasterization (include/ugu/util/raster_util.h:139-268) -----------------
+    def _uv_raster(self, attrs, attr_indices, uvs, uv_indices, texture, width, height, mask) -> bool:
+        a = np.ascontiguousarray(attrs, np.float32).reshape(-1, 3)
+        ui = np.ascontiguousarray(uv_indices, np.int32).reshape(-1, 3)
+        u = np.ascontiguousarray(uvs, np.float32).reshape(-1, 2)
+        per_face = attr_indices is None
+        ai = None if per_face else np.ascontiguousarray(attr_indices, np.int32).reshape(-1, 3)
+        # raster_util.h:148-151 / :238-240 — return false, before the texture is touched
+        if per_face:
+            if len(a) == 0 or len(a) != len(ui):
+                return False
+        elif len(ai) == 0 or len(ai) != len(ui):
+            return False
+        keep = not (width > 0 and height > 0)
+        if keep:
+            if texture.empty():
+                return False  # raster_util.h:153-155
+            width, height = texture.cols, texture.rows
+        else:
+            texture._init(width, height)
+        if mask is not None and (mask.cols != width or mask.rows != height):
+            LOGE("mask size differs from the texture size")  # out-of-bounds writes in the reference
+            return False
+        d = N.UvRasterDesc(len(a), len(ui), len(u), 1 if per_face else 0, a.ctypes.data,
+                           None if ai is None else ai.ctypes.data, u.ctypes.data, ui.ctypes.data,
+                           width, height, 1 if texture.dtype == np.float32 else 0, 1 if keep else 0,
+                           1, 0)  # the reference never clears the mask: in/out
+        rc = self._lib.ugu_b200_uv_raster(self._h, C.byref(d), texture.data.ctypes.data,
+                                          None if mask is None else mask.data.ctypes.data)
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        return True
+
+    def RasterizeVertexAttributeToTexture(self, vertex_attrs, vertex_attr_indices, uvs, uv_indices,
+                                          texture, width: int = 512, height: int = 512,
+                                          mask: Optional["Image1b"] = None) -> bool:
+        """ugu::RasterizeVertexAttributeToTexture<T> (raster_util.h:139-226), T = Vec3b (Image3b) or
+        Vec3f (Image3f), in the reference's sequential order (num_threads = 1): the highest covering
+        face index owns a texel.  width/height <= 0 rasterises over the existing texture."""
+        return self._uv_raster(vertex_attrs, vertex_attr_indices, uvs, uv_indices, texture, width,
+                               height, mask)
+
+    def RasterizeFaceAttributeToTexture(self, face_attrs, uvs, uv_indices, texture, width: int = 512,
+                                        height: int = 512, mask: Optional["Image1b"] = None) -> bool:
+        """ugu::RasterizeFaceAttributeToTexture<T> (raster_util.h:228-268)."""
+        return self._uv_raster(face_attrs, None, uvs, uv_indices, texture, width, height, mask)
+
+    def GenerateUvMask(self, uvs, uv_indices, mask: "Image1b", color: int = 255, width: int = 512,
+                       height: int = 512) -> bool:
+        """ugu::GenerateUvMask(uvs, uv_indices, Image1b&, uint8_t color, w, h)
+        (src/util/raster_util.cc:9-27)."""
+        ui = np.ascontiguousarray(uv_indices, np.int32).reshape(-1, 3)
+        u = np.ascontiguousarray(uvs, np.float32).reshape(-1, 2)
+        if width <= 0 or height <= 0:
+            return False
+        mask._init(width, height)
+        if len(ui) == 0:  # the reference returns false but still hands back a zero mask
+            mask.data[...] = 0
+            return False
+        rc = self._lib.ugu_b200_uv_mask(self._h, len(ui), len(u), u.ctypes.data, ui.ctypes.data, width,
+                                        height, int(color) & 0xFF, mask.data.ctypes.data)
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        return True
+
+    def uv_raster_device(self, desc: "N.UvRasterDesc", texture: int, mask: int = 0, stream: int = 0) -> None:
+        """Device-resident form: every pointer in `desc`, `texture` and `mask` are raw 16-byte
+        aligned device pointers; asynchronous on `stream`."""
+        rc = self._lib.ugu_b200_uv_raster_device(self._h, C.byref(desc), C.c_void_p(texture),
+                                                 C.c_void_p(mask) if mask else None, C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
     # -- device-resident / batch extensions (no reference counterpart; see INTEGRATION.md) --------
     def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
                       face_id=None, stream: int = 0) -> None:
