@@ -64,7 +64,7 @@ struct ugu_b200_rasterizer {
   bool copied_pending[2] = {false, false};
 
   // UV-space rasterization scratch (uv_raster_kernels.cuh)
-  DevBuf uv_win, uv_counter, uv_q_face, uv_q_job, uv_in, uv_tex, uv_mask;
+  DevBuf uv_win, uv_counter, uv_q_face, uv_q_job, uv_rec, uv_in, uv_tex, uv_mask;
   size_t uv_win_clean = 0;  // texels of uv_win known to hold -1
 
   // pinned staging for pageable destinations
@@ -645,7 +645,7 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
   FreeMesh(r);
   DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters,
-                    &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_in, &r->uv_tex, &r->uv_mask};
+                    &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask};
   for (DevBuf* b : bufs) FreeBuf(b);
   for (int i = 0; i < 2; i++) {
     FreeBuf(&r->out_color[i]);
@@ -1125,6 +1125,7 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
   if ((rc = Grow(r, &r->uv_win, P * 4 + 16))) return rc;
   if ((rc = Grow(r, &r->uv_q_face, (size_t)d->num_faces * 4))) return rc;
   if ((rc = Grow(r, &r->uv_q_job, (size_t)d->num_faces * 8))) return rc;
+  if ((rc = Grow(r, &r->uv_rec, (size_t)d->num_faces * 64))) return rc;
   if (!r->uv_counter.p) {
     if ((rc = Grow(r, &r->uv_counter, 16))) return rc;
     CU_TRY(r, cudaMemsetAsync(r->uv_counter.p, 0, 16, st));
@@ -1150,11 +1151,12 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
   p.counter = (unsigned long long*)r->uv_counter.p;
   p.q_face = (int*)r->uv_q_face.p;
   p.q_job = (unsigned long long*)r->uv_q_job.p;
+  p.rec = (float4*)r->uv_rec.p;
   p.texture = texture_dev;
   p.mask = mask_dev;
   uv_setup_kernel<<<Blocks((size_t)p.F, 256), 256, 0, st>>>(p);
   uv_tile_kernel<<<(unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, 0, st>>>(p);
-  uv_resolve_kernel<<<Blocks((P + 3) / 4, 256), 256, 0, st>>>(p);
+  uv_resolve_kernel<<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += 3;
   return UGU_B200_OK;

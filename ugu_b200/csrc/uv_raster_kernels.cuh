@@ -36,6 +36,8 @@ struct UvRasterParams {
   unsigned long long* counter;  // packed queue counter: [63:38] entries, [37:0] tile jobs
   int* q_face;            // F
   unsigned long long* q_job;    // F: first tile job of each queue entry
+  float4* rec;            // F x 64 B per-face records written by uv_setup_kernel, read by the resolve:
+                          // {x0 y0 x1 y1} {x2 y2 inv_area a0.x} {a0.y a0.z a1.x a1.y} {a1.z a2.x a2.y a2.z}
   void* texture;          // W*H*3 u8 or f32
   uint8_t* mask;          // W*H or null
 };
@@ -46,6 +48,9 @@ __device__ __forceinline__ int cvtt_x86(float f) {
   if (!(f > -2147483904.0f && f < 2147483648.0f)) return (int)0x80000000;
   return __float2int_rz(f);
 }
+
+constexpr int kUvInlineMax = 64;     // bbox texels up to which a face is rasterised inside uv_setup_kernel
+constexpr int kUvJobsPerChunk = 64;  // tile jobs a warp claims at a time in uv_tile_kernel
 
 struct UvTri {
   float x0, y0, x1, y1, x2, y2;
@@ -93,8 +98,9 @@ __device__ __forceinline__ void uv_weights(const UvTri& t, float px, float py, f
 }
 
 // ---------------------------------------------------------------------------------------------
-// UV-K1: per-face bbox -> tile jobs.  Lane = face; the warp's entries are appended to the queue with
-// one atomicAdd on the packed (entries, jobs) counter, so q_job is monotone over queue slots.
+// UV-K1: per-face setup.  Lane = face.  Faces whose bbox holds <= kUvInlineMax texels are rasterised
+// here by their own lane; larger ones become tile jobs: the warp's entries are appended to the queue
+// with one atomicAdd on the packed (entries, jobs) counter, so q_job is monotone over queue slots.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) uv_setup_kernel(const UvRasterParams p) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
@@ -103,12 +109,46 @@ __global__ void __launch_bounds__(256) uv_setup_kernel(const UvRasterParams p) {
   if (f < p.F) {
     UvTri t;
     uv_tri_setup(p, f, t);
+    {  // per-face record for the resolve: the projected triangle and the three corner attributes
+      int a0 = f, a1 = f, a2 = f;
+      if (!p.per_face) {
+        a0 = __ldg(p.attr_idx + 3 * (size_t)f + 0);
+        a1 = __ldg(p.attr_idx + 3 * (size_t)f + 1);
+        a2 = __ldg(p.attr_idx + 3 * (size_t)f + 2);
+      }
+      const float* q0 = p.attrs + 3 * (size_t)a0;
+      const float* q1 = p.attrs + 3 * (size_t)a1;
+      const float* q2 = p.attrs + 3 * (size_t)a2;
+      float4* r = p.rec + 4 * (size_t)f;
+      r[0] = make_float4(t.x0, t.y0, t.x1, t.y1);
+      r[1] = make_float4(t.x2, t.y2, t.inv_area, __ldg(q0 + 0));
+      r[2] = make_float4(__ldg(q0 + 1), __ldg(q0 + 2), __ldg(q1 + 0), __ldg(q1 + 1));
+      r[3] = make_float4(__ldg(q1 + 2), __ldg(q2 + 0), __ldg(q2 + 1), __ldg(q2 + 2));
+    }
     int x0, y0, x1, y1;
     uv_tri_bounds(p, t, x0, y0, x1, y1);
     if (x1 >= x0 && y1 >= y0) {
-      const unsigned long long njobs = (unsigned long long)((x1 - x0 + kJobW) / kJobW) *
-                                       (unsigned long long)((y1 - y0 + kJobH) / kJobH);
-      mine = (1ull << kQueueJobBits) | njobs;
+      const int nx = x1 - x0 + 1;
+      const long long ns = (long long)nx * (y1 - y0 + 1);
+      if (ns <= (long long)kUvInlineMax) {
+        // small bbox: walked by this lane (a warp covers 32 faces per step; meshes whose uv
+        // triangles are of similar size keep the lanes busy), ~25 instructions per texel instead of
+        // a queue entry + an 8x4 tile job per face
+        int x = x0, y = y0;
+        for (int k = 0; k < (int)ns; k++) {
+          float w0, w1, w2;
+          uv_weights(t, (float)x, (float)y, w0, w1, w2);
+          if (!(w0 < 0.f || w1 < 0.f || w2 < 0.f)) atomicMax(p.win + ((size_t)y * p.W + x), f);
+          if (++x > x1) {
+            x = x0;
+            ++y;
+          }
+        }
+      } else {
+        const unsigned long long njobs = (unsigned long long)((x1 - x0 + kJobW) / kJobW) *
+                                         (unsigned long long)((y1 - y0 + kJobH) / kJobH);
+        mine = (1ull << kQueueJobBits) | njobs;
+      }
     }
   }
   if (!__any_sync(0xffffffffu, mine != 0ull)) return;
@@ -145,7 +185,7 @@ __global__ void __launch_bounds__(128) uv_tile_kernel(const UvRasterParams p) {
   const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
   const unsigned long long gw = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const unsigned long long rounds =
-      (T + nwarps * (unsigned long long)kJobsPerChunk - 1) / (nwarps * (unsigned long long)kJobsPerChunk);
+      (T + nwarps * (unsigned long long)kUvJobsPerChunk - 1) / (nwarps * (unsigned long long)kUvJobsPerChunk);
   unsigned long long per = (T + nwarps * rounds - 1) / (nwarps * rounds);
   per = per < 2ull ? 2ull : per;
   const unsigned long long nchunks = (T + per - 1) / per;
@@ -169,31 +209,53 @@ __global__ void __launch_bounds__(128) uv_tile_kernel(const UvRasterParams p) {
     unsigned e = lo;
     unsigned long long j = jb;
     while (j < je) {
-      const int f = p.q_face[e];
-      const unsigned long long js = p.q_job[e];
-      const unsigned long long jn = (e + 1u < n) ? p.q_job[e + 1u] : T;
-      const unsigned long long jend = (jn < je) ? jn : je;
-      UvTri t;
-      uv_tri_setup(p, f, t);
-      int x0, y0, x1, y1;
-      uv_tri_bounds(p, t, x0, y0, x1, y1);
-      const unsigned ntx = (unsigned)((x1 - x0 + kJobW) / kJobW);
-      unsigned ty = (unsigned)(j - js) / ntx, tx = (unsigned)(j - js) - ty * ntx;
-      for (unsigned long long jj = j; jj < jend; ++jj, ++tx) {
-        if (tx == ntx) {
-          tx = 0u;
-          ++ty;
-        }
-        const int x = x0 + (int)tx * kJobW + lx;
-        const int y = y0 + (int)ty * kJobH + ly;
-        if (x <= x1 && y <= y1) {
-          float w0, w1, w2;
-          uv_weights(t, (float)x, (float)y, w0, w1, w2);
-          if (!(w0 < 0.f || w1 < 0.f || w2 < 0.f)) atomicMax(p.win + ((size_t)y * p.W + x), f);
-        }
+      // Batch of up to 31 queue entries, lane = entry: the dependent q_face -> uv_idx -> uv loads and
+      // the triangle setup of the whole batch are in flight together (one latency chain per batch
+      // instead of one per entry); lane i + 1 supplies the job range end of entry i.
+      const unsigned me = e + lane;
+      const unsigned long long js_l = (me < n) ? p.q_job[me] : T;
+      const bool mine = (me < n) && (js_l < je) && (lane < 31u);
+      UvTri t_l;
+      int bx0 = 0, by0 = 0, bx1 = -1, by1 = -1, f_l = -1;
+      if (mine) {
+        f_l = p.q_face[me];
+        uv_tri_setup(p, f_l, t_l);
+        uv_tri_bounds(p, t_l, bx0, by0, bx1, by1);
       }
-      j = jend;
-      ++e;
+      const int nb = __popc(__ballot_sync(0xffffffffu, mine));  // a prefix of the lanes: q_job is monotone
+      for (int i = 0; i < nb; i++) {
+        const int f = __shfl_sync(0xffffffffu, f_l, i);
+        const unsigned long long js = __shfl_sync(0xffffffffu, js_l, i);
+        const unsigned long long jn = __shfl_sync(0xffffffffu, js_l, i + 1);
+        const unsigned long long jend = (jn < je) ? jn : je;
+        UvTri t;
+        t.x0 = __shfl_sync(0xffffffffu, t_l.x0, i);
+        t.y0 = __shfl_sync(0xffffffffu, t_l.y0, i);
+        t.x1 = __shfl_sync(0xffffffffu, t_l.x1, i);
+        t.y1 = __shfl_sync(0xffffffffu, t_l.y1, i);
+        t.x2 = __shfl_sync(0xffffffffu, t_l.x2, i);
+        t.y2 = __shfl_sync(0xffffffffu, t_l.y2, i);
+        t.inv_area = __shfl_sync(0xffffffffu, t_l.inv_area, i);
+        const int x0 = __shfl_sync(0xffffffffu, bx0, i), y0 = __shfl_sync(0xffffffffu, by0, i);
+        const int x1 = __shfl_sync(0xffffffffu, bx1, i), y1 = __shfl_sync(0xffffffffu, by1, i);
+        const unsigned ntx = (unsigned)((x1 - x0 + kJobW) / kJobW);
+        unsigned ty = (unsigned)(j - js) / ntx, tx = (unsigned)(j - js) - ty * ntx;
+        for (unsigned long long jj = j; jj < jend; ++jj, ++tx) {
+          if (tx == ntx) {
+            tx = 0u;
+            ++ty;
+          }
+          const int x = x0 + (int)tx * kJobW + lx;
+          const int y = y0 + (int)ty * kJobH + ly;
+          if (x <= x1 && y <= y1) {
+            float w0, w1, w2;
+            uv_weights(t, (float)x, (float)y, w0, w1, w2);
+            if (!(w0 < 0.f || w1 < 0.f || w2 < 0.f)) atomicMax(p.win + ((size_t)y * p.W + x), f);
+          }
+        }
+        j = jend;
+      }
+      e += (unsigned)nb;
     }
   }
 }
@@ -204,57 +266,53 @@ __global__ void __launch_bounds__(128) uv_tile_kernel(const UvRasterParams p) {
 // (w0*c0 + w1*c1) + w2*c2 (raster_util.h:138-139), convert (saturate_cast, :106-115: std::round for
 // integer texels, then the truncating cast) and store 12 / 48 packed bytes + 4 mask bytes.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool uv_shade(const UvRasterParams& p, int f, int x, int y, float& c0,
-                                         float& c1, float& c2) {
-  c0 = c1 = c2 = 0.f;
-  if (f < 0) return false;
-  UvTri t;
-  uv_tri_setup(p, f, t);
-  int a0 = f, a1 = f, a2 = f;
-  if (!p.per_face) {
-    a0 = __ldg(p.attr_idx + 3 * (size_t)f + 0);
-    a1 = __ldg(p.attr_idx + 3 * (size_t)f + 1);
-    a2 = __ldg(p.attr_idx + 3 * (size_t)f + 2);
-  }
-  const float* q0 = p.attrs + 3 * (size_t)a0;
-  const float* q1 = p.attrs + 3 * (size_t)a1;
-  const float* q2 = p.attrs + 3 * (size_t)a2;
-  float w0, w1, w2;
-  uv_weights(t, (float)x, (float)y, w0, w1, w2);
-  c0 = (w0 * __ldg(q0 + 0) + w1 * __ldg(q1 + 0)) + w2 * __ldg(q2 + 0);
-  c1 = (w0 * __ldg(q0 + 1) + w1 * __ldg(q1 + 1)) + w2 * __ldg(q2 + 1);
-  c2 = (w0 * __ldg(q0 + 2) + w1 * __ldg(q1 + 2)) + w2 * __ldg(q2 + 2);
-  return true;
-}
-
 __device__ __forceinline__ unsigned uv_to_u8(float c) {  // (uint8_t)std::round(c) through cvttss2si
   return (unsigned)cvtt_x86(roundf(c)) & 0xFFu;
 }
 
-__global__ void __launch_bounds__(256) uv_resolve_kernel(const UvRasterParams p) {
-  const size_t P = (size_t)p.W * p.H;
-  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t == 0) p.counter[0] = 0ull;  // queue reset for the next call
-  const size_t base = t * 4;
-  if (base >= P) return;
-  int f[4] = {-1, -1, -1, -1};
-  const bool full = base + 3 < P;
-  if (full) {
-    const int4 w = *reinterpret_cast<const int4*>(p.win + base);
-    f[0] = w.x; f[1] = w.y; f[2] = w.z; f[3] = w.w;
-    *reinterpret_cast<int4*>(p.win + base) = make_int4(-1, -1, -1, -1);
-  } else {
-    for (int k = 0; k < 4 && base + k < P; k++) {
-      f[k] = p.win[base + k];
-      p.win[base + k] = -1;
-    }
-  }
+constexpr int kUvGroupsPerThread = 4;  // 4-texel groups per thread: 64 bytes of winners in flight per thread
+
+// One group of 4 consecutive texels starting at `base` whose winners are f[0..3].
+__device__ __forceinline__ void uv_resolve_group(const UvRasterParams& p, size_t P, size_t base, bool full,
+                                                 const int (&f)[4]) {
+  // One dependent level after the winners: the 64-byte face records of the (up to 4) distinct
+  // winners are requested together; a texel whose winner equals its left neighbour's reuses the
+  // neighbour's registers.
   float c[4][3];
   bool cov[4];
-  int y = (int)(base / (size_t)p.W), x = (int)(base - (size_t)y * p.W);
+  float4 r[4][4];
 #pragma unroll
   for (int k = 0; k < 4; k++) {
-    cov[k] = uv_shade(p, f[k], x, y, c[k][0], c[k][1], c[k][2]);
+    cov[k] = f[k] >= 0;
+    const bool need = cov[k] && (k == 0 || f[k] != f[k - 1]);
+    if (need) {
+      const float4* q = p.rec + 4 * (size_t)f[k];
+      r[k][0] = q[0];  // plain loads: written by uv_setup_kernel of this call
+      r[k][1] = q[1];
+      r[k][2] = q[2];
+      r[k][3] = q[3];
+    }
+  }
+  int y = (int)((unsigned)base / (unsigned)p.W), x = (int)((unsigned)base - (unsigned)y * (unsigned)p.W);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    if (k > 0 && cov[k] && f[k] == f[k - 1]) {
+      r[k][0] = r[k - 1][0];
+      r[k][1] = r[k - 1][1];
+      r[k][2] = r[k - 1][2];
+      r[k][3] = r[k - 1][3];
+    }
+    c[k][0] = c[k][1] = c[k][2] = 0.f;
+    if (cov[k]) {
+      UvTri t;
+      t.x0 = r[k][0].x; t.y0 = r[k][0].y; t.x1 = r[k][0].z; t.y1 = r[k][0].w;
+      t.x2 = r[k][1].x; t.y2 = r[k][1].y; t.inv_area = r[k][1].z;
+      float w0, w1, w2;
+      uv_weights(t, (float)x, (float)y, w0, w1, w2);
+      c[k][0] = (w0 * r[k][1].w + w1 * r[k][2].z) + w2 * r[k][3].y;
+      c[k][1] = (w0 * r[k][2].x + w1 * r[k][2].w) + w2 * r[k][3].z;
+      c[k][2] = (w0 * r[k][2].y + w1 * r[k][3].x) + w2 * r[k][3].w;
+    }
     if (++x == p.W) {
       x = 0;
       ++y;
@@ -299,6 +357,40 @@ __global__ void __launch_bounds__(256) uv_resolve_kernel(const UvRasterParams p)
         else if (!p.keep_mask) p.mask[base + k] = 0;
       }
     }
+  }
+}
+
+// A CTA owns 256 * 16 consecutive texels; group j of thread t is the 4 texels at
+// cta_base + j * 1024 + 4 t (every load / store instruction of a warp is contiguous).  All winner
+// loads of a thread are issued before the first is consumed: with the L2 cold, a single 16-byte
+// request per thread leaves too few bytes in flight to cover the DRAM latency.
+__global__ void __launch_bounds__(256, 2) uv_resolve_kernel(const UvRasterParams p) {
+  const size_t P = (size_t)p.W * p.H;
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.counter[0] = 0ull;  // queue reset for the next call
+  const size_t cta_base = (size_t)blockIdx.x * (256u * 4u * kUvGroupsPerThread);
+  int f[kUvGroupsPerThread][4];
+  size_t base[kUvGroupsPerThread];
+#pragma unroll
+  for (int j = 0; j < kUvGroupsPerThread; j++) {
+    base[j] = cta_base + (size_t)j * 1024u + (size_t)threadIdx.x * 4u;
+    f[j][0] = f[j][1] = f[j][2] = f[j][3] = -1;
+    if (base[j] + 3 < P) {
+      const int4 w = *reinterpret_cast<const int4*>(p.win + base[j]);
+      f[j][0] = w.x; f[j][1] = w.y; f[j][2] = w.z; f[j][3] = w.w;
+    } else {
+      for (int k = 0; k < 4 && base[j] + k < P; k++) f[j][k] = p.win[base[j] + k];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kUvGroupsPerThread; j++) {
+    if (base[j] >= P) continue;
+    const bool full = base[j] + 3 < P;
+    if (full) {
+      *reinterpret_cast<int4*>(p.win + base[j]) = make_int4(-1, -1, -1, -1);
+    } else {
+      for (int k = 0; k < 4 && base[j] + k < P; k++) p.win[base[j] + k] = -1;
+    }
+    uv_resolve_group(p, P, base[j], full, f[j]);
   }
 }
 
