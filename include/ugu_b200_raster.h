@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 3
+#define UGU_B200_ABI_VERSION 4
 
 enum {
   UGU_B200_OK = 0,
@@ -222,6 +222,32 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
 int ugu_b200_uv_mask(ugu_b200_rasterizer* r, int32_t num_faces, int32_t num_uv, const float* uv,
                      const int32_t* uv_indices, int32_t width, int32_t height, int32_t color,
                      uint8_t* mask_host);
+
+/* Face-visibility consumer of rendered face_id maps: the rasterizer-side counterpart
+ * of the per-keyframe face statistics the reference's texturing pipeline collects with BVH rays
+ * (ugu::FaceInfo / FaceInfoPerKeyframe, include/ugu/texturing/visibility_tester.h:135-181;
+ * FaceInfo::CalcStat's max_area_id, src/texturing/visibility_tester.cc:185-218).  There is no
+ * reference function that consumes face_id maps, so the definition below is this library's own:
+ *   pixel_count[f]  pixels owned by face f, summed over the views
+ *   view_count[f]   number of views in which f owns at least one pixel
+ *   best[f]         max over views of ((pixels of f in the view) << 32 | (0xFFFFFFFF - view id)),
+ *                   0 = never visible: the view that sees most of f, ties to the lowest view id
+ * Ids outside [0, num_faces) (-1 = background) are ignored.  The three vectors combine across ranks
+ * by SUM / SUM / MAX, so a multi-GPU job all-reduces 16 bytes per face instead of gathering maps.
+ * _device: `face_id_dev` holds num_views maps of pixels_per_view int32 each (the face_id output of
+ * render_batch); the accumulators are DEVICE arrays of num_faces elements that the caller zeroes
+ * once and may accumulate into over several calls (view ids first_view_id .. + num_views - 1);
+ * asynchronous on `stream`. */
+int ugu_b200_face_visibility_device(ugu_b200_rasterizer* r, const int32_t* face_id_dev,
+                                    int32_t num_views, int64_t pixels_per_view, int32_t first_view_id,
+                                    int32_t num_faces, uint32_t* pixel_count_dev,
+                                    uint32_t* view_count_dev, uint64_t* best_dev, void* stream);
+/* Host form: maps and results in host memory; results are computed from zero for these maps.
+ * best_view[f] = -1 and best_count[f] = 0 for faces never visible.  Any output may be NULL. */
+int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host, int32_t num_views,
+                             int64_t pixels_per_view, int32_t first_view_id, int32_t num_faces,
+                             uint32_t* pixel_count_host, uint32_t* view_count_host,
+                             int32_t* best_view_host, uint32_t* best_count_host);
 
 /* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
 int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);

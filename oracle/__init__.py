@@ -249,6 +249,31 @@ def ref_uv_mask(uv, uv_indices, width, height, color=255):
     return _uv_mask_call(C.CDLL(str(REF_LIB)), "ugu_ref_uv_mask", uv, uv_indices, width, height, color)
 
 
+def face_visibility(face_id_maps, num_faces, first_view_id=0):
+    """numpy restatement of the face-visibility consumer (include/ugu_b200_raster.h,
+    ugu_b200_face_visibility).  PARITY UNPINNED: the reference has no function that consumes face_id
+    maps (its VisibilityTester shoots BVH rays), so this checks the CUDA path against the stated
+    definition only: pixel_count / view_count / best_view (most pixels, ties -> lowest id, -1 =
+    never) / best_count."""
+    maps = np.asarray(face_id_maps, np.int32)
+    if maps.ndim == 2:
+        maps = maps[None]
+    pix = np.zeros(num_faces, np.int64)
+    views = np.zeros(num_faces, np.int64)
+    best_view = np.full(num_faces, -1, np.int64)
+    best_count = np.zeros(num_faces, np.int64)
+    for v, m in enumerate(maps):
+        ids = m[(m >= 0) & (m < num_faces)]
+        c = np.bincount(ids, minlength=num_faces)
+        pix += c
+        views += c > 0
+        better = c > best_count  # strict: an equal count keeps the earlier (lower) view id
+        best_view[better] = first_view_id + v
+        best_count[better] = c[better]
+    return dict(pixel_count=pix.astype(np.uint32), view_count=views.astype(np.uint32),
+                best_view=best_view.astype(np.int32), best_count=best_count.astype(np.uint32))
+
+
 class OracleRef:
     """The compiled, unmodified reference ugu::Rasterizer (present only where oracle/_ref was built)."""
 

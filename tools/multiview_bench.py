@@ -2,7 +2,7 @@
 """Multi-view dispatch over the GPUs of one box (BASELINE.json configs 3 and 5).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port 29511 tools/multiview_bench.py [c5|c3] [--views V] [--gather] [--check K]
+        --master-port 29511 tools/multiview_bench.py [c5|c3] [--views V] [--gather] [--check K] [--visibility]
 
 Every rank uploads the mesh to its own GPU (replicated, read-only), renders its contiguous slice of
 the view list with ONE device-resident batch call (no data-path collective), optionally gathers the
@@ -99,6 +99,26 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     render_ms, total_ms = float(t[0]), float(t[1])
 
+    vis_ms = vis_ok = None
+    if "--visibility" in args:
+        # SURVEY.md 8f consumer: per-face statistics over ALL views without moving a map — render the
+        # local slice in chunks, fold into device accumulators, all-reduce 16 bytes per face
+        mv.render_face_visibility(cams[: 2 * world], F)  # warm-up (scratch allocation)
+        barrier()
+        v0, v1 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
+        v0.record()
+        vis = mv.render_face_visibility(cams, F, chunk_views=32)
+        v1.record()
+        barrier()
+        tv = torch.tensor([v0.elapsed_time(v1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+        vis_ms = float(tv[0])
+        if gathered is not None and rank == 0:  # against a histogram of the gathered maps
+            ids = gathered.reshape(-1)
+            want = torch.bincount(ids[ids >= 0].to(torch.int64), minlength=F)
+            vis_ok = bool(torch.equal(want.to(torch.int32), vis["pixel_count"]))
+
     ok = None
     if check and rank == 0:
         sel = np.linspace(0, len(cams) - 1, check).astype(int)
@@ -116,6 +136,7 @@ def main():
                 "ms_per_view_per_gpu": render_ms / max(1, -(-len(cams) // world)),
                 "gather": gather, "render_plus_gather_ms": total_ms if gather else None,
                 "gathered_bytes": int(gathered.numel() * 4) if gathered is not None else 0,
+                "face_visibility_ms": vis_ms, "face_visibility_equals_histogram_of_gathered_maps": vis_ok,
                 "n_gpu_equals_1_gpu": ok, "checked_views": check, "wall_s": wall,
                 "timing": "CUDA events on the rendering stream, max over ranks, barrier on both sides; "
                           "views back to back (no L2 flush between views of a batch)"}

@@ -82,6 +82,10 @@ SYMBOLS = {
                                             C.c_void_p]),
     "ugu_b200_uv_mask": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32,
                                    C.c_int32, C.c_int32, C.c_void_p]),
+    "ugu_b200_face_visibility_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32,
+                                                  C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ugu_b200_face_visibility": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ugu_b200_rasterizer_set_profiling": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint32]),
     "ugu_b200_rasterizer_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "ugu_b200_rasterizer_reset_stats": (C.c_int, [C.c_void_p]),
@@ -109,7 +113,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 3:
+    if lib.ugu_b200_abi_version() != 4:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

@@ -16,6 +16,7 @@
 
 #include "raster_kernels.cuh"
 #include "uv_raster_kernels.cuh"
+#include "visibility_kernels.cuh"
 #include "ugu_b200_raster.h"
 
 using namespace ugu_b200;
@@ -66,6 +67,10 @@ struct ugu_b200_rasterizer {
   // UV-space rasterization scratch (uv_raster_kernels.cuh)
   DevBuf uv_win, uv_counter, uv_q_face, uv_q_job, uv_rec, uv_in, uv_tex, uv_mask;
   size_t uv_win_clean = 0;  // texels of uv_win known to hold -1
+
+  // face-visibility consumer scratch (visibility_kernels.cuh)
+  DevBuf vis_tmp, vis_in, vis_acc;
+  int vis_tmp_faces = 0;  // faces per slot the scratch was zeroed for
 
   // pinned staging for pageable destinations
   void* staging = nullptr;
@@ -645,7 +650,8 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
   FreeMesh(r);
   DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters,
-                    &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask};
+                    &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask,
+                    &r->vis_tmp, &r->vis_in, &r->vis_acc};
   for (DevBuf* b : bufs) FreeBuf(b);
   for (int i = 0; i < 2; i++) {
     FreeBuf(&r->out_color[i]);
@@ -1247,6 +1253,92 @@ int ugu_b200_uv_mask(ugu_b200_rasterizer* r, int32_t num_faces, int32_t num_uv, 
   if (rc) return rc;
   const size_t P = (size_t)width * height;
   for (size_t i = 0; i < P; i++) mask_host[i] = tex[i * 3];
+  return UGU_B200_OK;
+}
+
+int ugu_b200_face_visibility_device(ugu_b200_rasterizer* r, const int32_t* face_id_dev,
+                                    int32_t num_views, int64_t pixels_per_view, int32_t first_view_id,
+                                    int32_t num_faces, uint32_t* pixel_count_dev,
+                                    uint32_t* view_count_dev, uint64_t* best_dev, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!face_id_dev || !pixel_count_dev || !view_count_dev || !best_dev)
+    return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (num_views < 0 || pixels_per_view <= 0 || num_faces <= 0 || first_view_id < 0 ||
+      pixels_per_view > (1ll << 40) || (long long)first_view_id + num_views > 0x7fffffffll)
+    return Fail(r, UGU_B200_E_INVALID, "bad sizes");
+  if (num_views == 0) return UGU_B200_OK;
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  int rc;
+  const size_t tmp_bytes = (size_t)kVisSlots * (size_t)num_faces * 4;
+  if (r->vis_tmp.bytes < tmp_bytes || r->vis_tmp_faces != num_faces) {
+    // pass 2 leaves the scratch zero, but only in the slot layout (stride = num_faces) it ran with
+    if ((rc = Grow(r, &r->vis_tmp, tmp_bytes))) return rc;
+    CU_TRY(r, cudaMemsetAsync(r->vis_tmp.p, 0, r->vis_tmp.bytes, st));
+    r->vis_tmp_faces = num_faces;
+  }
+  VisParams p;
+  p.face_id = face_id_dev;
+  p.P = (unsigned long long)pixels_per_view;
+  p.F = num_faces;
+  p.first_view_id = first_view_id;
+  p.tmp = (unsigned*)r->vis_tmp.p;
+  p.pixel_count = pixel_count_dev;
+  p.view_count = view_count_dev;
+  p.best = (unsigned long long*)best_dev;
+  const bool vec = (pixels_per_view % 4 == 0) && (((uintptr_t)face_id_dev & 15u) == 0);
+  const unsigned gx = Blocks((size_t)((pixels_per_view + 3) / 4), 256);
+  for (int v0 = 0; v0 < num_views; v0 += kVisSlots) {
+    const dim3 grid(gx, (unsigned)std::min(kVisSlots, num_views - v0));
+    if (vec) {
+      vis_count_kernel<true><<<grid, 256, 0, st>>>(p, v0);
+      vis_fold_kernel<true><<<grid, 256, 0, st>>>(p, v0);
+    } else {
+      vis_count_kernel<false><<<grid, 256, 0, st>>>(p, v0);
+      vis_fold_kernel<false><<<grid, 256, 0, st>>>(p, v0);
+    }
+    r->stats.kernel_launches += 2;
+  }
+  CU_TRY(r, cudaGetLastError());
+  return UGU_B200_OK;
+}
+
+int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host, int32_t num_views,
+                             int64_t pixels_per_view, int32_t first_view_id, int32_t num_faces,
+                             uint32_t* pixel_count_host, uint32_t* view_count_host,
+                             int32_t* best_view_host, uint32_t* best_count_host) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!face_id_host && num_views > 0) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (num_views < 0 || pixels_per_view <= 0 || num_faces <= 0 || first_view_id < 0)
+    return Fail(r, UGU_B200_E_INVALID, "bad sizes");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = r->stream;
+  const size_t map_bytes = (size_t)num_views * (size_t)pixels_per_view * 4;
+  const size_t F = (size_t)num_faces;
+  int rc;
+  if ((rc = Grow(r, &r->vis_in, map_bytes + 16))) return rc;
+  if ((rc = Grow(r, &r->vis_acc, F * 16))) return rc;
+  CU_TRY(r, cudaMemsetAsync(r->vis_acc.p, 0, F * 16, st));
+  if (map_bytes) CU_TRY(r, cudaMemcpyAsync(r->vis_in.p, face_id_host, map_bytes, cudaMemcpyHostToDevice, st));
+  r->stats.h2d_bytes += map_bytes;
+  unsigned long long* best = (unsigned long long*)r->vis_acc.p;
+  uint32_t* pix = (uint32_t*)(best + F);
+  uint32_t* views = pix + F;
+  if ((rc = ugu_b200_face_visibility_device(r, (const int32_t*)r->vis_in.p, num_views, pixels_per_view,
+                                            first_view_id, num_faces, pix, views, (uint64_t*)best, st)))
+    return rc;
+  std::vector<unsigned long long> hb;
+  if (best_view_host || best_count_host) hb.resize(F);
+  std::vector<CopySeg> segs;
+  if (pixel_count_host) segs.push_back({pixel_count_host, pix, F * 4});
+  if (view_count_host) segs.push_back({view_count_host, views, F * 4});
+  if (!hb.empty()) segs.push_back({hb.data(), best, F * 8});
+  if ((rc = CopyOut(r, segs, st))) return rc;
+  for (size_t f = 0; f < hb.size(); f++) {
+    const unsigned long long b = hb[f];
+    if (best_view_host) best_view_host[f] = b ? (int32_t)(0xFFFFFFFFu - (uint32_t)(b & 0xFFFFFFFFull)) : -1;
+    if (best_count_host) best_count_host[f] = (uint32_t)(b >> 32);
+  }
   return UGU_B200_OK;
 }
 

@@ -67,6 +67,29 @@ def gather_view_maps(local: torch.Tensor, num_views: int, mode: str = "contiguou
     return out
 
 
+def decode_best(best: torch.Tensor):
+    """(best_view, best_count) from the packed accumulator `count << 32 | (0xFFFFFFFF - view)`
+    (int64; 0 = never visible -> view -1, count 0)."""
+    count = best >> 32
+    view = 0xFFFFFFFF - (best & 0xFFFFFFFF)
+    view = torch.where(best == 0, torch.full_like(view, -1), view)
+    return view.to(torch.int32), count.to(torch.int32)
+
+
+def reduce_face_visibility(pixel_count: torch.Tensor, view_count: torch.Tensor, best: torch.Tensor,
+                           group=None) -> None:
+    """Combine per-rank face-visibility accumulators in place on every rank: SUM / SUM / MAX.
+    Each rank accumulated over its own (disjoint) views, so this is exactly the statistic over all
+    views.  Tensors are int32 / int32 / int64 views of the u32 / u32 / u64 device arrays (counts
+    stay below 2^31).  16 bytes per face cross NVLink instead of every face_id map."""
+    world, _ = _world_rank(group)
+    if world == 1:
+        return
+    dist.all_reduce(pixel_count, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(view_count, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(best, op=dist.ReduceOp.MAX, group=group)
+
+
 class MultiViewRenderer:
     """Shards `cameras` over the ranks of the default process group and renders the local slice
     with one device-resident batch call.
@@ -76,11 +99,13 @@ class MultiViewRenderer:
     exercise the sharding / gather logic under gloo.)"""
 
     def __init__(self, rasterizer=None, mode: str = "contiguous",
-                 render_local: Optional[Callable] = None, group=None):
+                 render_local: Optional[Callable] = None, group=None,
+                 accumulate: Optional[Callable] = None):
         self.rasterizer = rasterizer
         self.mode = mode
         self.group = group
         self._render_local = render_local or self._render_local_cuda
+        self._accumulate = accumulate or self._accumulate_cuda
 
     def _render_local_cuda(self, cameras: Sequence, outputs: Sequence[str]):
         if self.rasterizer is None:
@@ -119,6 +144,38 @@ class MultiViewRenderer:
         """Render this rank's slice; returns (global view indices, {output: (n_local, H, W[, C])})."""
         idx = self.local_indices(len(cameras))
         return idx, self._render_local([cameras[i] for i in idx], tuple(outputs))
+
+    def render_face_visibility(self, cameras: Sequence, num_faces: int, chunk_views: int = 32):
+        """Per-face visibility statistics over ALL views: every rank renders the
+        face_id maps of its slice `chunk_views` at a time, folds them into device accumulators
+        (ugu_b200_face_visibility_device), and the accumulators are all-reduced — no map leaves its
+        GPU.  Returns {pixel_count, view_count, best_view, best_count} (int32 tensors, every rank)."""
+        idx = self.local_indices(len(cameras))
+        dev = "cuda" if self.rasterizer is not None else "cpu"
+        pix = torch.zeros(num_faces, dtype=torch.int32, device=dev)
+        views = torch.zeros(num_faces, dtype=torch.int32, device=dev)
+        best = torch.zeros(num_faces, dtype=torch.int64, device=dev)
+        runs = []  # consecutive global view ids -> one accumulate call each
+        for i in idx:
+            if runs and runs[-1][-1] + 1 == i and len(runs[-1]) < chunk_views:
+                runs[-1].append(i)
+            else:
+                runs.append([i])
+        for run in runs:
+            outs = self._render_local([cameras[i] for i in run], ("face_id",))
+            maps = outs["face_id"]
+            self._accumulate(maps, run[0], num_faces, pix, views, best)
+        reduce_face_visibility(pix, views, best, self.group)
+        bv, bc = decode_best(best)
+        return dict(pixel_count=pix, view_count=views, best_view=bv, best_count=bc)
+
+    def _accumulate_cuda(self, maps: torch.Tensor, first_view_id: int, num_faces: int, pix, views, best):
+        if self.rasterizer is None:
+            raise RuntimeError("face visibility needs a ugu_b200.Rasterizer (there is no CPU fallback)")
+        n = maps.shape[0]
+        self.rasterizer.face_visibility_device(
+            maps.data_ptr(), n, maps[0].numel(), num_faces, pix.data_ptr(), views.data_ptr(),
+            best.data_ptr(), first_view_id, torch.cuda.current_stream().cuda_stream)
 
     def render_and_gather(self, cameras: Sequence, output: str = "face_id", dst: int = 0):
         """Render, then gather one output of every view to rank `dst` in global view order."""

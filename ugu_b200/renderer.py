@@ -505,6 +505,37 @@ class Rasterizer:
         if rc != N.OK:
             raise RuntimeError(N.last_error(self._h))
 
+    # -- face-visibility consumer of face_id maps (no reference counterpart) --------
+    def face_visibility(self, face_id_maps: np.ndarray, num_faces: int, first_view_id: int = 0) -> dict:
+        """Per-face statistics over a stack of face_id maps (n_views, H, W) int32 in host memory:
+        pixel_count, view_count, best_view (-1 = never visible), best_count — see
+        include/ugu_b200_raster.h (ugu_b200_face_visibility)."""
+        maps = np.ascontiguousarray(face_id_maps, np.int32)
+        if maps.ndim == 2:
+            maps = maps[None]
+        n = maps.shape[0]
+        P = int(np.prod(maps.shape[1:])) if n else 1
+        out = dict(pixel_count=np.zeros(num_faces, np.uint32), view_count=np.zeros(num_faces, np.uint32),
+                   best_view=np.full(num_faces, -1, np.int32), best_count=np.zeros(num_faces, np.uint32))
+        rc = self._lib.ugu_b200_face_visibility(
+            self._h, maps.ctypes.data if n else None, n, P, first_view_id, num_faces,
+            out["pixel_count"].ctypes.data, out["view_count"].ctypes.data, out["best_view"].ctypes.data,
+            out["best_count"].ctypes.data)
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+        return out
+
+    def face_visibility_device(self, face_id: int, num_views: int, pixels_per_view: int, num_faces: int,
+                               pixel_count: int, view_count: int, best: int, first_view_id: int = 0,
+                               stream: int = 0) -> None:
+        """Device-resident form: raw device pointers; accumulates into caller-zeroed arrays of
+        num_faces u32 / u32 / u64 elements, asynchronously on `stream`."""
+        rc = self._lib.ugu_b200_face_visibility_device(
+            self._h, C.c_void_p(face_id), num_views, pixels_per_view, first_view_id, num_faces,
+            C.c_void_p(pixel_count), C.c_void_p(view_count), C.c_void_p(best), C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
     # -- device-resident / batch extensions (no reference counterpart; see INTEGRATION.md) --------
     def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
                       face_id=None, stream: int = 0) -> None:
