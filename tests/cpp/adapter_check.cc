@@ -17,6 +17,7 @@
 #include "ugu/log.h"
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/util/raster_util.h"
 #include "ugu/util/rgbd_util.h"
 #include "ugu/util/camera_util.h"
 #include "ugu/util/geom_util.h"
@@ -192,6 +193,46 @@ int main(int argc, char** argv) {
         if (!static_cast<ugu::RasterizerCuda*>(cuda.get())->Depth2PointCloud(dref, *camera, &p1, gl != 0)) failures++;
         if (CountDiff(p0, p1, 0)) failures++;
       }
+    }
+  }
+  {  // UV-space rasterization: the reference templates (num_threads = 1) vs the CUDA adapter
+    ugu::RasterizerCuda uv_owner{ugu::RendererCpuOption()};
+    if (!uv_owner.valid()) return 2;
+    auto* rc = &uv_owner;
+    const auto& uv = mesh->uv();
+    const auto& uvi = mesh->uv_indices();
+    const auto& vi = mesh->vertex_indices();
+    const auto& col = mesh->vertex_colors();
+    {
+      ugu::Image3b t0, t1;
+      ugu::Image1b m0 = ugu::Image1b::zeros(300, 200), m1 = ugu::Image1b::zeros(300, 200);
+      if (!ugu::RasterizeVertexAttributeToTexture(col, vi, uv, uvi, t0, 200, 300, &m0, 1)) failures++;
+      if (!rc->RasterizeVertexAttributeToTexture(col, vi, uv, uvi, t1, 200, 300, &m1)) failures++;
+      if (CountDiff(t0, t1, 0) || CountDiff(m0, m1, 0)) failures++;
+      // over the existing texture (width/height <= 0), per-face attributes
+      std::vector<Eigen::Vector3f> fa(uvi.size());
+      for (size_t i = 0; i < fa.size(); i++) fa[i] = Eigen::Vector3f(float(i % 251), float(i % 13) * 20.5f, 300.0f - float(i % 7));
+      std::vector<Eigen::Vector3i> half_i(uvi.begin(), uvi.begin() + uvi.size() / 2);
+      std::vector<Eigen::Vector3f> half_a(fa.begin(), fa.begin() + fa.size() / 2);
+      if (!ugu::RasterizeFaceAttributeToTexture(half_a, uv, half_i, t0, -1, -1, nullptr, 1)) failures++;
+      if (!rc->RasterizeFaceAttributeToTexture(half_a, uv, half_i, t1, -1, -1, nullptr)) failures++;
+      if (CountDiff(t0, t1, 0)) failures++;
+    }
+    {
+      ugu::Image3f p0, p1;  // a position map, as app/posmap_gen.cc:74
+      if (!ugu::RasterizeVertexAttributeToTexture(mesh->vertices(), vi, uv, uvi, p0, 257, 129, nullptr, 1)) failures++;
+      if (!rc->RasterizeVertexAttributeToTexture(mesh->vertices(), vi, uv, uvi, p1, 257, 129, nullptr)) failures++;
+      if (CountDiff(p0, p1, 0)) failures++;
+    }
+    {
+      ugu::Image1b g0, g1;
+      if (!ugu::GenerateUvMask(uv, uvi, g0, 200, 128, 96, 1)) failures++;
+      if (!rc->GenerateUvMask(uv, uvi, g1, 200, 128, 96)) failures++;
+      if (CountDiff(g0, g1, 0)) failures++;
+      ugu::Image3b e;
+      std::vector<Eigen::Vector3i> none;
+      if (rc->RasterizeVertexAttributeToTexture(col, none, uv, none, e, 8, 8, nullptr)) failures++;  // false like the reference
+      if (!e.empty()) failures++;
     }
   }
   std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);

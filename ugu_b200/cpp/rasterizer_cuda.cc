@@ -195,6 +195,97 @@ bool RasterizerCuda::Depth2PointCloud(const Image1f& depth, const Camera& camera
   return true;
 }
 
+namespace {
+// Shared body of the four Rasterize*AttributeToTexture overloads.  The Eigen vectors are plain
+// packed float/int triples (and pairs), so data() is exactly the AoS layout the C-ABI takes.
+template <typename ImageT>
+bool UvRaster(ugu_b200_rasterizer* h, const std::vector<Eigen::Vector3f>& attrs,
+              const std::vector<Eigen::Vector3i>* attr_indices, const std::vector<Eigen::Vector2f>& uvs,
+              const std::vector<Eigen::Vector3i>& uv_indices, ImageT& texture, int width, int height,
+              Image1b* mask, int texture_type) {
+  if (h == nullptr) {
+    LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
+    return false;
+  }
+  if (attr_indices != nullptr) {  // raster_util.h:148-151
+    if (attr_indices->empty() || attr_indices->size() != uv_indices.size()) return false;
+  } else if (attrs.empty() || attrs.size() != uv_indices.size()) {  // raster_util.h:238-240
+    return false;
+  }
+  const bool keep = !(width > 0 && height > 0);
+  if (!keep) {
+    texture = ImageT::zeros(height, width);  // raster_util.h:152
+  } else if (texture.empty()) {
+    return false;  // raster_util.h:153-155
+  }
+  if (mask != nullptr && (mask->cols != texture.cols || mask->rows != texture.rows)) {
+    LOGE("RasterizerCuda: mask size differs from the texture size\n");
+    return false;
+  }
+  ugu_b200_uv_raster_desc d{};
+  d.num_attrs = static_cast<int32_t>(attrs.size());
+  d.num_faces = static_cast<int32_t>(uv_indices.size());
+  d.num_uv = static_cast<int32_t>(uvs.size());
+  d.per_face = attr_indices == nullptr ? 1 : 0;
+  d.attrs = attrs.empty() ? nullptr : attrs[0].data();
+  d.attr_indices = attr_indices == nullptr ? nullptr : (*attr_indices)[0].data();
+  d.uv = uvs.empty() ? nullptr : uvs[0].data();
+  d.uv_indices = uv_indices[0].data();
+  d.width = texture.cols;
+  d.height = texture.rows;
+  d.texture_type = texture_type;
+  d.keep_texture = keep ? 1 : 0;
+  d.keep_mask = 1;  // the reference never clears the mask
+  if (ugu_b200_uv_raster(h, &d, texture.data, mask != nullptr ? mask->data : nullptr) != UGU_B200_OK) {
+    LOGE("%s\n", ugu_b200_last_error(h));
+    return false;
+  }
+  return true;
+}
+}  // namespace
+
+bool RasterizerCuda::RasterizeVertexAttributeToTexture(
+    const std::vector<Eigen::Vector3f>& vertex_attrs, const std::vector<Eigen::Vector3i>& vertex_attr_indices,
+    const std::vector<Eigen::Vector2f>& uvs, const std::vector<Eigen::Vector3i>& uv_indices, Image3b& texture,
+    int width, int height, Image1b* mask) const {
+  return UvRaster(pimpl_->handle_, vertex_attrs, &vertex_attr_indices, uvs, uv_indices, texture, width, height, mask, 0);
+}
+bool RasterizerCuda::RasterizeVertexAttributeToTexture(
+    const std::vector<Eigen::Vector3f>& vertex_attrs, const std::vector<Eigen::Vector3i>& vertex_attr_indices,
+    const std::vector<Eigen::Vector2f>& uvs, const std::vector<Eigen::Vector3i>& uv_indices, Image3f& texture,
+    int width, int height, Image1b* mask) const {
+  return UvRaster(pimpl_->handle_, vertex_attrs, &vertex_attr_indices, uvs, uv_indices, texture, width, height, mask, 1);
+}
+bool RasterizerCuda::RasterizeFaceAttributeToTexture(
+    const std::vector<Eigen::Vector3f>& face_attrs, const std::vector<Eigen::Vector2f>& uvs,
+    const std::vector<Eigen::Vector3i>& uv_indices, Image3b& texture, int width, int height, Image1b* mask) const {
+  return UvRaster(pimpl_->handle_, face_attrs, nullptr, uvs, uv_indices, texture, width, height, mask, 0);
+}
+bool RasterizerCuda::RasterizeFaceAttributeToTexture(
+    const std::vector<Eigen::Vector3f>& face_attrs, const std::vector<Eigen::Vector2f>& uvs,
+    const std::vector<Eigen::Vector3i>& uv_indices, Image3f& texture, int width, int height, Image1b* mask) const {
+  return UvRaster(pimpl_->handle_, face_attrs, nullptr, uvs, uv_indices, texture, width, height, mask, 1);
+}
+
+bool RasterizerCuda::GenerateUvMask(const std::vector<Eigen::Vector2f>& uvs,
+                                    const std::vector<Eigen::Vector3i>& uv_indices, Image1b& mask, uint8_t color,
+                                    int width, int height) const {
+  if (pimpl_->handle_ == nullptr) {
+    LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
+    return false;
+  }
+  if (width <= 0 || height <= 0) return false;
+  mask = Image1b::zeros(height, width);  // raster_util.cc:19,26: a fresh image even on failure
+  if (uv_indices.empty()) return false;
+  if (ugu_b200_uv_mask(pimpl_->handle_, static_cast<int32_t>(uv_indices.size()), static_cast<int32_t>(uvs.size()),
+                       uvs.empty() ? nullptr : uvs[0].data(), uv_indices[0].data(), width, height, color,
+                       mask.data) != UGU_B200_OK) {
+    LOGE("%s\n", ugu_b200_last_error(pimpl_->handle_));
+    return false;
+  }
+  return true;
+}
+
 void RasterizerCuda::set_option(const RendererCpuOption& option) {
   option.CopyTo(&pimpl_->option_);  // rasterizer.cc:73-75 (oren_nayar_sigma is not copied)
 }

@@ -11,6 +11,7 @@
 #pragma once
 
 #include <memory>
+#include <vector>
 
 #include "ugu/renderer/cpu/renderer.h"
 
@@ -47,6 +48,33 @@ class RasterizerCuda : public RendererCpu {
   // to 0 when its size differs, pixels with depth < FLT_MIN left as they were.  Pinhole cameras only.
   bool Depth2PointCloud(const Image1f& depth, const Camera& camera, Image3f* point_cloud,
                         bool gl_coord = false) const;
+
+  // ugu::RasterizeVertexAttributeToTexture<T> / RasterizeFaceAttributeToTexture<T> / GenerateUvMask
+  // (include/ugu/util/raster_util.h:139-278, src/util/raster_util.cc:9-27) on this renderer's device,
+  // T = Vec3b or Vec3f, in the reference's sequential semantics (num_threads = 1: the highest
+  // covering face index owns a texel; the reference is racy with more threads).  Same contract:
+  // false for empty / mismatched index arrays, width/height <= 0 rasterises over the existing
+  // texture, the mask (same size as the texture) is in/out.  Out-of-range indices return false.
+  bool RasterizeVertexAttributeToTexture(const std::vector<Eigen::Vector3f>& vertex_attrs,
+                                         const std::vector<Eigen::Vector3i>& vertex_attr_indices,
+                                         const std::vector<Eigen::Vector2f>& uvs,
+                                         const std::vector<Eigen::Vector3i>& uv_indices, Image3b& texture,
+                                         int width = 512, int height = 512, Image1b* mask = nullptr) const;
+  bool RasterizeVertexAttributeToTexture(const std::vector<Eigen::Vector3f>& vertex_attrs,
+                                         const std::vector<Eigen::Vector3i>& vertex_attr_indices,
+                                         const std::vector<Eigen::Vector2f>& uvs,
+                                         const std::vector<Eigen::Vector3i>& uv_indices, Image3f& texture,
+                                         int width = 512, int height = 512, Image1b* mask = nullptr) const;
+  bool RasterizeFaceAttributeToTexture(const std::vector<Eigen::Vector3f>& face_attrs,
+                                       const std::vector<Eigen::Vector2f>& uvs,
+                                       const std::vector<Eigen::Vector3i>& uv_indices, Image3b& texture,
+                                       int width = 512, int height = 512, Image1b* mask = nullptr) const;
+  bool RasterizeFaceAttributeToTexture(const std::vector<Eigen::Vector3f>& face_attrs,
+                                       const std::vector<Eigen::Vector2f>& uvs,
+                                       const std::vector<Eigen::Vector3i>& uv_indices, Image3f& texture,
+                                       int width = 512, int height = 512, Image1b* mask = nullptr) const;
+  bool GenerateUvMask(const std::vector<Eigen::Vector2f>& uvs, const std::vector<Eigen::Vector3i>& uv_indices,
+                      Image1b& mask, uint8_t color, int width = 512, int height = 512) const;
 
   // false when the CUDA library could not create a rasterizer (no B200 / no driver).
   bool valid() const;
