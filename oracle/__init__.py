@@ -274,6 +274,84 @@ def face_visibility(face_id_maps, num_faces, first_view_id=0):
                 best_view=best_view.astype(np.int32), best_count=best_count.astype(np.uint32))
 
 
+def _d2m_pack(nv, nf, has_uv, has_col, have_normals, bufs):
+    v, f, n, fn, uv, col, pc, ni = bufs
+    return dict(vertices=v[:nv].copy(), faces=f[:nf].copy(),
+                normals=n[:nv].copy() if have_normals else np.zeros((0, 3), np.float32),
+                face_normals=fn[:nf].copy(), uv=uv[:nv].copy() if has_uv else np.zeros((0, 2), np.float32),
+                colors=col[:nv].copy() if has_col else np.zeros((0, 3), np.float32),
+                point_cloud=pc, normal_image=ni)
+
+
+def _d2m_bufs(W, H, x_step, y_step):
+    G = max(1, ((W - 1) // max(x_step, 1)) * ((H - 1) // max(y_step, 1)))
+    return (np.zeros((G, 3), np.float32), np.zeros((2 * G, 3), np.int32), np.zeros((G, 3), np.float32),
+            np.zeros((2 * G, 3), np.float32), np.zeros((G, 2), np.float32), np.zeros((G, 3), np.float32),
+            np.zeros((H, W, 3), np.float32), np.zeros((H, W, 3), np.float32))
+
+
+def port_depth2mesh(cam_pod, depth, max_connect_z_diff, x_step=1, y_step=1, gl_coord=False, color=None,
+                    with_vertex_color=False):
+    """Plain-C restatement of ugu::Depth2Mesh (rgbd_util.cc:94-282 + Mesh::CalcNormal).  color None =
+    the depth-only overload, else the textured one.  Returns a dict of arrays or None (= false)."""
+    build_port()
+    lib = C.CDLL(str(PORT_LIB))
+    fn = lib.oracle_depth2mesh
+    fn.restype = C.c_int
+    fn.argtypes = [C.POINTER(_PortCamera), C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float,
+                   C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 9
+    cam = _PortCamera()
+    for name, _ in _PortCamera._fields_:
+        setattr(cam, name, getattr(cam_pod, name))
+    d = np.ascontiguousarray(depth, np.float32)
+    col = None if color is None else np.ascontiguousarray(color, np.uint8)
+    bufs = _d2m_bufs(cam.width, cam.height, x_step, y_step)
+    counts = np.zeros(3, np.int32)
+    rc = fn(C.byref(cam), d.ctypes.data, None if col is None else col.ctypes.data,
+            0 if col is None else col.shape[1], 0 if col is None else col.shape[0],
+            1 if with_vertex_color else 0, float(max_connect_z_diff), x_step, y_step, 1 if gl_coord else 0,
+            *[b.ctypes.data for b in bufs], counts.ctypes.data)
+    if rc != 0:
+        return None
+    return _d2m_pack(int(counts[0]), int(counts[1]), col is not None, col is not None and with_vertex_color,
+                     bool(counts[2]), bufs)
+
+
+def ref_depth2mesh(camera, depth, max_connect_z_diff, x_step=1, y_step=1, gl_coord=False, color=None,
+                   with_vertex_color=False):
+    """The compiled reference's ugu::Depth2Mesh through oracle/_ref."""
+    lib = C.CDLL(str(REF_LIB))
+    lib.ugu_ref_depth2mesh.restype = C.c_int
+    lib.ugu_ref_depth2mesh.argtypes = [C.POINTER(_RefCamera), C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                       C.c_int32, C.c_float, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    lib.ugu_ref_depth2mesh_copy.restype = C.c_int
+    lib.ugu_ref_depth2mesh_copy.argtypes = [C.c_void_p] * 8
+    cam = _RefCamera()
+    cam.width, cam.height = camera.width(), camera.height()
+    cam.fx, cam.fy = float(camera.focal_length()[0]), float(camera.focal_length()[1])
+    cam.cx, cam.cy = float(camera.principal_point()[0]), float(camera.principal_point()[1])
+    cam.c2w = (C.c_double * 16)(*np.asarray(camera.c2w(), np.float64).reshape(-1))
+    d = np.ascontiguousarray(depth, np.float32)
+    col = None if color is None else np.ascontiguousarray(color, np.uint8)
+    out = np.zeros(6, np.int32)
+    rc = lib.ugu_ref_depth2mesh(C.byref(cam), d.ctypes.data, None if col is None else col.ctypes.data,
+                                0 if col is None else col.shape[1], 0 if col is None else col.shape[0],
+                                1 if with_vertex_color else 0, float(max_connect_z_diff), x_step, y_step,
+                                1 if gl_coord else 0, out.ctypes.data)
+    if rc != 0:
+        return None
+    nv, nf = int(out[0]), int(out[1])
+    bufs = _d2m_bufs(cam.width, cam.height, x_step, y_step)
+    have_normals = nf > 0
+    ptrs = [b.ctypes.data for b in bufs]
+    if not have_normals:
+        ptrs[2] = None
+        ptrs[7] = None  # the reference reads normals()[i] of an empty vector here: undefined
+    bad = lib.ugu_ref_depth2mesh_copy(*ptrs)
+    assert bad == 0, "normal_indices / uv_indices differ from vertex_indices"
+    return _d2m_pack(nv, nf, bool(out[2]), bool(out[3]), have_normals, bufs)
+
+
 class OracleRef:
     """The compiled, unmodified reference ugu::Rasterizer (present only where oracle/_ref was built)."""
 

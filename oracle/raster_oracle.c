@@ -500,4 +500,147 @@ int oracle_uv_mask(int32_t num_faces, int32_t num_uv, const float* uv, const int
   return rc;
 }
 
-int oracle_abi_version(void) { return 3; }
+/* Eigen Vector3f::normalized() / normalize() (third_party/eigen/Eigen/src/Core/Dot.h:121-145):
+ * z = squaredNorm() = x*x + (y*y + z*z); if (z > 0) v / sqrt(z) (true divisions), else unchanged. */
+static void normalize3(float* v) {
+  const float z = v[0] * v[0] + (v[1] * v[1] + v[2] * v[2]);
+  if (z > 0.0f) {
+    const float s = sqrtf(z);
+    v[0] = v[0] / s;
+    v[1] = v[1] / s;
+    v[2] = v[2] / s;
+  }
+}
+
+/* Mesh::CalcFaceNormal (src/mesh.cc:339-349) for one face */
+static void face_normal3(const float* a, const float* b, const float* c, float* n) {
+  float v1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]};
+  float v2[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+  normalize3(v1);
+  normalize3(v2);
+  n[0] = v1[1] * v2[2] - v1[2] * v2[1];
+  n[1] = v1[2] * v2[0] - v1[0] * v2[2];
+  n[2] = v1[0] * v2[1] - v1[1] * v2[0];
+  normalize3(n);
+}
+
+/* ugu::Depth2Mesh — Depth2MeshImpl, src/util/rgbd_util.cc:94-282, with PinholeCamera::Unproject
+ * (include/ugu/camera.h:406-413), X2U / Y2V / U2X / V2Y (include/ugu/util/raster_util.h:18-28) and
+ * Mesh::CalcNormal (src/mesh.cc:297-337).  color == NULL: the depth-only overload (no uv, no colours);
+ * else the textured overload (uv always, vertex colours when with_vertex_color).
+ * Caller-sized outputs: vertices / normals / colors hold up to G*3 floats, uv G*2, faces /
+ * face_normals 2*G*3 with G = ((W-1)/x_step) * ((H-1)/y_step) grid points; point_cloud and
+ * normal_image are W*H*3 (zero-filled here like ugu::Init).  counts[0..1] = Nv, Nf.  Any output
+ * except counts may be NULL.  Returns 1 where the reference returns false. */
+int oracle_depth2mesh(const OracleCamera* cam, const float* depth, const uint8_t* color, int32_t cw,
+                      int32_t ch, int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                      int32_t y_step, int32_t gl_coord, float* vertices, int32_t* faces, float* normals,
+                      float* face_normals, float* uv, float* colors, float* point_cloud,
+                      float* normal_image, int32_t* counts) {
+  if (!cam || !depth || !counts) return 1;
+  if (max_connect_z_diff < 0 || x_step < 1 || y_step < 1) return 1; /* rgbd_util.cc:100-112 */
+  const int W = cam->width, H = cam->height;
+  if (color) { /* rgbd_util.cc:121-136 */
+    const float da = (float)W / (float)H, ca = (float)cw / (float)ch;
+    if (fabsf(da - ca) > 0.01f) return 1;
+  }
+  const size_t P = (size_t)W * (size_t)H;
+  int32_t* added = (int32_t*)malloc(P * sizeof(int32_t));
+  float* vbuf = (float*)malloc((P ? P : 1) * 3 * sizeof(float));
+  int32_t* fbuf = (int32_t*)malloc((P ? P : 1) * 6 * sizeof(int32_t));
+  int32_t* vxy = (int32_t*)malloc((P ? P : 1) * 2 * sizeof(int32_t));
+  if (!added || !vbuf || !fbuf || !vxy) {
+    free(added); free(vbuf); free(fbuf); free(vxy);
+    return 1;
+  }
+  for (size_t i = 0; i < P; i++) added[i] = -1;
+  int32_t nv = 0, nf = 0;
+  for (int y = y_step; y < H; y += y_step) {
+    for (int x = x_step; x < W; x += x_step) {
+      const float d = depth[(size_t)y * W + x];
+      if (d < FLT_MIN) continue;
+      float px = ((float)x - cam->cx) * d / cam->fx;
+      float py = ((float)y - cam->cy) * d / cam->fy;
+      float pz = d;
+      if (gl_coord) {
+        py = -py;
+        pz = -pz;
+      }
+      vbuf[nv * 3 + 0] = px;
+      vbuf[nv * 3 + 1] = py;
+      vbuf[nv * 3 + 2] = pz;
+      vxy[nv * 2 + 0] = x;
+      vxy[nv * 2 + 1] = y;
+      float u = ((float)x + 0.5f) / (float)W;            /* X2U */
+      float v = ((float)y + 0.5f) / (float)H;            /* Y2V, flip = false */
+      if (color && with_vertex_color && colors) {
+        const int cx_ = (int)roundf(u * (float)cw - 0.5f); /* U2X */
+        const int cy_ = (int)roundf(v * (float)ch - 0.5f); /* V2Y, flip = false */
+        const uint8_t* t = color + ((size_t)cy_ * cw + cx_) * 3;
+        colors[nv * 3 + 0] = (float)t[0];
+        colors[nv * 3 + 1] = (float)t[1];
+        colors[nv * 3 + 2] = (float)t[2];
+      }
+      if (color && uv) {
+        uv[nv * 2 + 0] = u;
+        uv[nv * 2 + 1] = 1.0f - v;
+      }
+      added[(size_t)y * W + x] = nv;
+      const int32_t ul = added[(size_t)(y - y_step) * W + (x - x_step)];
+      const int32_t up = added[(size_t)(y - y_step) * W + x];
+      const int32_t lf = added[(size_t)y * W + (x - x_step)];
+      const float ul_diff = fabsf(depth[(size_t)(y - y_step) * W + (x - x_step)] - d);
+      const float up_diff = fabsf(depth[(size_t)(y - y_step) * W + x] - d);
+      const float lf_diff = fabsf(depth[(size_t)y * W + (x - x_step)] - d);
+      /* sic: `> 0`, so vertex 0 never joins a face (rgbd_util.cc:222-234) */
+      if (ul > 0 && up > 0 && ul_diff < max_connect_z_diff && up_diff < max_connect_z_diff) {
+        fbuf[nf * 3 + 0] = ul; fbuf[nf * 3 + 1] = nv; fbuf[nf * 3 + 2] = up;
+        nf++;
+      }
+      if (ul > 0 && lf > 0 && ul_diff < max_connect_z_diff && lf_diff < max_connect_z_diff) {
+        fbuf[nf * 3 + 0] = ul; fbuf[nf * 3 + 1] = lf; fbuf[nf * 3 + 2] = nv;
+        nf++;
+      }
+      nv++;
+    }
+  }
+  /* Mesh::CalcNormal: returns early (no normals at all) when there are no faces (mesh.cc:298-300) */
+  float* nsum = (float*)calloc((size_t)(nv ? nv : 1) * 3, sizeof(float));
+  int32_t* ncnt = (int32_t*)calloc((size_t)(nv ? nv : 1), sizeof(int32_t));
+  const int have_normals = nf > 0;
+  for (int32_t i = 0; i < nf; i++) {
+    float n[3];
+    const int32_t* f = fbuf + i * 3;
+    face_normal3(vbuf + f[0] * 3, vbuf + f[1] * 3, vbuf + f[2] * 3, n);
+    if (face_normals) memcpy(face_normals + i * 3, n, sizeof(n));
+    for (int j = 0; j < 3; j++) {
+      for (int k = 0; k < 3; k++) nsum[f[j] * 3 + k] += n[k];
+      ncnt[f[j]]++;
+    }
+  }
+  for (int32_t i = 0; i < nv; i++) {
+    if (ncnt[i] > 0) {
+      for (int k = 0; k < 3; k++) nsum[i * 3 + k] /= (float)ncnt[i];
+      normalize3(nsum + i * 3);
+    } else {
+      nsum[i * 3] = nsum[i * 3 + 1] = nsum[i * 3 + 2] = 0.0f;
+    }
+  }
+  if (vertices) memcpy(vertices, vbuf, (size_t)nv * 3 * sizeof(float));
+  if (faces) memcpy(faces, fbuf, (size_t)nf * 3 * sizeof(int32_t));
+  if (normals && have_normals) memcpy(normals, nsum, (size_t)nv * 3 * sizeof(float));
+  if (point_cloud) memset(point_cloud, 0, P * 3 * sizeof(float));
+  if (normal_image) memset(normal_image, 0, P * 3 * sizeof(float));
+  for (int32_t i = 0; i < nv; i++) {
+    const size_t pix = (size_t)vxy[i * 2 + 1] * W + vxy[i * 2];
+    if (point_cloud) memcpy(point_cloud + pix * 3, vbuf + i * 3, 3 * sizeof(float));
+    if (normal_image && have_normals) memcpy(normal_image + pix * 3, nsum + i * 3, 3 * sizeof(float));
+  }
+  counts[0] = nv;
+  counts[1] = nf;
+  counts[2] = have_normals;
+  free(added); free(vbuf); free(fbuf); free(vxy); free(nsum); free(ncnt);
+  return 0;
+}
+
+int oracle_abi_version(void) { return 4; }

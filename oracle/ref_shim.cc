@@ -315,6 +315,77 @@ int ugu_ref_uv_mask(int32_t num_faces, int32_t num_uv, const float* uv, const in
   return 0;
 }
 
+// ugu::Depth2Mesh (include/ugu/util/rgbd_util.h:27-37, src/util/rgbd_util.cc:94-282,528-545): the step
+// examples/ex02_renderer.cc:156-158 runs on the rendered depth (and colour).  `color` null -> the
+// depth-only overload; else the textured overload (uv + material; vertex colours when asked).
+// The result is held until the next call; out[0..5] = Nv, Nf, has_uv, has_color, W, H.
+static ugu::Mesh g_d2m_mesh;
+static ugu::Image3f g_d2m_pc, g_d2m_nrm;
+int ugu_ref_depth2mesh(const UguRefCamera* cam, const float* depth, const uint8_t* color, int32_t cw,
+                       int32_t ch, int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                       int32_t y_step, int32_t gl_coord, int32_t* out) {
+  ugu::set_log_level(ugu::LogLevel::kError);
+  ugu::PinholeCamera camera(cam->width, cam->height, ToAffine(cam->c2w),
+                            Eigen::Vector2f(cam->cx, cam->cy), Eigen::Vector2f(cam->fx, cam->fy));
+  const size_t P = static_cast<size_t>(cam->width) * cam->height;
+  ugu::Image1f d;
+  ugu::Init(&d, cam->width, cam->height, 0.0f);
+  std::memcpy(d.data, depth, P * 4);
+  g_d2m_mesh.Clear();
+  bool ok;
+  if (color == nullptr) {
+    ok = ugu::Depth2Mesh(d, camera, &g_d2m_mesh, max_connect_z_diff, x_step, y_step, gl_coord != 0,
+                         &g_d2m_pc, &g_d2m_nrm);
+  } else {
+    ugu::Image3b c = ugu::Image3b::zeros(ch, cw);
+    std::memcpy(c.data, color, static_cast<size_t>(cw) * ch * 3);
+    ok = ugu::Depth2Mesh(d, c, camera, &g_d2m_mesh, max_connect_z_diff, x_step, y_step, gl_coord != 0,
+                         "Depth2Mesh_mat", with_vertex_color != 0, &g_d2m_pc, &g_d2m_nrm);
+  }
+  if (!ok) return 1;
+  out[0] = static_cast<int32_t>(g_d2m_mesh.vertices().size());
+  out[1] = static_cast<int32_t>(g_d2m_mesh.vertex_indices().size());
+  out[2] = g_d2m_mesh.uv().empty() ? 0 : 1;
+  out[3] = g_d2m_mesh.vertex_colors().empty() ? 0 : 1;
+  out[4] = g_d2m_pc.cols;
+  out[5] = g_d2m_pc.rows;
+  return 0;
+}
+
+// Copies the held result (any pointer may be null): vertices / normals Nv*3, faces Nf*3 (== the
+// mesh's normal_indices and uv_indices), face normals Nf*3, uv Nv*2, colours Nv*3, the organized
+// point-cloud and normal images W*H*3.  Returns 1 if an index array differs from vertex_indices.
+int ugu_ref_depth2mesh_copy(float* vertices, int32_t* faces, float* normals, float* face_normals,
+                            float* uv, float* colors, float* point_cloud, float* normal_image) {
+  const ugu::Mesh& m = g_d2m_mesh;
+  const size_t nv = m.vertices().size(), nf = m.vertex_indices().size();
+  for (size_t i = 0; i < nv; i++)
+    for (int k = 0; k < 3; k++) {
+      if (vertices) vertices[i * 3 + k] = m.vertices()[i][k];
+      if (normals && i < m.normals().size()) normals[i * 3 + k] = m.normals()[i][k];
+      if (colors && i < m.vertex_colors().size()) colors[i * 3 + k] = m.vertex_colors()[i][k];
+    }
+  if (uv)
+    for (size_t i = 0; i < m.uv().size(); i++) {
+      uv[i * 2] = m.uv()[i][0];
+      uv[i * 2 + 1] = m.uv()[i][1];
+    }
+  int bad = 0;
+  for (size_t i = 0; i < nf; i++)
+    for (int k = 0; k < 3; k++) {
+      if (faces) faces[i * 3 + k] = m.vertex_indices()[i][k];
+      if (face_normals && i < m.face_normals().size()) face_normals[i * 3 + k] = m.face_normals()[i][k];
+      if (i < m.normal_indices().size() && m.normal_indices()[i][k] != m.vertex_indices()[i][k]) bad = 1;
+      if (!m.uv().empty() && (i >= m.uv_indices().size() || m.uv_indices()[i][k] != m.vertex_indices()[i][k])) bad = 1;
+    }
+  if (nf > 0 && m.normal_indices().size() != nf) bad = 1;
+  if (!m.uv().empty() && m.material_ids().size() != nf) bad = 1;
+  const size_t P = static_cast<size_t>(g_d2m_pc.cols) * g_d2m_pc.rows;
+  if (point_cloud) std::memcpy(point_cloud, g_d2m_pc.data, P * 12);
+  if (normal_image) std::memcpy(normal_image, g_d2m_nrm.data, P * 12);
+  return bad;
+}
+
 // --- OBJ loading through the reference (fixture generation only) -------------------------------
 void* ugu_ref_mesh_load_obj(const char* obj_path, const char* mtl_dir) {
   ugu::set_log_level(ugu::LogLevel::kError);
