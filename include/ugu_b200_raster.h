@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 4
+#define UGU_B200_ABI_VERSION 5
 
 enum {
   UGU_B200_OK = 0,
@@ -248,6 +248,48 @@ int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host
                              int64_t pixels_per_view, int32_t first_view_id, int32_t num_faces,
                              uint32_t* pixel_count_host, uint32_t* view_count_host,
                              int32_t* best_view_host, uint32_t* best_count_host);
+
+/* ugu::Depth2Mesh (include/ugu/util/rgbd_util.h:27-37; Depth2MeshImpl, src/util/rgbd_util.cc:94-282,
+ * 528-545; Mesh::CalcNormal, src/mesh.cc:297-349) — the step examples/ex02_renderer.cc:156-158 runs on
+ * the rendered depth and colour: grid points (x = x_step, 2 x_step, .. < W; y likewise) with depth >=
+ * FLT_MIN become vertices in raster order (camera space; y, z negated for gl_coord), each connects to
+ * its upper-left / upper / left neighbours with up to two triangles when the depth differences are
+ * below max_connect_z_diff (and — sic — the neighbours are not vertex 0), then face and vertex
+ * normals.  `color` NULL = the depth-only overload; else the textured overload: uv per vertex, and
+ * nearest-texel vertex colours (float 0..255) when with_vertex_color.  Only size and intrinsics of
+ * `cam` are used; cam->width/height are the depth image's.
+ * Returns UGU_B200_E_INVALID where the reference returns false (negative max_connect_z_diff, steps <
+ * 1, aspect ratios of depth and colour differing by more than 0.01).
+ * The result stays in device memory until the next call; `counts` tells how much to fetch. */
+typedef struct ugu_b200_depth2mesh_counts {
+  int32_t num_vertices;
+  int32_t num_faces;
+  int32_t has_normals;   /* 0 when there are no faces: Mesh::CalcNormal returns early (mesh.cc:298-300) */
+  int32_t has_uv;
+  int32_t has_colors;
+  int32_t reserved;
+} ugu_b200_depth2mesh_counts;
+
+/* Host form: uploads depth (and colour), runs, returns the counts. */
+int ugu_b200_depth_to_mesh(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* depth_host,
+                           const uint8_t* color_host, int32_t color_width, int32_t color_height,
+                           int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                           int32_t y_step, int32_t gl_coord, ugu_b200_depth2mesh_counts* counts);
+/* Device form: depth_dev / color_dev are DEVICE pointers (e.g. outputs of render_device);
+ * asynchronous on `stream`; the counts come with the fetch. */
+int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                  const float* depth_dev, const uint8_t* color_dev, int32_t color_width,
+                                  int32_t color_height, int32_t with_vertex_color,
+                                  float max_connect_z_diff, int32_t x_step, int32_t y_step,
+                                  int32_t gl_coord, void* stream);
+/* Waits for the last depth_to_mesh call and copies its result to HOST arrays (any may be NULL):
+ * vertices / normals / colors num_vertices*3 f32, uv num_vertices*2, faces num_faces*3 i32 (they
+ * are the mesh's vertex_indices, normal_indices and uv_indices alike), face_normals num_faces*3,
+ * point_cloud / normal_image W*H*3 f32 (the organized images of rgbd_util.cc:257-277, zero where
+ * there is no vertex).  `counts` (may be NULL) receives the counts. */
+int ugu_b200_depth_to_mesh_fetch(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* counts,
+                                 float* vertices, int32_t* faces, float* normals, float* face_normals,
+                                 float* uv, float* colors, float* point_cloud, float* normal_image);
 
 /* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
 int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);

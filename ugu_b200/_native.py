@@ -51,6 +51,11 @@ class UvRasterDesc(C.Structure):
                 ("keep_mask", C.c_int32), ("reserved", C.c_int32)]
 
 
+class Depth2MeshCounts(C.Structure):
+    _fields_ = [("num_vertices", C.c_int32), ("num_faces", C.c_int32), ("has_normals", C.c_int32),
+                ("has_uv", C.c_int32), ("has_colors", C.c_int32), ("reserved", C.c_int32)]
+
+
 class Stats(C.Structure):
     _fields_ = [("stage_ms", C.c_double * NUM_STAGES), ("timed_views", C.c_uint64),
                 ("views", C.c_uint64), ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64),
@@ -86,6 +91,13 @@ SYMBOLS = {
                                                   C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ugu_b200_face_visibility": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ugu_b200_depth_to_mesh": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_int32,
+                                         C.c_int32, C.c_int32, C.c_float, C.c_int32, C.c_int32, C.c_int32,
+                                         C.POINTER(Depth2MeshCounts)]),
+    "ugu_b200_depth_to_mesh_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p,
+                                                C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_int32,
+                                                C.c_int32, C.c_int32, C.c_void_p]),
+    "ugu_b200_depth_to_mesh_fetch": (C.c_int, [C.c_void_p, C.POINTER(Depth2MeshCounts)] + [C.c_void_p] * 8),
     "ugu_b200_rasterizer_set_profiling": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint32]),
     "ugu_b200_rasterizer_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "ugu_b200_rasterizer_reset_stats": (C.c_int, [C.c_void_p]),
@@ -113,7 +125,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 4:
+    if lib.ugu_b200_abi_version() != 5:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

@@ -1,0 +1,319 @@
+// sm_100a kernels for ugu::Depth2Mesh: Depth2MeshImpl, reference
+// src/util/rgbd_util.cc:94-282, with PinholeCamera::Unproject (include/ugu/camera.h:406-413), the uv /
+// nearest-colour rules of rgbd_util.cc:171-196 and Mesh::CalcNormal / CalcFaceNormal
+// (src/mesh.cc:297-349) — the step examples/ex02_renderer.cc:156-158 runs on the rendered depth.
+//
+// The reference is one sequential raster scan over the grid points (x = x_step, 2 x_step, .. < W;
+// y likewise): a valid depth appends a vertex, and up to two triangles to its upper-left / upper /
+// left neighbours, so vertex and face numbering are a raster-order compaction.  Here that is a
+// prefix sum: every grid point contributes (1 vertex, 0..2 faces) packed in one 64-bit value;
+// block sums -> single-block scan -> per-block scan give each point its vertex id and first face id.
+// The `index > 0` quirk of rgbd_util.cc:222-234 (vertex 0 never joins a face) only needs to know
+// WHICH grid point becomes vertex 0 — the first valid one, found with an atomicMin beforehand.
+// Vertex normals: Mesh::CalcNormal adds face normals to their three corners in face order; a grid
+// vertex touches at most six faces (its own two, the right neighbour's second, the lower
+// neighbour's first, the lower-right neighbour's two) and raster order is exactly that order, so
+// each vertex sums its (up to) six face normals itself — no atomics, bit-identical sums.
+//
+// Float discipline as in raster_kernels.cuh (--fmad=false, reference association order).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ugu_b200 {
+
+constexpr int kD2MItems = 4;                       // grid points per thread
+constexpr int kD2MBlock = 256 * kD2MItems;         // grid points per CTA
+
+struct D2MParams {
+  int W, H, xs, ys, GX, GY;  // image size, steps, grid points per row / column
+  float fx, fy, cx, cy, th;
+  int gl, with_uv, with_color, cw, ch;
+  const float* depth;
+  const uint8_t* color;      // cw * ch * 3 or null
+  int* first;                // [0] = first valid grid point (INT_MAX if none)
+  unsigned long long* block_sums;  // per CTA packed (faces << 32 | vertices), scanned in place
+  unsigned long long* totals;      // [0] packed totals
+  int* vid;                  // per grid point: vertex id or -1
+  unsigned* fref;            // per grid point: first face id | has_t1 << 30 | has_t2 << 31
+  float* vertices;           // Nv * 3
+  int* faces;                // Nf * 3
+  float* normals;            // Nv * 3
+  float* face_normals;       // Nf * 3
+  float* uv;                 // Nv * 2
+  float* colors;             // Nv * 3
+  float* point_cloud;        // W*H*3 (pre-zeroed) or null
+  float* normal_image;       // W*H*3 (pre-zeroed) or null
+};
+
+__device__ __forceinline__ float d2m_depth(const D2MParams& p, int gx, int gy) {
+  return __ldg(p.depth + (size_t)((gy + 1) * p.ys) * p.W + (size_t)((gx + 1) * p.xs));
+}
+// the pixel (gx, gy) - one step; gx / gy may be -1 (pixel column / row 0, never a vertex)
+__device__ __forceinline__ bool d2m_valid(float d) { return !(d < 1.17549435e-38f); }  // rgbd_util.cc:158
+
+__device__ __forceinline__ void d2m_unproject(const D2MParams& p, int gx, int gy, float d, float (&o)[3]) {
+  const float x = (float)((gx + 1) * p.xs), y = (float)((gy + 1) * p.ys);
+  o[0] = (x - p.cx) * d / p.fx;  // camera.h:406-413
+  o[1] = (y - p.cy) * d / p.fy;
+  o[2] = d;
+  if (p.gl) {
+    o[1] = -o[1];
+    o[2] = -o[2];
+  }
+}
+
+// Which of the two triangles of grid point (gx, gy) exist (rgbd_util.cc:222-234).  A neighbour's
+// "index > 0" == it is a vertex and not vertex 0 (= grid point `first`).  Neighbours in pixel row /
+// column 0 are never vertices, but their depth still enters the difference test.
+__device__ __forceinline__ unsigned d2m_tris(const D2MParams& p, int gx, int gy, float d, int first) {
+  const size_t px = (size_t)((gx + 1) * p.xs), py = (size_t)((gy + 1) * p.ys);
+  const float d_ul = __ldg(p.depth + (py - p.ys) * p.W + (px - p.xs));
+  const float d_up = __ldg(p.depth + (py - p.ys) * p.W + px);
+  const float d_lf = __ldg(p.depth + py * p.W + (px - p.xs));
+  const int g = gy * p.GX + gx;
+  const bool ul = gx > 0 && gy > 0 && d2m_valid(d_ul) && (g - p.GX - 1) != first;
+  const bool up = gy > 0 && d2m_valid(d_up) && (g - p.GX) != first;
+  const bool lf = gx > 0 && d2m_valid(d_lf) && (g - 1) != first;
+  const bool c_ul = fabsf(d_ul - d) < p.th, c_up = fabsf(d_up - d) < p.th, c_lf = fabsf(d_lf - d) < p.th;
+  return ((ul && up && c_ul && c_up) ? 1u : 0u) | ((ul && lf && c_ul && c_lf) ? 2u : 0u);
+}
+
+// packed contribution of grid point g: vertices in the low word, faces in the high word
+__device__ __forceinline__ unsigned long long d2m_contrib(const D2MParams& p, int g, int G, int first,
+                                                          unsigned& tris) {
+  tris = 0u;
+  if (g >= G) return 0ull;
+  const int gy = g / p.GX, gx = g - gy * p.GX;
+  const float d = d2m_depth(p, gx, gy);
+  if (!d2m_valid(d)) return 0ull;
+  tris = d2m_tris(p, gx, gy, d, first);
+  return 1ull | ((unsigned long long)__popc(tris) << 32);
+}
+
+// exclusive scan of one value per thread over a 256-thread CTA; returns the CTA total in `total`
+__device__ __forceinline__ unsigned long long d2m_block_scan(unsigned long long v, unsigned long long& total) {
+  __shared__ unsigned long long s_w[8];
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  unsigned long long incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (unsigned)d) incl += o;
+  }
+  __syncthreads();  // s_w may still be read by a previous call
+  if (lane == 31u) s_w[warp] = incl;
+  __syncthreads();
+  unsigned long long base = 0ull, tot = 0ull;
+#pragma unroll
+  for (int w = 0; w < 8; w++) {
+    if ((unsigned)w < warp) base += s_w[w];
+    tot += s_w[w];
+  }
+  total = tot;
+  return base + incl - v;
+}
+
+// D2M-K1: index of the first valid grid point (it becomes vertex 0)
+__global__ void __launch_bounds__(256) d2m_first_kernel(const D2MParams p) {
+  const int G = p.GX * p.GY;
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  int mine = 0x7fffffff;
+  if (g < G) {
+    const int gy = g / p.GX, gx = g - gy * p.GX;
+    if (d2m_valid(d2m_depth(p, gx, gy))) mine = g;
+  }
+  mine = __reduce_min_sync(0xffffffffu, mine);
+  if ((threadIdx.x & 31u) == 0u && mine != 0x7fffffff) atomicMin(p.first, mine);
+}
+
+// D2M-K2: per-CTA sums of the packed contributions
+__global__ void __launch_bounds__(256) d2m_count_kernel(const D2MParams p) {
+  const int G = p.GX * p.GY;
+  const int first = p.first[0];
+  const int g0 = blockIdx.x * kD2MBlock + threadIdx.x * kD2MItems;
+  unsigned long long sum = 0ull;
+#pragma unroll
+  for (int k = 0; k < kD2MItems; k++) {
+    unsigned tris;
+    sum += d2m_contrib(p, g0 + k, G, first, tris);
+  }
+  unsigned long long total;
+  (void)d2m_block_scan(sum, total);
+  if (threadIdx.x == 0) p.block_sums[blockIdx.x] = total;
+}
+
+// D2M-K3: exclusive scan of the CTA sums (one CTA, running carry) + the totals
+__global__ void __launch_bounds__(256) d2m_scan_kernel(const D2MParams p, int nblocks) {
+  unsigned long long carry = 0ull;
+  for (int base = 0; base < nblocks; base += 256) {
+    const int i = base + (int)threadIdx.x;
+    const unsigned long long v = i < nblocks ? p.block_sums[i] : 0ull;
+    unsigned long long total;
+    const unsigned long long excl = d2m_block_scan(v, total);
+    if (i < nblocks) p.block_sums[i] = carry + excl;
+    carry += total;
+  }
+  if (threadIdx.x == 0) p.totals[0] = carry;
+}
+
+// D2M-K4: vertex ids / first face ids of every grid point (CTA-local scan + the scanned CTA sums),
+// and everything that belongs to the vertex alone: position, uv, nearest colour, point-cloud texel.
+__global__ void __launch_bounds__(256) d2m_emit_vertices_kernel(const D2MParams p) {
+  const int G = p.GX * p.GY;
+  const int first = p.first[0];
+  const int g0 = blockIdx.x * kD2MBlock + threadIdx.x * kD2MItems;
+  unsigned long long c[kD2MItems];
+  unsigned tris[kD2MItems];
+  unsigned long long sum = 0ull;
+#pragma unroll
+  for (int k = 0; k < kD2MItems; k++) {
+    c[k] = d2m_contrib(p, g0 + k, G, first, tris[k]);
+    sum += c[k];
+  }
+  unsigned long long total;
+  unsigned long long run = p.block_sums[blockIdx.x] + d2m_block_scan(sum, total);
+#pragma unroll
+  for (int k = 0; k < kD2MItems; k++) {
+    const int g = g0 + k;
+    if (g >= G) break;
+    if (c[k] == 0ull) {
+      p.vid[g] = -1;
+      p.fref[g] = 0u;
+      continue;
+    }
+    const int v = (int)(run & 0xFFFFFFFFull);
+    const unsigned f0 = (unsigned)(run >> 32);
+    run += c[k];
+    p.vid[g] = v;
+    p.fref[g] = f0 | (tris[k] << 30);
+    const int gy = g / p.GX, gx = g - gy * p.GX;
+    float pos[3];
+    d2m_unproject(p, gx, gy, d2m_depth(p, gx, gy), pos);
+    p.vertices[3 * (size_t)v + 0] = pos[0];
+    p.vertices[3 * (size_t)v + 1] = pos[1];
+    p.vertices[3 * (size_t)v + 2] = pos[2];
+    const int x = (gx + 1) * p.xs, y = (gy + 1) * p.ys;
+    if (p.point_cloud) {  // rgbd_util.cc:257-266
+      float* q = p.point_cloud + 3 * ((size_t)y * p.W + x);
+      q[0] = pos[0]; q[1] = pos[1]; q[2] = pos[2];
+    }
+    if (p.with_uv || p.with_color) {
+      const float u = ((float)x + 0.5f) / (float)p.W;   // X2U, raster_util.h:22-24
+      const float w = ((float)y + 0.5f) / (float)p.H;   // Y2V, flip = false
+      if (p.with_color) {  // nearest colour texel, rgbd_util.cc:178-190
+        const int tx = __float2int_rz(roundf(u * (float)p.cw - 0.5f));
+        const int ty = __float2int_rz(roundf(w * (float)p.ch - 0.5f));
+        const int txc = min(max(tx, 0), p.cw - 1), tyc = min(max(ty, 0), p.ch - 1);  // in range on contract
+        const uint8_t* t = p.color + 3 * ((size_t)tyc * p.cw + txc);
+        p.colors[3 * (size_t)v + 0] = (float)t[0];
+        p.colors[3 * (size_t)v + 1] = (float)t[1];
+        p.colors[3 * (size_t)v + 2] = (float)t[2];
+      }
+      if (p.with_uv) {  // rgbd_util.cc:192-195
+        p.uv[2 * (size_t)v + 0] = u;
+        p.uv[2 * (size_t)v + 1] = 1.0f - w;
+      }
+    }
+  }
+}
+
+// Vector3f::normalized(): x*x + (y*y + z*z), true divisions (Eigen Dot.h:121-145)
+__device__ __forceinline__ void d2m_normalize(float (&v)[3]) {
+  const float z = v[0] * v[0] + (v[1] * v[1] + v[2] * v[2]);
+  if (z > 0.0f) {
+    const float s = sqrtf(z);
+    v[0] = v[0] / s;
+    v[1] = v[1] / s;
+    v[2] = v[2] / s;
+  }
+}
+
+// D2M-K5: the (up to two) triangles of every vertex grid point and their face normals
+// (Mesh::CalcFaceNormal, src/mesh.cc:339-349).
+__global__ void __launch_bounds__(256) d2m_emit_faces_kernel(const D2MParams p) {
+  const int G = p.GX * p.GY;
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  const unsigned fr = p.fref[g];
+  const unsigned tris = fr >> 30;
+  if (tris == 0u) return;
+  unsigned f = fr & 0x3FFFFFFFu;
+  const int cur = p.vid[g], ul = p.vid[g - p.GX - 1];
+  const float* vc = p.vertices + 3 * (size_t)cur;
+  const float* vu = p.vertices + 3 * (size_t)ul;
+#pragma unroll
+  for (int t = 0; t < 2; t++) {
+    if (!(tris & (1u << t))) continue;
+    // t = 0: (upper_left, current, upper); t = 1: (upper_left, left, current)
+    const int other = t == 0 ? p.vid[g - p.GX] : p.vid[g - 1];
+    const int i1 = t == 0 ? cur : other, i2 = t == 0 ? other : cur;
+    const float* v1p = t == 0 ? vc : p.vertices + 3 * (size_t)other;
+    const float* v2p = t == 0 ? p.vertices + 3 * (size_t)other : vc;
+    p.faces[3 * (size_t)f + 0] = ul;
+    p.faces[3 * (size_t)f + 1] = i1;
+    p.faces[3 * (size_t)f + 2] = i2;
+    float a[3] = {v1p[0] - vu[0], v1p[1] - vu[1], v1p[2] - vu[2]};
+    float b[3] = {v2p[0] - vu[0], v2p[1] - vu[1], v2p[2] - vu[2]};
+    d2m_normalize(a);
+    d2m_normalize(b);
+    float n[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
+    d2m_normalize(n);
+    p.face_normals[3 * (size_t)f + 0] = n[0];
+    p.face_normals[3 * (size_t)f + 1] = n[1];
+    p.face_normals[3 * (size_t)f + 2] = n[2];
+    f++;
+  }
+}
+
+// D2M-K6: vertex normals (Mesh::CalcNormal, src/mesh.cc:310-336): sum of the adjacent face normals
+// in face order, divided by their number, normalised; zero for unreferenced vertices.
+__global__ void __launch_bounds__(256) d2m_vertex_normals_kernel(const D2MParams p) {
+  const int G = p.GX * p.GY;
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  const int v = p.vid[g];
+  if (v < 0) return;
+  const int gy = g / p.GX, gx = g - gy * p.GX;
+  float s[3] = {0.f, 0.f, 0.f};
+  int cnt = 0;
+  auto add = [&](unsigned f) {
+    s[0] += p.face_normals[3 * (size_t)f + 0];
+    s[1] += p.face_normals[3 * (size_t)f + 1];
+    s[2] += p.face_normals[3 * (size_t)f + 2];
+    cnt++;
+  };
+  auto visit = [&](int q, unsigned want) {  // the triangles `want` (bit 0 = first, bit 1 = second) of grid point q
+    const unsigned fr = p.fref[q];
+    const unsigned tris = fr >> 30;
+    unsigned f = fr & 0x3FFFFFFFu;
+    if (tris & 1u) {
+      if (want & 1u) add(f);
+      f++;
+    }
+    if ((tris & 2u) && (want & 2u)) add(f);
+  };
+  visit(g, 3u);                                              // current in both of its own triangles
+  if (gx + 1 < p.GX) visit(g + 1, 2u);                       // `left` of the right neighbour's second
+  if (gy + 1 < p.GY) visit(g + p.GX, 1u);                    // `upper` of the lower neighbour's first
+  if (gx + 1 < p.GX && gy + 1 < p.GY) visit(g + p.GX + 1, 3u);  // `upper_left` of the lower-right's two
+  if (cnt > 0) {
+    const float c = (float)cnt;
+    s[0] = s[0] / c;
+    s[1] = s[1] / c;
+    s[2] = s[2] / c;
+    d2m_normalize(s);
+  } else {
+    s[0] = s[1] = s[2] = 0.f;
+  }
+  p.normals[3 * (size_t)v + 0] = s[0];
+  p.normals[3 * (size_t)v + 1] = s[1];
+  p.normals[3 * (size_t)v + 2] = s[2];
+  if (p.normal_image) {  // rgbd_util.cc:268-277
+    float* q = p.normal_image + 3 * ((size_t)((gy + 1) * p.ys) * p.W + (size_t)((gx + 1) * p.xs));
+    q[0] = s[0]; q[1] = s[1]; q[2] = s[2];
+  }
+}
+
+}  // namespace ugu_b200

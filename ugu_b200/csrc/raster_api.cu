@@ -17,6 +17,7 @@
 #include "raster_kernels.cuh"
 #include "uv_raster_kernels.cuh"
 #include "visibility_kernels.cuh"
+#include "depth2mesh_kernels.cuh"
 #include "ugu_b200_raster.h"
 
 using namespace ugu_b200;
@@ -71,6 +72,14 @@ struct ugu_b200_rasterizer {
   // face-visibility consumer scratch (visibility_kernels.cuh)
   DevBuf vis_tmp, vis_in, vis_acc;
   int vis_tmp_faces = 0;  // faces per slot the scratch was zeroed for
+
+  // Depth2Mesh scratch + the device-resident result of the last call (depth2mesh_kernels.cuh)
+  DevBuf d2m_in_depth, d2m_in_color, d2m_small, d2m_block_sums, d2m_vid, d2m_fref, d2m_vertices, d2m_faces,
+      d2m_normals, d2m_face_normals, d2m_uv, d2m_colors, d2m_pc, d2m_nimg;
+  unsigned long long* d2m_totals_host = nullptr;  // pinned: packed (faces << 32 | vertices)
+  cudaStream_t d2m_stream = nullptr;               // stream of the last call
+  int d2m_w = 0, d2m_h = 0, d2m_has_uv = 0, d2m_has_colors = 0;
+  bool d2m_valid = false;
 
   // pinned staging for pageable destinations
   void* staging = nullptr;
@@ -651,7 +660,11 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   FreeMesh(r);
   DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters,
                     &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask,
-                    &r->vis_tmp, &r->vis_in, &r->vis_acc};
+                    &r->vis_tmp, &r->vis_in, &r->vis_acc,
+                    &r->d2m_in_depth, &r->d2m_in_color, &r->d2m_small, &r->d2m_block_sums, &r->d2m_vid,
+                    &r->d2m_fref, &r->d2m_vertices, &r->d2m_faces, &r->d2m_normals, &r->d2m_face_normals,
+                    &r->d2m_uv, &r->d2m_colors, &r->d2m_pc, &r->d2m_nimg};
+  if (r->d2m_totals_host) cudaFreeHost(r->d2m_totals_host);
   for (DevBuf* b : bufs) FreeBuf(b);
   for (int i = 0; i < 2; i++) {
     FreeBuf(&r->out_color[i]);
@@ -1340,6 +1353,160 @@ int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host
     if (best_count_host) best_count_host[f] = (uint32_t)(b >> 32);
   }
   return UGU_B200_OK;
+}
+
+int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                  const float* depth_dev, const uint8_t* color_dev, int32_t color_width,
+                                  int32_t color_height, int32_t with_vertex_color,
+                                  float max_connect_z_diff, int32_t x_step, int32_t y_step,
+                                  int32_t gl_coord, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!cam || !depth_dev) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  r->d2m_valid = false;
+  // rgbd_util.cc:100-112 (the reference's messages)
+  if (max_connect_z_diff < 0) return Fail(r, UGU_B200_E_INVALID, "Depth2Mesh max_connect_z_diff must be positive %f", max_connect_z_diff);
+  if (x_step < 1) return Fail(r, UGU_B200_E_INVALID, "Depth2Mesh x_step must be positive %d", x_step);
+  if (y_step < 1) return Fail(r, UGU_B200_E_INVALID, "Depth2Mesh y_step must be positive %d", y_step);
+  const int W = cam->width, H = cam->height;
+  if (W <= 0 || H <= 0 || (long long)W * H >= (1ll << 28))
+    return Fail(r, UGU_B200_E_INVALID, "depth size %dx%d is invalid", W, H);
+  if (color_dev) {  // rgbd_util.cc:121-136
+    if (color_width <= 0 || color_height <= 0) return Fail(r, UGU_B200_E_INVALID, "colour size is invalid");
+    const float da = (float)W / (float)H, ca = (float)color_width / (float)color_height;
+    if (std::fabs(da - ca) > 0.01f)
+      return Fail(r, UGU_B200_E_INVALID, "Depth2Mesh depth aspect ratio %f and color aspect ratio %f are very different", da, ca);
+  }
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  D2MParams p{};
+  p.W = W; p.H = H; p.xs = x_step; p.ys = y_step;
+  p.GX = (W - 1) / x_step;
+  p.GY = (H - 1) / y_step;
+  p.fx = cam->fx; p.fy = cam->fy; p.cx = cam->cx; p.cy = cam->cy;
+  p.th = max_connect_z_diff;
+  p.gl = gl_coord ? 1 : 0;
+  p.with_uv = color_dev ? 1 : 0;
+  p.with_color = (color_dev && with_vertex_color) ? 1 : 0;
+  p.cw = color_width; p.ch = color_height;
+  p.depth = depth_dev;
+  p.color = color_dev;
+  const size_t G = (size_t)p.GX * (size_t)p.GY, P = (size_t)W * H;
+  const int nblocks = (int)((G + kD2MBlock - 1) / kD2MBlock);
+  int rc;
+  if ((rc = Grow(r, &r->d2m_small, 64))) return rc;
+  if ((rc = Grow(r, &r->d2m_block_sums, (size_t)std::max(nblocks, 1) * 8))) return rc;
+  if ((rc = Grow(r, &r->d2m_vid, std::max<size_t>(G, 1) * 4))) return rc;
+  if ((rc = Grow(r, &r->d2m_fref, std::max<size_t>(G, 1) * 4))) return rc;
+  if ((rc = Grow(r, &r->d2m_vertices, std::max<size_t>(G, 1) * 12))) return rc;
+  if ((rc = Grow(r, &r->d2m_normals, std::max<size_t>(G, 1) * 12))) return rc;
+  if ((rc = Grow(r, &r->d2m_faces, std::max<size_t>(G, 1) * 24))) return rc;
+  if ((rc = Grow(r, &r->d2m_face_normals, std::max<size_t>(G, 1) * 24))) return rc;
+  if (p.with_uv && (rc = Grow(r, &r->d2m_uv, std::max<size_t>(G, 1) * 8))) return rc;
+  if (p.with_color && (rc = Grow(r, &r->d2m_colors, std::max<size_t>(G, 1) * 12))) return rc;
+  if ((rc = Grow(r, &r->d2m_pc, P * 12))) return rc;
+  if ((rc = Grow(r, &r->d2m_nimg, P * 12))) return rc;
+  if (!r->d2m_totals_host) CU_TRY(r, cudaHostAlloc((void**)&r->d2m_totals_host, 16, cudaHostAllocDefault));
+  p.first = (int*)r->d2m_small.p;
+  p.totals = (unsigned long long*)((char*)r->d2m_small.p + 16);
+  p.block_sums = (unsigned long long*)r->d2m_block_sums.p;
+  p.vid = (int*)r->d2m_vid.p;
+  p.fref = (unsigned*)r->d2m_fref.p;
+  p.vertices = (float*)r->d2m_vertices.p;
+  p.faces = (int*)r->d2m_faces.p;
+  p.normals = (float*)r->d2m_normals.p;
+  p.face_normals = (float*)r->d2m_face_normals.p;
+  p.uv = (float*)r->d2m_uv.p;
+  p.colors = (float*)r->d2m_colors.p;
+  p.point_cloud = (float*)r->d2m_pc.p;
+  p.normal_image = (float*)r->d2m_nimg.p;
+  CU_TRY(r, cudaMemsetAsync(r->d2m_small.p, 0x7f, 4, st));          // first = 0x7f7f7f7f > any grid index
+  CU_TRY(r, cudaMemsetAsync((char*)r->d2m_small.p + 16, 0, 8, st));
+  CU_TRY(r, cudaMemsetAsync(r->d2m_pc.p, 0, P * 12, st));            // ugu::Init(point_cloud, .., 0.0f)
+  CU_TRY(r, cudaMemsetAsync(r->d2m_nimg.p, 0, P * 12, st));
+  if (G > 0) {
+    d2m_first_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
+    d2m_count_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
+    d2m_scan_kernel<<<1, 256, 0, st>>>(p, nblocks);
+    d2m_emit_vertices_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
+    d2m_emit_faces_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
+    d2m_vertex_normals_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
+    r->stats.kernel_launches += 6;
+  }
+  CU_TRY(r, cudaGetLastError());
+  CU_TRY(r, cudaMemcpyAsync(r->d2m_totals_host, p.totals, 8, cudaMemcpyDeviceToHost, st));
+  r->d2m_stream = st;
+  r->d2m_w = W;
+  r->d2m_h = H;
+  r->d2m_has_uv = p.with_uv;
+  r->d2m_has_colors = p.with_color;
+  r->d2m_valid = true;
+  return UGU_B200_OK;
+}
+
+namespace {
+int D2MCounts(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* c) {
+  if (!r->d2m_valid) return Fail(r, UGU_B200_E_STATE, "no Depth2Mesh result to fetch");
+  CU_TRY(r, cudaSetDevice(r->device));
+  CU_TRY(r, cudaStreamSynchronize(r->d2m_stream));
+  const unsigned long long t = r->d2m_totals_host[0];
+  c->num_vertices = (int32_t)(t & 0xFFFFFFFFull);
+  c->num_faces = (int32_t)(t >> 32);
+  c->has_normals = c->num_faces > 0 ? 1 : 0;
+  c->has_uv = r->d2m_has_uv;
+  c->has_colors = r->d2m_has_colors;
+  c->reserved = 0;
+  return UGU_B200_OK;
+}
+}  // namespace
+
+int ugu_b200_depth_to_mesh(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* depth_host,
+                           const uint8_t* color_host, int32_t color_width, int32_t color_height,
+                           int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                           int32_t y_step, int32_t gl_coord, ugu_b200_depth2mesh_counts* counts) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (!cam || !depth_host || !counts) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (cam->width <= 0 || cam->height <= 0) return Fail(r, UGU_B200_E_INVALID, "depth size is invalid");
+  if (color_host && (color_width <= 0 || color_height <= 0)) return Fail(r, UGU_B200_E_INVALID, "colour size is invalid");
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t P = (size_t)cam->width * cam->height;
+  int rc;
+  if ((rc = Grow(r, &r->d2m_in_depth, P * 4))) return rc;
+  CU_TRY(r, cudaMemcpyAsync(r->d2m_in_depth.p, depth_host, P * 4, cudaMemcpyHostToDevice, r->stream));
+  r->stats.h2d_bytes += P * 4;
+  const uint8_t* cdev = nullptr;
+  if (color_host) {
+    const size_t cb = (size_t)color_width * color_height * 3;
+    if ((rc = Grow(r, &r->d2m_in_color, cb))) return rc;
+    CU_TRY(r, cudaMemcpyAsync(r->d2m_in_color.p, color_host, cb, cudaMemcpyHostToDevice, r->stream));
+    r->stats.h2d_bytes += cb;
+    cdev = (const uint8_t*)r->d2m_in_color.p;
+  }
+  if ((rc = ugu_b200_depth_to_mesh_device(r, cam, (const float*)r->d2m_in_depth.p, cdev, color_width,
+                                          color_height, with_vertex_color, max_connect_z_diff, x_step,
+                                          y_step, gl_coord, r->stream)))
+    return rc;
+  return D2MCounts(r, counts);
+}
+
+int ugu_b200_depth_to_mesh_fetch(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* counts,
+                                 float* vertices, int32_t* faces, float* normals, float* face_normals,
+                                 float* uv, float* colors, float* point_cloud, float* normal_image) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  ugu_b200_depth2mesh_counts c;
+  int rc = D2MCounts(r, &c);
+  if (rc) return rc;
+  if (counts) *counts = c;
+  const size_t nv = (size_t)c.num_vertices, nf = (size_t)c.num_faces, P = (size_t)r->d2m_w * r->d2m_h;
+  std::vector<CopySeg> segs;
+  if (vertices && nv) segs.push_back({vertices, r->d2m_vertices.p, nv * 12});
+  if (faces && nf) segs.push_back({faces, r->d2m_faces.p, nf * 12});
+  if (normals && nv && c.has_normals) segs.push_back({normals, r->d2m_normals.p, nv * 12});
+  if (face_normals && nf) segs.push_back({face_normals, r->d2m_face_normals.p, nf * 12});
+  if (uv && nv && c.has_uv) segs.push_back({uv, r->d2m_uv.p, nv * 8});
+  if (colors && nv && c.has_colors) segs.push_back({colors, r->d2m_colors.p, nv * 12});
+  if (point_cloud) segs.push_back({point_cloud, r->d2m_pc.p, P * 12});
+  if (normal_image) segs.push_back({normal_image, r->d2m_nimg.p, P * 12});
+  return CopyOut(r, segs, r->d2m_stream);
 }
 
 int ugu_b200_depth_to_u16(const float* depth, uint16_t* depth_w, size_t count) {

@@ -536,6 +536,82 @@ class Rasterizer:
         if rc != N.OK:
             raise RuntimeError(N.last_error(self._h))
 
+    # -- ugu::Depth2Mesh (include/ugu/util/rgbd_util.h:27-37, src/util/rgbd_util.cc:94-282) -------
+    def Depth2Mesh(self, depth: "Image1f", camera: "PinholeCamera", mesh: "Mesh", max_connect_z_diff: float,
+                   x_step: int = 1, y_step: int = 1, gl_coord: bool = False,
+                   point_cloud: Optional["Image3f"] = None, normal: Optional["Image3f"] = None,
+                   color: Optional["Image3b"] = None, with_vertex_color: bool = False) -> bool:
+        """Both overloads of ugu::Depth2Mesh: `color` None = depth only, else the textured one (uv,
+        material = the colour image, vertex colours when asked).  Fills `mesh` like the reference:
+        vertices, vertex_indices, normals + normal_indices + face_normals (Mesh::CalcNormal), uv +
+        uv_indices + materials + material_ids, vertex_colors; `point_cloud` / `normal` are the
+        organized images.  false + log on the reference's error conditions."""
+        if depth.cols != camera.width() or depth.rows != camera.height():  # rgbd_util.cc:113-119
+            LOGE(f"Depth2Mesh depth size ({depth.cols}, {depth.rows}) and camera size "
+                 f"({camera.width()}, {camera.height()}) are different")
+            return False
+        cam = camera.to_native()
+        cnt = N.Depth2MeshCounts()
+        col = None if color is None else np.ascontiguousarray(color.data, np.uint8)
+        rc = self._lib.ugu_b200_depth_to_mesh(
+            self._h, C.byref(cam), np.ascontiguousarray(depth.data, np.float32).ctypes.data,
+            None if col is None else col.ctypes.data, 0 if col is None else color.cols,
+            0 if col is None else color.rows, 1 if with_vertex_color else 0, float(max_connect_z_diff),
+            int(x_step), int(y_step), 1 if gl_coord else 0, C.byref(cnt))
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        nv, nf = cnt.num_vertices, cnt.num_faces
+        v = np.zeros((nv, 3), np.float32)
+        f = np.zeros((nf, 3), np.int32)
+        n = np.zeros((nv if cnt.has_normals else 0, 3), np.float32)
+        fn = np.zeros((nf, 3), np.float32)
+        uv = np.zeros((nv if cnt.has_uv else 0, 2), np.float32)
+        vc = np.zeros((nv if cnt.has_colors else 0, 3), np.float32)
+        if point_cloud is not None:
+            point_cloud._init(depth.cols, depth.rows)
+        if normal is not None:
+            normal._init(depth.cols, depth.rows)
+        rc = self._lib.ugu_b200_depth_to_mesh_fetch(
+            self._h, None, v.ctypes.data, f.ctypes.data, n.ctypes.data if n.size else None,
+            fn.ctypes.data if nf else None, uv.ctypes.data if uv.size else None,
+            vc.ctypes.data if vc.size else None,
+            None if point_cloud is None else point_cloud.data.ctypes.data,
+            None if normal is None else normal.data.ctypes.data)
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        mesh.vertices, mesh.vertex_indices = v, f
+        mesh.normals, mesh.face_normals = n, fn
+        mesh.normal_indices = f.copy() if cnt.has_normals else np.zeros((0, 3), np.int32)
+        mesh.vertex_colors = vc
+        mesh.uv = uv
+        mesh.uv_indices = f.copy() if cnt.has_uv else np.zeros((0, 3), np.int32)
+        mesh.material_ids = np.zeros(nf if cnt.has_uv else 0, np.int32)
+        mesh.materials = [Material(diffuse_tex=color.data.copy())] if color is not None else []
+        return True
+
+    def depth_to_mesh_device(self, camera, depth: int, max_connect_z_diff: float, x_step: int = 1,
+                             y_step: int = 1, gl_coord: bool = False, color: int = 0, color_width: int = 0,
+                             color_height: int = 0, with_vertex_color: bool = False, stream: int = 0) -> None:
+        """Device-resident form: `depth` / `color` are raw device pointers (e.g. outputs of
+        render_device); asynchronous on `stream`; the result stays on the device (depth_to_mesh_counts)."""
+        cam = camera.to_native() if isinstance(camera, PinholeCamera) else camera
+        rc = self._lib.ugu_b200_depth_to_mesh_device(
+            self._h, C.byref(cam), C.c_void_p(depth), C.c_void_p(color) if color else None, color_width,
+            color_height, 1 if with_vertex_color else 0, float(max_connect_z_diff), int(x_step), int(y_step),
+            1 if gl_coord else 0, C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
+    def depth_to_mesh_counts(self) -> dict:
+        """Waits for the last depth_to_mesh call; {num_vertices, num_faces, has_normals, ...}."""
+        cnt = N.Depth2MeshCounts()
+        rc = self._lib.ugu_b200_depth_to_mesh_fetch(self._h, C.byref(cnt), *([None] * 8))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+        return {k: getattr(cnt, k) for k, _ in N.Depth2MeshCounts._fields_ if k != "reserved"}
+
     # -- device-resident / batch extensions (no reference counterpart; see INTEGRATION.md) --------
     def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
                       face_id=None, stream: int = 0) -> None:
