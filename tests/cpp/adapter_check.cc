@@ -235,6 +235,51 @@ int main(int argc, char** argv) {
       if (!e.empty()) failures++;
     }
   }
+  {  // Depth2Mesh on a rendered view: the reference (rgbd_util.cc:94-282) vs the CUDA adapter, both overloads
+    ugu::RendererCpuOption o;
+    o.diffuse_color = ugu::DiffuseColor::kVertex;
+    ugu::Rasterizer rr(o);
+    rr.set_mesh(mesh);
+    if (!rr.PrepareMesh()) return 1;
+    rr.set_camera(camera);
+    ugu::Image3b col;
+    ugu::Image1f dep;
+    if (!rr.Render(&col, &dep, nullptr, nullptr, nullptr)) return 1;
+    ugu::RasterizerCuda rc{ugu::RendererCpuOption()};
+    if (!rc.valid()) return 2;
+    auto same3f = [](const std::vector<Eigen::Vector3f>& a, const std::vector<Eigen::Vector3f>& b) {
+      return a.size() == b.size() && (a.empty() || std::memcmp(a[0].data(), b[0].data(), a.size() * 12) == 0);
+    };
+    auto same3i = [](const std::vector<Eigen::Vector3i>& a, const std::vector<Eigen::Vector3i>& b) {
+      return a.size() == b.size() && (a.empty() || std::memcmp(a[0].data(), b[0].data(), a.size() * 12) == 0);
+    };
+    for (int variant = 0; variant < 4; variant++) {
+      const int xs = variant == 1 ? 2 : 1, ys = variant == 2 ? 3 : 1;
+      const bool gl = variant & 1, tex = variant >= 2, wvc = variant == 3;
+      const float th = variant == 0 ? 0.01f : 0.2f;
+      ugu::Mesh m0, m1;
+      ugu::Image3f p0, p1, n0, n1;
+      const bool ok0 = tex ? ugu::Depth2Mesh(dep, col, *camera, &m0, th, xs, ys, gl, "mat", wvc, &p0, &n0)
+                           : ugu::Depth2Mesh(dep, *camera, &m0, th, xs, ys, gl, &p0, &n0);
+      const bool ok1 = tex ? rc.Depth2Mesh(dep, col, *camera, &m1, th, xs, ys, gl, "mat", wvc, &p1, &n1)
+                           : rc.Depth2Mesh(dep, *camera, &m1, th, xs, ys, gl, &p1, &n1);
+      int bad = 0;
+      if (!ok0 || !ok1) bad++;
+      if (!same3f(m0.vertices(), m1.vertices()) || !same3i(m0.vertex_indices(), m1.vertex_indices())) bad++;
+      if (!same3f(m0.normals(), m1.normals()) || !same3f(m0.face_normals(), m1.face_normals())) bad++;
+      if (!same3i(m0.normal_indices(), m1.normal_indices()) || !same3i(m0.uv_indices(), m1.uv_indices())) bad++;
+      if (!same3f(m0.vertex_colors(), m1.vertex_colors())) bad++;
+      if (m0.uv().size() != m1.uv().size() ||
+          (!m0.uv().empty() && std::memcmp(m0.uv()[0].data(), m1.uv()[0].data(), m0.uv().size() * 8) != 0)) bad++;
+      if (m0.material_ids() != m1.material_ids() || m0.materials().size() != m1.materials().size()) bad++;
+      if (CountDiff(p0, p1, 0) || CountDiff(n0, n1, 0)) bad++;
+      std::printf("Depth2Mesh variant %d: %zu vertices %zu faces  %s\n", variant, m0.vertices().size(),
+                  m0.vertex_indices().size(), bad ? "MISMATCH" : "identical");
+      if (bad || m0.vertex_indices().empty()) failures++;
+    }
+    ugu::Mesh mm;
+    if (rc.Depth2Mesh(dep, *camera, &mm, -1.0f)) failures++;  // false like the reference
+  }
   std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);
   return failures ? 1 : 0;
 }

@@ -286,6 +286,93 @@ bool RasterizerCuda::GenerateUvMask(const std::vector<Eigen::Vector2f>& uvs,
   return true;
 }
 
+namespace {
+bool Depth2MeshCuda(ugu_b200_rasterizer* h, const Image1f& depth, const Image3b* color, const Camera& camera,
+                    Mesh* mesh, float max_connect_z_diff, int x_step, int y_step, bool gl_coord,
+                    const std::string& material_name, bool with_vertex_color, Image3f* point_cloud,
+                    Image3f* normal) {
+  if (h == nullptr) {
+    LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
+    return false;
+  }
+  const auto* pin = dynamic_cast<const PinholeCamera*>(&camera);
+  if (pin == nullptr || dynamic_cast<const OpenCvCamera*>(&camera) != nullptr || mesh == nullptr) {
+    LOGE("RasterizerCuda::Depth2Mesh supports PinholeCamera only\n");
+    return false;
+  }
+  // the reference checks its scalar arguments first (rgbd_util.cc:100-112), then the sizes (:113-119)
+  if (max_connect_z_diff >= 0 && x_step >= 1 && y_step >= 1 &&
+      (depth.cols != camera.width() || depth.rows != camera.height())) {
+    LOGE("Depth2Mesh depth size (%d, %d) and camera size (%d, %d) are different\n", depth.cols, depth.rows,
+         camera.width(), camera.height());
+    return false;
+  }
+  ugu_b200_camera c{};
+  c.width = depth.cols;
+  c.height = depth.rows;
+  c.fx = pin->focal_length().x();
+  c.fy = pin->focal_length().y();
+  c.cx = pin->principal_point().x();
+  c.cy = pin->principal_point().y();
+  ugu_b200_depth2mesh_counts cnt{};
+  if (ugu_b200_depth_to_mesh(h, &c, reinterpret_cast<const float*>(depth.data), color ? color->data : nullptr,
+                             color ? color->cols : 0, color ? color->rows : 0, with_vertex_color ? 1 : 0,
+                             max_connect_z_diff, x_step, y_step, gl_coord ? 1 : 0, &cnt) != UGU_B200_OK) {
+    LOGE("%s\n", ugu_b200_last_error(h));
+    return false;
+  }
+  mesh->Clear();  // rgbd_util.cc:138
+  const size_t nv = static_cast<size_t>(cnt.num_vertices), nf = static_cast<size_t>(cnt.num_faces);
+  std::vector<Eigen::Vector3f> vertices(nv), normals(cnt.has_normals ? nv : 0), face_normals(nf),
+      colors(cnt.has_colors ? nv : 0);
+  std::vector<Eigen::Vector3i> faces(nf);
+  std::vector<Eigen::Vector2f> uvs(cnt.has_uv ? nv : 0);
+  if (point_cloud != nullptr) Init(point_cloud, depth.cols, depth.rows, 0.0f);
+  if (normal != nullptr) Init(normal, depth.cols, depth.rows, 0.0f);
+  if (ugu_b200_depth_to_mesh_fetch(
+          h, nullptr, nv ? vertices[0].data() : nullptr, nf ? faces[0].data() : nullptr,
+          normals.empty() ? nullptr : normals[0].data(), nf ? face_normals[0].data() : nullptr,
+          uvs.empty() ? nullptr : uvs[0].data(), colors.empty() ? nullptr : colors[0].data(),
+          point_cloud ? reinterpret_cast<float*>(point_cloud->data) : nullptr,
+          normal ? reinterpret_cast<float*>(normal->data) : nullptr) != UGU_B200_OK) {
+    LOGE("%s\n", ugu_b200_last_error(h));
+    return false;
+  }
+  mesh->set_vertices(vertices);
+  mesh->set_vertex_indices(faces);
+  if (cnt.has_normals) {  // what Mesh::CalcNormal leaves behind (mesh.cc:297-337)
+    mesh->set_face_normals(face_normals);
+    mesh->set_normals(normals);
+    mesh->set_normal_indices(faces);
+  }
+  if (color != nullptr) {  // rgbd_util.cc:241-253
+    mesh->set_uv(uvs);
+    mesh->set_uv_indices(faces);
+    ObjMaterial material;
+    color->copyTo(material.diffuse_tex);
+    material.name = material_name;
+    mesh->set_materials({material});
+    mesh->set_material_ids(std::vector<int>(nf, 0));
+  }
+  if (cnt.has_colors) mesh->set_vertex_colors(colors);
+  return true;
+}
+}  // namespace
+
+bool RasterizerCuda::Depth2Mesh(const Image1f& depth, const Camera& camera, Mesh* mesh, float max_connect_z_diff,
+                                int x_step, int y_step, bool gl_coord, Image3f* point_cloud,
+                                Image3f* normal) const {
+  return Depth2MeshCuda(pimpl_->handle_, depth, nullptr, camera, mesh, max_connect_z_diff, x_step, y_step,
+                        gl_coord, "illegal_material", false, point_cloud, normal);
+}
+bool RasterizerCuda::Depth2Mesh(const Image1f& depth, const Image3b& color, const Camera& camera, Mesh* mesh,
+                                float max_connect_z_diff, int x_step, int y_step, bool gl_coord,
+                                const std::string& material_name, bool with_vertex_color, Image3f* point_cloud,
+                                Image3f* normal) const {
+  return Depth2MeshCuda(pimpl_->handle_, depth, &color, camera, mesh, max_connect_z_diff, x_step, y_step,
+                        gl_coord, material_name, with_vertex_color, point_cloud, normal);
+}
+
 void RasterizerCuda::set_option(const RendererCpuOption& option) {
   option.CopyTo(&pimpl_->option_);  // rasterizer.cc:73-75 (oren_nayar_sigma is not copied)
 }

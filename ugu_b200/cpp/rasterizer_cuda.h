@@ -11,6 +11,7 @@
 #pragma once
 
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "ugu/renderer/cpu/renderer.h"
@@ -75,6 +76,20 @@ class RasterizerCuda : public RendererCpu {
                                        int width = 512, int height = 512, Image1b* mask = nullptr) const;
   bool GenerateUvMask(const std::vector<Eigen::Vector2f>& uvs, const std::vector<Eigen::Vector3i>& uv_indices,
                       Image1b& mask, uint8_t color, int width = 512, int height = 512) const;
+
+  // ugu::Depth2Mesh, both overloads (include/ugu/util/rgbd_util.h:27-37, src/util/rgbd_util.cc:94-282,
+  // 528-545) on this renderer's device: raster-order vertex / face compaction as a prefix sum, face
+  // and vertex normals as Mesh::CalcNormal computes them.  Fills `mesh` exactly like the reference
+  // (vertices, vertex_indices, normals / normal_indices / face_normals, and for the textured
+  // overload uv / uv_indices / materials / material_ids and optional vertex colours) and the
+  // organized point-cloud / normal images.  Same false returns.  Pinhole cameras only.
+  bool Depth2Mesh(const Image1f& depth, const Camera& camera, Mesh* mesh, float max_connect_z_diff,
+                  int x_step = 1, int y_step = 1, bool gl_coord = false, Image3f* point_cloud = nullptr,
+                  Image3f* normal = nullptr) const;
+  bool Depth2Mesh(const Image1f& depth, const Image3b& color, const Camera& camera, Mesh* mesh,
+                  float max_connect_z_diff, int x_step = 1, int y_step = 1, bool gl_coord = false,
+                  const std::string& material_name = "Depth2Mesh_mat", bool with_vertex_color = false,
+                  Image3f* point_cloud = nullptr, Image3f* normal = nullptr) const;
 
   // false when the CUDA library could not create a rasterizer (no B200 / no driver).
   bool valid() const;

@@ -125,7 +125,8 @@ __global__ void __launch_bounds__(256) d2m_first_kernel(const D2MParams p) {
     if (d2m_valid(d2m_depth(p, gx, gy))) mine = g;
   }
   mine = __reduce_min_sync(0xffffffffu, mine);
-  if ((threadIdx.x & 31u) == 0u && mine != 0x7fffffff) atomicMin(p.first, mine);
+  // the value only ever decreases: a warp that cannot lower it skips the (same-address) atomic
+  if ((threadIdx.x & 31u) == 0u && mine != 0x7fffffff && mine < *(volatile int*)p.first) atomicMin(p.first, mine);
 }
 
 // D2M-K2: per-CTA sums of the packed contributions
