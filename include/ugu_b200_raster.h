@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 5
+#define UGU_B200_ABI_VERSION 6
 
 enum {
   UGU_B200_OK = 0,
@@ -290,6 +290,46 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
 int ugu_b200_depth_to_mesh_fetch(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* counts,
                                  float* vertices, int32_t* faces, float* normals, float* face_normals,
                                  float* uv, float* colors, float* point_cloud, float* normal_image);
+
+/* G-buffer outputs: the fields of ugu::GBuffer (include/ugu/renderer/base.h:34-77) as
+ * RendererGl::ReadGbuf fills them (src/renderer/gl/renderer.cc:501-650) from the gbuf shaders
+ * (src/shader/glsl/vert/gbuf.vert:42-56, geom/dummy.geom:26-80, frag/gbuf.frag:21-44), computed from the
+ * winners of THIS rasterizer (the CPU Rasterizer's sampling rule, rasterizer.cc:194-237) — the GL
+ * pipeline itself is not available headless.  Exact per-field definition and float op order: the header
+ * comment of ugu_b200/csrc/gbuffer_kernels.cuh.  Summary, per pixel with a visible winner (face f, depth
+ * z, weights (1-u-v, u, v)) whose window depth d lies in (0, 1):
+ *   stencil 255, depth_01 = d, face_id = f + 1, geo_id = opt.geo_id, bary = (u, v, 1-u-v),
+ *   pos_wld, pos_cam = w2c_t + w2c_R pos_wld, normal_wld (normalised interpolated vertex normal, or the
+ *   flat face normal), normal_cam = w2c_R normal_wld, uv = (s, t, 1-s-t); color = the Render colour.
+ * Elsewhere: depth_01 = clamp(d, 0, 1) (1 on background), everything else 0 (face_id 0, not -1).
+ * Sizes: 3-float images W*H*3 f32, depth_01 W*H f32, stencil W*H u8, face_id / geo_id W*H i32, color
+ * W*H*3 u8.  Any pointer may be NULL; all NULL is UGU_B200_E_INVALID.  GBuffer::shaded (the viewer's
+ * deferred lighting pass) is not produced. */
+typedef struct ugu_b200_gbuffer {
+  uint8_t* color;
+  float* normal_cam;
+  float* normal_wld;
+  float* pos_cam;
+  float* pos_wld;
+  float* depth_01;
+  uint8_t* stencil;
+  int32_t* face_id;
+  float* uv;
+  float* bary;
+  int32_t* geo_id;
+} ugu_b200_gbuffer;
+typedef struct ugu_b200_gbuffer_option {
+  float z_near, z_far;   /* RendererGl::SetNearFar (renderer.cc:751-754); 0 < z_near < z_far */
+  int32_t flat_normal;   /* RendererGl::SetFlatNormal: face normal from the world positions */
+  int32_t geo_id;        /* written to geo_id where stencil == 255 (one geometry per rasterizer) */
+} ugu_b200_gbuffer_option;
+/* Host form (synchronous, HOST pointers) and device form (16-byte aligned DEVICE pointers,
+ * asynchronous on `stream`).  Uses the options of set_option for colour and back-face culling. */
+int ugu_b200_rasterizer_render_gbuffer(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                       const ugu_b200_gbuffer_option* opt, const ugu_b200_gbuffer* host_out);
+int ugu_b200_rasterizer_render_gbuffer_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                              const ugu_b200_gbuffer_option* opt,
+                                              const ugu_b200_gbuffer* dev_out, void* stream);
 
 /* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
 int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);

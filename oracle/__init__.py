@@ -152,6 +152,40 @@ class OraclePort:
         return out
 
 
+GBUFFER_FIELDS = (("color", np.uint8, 3), ("normal_cam", np.float32, 3), ("normal_wld", np.float32, 3),
+                  ("pos_cam", np.float32, 3), ("pos_wld", np.float32, 3), ("depth_01", np.float32, 1),
+                  ("stencil", np.uint8, 1), ("face_id", np.int32, 1), ("uv", np.float32, 3),
+                  ("bary", np.float32, 3), ("geo_id", np.int32, 1))
+
+
+class _PortGBuffer(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n, _, _ in GBUFFER_FIELDS]
+
+
+def port_gbuffer(port: "OraclePort", cam_pod, option, z_near, z_far, flat_normal=False, geo_id=0, fields=None):
+    """oracle_gbuffer (oracle/raster_oracle.c): the G-buffer restatement on the port's winners.  PARITY
+    UNPINNED against the reference's OpenGL output (see the C header comment).  None on failure."""
+    lib = port.lib
+    lib.oracle_gbuffer.restype = C.c_int
+    lib.oracle_gbuffer.argtypes = [C.POINTER(_MeshDesc), C.POINTER(_PortCamera), C.POINTER(_PortOption),
+                                   C.c_float, C.c_float, C.c_int32, C.c_int32, C.POINTER(_PortGBuffer)]
+    cam = _PortCamera()
+    for name, _ in _PortCamera._fields_:
+        setattr(cam, name, getattr(cam_pod, name))
+    opt = _PortOption(int(option.diffuse_color), int(option.interp), int(option.shading_normal),
+                      int(option.diffuse_shading), 1 if option.backface_culling else 0,
+                      float(option.depth_scale), 0.3)
+    out, g = {}, _PortGBuffer()
+    for n, dt, ch in GBUFFER_FIELDS:
+        if fields is not None and n not in fields:
+            continue
+        out[n] = np.empty((cam.height, cam.width) if ch == 1 else (cam.height, cam.width, ch), dt)
+        setattr(g, n, out[n].ctypes.data)
+    rc = lib.oracle_gbuffer(C.byref(port.holder.desc), C.byref(cam), C.byref(opt), float(z_near), float(z_far),
+                            1 if flat_normal else 0, int(geo_id), C.byref(g))
+    return out if rc == 0 else None
+
+
 def port_depth2pointcloud(cam_pod, depth, point_cloud=None, gl_coord=False):
     """Plain-C restatement of ugu::Depth2PointCloud (organized Image3f form, rgbd_util.cc:472-513).
     `point_cloud` (H, W, 3) is the in/out image; None = a zero image."""

@@ -137,8 +137,28 @@ static inline int32_t sat_i32(float f) {
   return (int32_t)f;
 }
 
+/* Raw z-buffer state after rasterizer.cc:162-241 and BEFORE the cull / resolve loop (:244-301), for
+ * oracle_gbuffer: winner face (-1 = none), its depth, weights and back-face flag per pixel. */
+typedef struct RawWinners {
+  int32_t* fid;      /* P */
+  float* depth;      /* P */
+  float* weight;     /* P * 3 */
+  uint8_t* backface; /* P */
+  const uint8_t* erase; /* P or NULL: winners to erase before the resolve loop (set by a 2nd pass) */
+} RawWinners;
+
+static int render_impl(const OracleMesh* mesh, const OracleCamera* cam, const OracleOption* opt,
+                       uint8_t* color, float* depth, float* normal, uint8_t* mask, int32_t* face_id,
+                       RawWinners* raw);
+
 int oracle_render(const OracleMesh* mesh, const OracleCamera* cam, const OracleOption* opt,
                   uint8_t* color, float* depth, float* normal, uint8_t* mask, int32_t* face_id) {
+  return render_impl(mesh, cam, opt, color, depth, normal, mask, face_id, NULL);
+}
+
+static int render_impl(const OracleMesh* mesh, const OracleCamera* cam, const OracleOption* opt,
+                       uint8_t* color, float* depth, float* normal, uint8_t* mask, int32_t* face_id,
+                       RawWinners* raw) {
   const int W = cam->width, H = cam->height;
   const size_t P = (size_t)W * (size_t)H;
   const int V = mesh->num_vertices, F = mesh->num_faces;
@@ -251,6 +271,20 @@ int oracle_render(const OracleMesh* mesh, const OracleCamera* cam, const OracleO
         }
       }
     }
+  }
+
+  if (raw) {
+    if (raw->fid) memcpy(raw->fid, fid_, P * sizeof(int32_t));
+    if (raw->depth) memcpy(raw->depth, depth_, P * sizeof(float));
+    if (raw->weight) memcpy(raw->weight, weight, P * 3 * sizeof(float));
+    if (raw->backface) memcpy(raw->backface, backface, P);
+    if (raw->erase)
+      for (size_t i = 0; i < P; i++)
+        if (raw->erase[i]) {
+          depth_[i] = 0.0f;
+          fid_[i] = -1;
+          backface[i] = 0;
+        }
   }
 
   /* rasterizer.cc:244-301 */
@@ -643,4 +677,150 @@ int oracle_depth2mesh(const OracleCamera* cam, const float* depth, const uint8_t
   return 0;
 }
 
-int oracle_abi_version(void) { return 4; }
+/* ---------------------------------------------------------------------------------------------------
+ * G-buffer fields of ugu::GBuffer (include/ugu/renderer/base.h:34-77) as RendererGl::ReadGbuf derives
+ * them (src/renderer/gl/renderer.cc:501-650) from the gbuf shaders (src/shader/glsl/vert/gbuf.vert:42-56,
+ * geom/dummy.geom:26-80, frag/gbuf.frag:21-44), evaluated on the winners of the CPU Rasterizer above.
+ *
+ * PARITY UNPINNED: the reference computes these on an OpenGL pipeline, which cannot run on this box
+ * (no graphics stack), and GL's sampling rule (pixel centres at +0.5, top-left fill, clipping) differs
+ * from the Rasterizer's anyway.  This is a restatement of the shader / read-back arithmetic with a
+ * fixed single-operation float order; its inputs (winner, depth, weights) ARE reference-pinned.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct OracleGBuffer {
+  uint8_t* color;
+  float* normal_cam;
+  float* normal_wld;
+  float* pos_cam;
+  float* pos_wld;
+  float* depth_01;
+  uint8_t* stencil;
+  int32_t* face_id;
+  float* uv;
+  float* bary;
+  int32_t* geo_id;
+} OracleGBuffer;
+
+int oracle_gbuffer(const OracleMesh* mesh, const OracleCamera* cam, const OracleOption* opt, float z_near,
+                   float z_far, int32_t flat_normal, int32_t geo_id, const OracleGBuffer* out) {
+  const int W = cam->width, H = cam->height;
+  if (W <= 0 || H <= 0) return 2;
+  if (!(z_near > 0.0f) || !(z_far > z_near)) return 1;
+  const size_t P = (size_t)W * (size_t)H;
+  RawWinners raw;
+  raw.fid = (int32_t*)malloc(P * 4);
+  raw.depth = (float*)malloc(P * 4);
+  raw.weight = (float*)malloc(P * 12);
+  raw.backface = (uint8_t*)malloc(P);
+  raw.erase = NULL;
+  uint8_t* erase = (uint8_t*)calloc(P, 1);
+  int32_t* tmp_fid = (int32_t*)malloc(P * 4);
+  if (!raw.fid || !raw.depth || !raw.weight || !raw.backface || !erase || !tmp_fid) return 3;
+  OracleOption o1 = *opt; /* pass 1: z-buffer only; colour options must not trip the validations */
+  o1.diffuse_color = 0;
+  o1.diffuse_shading = 0;
+  if (mesh->num_face_normals > 0) o1.shading_normal = 0;
+  int rc = render_impl(mesh, cam, &o1, NULL, NULL, NULL, NULL, tmp_fid, &raw);
+  if (rc) goto done;
+
+  {
+    /* GetProjectionMatrixOpenGlForPinhole, src/util/camera_util.cc:254-255 */
+    const volatile float sum = z_far + z_near, diff = z_far - z_near, two_f = 2.f * z_far;
+    const volatile float two_fn = two_f * z_near;
+    const float A = -sum / diff;
+    const float B = -two_fn / diff;
+    const int have_normals = mesh->num_normals > 0 && mesh->normal_indices != NULL;
+    const int have_uv = mesh->num_uv > 0 && mesh->uv_indices != NULL;
+    float* f3[6] = {out->normal_cam, out->normal_wld, out->pos_cam, out->pos_wld, out->uv, out->bary};
+    for (int k = 0; k < 6; k++)
+      if (f3[k]) memset(f3[k], 0, P * 12);
+    if (out->stencil) memset(out->stencil, 0, P);
+    if (out->face_id) memset(out->face_id, 0, P * 4);
+    if (out->geo_id) memset(out->geo_id, 0, P * 4);
+    for (size_t pi = 0; pi < P; pi++) {
+      if (out->depth_01) out->depth_01[pi] = 1.0f; /* the cleared GL depth */
+      const int32_t fid = raw.fid[pi];
+      if (fid < 0) continue;
+      if (opt->backface_culling && raw.backface[pi] == 255) continue; /* rasterizer.cc:248-252 */
+      const float z = raw.depth[pi];
+      const float ndc = (A * (-z) + B) / z;
+      const float d = 0.5f * ndc + 0.5f;
+      if (out->depth_01) out->depth_01[pi] = fminf(fmaxf(d, 0.0f), 1.0f); /* renderer.cc:541 */
+      if (d <= 0.0f || 1.0f <= d) { /* renderer.cc:534-538; GL clips the fragment */
+        erase[pi] = 1;
+        continue;
+      }
+      if (out->stencil) out->stencil[pi] = 255;
+      if (out->face_id) out->face_id[pi] = fid + 1; /* gbuf.frag:36, renderer.cc:621 */
+      if (out->geo_id) out->geo_id[pi] = geo_id;    /* gbuf.frag:37, renderer.cc:615-620 */
+      const float u = raw.weight[pi * 3 + 1], v = raw.weight[pi * 3 + 2];
+      const float k0 = 1.0f - u - v;
+      if (out->bary) { /* dummy.geom:69-75, renderer.cc:637-640 */
+        out->bary[pi * 3 + 0] = u;
+        out->bary[pi * 3 + 1] = v;
+        out->bary[pi * 3 + 2] = k0;
+      }
+      const int32_t* vi = &mesh->vertex_indices[(size_t)fid * 3];
+      const float* P0 = &mesh->vertices[(size_t)vi[0] * 3];
+      const float* P1 = &mesh->vertices[(size_t)vi[1] * 3];
+      const float* P2 = &mesh->vertices[(size_t)vi[2] * 3];
+      float pw[3], pc[3];
+      for (int k = 0; k < 3; k++) pw[k] = (k0 * P0[k] + u * P1[k]) + v * P2[k]; /* gbuf.vert:43,45 */
+      mat3_mul(cam->w2c_R, pw, pc);
+      for (int k = 0; k < 3; k++) pc[k] = cam->w2c_t[k] + pc[k]; /* renderer.cc:561 */
+      if (out->pos_wld) memcpy(&out->pos_wld[pi * 3], pw, 12);
+      if (out->pos_cam) memcpy(&out->pos_cam[pi * 3], pc, 12);
+      float n[3] = {0.0f, 0.0f, 0.0f}, nc[3];
+      if (flat_normal) { /* dummy.geom:58-59 */
+        float a[3], b[3];
+        for (int k = 0; k < 3; k++) {
+          a[k] = P1[k] - P0[k];
+          b[k] = P2[k] - P0[k];
+        }
+        normalize3(a);
+        normalize3(b);
+        n[0] = a[1] * b[2] - a[2] * b[1];
+        n[1] = a[2] * b[0] - a[0] * b[2];
+        n[2] = a[0] * b[1] - a[1] * b[0];
+        normalize3(n);
+      } else if (have_normals) { /* gbuf.frag:25 */
+        const int32_t* ni = &mesh->normal_indices[(size_t)fid * 3];
+        const float* N0 = &mesh->normals[(size_t)ni[0] * 3];
+        const float* N1 = &mesh->normals[(size_t)ni[1] * 3];
+        const float* N2 = &mesh->normals[(size_t)ni[2] * 3];
+        for (int k = 0; k < 3; k++) n[k] = (k0 * N0[k] + u * N1[k]) + v * N2[k];
+        normalize3(n);
+      }
+      mat3_mul(cam->w2c_R, n, nc); /* renderer.cc:583 */
+      if (out->normal_wld) memcpy(&out->normal_wld[pi * 3], n, 12);
+      if (out->normal_cam) memcpy(&out->normal_cam[pi * 3], nc, 12);
+      if (have_uv && out->uv) { /* renderer.cc:641-644 */
+        const int32_t* ui = &mesh->uv_indices[(size_t)fid * 3];
+        const float* t0 = &mesh->uv[(size_t)ui[0] * 2];
+        const float* t1 = &mesh->uv[(size_t)ui[1] * 2];
+        const float* t2 = &mesh->uv[(size_t)ui[2] * 2];
+        const float s = (k0 * t0[0] + u * t1[0]) + v * t2[0];
+        const float t = (k0 * t0[1] + u * t1[1]) + v * t2[1];
+        out->uv[pi * 3 + 0] = s;
+        out->uv[pi * 3 + 1] = t;
+        out->uv[pi * 3 + 2] = 1.0f - s - t;
+      }
+    }
+  }
+  if (out->color) { /* pass 2: the Rasterizer's colour with the clipped winners erased */
+    RawWinners r2;
+    memset(&r2, 0, sizeof(r2));
+    r2.erase = erase;
+    rc = render_impl(mesh, cam, opt, out->color, NULL, NULL, NULL, NULL, &r2);
+  }
+done:
+  free(raw.fid);
+  free(raw.depth);
+  free(raw.weight);
+  free(raw.backface);
+  free(erase);
+  free(tmp_fid);
+  return rc;
+}
+
+int oracle_abi_version(void) { return 5; }

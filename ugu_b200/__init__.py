@@ -7,10 +7,10 @@ renderer.py (the same interface for Python hosts), multiview.py (view sharding o
 meshgen.py (synthetic inputs).  There is no CPU fallback: importing the renderer without the built
 CUDA library raises.
 """
-from .renderer import (ColorInterpolation, DiffuseColor, DiffuseShading, Image1b, Image1f, Image1i,
+from .renderer import (ColorInterpolation, DiffuseColor, DiffuseShading, GBuffer, Image1b, Image1f, Image1i,
                        Image1w, Image3b, Image3f, Material, Mesh, PinholeCamera, Rasterizer,
                        RendererCpuOption, ShadingNormal)
 
-__all__ = ["ColorInterpolation", "DiffuseColor", "DiffuseShading", "Image1b", "Image1f", "Image1i",
+__all__ = ["ColorInterpolation", "DiffuseColor", "DiffuseShading", "GBuffer", "Image1b", "Image1f", "Image1i",
            "Image1w", "Image3b", "Image3f", "Material", "Mesh", "PinholeCamera", "Rasterizer",
            "RendererCpuOption", "ShadingNormal"]

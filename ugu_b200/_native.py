@@ -56,6 +56,16 @@ class Depth2MeshCounts(C.Structure):
                 ("has_uv", C.c_int32), ("has_colors", C.c_int32), ("reserved", C.c_int32)]
 
 
+class GBuffer(C.Structure):
+    FIELDS = ("color", "normal_cam", "normal_wld", "pos_cam", "pos_wld", "depth_01", "stencil", "face_id",
+              "uv", "bary", "geo_id")
+    _fields_ = [(n, C.c_void_p) for n in FIELDS]
+
+
+class GBufferOption(C.Structure):
+    _fields_ = [("z_near", C.c_float), ("z_far", C.c_float), ("flat_normal", C.c_int32), ("geo_id", C.c_int32)]
+
+
 class Stats(C.Structure):
     _fields_ = [("stage_ms", C.c_double * NUM_STAGES), ("timed_views", C.c_uint64),
                 ("views", C.c_uint64), ("kernel_launches", C.c_uint64), ("h2d_bytes", C.c_uint64),
@@ -98,6 +108,11 @@ SYMBOLS = {
                                                 C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_int32,
                                                 C.c_int32, C.c_int32, C.c_void_p]),
     "ugu_b200_depth_to_mesh_fetch": (C.c_int, [C.c_void_p, C.POINTER(Depth2MeshCounts)] + [C.c_void_p] * 8),
+    "ugu_b200_rasterizer_render_gbuffer": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(GBufferOption),
+                                                     C.POINTER(GBuffer)]),
+    "ugu_b200_rasterizer_render_gbuffer_device": (C.c_int, [C.c_void_p, C.POINTER(Camera),
+                                                            C.POINTER(GBufferOption), C.POINTER(GBuffer),
+                                                            C.c_void_p]),
     "ugu_b200_rasterizer_set_profiling": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint32]),
     "ugu_b200_rasterizer_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "ugu_b200_rasterizer_reset_stats": (C.c_int, [C.c_void_p]),
@@ -125,7 +140,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 5:
+    if lib.ugu_b200_abi_version() != 6:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

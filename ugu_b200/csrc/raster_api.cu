@@ -18,6 +18,7 @@
 #include "uv_raster_kernels.cuh"
 #include "visibility_kernels.cuh"
 #include "depth2mesh_kernels.cuh"
+#include "gbuffer_kernels.cuh"
 #include "ugu_b200_raster.h"
 
 using namespace ugu_b200;
@@ -80,6 +81,8 @@ struct ugu_b200_rasterizer {
   cudaStream_t d2m_stream = nullptr;               // stream of the last call
   int d2m_w = 0, d2m_h = 0, d2m_has_uv = 0, d2m_has_colors = 0;
   bool d2m_valid = false;
+
+  DevBuf gbuf_arena;  // device outputs of the host-form G-buffer call (gbuffer_kernels.cuh)
 
   // pinned staging for pageable destinations
   void* staging = nullptr;
@@ -337,7 +340,7 @@ cudaError_t LaunchView(void (*kernel)(KArgs...), unsigned grid, unsigned block, 
 
 // Launch the four kernels of one view into device outputs `dout` on stream `st`.
 int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
-               cudaStream_t st) {
+               cudaStream_t st, const GBufParams* gbuf = nullptr) {
   int rc = EnsureFrame(r, cam->width, cam->height, st);
   if (rc) return rc;
   ViewParams vp;
@@ -400,6 +403,18 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
     // persistent: exactly one resident wave
     CU_TRY(r, LaunchView(binned_kernel, (unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, st, pdl, vp, m, fr));
+  }
+  if (gbuf) {
+    // G-buffer fields from the finished visibility buffer, before the resolve kernel consumes and
+    // clears it; a plain (fully serialised) launch, so the resolve kernel behind it starts when it ends
+    GBufParams gp = *gbuf;
+    gp.backface_culling = sp.backface_culling;
+    gp.have_normals = (m.num_normals > 0 && r->has_nidx) ? 1 : 0;
+    gp.have_uv = (m.num_uv > 0 && r->has_uvidx) ? 1 : 0;
+    const unsigned chunks = (unsigned)((P + 31) / 32);
+    const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 8), (chunks + 7) / 8));
+    CU_TRY(r, LaunchView(gbuffer_kernel, grid, 256, st, false, vp, m, fr, gp));
+    r->stats.kernel_launches++;
   }
   {
     StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
@@ -675,6 +690,7 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
     if (r->ev_render[i]) cudaEventDestroy(r->ev_render[i]);
     if (r->ev_copied[i]) cudaEventDestroy(r->ev_copied[i]);
   }
+  FreeBuf(&r->gbuf_arena);
   for (auto ev : r->ev_pool)
     if (ev) cudaEventDestroy(ev);
   for (auto ev : r->chunk_events) cudaEventDestroy(ev);
@@ -978,6 +994,111 @@ int ugu_b200_rasterizer_render(ugu_b200_rasterizer* r, const ugu_b200_camera* ca
                             r->stream));
   std::vector<CopySeg> segs;
   CollectSegs(host_out, &dout, P, 0, &segs);
+  if ((rc = CopyOut(r, segs, r->stream))) return rc;
+  SnapshotCounters(r);
+  return UGU_B200_OK;
+}
+
+namespace {
+// Shared front end of the two G-buffer entry points: validation and the kernel parameter block.
+int PrepareGbuf(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_gbuffer_option* opt,
+                const ugu_b200_gbuffer* out, GBufParams* gp) {
+  if (!opt) return Fail(r, UGU_B200_E_INVALID, "gbuffer option is NULL");
+  if (!out || (!out->color && !out->normal_cam && !out->normal_wld && !out->pos_cam && !out->pos_wld &&
+               !out->depth_01 && !out->stencil && !out->face_id && !out->uv && !out->bary && !out->geo_id))
+    return Fail(r, UGU_B200_E_INVALID, "all arguments are nullptr. nothing to do");
+  // the Render preconditions (util_private.cc:12-90); without a colour request only the camera, the
+  // mesh and back-face culling matter, so validate as a depth-only Render
+  ugu_b200_outputs probe{};
+  float dummy = 0.f;
+  if (out->color) probe.color = out->color;
+  else probe.depth = &dummy;
+  ugu_b200_option saved = r->opt;
+  if (!out->color) {
+    r->opt.diffuse_color = UGU_B200_COLOR_NONE;
+    r->opt.diffuse_shading = 0;
+    r->opt.shading_normal = (r->mesh.num_face_normals > 0) ? UGU_B200_NORMAL_FACE : r->opt.shading_normal;
+  }
+  const int rc = Validate(r, cam, &probe);
+  r->opt = saved;
+  if (rc) return rc;
+  if (!(opt->z_near > 0.0f) || !(opt->z_far > opt->z_near))
+    return Fail(r, UGU_B200_E_INVALID, "gbuffer needs 0 < z_near < z_far (got %g, %g)", opt->z_near, opt->z_far);
+  memset(gp, 0, sizeof(*gp));
+  gp->normal_cam = out->normal_cam;
+  gp->normal_wld = out->normal_wld;
+  gp->pos_cam = out->pos_cam;
+  gp->pos_wld = out->pos_wld;
+  gp->depth_01 = out->depth_01;
+  gp->stencil = out->stencil;
+  gp->face_id = out->face_id;
+  gp->uv = out->uv;
+  gp->bary = out->bary;
+  gp->geo_id = out->geo_id;
+  // GetProjectionMatrixOpenGlForPinhole (camera_util.cc:254-255), single float operations
+  const volatile float zn = opt->z_near, zf = opt->z_far;
+  const volatile float sum = zf + zn, diff = zf - zn, two_f = 2.f * zf;
+  const volatile float two_fn = two_f * zn;
+  gp->A = -sum / diff;
+  gp->B = -two_fn / diff;
+  gp->flat_normal = opt->flat_normal ? 1 : 0;
+  gp->geo_id_value = opt->geo_id;
+  return UGU_B200_OK;
+}
+}  // namespace
+
+int ugu_b200_rasterizer_render_gbuffer_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                              const ugu_b200_gbuffer_option* opt,
+                                              const ugu_b200_gbuffer* dev_out, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  GBufParams gp{};
+  int rc = PrepareGbuf(r, cam, opt, dev_out, &gp);
+  if (rc) return rc;
+  const uintptr_t align = (uintptr_t)dev_out->color | (uintptr_t)gp.normal_cam | (uintptr_t)gp.normal_wld |
+                          (uintptr_t)gp.pos_cam | (uintptr_t)gp.pos_wld | (uintptr_t)gp.depth_01 |
+                          (uintptr_t)gp.stencil | (uintptr_t)gp.face_id | (uintptr_t)gp.uv |
+                          (uintptr_t)gp.bary | (uintptr_t)gp.geo_id;
+  if (align & 15u) return Fail(r, UGU_B200_E_INVALID, "device outputs must be 16-byte aligned");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  ugu_b200_outputs dout{};
+  dout.color = dev_out->color;
+  return RenderView(r, cam, &dout, st, &gp);
+}
+
+int ugu_b200_rasterizer_render_gbuffer(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                       const ugu_b200_gbuffer_option* opt, const ugu_b200_gbuffer* host_out) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  GBufParams gp{};
+  int rc = PrepareGbuf(r, cam, opt, host_out, &gp);
+  if (rc) return rc;
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t P = (size_t)cam->width * cam->height;
+  // one device arena for the requested fields (each slice 256-byte aligned)
+  struct Field { void* host; void** dev; size_t bytes; };
+  ugu_b200_outputs dout{};
+  Field fields[] = {
+      {host_out->color, (void**)&dout.color, P * 3},        {host_out->normal_cam, (void**)&gp.normal_cam, P * 12},
+      {host_out->normal_wld, (void**)&gp.normal_wld, P * 12}, {host_out->pos_cam, (void**)&gp.pos_cam, P * 12},
+      {host_out->pos_wld, (void**)&gp.pos_wld, P * 12},     {host_out->depth_01, (void**)&gp.depth_01, P * 4},
+      {host_out->stencil, (void**)&gp.stencil, P},          {host_out->face_id, (void**)&gp.face_id, P * 4},
+      {host_out->uv, (void**)&gp.uv, P * 12},               {host_out->bary, (void**)&gp.bary, P * 12},
+      {host_out->geo_id, (void**)&gp.geo_id, P * 4}};
+  size_t total = 0;
+  for (const Field& f : fields)
+    if (f.host) total += (f.bytes + 255) & ~size_t(255);
+  if ((rc = Grow(r, &r->gbuf_arena, total + 256))) return rc;
+  std::vector<CopySeg> segs;
+  size_t off = 0;
+  for (const Field& f : fields) {
+    if (!f.host) continue;
+    *f.dev = (char*)r->gbuf_arena.p + off;
+    segs.push_back({f.host, *f.dev, f.bytes});
+    off += (f.bytes + 255) & ~size_t(255);
+  }
+  if ((rc = RenderView(r, cam, &dout, r->stream, &gp))) return rc;
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+                            r->stream));
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
   SnapshotCounters(r);
   return UGU_B200_OK;

@@ -252,6 +252,23 @@ class Image1w(Image):
     dtype, channels = np.uint16, 1
 
 
+class GBuffer:
+    """ugu::GBuffer (include/ugu/renderer/base.h:34-77) without `shaded` (the GL viewer's deferred
+    lighting pass): the images RendererGl::ReadGbuf fills (src/renderer/gl/renderer.cc:501-650)."""
+
+    TYPES = {"color": Image3b, "normal_cam": Image3f, "normal_wld": Image3f, "pos_cam": Image3f,
+             "pos_wld": Image3f, "depth_01": Image1f, "stencil": Image1b, "face_id": Image1i, "uv": Image3f,
+             "bary": Image3f, "geo_id": Image1i}
+
+    def __init__(self, pinned: bool = True):
+        for name, cls in self.TYPES.items():
+            setattr(self, name, cls(pinned))
+
+    def Init(self, w: int, h: int) -> None:  # base.h:48-61 (contents are rewritten by every render)
+        for name in self.TYPES:
+            getattr(self, name)._init(w, h)
+
+
 def _ptr(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
@@ -611,6 +628,47 @@ class Rasterizer:
         if rc != N.OK:
             raise RuntimeError(N.last_error(self._h))
         return {k: getattr(cnt, k) for k, _ in N.Depth2MeshCounts._fields_ if k != "reserved"}
+
+    def RenderGBuffer(self, gbuf: GBuffer, z_near: float = 0.01, z_far: float = 1000.0,
+                      flat_normal: bool = False, geo_id: int = 0, fields: Optional[Sequence[str]] = None) -> bool:
+        """The G-buffer of RendererGl::ReadGbuf (src/renderer/gl/renderer.cc:501-650; near / far as
+        RendererGl::SetNearFar, :751-754) from this rasterizer's winners — definition in
+        include/ugu_b200_raster.h (ugu_b200_rasterizer_render_gbuffer).  `fields` restricts the images
+        written (default: all of GBuffer.TYPES); False + log on the Render precondition failures."""
+        if self._camera is None:
+            LOGE("camera has not been set")
+            return False
+        if not self._mesh_initialized:
+            LOGE("mesh has not been initialized")
+            return False
+        opt = self._native_option()
+        self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+        cam = self._camera.to_native()
+        names = list(GBuffer.TYPES) if fields is None else list(fields)
+        out = N.GBuffer()
+        for n in names:
+            im = getattr(gbuf, n)
+            im._init(cam.width, cam.height)
+            setattr(out, n, im.data.ctypes.data)
+        go = N.GBufferOption(float(z_near), float(z_far), 1 if flat_normal else 0, int(geo_id))
+        rc = self._lib.ugu_b200_rasterizer_render_gbuffer(self._h, C.byref(cam), C.byref(go), C.byref(out))
+        if rc != N.OK:
+            LOGE(N.last_error(self._h))
+            return False
+        return True
+
+    def render_gbuffer_device(self, camera: PinholeCamera, z_near: float, z_far: float, flat_normal: bool = False,
+                              geo_id: int = 0, stream: int = 0, **fields: int) -> None:
+        """Device form: `fields` are raw 16-byte aligned DEVICE pointers by GBuffer field name."""
+        opt = self._native_option()
+        self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+        cam = camera.to_native() if isinstance(camera, PinholeCamera) else camera
+        out = N.GBuffer(**fields)
+        go = N.GBufferOption(float(z_near), float(z_far), 1 if flat_normal else 0, int(geo_id))
+        rc = self._lib.ugu_b200_rasterizer_render_gbuffer_device(self._h, C.byref(cam), C.byref(go), C.byref(out),
+                                                                 C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
 
     # -- device-resident / batch extensions (no reference counterpart; see INTEGRATION.md) --------
     def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
