@@ -280,6 +280,49 @@ int main(int argc, char** argv) {
     ugu::Mesh mm;
     if (rc.Depth2Mesh(dep, *camera, &mm, -1.0f)) failures++;  // false like the reference
   }
+  {  // G-buffer: no GL reference can run here, so RasterizerCuda::RenderGBuffer is checked
+     // for consistency with the reference Rasterizer on the same mesh / camera (winners, depth, colour)
+    ugu::RendererCpuOption o;
+    o.diffuse_color = ugu::DiffuseColor::kTexture;
+    ugu::Rasterizer rr(o);
+    rr.set_mesh(mesh);
+    if (!rr.PrepareMesh()) return 1;
+    rr.set_camera(camera);
+    ugu::Image3b col;
+    ugu::Image1f dep;
+    ugu::Image1i fid;
+    if (!rr.Render(&col, &dep, nullptr, nullptr, &fid)) return 1;
+    ugu::RasterizerCuda rc(o);
+    rc.set_mesh(mesh);
+    if (!rc.PrepareMesh()) return 2;
+    rc.set_camera(camera);
+    ugu::GBuffer g;
+    int bad = 0;
+    if (!rc.RenderGBuffer(&g)) bad++;
+    if (rc.RenderGBuffer(&g, 1.0f, 0.5f)) bad++;  // far < near -> false
+    size_t covered = 0;
+    const Eigen::Matrix3f R = camera->w2c().rotation().cast<float>();
+    for (int y = 0; y < dep.rows && !bad; y++)
+      for (int x = 0; x < dep.cols; x++) {
+        const int f = fid.at<int>(y, x);
+        const bool vis = g.stencil.at<uint8_t>(y, x) == 255;
+        if (vis != (f >= 0) || g.face_id.at<int>(y, x) != (vis ? f + 1 : 0)) bad++;
+        if (std::memcmp(&g.color.at<ugu::Vec3b>(y, x), &col.at<ugu::Vec3b>(y, x), 3) != 0) bad++;
+        if (!vis) continue;
+        covered++;
+        const ugu::Vec3f pc = g.pos_cam.at<ugu::Vec3f>(y, x), nw = g.normal_wld.at<ugu::Vec3f>(y, x);
+        const ugu::Vec3f nc = g.normal_cam.at<ugu::Vec3f>(y, x), b = g.bary.at<ugu::Vec3f>(y, x);
+        const float d = dep.at<float>(y, x);
+        if (std::abs(pc[2] - d) > 2e-5f * d) bad++;
+        const Eigen::Vector3f ncr = R * Eigen::Vector3f(nw[0], nw[1], nw[2]);
+        if (ncr[0] != nc[0] || ncr[1] != nc[1] || ncr[2] != nc[2]) bad++;  // renderer.cc:583, same Eigen expression
+        if (std::abs(b[0] + b[1] + b[2] - 1.0f) > 1e-6f) bad++;
+        const float d01 = g.depth_01.at<float>(y, x);
+        if (!(d01 > 0.0f && d01 < 1.0f)) bad++;
+      }
+    std::printf("GBuffer vs Rasterizer: %zu covered pixels  %s\n", covered, bad ? "MISMATCH" : "consistent");
+    if (bad || covered == 0) failures++;
+  }
   std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);
   return failures ? 1 : 0;
 }

@@ -81,10 +81,10 @@ class RasterizerCuda::Impl {
     return true;
   }
 
-  bool Render(Image3b* color, Image1f* depth, Image3f* normal, Image1b* mask,
-              Image1i* face_id) const {
-    // Preconditions in the order of ValidateAndInitBeforeRender (util_private.cc:19-67); the
-    // mesh/option dependent ones are checked by the library against the uploaded mesh.
+  // Preconditions shared by Render and RenderGBuffer, in the order of ValidateAndInitBeforeRender
+  // (util_private.cc:19-67; the mesh/option dependent ones are checked by the library against the
+  // uploaded mesh), then the option and camera PODs of the C-ABI.
+  bool Begin(ugu_b200_camera* cam) const {
     if (camera_ == nullptr) {
       LOGE("camera has not been set\n");
       return false;
@@ -98,11 +98,6 @@ class RasterizerCuda::Impl {
       LOGE("RasterizerCuda supports PinholeCamera only (no CPU fallback)\n");
       return false;
     }
-    if (color == nullptr && depth == nullptr && normal == nullptr && mask == nullptr &&
-        face_id == nullptr) {
-      LOGE("all arguments are nullptr. nothing to do\n");
-      return false;
-    }
     ugu_b200_option o;
     o.diffuse_color = static_cast<int32_t>(option_.diffuse_color);
     o.interp = static_cast<int32_t>(option_.interp);
@@ -114,7 +109,7 @@ class RasterizerCuda::Impl {
     ugu_b200_rasterizer_set_option(handle_, &o);
 
     // Camera constants exactly as rasterizer.cc:118-119 and camera.h:321 derive them.
-    ugu_b200_camera c;
+    ugu_b200_camera& c = *cam;
     c.width = camera_->width();
     c.height = camera_->height();
     c.fx = pin->focal_length().x();
@@ -130,6 +125,53 @@ class RasterizerCuda::Impl {
         c.c2w_R[i * 3 + j] = c2w_R(i, j);
       }
       c.w2c_t[i] = w2c_t[i];
+    }
+    return true;
+  }
+
+  // ugu::GBuffer as RendererGl::ReadGbuf fills it (src/renderer/gl/renderer.cc:501-650), from this
+  // rasterizer's winners.  Like ReadGbuf (:515-518) the images are (re)allocated when the size differs.
+  bool RenderGBuffer(GBuffer* g, float z_near, float z_far, bool flat_normal, int geo_id) const {
+    if (g == nullptr) {
+      LOGE("gbuffer is nullptr\n");
+      return false;
+    }
+    ugu_b200_camera c;
+    if (!Begin(&c)) return false;
+    if (g->color.cols != c.width || g->color.rows != c.height) g->Init(c.width, c.height);
+    ugu_b200_gbuffer out;
+    out.color = g->color.data;
+    out.normal_cam = reinterpret_cast<float*>(g->normal_cam.data);
+    out.normal_wld = reinterpret_cast<float*>(g->normal_wld.data);
+    out.pos_cam = reinterpret_cast<float*>(g->pos_cam.data);
+    out.pos_wld = reinterpret_cast<float*>(g->pos_wld.data);
+    out.depth_01 = reinterpret_cast<float*>(g->depth_01.data);
+    out.stencil = g->stencil.data;
+    out.face_id = reinterpret_cast<int32_t*>(g->face_id.data);
+    out.uv = reinterpret_cast<float*>(g->uv.data);
+    out.bary = reinterpret_cast<float*>(g->bary.data);
+    out.geo_id = reinterpret_cast<int32_t*>(g->geo_id.data);
+    ugu_b200_gbuffer_option go;
+    go.z_near = z_near;
+    go.z_far = z_far;
+    go.flat_normal = flat_normal ? 1 : 0;
+    go.geo_id = geo_id;
+    if (ugu_b200_rasterizer_render_gbuffer(handle_, &c, &go, &out) != UGU_B200_OK) {
+      LOGE("%s\n", ugu_b200_last_error(handle_));
+      return false;
+    }
+    g->shaded.setTo(0.0);  // the viewer's deferred lighting pass is not produced
+    return true;
+  }
+
+  bool Render(Image3b* color, Image1f* depth, Image3f* normal, Image1b* mask,
+              Image1i* face_id) const {
+    ugu_b200_camera c;
+    if (!Begin(&c)) return false;
+    if (color == nullptr && depth == nullptr && normal == nullptr && mask == nullptr &&
+        face_id == nullptr) {
+      LOGE("all arguments are nullptr. nothing to do\n");
+      return false;
     }
     // ugu::Init: (re)allocate only when the size differs (image.h:963-985).  The library writes
     // every pixel of every requested image, so the clear is part of the kernel.
@@ -409,6 +451,10 @@ bool RasterizerCuda::RenderMask(Image1b* mask) const {
 }
 bool RasterizerCuda::RenderFaceId(Image1i* face_id) const {
   return Render(nullptr, nullptr, nullptr, nullptr, face_id);
+}
+
+bool RasterizerCuda::RenderGBuffer(GBuffer* gbuf, float z_near, float z_far, bool flat_normal, int geo_id) const {
+  return pimpl_->RenderGBuffer(gbuf, z_near, z_far, flat_normal, geo_id);
 }
 
 bool RasterizerCuda::RenderW(Image3b* color, Image1w* depth, Image3f* normal, Image1b* mask,

@@ -14,6 +14,8 @@
 #include <string>
 #include <vector>
 
+#include "ugu/image.h"  // renderer/base.h (GBuffer) uses the image types without including them
+#include "ugu/renderer/base.h"
 #include "ugu/renderer/cpu/renderer.h"
 
 namespace ugu {
@@ -90,6 +92,16 @@ class RasterizerCuda : public RendererCpu {
                   float max_connect_z_diff, int x_step = 1, int y_step = 1, bool gl_coord = false,
                   const std::string& material_name = "Depth2Mesh_mat", bool with_vertex_color = false,
                   Image3f* point_cloud = nullptr, Image3f* normal = nullptr) const;
+
+  // ugu::GBuffer (include/ugu/renderer/base.h:34-77) as RendererGl::ReadGbuf fills it
+  // (src/renderer/gl/renderer.cc:501-650) from the gbuf shaders (src/shader/glsl/{vert/gbuf.vert,
+  // geom/dummy.geom,frag/gbuf.frag}), computed headless from THIS rasterizer's winners: stencil,
+  // depth_01 (near / far as RendererGl::SetNearFar), face_id (+1, 0 = background), geo_id, bary, uv,
+  // pos_wld / pos_cam, normal_wld / normal_cam, color (= Render's); `shaded` is zeroed.  The sampling
+  // rule is the CPU Rasterizer's (integer pixel centres, inclusive edges), not OpenGL's; definition in
+  // include/ugu_b200_raster.h.  false + log on Render's precondition failures or bad near / far.
+  bool RenderGBuffer(GBuffer* gbuf, float z_near = 0.01f, float z_far = 1000.0f, bool flat_normal = false,
+                     int geo_id = 0) const;
 
   // false when the CUDA library could not create a rasterizer (no B200 / no driver).
   bool valid() const;
