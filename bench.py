@@ -197,6 +197,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: ugu_b200 has no CPU fallback")
     torch.cuda.set_device(local)
+    # host cores / pinned memory local to this rank's GPU (matters for e2e at N > 2: the D2H of N ranks)
+    from ugu_b200.multiview import bind_rank_to_gpu_numa
+    numa = bind_rank_to_gpu_numa(local) if world > 1 else {"bound": False, "note": "single rank: not bound"}
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     warmup = max(3, args.warmup)
@@ -345,7 +348,9 @@ def main():
                     "api": "ugu_b200.Rasterizer.Render -> ugu_b200_rasterizer_render, pinned host images",
                     "host_link": {"pinned_d2h_gbs": d2h_bytes / (link_ms * 1e-3) / 1e9,
                                   "ms_for_one_view_of_outputs": link_ms,
-                                  "note": "a view returns 24 B/pixel; e2e is bounded by this copy"}},
+                                  "note": "a view returns 24 B/pixel; e2e is bounded by this copy; at N > 1 "
+                                          "all ranks copy at the same time and share the host's memory system"},
+                    "numa_rank0": numa},
             "gpu_launches": int(launches),
             "stage_us": {k: round(v * 1e3, 2) for k, v in stage_ms.items()},
             "ms_per_step_stage_timed_pass": prof_ms / K,

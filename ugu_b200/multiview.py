@@ -17,6 +17,38 @@ import torch
 import torch.distributed as dist
 
 
+def bind_rank_to_gpu_numa(device_index: int) -> dict:
+    """Pin this process to the host cores that are local to GPU `device_index` (sysfs
+    /sys/bus/pci/devices/<bdf>/local_cpulist), BEFORE it allocates pinned host memory: first-touch then
+    places the D2H landing buffers on the GPU's own NUMA node, so that N ranks copying their views back
+    at the same time do not all write through one socket's memory controllers.  No-op (reported as such)
+    when the platform does not expose the topology (numa_node = -1, e.g. a flat VM)."""
+    import os
+    info = {"bound": False}
+    try:
+        props = torch.cuda.get_device_properties(device_index)
+        bdf = f"{props.pci_domain_id:04x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bdf}"
+        node = int(open(f"{base}/numa_node").read().strip())
+        cpulist = open(f"{base}/local_cpulist").read().strip()
+        info.update(pci=bdf, numa_node=node, local_cpulist=cpulist)
+        cpus = set()
+        for part in cpulist.split(","):
+            if not part:
+                continue
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if node >= 0 and cpus and cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+            info["bound"] = True
+        info["cpus"] = len(cpus) if cpus else len(allowed)
+    except Exception as e:  # topology not exposed: leave the affinity alone
+        info["error"] = f"{type(e).__name__}: {e}"[:120]
+    return info
+
+
 def partition(num_views: int, world: int, rank: int, mode: str = "contiguous") -> List[int]:
     """Indices of the views rank `rank` renders.  contiguous: ranks get ceil/floor(num/world)
     consecutive views (the first num % world ranks get one more); round_robin: i % world == rank."""
