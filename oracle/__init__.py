@@ -152,6 +152,26 @@ class OraclePort:
         return out
 
 
+def port_raytrace(port: "OraclePort", cam_pod, org_w, option, want=ALL_OUTPUTS):
+    """oracle_raytrace (oracle/raster_oracle.c): ugu::Raytracer::Render restated with a brute-force nearest
+    hit over nanort's intersector.  `org_w` = c2w translation as float32.  None on failure."""
+    lib = port.lib
+    lib.oracle_raytrace.restype = C.c_int
+    lib.oracle_raytrace.argtypes = [C.POINTER(_MeshDesc), C.POINTER(_PortCamera), C.POINTER(C.c_float),
+                                    C.POINTER(_PortOption)] + [C.c_void_p] * 5
+    cam = _PortCamera()
+    for name, _ in _PortCamera._fields_:
+        setattr(cam, name, getattr(cam_pod, name))
+    opt = _PortOption(int(option.diffuse_color), int(option.interp), int(option.shading_normal),
+                      int(option.diffuse_shading), 1 if option.backface_culling else 0,
+                      float(option.depth_scale), 0.3)
+    org = (C.c_float * 3)(*[float(np.float32(x)) for x in org_w])
+    out = _alloc_outputs(cam.width, cam.height, want)
+    rc = lib.oracle_raytrace(C.byref(port.holder.desc), C.byref(cam), org, C.byref(opt),
+                             *[_optr(out, k) for k in ALL_OUTPUTS])
+    return out if rc == 0 else None
+
+
 GBUFFER_FIELDS = (("color", np.uint8, 3), ("normal_cam", np.float32, 3), ("normal_wld", np.float32, 3),
                   ("pos_cam", np.float32, 3), ("pos_wld", np.float32, 3), ("depth_01", np.float32, 1),
                   ("stencil", np.uint8, 1), ("face_id", np.int32, 1), ("uv", np.float32, 3),
@@ -441,6 +461,26 @@ class OracleRef:
         if rc != 0:
             return None
         return out
+
+    def raytrace(self, camera, option, want=ALL_OUTPUTS):
+        """The compiled reference ugu::Raytracer (src/renderer/cpu/raytracer.cc, nanort BVH) on this mesh."""
+        self.lib.ugu_ref_raytrace.restype = C.c_int
+        self.lib.ugu_ref_raytrace.argtypes = [C.c_void_p, C.POINTER(_RefCamera), C.POINTER(_RefOption)] + \
+            [C.c_void_p] * 5 + [C.POINTER(C.c_double)]
+        cam = _RefCamera()
+        cam.width, cam.height = camera.width(), camera.height()
+        cam.fx, cam.fy = float(camera.focal_length()[0]), float(camera.focal_length()[1])
+        cam.cx, cam.cy = float(camera.principal_point()[0]), float(camera.principal_point()[1])
+        cam.c2w = (C.c_double * 16)(*np.asarray(camera.c2w(), np.float64).reshape(-1))
+        opt = _RefOption(int(option.diffuse_color), int(option.interp), int(option.shading_normal),
+                         int(option.diffuse_shading), 1 if option.backface_culling else 0,
+                         float(option.depth_scale))
+        out = _alloc_outputs(cam.width, cam.height, want)
+        timing = (C.c_double * 1)()
+        rc = self.lib.ugu_ref_raytrace(self.h, C.byref(cam), C.byref(opt),
+                                       *[_optr(out, k) for k in ALL_OUTPUTS], timing)
+        self.last_raytrace_ms = timing[0]
+        return out if rc == 0 else None
 
     def camera_constants(self, c2w):
         m = (C.c_double * 16)(*np.asarray(c2w, np.float64).reshape(-1))

@@ -137,6 +137,78 @@ static inline int32_t sat_i32(float f) {
   return (int32_t)f;
 }
 
+/* The colourizer + shader of one pixel: PixelShader::Process (include/ugu/renderer/cpu/pixel_shader.h:
+ * 115-140,222-422) as both CPU renderers call it (rasterizer.cc:291-298, raytracer.cc:205-211), with
+ * (u, v) the barycentrics of vertices 1 and 2, `ray` the world ray (== light direction), `n_w` the world
+ * shading normal. */
+static void shade_pixel(const OracleMesh* mesh, const OracleOption* opt, float on_A, float on_B, int32_t fid,
+                        float u, float v, const float* ray, const float* n_w, uint8_t* c) {
+  /* colourizer: pixel_shader.h:222-359 */
+  if (opt->diffuse_color == 2) {
+    const int32_t* f = &mesh->vertex_indices[(size_t)fid * 3];
+    const float* c0 = &mesh->vertex_colors[(size_t)f[0] * 3];
+    const float* c1 = &mesh->vertex_colors[(size_t)f[1] * 3];
+    const float* c2 = &mesh->vertex_colors[(size_t)f[2] * 3];
+    const float k0 = 1.0f - u - v;
+    for (int k = 0; k < 3; k++) c[k] = f2u8((k0 * c0[k] + u * c1[k]) + v * c2[k]);
+  } else if (opt->diffuse_color == 1) {
+    const int32_t* ui = &mesh->uv_indices[(size_t)fid * 3];
+    const float* t0 = &mesh->uv[(size_t)ui[0] * 2];
+    const float* t1 = &mesh->uv[(size_t)ui[1] * 2];
+    const float* t2 = &mesh->uv[(size_t)ui[2] * 2];
+    const int mat = mesh->material_ids[fid];
+    const uint8_t* tex = mesh->tex_data[mat];
+    const int tw = mesh->tex_w[mat], th = mesh->tex_h[mat];
+    const float k0 = 1.0f - u - v;
+    const float iu = (k0 * t0[0] + u * t1[0]) + v * t2[0];
+    const float iv = (k0 * t0[1] + u * t1[1]) + v * t2[1];
+    const float tx = iu * (float)(tw - 1);
+    const float ty = (1.0f - iv) * (float)(th - 1);
+    if (opt->interp == 0) {
+      float rgb[3];
+      texel(tex, tw, th, sat_i32(roundf(tx)), sat_i32(roundf(ty)), rgb);
+      for (int k = 0; k < 3; k++) c[k] = f2u8(rgb[k]);
+    } else {
+      const int xm = sat_i32(floorf(tx)), ym = sat_i32(floorf(ty));
+      const float lu = tx - (float)xm, lv = ty - (float)ym;
+      float a[3], b[3], cc[3], dd[3];
+      texel(tex, tw, th, xm, ym, a);
+      texel(tex, tw, th, xm + 1, ym, b);
+      texel(tex, tw, th, xm, ym + 1, cc);
+      texel(tex, tw, th, xm + 1, ym + 1, dd);
+      for (int k = 0; k < 3; k++) {
+        float val = (1.0f - lu) * (1.0f - lv) * a[k] + lu * (1.0f - lv) * b[k] +
+                    (1.0f - lu) * lv * cc[k] + lu * lv * dd[k];
+        c[k] = f2u8(val);
+      }
+    }
+  } else {
+    c[0] = c[1] = c[2] = 255;
+  }
+  /* shader: pixel_shader.h:363-422; light_dir == ray_w (rasterizer.cc:293) */
+  if (opt->diffuse_shading == 1) {
+    float coeff = -dot3(ray, n_w);
+    if (coeff < 0.0f) coeff = 0.0f;
+    for (int k = 0; k < 3; k++) c[k] = f2u8(coeff * (float)c[k]);
+  } else if (opt->diffuse_shading == 2) {
+    float dot_light = -dot3(ray, n_w);
+    float theta_i = acosf(dot_light);
+    float dot_ray = -dot3(ray, n_w);
+    float theta_r = acosf(dot_ray);
+    float bl[3], br[3];
+    for (int k = 0; k < 3; k++) {
+      bl[k] = (-n_w[k]) * dot_light - ray[k];
+      br[k] = (-n_w[k]) * dot_light - ray[k];
+    }
+    float phi_diff_cos = fmaxf(0.0f, dot3(bl, br));
+    float alpha = (theta_i < theta_r) ? theta_r : theta_i; /* std::max(theta_i, theta_r) */
+    float beta = (theta_r < theta_i) ? theta_r : theta_i;  /* std::min(theta_i, theta_r) */
+    float coeff = (dot_light > 0.0f ? dot_light : 0.0f) *
+                  (on_A + (on_B * phi_diff_cos * sinf(alpha) * tanf(beta)));
+    for (int k = 0; k < 3; k++) c[k] = f2u8(coeff * (float)c[k]);
+  }
+}
+
 /* Raw z-buffer state after rasterizer.cc:162-241 and BEFORE the cull / resolve loop (:244-301), for
  * oracle_gbuffer: winner face (-1 = none), its depth, weights and back-face flag per pixel. */
 typedef struct RawWinners {
@@ -315,74 +387,7 @@ static int render_impl(const OracleMesh* mesh, const OracleCamera* cam, const Or
         }
         if (normal) mat3_mul(cam->w2c_R, n_w, &normal[pi * 3]);
 
-        if (color) {
-          const float u = w1, v = w2;
-          uint8_t* c = &color[pi * 3];
-          /* colourizer: pixel_shader.h:222-359 */
-          if (opt->diffuse_color == 2) {
-            const int32_t* f = &mesh->vertex_indices[(size_t)fid * 3];
-            const float* c0 = &mesh->vertex_colors[(size_t)f[0] * 3];
-            const float* c1 = &mesh->vertex_colors[(size_t)f[1] * 3];
-            const float* c2 = &mesh->vertex_colors[(size_t)f[2] * 3];
-            const float k0 = 1.0f - u - v;
-            for (int k = 0; k < 3; k++) c[k] = f2u8((k0 * c0[k] + u * c1[k]) + v * c2[k]);
-          } else if (opt->diffuse_color == 1) {
-            const int32_t* ui = &mesh->uv_indices[(size_t)fid * 3];
-            const float* t0 = &mesh->uv[(size_t)ui[0] * 2];
-            const float* t1 = &mesh->uv[(size_t)ui[1] * 2];
-            const float* t2 = &mesh->uv[(size_t)ui[2] * 2];
-            const int mat = mesh->material_ids[fid];
-            const uint8_t* tex = mesh->tex_data[mat];
-            const int tw = mesh->tex_w[mat], th = mesh->tex_h[mat];
-            const float k0 = 1.0f - u - v;
-            const float iu = (k0 * t0[0] + u * t1[0]) + v * t2[0];
-            const float iv = (k0 * t0[1] + u * t1[1]) + v * t2[1];
-            const float tx = iu * (float)(tw - 1);
-            const float ty = (1.0f - iv) * (float)(th - 1);
-            if (opt->interp == 0) {
-              float rgb[3];
-              texel(tex, tw, th, sat_i32(roundf(tx)), sat_i32(roundf(ty)), rgb);
-              for (int k = 0; k < 3; k++) c[k] = f2u8(rgb[k]);
-            } else {
-              const int xm = sat_i32(floorf(tx)), ym = sat_i32(floorf(ty));
-              const float lu = tx - (float)xm, lv = ty - (float)ym;
-              float a[3], b[3], cc[3], dd[3];
-              texel(tex, tw, th, xm, ym, a);
-              texel(tex, tw, th, xm + 1, ym, b);
-              texel(tex, tw, th, xm, ym + 1, cc);
-              texel(tex, tw, th, xm + 1, ym + 1, dd);
-              for (int k = 0; k < 3; k++) {
-                float val = (1.0f - lu) * (1.0f - lv) * a[k] + lu * (1.0f - lv) * b[k] +
-                            (1.0f - lu) * lv * cc[k] + lu * lv * dd[k];
-                c[k] = f2u8(val);
-              }
-            }
-          } else {
-            c[0] = c[1] = c[2] = 255;
-          }
-          /* shader: pixel_shader.h:363-422; light_dir == ray_w (rasterizer.cc:293) */
-          if (opt->diffuse_shading == 1) {
-            float coeff = -dot3(ray, n_w);
-            if (coeff < 0.0f) coeff = 0.0f;
-            for (int k = 0; k < 3; k++) c[k] = f2u8(coeff * (float)c[k]);
-          } else if (opt->diffuse_shading == 2) {
-            float dot_light = -dot3(ray, n_w);
-            float theta_i = acosf(dot_light);
-            float dot_ray = -dot3(ray, n_w);
-            float theta_r = acosf(dot_ray);
-            float bl[3], br[3];
-            for (int k = 0; k < 3; k++) {
-              bl[k] = (-n_w[k]) * dot_light - ray[k];
-              br[k] = (-n_w[k]) * dot_light - ray[k];
-            }
-            float phi_diff_cos = fmaxf(0.0f, dot3(bl, br));
-            float alpha = (theta_i < theta_r) ? theta_r : theta_i; /* std::max(theta_i, theta_r) */
-            float beta = (theta_r < theta_i) ? theta_r : theta_i;  /* std::min(theta_i, theta_r) */
-            float coeff = (dot_light > 0.0f ? dot_light : 0.0f) *
-                          (on_A + (on_B * phi_diff_cos * sinf(alpha) * tanf(beta)));
-            for (int k = 0; k < 3; k++) c[k] = f2u8(coeff * (float)c[k]);
-          }
-        }
+        if (color) shade_pixel(mesh, opt, on_A, on_B, fid, w1, w2, ray, n_w, &color[pi * 3]);
       }
     }
   }
@@ -823,4 +828,173 @@ done:
   return rc;
 }
 
-int oracle_abi_version(void) { return 5; }
+/* ---------------------------------------------------------------------------------------------------
+ * ugu::Raytracer::Impl::Render (src/renderer/cpu/raytracer.cc:117-225) with the nanort nearest-hit query
+ * of BvhNanort::Intersect(ray, test_all = false) (include/ugu/accel/bvh_nanort.h:109-152).
+ *
+ * nanort (third_party/nanort/nanort.h, vendored in the reference tree) finds the hit with a BVH; the
+ * value it returns is min over the triangles of the watertight intersector's t
+ * (TriangleIntersector::Intersect / PrepareTraversal, nanort.h:1050-1199), because the traversal only
+ * prunes boxes against the current nearest t (nanort.h:2485-2552).  This restatement therefore evaluates
+ * the same intersector arithmetic on EVERY triangle (brute force) — usable on small cases only.
+ * Traversal-order dependence that cannot be restated without the BVH: two triangles with bit-identical t
+ * at a pixel (nanort keeps the LAST one visited, `tt > t` rejects; here the HIGHEST face index wins, which
+ * is what nanort does too whenever the tied triangles share a leaf in index order), and
+ * the non-conservative lower slab bound of IntersectRayAABB (nanort.h:2281-2321).  PINNED differentially:
+ * tests/golden/raytrace_*.npz (compiled reference Raytracer) and the live reference where oracle/_ref exists.
+ * ------------------------------------------------------------------------------------------------- */
+typedef struct RtRay {
+  float org[3], dir[3];
+  float Sx, Sy, Sz;
+  int kx, ky, kz;
+} RtRay;
+
+static void rt_prepare(RtRay* r) { /* nanort.h:1160-1199 */
+  r->kz = 0;
+  float absDir = fabsf(r->dir[0]);
+  if (absDir < fabsf(r->dir[1])) {
+    r->kz = 1;
+    absDir = fabsf(r->dir[1]);
+  }
+  if (absDir < fabsf(r->dir[2])) {
+    r->kz = 2;
+    absDir = fabsf(r->dir[2]);
+  }
+  r->kx = r->kz + 1;
+  if (r->kx == 3) r->kx = 0;
+  r->ky = r->kx + 1;
+  if (r->ky == 3) r->ky = 0;
+  if (r->dir[r->kz] < 0.0f) {
+    const int t = r->kx;
+    r->kx = r->ky;
+    r->ky = t;
+  }
+  r->Sx = r->dir[r->kx] / r->dir[r->kz];
+  r->Sy = r->dir[r->ky] / r->dir[r->kz];
+  r->Sz = 1.0f / r->dir[r->kz];
+}
+
+/* nanort.h:1050-1148; *t is the current nearest distance (in/out).  Returns 1 on an accepted hit. */
+static int rt_intersect(const RtRay* r, const float* p0, const float* p1, const float* p2, float t_min,
+                        float* t, float* u, float* v) {
+  float A[3], B[3], Cc[3];
+  for (int k = 0; k < 3; k++) {
+    A[k] = p0[k] - r->org[k];
+    B[k] = p1[k] - r->org[k];
+    Cc[k] = p2[k] - r->org[k];
+  }
+  const float Ax = A[r->kx] - r->Sx * A[r->kz];
+  const float Ay = A[r->ky] - r->Sy * A[r->kz];
+  const float Bx = B[r->kx] - r->Sx * B[r->kz];
+  const float By = B[r->ky] - r->Sy * B[r->kz];
+  const float Cx = Cc[r->kx] - r->Sx * Cc[r->kz];
+  const float Cy = Cc[r->ky] - r->Sy * Cc[r->kz];
+  float U = Cx * By - Cy * Bx;
+  float V = Ax * Cy - Ay * Cx;
+  float W = Bx * Ay - By * Ax;
+  if (U == 0.0f || V == 0.0f || W == 0.0f) {
+    const double CxBy = (double)Cx * (double)By, CyBx = (double)Cy * (double)Bx;
+    U = (float)(CxBy - CyBx);
+    const double AxCy = (double)Ax * (double)Cy, AyCx = (double)Ay * (double)Cx;
+    V = (float)(AxCy - AyCx);
+    const double BxAy = (double)Bx * (double)Ay, ByAx = (double)By * (double)Ax;
+    W = (float)(BxAy - ByAx);
+  }
+  if (U < 0.0f || V < 0.0f || W < 0.0f) {
+    if (U > 0.0f || V > 0.0f || W > 0.0f) return 0; /* cull_back_face is false (BVHTraceOptions default) */
+  }
+  const float det = U + V + W;
+  if (det == 0.0f) return 0;
+  const float Az = r->Sz * A[r->kz];
+  const float Bz = r->Sz * B[r->kz];
+  const float Cz = r->Sz * Cc[r->kz];
+  const float D = U * Az + V * Bz + W * Cz;
+  const float rcpDet = 1.0f / det;
+  const float tt = D * rcpDet;
+  if (tt > *t) return 0;
+  if (tt < t_min) return 0;
+  *t = tt;
+  *u = V * rcpDet;
+  *v = W * rcpDet;
+  return 1;
+}
+
+/* org_w = PinholeCamera::org_ray_w = c2w translation cast to float (camera.h:431-436). */
+int oracle_raytrace(const OracleMesh* mesh, const OracleCamera* cam, const float* org_w,
+                    const OracleOption* opt, uint8_t* color, float* depth, float* normal, uint8_t* mask,
+                    int32_t* face_id) {
+  const int W = cam->width, H = cam->height;
+  const size_t P = (size_t)W * (size_t)H;
+  const int F = mesh->num_faces;
+  if (W <= 0 || H <= 0) return 2;
+  /* util_private.cc:19-67 (shared with the Rasterizer) */
+  if (opt->backface_culling && mesh->num_face_normals == 0) return 1;
+  if (opt->diffuse_color == 1 && mesh->num_materials == 0) return 1;
+  if (opt->diffuse_color == 1) {
+    for (int i = 0; i < mesh->num_materials; i++)
+      if (mesh->tex_data[i] == NULL || mesh->tex_w[i] < 1 || mesh->tex_h[i] < 1) return 1;
+  }
+  if (opt->diffuse_color == 2 && mesh->num_colors == 0) return 1;
+  if (opt->shading_normal == 0 && mesh->num_face_normals == 0) return 1;
+  if (opt->shading_normal == 1 && mesh->num_normals == 0) return 1;
+  if (!color && !depth && !normal && !mask && !face_id) return 1;
+  if (color) memset(color, 0, P * 3);
+  if (depth) memset(depth, 0, P * 4);
+  if (normal) memset(normal, 0, P * 12);
+  if (mask) memset(mask, 0, P);
+  if (face_id)
+    for (size_t i = 0; i < P; i++) face_id[i] = -1;
+  const float sigma = opt->oren_nayar_sigma, sigma_2 = sigma * sigma;
+  const float on_A = 1.0f - (0.5f * sigma_2 / (sigma_2 + 0.33f));
+  const float on_B = 0.45f * sigma_2 / (sigma_2 + 0.09f);
+
+  for (int y = 0; y < H; y++) {
+    for (int x = 0; x < W; x++) {
+      RtRay r;
+      ray_w(cam, x, y, r.dir);
+      memcpy(r.org, org_w, 12);
+      rt_prepare(&r);
+      float t = 1.0e+30f, u = 0.0f, v = 0.0f; /* bvh_nanort.h:119-121: min_t 1e-4, max_t 1e30 */
+      int32_t fid = -1;
+      for (int i = 0; i < F; i++) {
+        const int32_t* f = &mesh->vertex_indices[(size_t)i * 3];
+        float tl = t, ul, vl;
+        if (rt_intersect(&r, &mesh->vertices[(size_t)f[0] * 3], &mesh->vertices[(size_t)f[1] * 3],
+                         &mesh->vertices[(size_t)f[2] * 3], 0.0001f, &tl, &ul, &vl)) {
+          t = tl;
+          u = ul;
+          v = vl;
+          fid = i;
+        }
+      }
+      if (fid < 0 || !(t < 1.0e+30f)) continue; /* nanort.h:2548 */
+      const float* ray = r.dir;
+      if (opt->backface_culling && dot3(&mesh->face_normals[(size_t)fid * 3], ray) > 0.0f) continue;
+      const size_t pi = (size_t)y * W + x;
+      if (face_id) face_id[pi] = fid;
+      if (mask) mask[pi] = 255;
+      if (depth) { /* raytracer.cc:167-172 */
+        float hw[3], hc[3];
+        for (int k = 0; k < 3; k++) hw[k] = r.org[k] + ray[k] * t;
+        mat3_mul(cam->w2c_R, hw, hc);
+        depth[pi] = (hc[2] + cam->w2c_t[2]) * opt->depth_scale;
+      }
+      float n_w[3] = {0.0f, 0.0f, 0.0f};
+      if (opt->shading_normal == 0) {
+        memcpy(n_w, &mesh->face_normals[(size_t)fid * 3], 12);
+      } else if (opt->shading_normal == 1) { /* raytracer.cc:178-186 */
+        const int32_t* ni = &mesh->normal_indices[(size_t)fid * 3];
+        const float* n0 = &mesh->normals[(size_t)ni[0] * 3];
+        const float* n1 = &mesh->normals[(size_t)ni[1] * 3];
+        const float* n2 = &mesh->normals[(size_t)ni[2] * 3];
+        const float k0 = 1.0f - u - v;
+        for (int k = 0; k < 3; k++) n_w[k] = (k0 * n0[k] + u * n1[k]) + v * n2[k];
+      }
+      if (normal) mat3_mul(cam->w2c_R, n_w, &normal[pi * 3]);
+      if (color) shade_pixel(mesh, opt, on_A, on_B, fid, u, v, ray, n_w, &color[pi * 3]);
+    }
+  }
+  return 0;
+}
+
+int oracle_abi_version(void) { return 6; }

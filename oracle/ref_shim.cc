@@ -19,6 +19,7 @@
 #include "ugu/log.h"
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/renderer/cpu/raytracer.h"
 #include "ugu/util/raster_util.h"
 #include "ugu/util/rgbd_util.h"
 
@@ -70,6 +71,7 @@ struct RefHandle {
   std::shared_ptr<ugu::Mesh> mesh;
   std::shared_ptr<ugu::PinholeCamera> camera;
   std::unique_ptr<ugu::Rasterizer> renderer;
+  std::unique_ptr<ugu::Raytracer> raytracer;  // created by the first ugu_ref_raytrace (builds the nanort BVH)
   ugu::Image3b color;
   ugu::Image1f depth;
   ugu::Image3f normal;
@@ -145,6 +147,53 @@ void* ugu_ref_create(const UguRefMeshDesc* d) {
 }
 
 void ugu_ref_destroy(void* handle) { delete static_cast<RefHandle*>(handle); }
+
+// ugu::Raytracer (src/renderer/cpu/raytracer.cc:117-225, BVH = BvhNanort, include/ugu/accel/bvh_nanort.h)
+// on the same mesh / camera conventions as ugu_ref_render.  `timing_ms` (optional, 1 double): wall ms of
+// set_c2w + Render.
+int ugu_ref_raytrace(void* handle, const UguRefCamera* cam, const UguRefOption* opt, uint8_t* color,
+                     float* depth, float* normal, uint8_t* mask, int32_t* face_id, double* timing_ms) {
+  RefHandle* h = static_cast<RefHandle*>(handle);
+  if (h == nullptr) return -1;
+  if (!h->raytracer) {
+    h->raytracer = std::make_unique<ugu::Raytracer>();
+    h->raytracer->set_mesh(h->mesh);
+    if (!h->raytracer->PrepareMesh()) {
+      h->raytracer.reset();
+      return 2;
+    }
+  }
+  ugu::RendererCpuOption o;
+  o.diffuse_color = static_cast<ugu::DiffuseColor>(opt->diffuse_color);
+  o.interp = static_cast<ugu::ColorInterpolation>(opt->interp);
+  o.shading_normal = static_cast<ugu::ShadingNormal>(opt->shading_normal);
+  o.diffuse_shading = static_cast<ugu::DiffuseShading>(opt->diffuse_shading);
+  o.backface_culling = opt->backface_culling != 0;
+  o.depth_scale = opt->depth_scale;
+  h->raytracer->set_option(o);
+  auto camera = std::make_shared<ugu::PinholeCamera>(cam->width, cam->height, ToAffine(cam->c2w),
+                                                     Eigen::Vector2f(cam->cx, cam->cy),
+                                                     Eigen::Vector2f(cam->fx, cam->fy));
+  h->raytracer->set_camera(camera);
+  ugu::Image3b c;
+  ugu::Image1f d;
+  ugu::Image3f n;
+  ugu::Image1b m;
+  ugu::Image1i f;
+  const double t0 = NowMs();
+  camera->set_c2w(ToAffine(cam->c2w));
+  const bool ok = h->raytracer->Render(color ? &c : nullptr, depth ? &d : nullptr, normal ? &n : nullptr,
+                                       mask ? &m : nullptr, face_id ? &f : nullptr);
+  if (timing_ms) timing_ms[0] = NowMs() - t0;
+  if (!ok) return 1;
+  const size_t P = static_cast<size_t>(cam->width) * cam->height;
+  if (color) std::memcpy(color, c.data, P * 3);
+  if (depth) std::memcpy(depth, d.data, P * 4);
+  if (normal) std::memcpy(normal, n.data, P * 12);
+  if (mask) std::memcpy(mask, m.data, P);
+  if (face_id) std::memcpy(face_id, f.data, P * 4);
+  return 0;
+}
 
 // Renders one view.  Any output pointer may be null.  `timing_ms` (optional, 2 doubles) receives
 // [0] wall ms of the whole caller-visible step (set_c2w + Render, i.e. including the lazy ray-table
