@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 6
+#define UGU_B200_ABI_VERSION 7
 
 enum {
   UGU_B200_OK = 0,
@@ -330,6 +330,23 @@ int ugu_b200_rasterizer_render_gbuffer(ugu_b200_rasterizer* r, const ugu_b200_ca
 int ugu_b200_rasterizer_render_gbuffer_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
                                               const ugu_b200_gbuffer_option* opt,
                                               const ugu_b200_gbuffer* dev_out, void* stream);
+
+/* Raytracer parity mode: the outputs of ugu::Raytracer::Render
+ * (src/renderer/cpu/raytracer.cc:117-225) — per pixel the nearest hit of the primary ray as
+ * BvhNanort::Intersect(ray, test_all = false) finds it (include/ugu/accel/bvh_nanort.h:109-152; nanort's
+ * watertight TriangleIntersector, third_party/nanort/nanort.h:1050-1199, t in [1e-4, 1e30)), back-face
+ * test on the hit (face_normal . ray_w > 0 leaves the pixel empty), face_id = the hit face (face 0
+ * included), mask 255, depth = (w2c_R (org + ray_w t) + w2c_t).z * option.depth_scale, normal and colour
+ * from the intersector's (u, v) through the same pixel shaders.  No BVH on the device: triangles are
+ * scattered to the pixels their projection can cover and reduced with a 64-bit atomicMin on (t, ~face)
+ * (ugu_b200/csrc/raytrace_kernels.cuh).  Two triangles with bit-identical t at a pixel: the highest face
+ * index wins (nanort: the last one its traversal visits).
+ * `org_w` = 3 floats, PinholeCamera::org_ray_w = the c2w translation cast to float (camera.h:431-436).
+ * Same options, validation, outputs and error behaviour as ugu_b200_rasterizer_render. */
+int ugu_b200_rasterizer_raytrace(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* org_w,
+                                 const ugu_b200_outputs* host_out);
+int ugu_b200_rasterizer_raytrace_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* org_w,
+                                        const ugu_b200_outputs* dev_out, void* stream);
 
 /* Enable (1) / disable (0) per-stage CUDA-event timing; `stage_mask` bit s times stage s. */
 int ugu_b200_rasterizer_set_profiling(ugu_b200_rasterizer* r, int32_t enable, uint32_t stage_mask);

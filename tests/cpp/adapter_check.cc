@@ -17,6 +17,7 @@
 #include "ugu/log.h"
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
+#include "ugu/renderer/cpu/raytracer.h"
 #include "ugu/util/raster_util.h"
 #include "ugu/util/rgbd_util.h"
 #include "ugu/util/camera_util.h"
@@ -279,6 +280,50 @@ int main(int argc, char** argv) {
     }
     ugu::Mesh mm;
     if (rc.Depth2Mesh(dep, *camera, &mm, -1.0f)) failures++;  // false like the reference
+  }
+  {  // Raytracer parity mode: ugu::Raytracer (nanort BVH) vs ugu::RaytracerCuda behind the
+     // same RendererCpu interface; all five outputs compared bit for bit (texture colour: nearest texel,
+     // the unclamped bilinear taps of pixel_shader.h:318-343 read past the texture on this mesh)
+    for (int variant = 0; variant < 2; variant++) {
+      ugu::RendererCpuOption o;
+      o.diffuse_color = variant == 0 ? ugu::DiffuseColor::kVertex : ugu::DiffuseColor::kTexture;
+      o.interp = ugu::ColorInterpolation::kNn;
+      o.shading_normal = variant == 0 ? ugu::ShadingNormal::kVertex : ugu::ShadingNormal::kFace;
+      o.diffuse_shading = variant == 0 ? ugu::DiffuseShading::kLambertian : ugu::DiffuseShading::kNone;
+      o.backface_culling = variant == 0;
+      o.depth_scale = variant == 0 ? 1.0f : 1000.0f;
+      std::unique_ptr<ugu::RendererCpu> ref = std::make_unique<ugu::Raytracer>(o);
+      std::unique_ptr<ugu::RendererCpu> cuda = std::make_unique<ugu::RaytracerCuda>(o);
+      for (ugu::RendererCpu* r : {ref.get(), cuda.get()}) {
+        r->set_mesh(mesh);
+        if (!r->PrepareMesh()) return 1;
+        r->set_camera(camera);
+      }
+      for (int k = 0; k < 3; k++) {
+        const double a = 2.0 * 3.14159265358979323846 * k / 3 + 0.7;
+        Eigen::Matrix4d c2w;
+        ugu::c2w(Eigen::Vector3d(2.9 * std::sin(a), 0.5 * std::cos(2 * a), 2.9 * std::cos(a)),
+                 Eigen::Vector3d(0.02, -0.03, 0.01), Eigen::Vector3d(0, -1, 0), &c2w);
+        camera->set_c2w(Eigen::Affine3d(c2w));
+        Outs o0, o1;
+        if (!ref->Render(&o0.color, &o0.depth, &o0.normal, &o0.mask, &o0.face_id)) return 1;
+        if (!cuda->Render(&o1.color, &o1.depth, &o1.normal, &o1.mask, &o1.face_id)) return 1;
+        const size_t P = static_cast<size_t>(W) * H;
+        const long d_fid = CountDiff(o0.face_id, o1.face_id, 0), d_mask = CountDiff(o0.mask, o1.mask, 0);
+        const long d_depth = CountDiffFloat(reinterpret_cast<float*>(o0.depth.data),
+                                            reinterpret_cast<float*>(o1.depth.data), P);
+        const long d_normal = CountDiffFloat(reinterpret_cast<float*>(o0.normal.data),
+                                             reinterpret_cast<float*>(o1.normal.data), P * 3);
+        const long d_color = CountDiff(o0.color, o1.color, 0);
+        long covered = 0;
+        for (size_t i = 0; i < P; i++) covered += reinterpret_cast<int32_t*>(o0.face_id.data)[i] >= 0;
+        std::printf("Raytracer variant %d view %d: covered %ld  diff face_id %ld mask %ld depth %ld normal %ld "
+                    "color %ld\n", variant, k, covered, d_fid, d_mask, d_depth, d_normal, d_color);
+        if (d_fid || d_mask || d_depth || d_normal || d_color || covered == 0) failures++;
+      }
+      ugu::Image1w w0, w1;
+      if (!ref->RenderDepthW(&w0) || !cuda->RenderDepthW(&w1) || CountDiff(w0, w1, 0)) failures++;
+    }
   }
   {  // G-buffer: no GL reference can run here, so RasterizerCuda::RenderGBuffer is checked
      // for consistency with the reference Rasterizer on the same mesh / camera (winners, depth, colour)

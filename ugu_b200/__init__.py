@@ -8,9 +8,9 @@ meshgen.py (synthetic inputs).  There is no CPU fallback: importing the renderer
 CUDA library raises.
 """
 from .renderer import (ColorInterpolation, DiffuseColor, DiffuseShading, GBuffer, Image1b, Image1f, Image1i,
-                       Image1w, Image3b, Image3f, Material, Mesh, PinholeCamera, Rasterizer,
+                       Image1w, Image3b, Image3f, Material, Mesh, PinholeCamera, Rasterizer, Raytracer,
                        RendererCpuOption, ShadingNormal)
 
 __all__ = ["ColorInterpolation", "DiffuseColor", "DiffuseShading", "GBuffer", "Image1b", "Image1f", "Image1i",
-           "Image1w", "Image3b", "Image3f", "Material", "Mesh", "PinholeCamera", "Rasterizer",
+           "Image1w", "Image3b", "Image3f", "Material", "Mesh", "PinholeCamera", "Rasterizer", "Raytracer",
            "RendererCpuOption", "ShadingNormal"]

@@ -113,6 +113,10 @@ SYMBOLS = {
     "ugu_b200_rasterizer_render_gbuffer_device": (C.c_int, [C.c_void_p, C.POINTER(Camera),
                                                             C.POINTER(GBufferOption), C.POINTER(GBuffer),
                                                             C.c_void_p]),
+    "ugu_b200_rasterizer_raytrace": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(C.c_float),
+                                               C.POINTER(Outputs)]),
+    "ugu_b200_rasterizer_raytrace_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(C.c_float),
+                                                      C.POINTER(Outputs), C.c_void_p]),
     "ugu_b200_rasterizer_set_profiling": (C.c_int, [C.c_void_p, C.c_int32, C.c_uint32]),
     "ugu_b200_rasterizer_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
     "ugu_b200_rasterizer_reset_stats": (C.c_int, [C.c_void_p]),
@@ -140,7 +144,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 6:
+    if lib.ugu_b200_abi_version() != 7:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

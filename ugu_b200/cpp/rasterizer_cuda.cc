@@ -18,6 +18,7 @@ class RasterizerCuda::Impl {
   std::shared_ptr<const Camera> camera_;
   std::shared_ptr<const Mesh> mesh_;
   RendererCpuOption option_;
+  bool raytrace_ = false;  // RaytracerCuda: Render answers like ugu::Raytracer
 
   explicit Impl(int device) {
     if (ugu_b200_rasterizer_create(device, &handle_) != UGU_B200_OK) {
@@ -187,7 +188,14 @@ class RasterizerCuda::Impl {
     out.normal = normal ? reinterpret_cast<float*>(normal->data) : nullptr;
     out.mask = mask ? mask->data : nullptr;
     out.face_id = face_id ? reinterpret_cast<int32_t*>(face_id->data) : nullptr;
-    if (ugu_b200_rasterizer_render(handle_, &c, &out) != UGU_B200_OK) {
+    int rc;
+    if (raytrace_) {  // ugu::Raytracer semantics; ray origin = PinholeCamera::org_ray_w (camera.h:431-436)
+      const Eigen::Vector3f org = camera_->c2w().translation().cast<float>();
+      rc = ugu_b200_rasterizer_raytrace(handle_, &c, org.data(), &out);
+    } else {
+      rc = ugu_b200_rasterizer_render(handle_, &c, &out);
+    }
+    if (rc != UGU_B200_OK) {
       LOGE("%s\n", ugu_b200_last_error(handle_));
       return false;
     }
@@ -452,6 +460,14 @@ bool RasterizerCuda::RenderMask(Image1b* mask) const {
 bool RasterizerCuda::RenderFaceId(Image1i* face_id) const {
   return Render(nullptr, nullptr, nullptr, nullptr, face_id);
 }
+
+void RasterizerCuda::set_raytrace_mode(bool on) { pimpl_->raytrace_ = on; }
+
+RaytracerCuda::RaytracerCuda() : RasterizerCuda() { set_raytrace_mode(true); }
+RaytracerCuda::RaytracerCuda(const RendererCpuOption& option, int device) : RasterizerCuda(option, device) {
+  set_raytrace_mode(true);
+}
+RaytracerCuda::~RaytracerCuda() = default;
 
 bool RasterizerCuda::RenderGBuffer(GBuffer* gbuf, float z_near, float z_far, bool flat_normal, int geo_id) const {
   return pimpl_->RenderGBuffer(gbuf, z_near, z_far, flat_normal, geo_id);

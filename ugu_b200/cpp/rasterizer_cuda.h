@@ -105,6 +105,22 @@ class RasterizerCuda : public RendererCpu {
 
   // false when the CUDA library could not create a rasterizer (no B200 / no driver).
   bool valid() const;
+
+ protected:
+  void set_raytrace_mode(bool on);  // Render / RenderW answer like ugu::Raytracer (see RaytracerCuda)
+};
+
+// Drop-in for ugu::Raytracer (include/ugu/renderer/cpu/raytracer.h:14-53, src/renderer/cpu/raytracer.cc:
+// 117-225): the same RendererCpu interface and call order; Render produces the outputs of the reference's
+// nanort ray caster — nearest hit of each pixel's primary ray (watertight intersector,
+// third_party/nanort/nanort.h:1050-1199, t in [1e-4, 1e30)), back-face test on the hit, face 0 shaded,
+// depth = camera-space z of the hit point * depth_scale, normal / colour from the intersector's (u, v).
+// No BVH is built: PrepareMesh uploads the mesh as for the rasterizer (ugu_b200_rasterizer_raytrace).
+class RaytracerCuda : public RasterizerCuda {
+ public:
+  RaytracerCuda();
+  ~RaytracerCuda() override;
+  explicit RaytracerCuda(const RendererCpuOption& option, int device = 0);
 };
 
 }  // namespace ugu

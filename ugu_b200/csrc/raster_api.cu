@@ -19,6 +19,7 @@
 #include "visibility_kernels.cuh"
 #include "depth2mesh_kernels.cuh"
 #include "gbuffer_kernels.cuh"
+#include "raytrace_kernels.cuh"
 #include "ugu_b200_raster.h"
 
 using namespace ugu_b200;
@@ -83,6 +84,8 @@ struct ugu_b200_rasterizer {
   bool d2m_valid = false;
 
   DevBuf gbuf_arena;  // device outputs of the host-form G-buffer call (gbuffer_kernels.cuh)
+  DevBuf rt_rays;     // per-pixel ray tables of the Raytracer parity mode (raytrace_kernels.cuh), 32 B / pixel
+  float mesh_max_abs = 0.f;  // max |vertex coordinate| of the uploaded mesh
 
   // pinned staging for pageable destinations
   void* staging = nullptr;
@@ -691,6 +694,7 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
     if (r->ev_copied[i]) cudaEventDestroy(r->ev_copied[i]);
   }
   FreeBuf(&r->gbuf_arena);
+  FreeBuf(&r->rt_rays);
   for (auto ev : r->ev_pool)
     if (ev) cudaEventDestroy(ev);
   for (auto ev : r->chunk_events) cudaEventDestroy(ev);
@@ -740,6 +744,14 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   Reorder ro_v, ro_n, ro_uv;
   std::vector<float> pos_p, col_p, nrm_p, uv_p;
   const float* h_vertices = d->vertices;
+  {
+    float mx = 0.f;
+    for (size_t i = 0; i < (size_t)V * 3; i++) {
+      const float a = fabsf(d->vertices[i]);
+      if (a > mx) mx = a;  // NaNs are skipped
+    }
+    r->mesh_max_abs = mx;
+  }
   const float* h_colors = d->vertex_colors;
   const float* h_normals = d->normals;
   const float* h_uv = d->uv;
@@ -1099,6 +1111,105 @@ int ugu_b200_rasterizer_render_gbuffer(ugu_b200_rasterizer* r, const ugu_b200_ca
   if ((rc = RenderView(r, cam, &dout, r->stream, &gp))) return rc;
   CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
                             r->stream));
+  if ((rc = CopyOut(r, segs, r->stream))) return rc;
+  SnapshotCounters(r);
+  return UGU_B200_OK;
+}
+
+namespace {
+// The five kernels of one Raytracer-mode view into device outputs `dout` on stream `st`.
+int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* org_w,
+                 const ugu_b200_outputs* dout, cudaStream_t st) {
+  int rc = EnsureFrame(r, cam->width, cam->height, st);
+  if (rc) return rc;
+  const size_t P = (size_t)cam->width * cam->height;
+  if ((rc = Grow(r, &r->rt_rays, P * 32))) return rc;
+  ViewParams vp;
+  MakeViewParams(cam, &vp);
+  FrameDev fr;
+  fr.proj = (float4*)r->proj.p;
+  fr.ray_dx = (float*)r->ray_dx.p;
+  fr.ray_dy = (float*)r->ray_dy.p;
+  fr.vis = (unsigned long long*)r->vis.p;
+  fr.counters = (unsigned long long*)r->counters.p;
+  fr.q_face = (int*)r->q_face.p;
+  fr.q_job = (unsigned long long*)r->q_job.p;
+  fr.coop_max = 0;
+  const MeshDev& m = r->mesh;
+  RtParams rp;
+  rp.org[0] = org_w[0];
+  rp.org[1] = org_w[1];
+  rp.org[2] = org_w[2];
+  rp.t_min = 0.0001f;  // bvh_nanort.h:119-121
+  rp.t_max = 1.0e+30f;
+  rp.depth_scale = r->opt.depth_scale;
+  rp.coord_scale = fmaxf(r->mesh_max_abs, fmaxf(fabsf(org_w[0]), fmaxf(fabsf(org_w[1]), fabsf(org_w[2]))));
+  rp.ray_a = (float4*)r->rt_rays.p;
+  rp.ray_b = rp.ray_a + P;
+  ShadeParams sp;
+  sp.diffuse_color = r->opt.diffuse_color;
+  sp.interp = r->opt.interp;
+  sp.shading_normal = r->opt.shading_normal;
+  sp.diffuse_shading = r->opt.diffuse_shading;
+  sp.backface_culling = r->opt.backface_culling;
+  {  // OrenNayarParam (pixel_shader.h:143-148)
+    const float sigma = r->opt.oren_nayar_sigma;
+    const float s2 = sigma * sigma;
+    sp.on_A = 1.0f - (0.5f * s2 / (s2 + 0.33f));
+    sp.on_B = 0.45f * s2 / (s2 + 0.09f);
+  }
+  sp.color = dout->color;
+  sp.depth = dout->depth;
+  sp.normal = dout->normal;
+  sp.mask = dout->mask;
+  sp.face_id = dout->face_id;
+  const size_t vthreads = std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H);
+  CU_TRY(r, LaunchView(vertex_kernel_1, Blocks(vthreads, 256), 256, st, false, vp, m, fr));
+  CU_TRY(r, LaunchView(rt_ray_kernel, Blocks(P, 256), 256, st, false, vp, fr, rp));
+  int launches = 3;
+  if (m.F > 0) {
+    CU_TRY(r, LaunchView(rt_raster_kernel, Blocks((size_t)m.F, 256), 256, st, false, vp, m, fr, rp));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(g_num_sms * 2), kRtSlices);
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    CU_TRY(r, cudaLaunchKernelEx(&cfg, rt_large_kernel, vp, m, fr, rp));
+    launches += 2;
+  }
+  CU_TRY(r, LaunchView(rt_resolve_kernel, Blocks(P, 256), 256, st, false, vp, m, fr, rp, sp));
+  CU_TRY(r, cudaGetLastError());
+  r->stats.kernel_launches += launches;
+  r->stats.views++;
+  r->stats.h2d_bytes += sizeof(ViewParams) + sizeof(RtParams);
+  return UGU_B200_OK;
+}
+}  // namespace
+
+int ugu_b200_rasterizer_raytrace_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* org_w,
+                                        const ugu_b200_outputs* dev_out, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  int rc = Validate(r, cam, dev_out);
+  if (rc) return rc;
+  if (!org_w) return Fail(r, UGU_B200_E_INVALID, "ray origin is NULL");
+  CU_TRY(r, cudaSetDevice(r->device));
+  return RaytraceView(r, cam, org_w, dev_out, stream ? (cudaStream_t)stream : r->stream);
+}
+
+int ugu_b200_rasterizer_raytrace(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* org_w,
+                                 const ugu_b200_outputs* host_out) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  int rc = Validate(r, cam, host_out);
+  if (rc) return rc;
+  if (!org_w) return Fail(r, UGU_B200_E_INVALID, "ray origin is NULL");
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t P = (size_t)cam->width * cam->height;
+  ugu_b200_outputs dout;
+  if ((rc = EnsureInternalOutputs(r, 0, host_out, P, &dout))) return rc;
+  if ((rc = RaytraceView(r, cam, org_w, &dout, r->stream))) return rc;
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+                            r->stream));
+  std::vector<CopySeg> segs;
+  CollectSegs(host_out, &dout, P, 0, &segs);
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
   SnapshotCounters(r);
   return UGU_B200_OK;

@@ -377,11 +377,14 @@ class Rasterizer:
             if im is not None:
                 im._init(cam.width, cam.height)
         out = N.Outputs(*[None if im is None else im.data.ctypes.data for im in imgs])
-        rc = self._lib.ugu_b200_rasterizer_render(self._h, C.byref(cam), C.byref(out))
+        rc = self._render_call(cam, out)
         if rc != N.OK:
             LOGE(N.last_error(self._h))
             return False
         return True
+
+    def _render_call(self, cam: "N.Camera", out: "N.Outputs") -> int:
+        return self._lib.ugu_b200_rasterizer_render(self._h, C.byref(cam), C.byref(out))
 
     def RenderColor(self, color: Image3b) -> bool:
         return self.Render(color, None, None, None, None)
@@ -720,3 +723,30 @@ class Rasterizer:
 
     def reset_stats(self) -> None:
         self._lib.ugu_b200_rasterizer_reset_stats(self._h)
+
+
+class Raytracer(Rasterizer):
+    """The CUDA-backed drop-in for ugu::Raytracer (include/ugu/renderer/cpu/raytracer.h,
+    src/renderer/cpu/raytracer.cc:117-225): same interface and call order as the Rasterizer, the outputs
+    are those of the reference's nanort ray caster (nearest hit of the primary ray, back-face test on
+    the hit, depth_scale applied, face 0 shaded) — see ugu_b200_rasterizer_raytrace in the C header."""
+
+    def _org(self, camera: PinholeCamera):
+        o = np.asarray(camera.c2w(), np.float64)[:3, 3].astype(np.float32)  # c2w_t_f_, camera.h:431-436
+        return (C.c_float * 3)(float(o[0]), float(o[1]), float(o[2]))
+
+    def _render_call(self, cam: "N.Camera", out: "N.Outputs") -> int:
+        return self._lib.ugu_b200_rasterizer_raytrace(self._h, C.byref(cam), self._org(self._camera), C.byref(out))
+
+    def render_device(self, camera: PinholeCamera, color=None, depth=None, normal=None, mask=None,
+                      face_id=None, stream: int = 0) -> None:
+        opt = self._native_option()
+        self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+        out = N.Outputs(color, depth, normal, mask, face_id)
+        rc = self._lib.ugu_b200_rasterizer_raytrace_device(self._h, C.byref(camera.to_native()), self._org(camera),
+                                                           C.byref(out), C.c_void_p(stream))
+        if rc != N.OK:
+            raise RuntimeError(N.last_error(self._h))
+
+    def render_batch(self, *a, **k):
+        raise NotImplementedError("the Raytracer mode renders one view per call")
