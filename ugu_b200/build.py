@@ -22,8 +22,7 @@ LIBDIR = ROOT / "lib"
 LIB = LIBDIR / "libugu_b200_raster.so"
 
 SOURCES = [CSRC / "raster_api.cu", CSRC / "camera_host.cc"]
-DEPS = SOURCES + [CSRC / "raster_kernels.cuh", CSRC / "uv_raster_kernels.cuh", CSRC / "visibility_kernels.cuh", CSRC / "depth2mesh_kernels.cuh",
-                  REPO / "include" / "ugu_b200_raster.h"]
+DEPS = SOURCES + sorted(CSRC.glob("*.cuh")) + [REPO / "include" / "ugu_b200_raster.h"]  # every kernel header
 
 NVCC_FLAGS = [
     "-std=c++17", "-O3", "--fmad=false", "-lineinfo",

@@ -12,9 +12,9 @@
 // and the ray set-up (PrepareTraversal, nanort.h:1160-1199) are evaluated with the reference's single
 // float operations in its order (--fmad=false), the U/V/W == 0 edge case in double like nanort.
 //
-// Candidates must be a superset of the hits: the bbox of the projected vertices is widened by half a
-// pixel plus a bound on the projection's rounding error (it grows as a vertex approaches the camera
-// plane); a triangle with a vertex at or behind the camera plane is tested against every pixel.
+// Candidates must be a superset of the hits: the bbox of the projected vertices is widened by a bound on
+// the rounding error of the projection and of the intersector (it grows as a vertex approaches the camera
+// plane), and the integer points inside it are the candidates; a triangle with a vertex at or behind the camera plane is tested against every pixel.
 //
 // Equal t at a pixel (duplicate / coincident triangles): nanort keeps the last triangle VISITED, which
 // depends on its BVH; here the HIGHEST face index wins (what nanort does when the tied triangles share
@@ -139,13 +139,16 @@ __device__ __forceinline__ int rt_bounds(const ViewParams& vp, const RtParams& r
   // rounding error of a projected coordinate X (pixels from the principal point): the projection's own
   // few ulps plus the cancellation error of the camera-space z (~1e-6 * coord_scale) relative to z
   const float ext = fmaxf(fmaxf(fabsf(xmin - vp.cx), fabsf(xmax - vp.cx)), fmaxf(fabsf(ymin - vp.cy), fabsf(ymax - vp.cy)));
-  const float margin = 0.5f + ext * (4e-6f + 1e-6f * rp.coord_scale / zmin);
+  // (pixel (x, y)'s ray passes exactly through image point (x, y): only rounding separates "the ray hits"
+  //  from "the integer point lies in the projected triangle", so the margin is an error bound, not a
+  //  pixel footprint: 0.02 px floor + 4x the estimated relative error)
+  const float margin = 0.02f + ext * (1.6e-5f + 4e-6f * rp.coord_scale / zmin);
   if (!(margin < 64.0f)) return 2;
   if (xmin - margin > vp.wm1 || xmax + margin < 0.0f || ymin - margin > vp.hm1 || ymax + margin < 0.0f) return 0;
-  x0 = max(0, sat_int(floorf(xmin - margin)));
-  x1 = min(vp.W - 1, sat_int(ceilf(xmax + margin)));
-  y0 = max(0, sat_int(floorf(ymin - margin)));
-  y1 = min(vp.H - 1, sat_int(ceilf(ymax + margin)));
+  x0 = max(0, sat_int(ceilf(xmin - margin)));
+  x1 = min(vp.W - 1, sat_int(floorf(xmax + margin)));
+  y0 = max(0, sat_int(ceilf(ymin - margin)));
+  y1 = min(vp.H - 1, sat_int(floorf(ymax + margin)));
   return (x1 >= x0 && y1 >= y0) ? 1 : 0;
 }
 
