@@ -95,9 +95,10 @@ __device__ __forceinline__ bool gbuffer_pixel(const ViewParams& vp, const MeshDe
 
   const int4 vr = __ldg(m.frec + 2 * (size_t)fid);
   const float4 p0 = fr.proj[vr.x], p1 = fr.proj[vr.y], p2 = fr.proj[vr.z];
-  const float P0x = __ldg(m.pos_x + vr.x), P0y = __ldg(m.pos_y + vr.x), P0z = __ldg(m.pos_z + vr.x);
-  const float P1x = __ldg(m.pos_x + vr.y), P1y = __ldg(m.pos_y + vr.y), P1z = __ldg(m.pos_z + vr.y);
-  const float P2x = __ldg(m.pos_x + vr.z), P2y = __ldg(m.pos_y + vr.z), P2z = __ldg(m.pos_z + vr.z);
+  const float4 q0 = __ldg(m.pos4 + vr.x), q1 = __ldg(m.pos4 + vr.y), q2 = __ldg(m.pos4 + vr.z);
+  const float P0x = q0.x, P0y = q0.y, P0z = q0.z;
+  const float P1x = q1.x, P1y = q1.y, P1z = q1.z;
+  const float P2x = q2.x, P2y = q2.y, P2z = q2.z;
   float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
   const bool vnormal = !gp.flat_normal && gp.have_normals;
   if (vnormal) {

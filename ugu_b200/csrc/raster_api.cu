@@ -822,6 +822,11 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     UP_TRY(upload(h_vertices, (size_t)V * 12, &t));
     repack_vec3_to_planes<<<Blocks(V, 256), 256, 0, st>>>((const float*)t, V, px, py, pz);
     r->stats.kernel_launches++;
+    float4* p4 = nullptr;
+    UP_TRY(MeshAlloc(r, &p4, V));
+    repack_vec3_to_float4<<<Blocks(V, 256), 256, 0, st>>>((const float*)t, V, p4);
+    r->stats.kernel_launches++;
+    m.pos4 = p4;
   }
   m.pos_x = px; m.pos_y = py; m.pos_z = pz;
 

@@ -55,6 +55,7 @@ struct MeshDev {
   const float* pos_x;
   const float* pos_y;
   const float* pos_z;
+  const float4* pos4;   // the same positions as one 16-byte record per vertex (gathers by vertex index)
   const int* idx0;
   const int* idx1;
   const int* idx2;

@@ -157,17 +157,32 @@ __device__ __forceinline__ void rt_load_face(const MeshDev& m, const RtParams& r
   i0 = __ldg(m.idx0 + f);
   i1 = __ldg(m.idx1 + f);
   i2 = __ldg(m.idx2 + f);
-  A[0] = __ldg(m.pos_x + i0) - rp.org[0]; A[1] = __ldg(m.pos_y + i0) - rp.org[1]; A[2] = __ldg(m.pos_z + i0) - rp.org[2];
-  B[0] = __ldg(m.pos_x + i1) - rp.org[0]; B[1] = __ldg(m.pos_y + i1) - rp.org[1]; B[2] = __ldg(m.pos_z + i1) - rp.org[2];
-  C[0] = __ldg(m.pos_x + i2) - rp.org[0]; C[1] = __ldg(m.pos_y + i2) - rp.org[1]; C[2] = __ldg(m.pos_z + i2) - rp.org[2];
+  const float4 p0 = __ldg(m.pos4 + i0), p1 = __ldg(m.pos4 + i1), p2 = __ldg(m.pos4 + i2);
+  A[0] = p0.x - rp.org[0]; A[1] = p0.y - rp.org[1]; A[2] = p0.z - rp.org[2];
+  B[0] = p1.x - rp.org[0]; B[1] = p1.y - rp.org[1]; B[2] = p1.z - rp.org[2];
+  C[0] = p2.x - rp.org[0]; C[1] = p2.y - rp.org[1]; C[2] = p2.z - rp.org[2];
 }
 
-// RT-K2: a lane per face.  Faces whose candidate bbox holds <= kRtInLaneMax pixels are traced by their
-// lane; larger ones are appended to the queue (one atomicAdd per warp) for RT-K3.
+// RT-K2: a warp per 32 faces.  Phase A (lane = face): gather, candidate bbox; faces whose bbox holds more
+// than kRtInLaneMax pixels are appended to the queue (one atomicAdd per warp) for RT-K3, the others are
+// compacted into a per-warp shared-memory table.  Phase B (lane = candidate pixel): the candidates of
+// all tabled faces form one index space [0, T) that the warp walks 32 at a time, so lanes stay busy
+// whatever the mix of bbox sizes (the owner of a candidate is found from a REDUX.OR bitmask of the
+// faces' start offsets, as in raster_kernel).
+struct __align__(16) RtWarpFaces {
+  float4 a[32];   // A.xyz, B.x        (A = p0 - org, ...)
+  float4 b[32];   // B.yz, C.xy
+  float4 c[32];   // C.z, (x0 | y0 << 16), face, -
+  int2 meta[32];  // first candidate of the face in the warp's index space; nx | ceil(65536 / nx) << 9
+};
+
 __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, const MeshDev m, const FrameDev fr,
                                                         const RtParams rp) {
+  __shared__ RtWarpFaces sh[8];
+  RtWarpFaces& S = sh[threadIdx.x >> 5];
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
+  const unsigned lt_mask = (1u << lane) - 1u;
   int x0 = 0, y0 = 0, x1 = -1, y1 = -1, kind = 0;
   float A[3], B[3], C[3];
   if (f < m.F) {
@@ -182,11 +197,50 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
     unsigned long long base = 0ull;
     if (lane == 0u) base = atomicAdd(fr.counters, (unsigned long long)__popc(lb));
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (large) fr.q_face[base + __popc(lb & ((1u << lane) - 1u))] = f;
+    if (large) fr.q_face[base + __popc(lb & lt_mask)] = f;
   }
-  if (kind == 0 || large) return;
-  for (int y = y0; y <= y1; y++)
-    for (int x = x0; x <= x1; x++) rt_sample(rp, fr, (unsigned)y * (unsigned)vp.W + (unsigned)x, f, A, B, C);
+  const int cnt = (kind != 0 && !large) ? nx * ny : 0;
+  const unsigned rec = __ballot_sync(0xffffffffu, cnt > 0);
+  if (rec == 0u) return;
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (unsigned)d) incl += o;
+  }
+  const int T = __shfl_sync(0xffffffffu, incl, 31);
+  if (cnt > 0) {
+    const int slot = __popc(rec & lt_mask);
+    S.a[slot] = make_float4(A[0], A[1], A[2], B[0]);
+    S.b[slot] = make_float4(B[1], B[2], C[0], C[1]);
+    S.c[slot] = make_float4(C[2], __int_as_float(x0 | (y0 << 16)), __int_as_float(f), 0.f);
+    const int recip = (int)(65536.0f / small_int_to_float(nx));  // ceil(65536 / nx), nx <= 64
+    S.meta[slot] = make_int2(incl - cnt, nx | ((recip + ((recip * nx) < 65536 ? 1 : 0)) << 9));
+  }
+  __syncwarp();
+  const int nslots = __popc(rec);
+  const int st = ((int)lane < nslots) ? S.meta[lane].x : 0x7fffffff;
+  const unsigned le_mask = lt_mask | (1u << lane);
+  int started = 0;
+  for (int sb = 0; sb < T; sb += 32) {
+    const unsigned rr = (unsigned)(st - sb);
+    const unsigned starts = __reduce_or_sync(0xffffffffu, rr < 32u ? (1u << rr) : 0u);
+    const int s = sb + (int)lane;
+    if (s < T) {
+      const int slot = started + __popc(starts & le_mask) - 1;
+      const int2 mt = S.meta[slot];
+      const float4 ta = S.a[slot], tb = S.b[slot], tc = S.c[slot];
+      const int k = s - mt.x;
+      const int w = mt.y & 511;
+      const int dy = (k * (mt.y >> 9)) >> 16;  // k / w, exact for k, w <= 256
+      const int dx = k - dy * w;
+      const unsigned xy = __float_as_uint(tc.y);
+      const unsigned x = (xy & 0xFFFFu) + (unsigned)dx, y = (xy >> 16) + (unsigned)dy;
+      const float FA[3] = {ta.x, ta.y, ta.z}, FB[3] = {ta.w, tb.x, tb.y}, FC[3] = {tb.z, tb.w, tc.x};
+      rt_sample(rp, fr, y * (unsigned)vp.W + x, __float_as_int(tc.z), FA, FB, FC);
+    }
+    started += __popc(starts);
+  }
 }
 
 // RT-K3: queued faces.  CTA (q, s) takes queue entries q, q + gridDim.x, ... and of each entry's bbox the
@@ -276,6 +330,8 @@ __device__ __forceinline__ unsigned rt_shade(const MeshDev& m, const ShadeParams
 // (t, u, v) are recomputed from the winner with the same intersector (bit-identical).
 __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, const MeshDev m, const FrameDev fr,
                                                          const RtParams rp, const ShadeParams sp) {
+  __shared__ __align__(16) float s_n[8][96];
+  __shared__ __align__(16) unsigned char s_c[8][96];
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
   const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0u) {
@@ -283,8 +339,7 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
     fr.counters[5] = 0ull;
     fr.counters[0] = 0ull;
   }
-  if (p >= P) return;
-  const unsigned long long key = fr.vis[p];
+  const unsigned long long key = p < P ? fr.vis[p] : kVisEmpty;
   unsigned color = 0u;
   float depth = 0.0f, nx = 0.0f, ny = 0.0f, nz = 0.0f;
   bool mask = false;
@@ -300,9 +355,10 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
       keep = !(dot3(__ldg(m.fn_x + fid), __ldg(m.fn_y + fid), __ldg(m.fn_z + fid), ra.x, ra.y, ra.z) > 0.0f);
     if (keep) {
       float A[3], B[3], C[3], t, u, v;
-      A[0] = __ldg(m.pos_x + vr.x) - rp.org[0]; A[1] = __ldg(m.pos_y + vr.x) - rp.org[1]; A[2] = __ldg(m.pos_z + vr.x) - rp.org[2];
-      B[0] = __ldg(m.pos_x + vr.y) - rp.org[0]; B[1] = __ldg(m.pos_y + vr.y) - rp.org[1]; B[2] = __ldg(m.pos_z + vr.y) - rp.org[2];
-      C[0] = __ldg(m.pos_x + vr.z) - rp.org[0]; C[1] = __ldg(m.pos_y + vr.z) - rp.org[1]; C[2] = __ldg(m.pos_z + vr.z) - rp.org[2];
+      const float4 p0 = __ldg(m.pos4 + vr.x), p1 = __ldg(m.pos4 + vr.y), p2 = __ldg(m.pos4 + vr.z);
+      A[0] = p0.x - rp.org[0]; A[1] = p0.y - rp.org[1]; A[2] = p0.z - rp.org[2];
+      B[0] = p1.x - rp.org[0]; B[1] = p1.y - rp.org[1]; B[2] = p1.z - rp.org[2];
+      C[0] = p2.x - rp.org[0]; C[1] = p2.y - rp.org[1]; C[2] = p2.z - rp.org[2];
       (void)rt_intersect(rb, ra.w, A, B, C, t, u, v);
       face_id = fid;
       mask = true;
@@ -330,19 +386,50 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
       if (sp.color) color = rt_shade(m, sp, fid, vr, u, v, ra.x, ra.y, ra.z, nwx, nwy, nwz);
     }
   }
-  if (sp.color) {
-    sp.color[(size_t)p * 3 + 0] = (uint8_t)(color & 0xFFu);
-    sp.color[(size_t)p * 3 + 1] = (uint8_t)((color >> 8) & 0xFFu);
-    sp.color[(size_t)p * 3 + 2] = (uint8_t)((color >> 16) & 0xFFu);
+  // stores: a warp owns 32 consecutive pixels; colour / normal are staged through shared memory so that
+  // every global store is a full 16-byte vector (as resolve_kernel does)
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const unsigned wbase = p - lane;
+  if (wbase + 32u <= P) {
+    if (sp.depth) sp.depth[p] = depth;
+    if (sp.face_id) sp.face_id[p] = face_id;
+    if (sp.mask) {
+      const unsigned bal = __ballot_sync(0xffffffffu, mask);
+      if (lane < 8u) {
+        const unsigned nb = (bal >> (lane * 4u)) & 15u;  // nibble -> 4 bytes of 0x00 / 0xFF
+        *reinterpret_cast<unsigned*>(sp.mask + wbase + lane * 4u) = ((nb * 0x00204081u) & 0x01010101u) * 0xFFu;
+      }
+    }
+    if (sp.normal) {
+      s_n[warp][lane * 3u + 0u] = nx;
+      s_n[warp][lane * 3u + 1u] = ny;
+      s_n[warp][lane * 3u + 2u] = nz;
+    }
+    if (sp.color) {
+      s_c[warp][lane * 3u + 0u] = (unsigned char)(color & 0xFFu);
+      s_c[warp][lane * 3u + 1u] = (unsigned char)((color >> 8) & 0xFFu);
+      s_c[warp][lane * 3u + 2u] = (unsigned char)((color >> 16) & 0xFFu);
+    }
+    __syncwarp();
+    if (sp.normal && lane < 24u)
+      reinterpret_cast<float4*>(sp.normal + (size_t)wbase * 3u)[lane] = reinterpret_cast<const float4*>(s_n[warp])[lane];
+    if (sp.color && lane < 6u)
+      reinterpret_cast<uint4*>(sp.color + (size_t)wbase * 3u)[lane] = reinterpret_cast<const uint4*>(s_c[warp])[lane];
+  } else if (p < P) {  // ragged last chunk of the image
+    if (sp.color) {
+      sp.color[(size_t)p * 3 + 0] = (uint8_t)(color & 0xFFu);
+      sp.color[(size_t)p * 3 + 1] = (uint8_t)((color >> 8) & 0xFFu);
+      sp.color[(size_t)p * 3 + 2] = (uint8_t)((color >> 16) & 0xFFu);
+    }
+    if (sp.depth) sp.depth[p] = depth;
+    if (sp.normal) {
+      sp.normal[(size_t)p * 3 + 0] = nx;
+      sp.normal[(size_t)p * 3 + 1] = ny;
+      sp.normal[(size_t)p * 3 + 2] = nz;
+    }
+    if (sp.mask) sp.mask[p] = mask ? 255 : 0;
+    if (sp.face_id) sp.face_id[p] = face_id;
   }
-  if (sp.depth) sp.depth[p] = depth;
-  if (sp.normal) {
-    sp.normal[(size_t)p * 3 + 0] = nx;
-    sp.normal[(size_t)p * 3 + 1] = ny;
-    sp.normal[(size_t)p * 3 + 2] = nz;
-  }
-  if (sp.mask) sp.mask[p] = mask ? 255 : 0;
-  if (sp.face_id) sp.face_id[p] = face_id;
 }
 
 }  // namespace ugu_b200
