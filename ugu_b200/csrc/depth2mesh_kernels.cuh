@@ -115,18 +115,39 @@ __device__ __forceinline__ unsigned long long d2m_block_scan(unsigned long long 
   return base + incl - v;
 }
 
-// D2M-K1: index of the first valid grid point (it becomes vertex 0)
+// D2M-K1: index of the first valid grid point (it becomes vertex 0).  A resident grid walks the
+// kD2MBlock-point chunks in ascending order; a warp stops as soon as a grid point below its next chunk is
+// known to be valid, so the image is read only up to (one round past) the first valid depth.
 __global__ void __launch_bounds__(256) d2m_first_kernel(const D2MParams p) {
+  __shared__ int s_known;
+  __shared__ int s_min[8];
   const int G = p.GX * p.GY;
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
-  int mine = 0x7fffffff;
-  if (g < G) {
-    const int gy = g / p.GX, gx = g - gy * p.GX;
-    if (d2m_valid(d2m_depth(p, gx, gy))) mine = g;
+  const int nchunks = (G + kD2MBlock - 1) / kD2MBlock;
+  for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
+    const int base = chunk * kD2MBlock;
+    if (threadIdx.x == 0) s_known = *(volatile int*)p.first;
+    __syncthreads();
+    if (base > s_known) break;  // CTA-uniform
+    int mine = 0x7fffffff;
+#pragma unroll
+    for (int k = kD2MItems - 1; k >= 0; k--) {
+      const int g = base + k * 256 + (int)threadIdx.x;
+      if (g < G) {
+        const int gy = g / p.GX, gx = g - gy * p.GX;
+        if (d2m_valid(d2m_depth(p, gx, gy))) mine = g;  // descending k: the lowest valid g survives
+      }
+    }
+    mine = __reduce_min_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31u) == 0u) s_min[threadIdx.x >> 5] = mine;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int m = s_min[0];
+#pragma unroll
+      for (int w = 1; w < 8; w++) m = min(m, s_min[w]);
+      // one same-address atomic per CTA at most, and only if it can still lower the (re-read) value
+      if (m < *(volatile int*)p.first) atomicMin(p.first, m);
+    }
   }
-  mine = __reduce_min_sync(0xffffffffu, mine);
-  // the value only ever decreases: a warp that cannot lower it skips the (same-address) atomic
-  if ((threadIdx.x & 31u) == 0u && mine != 0x7fffffff && mine < *(volatile int*)p.first) atomicMin(p.first, mine);
 }
 
 // D2M-K2: per-CTA sums of the packed contributions
@@ -164,31 +185,29 @@ __global__ void __launch_bounds__(256) d2m_scan_kernel(const D2MParams p, int nb
 __global__ void __launch_bounds__(256) d2m_emit_vertices_kernel(const D2MParams p) {
   const int G = p.GX * p.GY;
   const int first = p.first[0];
-  const int g0 = blockIdx.x * kD2MBlock + threadIdx.x * kD2MItems;
-  unsigned long long c[kD2MItems];
-  unsigned tris[kD2MItems];
-  unsigned long long sum = 0ull;
-#pragma unroll
+  // The CTA owns the same kD2MBlock consecutive grid points as in d2m_count_kernel, but walks them as
+  // kD2MItems slabs of 256 with lane = consecutive grid point: loads of depth and stores of the per-point
+  // images are coalesced, and the compacted vertex ids of a warp are (nearly) consecutive, so the
+  // vertex / uv / colour stores of a warp land in adjacent sectors.  One CTA scan per slab, running carry.
+  unsigned long long carry = p.block_sums[blockIdx.x];
+#pragma unroll 1
   for (int k = 0; k < kD2MItems; k++) {
-    c[k] = d2m_contrib(p, g0 + k, G, first, tris[k]);
-    sum += c[k];
-  }
-  unsigned long long total;
-  unsigned long long run = p.block_sums[blockIdx.x] + d2m_block_scan(sum, total);
-#pragma unroll
-  for (int k = 0; k < kD2MItems; k++) {
-    const int g = g0 + k;
-    if (g >= G) break;
-    if (c[k] == 0ull) {
+    const int g = blockIdx.x * kD2MBlock + k * 256 + (int)threadIdx.x;
+    unsigned tris;
+    const unsigned long long c = d2m_contrib(p, g, G, first, tris);
+    unsigned long long total;
+    const unsigned long long run = carry + d2m_block_scan(c, total);
+    carry += total;
+    if (g >= G) continue;
+    if (c == 0ull) {
       p.vid[g] = -1;
       p.fref[g] = 0u;
       continue;
     }
     const int v = (int)(run & 0xFFFFFFFFull);
     const unsigned f0 = (unsigned)(run >> 32);
-    run += c[k];
     p.vid[g] = v;
-    p.fref[g] = f0 | (tris[k] << 30);
+    p.fref[g] = f0 | (tris << 30);
     const int gy = g / p.GX, gx = g - gy * p.GX;
     float pos[3];
     d2m_unproject(p, gx, gy, d2m_depth(p, gx, gy), pos);

@@ -1661,7 +1661,7 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
   CU_TRY(r, cudaMemsetAsync(r->d2m_pc.p, 0, P * 12, st));            // ugu::Init(point_cloud, .., 0.0f)
   CU_TRY(r, cudaMemsetAsync(r->d2m_nimg.p, 0, P * 12, st));
   if (G > 0) {
-    d2m_first_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
+    d2m_first_kernel<<<(unsigned)std::min<size_t>((size_t)nblocks, (size_t)g_num_sms * 8), 256, 0, st>>>(p);
     d2m_count_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
     d2m_scan_kernel<<<1, 256, 0, st>>>(p, nblocks);
     d2m_emit_vertices_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
