@@ -41,13 +41,10 @@ __device__ __forceinline__ float rt_sel(float a0, float a1, float a2, int k) {
   return k == 0 ? a0 : (k == 1 ? a1 : a2);
 }
 
-// RT-K1: the per-pixel ray (PinholeCamera::ray_w, camera.h:438-448) and nanort's per-ray constants
-// (TriangleIntersector::PrepareTraversal, nanort.h:1160-1199).
-__global__ void __launch_bounds__(256) rt_ray_kernel(const ViewParams vp, const FrameDev fr, const RtParams rp) {
-  const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
-  const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= P) return;
-  const unsigned y = p / (unsigned)vp.W, x = p - y * (unsigned)vp.W;
+// The ray of pixel (x, y) (PinholeCamera::ray_w, camera.h:438-448) and nanort's per-ray constants
+// (TriangleIntersector::PrepareTraversal, nanort.h:1160-1199): ra = dir.xyz, Sz; rb = Sx, Sy, k-pack.
+__device__ __forceinline__ void rt_make_ray(const ViewParams& vp, const FrameDev& fr, unsigned x, unsigned y,
+                                            float4& ra, float4& rb) {
   float d[3];
   ray_world(vp, fr.ray_dx[x], fr.ray_dy[y], d[0], d[1], d[2]);
   int kz = 0;
@@ -73,8 +70,21 @@ __global__ void __launch_bounds__(256) rt_ray_kernel(const ViewParams vp, const 
   const float Sx = rt_sel(d[0], d[1], d[2], kx) / dz;
   const float Sy = rt_sel(d[0], d[1], d[2], ky) / dz;
   const float Sz = 1.0f / dz;
-  rp.ray_a[p] = make_float4(d[0], d[1], d[2], Sz);
-  rp.ray_b[p] = make_float4(Sx, Sy, __int_as_float(kx | (ky << 2) | (kz << 4)), 0.f);
+  ra = make_float4(d[0], d[1], d[2], Sz);
+  rb = make_float4(Sx, Sy, __int_as_float(kx | (ky << 2) | (kz << 4)), 0.f);
+}
+
+// RT-K1: the ray table read by the candidate tests of RT-K2 / RT-K3 (32 bytes per pixel, L2-resident at
+// the BASELINE image sizes).
+__global__ void __launch_bounds__(256) rt_ray_kernel(const ViewParams vp, const FrameDev fr, const RtParams rp) {
+  const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
+  const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const unsigned y = p / (unsigned)vp.W, x = p - y * (unsigned)vp.W;
+  float4 ra, rb;
+  rt_make_ray(vp, fr, x, y, ra, rb);
+  rp.ray_a[p] = ra;
+  rp.ray_b[p] = rb;
 }
 
 // TriangleIntersector::Intersect (nanort.h:1050-1148) for one (ray, triangle) pair without the running
@@ -347,9 +357,14 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
   if (key != kVisEmpty) {
     fr.vis[p] = kVisEmpty;
     const int fid = (int)(0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull));
-    const float4 ra = rp.ray_a[p];
-    const float4 rb = rp.ray_b[p];
-    const int4 vr = __ldg(m.frec + 2 * (size_t)fid);
+    const int4 vr = __ldg(m.frec + 2 * (size_t)fid);  // issued first: the head of the gather chain
+    // the winner's ray is recomputed (same function as the table: identical bits) instead of read back:
+    // hits are a minority of the pixels and the table is 32 bytes per pixel
+    float4 ra, rb;
+    {
+      const unsigned y = (vp.W == 1) ? p : (__umulhi(p, vp.w_magic) >> vp.w_shift);
+      rt_make_ray(vp, fr, p - y * (unsigned)vp.W, y, ra, rb);
+    }
     bool keep = true;
     if (sp.backface_culling)  // raytracer.cc:155-160: face normal . ray > 0 -> the pixel stays empty
       keep = !(dot3(__ldg(m.fn_x + fid), __ldg(m.fn_y + fid), __ldg(m.fn_z + fid), ra.x, ra.y, ra.z) > 0.0f);
