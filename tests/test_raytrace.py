@@ -154,6 +154,29 @@ def test_cuda_raytracer_vs_live_reference_larger_views():
 
 
 @pytest.mark.gpu
+def test_cuda_raytracer_state_machine_and_failures():
+    """false + log where the reference returns false: empty mesh at PrepareMesh (raytracer.cc:96-99), Render
+    before PrepareMesh / without a camera, all-null outputs, texture colour without materials."""
+    from ugu_b200 import Image1i, Image3b, Mesh, Raytracer
+    mesh, cam, opt, _ = _load("ico4_vertex_cull")
+    r = Raytracer(opt)
+    r.set_mesh(Mesh(vertices=np.zeros((0, 3), np.float32), vertex_indices=np.zeros((0, 3), np.int32)))
+    assert not r.PrepareMesh()
+    r.set_mesh(mesh)
+    fid = Image1i()
+    r.set_camera(cam)
+    assert not r.RenderFaceId(fid)            # set_mesh invalidates PrepareMesh (raytracer.cc:79)
+    assert r.PrepareMesh()
+    assert not r.Render(None, None, None, None, None)
+    assert r.RenderFaceId(fid) and (fid.data >= 0).any()
+    r.set_option(RendererCpuOption(diffuse_color=DiffuseColor.kTexture))
+    assert not r.RenderColor(Image3b())       # no materials on the icosphere
+    assert not r.RenderFaceId(fid)            # ... whichever output is asked for (util_private.cc:31-35)
+    r.set_option(opt)
+    assert r.RenderFaceId(fid)
+
+
+@pytest.mark.gpu
 def test_cuda_raytracer_device_form():
     import torch
     from ugu_b200 import Raytracer

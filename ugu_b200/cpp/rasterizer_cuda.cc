@@ -33,6 +33,10 @@ class RasterizerCuda::Impl {
       LOGE("mesh has not been set\n");
       return false;
     }
+    if (raytrace_ && (mesh_->vertices().empty() || mesh_->vertex_indices().empty())) {
+      LOGE("mesh is empty\n");  // Raytracer::Impl::PrepareMesh, raytracer.cc:96-99
+      return false;
+    }
     if (handle_ == nullptr) {
       LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
       return false;

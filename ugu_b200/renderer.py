@@ -731,6 +731,14 @@ class Raytracer(Rasterizer):
     are those of the reference's nanort ray caster (nearest hit of the primary ray, back-face test on
     the hit, depth_scale applied, face 0 shaded) — see ugu_b200_rasterizer_raytrace in the C header."""
 
+    def PrepareMesh(self) -> bool:
+        m = self._mesh
+        if m is not None and (m.vertices is None or len(m.vertices) == 0 or m.vertex_indices is None
+                              or len(m.vertex_indices) == 0):
+            LOGE("mesh is empty")  # Raytracer::Impl::PrepareMesh, raytracer.cc:96-99
+            return False
+        return super().PrepareMesh()
+
     def _org(self, camera: PinholeCamera):
         o = np.asarray(camera.c2w(), np.float64)[:3, 3].astype(np.float32)  # c2w_t_f_, camera.h:431-436
         return (C.c_float * 3)(float(o[0]), float(o[1]), float(o[2]))
