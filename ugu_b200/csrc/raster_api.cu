@@ -1196,6 +1196,9 @@ int ugu_b200_rasterizer_raytrace_device(ugu_b200_rasterizer* r, const ugu_b200_c
   int rc = Validate(r, cam, dev_out);
   if (rc) return rc;
   if (!org_w) return Fail(r, UGU_B200_E_INVALID, "ray origin is NULL");
+  const uintptr_t align = (uintptr_t)dev_out->color | (uintptr_t)dev_out->depth | (uintptr_t)dev_out->normal |
+                          (uintptr_t)dev_out->mask | (uintptr_t)dev_out->face_id;
+  if (align & 15u) return Fail(r, UGU_B200_E_INVALID, "device outputs must be 16-byte aligned");
   CU_TRY(r, cudaSetDevice(r->device));
   return RaytraceView(r, cam, org_w, dev_out, stream ? (cudaStream_t)stream : r->stream);
 }
