@@ -200,6 +200,28 @@ def test_cuda_raytracer_full_size_config4_agrees_with_the_rasterizer():
 
 
 @pytest.mark.gpu
+def test_cuda_raytracer_far_from_origin_and_tiny_scale():
+    """The candidate bbox must stay a superset of nanort's hits when float cancellation makes the projected
+    vertices coarse (mesh and camera thousands of units from the origin) and when everything is tiny
+    (hits near t_min = 1e-4): compared with the brute-force restatement, which tests every triangle."""
+    from ugu_b200 import Mesh
+    base = meshgen.icosphere(4)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, backface_culling=False)
+    for off, scale, dist in (((5000.0, -3000.0, 2000.0), 1.0, 2.7), ((0.0, 0.0, 0.0), 1e-3, 2.7e-3),
+                             ((-40000.0, 100.0, 7.0), 30.0, 95.0)):
+        off = np.asarray(off, np.float32)
+        mesh = Mesh(vertices=(base.vertices * np.float32(scale) + off).astype(np.float32),
+                    vertex_indices=base.vertex_indices, face_normals=base.face_normals, normals=base.normals,
+                    normal_indices=base.normal_indices, vertex_colors=base.vertex_colors)
+        eye = off.astype(np.float64) + np.array([0.3 * dist, 0.2 * dist, -dist])
+        cam = PinholeCamera(96, 72, meshgen.look_at_c2w(eye, off.astype(np.float64), (0, -1, 0)), fov_y_deg=45.0)
+        want = port_raytrace(OraclePort(mesh), cam.to_native(), _org(cam), opt)
+        _, got = _cuda_raytrace(mesh, cam, opt)
+        assert (want["face_id"] >= 0).sum() > 500, (off, scale)
+        _assert_same(got, want, f"offset {off.tolist()} scale {scale}")
+
+
+@pytest.mark.gpu
 def test_cuda_raytracer_state_machine_and_failures():
     """false + log where the reference returns false: empty mesh at PrepareMesh (raytracer.cc:96-99), Render
     before PrepareMesh / without a camera, all-null outputs, texture colour without materials."""
