@@ -72,6 +72,20 @@ def test_port_vs_live_reference_orbit():
                      f"orbit {k}")
 
 
+@pytest.mark.skipif(not ref_available(), reason="oracle/_ref not built here")
+@pytest.mark.parametrize("seed", [31, 32, 33, 34])
+def test_port_vs_live_reference_random_soups(seed):
+    """Random triangle soups (large + sub-pixel triangles, flipped / unnormalised face normals, two
+    textures) under every option set: the brute-force restatement against the reference's BVH query."""
+    from oracle import OracleRef
+    mesh = cases.random_soup(250, seed)
+    ref, port = OracleRef(mesh), OraclePort(mesh)
+    cam = cases.kat_camera(80, 60)
+    for tag, opt in cases.ALL_OPTIONS:
+        opt = RendererCpuOption(**{**opt.__dict__, "depth_scale": 1.0 + seed})
+        _assert_same(port_raytrace(port, cam.to_native(), _org(cam), opt), ref.raytrace(cam, opt), f"soup {seed} {tag}")
+
+
 # ---------------------------------------------------------------------------------------------- GPU
 def _cuda_raytrace(mesh, cam, opt, want=cases.OUTPUT_KEYS, pinned=True):
     from ugu_b200 import Image1b, Image1f, Image1i, Image3b, Image3f, Raytracer
@@ -91,6 +105,28 @@ def test_cuda_raytracer_vs_reference_fixture(name):
     mesh, cam, opt, want = _load(name)
     _, got = _cuda_raytrace(mesh, cam, opt)
     _assert_same(got, want, name)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [41, 42, 43])
+def test_cuda_raytracer_vs_port_random_soups(seed):
+    """2000-triangle soups (10 % large: the queued path) under every option set, odd image sizes."""
+    from ugu_b200 import Image1b, Image1f, Image1i, Image3b, Image3f, Raytracer
+    mesh = cases.random_soup(2000, seed)
+    port = OraclePort(mesh)
+    cam = cases.kat_camera(131, 77)
+    r = Raytracer()
+    r.set_mesh(mesh)
+    assert r.PrepareMesh()
+    r.set_camera(cam)
+    imgs = (Image3b(), Image1f(), Image3f(), Image1b(), Image1i())
+    for tag, opt in cases.ALL_OPTIONS:
+        opt = RendererCpuOption(**{**opt.__dict__, "depth_scale": 0.5 * seed})
+        r.set_option(opt)
+        assert r.Render(*imgs)
+        got = {k: im.data for k, im in zip(cases.OUTPUT_KEYS, imgs)}
+        _assert_same(got, port_raytrace(port, cam.to_native(), _org(cam), opt), f"soup {seed} {tag}")
+    assert r.stats()["large_triangles"] > 0
 
 
 @pytest.mark.gpu
