@@ -298,3 +298,35 @@ def test_cuda_raytracer_device_form():
     assert np.array_equal(fid.cpu().numpy().reshape(want["face_id"].shape), want["face_id"])
     assert np.array_equal(dep.cpu().numpy().view(np.uint32).reshape(want["depth"].shape), want["depth"].view(np.uint32))
     assert np.array_equal(col.cpu().numpy().reshape(want["color"].shape), want["color"])
+
+
+@pytest.mark.gpu
+def test_multiview_renderer_with_the_raytracer_and_visibility_fold():
+    """The multi-view driver on ray-cast face_id maps (what the reference's own visibility pass uses: BVH
+    rays, include/ugu/texturing/visibility_tester.h): batch == per-view renders, and the per-face
+    visibility fold of those maps == a histogram of them."""
+    import torch
+    from oracle import face_visibility
+    from ugu_b200 import Image1i, Raytracer
+    from ugu_b200.multiview import MultiViewRenderer
+    mesh = meshgen.icosphere(5)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex)
+    r = Raytracer(opt)
+    r.set_mesh(mesh)
+    assert r.PrepareMesh()
+    cams = [PinholeCamera(128, 96, c2w, fov_y_deg=45.0) for c2w in meshgen.orbit_poses((0, 0, 0), 2.7, 6)]
+    mv = MultiViewRenderer(r)
+    idx, outs = mv.render(cams, ("face_id", "depth"))
+    torch.cuda.synchronize()
+    maps = outs["face_id"].cpu().numpy()
+    fid = Image1i()
+    for i, cam in zip(idx, cams):
+        r.set_camera(cam)
+        assert r.RenderFaceId(fid)
+        assert np.array_equal(maps[i], fid.data), i
+    F = len(mesh.vertex_indices)
+    vis = mv.render_face_visibility(cams, F)
+    torch.cuda.synchronize()
+    want = face_visibility(maps, F)
+    for k in ("pixel_count", "view_count", "best_view", "best_count"):
+        assert np.array_equal(vis[k].cpu().numpy(), want[k]), k

@@ -756,5 +756,20 @@ class Raytracer(Rasterizer):
         if rc != N.OK:
             raise RuntimeError(N.last_error(self._h))
 
-    def render_batch(self, *a, **k):
-        raise NotImplementedError("the Raytracer mode renders one view per call")
+    def render_batch(self, cameras: Sequence, color=None, depth=None, normal=None, mask=None,
+                     face_id=None, on_device: bool = False, stream: int = 0) -> None:
+        """len(cameras) views back to back on one stream; view i lands at element offset i*W*H of each
+        output (DEVICE pointers; the multi-view driver's path, ugu_b200.multiview.MultiViewRenderer — the
+        reference's own visibility pass casts BVH rays, include/ugu/texturing/visibility_tester.h)."""
+        if not on_device:
+            raise NotImplementedError("Raytracer.render_batch takes device outputs (use Render for host images)")
+        if not cameras:
+            return
+        P = cameras[0].width() * cameras[0].height()
+        for i, cam in enumerate(cameras):
+            self.render_device(cam,
+                               color=None if color is None else color + i * P * 3,
+                               depth=None if depth is None else depth + i * P * 4,
+                               normal=None if normal is None else normal + i * P * 12,
+                               mask=None if mask is None else mask + i * P,
+                               face_id=None if face_id is None else face_id + i * P * 4, stream=stream)
