@@ -2,7 +2,7 @@
 """Multi-view dispatch over the GPUs of one box (BASELINE.json configs 3 and 5).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port 29511 tools/multiview_bench.py [c5|c3] [--views V] [--gather] [--check K] [--visibility]
+        --master-port 29511 tools/multiview_bench.py [c5|c3] [--views V] [--gather] [--check K] [--visibility] [--raytrace]
 
 Every rank uploads the mesh to its own GPU (replicated, read-only), renders its contiguous slice of
 the view list with ONE device-resident batch call (no data-path collective), optionally gathers the
@@ -64,7 +64,12 @@ def main():
     W, H = cams[0].width(), cams[0].height()
     F = len(mesh.vertex_indices)
 
-    r = Rasterizer(opt, device=local)
+    if "--raytrace" in args:  # the Raytracer parity mode (ugu::Raytracer outputs) through the same driver
+        from ugu_b200 import Raytracer
+        r = Raytracer(opt, device=local)
+        desc += " [Raytracer mode]"
+    else:
+        r = Rasterizer(opt, device=local)
     r.set_mesh(mesh)
     assert r.PrepareMesh()
     stream = torch.cuda.Stream()
@@ -125,7 +130,8 @@ def main():
         ok = True
         for i in sel:
             one = torch.empty((H, W), dtype=torch.int32, device="cuda")
-            r.render_device(cams[int(i)].to_native(), stream=stream.cuda_stream, face_id=one.data_ptr())
+            r.render_device(cams[int(i)] if "--raytrace" in args else cams[int(i)].to_native(),
+                            stream=stream.cuda_stream, face_id=one.data_ptr())
             torch.cuda.synchronize()
             ok = ok and bool(torch.equal(one, gathered[int(i)]))
     if rank == 0:
