@@ -1174,11 +1174,8 @@ int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float
   int launches = 3;
   if (m.F > 0) {
     CU_TRY(r, LaunchView(rt_raster_kernel, Blocks((size_t)m.F, 256), 256, st, false, vp, m, fr, rp));
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)(g_num_sms * 2), kRtSlices);
-    cfg.blockDim = dim3(256);
-    cfg.stream = st;
-    CU_TRY(r, cudaLaunchKernelEx(&cfg, rt_large_kernel, vp, m, fr, rp));
+    // resident grid: 8 CTAs of 8 warps per SM share the global job space
+    CU_TRY(r, LaunchView(rt_large_kernel, (unsigned)(g_num_sms * 8), 256, st, false, vp, m, fr, rp));
     launches += 2;
   }
   CU_TRY(r, LaunchView(rt_resolve_kernel, Blocks(P, 256), 256, st, false, vp, m, fr, rp, sp));

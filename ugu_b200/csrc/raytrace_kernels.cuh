@@ -26,7 +26,7 @@
 namespace ugu_b200 {
 
 constexpr int kRtInLaneMax = 64;   // bbox samples up to which a face is traced by its own lane
-constexpr int kRtSlices = 8;       // CTAs that share one queued (large-bbox) face, by interleaved rows
+constexpr int kRtJob = 512;        // candidate pixels per job of a queued (large-bbox) face
 
 struct RtParams {
   float org[3];          // PinholeCamera::org_ray_w: c2w translation as float (camera.h:431-436)
@@ -174,7 +174,7 @@ __device__ __forceinline__ void rt_load_face(const MeshDev& m, const RtParams& r
 }
 
 // RT-K2: a warp per 32 faces.  Phase A (lane = face): gather, candidate bbox; faces whose bbox holds more
-// than kRtInLaneMax pixels are appended to the queue (one atomicAdd per warp) for RT-K3, the others are
+// than kRtInLaneMax pixels are appended to the job queue (one atomicAdd per warp) for RT-K3, the others are
 // compacted into a per-warp shared-memory table.  Phase B (lane = candidate pixel): the candidates of
 // all tabled faces form one index space [0, T) that the warp walks 32 at a time, so lanes stay busy
 // whatever the mix of bbox sizes (the owner of a candidate is found from a REDUX.OR bitmask of the
@@ -203,11 +203,26 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
   const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
   const bool large = kind != 0 && (long long)nx * ny > kRtInLaneMax;
   const unsigned lb = __ballot_sync(0xffffffffu, large);
-  if (lb) {
-    unsigned long long base = 0ull;
-    if (lane == 0u) base = atomicAdd(fr.counters, (unsigned long long)__popc(lb));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (large) fr.q_face[base + __popc(lb & lt_mask)] = f;
+  if (lb) {  // queue: packed (entries, jobs) counter as in raster_kernel — one atomicAdd per warp hands every
+             // queued face its entry slot and its first job in the global job space
+    const unsigned long long njobs = large ? ((unsigned long long)nx * (unsigned long long)ny + kRtJob - 1) / kRtJob : 0ull;
+    const unsigned long long mine = large ? ((1ull << kQueueJobBits) | njobs) : 0ull;
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= (unsigned)d) incl += o;
+    }
+    const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
+    unsigned long long qbase = 0ull;
+    if (lane == 31u) qbase = atomicAdd(fr.counters, total);
+    qbase = __shfl_sync(0xffffffffu, qbase, 31);
+    if (large) {
+      const unsigned long long excl = qbase + incl - mine;
+      const unsigned qslot = (unsigned)(excl >> kQueueJobBits);
+      fr.q_face[qslot] = f;
+      fr.q_job[qslot] = excl & kQueueJobMask;
+    }
   }
   const int cnt = (kind != 0 && !large) ? nx * ny : 0;
   const unsigned rec = __ballot_sync(0xffffffffu, cnt > 0);
@@ -253,24 +268,50 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
   }
 }
 
-// RT-K3: queued faces.  CTA (q, s) takes queue entries q, q + gridDim.x, ... and of each entry's bbox the
-// rows y0 + s, y0 + s + kRtSlices, ...; its threads stride over the pixels of those rows.
+// RT-K3: queued faces.  Their candidate pixels are cut into jobs of kRtJob pixels that form one global job
+// space [0, T) (the queue orders entries by first job), so the work is balanced whatever the mix of bbox
+// sizes: every warp of a resident grid takes a contiguous range of jobs, finds the entry that owns its first
+// job with one binary search and walks forward from there; lanes stride over a job's pixels.
 __global__ void __launch_bounds__(256) rt_large_kernel(const ViewParams vp, const MeshDev m, const FrameDev fr,
                                                        const RtParams rp) {
-  const unsigned n = (unsigned)fr.counters[0];
-  for (unsigned q = blockIdx.x; q < n; q += gridDim.x) {
-    const int f = fr.q_face[q];
+  const unsigned long long packed = fr.counters[0];
+  const unsigned long long T = packed & kQueueJobMask;
+  const unsigned n = (unsigned)(packed >> kQueueJobBits);
+  if (T == 0ull) return;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
+  const unsigned long long gw = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const unsigned long long per = (T + nwarps - 1) / nwarps;
+  unsigned long long j = gw * per;
+  const unsigned long long jend = (j + per < T) ? j + per : T;
+  if (j >= jend) return;
+  unsigned lo = 0u, hi = n;  // last entry e with q_job[e] <= j
+  while (hi - lo > 1u) {
+    const unsigned mid = (lo + hi) >> 1;
+    if (fr.q_job[mid] <= j) lo = mid; else hi = mid;
+  }
+  unsigned e = lo;
+  while (j < jend) {
+    const unsigned long long first = fr.q_job[e];
+    const unsigned long long next = (e + 1u < n) ? fr.q_job[e + 1u] : T;  // jobs of entry e: [first, next)
+    const int f = fr.q_face[e];
     int i0, i1, i2, x0, y0, x1, y1;
     float A[3], B[3], C[3];
     rt_load_face(m, rp, f, i0, i1, i2, A, B, C);
-    if (rt_bounds(vp, rp, fr.proj[i0], fr.proj[i1], fr.proj[i2], x0, y0, x1, y1) == 0) continue;
+    const int kind = rt_bounds(vp, rp, fr.proj[i0], fr.proj[i1], fr.proj[i2], x0, y0, x1, y1);
     const unsigned nx = (unsigned)(x1 - x0 + 1);
-    const unsigned rows = ((unsigned)(y1 - y0) >= blockIdx.y) ? ((unsigned)(y1 - y0) - blockIdx.y) / kRtSlices + 1u : 0u;
-    for (unsigned k = threadIdx.x; k < rows * nx; k += blockDim.x) {
-      const unsigned r = k / nx, dx = k - r * nx;
-      const unsigned y = (unsigned)y0 + blockIdx.y + r * kRtSlices;
-      rt_sample(rp, fr, y * (unsigned)vp.W + (unsigned)x0 + dx, f, A, B, C);
+    const unsigned long long ns = kind ? (unsigned long long)nx * (unsigned long long)(y1 - y0 + 1) : 0ull;
+    const unsigned long long jstop = next < jend ? next : jend;
+    for (; j < jstop; j++) {
+      // ns <= W*H < 2^31 (validated by the host): 32-bit pixel arithmetic
+      const unsigned k0 = (unsigned)(j - first) * (unsigned)kRtJob;
+      const unsigned k1 = min(k0 + (unsigned)kRtJob, (unsigned)ns);
+      for (unsigned k = k0 + lane; k < k1; k += 32u) {
+        const unsigned r = k / nx, dx = k - r * nx;
+        rt_sample(rp, fr, ((unsigned)y0 + r) * (unsigned)vp.W + (unsigned)x0 + dx, f, A, B, C);
+      }
     }
+    e++;
   }
 }
 
@@ -345,7 +386,7 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
   const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0u) {
-    fr.counters[4] = fr.counters[0] << kQueueJobBits;  // host snapshot: queued faces, no tile jobs
+    fr.counters[4] = fr.counters[0];  // host snapshot: packed (queued faces, jobs)
     fr.counters[5] = 0ull;
     fr.counters[0] = 0ull;
   }
