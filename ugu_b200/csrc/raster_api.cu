@@ -1149,6 +1149,9 @@ int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float
   rp.t_max = 1.0e+30f;
   rp.depth_scale = r->opt.depth_scale;
   rp.coord_scale = fmaxf(r->mesh_max_abs, fmaxf(fabsf(org_w[0]), fmaxf(fabsf(org_w[1]), fabsf(org_w[2]))));
+  // like coop_max of the rasterizer: with fewer face warps than the machine holds, mid-size bboxes are better
+  // spread over the whole GPU by the job queue than walked by their own warp
+  rp.inlane_max = (r->mesh.F >= 4 * 32 * 32 * g_num_sms) ? kRtInLaneMax : 16;
   rp.ray_a = (float4*)r->rt_rays.p;
   rp.ray_b = rp.ray_a + P;
   ShadeParams sp;

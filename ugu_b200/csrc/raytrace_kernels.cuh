@@ -33,6 +33,7 @@ struct RtParams {
   float t_min, t_max;    // bvh_nanort.h:119-121: 1e-4, 1e30
   float depth_scale;     // RendererCpuOption::depth_scale (raytracer.cc:171)
   float coord_scale;     // max |world coordinate| of the mesh and the ray origin (error bound of the bbox)
+  int inlane_max;        // candidate-bbox size up to which RT-K2 traces a face itself (<= kRtInLaneMax)
   float4* ray_a;         // per pixel: dir.x dir.y dir.z Sz
   float4* ray_b;         // per pixel: Sx Sy (kx | ky << 2 | kz << 4) -
 };
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
     kind = rt_bounds(vp, rp, fr.proj[i0], fr.proj[i1], fr.proj[i2], x0, y0, x1, y1);
   }
   const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
-  const bool large = kind != 0 && (long long)nx * ny > kRtInLaneMax;
+  const bool large = kind != 0 && (long long)nx * ny > (long long)rp.inlane_max;
   const unsigned lb = __ballot_sync(0xffffffffu, large);
   if (lb) {  // queue: packed (entries, jobs) counter as in raster_kernel — one atomicAdd per warp hands every
              // queued face its entry slot and its first job in the global job space
@@ -285,10 +286,16 @@ __global__ void __launch_bounds__(256) rt_large_kernel(const ViewParams vp, cons
   unsigned long long j = gw * per;
   const unsigned long long jend = (j + per < T) ? j + per : T;
   if (j >= jend) return;
-  unsigned lo = 0u, hi = n;  // last entry e with q_job[e] <= j
+  // last entry e with q_job[e] <= j: warp-cooperative 32-ary search (q_job is ascending, q_job[0] == 0) —
+  // log32(n) dependent loads instead of log2(n)
+  unsigned lo = 0u, hi = n;
   while (hi - lo > 1u) {
-    const unsigned mid = (lo + hi) >> 1;
-    if (fr.q_job[mid] <= j) lo = mid; else hi = mid;
+    const unsigned step = (hi - lo + 31u) / 32u;
+    const unsigned idx = lo + (lane + 1u) * step;
+    const bool le = idx < hi && fr.q_job[idx] <= j;
+    const unsigned c = (unsigned)__popc(__ballot_sync(0xffffffffu, le));  // the pivots <= j are a prefix
+    lo += c * step;
+    hi = min(hi, lo + step);
   }
   unsigned e = lo;
   while (j < jend) {
