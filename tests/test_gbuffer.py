@@ -203,17 +203,22 @@ def test_cuda_gbuffer_full_size_config2_properties_and_errors():
 def test_cuda_gbuffer_device_form_chains_on_a_stream():
     import torch
     mesh, cam, opt = _spot_case(w=256, h=192)
-    kw = dict(z_near=0.01, z_far=100.0)
+    kw = dict(z_near=0.01, z_far=100.0, geo_id=3)
     want = _oracle(mesh, cam, opt, kw)
     from ugu_b200 import Rasterizer
     r = Rasterizer(opt)
     r.set_mesh(mesh)
     assert r.PrepareMesh()
     P = cam.width() * cam.height()
-    bufs = {n: torch.empty(P * ch * np.dtype(dt).itemsize, dtype=torch.uint8, device="cuda")
+    # pre-filled, so that a field the call skipped cannot pass by landing on fresh zeroed memory
+    bufs = {n: torch.full((P * ch * np.dtype(dt).itemsize,), 0xA5, dtype=torch.uint8, device="cuda")
             for n, dt, ch in GBUFFER_FIELDS}
     st = torch.cuda.Stream()
-    r.render_gbuffer_device(cam, 0.01, 100.0, stream=st.cuda_stream, **{n: b.data_ptr() for n, b in bufs.items()})
+    st.wait_stream(torch.cuda.current_stream())
+    r.render_gbuffer_device(cam, 0.01, 100.0, geo_id_value=3, stream=st.cuda_stream,
+                            **{n: b.data_ptr() for n, b in bufs.items()})
+    with pytest.raises(TypeError):
+        r.render_gbuffer_device(cam, 0.01, 100.0, shaded=bufs["color"].data_ptr())
     st.synchronize()
     for n, dt, ch in GBUFFER_FIELDS:
         got = bufs[n].cpu().numpy().view(dt).reshape(want[n].shape)

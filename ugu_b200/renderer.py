@@ -661,13 +661,17 @@ class Rasterizer:
         return True
 
     def render_gbuffer_device(self, camera: PinholeCamera, z_near: float, z_far: float, flat_normal: bool = False,
-                              geo_id: int = 0, stream: int = 0, **fields: int) -> None:
-        """Device form: `fields` are raw 16-byte aligned DEVICE pointers by GBuffer field name."""
+                              geo_id_value: int = 0, stream: int = 0, **fields: int) -> None:
+        """Device form: `fields` are raw 16-byte aligned DEVICE pointers by GBuffer field name (`geo_id`
+        is the geo_id IMAGE; the id written into it is `geo_id_value`)."""
+        unknown = set(fields) - set(GBuffer.TYPES)
+        if unknown:
+            raise TypeError(f"unknown G-buffer field(s): {sorted(unknown)}")
         opt = self._native_option()
         self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
         cam = camera.to_native() if isinstance(camera, PinholeCamera) else camera
         out = N.GBuffer(**fields)
-        go = N.GBufferOption(float(z_near), float(z_far), 1 if flat_normal else 0, int(geo_id))
+        go = N.GBufferOption(float(z_near), float(z_far), 1 if flat_normal else 0, int(geo_id_value))
         rc = self._lib.ugu_b200_rasterizer_render_gbuffer_device(self._h, C.byref(cam), C.byref(go), C.byref(out),
                                                                  C.c_void_p(stream))
         if rc != N.OK:
