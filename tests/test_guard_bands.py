@@ -181,3 +181,28 @@ def test_depth_consumers_stay_inside_their_outputs(size):
     hist = np.bincount(fid[fid >= 0], minlength=F).astype(np.int32)
     assert np.array_equal(got["pix"].view(np.int32), hist)
     assert np.array_equal(got["views"].view(np.int32), (hist > 0).astype(np.int32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("size", [(37, 29), (33, 1), (1, 1), (255, 3), (130, 67)], ids=lambda s: f"{s[0]}x{s[1]}")
+def test_uv_raster_device_stays_inside_its_texture(size):
+    """UV-space attribute raster, device form, at texture sizes that are not multiples of anything."""
+    import torch
+    import uvcases
+    from oracle import port_uv_raster
+    from ugu_b200 import Rasterizer, _native as N
+    w, h = size
+    c = uvcases.spot_case("vertex_u8_256")
+    want = port_uv_raster(c["attrs"], c["attr_indices"], c["uv"], c["uv_indices"], w, h, 0, None,
+                          np.zeros((h, w), np.uint8))
+    dev = {k: torch.from_numpy(np.ascontiguousarray(c[k])).cuda() for k in ("attrs", "attr_indices", "uv", "uv_indices")}
+    arena = Arena(dict(texture=w * h * 3, mask=w * h))
+    r = Rasterizer()
+    d = N.UvRasterDesc(len(c["attrs"]), len(c["uv_indices"]), len(c["uv"]), 0, dev["attrs"].data_ptr(),
+                       dev["attr_indices"].data_ptr(), dev["uv"].data_ptr(), dev["uv_indices"].data_ptr(),
+                       w, h, 0, 0, 0, 0)
+    r.uv_raster_device(d, arena.ptr("texture"), arena.ptr("mask"), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    got = arena.check()
+    assert np.array_equal(got["texture"], np.ascontiguousarray(want[0]).reshape(-1).view(np.uint8))
+    assert np.array_equal(got["mask"], np.ascontiguousarray(want[1]).reshape(-1).view(np.uint8))
