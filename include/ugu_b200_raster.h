@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 7
+#define UGU_B200_ABI_VERSION 8
 
 enum {
   UGU_B200_OK = 0,
@@ -248,6 +248,140 @@ int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host
                              int64_t pixels_per_view, int32_t first_view_id, int32_t num_faces,
                              uint32_t* pixel_count_host, uint32_t* view_count_host,
                              int32_t* best_view_host, uint32_t* best_count_host);
+
+/* Keyframe visibility pass: replaces ugu::VisibilityTester
+ * (include/ugu/texturing/visibility_tester.h:216-265; src/texturing/visibility_tester.cc:416-529 TestVertex,
+ * :531-549 TestVertices, :551-604 TestFaces, :606-668 TestFacewiseVertices, :670-733 Test) and the folds of
+ * ugu::VisibilityInfo (FaceInfo::CalcStat :185-218; the min / mean part of VertexInfo::CalcStat :66-152).
+ * Per keyframe (a pinhole camera + colour / depth / mask images) every mesh vertex is projected, bounds-,
+ * mask- and depth-checked at its nearest pixel, back-face tested with its vertex normal against the ray through
+ * its sub-pixel projection, occlusion-tested, and sampled for colour (NN or the reference's bilinear) and
+ * intensity; a face is visible when its three vertices are, with the mean viewing angle / distance and the
+ * projected area of FaceInfoPerKeyframe.  `facewise` selects TestFacewiseVertices (the reference's default:
+ * each corner pulled 1e-3 of the way to the face centre; a vertex keeps the record of the first passing (face,
+ * corner) in face order — the reference's sequential order, its OpenMP form is racy).
+ * ONE substitution: the reference asks a BVH for the nearest hit of the vertex ray (:457-483); this library reads
+ * `zbuf`, the depth map of the mesh itself from the keyframe camera as ITS rasterizer renders it with back-face
+ * culling off, at the nearest pixel: with t_v = |camera_p| and t_s = zbuf(nn) * (t_v / camera_p.z), the vertex
+ * is occluded iff zbuf(nn) >= FLT_MIN and t_v - t_s > eps; `distance` = t_v (reference: the hit's t, which is
+ * smaller when a nearer surface lies within eps); the depth check uses camera_p.z.  On the (vertex, keyframe)
+ * pairs both methods call visible, projected_pos, colour, intensity and area are bit-identical to the compiled
+ * reference, viewing_angle to a few ulp (device acosf), distance to float tolerance; the decisions differ on
+ * < 1 % of the pairs (sub-pixel rays vs nearest-pixel depth at silhouettes; tests/test_visibility_tester.py
+ * states the set).  Field names and defaults: ugu::VisibilityTesterOption (visibility_tester.h:39-58) — note
+ * that the reference's CopyTo (:43-53) copies only the first seven fields, so through its public API
+ * max_viewing_angle / max_distance / max_depth_difference / eps always keep their defaults. */
+typedef struct ugu_b200_vis_option {
+  float backface_culling_angle_rad_th;        /* default radians(90) */
+  int32_t use_mask, use_depth;                /* default 1, 1 */
+  int32_t interp;                             /* UGU_B200_INTERP_*, default bilinear */
+  float max_viewing_angle;                    /* default radians(90) */
+  float max_distance_from_camera_to_vertex;   /* default FLT_MAX */
+  float max_depth_difference;                 /* default FLT_MAX */
+  float eps;                                  /* default 0.1 */
+  int32_t facewise;                           /* Test(..., facewise): default 1 */
+  int32_t self_occlusion;                     /* 1: use the keyframe's zbuf, or render it from the uploaded
+                                                 rasterizer mesh when the pointer is NULL; 0: no occlusion test */
+} ugu_b200_vis_option;
+typedef struct ugu_b200_vis_vertex {          /* ugu::VertexInfoPerKeyframe (visibility_tester.h:60-72) */
+  float color[3];
+  float intensity;
+  float projected_pos[2];
+  float viewing_angle;
+  float distance;
+} ugu_b200_vis_vertex;
+typedef struct ugu_b200_vis_face {            /* ugu::FaceInfoPerKeyframe (visibility_tester.h:130-144) */
+  float area, viewing_angle, distance;
+  float projected_tri[6];
+} ugu_b200_vis_face;
+/* ugu::Keyframe (visibility_tester.h:201-214) + the float constants the tester reads from its camera:
+ * cam.{width,height,fx,fy,cx,cy,c2w_R}, w2c = camera->w2c().cast<float>() (row-major 3x4), c2w_t = c2w_t_f_.
+ * cam.w2c_R / cam.w2c_t are used only when the library renders zbuf itself.  Images: colour W*H*3 u8, depth W*H
+ * f32 (may be NULL when !use_depth), mask W*H u8 (NULL when !use_mask), zbuf W*H f32 (see self_occlusion). */
+typedef struct ugu_b200_keyframe {
+  int32_t id;
+  int32_t reserved;
+  ugu_b200_camera cam;
+  float w2c[12];
+  float c2w_t[3];
+  float reserved2;
+  const uint8_t* color;
+  const float* depth;
+  const uint8_t* mask;
+  const float* zbuf;
+} ugu_b200_keyframe;
+/* Dense per-keyframe records: row k (keyframe k of the call) holds num_vertices / num_faces entries; entries of
+ * invisible elements are zero.  Any pointer may be NULL. */
+typedef struct ugu_b200_vis_records {
+  uint8_t* vertex_visible;           /* K * V */
+  ugu_b200_vis_vertex* vertex;       /* K * V, 16-byte aligned */
+  uint8_t* face_visible;             /* K * F */
+  ugu_b200_vis_face* face;           /* K * F */
+} ugu_b200_vis_records;
+/* VisibilityInfo after CalcStatFaceInfo / CalcStatVertexInfo, restricted to what the device folds: per face the
+ * number of keyframes that see it and the FIRST keyframe (in call order, `order` = first_order + position) with
+ * the largest area / smallest viewing angle / smallest distance — FaceInfo::max_area_id, min_viewing_angle_id,
+ * min_distance_id are keyframes[order].id; per vertex the count, VertexInfo::mean_color / mean_viewing_angle /
+ * mean_distance, min_viewing_angle_id / _color, min_distance_id / _color.  -1 / 0 where never visible.  Medians,
+ * weighted medians and modes need the per-keyframe lists: take them from the dense records.  HOST arrays, any NULL. */
+typedef struct ugu_b200_vis_stats {
+  uint32_t* face_count;
+  int32_t* face_max_area_order;
+  int32_t* face_min_viewing_angle_order;
+  int32_t* face_min_distance_order;
+  float* face_max_area;
+  float* face_min_viewing_angle;
+  float* face_min_distance;
+  uint32_t* vertex_count;
+  int32_t* vertex_min_viewing_angle_order;
+  int32_t* vertex_min_distance_order;
+  float* vertex_mean_color;               /* V * 3 */
+  float* vertex_mean_viewing_angle;
+  float* vertex_mean_distance;
+  float* vertex_min_viewing_angle_color;  /* V * 3 */
+  float* vertex_min_distance_color;       /* V * 3 */
+} ugu_b200_vis_stats;
+/* Raw DEVICE accumulators (for multi-GPU jobs: ranks fold disjoint keyframes and combine with
+ * SUM / MAX / MIN / MIN, SUM / SUM / SUM / MIN / MIN; see ugu_b200/csrc/visibility_tester_kernels.cuh). */
+typedef struct ugu_b200_vis_accumulators {
+  uint32_t* face_count;        /* F, SUM */
+  uint64_t* face_max_area;     /* F, MAX: area bits << 32 | (0xFFFFFFFF - order); 0 = never */
+  uint64_t* face_min_angle;    /* F, MIN: angle bits << 32 | order; ~0 = never */
+  uint64_t* face_min_dist;     /* F, MIN */
+  uint32_t* vertex_count;      /* V, SUM */
+  float* vertex_sum_color;     /* V * 4 (r g b -), SUM */
+  float* vertex_sum_angle_dist;/* V * 2, SUM */
+  uint64_t* vertex_min_angle;  /* V, MIN */
+  uint64_t* vertex_min_dist;   /* V, MIN */
+  uint32_t* vertex_min_colors; /* V * 2: packed r | g << 8 | b << 16 of the min_angle / min_dist winner */
+} ugu_b200_vis_accumulators;
+
+/* VisibilityTester::set_data + PrepareData (visibility_tester.cc:236-270): uploads vertices (V*3), per-vertex
+ * normals (V*3) and indices (F*3) and clears the accumulators.  E_INVALID for an empty mesh (PrepareData's false). */
+int ugu_b200_visibility_set_data(ugu_b200_rasterizer* r, int32_t num_vertices, const float* vertices,
+                                 const float* normals, int32_t num_faces, const int32_t* indices);
+/* A fresh VisibilityInfo: clears the accumulators. */
+int ugu_b200_visibility_reset(ugu_b200_rasterizer* r);
+/* VisibilityTester::Test over `num_keyframes` keyframes with HOST images (uploads them, runs, copies the
+ * requested dense records to HOST arrays, returns when complete) and folds them into the accumulators with
+ * orders first_order .. first_order + num_keyframes - 1.  E_INVALID where the reference returns false (colour
+ * empty, use_mask / use_depth without the image, no data set). */
+int ugu_b200_visibility_test(ugu_b200_rasterizer* r, int32_t num_keyframes, const ugu_b200_keyframe* keyframes,
+                             int32_t first_order, const ugu_b200_vis_option* opt,
+                             const ugu_b200_vis_records* host_records);
+/* Same with DEVICE images and DEVICE record arrays (e.g. the colour / depth / mask outputs of render_batch),
+ * asynchronous on `stream`. */
+int ugu_b200_visibility_test_device(ugu_b200_rasterizer* r, int32_t num_keyframes,
+                                    const ugu_b200_keyframe* keyframes, int32_t first_order,
+                                    const ugu_b200_vis_option* opt, const ugu_b200_vis_records* dev_records,
+                                    void* stream);
+/* Finalises the accumulators (means = sums / count in float) into HOST arrays; waits for pending work. */
+int ugu_b200_visibility_stats(ugu_b200_rasterizer* r, const ugu_b200_vis_stats* host_out);
+int ugu_b200_visibility_accumulators(ugu_b200_rasterizer* r, ugu_b200_vis_accumulators* out);
+/* The float constants of a keyframe camera from a row-major 4x4 double c2w, as PinholeCamera::set_c2w derives
+ * them (camera.h:317-331): fills kf->cam (like ugu_b200_camera_from_c2w), kf->w2c and kf->c2w_t.  Host only. */
+int ugu_b200_keyframe_camera_from_c2w(const double* c2w16, int32_t width, int32_t height, float fx, float fy,
+                                      float cx, float cy, ugu_b200_keyframe* kf);
 
 /* ugu::Depth2Mesh (include/ugu/util/rgbd_util.h:27-37; Depth2MeshImpl, src/util/rgbd_util.cc:94-282,
  * 528-545; Mesh::CalcNormal, src/mesh.cc:297-349) — the step examples/ex02_renderer.cc:156-158 runs on

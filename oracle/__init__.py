@@ -515,3 +515,163 @@ class OracleRef:
         self.lib.ugu_ref_mesh_free(h)
         a["num_materials"] = M
         return a
+
+
+# ---- ugu::VisibilityTester through oracle/_ref (reference-pinned side of the visibility consumer) -------------
+class _RefKeyframe(C.Structure):
+    _fields_ = [("id", C.c_int32), ("pad_", C.c_int32), ("cam", _RefCamera), ("color", C.c_void_p),
+                ("depth", C.c_void_p), ("mask", C.c_void_p)]
+
+
+class _RefVisOption(C.Structure):
+    _fields_ = [("backface_culling_angle_rad_th", C.c_float), ("use_mask", C.c_int32), ("use_depth", C.c_int32),
+                ("interp", C.c_int32), ("facewise", C.c_int32), ("num_threads", C.c_int32)]
+
+
+def _ref_camera(camera) -> "_RefCamera":
+    cam = _RefCamera()
+    cam.width, cam.height = camera.width(), camera.height()
+    cam.fx, cam.fy = float(camera.focal_length()[0]), float(camera.focal_length()[1])
+    cam.cx, cam.cy = float(camera.principal_point()[0]), float(camera.principal_point()[1])
+    cam.c2w = (C.c_double * 16)(*np.asarray(camera.c2w(), np.float64).reshape(-1))
+    return cam
+
+
+VERTEX_STAT_COLORS = ("mean", "median", "min_viewing_angle", "mean_viewing_angle", "median_viewing_angle",
+                      "min_distance", "mean_distance", "median_distance", "median_intensity", "min_intensity")
+VERTEX_STAT_SCALARS = ("mean_viewing_angle", "median_viewing_angle", "mean_distance", "median_distance",
+                       "min_intensity", "median_intensity", "num_visible")
+
+
+def ref_visibility(vertices, normals, indices, keyframes, backface_culling_angle_rad_th=np.pi / 2, use_mask=True,
+                   use_depth=True, interp=1, facewise=True, num_threads=1):
+    """The compiled reference's ugu::VisibilityTester::Test(keyframes, info, facewise)
+    (src/texturing/visibility_tester.cc:657-733) on `keyframes` = [(id, camera, color, depth, mask)] (host
+    images; depth / mask may be None).  Returns dense per-(keyframe, vertex) and per-(keyframe, face) records
+    plus the CalcStat results, or None when the reference returns false."""
+    lib = C.CDLL(str(REF_LIB))
+    lib.ugu_ref_visibility_run.restype = C.c_void_p
+    lib.ugu_ref_visibility_run.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32,
+                                           C.POINTER(_RefKeyframe), C.POINTER(_RefVisOption)]
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+    n = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+    f = np.ascontiguousarray(indices, np.int32).reshape(-1, 3)
+    V, F, K = len(v), len(f), len(keyframes)
+    keep = []
+    kfs = (_RefKeyframe * K)()
+    for k, (kid, cam, color, depth, mask) in enumerate(keyframes):
+        kfs[k].id = int(kid)
+        kfs[k].cam = _ref_camera(cam)
+        c = np.ascontiguousarray(color, np.uint8)
+        d = None if depth is None else np.ascontiguousarray(depth, np.float32)
+        m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+        keep += [c, d, m]
+        kfs[k].color = c.ctypes.data
+        kfs[k].depth = None if d is None else d.ctypes.data
+        kfs[k].mask = None if m is None else m.ctypes.data
+    opt = _RefVisOption(float(backface_culling_angle_rad_th), int(bool(use_mask)), int(bool(use_depth)), int(interp),
+                        int(bool(facewise)), int(num_threads))
+    h = lib.ugu_ref_visibility_run(V, v.ctypes.data, n.ctypes.data, F, f.ctypes.data, K, kfs, C.byref(opt))
+    if not h:
+        return None
+    h = C.c_void_p(h)
+    out = dict(
+        v_visible=np.zeros((K, V), np.uint8), v_color=np.zeros((K, V, 3), np.float32),
+        v_intensity=np.zeros((K, V), np.float32), v_projected=np.zeros((K, V, 2), np.float32),
+        v_viewing_angle=np.zeros((K, V), np.float32), v_distance=np.zeros((K, V), np.float32),
+        f_visible=np.zeros((K, F), np.uint8), f_area=np.zeros((K, F), np.float32),
+        f_viewing_angle=np.zeros((K, F), np.float32), f_distance=np.zeros((K, F), np.float32),
+        f_projected_tri=np.zeros((K, F, 6), np.float32),
+        face_ids=np.zeros((F, 3), np.int32), vertex_ids=np.zeros((V, 2), np.int32),
+        vertex_scalars=np.zeros((V, 7), np.float32), vertex_colors=np.zeros((V, 10, 3), np.float32))
+    p = lambda name: out[name].ctypes.data_as(C.c_void_p)
+    lib.ugu_ref_visibility_vertex_records.argtypes = [C.c_void_p] * 7
+    lib.ugu_ref_visibility_vertex_records(h, p("v_visible"), p("v_color"), p("v_intensity"), p("v_projected"),
+                                          p("v_viewing_angle"), p("v_distance"))
+    lib.ugu_ref_visibility_face_records.argtypes = [C.c_void_p] * 6
+    lib.ugu_ref_visibility_face_records(h, p("f_visible"), p("f_area"), p("f_viewing_angle"), p("f_distance"),
+                                        p("f_projected_tri"))
+    lib.ugu_ref_visibility_stats.argtypes = [C.c_void_p] * 5
+    lib.ugu_ref_visibility_stats(h, p("face_ids"), p("vertex_ids"), p("vertex_scalars"), p("vertex_colors"))
+    lib.ugu_ref_visibility_free.argtypes = [C.c_void_p]
+    lib.ugu_ref_visibility_free(h)
+    return out
+
+
+def ref_visibility_camera_constants(camera):
+    """(w2c 3x4 float, c2w_R 3x3 float, c2w_t 3 float) exactly as the tester reads them from ugu::PinholeCamera."""
+    lib = C.CDLL(str(REF_LIB))
+    lib.ugu_ref_visibility_camera_constants.argtypes = [C.POINTER(_RefCamera), C.c_void_p, C.c_void_p, C.c_void_p]
+    w2c, R, t = np.zeros((3, 4), np.float32), np.zeros((3, 3), np.float32), np.zeros(3, np.float32)
+    cam = _ref_camera(camera)
+    lib.ugu_ref_visibility_camera_constants(C.byref(cam), w2c.ctypes.data, R.ctypes.data, t.ctypes.data)
+    return w2c, R, t
+
+
+class _VisCamera(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("w2c", C.c_float * 12), ("c2w_R", C.c_float * 9),
+                ("c2w_t", C.c_float * 3)]
+
+
+class _VisOption(C.Structure):
+    _fields_ = [("backface_culling_angle_rad_th", C.c_float), ("use_mask", C.c_int32), ("use_depth", C.c_int32),
+                ("interp", C.c_int32), ("max_viewing_angle", C.c_float),
+                ("max_distance_from_camera_to_vertex", C.c_float), ("max_depth_difference", C.c_float),
+                ("eps", C.c_float), ("facewise", C.c_int32), ("reserved", C.c_int32)]
+
+
+VIS_VERTEX_DTYPE = np.dtype([("color", np.float32, 3), ("intensity", np.float32), ("projected", np.float32, 2),
+                             ("viewing_angle", np.float32), ("distance", np.float32)])
+
+
+def vis_option(backface_culling_angle_rad_th=None, use_mask=True, use_depth=True, interp=1, facewise=True,
+               max_viewing_angle=None, max_distance=None, max_depth_difference=None, eps=0.1):
+    """Defaults of ugu::VisibilityTesterOption (visibility_tester.h:39-58)."""
+    half_pi = float(np.float32(90.0) * np.float32(np.pi / 180.0))  # ugu::radians(90.0f)
+    fmax = float(np.finfo(np.float32).max)
+    return _VisOption(half_pi if backface_culling_angle_rad_th is None else float(backface_culling_angle_rad_th),
+                      int(bool(use_mask)), int(bool(use_depth)), int(interp),
+                      half_pi if max_viewing_angle is None else float(max_viewing_angle),
+                      fmax if max_distance is None else float(max_distance),
+                      fmax if max_depth_difference is None else float(max_depth_difference), float(eps),
+                      int(bool(facewise)), 0)
+
+
+def vis_camera(cam_consts, width, height, fx, fy, cx, cy):
+    """cam_consts = (w2c 3x4, c2w_R 3x3, c2w_t 3) float32."""
+    w2c, R, t = cam_consts
+    return _VisCamera(int(width), int(height), float(fx), float(fy), float(cx), float(cy),
+                      (C.c_float * 12)(*np.asarray(w2c, np.float32).reshape(-1)),
+                      (C.c_float * 9)(*np.asarray(R, np.float32).reshape(-1)),
+                      (C.c_float * 3)(*np.asarray(t, np.float32).reshape(-1)))
+
+
+def port_visibility_keyframe(vertices, normals, indices, cam: "_VisCamera", opt: "_VisOption", color, depth, mask,
+                             zbuf):
+    """oracle_visibility_keyframe (oracle/raster_oracle.c): one keyframe of the visibility pass with the
+    z-buffer in place of the BVH query.  Returns dict(v_visible, v_rec (structured), f_visible, f_area,
+    f_viewing_angle, f_distance, f_projected_tri)."""
+    build_port()
+    lib = C.CDLL(str(PORT_LIB))
+    fn = lib.oracle_visibility_keyframe
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.POINTER(_VisCamera),
+                   C.POINTER(_VisOption)] + [C.c_void_p] * 11
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+    n = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+    f = np.ascontiguousarray(indices, np.int32).reshape(-1, 3)
+    V, F = len(v), len(f)
+    c = np.ascontiguousarray(color, np.uint8)
+    d = None if depth is None else np.ascontiguousarray(depth, np.float32)
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+    z = None if zbuf is None else np.ascontiguousarray(zbuf, np.float32)
+    out = dict(v_visible=np.zeros(V, np.uint8), v_rec=np.zeros(V, VIS_VERTEX_DTYPE),
+               f_visible=np.zeros(F, np.uint8), f_area=np.zeros(F, np.float32),
+               f_viewing_angle=np.zeros(F, np.float32), f_distance=np.zeros(F, np.float32),
+               f_projected_tri=np.zeros((F, 6), np.float32))
+    q = lambda a: None if a is None else a.ctypes.data
+    rc = fn(V, v.ctypes.data, n.ctypes.data, F, f.ctypes.data, C.byref(cam), C.byref(opt), q(c), q(d), q(m), q(z),
+            q(out["v_visible"]), q(out["v_rec"]), q(out["f_visible"]), q(out["f_area"]),
+            q(out["f_viewing_angle"]), q(out["f_distance"]), q(out["f_projected_tri"]))
+    return out if rc == 0 else None

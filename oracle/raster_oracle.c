@@ -997,4 +997,185 @@ int oracle_raytrace(const OracleMesh* mesh, const OracleCamera* cam, const float
   return 0;
 }
 
-int oracle_abi_version(void) { return 6; }
+
+/* ================================================================================================
+ * Visibility pass: ugu::VisibilityTester's per-keyframe vertex / face tests
+ * (src/texturing/visibility_tester.cc:416-529 TestVertex, 531-549 TestVertices, 551-604 TestFaces,
+ * 606-668 TestFacewiseVertices) and the folds of FaceInfo::CalcStat (:185-218) / VertexInfo::CalcStat
+ * (:66-152, the min / mean subset), restated with ONE substitution: the reference asks a BVH for the
+ * nearest hit of the ray through the vertex's sub-pixel projection (:457-483); this restatement — like the
+ * CUDA consumer it checks — reads `zbuf`, the mesh's own depth map rendered from the keyframe camera by
+ * the rasterizer (back-face culling off), at the nearest pixel:
+ *     t_v = |camera_p|                      distance of the (offset) vertex along its own ray
+ *     t_s = zbuf(nn) * (t_v / camera_p.z)   distance of the surface seen at that pixel along that ray
+ *     occluded  iff  zbuf(nn) >= FLT_MIN  and  t_v - t_s > eps        (reference: |hit - vertex| > eps)
+ *     distance  =  t_v                                               (reference: the BVH hit's t)
+ *     depth check uses camera_p.z                                     (reference: the hit's camera z)
+ * Everything else follows the reference expression by expression.  Parity status: PINNED on the pairs
+ * both methods call visible — tests/test_visibility_tester.py compares with fixtures generated by the
+ * compiled reference tester (projected_pos, viewing_angle, colour, intensity, area bit-exact; distance to
+ * float tolerance) and states the size of the disagreement set (sub-pixel rays vs the z-buffer at
+ * silhouettes).
+ * ================================================================================================ */
+typedef struct OracleVisCamera {
+  int32_t width, height;
+  float fx, fy, cx, cy;
+  float w2c[12];   /* row-major 3x4: camera->w2c().cast<float>() */
+  float c2w_R[9];  /* c2w_R_f_ (camera.h:321) */
+  float c2w_t[3];  /* c2w_t_f_ (camera.h:322) = org_ray_w */
+} OracleVisCamera;
+
+typedef struct OracleVisOption {
+  float backface_culling_angle_rad_th;
+  int32_t use_mask, use_depth, interp;
+  float max_viewing_angle, max_distance_from_camera_to_vertex, max_depth_difference, eps;
+  int32_t facewise;
+  int32_t reserved;
+} OracleVisOption;
+
+typedef struct OracleVisVertex {
+  float color[3];
+  float intensity;
+  float projected[2];
+  float viewing_angle;
+  float distance;
+} OracleVisVertex;
+
+/* image_util.h:156-193 (T = Vec3b) */
+static void vis_bilinear(float x, float y, const uint8_t* img, int cols, int rows, float* out) {
+  int x0 = (int)floorf(x), y0 = (int)floorf(y);
+  int x1 = x0 + 1, y1 = y0 + 1;
+  if (x0 < 0) x0 = 0;
+  if (y0 < 0) y0 = 0;
+  if (cols <= x1) x1 = cols - 1;
+  if (rows <= y1) y1 = rows - 1;
+  const float lu = x - (float)x0, lv = y - (float)y0;
+  for (int i = 0; i < 3; i++) {
+    const float c = (1.0f - lu) * (1.0f - lv) * (float)img[((size_t)y0 * cols + x0) * 3 + i] +
+                    lu * (1.0f - lv) * (float)img[((size_t)y0 * cols + x1) * 3 + i] +
+                    (1.0f - lu) * lv * (float)img[((size_t)y1 * cols + x0) * 3 + i] +
+                    lu * lv * (float)img[((size_t)y1 * cols + x1) * 3 + i];
+    out[i] = (float)f2u8(c);  /* static_cast<unsigned char>(colorf), then widened back to float */
+  }
+}
+
+/* visibility_tester.cc:416-529 with the substitution above.  world_p = vertex + offset. */
+static int vis_test_vertex(const OracleVisCamera* cam, const OracleVisOption* opt, const float* vtx,
+                           const float* nrm, const float* offset, const uint8_t* color, const float* depth,
+                           const uint8_t* mask, const float* zbuf, OracleVisVertex* out) {
+  float wp[3] = {vtx[0] + offset[0], vtx[1] + offset[1], vtx[2] + offset[2]};
+  /* Affine3f * Vector3f: translation + linear * v, rows reduced like dot3 (Eigen Transform.h) */
+  float cp[3];
+  for (int r = 0; r < 3; r++)
+    cp[r] = cam->w2c[r * 4 + 3] + (cam->w2c[r * 4 + 0] * wp[0] + (cam->w2c[r * 4 + 1] * wp[1] + cam->w2c[r * 4 + 2] * wp[2]));
+  /* PinholeCamera::Project (camera.h:380-387) */
+  const float ix = cam->fx / cp[2] * cp[0] + cam->cx;
+  const float iy = cam->fy / cp[2] * cp[1] + cam->cy;
+  const float d = cp[2];
+  if (d < 0 || ix < 0 || (float)(cam->width - 1) < ix || iy < 0 || (float)(cam->height - 1) < iy) return 0;
+  const int nn_x = (int)roundf(ix), nn_y = (int)roundf(iy);
+  const size_t nn = (size_t)nn_y * cam->width + nn_x;
+  if (opt->use_mask && mask[nn] != 255) return 0;
+  if (opt->use_depth && depth[nn] < FLT_EPSILON) return 0;
+  /* ray_w(float, float): camera.h:438-448 */
+  float dir[3] = {(ix - cam->cx) / cam->fx, (iy - cam->cy) / cam->fy, 1.0f};
+  const float n2 = dir[0] * dir[0] + (dir[1] * dir[1] + dir[2] * dir[2]);
+  if (n2 > 0.0f) {
+    const float s = sqrtf(n2);
+    dir[0] = dir[0] / s;
+    dir[1] = dir[1] / s;
+    dir[2] = dir[2] / s;
+  }
+  float ray[3];
+  mat3_mul(cam->c2w_R, dir, ray);
+  const float dot = -dot3(nrm, ray);
+  const float viewing_angle = acosf(dot);
+  if (opt->backface_culling_angle_rad_th < viewing_angle) return 0;
+  /* the BVH query of :457-483, replaced by the z-buffer */
+  const float t_v = sqrtf(cp[0] * cp[0] + (cp[1] * cp[1] + cp[2] * cp[2]));
+  if (zbuf) {
+    const float z_s = zbuf[nn];
+    if (z_s >= FLT_MIN) {
+      const float t_s = z_s * (t_v / cp[2]);
+      if (t_v - t_s > opt->eps) return 0;
+    }
+  }
+  if (opt->use_depth) {
+    const float diff = fabsf(cp[2] - depth[nn]);
+    if (opt->max_depth_difference < diff) return 0;
+  }
+  out->projected[0] = ix;
+  out->projected[1] = iy;
+  out->viewing_angle = viewing_angle;
+  out->distance = t_v;
+  if (out->distance > opt->max_distance_from_camera_to_vertex || out->viewing_angle > opt->max_viewing_angle) return 0;
+  if (opt->interp == 0) {
+    for (int i = 0; i < 3; i++) out->color[i] = (float)color[nn * 3 + i];
+  } else {
+    vis_bilinear(ix, iy, color, cam->width, cam->height, out->color);
+  }
+  /* Color2Gray (image_util.h:228-244): double arithmetic, cast to float */
+  out->intensity = (float)(0.2989 * out->color[0] + 0.5870 * out->color[1] + 0.1140 * out->color[2]);
+  return 1;
+}
+
+/* One keyframe.  Outputs are dense: v_visible[V] (0/1) + v_rec[V]; f_visible[F] + f_area / f_angle /
+ * f_distance [F] + f_tri [F*6]; rows of invisible elements are left untouched. */
+int oracle_visibility_keyframe(int32_t V, const float* vertices, const float* normals, int32_t F,
+                               const int32_t* indices, const OracleVisCamera* cam, const OracleVisOption* opt,
+                               const uint8_t* color, const float* depth, const uint8_t* mask, const float* zbuf,
+                               uint8_t* v_visible, OracleVisVertex* v_rec, uint8_t* f_visible, float* f_area,
+                               float* f_angle, float* f_distance, float* f_tri) {
+  if (!color || (opt->use_mask && !mask) || (opt->use_depth && !depth)) return 1;
+  const float zero[3] = {0.f, 0.f, 0.f};
+  if (!opt->facewise) {
+    for (int32_t v = 0; v < V; v++) {  /* TestVertices */
+      OracleVisVertex r;
+      if (vis_test_vertex(cam, opt, vertices + 3 * (size_t)v, normals + 3 * (size_t)v, zero, color, depth, mask, zbuf, &r)) {
+        v_visible[v] = 1;
+        v_rec[v] = r;
+      }
+    }
+  }
+  for (int32_t i = 0; i < F; i++) {  /* TestFaces / TestFacewiseVertices */
+    float angle = 0.0f, dist = 0.0f, tri[6];
+    int ok = 1;
+    float center[3] = {0.f, 0.f, 0.f};
+    if (opt->facewise) {  /* face_centers_ (PrepareData, :259-266): setZero, += each corner, /= 3 */
+      for (int j = 0; j < 3; j++)
+        for (int k = 0; k < 3; k++) center[k] += vertices[3 * (size_t)indices[3 * (size_t)i + j] + k];
+      for (int k = 0; k < 3; k++) center[k] /= 3;
+    }
+    for (int j = 0; j < 3 && ok; j++) {
+      const int32_t vid = indices[3 * (size_t)i + j];
+      const float* vtx = vertices + 3 * (size_t)vid;
+      OracleVisVertex r;
+      if (opt->facewise) {
+        float off[3];
+        for (int k = 0; k < 3; k++) off[k] = (center[k] - vtx[k]) * 1e-3f;
+        ok = vis_test_vertex(cam, opt, vtx, normals + 3 * (size_t)vid, off, color, depth, mask, zbuf, &r);
+        if (ok && !v_visible[vid]) {  /* "Update only once per vertex", sequential order */
+          v_visible[vid] = 1;
+          v_rec[vid] = r;
+        }
+      } else {
+        ok = v_visible[vid];
+        if (ok) r = v_rec[vid];
+      }
+      if (!ok) break;
+      angle += r.viewing_angle;
+      dist += r.distance;
+      tri[2 * j] = r.projected[0];
+      tri[2 * j + 1] = r.projected[1];
+    }
+    if (!ok) continue;
+    f_visible[i] = 1;
+    f_angle[i] = angle / 3;
+    f_distance[i] = dist / 3;
+    f_area[i] = 0.5f * fabsf(edge_function(tri, tri + 2, tri + 4));
+    for (int k = 0; k < 6; k++) f_tri[6 * (size_t)i + k] = tri[k];
+  }
+  return 0;
+}
+
+int oracle_abi_version(void) { return 7; }

@@ -10,6 +10,9 @@
 // reference's public API in the call order of examples/ex02_renderer.cc:245-278,142-143.
 
 #include <chrono>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -20,6 +23,7 @@
 #include "ugu/mesh.h"
 #include "ugu/renderer/cpu/rasterizer.h"
 #include "ugu/renderer/cpu/raytracer.h"
+#include "ugu/texturing/visibility_tester.h"
 #include "ugu/util/raster_util.h"
 #include "ugu/util/rgbd_util.h"
 
@@ -493,6 +497,184 @@ void ugu_ref_mesh_copy(void* mesh, float* vertices, float* normals, float* color
   if (tex0 && !m.materials().empty()) {
     const ugu::Image3b& t = m.materials()[0].diffuse_tex;
     std::memcpy(tex0, t.data, static_cast<size_t>(t.rows) * t.cols * 3);
+  }
+}
+
+
+// ---- ugu::VisibilityTester (include/ugu/texturing/visibility_tester.h:216-265,
+// src/texturing/visibility_tester.cc:416-733): the reference's per-keyframe vertex / face visibility pass
+// (BVH rays) and the statistics of VisibilityInfo.  The keyframes carry HOST images (colour, depth, mask)
+// and a pinhole camera; the tester is driven through its public API only (so, like every reference caller,
+// only the seven option fields VisibilityTesterOption::CopyTo copies take effect).  `num_threads` = 1 pins
+// the order of the face-wise mode, whose `v_succeeded` bookkeeping is racy under OpenMP
+// (visibility_tester.cc:608-629).
+struct UguRefKeyframe {
+  int32_t id;
+  int32_t pad_;
+  UguRefCamera cam;
+  const uint8_t* color;  // H*W*3
+  const float* depth;    // H*W or null
+  const uint8_t* mask;   // H*W or null
+};
+struct UguRefVisOption {
+  float backface_culling_angle_rad_th;
+  int32_t use_mask, use_depth, interp;
+  int32_t facewise;
+  int32_t num_threads;  // <= 0: leave OpenMP alone
+};
+
+struct RefVisHandle {
+  ugu::VisibilityInfo info;
+  std::vector<int> kf_ids;
+  int V = 0, F = 0;
+};
+
+void* ugu_ref_visibility_run(int32_t V, const float* vertices, const float* normals, int32_t F,
+                             const int32_t* indices, int32_t K, const UguRefKeyframe* kfs,
+                             const UguRefVisOption* o) {
+  ugu::set_log_level(ugu::LogLevel::kError);
+#ifdef _OPENMP
+  if (o->num_threads > 0) omp_set_num_threads(o->num_threads);
+#endif
+  ugu::VisibilityTesterOption opt;
+  opt.backface_culling_angle_rad_th = o->backface_culling_angle_rad_th;
+  opt.use_mask = o->use_mask != 0;
+  opt.use_depth = o->use_depth != 0;
+  opt.interp = static_cast<ugu::ColorInterpolation>(o->interp);
+  ugu::VisibilityTester tester(opt);
+  tester.set_data(ToVec<Eigen::Vector3f>(vertices, V), ToVec<Eigen::Vector3f>(normals, V),
+                  ToVec<Eigen::Vector3i>(indices, F));
+  if (!tester.PrepareData()) return nullptr;
+  std::vector<std::shared_ptr<ugu::Keyframe>> keyframes;
+  auto h = new RefVisHandle;
+  h->V = V;
+  h->F = F;
+  for (int k = 0; k < K; k++) {
+    auto kf = ugu::Keyframe::Create();
+    const UguRefKeyframe& s = kfs[k];
+    kf->id = s.id;
+    h->kf_ids.push_back(s.id);
+    const int W = s.cam.width, H = s.cam.height;
+    kf->color = ugu::Image3b::zeros(H, W);
+    std::memcpy(kf->color.data, s.color, static_cast<size_t>(W) * H * 3);
+    if (s.depth) {
+      kf->depth = ugu::Image1f::zeros(H, W);
+      std::memcpy(kf->depth.data, s.depth, static_cast<size_t>(W) * H * 4);
+    }
+    if (s.mask) {
+      kf->mask = ugu::Image1b::zeros(H, W);
+      std::memcpy(kf->mask.data, s.mask, static_cast<size_t>(W) * H);
+    }
+    kf->camera = std::make_shared<ugu::PinholeCamera>(W, H, ToAffine(s.cam.c2w), Eigen::Vector2f(s.cam.cx, s.cam.cy),
+                                                      Eigen::Vector2f(s.cam.fx, s.cam.fy));
+    keyframes.push_back(kf);
+  }
+  h->info.vertex_info_list.resize(V);
+  h->info.face_info_list.resize(F);
+  if (!tester.Test(keyframes, &h->info, o->facewise != 0)) {
+    delete h;
+    return nullptr;
+  }
+  return h;
+}
+
+void ugu_ref_visibility_free(void* handle) { delete static_cast<RefVisHandle*>(handle); }
+
+// Dense per-(keyframe, vertex) records, K*V each: visible (u8), colour (3 f32), intensity, projected_pos (2),
+// viewing_angle, distance.  Rows of keyframes in which the vertex is not visible are left untouched.
+void ugu_ref_visibility_vertex_records(void* handle, uint8_t* visible, float* color, float* intensity,
+                                       float* projected, float* viewing_angle, float* distance) {
+  auto* h = static_cast<RefVisHandle*>(handle);
+  const size_t V = h->V;
+  for (size_t v = 0; v < V; v++) {
+    for (const auto& r : h->info.vertex_info_list[v].visible_keyframes) {
+      size_t k = 0;
+      while (k < h->kf_ids.size() && h->kf_ids[k] != r.kf_id) k++;
+      const size_t i = k * V + v;
+      visible[i] = 1;
+      for (int c = 0; c < 3; c++) color[i * 3 + c] = r.color[c];
+      intensity[i] = r.intensity;
+      projected[i * 2 + 0] = r.projected_pos[0];
+      projected[i * 2 + 1] = r.projected_pos[1];
+      viewing_angle[i] = r.viewing_angle;
+      distance[i] = r.distance;
+    }
+  }
+}
+
+// Dense per-(keyframe, face) records, K*F each: visible (u8), area, viewing_angle, distance, projected_tri (6).
+void ugu_ref_visibility_face_records(void* handle, uint8_t* visible, float* area, float* viewing_angle,
+                                     float* distance, float* projected_tri) {
+  auto* h = static_cast<RefVisHandle*>(handle);
+  const size_t F = h->F;
+  for (size_t f = 0; f < F; f++) {
+    for (const auto& r : h->info.face_info_list[f].visible_keyframes) {
+      size_t k = 0;
+      while (k < h->kf_ids.size() && h->kf_ids[k] != r.kf_id) k++;
+      const size_t i = k * F + f;
+      visible[i] = 1;
+      area[i] = r.area;
+      viewing_angle[i] = r.viewing_angle;
+      distance[i] = r.distance;
+      for (int j = 0; j < 3; j++) {
+        projected_tri[i * 6 + 2 * j] = r.projected_tri[j][0];
+        projected_tri[i * 6 + 2 * j + 1] = r.projected_tri[j][1];
+      }
+    }
+  }
+}
+
+// FaceInfo::CalcStat (visibility_tester.cc:185-218): F x {max_area_id, min_viewing_angle_id, min_distance_id}
+// (-1 where the face was never visible), and VertexInfo::CalcStat (visibility_tester.cc:66-152): per vertex
+// ids[2] = {min_viewing_angle_id, min_distance_id}, scalars[7] = {mean_viewing_angle, median_viewing_angle,
+// mean_distance, median_distance, min_intensity, median_intensity, number of visible keyframes}, colors[10][3] =
+// {mean, median, min_viewing_angle, mean_viewing_angle, median_viewing_angle, min_distance, mean_distance,
+//  median_distance, median_intensity, min_intensity}_color.
+void ugu_ref_visibility_stats(void* handle, int32_t* face_ids, int32_t* vertex_ids, float* vertex_scalars,
+                              float* vertex_colors) {
+  auto* h = static_cast<RefVisHandle*>(handle);
+  for (int f = 0; f < h->F; f++) {
+    const auto& fi = h->info.face_info_list[f];
+    face_ids[f * 3 + 0] = fi.max_area_id;
+    face_ids[f * 3 + 1] = fi.min_viewing_angle_id;
+    face_ids[f * 3 + 2] = fi.min_distance_id;
+  }
+  for (int v = 0; v < h->V; v++) {
+    const auto& vi = h->info.vertex_info_list[v];
+    vertex_ids[v * 2 + 0] = vi.min_viewing_angle_id;
+    vertex_ids[v * 2 + 1] = vi.min_distance_id;
+    float* s = vertex_scalars + static_cast<size_t>(v) * 7;
+    s[0] = vi.mean_viewing_angle;
+    s[1] = vi.median_viewing_angle;
+    s[2] = vi.mean_distance;
+    s[3] = vi.median_distance;
+    s[4] = vi.min_intensity;
+    s[5] = vi.median_intensity;
+    s[6] = static_cast<float>(vi.visible_keyframes.size());
+    const Eigen::Vector3f* cs[10] = {&vi.mean_color, &vi.median_color, &vi.min_viewing_angle_color,
+                                     &vi.mean_viewing_angle_color, &vi.median_viewing_angle_color,
+                                     &vi.min_distance_color, &vi.mean_distance_color, &vi.median_distance_color,
+                                     &vi.median_intensity_color, &vi.min_intensity_color};
+    const bool any = !vi.visible_keyframes.empty();
+    for (int c = 0; c < 10; c++)
+      for (int k = 0; k < 3; k++)
+        // the last two are never initialised by the reference for vertices without a visible keyframe
+        vertex_colors[(static_cast<size_t>(v) * 10 + c) * 3 + k] = (any || c < 8) ? (*cs[c])[k] : 0.0f;
+  }
+}
+
+// The float camera constants the tester reads: w2c().cast<float>() as a row-major 3x4, c2w_R_f_ (3x3) and
+// c2w_t_f_ (camera.h:317-331).
+void ugu_ref_visibility_camera_constants(const UguRefCamera* cam, float* w2c34, float* c2w_R, float* c2w_t) {
+  ugu::PinholeCamera c(cam->width, cam->height, ToAffine(cam->c2w), Eigen::Vector2f(cam->cx, cam->cy),
+                       Eigen::Vector2f(cam->fx, cam->fy));
+  const Eigen::Affine3f w2c = c.w2c().cast<float>();
+  for (int r = 0; r < 3; r++)
+    for (int k = 0; k < 4; k++) w2c34[r * 4 + k] = w2c.matrix()(r, k);
+  const Eigen::Affine3f c2w = c.c2w().cast<float>();
+  for (int r = 0; r < 3; r++) {
+    for (int k = 0; k < 3; k++) c2w_R[r * 3 + k] = c2w.matrix()(r, k);
+    c2w_t[r] = c2w.matrix()(r, 3);
   }
 }
 

@@ -189,6 +189,72 @@ def test_batch_equals_single_views_device_and_host():
             assert np.array_equal(util.bits(hb[k][i]), util.bits(singles[i][k])), (i, k)
 
 
+@pytest.mark.parametrize("size,n_views", [((37, 29), 37), ((64, 48), 19), ((33, 1), 3)],
+                         ids=lambda v: str(v).replace(" ", ""))
+def test_batch_launch_sets_at_ragged_sizes(size, n_views):
+    """More views than one launch set holds (16), at image sizes whose per-view slabs lose their 16-byte
+    alignment (odd W*H: the kernels fall back to scalar stores for those slabs), device and host forms,
+    on a caller stream and on the library's own."""
+    import torch
+    w, h = size
+    mesh = meshgen.icosphere(3)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, backface_culling=False)
+    run = util.CudaRunner(mesh, opt)
+    cams = [PinholeCamera(w, h, p, fov_y_deg=50.0) for p in meshgen.orbit_poses((0, 0, 0), 2.6, n_views)]
+    singles = [run.render(cm, opt) for cm in cams]
+    P = w * h
+    spec = dict(color=(torch.uint8, 3), depth=(torch.float32, 1), normal=(torch.float32, 3),
+                mask=(torch.uint8, 1), face_id=(torch.int32, 1))
+    for own_stream in (False, True):
+        dev = {k: torch.full((n_views * P * ch,), 7, dtype=dt, device="cuda") for k, (dt, ch) in spec.items()}
+        torch.cuda.synchronize()
+        stream = 0 if own_stream else torch.cuda.current_stream().cuda_stream
+        run.r.render_batch(cams, **{k: v.data_ptr() for k, v in dev.items()}, on_device=True, stream=stream)
+        run.r.sync()
+        torch.cuda.synchronize()
+        for k, (dt, ch) in spec.items():
+            got = dev[k].cpu().numpy().reshape((n_views,) + singles[0][k].shape)
+            for i in range(n_views):
+                assert np.array_equal(util.bits(got[i]), util.bits(singles[i][k])), (own_stream, i, k)
+    for pinned in (True, False):
+        if pinned:
+            from ugu_b200.renderer import pinned_empty
+            hb = {k: pinned_empty((n_views,) + singles[0][k].shape, singles[0][k].dtype) for k in spec}
+        else:
+            hb = {k: np.empty((n_views,) + singles[0][k].shape, singles[0][k].dtype) for k in spec}
+        run.r.render_batch(cams, **{k: v.ctypes.data for k, v in hb.items()}, on_device=False)
+        for k in spec:
+            for i in range(n_views):
+                assert np.array_equal(util.bits(hb[k][i]), util.bits(singles[i][k])), (pinned, i, k)
+    # the scratch is left clean: a single view afterwards is unchanged
+    util.assert_parity(run.render(cams[1], opt), singles[1], strict=True, what="single after batch")
+
+
+def test_calls_on_different_streams_are_ordered():
+    """One handle, one set of scratch buffers: back-to-back calls on different streams (and on the
+    library's own) must not race on them (each launch set waits for the previous one's event)."""
+    import torch
+    mesh = meshgen.icosphere(5)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex)
+    run = util.CudaRunner(mesh, opt)
+    cams = [PinholeCamera(256, 192, p, fov_y_deg=45.0) for p in meshgen.orbit_poses((0, 0, 0), 2.7, 6)]
+    singles = [run.render(cm, opt, want=("face_id", "depth")) for cm in cams]
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    P = 256 * 192
+    fid = [torch.empty(P, dtype=torch.int32, device="cuda") for _ in cams]
+    dep = [torch.empty(P, dtype=torch.float32, device="cuda") for _ in cams]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        for i, cm in enumerate(cams):
+            st = streams[i % 3].cuda_stream if (i + rep) % 4 else 0
+            run.r.render_device(cm, face_id=fid[i].data_ptr(), depth=dep[i].data_ptr(), stream=st)
+        run.r.sync()
+        torch.cuda.synchronize()
+        for i in range(len(cams)):
+            assert np.array_equal(fid[i].cpu().numpy().reshape(192, 256), singles[i]["face_id"]), (rep, i)
+            assert np.array_equal(util.bits(dep[i].cpu().numpy().reshape(192, 256)), util.bits(singles[i]["depth"])), (rep, i)
+
+
 @pytest.mark.skipif(not ref_available(), reason="oracle/_ref did not travel to this box")
 def test_cuda_vs_live_compiled_reference_spot_640x480():
     """BASELINE.json config 1: spot, 640x480, ex02 intrinsics (r = 1) and six poses, textured

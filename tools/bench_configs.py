@@ -57,7 +57,10 @@ def config(name):
 
 
 def run(name, max_views, cpu):
+    from bench import ClockSampler
     mesh, opt, cams, outs, desc = config(name)
+    sampler = ClockSampler(0)
+    sampler.start()
     W, H = cams[0].width(), cams[0].height()
     P, F = W * H, len(mesh.vertex_indices)
     r = Rasterizer(opt)
@@ -93,7 +96,35 @@ def run(name, max_views, cpu):
     timed_pass()
     st = r.stats()
     r.set_profiling(False, ())
+    # the batched multi-view path: ONE render_batch call over all n views (launch sets of up to 16 views,
+    # view = blockIdx.y), outputs device-resident, one event pair around the call; L2 flushed before the
+    # batch, NOT between its views (a batch is one unit of work)
+    bdev = {k: torch.empty(n * P * spec[k][1], dtype=spec[k][0], device="cuda") for k in outs}
+    bptrs = {k: v.data_ptr() for k, v in bdev.items()}
+    blist = [natives[i % len(natives)] for i in range(n)]
+    r.render_batch(blist, on_device=True, stream=ts.cuda_stream, **bptrs)
+    torch.cuda.synchronize()
+    bt = []
+    for rep in range(5):
+        flush.zero_()
+        b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        b0.record()
+        r.render_batch(blist, on_device=True, stream=ts.cuda_stream, **bptrs)
+        b1.record()
+        torch.cuda.synchronize()
+        bt.append(b0.elapsed_time(b1) / n)
+    r.reset_stats()
+    r.set_profiling(True, (0, 1, 2, 3))    # per-stage event pairs around each launch set of the batch
+    r.render_batch(blist, on_device=True, stream=ts.cuda_stream, **bptrs)
+    torch.cuda.synchronize()
+    bst = r.stats()
+    r.set_profiling(False, ())
+    batch_stage_us = {k: round(v / max(1, bst["timed_views"]) * 1e3, 2) for k, v in bst["stage_ms"].items()}
+    del bdev
     line = {"config": desc, "views": n, "ms_per_view": ms, "mpix_per_s": P / ms / 1e3,
+            "batch_ms_per_view": {"min": min(bt), "median": sorted(bt)[len(bt) // 2], "max": max(bt),
+                                  "stage_us_per_view": batch_stage_us,
+                                  "note": "one render_batch call over all views, L2 flushed before the batch only"},
             "mtri_per_s": F / ms / 1e3,
             "stage_us": {k: round(v / max(1, st["timed_views"]) * 1e3, 2) for k, v in st["stage_ms"].items()},
             "large_triangles": st["large_triangles"], "tile_jobs": st["tile_jobs"]}
@@ -109,6 +140,7 @@ def run(name, max_views, cpu):
         r.set_camera(cams[i % len(cams)])
         assert r.Render(**args)
     line["e2e_ms_per_view"] = (time.perf_counter() - t0) / ne * 1e3
+    line["clocks"] = sampler.stop()
     if cpu:
         import oracle
         if oracle.ref_available():

@@ -161,3 +161,24 @@ extern "C" int ugu_b200_camera_from_c2w(const double* c2w16, int32_t width, int3
   }
   return UGU_B200_OK;
 }
+
+extern "C" int ugu_b200_keyframe_camera_from_c2w(const double* c2w16, int32_t width, int32_t height, float fx,
+                                                 float fy, float cx, float cy, ugu_b200_keyframe* kf) {
+  if (c2w16 == nullptr || kf == nullptr) return UGU_B200_E_INVALID;
+  const int rc = ugu_b200_camera_from_c2w(c2w16, width, height, fx, fy, cx, cy, &kf->cam);
+  if (rc != UGU_B200_OK) return rc;
+  M3 lin, inv;
+  double t[3];
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < 3; j++) lin.m[i][j] = c2w16[i * 4 + j];
+    t[i] = c2w16[i * 4 + 3];
+  }
+  if (!Inverse(lin, &inv)) return UGU_B200_E_INVALID;
+  // w2c_ = c2w_.inverse() (Affine: [L^-1 | -(L^-1 t)]), then .cast<float>() (visibility_tester.cc:422)
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < 3; j++) kf->w2c[i * 4 + j] = static_cast<float>(inv.m[i][j]);
+    kf->w2c[i * 4 + 3] = static_cast<float>(-(inv.m[i][0] * t[0] + inv.m[i][1] * t[1] + inv.m[i][2] * t[2]));
+    kf->c2w_t[i] = static_cast<float>(t[i]);
+  }
+  return UGU_B200_OK;
+}

@@ -17,6 +17,7 @@
 #include "raster_kernels.cuh"
 #include "uv_raster_kernels.cuh"
 #include "visibility_kernels.cuh"
+#include "visibility_tester_kernels.cuh"
 #include "depth2mesh_kernels.cuh"
 #include "gbuffer_kernels.cuh"
 #include "raytrace_kernels.cuh"
@@ -54,12 +55,16 @@ struct ugu_b200_rasterizer {
 
   // per-view scratch
   DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
-  size_t vis_pixels = 0;
+  size_t vis_pixels = 0;  // pixels per visibility slab
+  size_t vis_slabs = 0;   // slabs known to hold EMPTY
+  int max_batch = 0;      // views per launch set of render_batch (0 = adaptive, UGU_B200_BATCH overrides)
+  unsigned long long hazard_seen = 0;  // device hazard total already reported (see SnapshotCounters)
+  cudaEvent_t ev_scratch = nullptr;    // recorded after every launch set: cross-stream ordering of the scratch
+  cudaStream_t last_stream = nullptr;  // stream of the last launch set that used the scratch
+  bool scratch_used = false;
   int coop_max = 0;  // bbox samples up to which a triangle is rasterised inside raster_kernel; larger
                      // ones go to the tile-job queue.  0 = adaptive (see RenderView)
   bool use_pdl = true;  // programmatic dependent launch of the per-view kernels (UGU_B200_PDL=0 disables)
-  int vertex_vpt = 1;    // vertices per thread of the vertex kernel (4 or 1)
-  int raster_minb = 6;   // resident CTAs per SM the raster kernel is compiled for (4, 5, 6)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
   DevBuf out_color[2], out_depth[2], out_normal[2], out_mask[2], out_fid[2];
@@ -74,6 +79,11 @@ struct ugu_b200_rasterizer {
   // face-visibility consumer scratch (visibility_kernels.cuh)
   DevBuf vis_tmp, vis_in, vis_acc;
   int vis_tmp_faces = 0;  // faces per slot the scratch was zeroed for
+
+  // keyframe visibility pass (visibility_tester_kernels.cuh): mesh copy, accumulators, record / image scratch
+  DevBuf vt_pos, vt_nrm, vt_idx, vt_acc, vt_owner, vt_vvis, vt_vrec, vt_fvis, vt_frec, vt_img, vt_zbuf;
+  int vt_V = 0, vt_F = 0;
+  size_t vt_owner_clean = 0;  // elements of vt_owner known to hold kVtNoOwner
 
   // Depth2Mesh scratch + the device-resident result of the last call (depth2mesh_kernels.cuh)
   DevBuf d2m_in_depth, d2m_in_color, d2m_small, d2m_block_sums, d2m_vid, d2m_fref, d2m_vertices, d2m_faces,
@@ -270,18 +280,28 @@ int Validate(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_
 }
 
 // ---- per-view scratch --------------------------------------------------------------------------
-int EnsureFrame(ugu_b200_rasterizer* r, int W, int H, cudaStream_t st) {
+// Slabs for `B` views of W x H: ray tables, visibility buffers (EMPTY between calls), projected vertices and
+// the large-triangle queues.  A (re)sized visibility area is filled with EMPTY here; afterwards resolve_kernel
+// leaves every slab it consumed EMPTY again.
+int EnsureFrame(ugu_b200_rasterizer* r, int W, int H, int B, cudaStream_t st) {
   const size_t P = (size_t)W * H;
+  const size_t Vpad = std::max<size_t>(((size_t)r->mesh.V + 3) & ~size_t(3), 4);
+  const size_t Fq = std::max<size_t>((size_t)r->mesh.F, 1);
   int rc;
-  if ((rc = Grow(r, &r->ray_dx, (size_t)W * 4))) return rc;
-  if ((rc = Grow(r, &r->ray_dy, (size_t)H * 4))) return rc;
-  if (P != r->vis_pixels || r->vis.bytes < P * 8) {
-    // (re)size + fill with EMPTY; afterwards resolve_kernel leaves it EMPTY after every view
-    if ((rc = Grow(r, &r->vis, P * 8))) return rc;
-    fill_u64<<<Blocks(P, 256), 256, 0, st>>>((unsigned long long*)r->vis.p, P, kVisEmpty);
+  if ((rc = Grow(r, &r->ray_dx, (size_t)B * W * 4))) return rc;
+  if ((rc = Grow(r, &r->ray_dy, (size_t)B * H * 4))) return rc;
+  if ((rc = Grow(r, &r->proj, (size_t)B * Vpad * sizeof(float4)))) return rc;
+  if ((rc = Grow(r, &r->q_face, (size_t)B * Fq * 4))) return rc;
+  if ((rc = Grow(r, &r->q_job, (size_t)B * Fq * 8))) return rc;
+  if (P != r->vis_pixels || (size_t)B > r->vis_slabs) {
+    // the slabs of one size are contiguous, so a new size or more slabs re-fills the whole area
+    if ((rc = Grow(r, &r->vis, (size_t)B * P * 8))) return rc;
+    const size_t n = (size_t)B * P;
+    fill_u64<<<Blocks(n, 256), 256, 0, st>>>((unsigned long long*)r->vis.p, n, kVisEmpty);
     r->stats.kernel_launches++;
     CU_TRY(r, cudaGetLastError());
     r->vis_pixels = P;
+    r->vis_slabs = (size_t)B;
   }
   return UGU_B200_OK;
 }
@@ -326,10 +346,10 @@ int g_binned_ctas_per_sm = 8;
 // Launch with programmatic stream serialization (PDL): the kernel may be scheduled into the tail of
 // its predecessor on the stream; it synchronises on the predecessor's results itself (pdl_wait()).
 template <typename... KArgs, typename... Args>
-cudaError_t LaunchView(void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, bool pdl,
+cudaError_t LaunchView(void (*kernel)(KArgs...), dim3 grid, unsigned block, cudaStream_t st, bool pdl,
                        Args&&... args) {
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(grid);
+  cfg.gridDim = grid;
   cfg.blockDim = dim3(block);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = st;
@@ -341,13 +361,20 @@ cudaError_t LaunchView(void (*kernel)(KArgs...), unsigned grid, unsigned block, 
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
-// Launch the four kernels of one view into device outputs `dout` on stream `st`.
-int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
-               cudaStream_t st, const GBufParams* gbuf = nullptr) {
-  int rc = EnsureFrame(r, cam->width, cam->height, st);
-  if (rc) return rc;
-  ViewParams vp;
-  MakeViewParams(cam, &vp);
+// Cross-stream ordering of the handle's single set of scratch buffers (proj / vis / queues / counters / ray
+// tables ...): every launch set records an event; a call on a DIFFERENT stream first waits for it.
+int AcquireScratch(ugu_b200_rasterizer* r, cudaStream_t st) {
+  if (r->scratch_used && r->last_stream != st) CU_TRY(r, cudaStreamWaitEvent(st, r->ev_scratch, 0));
+  return UGU_B200_OK;
+}
+int ReleaseScratch(ugu_b200_rasterizer* r, cudaStream_t st) {
+  CU_TRY(r, cudaEventRecord(r->ev_scratch, st));
+  r->last_stream = st;
+  r->scratch_used = true;
+  return UGU_B200_OK;
+}
+
+FrameDev MakeFrame(const ugu_b200_rasterizer* r, int W, int H) {
   FrameDev fr;
   fr.proj = (float4*)r->proj.p;
   fr.ray_dx = (float*)r->ray_dx.p;
@@ -356,14 +383,17 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   fr.counters = (unsigned long long*)r->counters.p;
   fr.q_face = (int*)r->q_face.p;
   fr.q_job = (unsigned long long*)r->q_job.p;
-  // Triangles up to coop_max bbox samples are rasterised inside raster_kernel (one warp per 32
-  // faces); larger ones go to the globally load-balanced tile-job queue.  The in-kernel path is the
-  // cheaper one per triangle but only as parallel as the face count: with fewer raster warps than
-  // the machine holds (F < ~600k) mid-size triangles are better spread over the whole GPU by the
-  // queue (measured: config 4, 10M faces, 1.17 -> 0.93 ms with 32; spot, 5.9k faces, 33 -> 38 us).
-  fr.coop_max = r->coop_max > 0 ? r->coop_max : (r->mesh.F >= 4 * 32 * 32 * g_num_sms ? 32 : 16);
-  const MeshDev& m = r->mesh;
+  fr.coop_max = 0;
+  fr.s_proj = std::max<size_t>(((size_t)r->mesh.V + 3) & ~size_t(3), 4);
+  fr.s_ray_dx = (size_t)W;
+  fr.s_ray_dy = (size_t)H;
+  fr.s_vis = (size_t)W * H;
+  fr.s_q = std::max<size_t>((size_t)r->mesh.F, 1);
+  return fr;
+}
 
+ShadeParams MakeShade(const ugu_b200_rasterizer* r, const ugu_b200_outputs* dout, size_t view_pixels,
+                      unsigned first_view = 0) {
   ShadeParams sp;
   sp.diffuse_color = r->opt.diffuse_color;
   sp.interp = r->opt.interp;
@@ -381,31 +411,59 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   sp.normal = dout->normal;
   sp.mask = dout->mask;
   sp.face_id = dout->face_id;
+  sp.view_pixels = view_pixels;
+  sp.first_view = first_view;
+  return sp;
+}
 
-  const size_t P = (size_t)vp.W * vp.H;
+// Views per launch set for a batch of `n` views: as many as the scratch budget allows, at most kMaxBatch.
+int BatchViews(const ugu_b200_rasterizer* r, int n, int W, int H) {
+  if (n <= 1) return 1;
+  const size_t P = (size_t)W * H;
+  const size_t per_view = (((size_t)r->mesh.V + 3) & ~size_t(3)) * 16 + P * 8 + (size_t)r->mesh.F * 12 + ((size_t)W + H) * 4;
+  const size_t budget = (size_t)3 << 29;  // 1.5 GiB of per-view scratch
+  int b = (int)std::max<size_t>(1, std::min<size_t>(kMaxBatch, budget / std::max<size_t>(per_view, 1)));
+  if (r->max_batch > 0) b = std::min(b, r->max_batch);
+  return std::min(b, n);
+}
+
+// One launch set (vertex, raster, tile jobs, resolve) for `n` <= kMaxBatch views of one image size into
+// device outputs on stream `st`; view v writes at element offset v * W*H of every requested output.
+template <int NV>
+int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, const ugu_b200_outputs* dout,
+                  unsigned first_view, cudaStream_t st, const GBufParams* gbuf) {
+  const int W = cams[0].width, H = cams[0].height;
+  int rc = EnsureFrame(r, W, H, n, st);
+  if (rc) return rc;
+  ViewBatch<NV> vb;
+  for (int v = 0; v < NV; v++) MakeViewParams(&cams[std::min(v, n - 1)], &vb.v[v]);
+  FrameDev fr = MakeFrame(r, W, H);
+  // Triangles up to coop_max bbox samples are rasterised inside raster_kernel (one warp per 32
+  // faces); larger ones go to the globally load-balanced tile-job queue.  The in-kernel path is the
+  // cheaper one per triangle but only as parallel as the face count: with fewer raster warps than
+  // the machine holds (F < ~600k) mid-size triangles are better spread over the whole GPU by the
+  // queue (measured: config 4, 10M faces, 1.17 -> 0.93 ms with 32; spot, 5.9k faces, 33 -> 38 us).
+  fr.coop_max = r->coop_max > 0 ? r->coop_max : (r->mesh.F >= 4 * 32 * 32 * g_num_sms ? 32 : 16);
+  const MeshDev& m = r->mesh;
+  const size_t P = (size_t)W * H;
+  const ShadeParams sp = MakeShade(r, dout, P, first_view);
   const bool pdl = r->use_pdl;
+  const unsigned ny = (unsigned)n;
   {
     StageTimer t(r, st, UGU_B200_STAGE_VERTEX);
-    if (r->vertex_vpt == 1) {
-      const size_t threads = std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H);
-      CU_TRY(r, LaunchView(vertex_kernel_1, Blocks(threads, 256), 256, st, pdl, vp, m, fr));
-    } else {
-      const size_t threads = std::max<size_t>((size_t)(m.V + 3) / 4, (size_t)vp.W + vp.H);
-      CU_TRY(r, LaunchView(vertex_kernel, Blocks(threads, 256), 256, st, pdl, vp, m, fr));
-    }
+    const size_t threads = std::max<size_t>((size_t)m.V, (size_t)W + H);
+    CU_TRY(r, LaunchView(vertex_kernel_b<NV>, dim3(Blocks(threads, 256)), 256, st, pdl, vb, n, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
     // 6 resident CTAs per SM (40 registers, no spills) measured 2-4 % faster than 4 on every config
-    if (r->raster_minb == 4)
-      CU_TRY(r, LaunchView(raster_kernel<1, 4>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
-    else
-      CU_TRY(r, LaunchView(raster_kernel<1, 6>, Blocks((size_t)m.F, 8 * 32), 256, st, pdl, vp, m, fr));
+    CU_TRY(r, LaunchView(raster_kernel<1, 6, NV>, dim3(Blocks((size_t)m.F, 8 * 32), ny), 256, st, pdl, vb, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
-    // persistent: exactly one resident wave
-    CU_TRY(r, LaunchView(binned_kernel, (unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, st, pdl, vp, m, fr));
+    // persistent: exactly one resident wave, shared by the views of the batch
+    const unsigned resident = (unsigned)(g_num_sms * g_binned_ctas_per_sm);
+    CU_TRY(r, LaunchView(binned_kernel<NV>, dim3(std::max(1u, (resident + ny - 1) / ny), ny), 128, st, pdl, vb, m, fr));
   }
   if (gbuf) {
     // G-buffer fields from the finished visibility buffer, before the resolve kernel consumes and
@@ -416,7 +474,7 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
     gp.have_uv = (m.num_uv > 0 && r->has_uvidx) ? 1 : 0;
     const unsigned chunks = (unsigned)((P + 31) / 32);
     const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 8), (chunks + 7) / 8));
-    CU_TRY(r, LaunchView(gbuffer_kernel, grid, 256, st, false, vp, m, fr, gp));
+    CU_TRY(r, LaunchView(gbuffer_kernel, dim3(grid), 256, st, false, vb.v[0], m, fr, gp));
     r->stats.kernel_launches++;
   }
   {
@@ -427,12 +485,13 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
     const bool need_nrm = sp.normal != nullptr || (need_color && sp.diffuse_shading != 0);
     const int color_mode = need_color ? sp.diffuse_color : 0;
     const int nmode = !need_nrm ? 0 : (sp.shading_normal == 0 ? 1 : (m.vattr ? 3 : 2));
-    const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 4), (chunks + 7) / 8));
+    const unsigned gx = std::max(1u, std::min(((unsigned)(g_num_sms * 4) + ny - 1) / ny, (chunks + 7) / 8));
+    const dim3 grid(gx, ny);
     // (the one-chunk-deeper variant <.., true>, which also prefetches the projected vertices, measured
     //  slower on every config: its extra live registers spill at 4 CTAs/SM — see DESIGN.md)
-#define UGU_RESOLVE_CASE(C, N)                                                                   \
-  case (C)*4 + (N):                                                                              \
-    CU_TRY(r, LaunchView(resolve_kernel<C, N, 4, false>, grid, 256, st, pdl, vp, m, fr, sp));    \
+#define UGU_RESOLVE_CASE(C, N)                                                                      \
+  case (C)*4 + (N):                                                                                 \
+    CU_TRY(r, LaunchView(resolve_kernel<C, N, 4, false, NV>, grid, 256, st, pdl, vb, m, fr, sp));   \
     break;
     switch (color_mode * 4 + nmode) {
       UGU_RESOLVE_CASE(0, 0)
@@ -454,10 +513,34 @@ int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b20
   }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
-  r->stats.views++;
-  if (r->profiling) r->stats.timed_views++;
-  r->stats.h2d_bytes += sizeof(ViewParams);
+  r->stats.views += (uint64_t)n;
+  if (r->profiling) r->stats.timed_views += (uint64_t)n;
+  r->stats.h2d_bytes += sizeof(ViewParams) * (size_t)n;
   return UGU_B200_OK;
+}
+
+// `n` views of one image size into device outputs (view i at element offset i * W*H), cut into launch sets
+// of at most `batch` views.
+int RenderViews(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, const ugu_b200_outputs* dout,
+                cudaStream_t st, int batch) {
+  int rc = AcquireScratch(r, st);
+  if (rc) return rc;
+  for (int i = 0; i < n; i += batch) {
+    const int k = std::min(batch, n - i);
+    if (k == 1 && i == 0) rc = LaunchViewSet<1>(r, cams, 1, dout, 0u, st, nullptr);
+    else rc = LaunchViewSet<kMaxBatch>(r, cams + i, k, dout, (unsigned)i, st, nullptr);
+    if (rc) return rc;
+  }
+  return ReleaseScratch(r, st);
+}
+
+// One view (optionally with the G-buffer kernel between the tile-job and the resolve kernel).
+int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
+               cudaStream_t st, const GBufParams* gbuf = nullptr) {
+  int rc = AcquireScratch(r, st);
+  if (rc) return rc;
+  if ((rc = LaunchViewSet<1>(r, cam, 1, dout, 0u, st, gbuf))) return rc;
+  return ReleaseScratch(r, st);
 }
 
 bool IsPinnedHost(const void* p) {
@@ -502,13 +585,15 @@ struct CopySeg {
   size_t bytes;
 };
 
-int CollectSegs(const ugu_b200_outputs* host, const ugu_b200_outputs* dev, size_t P, size_t view,
+// `count` consecutive views starting at host view index `view` <- the first `count` view slabs of `dev`
+int CollectSegs(const ugu_b200_outputs* host, const ugu_b200_outputs* dev, size_t P, size_t view, size_t count,
                 std::vector<CopySeg>* segs) {
-  if (host->color) segs->push_back({host->color + view * P * 3, dev->color, P * 3});
-  if (host->depth) segs->push_back({host->depth + view * P, dev->depth, P * 4});
-  if (host->normal) segs->push_back({host->normal + view * P * 3, dev->normal, P * 12});
-  if (host->mask) segs->push_back({host->mask + view * P, dev->mask, P});
-  if (host->face_id) segs->push_back({host->face_id + view * P, dev->face_id, P * 4});
+  const size_t n = P * count;
+  if (host->color) segs->push_back({host->color + view * P * 3, dev->color, n * 3});
+  if (host->depth) segs->push_back({host->depth + view * P, dev->depth, n * 4});
+  if (host->normal) segs->push_back({host->normal + view * P * 3, dev->normal, n * 12});
+  if (host->mask) segs->push_back({host->mask + view * P, dev->mask, n});
+  if (host->face_id) segs->push_back({host->face_id + view * P, dev->face_id, n * 4});
   return UGU_B200_OK;
 }
 
@@ -567,11 +652,14 @@ int CopyOut(ugu_b200_rasterizer* r, const std::vector<CopySeg>& segs, cudaStream
 }
 
 int SnapshotCounters(ugu_b200_rasterizer* r) {
-  // counters[4..6] hold the previous view's (queue, hazards, -) as saved by resolve_kernel
+  // slab 0 words [4..6]: the last single view's (queue, hazards) as saved by resolve_kernel, and the
+  // running hazard total over every view of every batch (reported as the delta since the last snapshot)
   const unsigned long long packed = r->counters_host[0];
   r->stats.large_triangles = packed >> kQueueJobBits;
   r->stats.tile_jobs = packed & kQueueJobMask;
-  r->stats.hazard_fragments = r->counters_host[1];
+  const unsigned long long total = r->counters_host[2];
+  r->stats.hazard_fragments = total - r->hazard_seen;
+  r->hazard_seen = total;
   return UGU_B200_OK;
 }
 
@@ -622,7 +710,7 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   g_num_sms = prop.multiProcessorCount;
   {
     int n_ctas = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n_ctas, binned_kernel, 128, 0) == cudaSuccess && n_ctas > 0)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n_ctas, binned_kernel<1>, 128, 0) == cudaSuccess && n_ctas > 0)
       g_binned_ctas_per_sm = n_ctas;
     if (const char* e = getenv("UGU_B200_BINNED_CTAS")) g_binned_ctas_per_sm = std::max(1, atoi(e));
   }
@@ -639,8 +727,7 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
     r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
   }
   if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
-  if (const char* e = getenv("UGU_B200_VERTEX_VPT")) r->vertex_vpt = atoi(e) == 4 ? 4 : 1;
-  if (const char* e = getenv("UGU_B200_RASTER_MINB")) r->raster_minb = atoi(e) == 4 ? 4 : 6;
+  if (const char* e = getenv("UGU_B200_BATCH")) r->max_batch = std::max(1, std::min(atoi(e), (int)kMaxBatch));
   auto fail = [&](cudaError_t err, const char* what) {
     int rc = Fail(nullptr, UGU_B200_E_CUDA, "%s failed: %s", what, cudaGetErrorString(err));
     ugu_b200_rasterizer_destroy(r);
@@ -660,9 +747,12 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   r->ev_stage.resize(kEventPool, 0);
   for (auto& ev : r->ev_pool)
     if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail(e, "cudaEventCreate");
-  if ((e = cudaMalloc(&r->counters.p, 64)) != cudaSuccess) return fail(e, "cudaMalloc");
-  r->counters.bytes = 64;
-  if ((e = cudaMemset(r->counters.p, 0, 64)) != cudaSuccess) return fail(e, "cudaMemset");
+  const size_t counter_bytes = (size_t)kMaxBatch * kCounterSlab * 8;
+  if ((e = cudaMalloc(&r->counters.p, counter_bytes)) != cudaSuccess) return fail(e, "cudaMalloc");
+  r->counters.bytes = counter_bytes;
+  if ((e = cudaMemset(r->counters.p, 0, counter_bytes)) != cudaSuccess) return fail(e, "cudaMemset");
+  if ((e = cudaEventCreateWithFlags(&r->ev_scratch, cudaEventDisableTiming)) != cudaSuccess)
+    return fail(e, "cudaEventCreate");
   if ((e = cudaHostAlloc((void**)&r->counters_host, 64, cudaHostAllocDefault)) != cudaSuccess)
     return fail(e, "cudaHostAlloc");
   memset(r->counters_host, 0, 64);
@@ -679,6 +769,8 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters,
                     &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask,
                     &r->vis_tmp, &r->vis_in, &r->vis_acc,
+                    &r->vt_pos, &r->vt_nrm, &r->vt_idx, &r->vt_acc, &r->vt_owner, &r->vt_vvis, &r->vt_vrec,
+                    &r->vt_fvis, &r->vt_frec, &r->vt_img, &r->vt_zbuf,
                     &r->d2m_in_depth, &r->d2m_in_color, &r->d2m_small, &r->d2m_block_sums, &r->d2m_vid,
                     &r->d2m_fref, &r->d2m_vertices, &r->d2m_faces, &r->d2m_normals, &r->d2m_face_normals,
                     &r->d2m_uv, &r->d2m_colors, &r->d2m_pc, &r->d2m_nimg};
@@ -700,6 +792,7 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   for (auto ev : r->chunk_events) cudaEventDestroy(ev);
   if (r->staging) cudaFreeHost(r->staging);
   if (r->counters_host) cudaFreeHost(r->counters_host);
+  if (r->ev_scratch) cudaEventDestroy(r->ev_scratch);
   if (r->stream) cudaStreamDestroy(r->stream);
   if (r->copy_stream) cudaStreamDestroy(r->copy_stream);
   delete r;
@@ -978,6 +1071,7 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   if ((rc = Grow(r, &r->proj, std::max<size_t>(Vpad, 4) * sizeof(float4)))) return cleanup(rc);
   if ((rc = Grow(r, &r->q_face, std::max<size_t>(F, 1) * 4))) return cleanup(rc);
   if ((rc = Grow(r, &r->q_job, std::max<size_t>(F, 1) * 8))) return cleanup(rc);
+  r->scratch_used = false;  // the stream was synchronised above: nothing in flight uses the scratch
   r->mesh = m;
   r->mesh_ready = true;
   return cleanup(UGU_B200_OK);
@@ -1007,10 +1101,10 @@ int ugu_b200_rasterizer_render(ugu_b200_rasterizer* r, const ugu_b200_camera* ca
   ugu_b200_outputs dout;
   if ((rc = EnsureInternalOutputs(r, 0, host_out, P, &dout))) return rc;
   if ((rc = RenderView(r, cam, &dout, r->stream))) return rc;
-  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
                             r->stream));
   std::vector<CopySeg> segs;
-  CollectSegs(host_out, &dout, P, 0, &segs);
+  CollectSegs(host_out, &dout, P, 0, 1, &segs);
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
   SnapshotCounters(r);
   return UGU_B200_OK;
@@ -1114,7 +1208,7 @@ int ugu_b200_rasterizer_render_gbuffer(ugu_b200_rasterizer* r, const ugu_b200_ca
     off += (f.bytes + 255) & ~size_t(255);
   }
   if ((rc = RenderView(r, cam, &dout, r->stream, &gp))) return rc;
-  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
                             r->stream));
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
   SnapshotCounters(r);
@@ -1125,21 +1219,15 @@ namespace {
 // The five kernels of one Raytracer-mode view into device outputs `dout` on stream `st`.
 int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* org_w,
                  const ugu_b200_outputs* dout, cudaStream_t st) {
-  int rc = EnsureFrame(r, cam->width, cam->height, st);
+  int rc = AcquireScratch(r, st);
   if (rc) return rc;
+  if ((rc = EnsureFrame(r, cam->width, cam->height, 1, st))) return rc;
   const size_t P = (size_t)cam->width * cam->height;
   if ((rc = Grow(r, &r->rt_rays, P * 32))) return rc;
-  ViewParams vp;
-  MakeViewParams(cam, &vp);
-  FrameDev fr;
-  fr.proj = (float4*)r->proj.p;
-  fr.ray_dx = (float*)r->ray_dx.p;
-  fr.ray_dy = (float*)r->ray_dy.p;
-  fr.vis = (unsigned long long*)r->vis.p;
-  fr.counters = (unsigned long long*)r->counters.p;
-  fr.q_face = (int*)r->q_face.p;
-  fr.q_job = (unsigned long long*)r->q_job.p;
-  fr.coop_max = 0;
+  ViewBatch<1> vb;
+  MakeViewParams(cam, &vb.v[0]);
+  const ViewParams& vp = vb.v[0];
+  FrameDev fr = MakeFrame(r, cam->width, cam->height);
   const MeshDev& m = r->mesh;
   RtParams rp;
   rp.org[0] = org_w[0];
@@ -1154,25 +1242,9 @@ int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float
   rp.inlane_max = (r->mesh.F >= 4 * 32 * 32 * g_num_sms) ? kRtInLaneMax : 16;
   rp.ray_a = (float4*)r->rt_rays.p;
   rp.ray_b = rp.ray_a + P;
-  ShadeParams sp;
-  sp.diffuse_color = r->opt.diffuse_color;
-  sp.interp = r->opt.interp;
-  sp.shading_normal = r->opt.shading_normal;
-  sp.diffuse_shading = r->opt.diffuse_shading;
-  sp.backface_culling = r->opt.backface_culling;
-  {  // OrenNayarParam (pixel_shader.h:143-148)
-    const float sigma = r->opt.oren_nayar_sigma;
-    const float s2 = sigma * sigma;
-    sp.on_A = 1.0f - (0.5f * s2 / (s2 + 0.33f));
-    sp.on_B = 0.45f * s2 / (s2 + 0.09f);
-  }
-  sp.color = dout->color;
-  sp.depth = dout->depth;
-  sp.normal = dout->normal;
-  sp.mask = dout->mask;
-  sp.face_id = dout->face_id;
+  const ShadeParams sp = MakeShade(r, dout, P);
   const size_t vthreads = std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H);
-  CU_TRY(r, LaunchView(vertex_kernel_1, Blocks(vthreads, 256), 256, st, false, vp, m, fr));
+  CU_TRY(r, LaunchView(vertex_kernel_b<1>, Blocks(vthreads, 256), 256, st, false, vb, 1, m, fr));
   CU_TRY(r, LaunchView(rt_ray_kernel, Blocks(P, 256), 256, st, false, vp, fr, rp));
   int launches = 3;
   if (m.F > 0) {
@@ -1186,7 +1258,7 @@ int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float
   r->stats.kernel_launches += launches;
   r->stats.views++;
   r->stats.h2d_bytes += sizeof(ViewParams) + sizeof(RtParams);
-  return UGU_B200_OK;
+  return ReleaseScratch(r, st);
 }
 }  // namespace
 
@@ -1214,10 +1286,10 @@ int ugu_b200_rasterizer_raytrace(ugu_b200_rasterizer* r, const ugu_b200_camera* 
   ugu_b200_outputs dout;
   if ((rc = EnsureInternalOutputs(r, 0, host_out, P, &dout))) return rc;
   if ((rc = RaytraceView(r, cam, org_w, &dout, r->stream))) return rc;
-  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
                             r->stream));
   std::vector<CopySeg> segs;
-  CollectSegs(host_out, &dout, P, 0, &segs);
+  CollectSegs(host_out, &dout, P, 0, 1, &segs);
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
   SnapshotCounters(r);
   return UGU_B200_OK;
@@ -1235,49 +1307,40 @@ int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
       return Fail(r, UGU_B200_E_INVALID, "all views of a batch must share one image size");
   }
   CU_TRY(r, cudaSetDevice(r->device));
-  const size_t P = (size_t)cams[0].width * cams[0].height;
+  const int W = cams[0].width, H = cams[0].height;
+  const size_t P = (size_t)W * H;
+  const int batch = BatchViews(r, num_views, W, H);
   if (outputs_on_device) {
-    if ((P % 16) != 0) {
-      // per-view offsets keep every pointer 16-byte aligned only when P*1 (mask) is a multiple of 16
-      if (out->mask || out->color)
-        return Fail(r, UGU_B200_E_INVALID,
-                    "device batch with color/mask needs W*H to be a multiple of 16");
-    }
+    // only the bases must be 16-byte aligned: a view slab that is not (odd W*H) is written with scalar stores
+    const uintptr_t align = (uintptr_t)out->color | (uintptr_t)out->depth | (uintptr_t)out->normal |
+                            (uintptr_t)out->mask | (uintptr_t)out->face_id;
+    if (align & 15u) return Fail(r, UGU_B200_E_INVALID, "device outputs must be 16-byte aligned");
     cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
-    for (int i = 0; i < num_views; i++) {
-      ugu_b200_outputs o;
-      o.color = out->color ? out->color + (size_t)i * P * 3 : nullptr;
-      o.depth = out->depth ? out->depth + (size_t)i * P : nullptr;
-      o.normal = out->normal ? out->normal + (size_t)i * P * 3 : nullptr;
-      o.mask = out->mask ? out->mask + (size_t)i * P : nullptr;
-      o.face_id = out->face_id ? out->face_id + (size_t)i * P : nullptr;
-      const uintptr_t align = (uintptr_t)o.color | (uintptr_t)o.depth | (uintptr_t)o.normal |
-                              (uintptr_t)o.mask | (uintptr_t)o.face_id;
-      if (align & 15u) return Fail(r, UGU_B200_E_INVALID, "device outputs must be 16-byte aligned");
-      if ((rc = RenderView(r, &cams[i], &o, st))) return rc;
-    }
-    return UGU_B200_OK;
+    return RenderViews(r, cams, num_views, out, st, batch);
   }
-  // Host destinations.  Pinned: render view i into output set i%2 on the compute stream while the
-  // copy stream drains view i-1 by DMA.  Pageable: staged, one view at a time.
+  // Host destinations: launch sets of `batch` views render into one of two internal output sets on the
+  // compute stream; pinned destinations are drained by DMA on the copy stream while the next set renders
+  // (one copy per output and set: the views of a set are contiguous on both sides), pageable ones through
+  // the staging ring.
   bool all_pinned = true;
   {
     std::vector<CopySeg> probe;
     ugu_b200_outputs none{};
-    CollectSegs(out, &none, P, 0, &probe);
+    CollectSegs(out, &none, P, 0, 1, &probe);
     for (const CopySeg& s : probe) all_pinned = all_pinned && IsPinnedHost(s.dst);
   }
-  for (int i = 0; i < num_views; i++) {
-    const int set = all_pinned ? (i & 1) : 0;
+  int set = 0;
+  for (int i = 0; i < num_views; i += batch, set ^= (all_pinned ? 1 : 0)) {
+    const int k = std::min(batch, num_views - i);
     ugu_b200_outputs dout;
-    if ((rc = EnsureInternalOutputs(r, set, out, P, &dout))) return rc;
+    if ((rc = EnsureInternalOutputs(r, set, out, P * (size_t)batch, &dout))) return rc;
+    if (all_pinned && r->copied_pending[set]) CU_TRY(r, cudaStreamWaitEvent(r->stream, r->ev_copied[set], 0));
+    if ((rc = RenderViews(r, cams + i, k, &dout, r->stream, batch))) return rc;
+    std::vector<CopySeg> segs;
+    CollectSegs(out, &dout, P, (size_t)i, (size_t)k, &segs);
     if (all_pinned) {
-      if (r->copied_pending[set]) CU_TRY(r, cudaStreamWaitEvent(r->stream, r->ev_copied[set], 0));
-      if ((rc = RenderView(r, &cams[i], &dout, r->stream))) return rc;
       CU_TRY(r, cudaEventRecord(r->ev_render[set], r->stream));
       CU_TRY(r, cudaStreamWaitEvent(r->copy_stream, r->ev_render[set], 0));
-      std::vector<CopySeg> segs;
-      CollectSegs(out, &dout, P, (size_t)i, &segs);
       for (const CopySeg& s : segs) {
         r->stats.d2h_bytes += s.bytes;
         CU_TRY(r, cudaMemcpyAsync(s.dst, s.src, s.bytes, cudaMemcpyDeviceToHost, r->copy_stream));
@@ -1285,13 +1348,10 @@ int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
       CU_TRY(r, cudaEventRecord(r->ev_copied[set], r->copy_stream));
       r->copied_pending[set] = true;
     } else {
-      if ((rc = RenderView(r, &cams[i], &dout, r->stream))) return rc;
-      std::vector<CopySeg> segs;
-      CollectSegs(out, &dout, P, (size_t)i, &segs);
       if ((rc = CopyOut(r, segs, r->stream))) return rc;
     }
   }
-  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 16, cudaMemcpyDeviceToHost,
+  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
                             r->stream));
   CU_TRY(r, cudaStreamSynchronize(r->stream));
   CU_TRY(r, cudaStreamSynchronize(r->copy_stream));
@@ -1591,6 +1651,382 @@ int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host
     const unsigned long long b = hb[f];
     if (best_view_host) best_view_host[f] = b ? (int32_t)(0xFFFFFFFFu - (uint32_t)(b & 0xFFFFFFFFull)) : -1;
     if (best_count_host) best_count_host[f] = (uint32_t)(b >> 32);
+  }
+  return UGU_B200_OK;
+}
+
+// ---- keyframe visibility pass (ugu::VisibilityTester) -----------------------------------------------------------
+namespace {
+
+// device layout of the accumulators inside vt_acc (one allocation, 16-byte aligned slices)
+struct VtAccLayout {
+  size_t f_count, f_max_area, f_min_angle, f_min_dist, v_count, v_sum_color, v_sum_ad, v_min_angle, v_min_dist,
+      v_min_colors, total;
+};
+VtAccLayout VtLayout(size_t V, size_t F) {
+  VtAccLayout l{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    const size_t at = off;
+    off += (bytes + 255) & ~size_t(255);
+    return at;
+  };
+  l.f_count = take(F * 4);
+  l.f_max_area = take(F * 8);
+  l.f_min_angle = take(F * 8);
+  l.f_min_dist = take(F * 8);
+  l.v_count = take(V * 4);
+  l.v_sum_color = take(V * 16);
+  l.v_sum_ad = take(V * 8);
+  l.v_min_angle = take(V * 8);
+  l.v_min_dist = take(V * 8);
+  l.v_min_colors = take(V * 8);
+  l.total = off;
+  return l;
+}
+VtAcc VtAccPointers(ugu_b200_rasterizer* r) {
+  const VtAccLayout l = VtLayout((size_t)r->vt_V, (size_t)r->vt_F);
+  char* b = (char*)r->vt_acc.p;
+  VtAcc a;
+  a.f_count = (unsigned*)(b + l.f_count);
+  a.f_max_area = (unsigned long long*)(b + l.f_max_area);
+  a.f_min_angle = (unsigned long long*)(b + l.f_min_angle);
+  a.f_min_dist = (unsigned long long*)(b + l.f_min_dist);
+  a.v_count = (unsigned*)(b + l.v_count);
+  a.v_sum_color = (float4*)(b + l.v_sum_color);
+  a.v_sum_ad = (float2*)(b + l.v_sum_ad);
+  a.v_min_angle = (unsigned long long*)(b + l.v_min_angle);
+  a.v_min_dist = (unsigned long long*)(b + l.v_min_dist);
+  a.v_min_colors = (uint2*)(b + l.v_min_colors);
+  return a;
+}
+
+int VtResetAcc(ugu_b200_rasterizer* r, cudaStream_t st) {
+  const size_t V = (size_t)r->vt_V, F = (size_t)r->vt_F;
+  const VtAccLayout l = VtLayout(V, F);
+  CU_TRY(r, cudaMemsetAsync(r->vt_acc.p, 0, l.total, st));
+  const VtAcc a = VtAccPointers(r);
+  vt_fill_u64<<<Blocks(F, 256), 256, 0, st>>>(a.f_min_angle, F, ~0ull);
+  vt_fill_u64<<<Blocks(F, 256), 256, 0, st>>>(a.f_min_dist, F, ~0ull);
+  vt_fill_u64<<<Blocks(V, 256), 256, 0, st>>>(a.v_min_angle, V, ~0ull);
+  vt_fill_u64<<<Blocks(V, 256), 256, 0, st>>>(a.v_min_dist, V, ~0ull);
+  r->stats.kernel_launches += 4;
+  CU_TRY(r, cudaGetLastError());
+  return UGU_B200_OK;
+}
+
+int VtValidate(ugu_b200_rasterizer* r, int K, const ugu_b200_keyframe* kfs, int first_order,
+               const ugu_b200_vis_option* opt) {
+  if (r->vt_V == 0) return Fail(r, UGU_B200_E_STATE, "mesh has not been initialized");  // :283-286
+  if (K <= 0 || !kfs) return Fail(r, UGU_B200_E_INVALID, "keyframe has not been set");  // :279-282
+  if (!opt) return Fail(r, UGU_B200_E_INVALID, "option is NULL");
+  if (first_order < 0 || (long long)first_order + K > 0x7fffffffll) return Fail(r, UGU_B200_E_INVALID, "bad order");
+  if (opt->interp < 0 || opt->interp > 1) return Fail(r, UGU_B200_E_INVALID, "option enumerator out of range");
+  for (int k = 0; k < K; k++) {
+    const ugu_b200_keyframe& kf = kfs[k];
+    if (kf.cam.width <= 0 || kf.cam.height <= 0 || (long long)kf.cam.width * kf.cam.height >= (1ll << 31))
+      return Fail(r, UGU_B200_E_INVALID, "keyframe %d: camera size %dx%d is invalid", k, kf.cam.width, kf.cam.height);
+    if (!kf.color) return Fail(r, UGU_B200_E_INVALID, "keyframe color is empty");  // :288-291
+    if (opt->use_mask && !kf.mask) return Fail(r, UGU_B200_E_INVALID, "use_mask is true but keyframe mask is empty");
+    if (opt->use_depth && !kf.depth) return Fail(r, UGU_B200_E_INVALID, "use_depth is true but keyframe depth is empty");
+    if (opt->self_occlusion && !kf.zbuf && !r->mesh_ready)
+      return Fail(r, UGU_B200_E_STATE, "self_occlusion without a zbuf needs the mesh uploaded to the rasterizer");
+  }
+  return UGU_B200_OK;
+}
+
+// Core: keyframes with DEVICE images; `rec` = DEVICE record arrays (any NULL).  Launch sets of kVtMaxKeyframes.
+int VtRun(ugu_b200_rasterizer* r, int K, const ugu_b200_keyframe* kfs, int first_order, const ugu_b200_vis_option* o,
+          const ugu_b200_vis_records* rec, cudaStream_t st) {
+  const size_t V = (size_t)r->vt_V, F = (size_t)r->vt_F;
+  int rc;
+  // internal rows for the record arrays the caller does not want
+  if (!rec || !rec->vertex_visible) if ((rc = Grow(r, &r->vt_vvis, kVtMaxKeyframes * V))) return rc;
+  if (!rec || !rec->vertex) if ((rc = Grow(r, &r->vt_vrec, kVtMaxKeyframes * V * sizeof(VtVertexRec)))) return rc;
+  if (!rec || !rec->face_visible) if ((rc = Grow(r, &r->vt_fvis, kVtMaxKeyframes * F))) return rc;
+  if (!rec || !rec->face) if ((rc = Grow(r, &r->vt_frec, kVtMaxKeyframes * F * sizeof(VtFaceRec)))) return rc;
+  if (o->facewise) {
+    const size_t n = kVtMaxKeyframes * V;
+    if ((rc = Grow(r, &r->vt_owner, n * 4))) return rc;
+    if (r->vt_owner_clean < n) {
+      vt_fill_u32<<<Blocks(n, 256), 256, 0, st>>>((unsigned*)r->vt_owner.p, n, kVtNoOwner);
+      r->stats.kernel_launches++;
+      r->vt_owner_clean = n;
+    }
+  }
+  VtOption vo;
+  vo.backface_culling_angle_rad_th = o->backface_culling_angle_rad_th;
+  vo.use_mask = o->use_mask;
+  vo.use_depth = o->use_depth;
+  vo.interp = o->interp;
+  vo.max_viewing_angle = o->max_viewing_angle;
+  vo.max_distance = o->max_distance_from_camera_to_vertex;
+  vo.max_depth_difference = o->max_depth_difference;
+  vo.eps = o->eps;
+  VtMesh m;
+  m.V = r->vt_V;
+  m.F = r->vt_F;
+  m.pos = (const float*)r->vt_pos.p;
+  m.nrm = (const float*)r->vt_nrm.p;
+  m.idx = (const int*)r->vt_idx.p;
+  const VtAcc acc = VtAccPointers(r);
+  for (int k0 = 0; k0 < K; k0 += kVtMaxKeyframes) {
+    const int nk = std::min((int)kVtMaxKeyframes, K - k0);
+    // self depth maps the caller did not supply: one depth-only batch render with back-face culling off
+    const float* zbuf[kVtMaxKeyframes] = {};
+    if (o->self_occlusion) {
+      std::vector<ugu_b200_camera> cams;
+      std::vector<int> slot;
+      for (int k = 0; k < nk; k++) {
+        zbuf[k] = kfs[k0 + k].zbuf;
+        if (!zbuf[k]) {
+          cams.push_back(kfs[k0 + k].cam);
+          slot.push_back(k);
+        }
+      }
+      if (!cams.empty()) {
+        const ugu_b200_option saved = r->opt;
+        r->opt.diffuse_color = UGU_B200_COLOR_NONE;
+        r->opt.diffuse_shading = UGU_B200_SHADING_NONE;
+        r->opt.backface_culling = 0;
+        size_t off = 0;
+        std::vector<size_t> offs;
+        for (const ugu_b200_camera& c : cams) {
+          offs.push_back(off);
+          off += (((size_t)c.width * c.height * 4) + 255) & ~size_t(255);
+        }
+        rc = Grow(r, &r->vt_zbuf, off + 256);
+        for (size_t i = 0; i < cams.size() && !rc; i++) {
+          ugu_b200_outputs d{};
+          d.depth = (float*)((char*)r->vt_zbuf.p + offs[i]);
+          // consecutive cameras of one size render as one launch set
+          size_t j = i + 1;
+          const size_t P = (size_t)cams[i].width * cams[i].height;
+          while (j < cams.size() && cams[j].width == cams[i].width && cams[j].height == cams[i].height &&
+                 (P * 4) % 256 == 0)
+            j++;
+          rc = Validate(r, &cams[i], &d);
+          if (!rc) rc = RenderViews(r, &cams[i], (int)(j - i), &d, st, (int)(j - i));
+          i = j - 1;
+        }
+        r->opt = saved;
+        if (rc) return rc;
+        for (size_t i = 0; i < slot.size(); i++) zbuf[slot[i]] = (const float*)((char*)r->vt_zbuf.p + offs[i]);
+      }
+    }
+    VtBatch kb;
+    memset(&kb, 0, sizeof(kb));
+    for (int k = 0; k < nk; k++) {
+      const ugu_b200_keyframe& s = kfs[k0 + k];
+      VtKeyframe& d = kb.k[k];
+      d.cam.W = s.cam.width;
+      d.cam.H = s.cam.height;
+      d.cam.fx = s.cam.fx;
+      d.cam.fy = s.cam.fy;
+      d.cam.cx = s.cam.cx;
+      d.cam.cy = s.cam.cy;
+      memcpy(d.cam.w2c, s.w2c, sizeof(d.cam.w2c));
+      memcpy(d.cam.c2w_R, s.cam.c2w_R, sizeof(d.cam.c2w_R));
+      d.color = s.color;
+      d.depth = s.depth;
+      d.mask = s.mask;
+      d.zbuf = zbuf[k];
+      d.order = (unsigned)(first_order + k0 + k);
+    }
+    VtOut out;
+    out.row0 = 0;
+    out.v_visible = (rec && rec->vertex_visible) ? rec->vertex_visible + (size_t)k0 * V : (uint8_t*)r->vt_vvis.p;
+    out.v_rec = (rec && rec->vertex) ? (VtVertexRec*)rec->vertex + (size_t)k0 * V : (VtVertexRec*)r->vt_vrec.p;
+    out.f_visible = (rec && rec->face_visible) ? rec->face_visible + (size_t)k0 * F : (uint8_t*)r->vt_fvis.p;
+    out.f_rec = (rec && rec->face) ? (VtFaceRec*)rec->face + (size_t)k0 * F : (VtFaceRec*)r->vt_frec.p;
+    out.owner = (unsigned*)r->vt_owner.p;
+    const dim3 gv(Blocks(V, 256), (unsigned)nk), gf(Blocks(F, 256), (unsigned)nk);
+    if (o->facewise) {
+      vt_facewise_kernel<<<gf, 256, 0, st>>>(kb, vo, m, out);
+      vt_owner_kernel<<<gv, 256, 0, st>>>(kb, vo, m, out);
+    } else {
+      vt_vertex_kernel<<<gv, 256, 0, st>>>(kb, vo, m, out);
+      vt_face_kernel<<<gf, 256, 0, st>>>(m, out);
+    }
+    vt_fold_face_kernel<<<Blocks(F, 256), 256, 0, st>>>(kb, nk, m, out, acc);
+    vt_fold_vertex_kernel<<<Blocks(V, 256), 256, 0, st>>>(kb, nk, m, out, acc);
+    r->stats.kernel_launches += 4;
+    CU_TRY(r, cudaGetLastError());
+  }
+  return UGU_B200_OK;
+}
+
+}  // namespace
+
+int ugu_b200_visibility_set_data(ugu_b200_rasterizer* r, int32_t V, const float* vertices, const float* normals,
+                                 int32_t F, const int32_t* indices) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  r->vt_V = r->vt_F = 0;
+  if (V <= 0 || F <= 0 || !vertices || !normals || !indices) return Fail(r, UGU_B200_E_INVALID, "mesh is empty");  // :237-240
+  if (!IndicesInRange(indices, (size_t)F * 3, V))
+    return Fail(r, UGU_B200_E_INVALID, "indices reference a vertex outside [0, %d)", V);
+  if ((unsigned long long)F >= (1ull << 30)) return Fail(r, UGU_B200_E_INVALID, "too many faces");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = r->stream;
+  int rc;
+  if ((rc = Grow(r, &r->vt_pos, (size_t)V * 12))) return rc;
+  if ((rc = Grow(r, &r->vt_nrm, (size_t)V * 12))) return rc;
+  if ((rc = Grow(r, &r->vt_idx, (size_t)F * 12))) return rc;
+  if ((rc = Grow(r, &r->vt_acc, VtLayout((size_t)V, (size_t)F).total))) return rc;
+  CU_TRY(r, cudaMemcpyAsync(r->vt_pos.p, vertices, (size_t)V * 12, cudaMemcpyHostToDevice, st));
+  CU_TRY(r, cudaMemcpyAsync(r->vt_nrm.p, normals, (size_t)V * 12, cudaMemcpyHostToDevice, st));
+  CU_TRY(r, cudaMemcpyAsync(r->vt_idx.p, indices, (size_t)F * 12, cudaMemcpyHostToDevice, st));
+  r->stats.h2d_bytes += (size_t)V * 24 + (size_t)F * 12;
+  r->vt_V = V;
+  r->vt_F = F;
+  r->vt_owner_clean = 0;
+  if ((rc = VtResetAcc(r, st))) return rc;
+  CU_TRY(r, cudaStreamSynchronize(st));  // the host arrays may go away
+  return UGU_B200_OK;
+}
+
+int ugu_b200_visibility_reset(ugu_b200_rasterizer* r) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  if (r->vt_V == 0) return Fail(r, UGU_B200_E_STATE, "mesh has not been initialized");
+  CU_TRY(r, cudaSetDevice(r->device));
+  return VtResetAcc(r, r->stream);
+}
+
+int ugu_b200_visibility_test_device(ugu_b200_rasterizer* r, int32_t K, const ugu_b200_keyframe* kfs,
+                                    int32_t first_order, const ugu_b200_vis_option* opt,
+                                    const ugu_b200_vis_records* rec, void* stream) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  int rc = VtValidate(r, K, kfs, first_order, opt);
+  if (rc) return rc;
+  if (rec && ((uintptr_t)rec->vertex & 15u)) return Fail(r, UGU_B200_E_INVALID, "vertex records must be 16-byte aligned");
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = stream ? (cudaStream_t)stream : r->stream;
+  if ((rc = AcquireScratch(r, st))) return rc;
+  if ((rc = VtRun(r, K, kfs, first_order, opt, rec, st))) return rc;
+  return ReleaseScratch(r, st);
+}
+
+int ugu_b200_visibility_test(ugu_b200_rasterizer* r, int32_t K, const ugu_b200_keyframe* kfs, int32_t first_order,
+                             const ugu_b200_vis_option* opt, const ugu_b200_vis_records* rec) {
+  if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
+  int rc = VtValidate(r, K, kfs, first_order, opt);
+  if (rc) return rc;
+  CU_TRY(r, cudaSetDevice(r->device));
+  cudaStream_t st = r->stream;
+  if ((rc = AcquireScratch(r, st))) return rc;
+  const size_t V = (size_t)r->vt_V, F = (size_t)r->vt_F;
+  const bool want = rec && (rec->vertex_visible || rec->vertex || rec->face_visible || rec->face);
+  // keyframes go through the device in launch sets: upload the set's images, run, copy its records back
+  for (int k0 = 0; k0 < K; k0 += kVtMaxKeyframes) {
+    const int nk = std::min((int)kVtMaxKeyframes, K - k0);
+    size_t bytes = 0;
+    for (int k = 0; k < nk; k++) {
+      const size_t P = (size_t)kfs[k0 + k].cam.width * kfs[k0 + k].cam.height;
+      bytes += ((P * 3 + 255) & ~size_t(255)) + ((P * 4 + 255) & ~size_t(255)) * 2 + ((P + 255) & ~size_t(255));
+    }
+    if ((rc = Grow(r, &r->vt_img, bytes))) return rc;
+    std::vector<ugu_b200_keyframe> dk(kfs + k0, kfs + k0 + nk);
+    size_t off = 0;
+    auto up = [&](const void* host, size_t n) -> const void* {
+      if (!host) return nullptr;
+      void* d = (char*)r->vt_img.p + off;
+      off += (n + 255) & ~size_t(255);
+      if (cudaMemcpyAsync(d, host, n, cudaMemcpyHostToDevice, st) != cudaSuccess) return nullptr;
+      r->stats.h2d_bytes += n;
+      return d;
+    };
+    for (int k = 0; k < nk; k++) {
+      const size_t P = (size_t)dk[k].cam.width * dk[k].cam.height;
+      dk[k].color = (const uint8_t*)up(kfs[k0 + k].color, P * 3);
+      dk[k].depth = (const float*)up(opt->use_depth ? kfs[k0 + k].depth : nullptr, P * 4);
+      dk[k].mask = (const uint8_t*)up(opt->use_mask ? kfs[k0 + k].mask : nullptr, P);
+      dk[k].zbuf = (const float*)up(opt->self_occlusion ? kfs[k0 + k].zbuf : nullptr, P * 4);
+    }
+    CU_TRY(r, cudaGetLastError());
+    if ((rc = VtRun(r, nk, dk.data(), first_order + k0, opt, nullptr, st))) return rc;
+    if (want) {
+      std::vector<CopySeg> segs;
+      if (rec->vertex_visible) segs.push_back({rec->vertex_visible + (size_t)k0 * V, r->vt_vvis.p, (size_t)nk * V});
+      if (rec->vertex) segs.push_back({rec->vertex + (size_t)k0 * V, r->vt_vrec.p, (size_t)nk * V * sizeof(VtVertexRec)});
+      if (rec->face_visible) segs.push_back({rec->face_visible + (size_t)k0 * F, r->vt_fvis.p, (size_t)nk * F});
+      if (rec->face) segs.push_back({rec->face + (size_t)k0 * F, r->vt_frec.p, (size_t)nk * F * sizeof(VtFaceRec)});
+      if ((rc = CopyOut(r, segs, st))) return rc;
+    } else {
+      CU_TRY(r, cudaStreamSynchronize(st));  // the image scratch is reused by the next set
+    }
+  }
+  return ReleaseScratch(r, st);
+}
+
+int ugu_b200_visibility_accumulators(ugu_b200_rasterizer* r, ugu_b200_vis_accumulators* out) {
+  if (!r || !out) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (r->vt_V == 0) return Fail(r, UGU_B200_E_STATE, "mesh has not been initialized");
+  const VtAcc a = VtAccPointers(r);
+  out->face_count = a.f_count;
+  out->face_max_area = (uint64_t*)a.f_max_area;
+  out->face_min_angle = (uint64_t*)a.f_min_angle;
+  out->face_min_dist = (uint64_t*)a.f_min_dist;
+  out->vertex_count = a.v_count;
+  out->vertex_sum_color = (float*)a.v_sum_color;
+  out->vertex_sum_angle_dist = (float*)a.v_sum_ad;
+  out->vertex_min_angle = (uint64_t*)a.v_min_angle;
+  out->vertex_min_dist = (uint64_t*)a.v_min_dist;
+  out->vertex_min_colors = (uint32_t*)a.v_min_colors;
+  return UGU_B200_OK;
+}
+
+int ugu_b200_visibility_stats(ugu_b200_rasterizer* r, const ugu_b200_vis_stats* o) {
+  if (!r || !o) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (r->vt_V == 0) return Fail(r, UGU_B200_E_STATE, "mesh has not been initialized");
+  CU_TRY(r, cudaSetDevice(r->device));
+  const size_t V = (size_t)r->vt_V, F = (size_t)r->vt_F;
+  const VtAccLayout l = VtLayout(V, F);
+  std::vector<char> host(l.total);
+  if (r->scratch_used) CU_TRY(r, cudaEventSynchronize(r->ev_scratch));
+  CU_TRY(r, cudaMemcpy(host.data(), r->vt_acc.p, l.total, cudaMemcpyDeviceToHost));
+  r->stats.d2h_bytes += l.total;
+  const unsigned* fc = (const unsigned*)(host.data() + l.f_count);
+  const unsigned long long* fa = (const unsigned long long*)(host.data() + l.f_max_area);
+  const unsigned long long* fg = (const unsigned long long*)(host.data() + l.f_min_angle);
+  const unsigned long long* fd = (const unsigned long long*)(host.data() + l.f_min_dist);
+  auto f32 = [](unsigned long long key) {
+    const unsigned u = (unsigned)(key >> 32);
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+  };
+  for (size_t f = 0; f < F; f++) {
+    const bool any = fc[f] != 0;
+    if (o->face_count) o->face_count[f] = fc[f];
+    if (o->face_max_area_order) o->face_max_area_order[f] = any ? (int32_t)(0xFFFFFFFFu - (unsigned)fa[f]) : -1;
+    if (o->face_min_viewing_angle_order) o->face_min_viewing_angle_order[f] = any ? (int32_t)(unsigned)fg[f] : -1;
+    if (o->face_min_distance_order) o->face_min_distance_order[f] = any ? (int32_t)(unsigned)fd[f] : -1;
+    if (o->face_max_area) o->face_max_area[f] = any ? f32(fa[f]) : 0.f;
+    if (o->face_min_viewing_angle) o->face_min_viewing_angle[f] = any ? f32(fg[f]) : 0.f;
+    if (o->face_min_distance) o->face_min_distance[f] = any ? f32(fd[f]) : 0.f;
+  }
+  const unsigned* vc = (const unsigned*)(host.data() + l.v_count);
+  const float* sc = (const float*)(host.data() + l.v_sum_color);
+  const float* sad = (const float*)(host.data() + l.v_sum_ad);
+  const unsigned long long* vg = (const unsigned long long*)(host.data() + l.v_min_angle);
+  const unsigned long long* vd = (const unsigned long long*)(host.data() + l.v_min_dist);
+  const unsigned* mc = (const unsigned*)(host.data() + l.v_min_colors);
+  for (size_t v = 0; v < V; v++) {
+    const bool any = vc[v] != 0;
+    const float n = (float)vc[v];
+    if (o->vertex_count) o->vertex_count[v] = vc[v];
+    if (o->vertex_min_viewing_angle_order) o->vertex_min_viewing_angle_order[v] = any ? (int32_t)(unsigned)vg[v] : -1;
+    if (o->vertex_min_distance_order) o->vertex_min_distance_order[v] = any ? (int32_t)(unsigned)vd[v] : -1;
+    for (int c = 0; c < 3; c++) {
+      // mean_color /= static_cast<float>(size) (visibility_tester.cc:80)
+      if (o->vertex_mean_color) o->vertex_mean_color[v * 3 + c] = any ? sc[v * 4 + c] / n : 0.f;
+      if (o->vertex_min_viewing_angle_color)
+        o->vertex_min_viewing_angle_color[v * 3 + c] = any ? (float)((mc[v * 2] >> (8 * c)) & 255u) : 0.f;
+      if (o->vertex_min_distance_color)
+        o->vertex_min_distance_color[v * 3 + c] = any ? (float)((mc[v * 2 + 1] >> (8 * c)) & 255u) : 0.f;
+    }
+    if (o->vertex_mean_viewing_angle) o->vertex_mean_viewing_angle[v] = any ? sad[v * 2] / n : 0.f;
+    if (o->vertex_mean_distance) o->vertex_mean_distance[v] = any ? sad[v * 2 + 1] / n : 0.f;
   }
   return UGU_B200_OK;
 }

@@ -49,6 +49,15 @@ struct ViewParams {
   float c2w_R[9];
 };
 
+// A batch of views rendered by ONE launch set (blockIdx.y = view of the batch; the vertex kernel loops
+// over the views itself).  The parameter blocks travel as a kernel-parameter array: indexing it with
+// the CTA-uniform view index compiles to LDCU c[0x0][UR + offset] — constant-bank speed, no local copy.
+constexpr int kMaxBatch = 16;
+template <int NV>
+struct ViewBatch {
+  ViewParams v[NV];
+};
+
 struct MeshDev {
   int V, F;
   int num_normals, num_colors, num_face_normals, num_uv, num_materials;
@@ -81,7 +90,28 @@ struct FrameDev {
   int* q_face;                   // F
   unsigned long long* q_job;     // F : first tile job of each queued triangle
   int coop_max;                  // bbox sample count up to which a triangle takes the cooperative path
+  // element strides between the per-view slabs of a batch (view v uses base + v * stride); the
+  // counters slab of a view is 8 words: [0] packed large queue counter, [1] hazard fragments, [2] chunk
+  // cursor, [4] / [5] the view's (queue, hazards) as saved by resolve_kernel for the host.  Word 6 of
+  // slab 0: hazard fragments summed over every view since the handle was created (never reset; the
+  // host reports deltas).
+  unsigned long long s_proj, s_ray_dx, s_ray_dy, s_vis, s_q;
 };
+constexpr int kCounterSlab = 8;
+constexpr int kTotalsOffset = 6;
+
+__device__ __forceinline__ FrameDev frame_view(const FrameDev& b, int view) {
+  FrameDev f = b;
+  const unsigned long long v = (unsigned long long)view;
+  f.proj = b.proj + v * b.s_proj;
+  f.ray_dx = b.ray_dx + v * b.s_ray_dx;
+  f.ray_dy = b.ray_dy + v * b.s_ray_dy;
+  f.vis = b.vis + v * b.s_vis;
+  f.counters = b.counters + v * (unsigned long long)kCounterSlab;
+  f.q_face = b.q_face + v * b.s_q;
+  f.q_job = b.q_job + v * b.s_q;
+  return f;
+}
 
 struct ShadeParams {
   int diffuse_color, interp, shading_normal, diffuse_shading, backface_culling;
@@ -91,7 +121,21 @@ struct ShadeParams {
   float* normal;
   uint8_t* mask;
   int* face_id;
+  // batch: view v of the launch set writes at element offset (first_view + v) * view_pixels of every output
+  unsigned long long view_pixels;
+  unsigned first_view;
 };
+
+__device__ __forceinline__ ShadeParams shade_view(const ShadeParams& b, int view) {
+  ShadeParams s = b;
+  const unsigned long long off = (unsigned long long)(b.first_view + (unsigned)view) * b.view_pixels;
+  if (b.color) s.color = b.color + off * 3ull;
+  if (b.depth) s.depth = b.depth + off;
+  if (b.normal) s.normal = b.normal + off * 3ull;
+  if (b.mask) s.mask = b.mask + off;
+  if (b.face_id) s.face_id = b.face_id + off;
+  return s;
+}
 
 // ---------------------------------------------------------------------------------------------
 // Exact-order float helpers (Eigen fixed-size reduction order: a0*b0 + (a1*b1 + a2*b2)).
@@ -199,7 +243,7 @@ __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis,
 
 // ---------------------------------------------------------------------------------------------
 // K1: vertex transform + projection (rasterizer.cc:125-136, camera.h:380-387) and the per-view ray
-// numerator tables.  4 vertices per thread, float4 SoA loads, float4 AoS stores.
+// numerator tables.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ float4 project_vertex(const ViewParams& vp, float x, float y, float z) {
   float px = dot3(vp.w2c_R[0], vp.w2c_R[1], vp.w2c_R[2], x, y, z);
@@ -216,48 +260,30 @@ __device__ __forceinline__ float4 project_vertex(const ViewParams& vp, float x, 
   return o;
 }
 
-__global__ void __launch_bounds__(256) vertex_kernel(const ViewParams vp, const MeshDev m,
-                                                     const FrameDev fr) {
-  pdl_launch_dependents();
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int v = t * 4;
-  if (v + 3 < m.V) {
-    // the mesh is immutable: its loads may precede the wait on the previous view's kernels
-    const float4 x = __ldg(reinterpret_cast<const float4*>(m.pos_x + v));
-    const float4 y = __ldg(reinterpret_cast<const float4*>(m.pos_y + v));
-    const float4 z = __ldg(reinterpret_cast<const float4*>(m.pos_z + v));
-    pdl_wait();
-    fr.proj[v + 0] = project_vertex(vp, x.x, y.x, z.x);
-    fr.proj[v + 1] = project_vertex(vp, x.y, y.y, z.y);
-    fr.proj[v + 2] = project_vertex(vp, x.z, y.z, z.z);
-    fr.proj[v + 3] = project_vertex(vp, x.w, y.w, z.w);
-  } else {
-    pdl_wait();
-    for (int k = v; k < m.V; k++)
-      fr.proj[k] = project_vertex(vp, __ldg(m.pos_x + k), __ldg(m.pos_y + k), __ldg(m.pos_z + k));
-  }
-  // ray tables: the first W + H threads
-  if (t < vp.W) fr.ray_dx[t] = ((float)t - vp.cx) / vp.fx;
-  else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
-}
-
-// One vertex per thread: 4x the warps of vertex_kernel for the same bytes (the kernel is a few
-// microseconds of pure latency at mesh sizes that fit one wave), fully coalesced 4-byte loads and
-// 16-byte stores.
-__global__ void __launch_bounds__(256) vertex_kernel_1(const ViewParams vp, const MeshDev m,
-                                                       const FrameDev fr) {
+// One vertex per thread (fully coalesced 4-byte loads, 16-byte stores; the kernel is a few
+// microseconds of pure latency at mesh sizes that fit one wave).  A batch loads every position once
+// and projects it through each view of the batch: 12 bytes in, 16 bytes out per (vertex, view).
+template <int NV>
+__global__ void __launch_bounds__(256) vertex_kernel_b(const ViewBatch<NV> vb, const int nviews,
+                                                       const MeshDev m, const FrameDev fr) {
   pdl_launch_dependents();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   float x = 0.f, y = 0.f, z = 0.f;
-  if (t < m.V) {
+  if (t < m.V) {  // the mesh is immutable: its loads may precede the wait on the previous batch's kernels
     x = __ldg(m.pos_x + t);
     y = __ldg(m.pos_y + t);
     z = __ldg(m.pos_z + t);
   }
   pdl_wait();
-  if (t < m.V) fr.proj[t] = project_vertex(vp, x, y, z);
-  if (t < vp.W) fr.ray_dx[t] = ((float)t - vp.cx) / vp.fx;
-  else if (t < vp.W + vp.H) fr.ray_dy[t - vp.W] = ((float)(t - vp.W) - vp.cy) / vp.fy;
+  const int n = (NV == 1) ? 1 : nviews;
+  for (int v = 0; v < n; v++) {
+    const ViewParams& vp = vb.v[v];
+    if (t < m.V) fr.proj[(unsigned long long)v * fr.s_proj + t] = project_vertex(vp, x, y, z);
+    // ray tables: the first W + H threads
+    if (t < vp.W) fr.ray_dx[(unsigned long long)v * fr.s_ray_dx + t] = ((float)t - vp.cx) / vp.fx;
+    else if (t < vp.W + vp.H)
+      fr.ray_dy[(unsigned long long)v * fr.s_ray_dy + (t - vp.W)] = ((float)(t - vp.W) - vp.cy) / vp.fy;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -389,9 +415,12 @@ __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const Mes
   }
 }
 
-template <int HALVES, int MINB>
-__global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewParams vp, const MeshDev m,
-                                                        const FrameDev fr) {
+template <int HALVES, int MINB, int NV>
+__global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> vb, const MeshDev m,
+                                                           const FrameDev fr0) {
+  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
+  const ViewParams& vp = vb.v[view];
+  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
   __shared__ WarpTris<HALVES> sh[8];
   WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
   const unsigned lane = threadIdx.x & 31u;
@@ -580,8 +609,12 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewParams vp, 
 // 32-ary search, then walks entries; a job is an 8x4 pixel block of the triangle's bbox, one lane
 // per pixel.  Persistent grid (multiple of the SM count); exits at once when the queue is empty.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) binned_kernel(const ViewParams vp, const MeshDev m,
-                                                     const FrameDev fr) {
+template <int NV>
+__global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, const MeshDev m,
+                                                     const FrameDev fr0) {
+  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
+  const ViewParams& vp = vb.v[view];
+  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
   pdl_launch_dependents();
   pdl_wait();
   const unsigned long long packed = fr.counters[0];
@@ -925,9 +958,18 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
 // vertices (and uvs) of chunk i+1, the face record of chunk i+2 and the key of chunk i+3 are in
 // flight, so of the dependent chain key -> face record -> projected vertices / attributes -> texels
 // only the last links are exposed, and those overlap the weight arithmetic of the same chunk.
-template <int COLOR, int NMODE, int MINB, bool DEEP>
-__global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewParams vp, const MeshDev m,
-                                                            const FrameDev fr, const ShadeParams sp) {
+template <int COLOR, int NMODE, int MINB, bool DEEP, int NV>
+__global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> vb, const MeshDev m,
+                                                            const FrameDev fr0, const ShadeParams sp0) {
+  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
+  const ViewParams& vp = vb.v[view];
+  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
+  // (the single-view instantiation is only launched with first_view == 0: everything stays in the constant bank)
+  const ShadeParams sp = (NV == 1) ? sp0 : shade_view(sp0, view);
+  // full-width vector stores need the view's slab of every output 16-byte aligned: the bases are (validated
+  // by the host), so every slab is when W*H is a multiple of 16; other slabs take the scalar stores
+  const bool vec_ok =
+      (NV == 1) || ((((unsigned long long)(sp0.first_view + (unsigned)view) * sp0.view_pixels) & 15ull) == 0ull);
   __shared__ __align__(16) float s_n[8][96];
   __shared__ __align__(16) unsigned char s_c[8][96];
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;  // W*H < 2^31 is validated by the host
@@ -941,6 +983,7 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewParams vp,
     // reset them for the next view
     fr.counters[4] = fr.counters[0];
     fr.counters[5] = fr.counters[1];
+    if (fr.counters[1] != 0ull) atomicAdd(fr0.counters + kTotalsOffset, fr.counters[1]);
     fr.counters[0] = 0ull;
     fr.counters[1] = 0ull;
     fr.counters[2] = 0ull;
@@ -966,7 +1009,7 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewParams vp,
     const unsigned p = wbase + lane;
     const unsigned y = (vp.W == 1) ? p : (__umulhi(p, vp.w_magic) >> vp.w_shift);
     const unsigned x = p - y * (unsigned)vp.W;
-    if (wbase + 32u <= P && __all_sync(0xffffffffu, a.key == kVisEmpty)) {
+    if (vec_ok && wbase + 32u <= P && __all_sync(0xffffffffu, a.key == kVisEmpty)) {
       // Nothing landed on these 32 pixels (most of a typical frame): write the cleared values
       // (util_private.cc:72-87) with full-width stores and move on.
       if (sp.depth) sp.depth[p] = 0.0f;
@@ -985,7 +1028,7 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewParams vp,
     PixelOut o;
     resolve_pixel<COLOR, NMODE>(vp, m, fr, sp, a, (int)x, (int)y, o);
 
-    if (wbase + 32u <= P) {
+    if (vec_ok && wbase + 32u <= P) {
       if (sp.depth) sp.depth[p] = o.depth;
       if (sp.face_id) sp.face_id[p] = o.face_id;
       if (sp.mask) {

@@ -11,6 +11,7 @@ The model of the loop being replaced is the reference's sequential orbit loop
 """
 from __future__ import annotations
 
+import contextlib
 from typing import Callable, List, Optional, Sequence
 
 import torch
@@ -138,6 +139,7 @@ class MultiViewRenderer:
         self.group = group
         self._render_local = render_local or self._render_local_cuda
         self._accumulate = accumulate or self._accumulate_cuda
+        self._stream = None  # side stream of the CUDA path, see _on_work_stream
 
     def _render_local_cuda(self, cameras: Sequence, outputs: Sequence[str]):
         if self.rasterizer is None:
@@ -146,7 +148,6 @@ class MultiViewRenderer:
         if n == 0:
             return {}
         w, h = cameras[0].width(), cameras[0].height()
-        P = w * h
         spec = dict(color=(torch.uint8, 3), depth=(torch.float32, 1), normal=(torch.float32, 3),
                     mask=(torch.uint8, 1), face_id=(torch.int32, 1))
         dev = {}
@@ -154,19 +155,27 @@ class MultiViewRenderer:
             dt, ch = spec[k]
             shape = (n, h, w) if ch == 1 else (n, h, w, ch)
             dev[k] = torch.empty(shape, dtype=dt, device="cuda")
-        stream = torch.cuda.current_stream().cuda_stream
-        if (P % 16) == 0 or not ({"color", "mask"} & set(outputs)):
+        with self._on_work_stream() as stream:
+            # view slabs that are not 16-byte aligned (odd W*H) are handled inside the library
             self.rasterizer.render_batch(list(cameras), on_device=True, stream=stream,
                                          **{k: v.data_ptr() for k, v in dev.items()})
-        else:  # odd sizes: per-view pointers would lose their 16-byte alignment -> one view at a time
-            for i, cam in enumerate(cameras):
-                tmp = {k: torch.empty_like(v[0]) for k, v in dev.items()}
-                self.rasterizer.render_device(cam, stream=stream, **{k: v.data_ptr() for k, v in tmp.items()})
-                for k in dev:
-                    dev[k][i].copy_(tmp[k])
-        if stream == 0:
-            self.rasterizer.sync()  # handle 0 = the rasterizer's own stream
         return dev
+
+    @contextlib.contextmanager
+    def _on_work_stream(self):
+        """The library is never handed stream handle 0 from torch code (to the C-ABI, 0 means "the
+        rasterizer's own stream", which torch knows nothing about): the work runs on a real side stream that
+        first waits for torch's current stream (allocations, zero fills, earlier consumers) and that the
+        current stream waits for afterwards, so whatever follows on torch's side — a collective, a decode,
+        a copy to the host — is ordered after the library's kernels."""
+        cur = torch.cuda.current_stream()
+        if self._stream is None:
+            self._stream = torch.cuda.Stream()
+        self._stream.wait_stream(cur)
+        try:
+            yield self._stream.cuda_stream
+        finally:
+            cur.wait_stream(self._stream)
 
     def local_indices(self, num_views: int) -> List[int]:
         world, rank = _world_rank(self.group)
@@ -205,9 +214,10 @@ class MultiViewRenderer:
         if self.rasterizer is None:
             raise RuntimeError("face visibility needs a ugu_b200.Rasterizer (there is no CPU fallback)")
         n = maps.shape[0]
-        self.rasterizer.face_visibility_device(
-            maps.data_ptr(), n, maps[0].numel(), num_faces, pix.data_ptr(), views.data_ptr(),
-            best.data_ptr(), first_view_id, torch.cuda.current_stream().cuda_stream)
+        with self._on_work_stream() as stream:
+            self.rasterizer.face_visibility_device(
+                maps.data_ptr(), n, maps[0].numel(), num_faces, pix.data_ptr(), views.data_ptr(),
+                best.data_ptr(), first_view_id, stream)
 
     def render_and_gather(self, cameras: Sequence, output: str = "face_id", dst: int = 0):
         """Render, then gather one output of every view to rank `dst` in global view order."""

@@ -171,37 +171,34 @@ class PinholeCamera:
         return cam
 
 
-def pinned_empty(shape, dtype) -> np.ndarray:
-    """A numpy array over pinned host memory from the C-ABI (so Render's D2H is one DMA)."""
-    lib = N.load()
-    dtype = np.dtype(dtype)
-    nbytes = int(np.prod(shape)) * dtype.itemsize
-    ptr = lib.ugu_b200_host_alloc(max(nbytes, 1))
-    if not ptr:
-        raise MemoryError(N.last_error())
-    buf = (C.c_uint8 * max(nbytes, 1)).from_address(ptr)
-    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+class _PinnedBlock:
+    """Owner of one cudaHostAlloc block, exposed to numpy through __array_interface__: every array / view
+    made from it keeps it alive through `.base`, and the block is freed when the last one is gone."""
 
-    class _Owner:
-        def __init__(self, p):
-            self.p = p
+    def __init__(self, lib, nbytes: int):
+        self._lib = lib
+        self.ptr = lib.ugu_b200_host_alloc(max(nbytes, 1))
+        if not self.ptr:
+            raise MemoryError(N.last_error())
+        self.__array_interface__ = {"shape": (max(nbytes, 1),), "typestr": "|u1", "data": (self.ptr, False),
+                                    "version": 3}
 
-        def __del__(self):
+    def __del__(self):
+        ptr, self.ptr = getattr(self, "ptr", None), None
+        if ptr:
             try:
-                lib.ugu_b200_host_free(self.p)
+                self._lib.ugu_b200_host_free(ptr)
             except Exception:
                 pass
 
-    _PINNED_OWNERS[ptr] = _Owner(ptr)
-    return arr
 
-
-_PINNED_OWNERS: dict = {}
-
-
-def free_pinned(arr: np.ndarray) -> None:
-    ptr = arr.ctypes.data
-    _PINNED_OWNERS.pop(ptr, None)
+def pinned_empty(shape, dtype) -> np.ndarray:
+    """A numpy array over pinned host memory from the C-ABI (so Render's D2H is one DMA).  The memory
+    lives exactly as long as the array and the views taken from it."""
+    dtype = np.dtype(dtype)
+    count = int(np.prod(shape))
+    raw = np.asarray(_PinnedBlock(N.load(), count * dtype.itemsize))
+    return raw[: count * dtype.itemsize].view(dtype).reshape(shape)
 
 
 class Image:
@@ -222,8 +219,6 @@ class Image:
     def _init(self, width: int, height: int) -> None:
         if self.cols != width or self.rows != height:
             shape = (height, width) if self.channels == 1 else (height, width, self.channels)
-            if self.pinned and self.data.size:
-                free_pinned(self.data)
             self.data = pinned_empty(shape, self.dtype) if self.pinned else np.empty(shape, self.dtype)
             self.rows, self.cols = height, width
 
@@ -406,7 +401,9 @@ class Rasterizer:
         if depth is None:  # rasterizer.cc:331-334
             LOGE("depth is nullptr")
             return False
-        f_depth = Image1f()
+        f_depth = getattr(self, "_w_depth", None)  # one scratch image per renderer, not one per call
+        if f_depth is None:
+            f_depth = self._w_depth = Image1f()
         ok = self.Render(color, f_depth, normal, mask, face_id)
         if ok:
             depth._init(f_depth.cols, f_depth.rows)
