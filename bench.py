@@ -117,16 +117,21 @@ class ClockSampler:
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def time_reference(mesh, opt, cams, steps, warmup, budget_s=None):
+def time_reference(mesh, opt, cams, steps, warmup, budget_s=None, split=False):
     """The reference's own CPU implementation: oracle/_ref (compiled reference) when it travelled,
-    else the plain-C oracle port.  One step = camera->set_c2w + Render, as callers do."""
+    else the plain-C oracle port.  One step = camera->set_c2w + Render, as callers do.  With `split`
+    (compiled reference only) a few extra steps separate what a step is made of: the Render
+    itself with the ray table warm, the per-pose ray-table rebuild (include/ugu/camera.h:482-513, the only
+    OpenMP-parallel part), and the same with OMP_NUM_THREADS = 1."""
     # all the host threads the reference can use (torchrun exports OMP_NUM_THREADS=1 by default);
     # must be set before libgomp is loaded with the reference library
     os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     import oracle
+    extra = {}
     if oracle.ref_available():
         kind = "reference"
         runner = oracle.OracleRef(mesh)
+        runner.set_num_threads(os.cpu_count() or 1)
         render = lambda cam: runner.render(cam, opt)
         cores = os.cpu_count() or 1
         note = ("unmodified ugu::Rasterizer; its Render loop is single-threaded, only the per-pose "
@@ -147,7 +152,23 @@ def time_reference(mesh, opt, cams, steps, warmup, budget_s=None):
         if budget_s is not None and time.perf_counter() - t0 > budget_s:
             break
     dt = time.perf_counter() - t0
-    return dict(kind=kind, cores=cores, steps=done, seconds=dt, note=note)
+    if split and kind == "reference":
+        def cold_warm(n):
+            cold, warm = [], []
+            for i in range(n):
+                runner.render(cams[(7 + i) % len(cams)], opt, repeat_warm=True)
+                cold.append(runner.last_timing_ms[0])
+                warm.append(runner.last_timing_ms[1])
+            return statistics.median(cold), statistics.median(warm)
+        c_all, w_all = cold_warm(3)
+        runner.set_num_threads(1)
+        c_one, w_one = cold_warm(3)
+        runner.set_num_threads(os.cpu_count() or 1)
+        extra = {"render_ms_ray_table_warm": w_all, "ray_table_rebuild_ms": max(0.0, c_all - w_all),
+                 "omp_num_threads_1": {"ms_per_step": c_one, "render_ms_ray_table_warm": w_one,
+                                       "ray_table_rebuild_ms": max(0.0, c_one - w_one)},
+                 "split_sample": "median of 3 views each (set_c2w + Render, then Render again with the camera untouched)"}
+    return dict(kind=kind, cores=cores, steps=done, seconds=dt, note=note, extra=extra)
 
 
 def run_reference_arm(args):
@@ -177,6 +198,120 @@ def run_reference_arm(args):
     return 0
 
 
+def multiview_records(world, rank, r_ico, ico_mesh, barrier):
+    """BASELINE configs 5 and 3 — the configs the multi-GPU target is stated on — as STRONG scaling through the
+    batched multi-view path (ugu_b200.multiview.MultiViewRenderer -> ugu_b200_rasterizer_render_batch): a fixed
+    view list is split contiguously over the ranks; timed are (a) render only, outputs left on each GPU, (b)
+    render + gather of every face_id map to rank 0 with the exchange overlapped (chunks sent as they finish,
+    straight into the view-ordered destination), (c) config 5 only: render + per-GPU fold of the maps into per-face
+    visibility statistics + an all-reduce of 16 bytes per face instead of the maps.  Device time between barriers,
+    max over ranks (CUDA events on the current stream, which the library's work stream joins), median of 3 after
+    one warm-up.  L2 is flushed before each measurement, not between the views of a batch (a batch is one unit of
+    work; the views of a rank reuse the mesh in L2 by design)."""
+    import torch
+    import torch.distributed as dist
+    import cases
+    from ugu_b200 import DiffuseColor, PinholeCamera, Rasterizer, RendererCpuOption, meshgen
+    from ugu_b200.multiview import MultiViewRenderer
+
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device="cuda")
+
+    def timed(fn, reps=3):
+        out = []
+        for i in range(reps + 1):
+            flush.zero_()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            res = fn()
+            e1.record()
+            barrier()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if i:
+                out.append(float(t[0]))
+            del res
+        return statistics.median(out)
+
+    records = {}
+    # ---- config 5: 1024 random views of the 1.31M-triangle icosphere at 512x512, face_id only -------------------
+    n5 = 1024
+    cams5 = [PinholeCamera(512, 512, p, fov_y_deg=45.0) for p in meshgen.random_sphere_poses(n5, seed=0)]
+    cams5 = [c.to_native() for c in cams5]
+    for c in cams5:      # MultiViewRenderer reads sizes through the PinholeCamera accessors
+        c.width_ = c.width
+    class _Cam:          # thin accessor shim over the native POD (avoids 1024 host-side matrix inversions per call)
+        def __init__(self, n):
+            self.n = n
+        def width(self):
+            return self.n.width
+        def height(self):
+            return self.n.height
+    saved = r_ico._option
+    r_ico.set_option(RendererCpuOption(diffuse_color=DiffuseColor.kNone))
+    mv = MultiViewRenderer(r_ico)
+    F = len(ico_mesh.vertex_indices)
+    wrap5 = [_Cam(c) for c in cams5]
+    mv._render_local_cuda_orig = mv._render_local_cuda
+
+    def render_native(cameras, outputs, into=None):  # hand the native PODs to render_batch
+        n = len(cameras)
+        w, h = cameras[0].width(), cameras[0].height()
+        from ugu_b200.multiview import OUTPUT_SPEC
+        dev = into if into is not None else {k: torch.empty(mv.view_shape(n, h, w, k), dtype=OUTPUT_SPEC[k][0],
+                                                            device="cuda") for k in outputs}
+        with mv._on_work_stream() as stream:
+            mv.rasterizer.render_batch([c.n for c in cameras], on_device=True, stream=stream,
+                                       **{k: v.data_ptr() for k, v in dev.items()})
+        return dev
+    mv._render_local_cuda = render_native
+    mv._render_local = render_native
+    P5 = 512 * 512
+    t_render = timed(lambda: mv.render(wrap5, ("face_id",)))
+    t_gather = timed(lambda: mv.render_and_gather_overlapped(wrap5, "face_id", dst=0, chunk_views=16))
+    t_fold = timed(lambda: mv.render_face_visibility(wrap5, F, chunk_views=32))
+    gbytes = (n5 - len(mv.local_indices(n5)) if rank == 0 else 0) * P5 * 4
+    records["config5"] = {
+        "workload": "config5: icosphere L8 (F=1310720), 1024 random views, 512x512, face_id only",
+        "scaling": "strong", "views": n5, "n_gpus": world,
+        "render": {"ms": t_render, "views_per_s": n5 / (t_render * 1e-3), "us_per_view_per_gpu": t_render * 1e3 / (n5 / world),
+                   "mpix_per_s": n5 * P5 / (t_render * 1e-3) / 1e6, "mtri_per_s": n5 * F / (t_render * 1e-3) / 1e6},
+        "render_gather_to_rank0": {"ms": t_gather, "views_per_s": n5 / (t_gather * 1e-3),
+                                   "bytes_into_root": gbytes,
+                                   "exposed_gather_ms": max(0.0, t_gather - t_render),
+                                   "note": "NCCL send/recv per 16-view chunk as it finishes, directly into the "
+                                           "view-ordered buffer on rank 0"},
+        "render_fold_allreduce": {"ms": t_fold, "views_per_s": n5 / (t_fold * 1e-3),
+                                  "note": "per-GPU fold into per-face pixel / view counts and best view, then "
+                                          "all-reduce of 16 B per face"},
+        "algorithmic_bytes_per_view": 12 * len(ico_mesh.vertices) + 24 * F + 4 * P5,
+    }
+    r_ico.set_option(saved)
+    del mv
+    # ---- config 3: spot, 36-view turntable at 1024x1024, all five outputs ---------------------------------------
+    spot = cases.load_spot()
+    r3 = Rasterizer(RendererCpuOption(diffuse_color=DiffuseColor.kTexture), device=torch.cuda.current_device())
+    r3.set_mesh(spot)
+    assert r3.PrepareMesh()
+    c, ext = cases.bbox_center_and_extent(spot)
+    cams3 = [PinholeCamera(1024, 1024, p, fov_y_deg=45.0) for p in meshgen.orbit_poses(c, 1.5 * ext, 36)]
+    mv3 = MultiViewRenderer(r3)
+    outs = ("color", "depth", "normal", "mask", "face_id")
+    t3 = timed(lambda: mv3.render(cams3, outs))
+    t3g = timed(lambda: mv3.render_and_gather_overlapped(cams3, "face_id", dst=0, chunk_views=2))
+    P3 = 1024 * 1024
+    records["config3"] = {
+        "workload": "config3: spot (F=5856) 36-view turntable, 1024x1024, texture bilinear, 5 outputs",
+        "scaling": "strong", "views": 36, "n_gpus": world,
+        "render": {"ms": t3, "views_per_s": 36 / (t3 * 1e-3), "us_per_view_per_gpu": t3 * 1e3 / -(-36 // world),
+                   "mpix_per_s": 36 * P3 / (t3 * 1e-3) / 1e6},
+        "render_gather_to_rank0": {"ms": t3g, "views_per_s": 36 / (t3g * 1e-3),
+                                   "note": "face_id maps only are rendered and gathered (2-view chunks)"},
+    }
+    return records
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -184,6 +319,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ugu_b200", choices=["ugu_b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-multiview", action="store_true", help="skip the config 3 / config 5 multi-view records")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -262,18 +398,19 @@ def main():
             device_step(warmup + i)
             ev1[i].record()
         barrier()
-        return sum(a.elapsed_time(b) for a, b in zip(ev0, ev1)), time.perf_counter() - w0
+        per = [a.elapsed_time(b) for a, b in zip(ev0, ev1)]
+        return sum(per), time.perf_counter() - w0, per
 
     # pass 1 — the timed K steps behind `value`: nothing but the view's kernels between the events
     r.reset_stats()
-    dev_ms, wall_dev = timed_pass()
+    dev_ms, wall_dev, per_step = timed_pass()
     launches = r.stats()["kernel_launches"]
     # pass 2 — the same K steps again with the library's per-stage CUDA-event pairs switched on: the
     # per-kernel durations behind `roofline` / `stage_us` (the extra event records serialise the
     # kernels that pass 1 launches back to back, so this pass is slower and is not the bench value)
     r.reset_stats()
     r.set_profiling(True, (0, 1, 2, 3))
-    prof_ms, _ = timed_pass()
+    prof_ms, _, _ = timed_pass()
     st = r.stats()
     r.set_profiling(False, ())
 
@@ -297,6 +434,23 @@ def main():
         assert ok
     st_e = r.stats()
     barrier()
+    # the same Render into PAGEABLE destinations — what ugu::Image really is (a std::vector, image.h:354): the
+    # library stages the D2H through its pinned ring and memcpy's into the caller's images
+    pimgs = (Image3b(pinned=False), Image1f(pinned=False), Image3f(pinned=False), Image1b(pinned=False),
+             Image1i(pinned=False))
+    for i in range(2):
+        assert r.Render(*pimgs)
+    e2e_pg = []
+    for i in range(max(1, min(K, 50))):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r.set_camera(cams[((warmup + i) * world + rank) % N_POSES])
+        ok = r.Render(*pimgs)
+        e2e_pg.append(time.perf_counter() - t0)
+        assert ok
+    barrier()
+    mv = multiview_records(world, rank, r, mesh, barrier) if not args.no_multiview else None
     clocks = sampler.stop()
     # context for e2e: the host link.  One pinned D2H copy of the same number of bytes a view returns.
     d2h_bytes = P * 24
@@ -313,10 +467,10 @@ def main():
     link_ms = le0.elapsed_time(le1) / 10
 
     # ---- max over ranks ---------------------------------------------------------------------------
-    t = torch.tensor([dev_ms, e2e_t * 1e3], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, e2e_t * 1e3, sum(e2e_pg) * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms_max, e2e_ms_max = float(t[0]), float(t[1])
+    dev_ms_max, e2e_ms_max, e2e_pg_ms_max = float(t[0]), float(t[1]), float(t[2])
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
@@ -350,8 +504,14 @@ def main():
                                   "ms_for_one_view_of_outputs": link_ms,
                                   "note": "a view returns 24 B/pixel; e2e is bounded by this copy; at N > 1 "
                                           "all ranks copy at the same time and share the host's memory system"},
+                    "pageable": {"value": world * P * len(e2e_pg) / (e2e_pg_ms_max * 1e-3) / 1e6, "unit": "Mpix/s",
+                                 "ms_per_step": e2e_pg_ms_max / len(e2e_pg), "steps": len(e2e_pg),
+                                 "note": "same call, pageable destinations (the layout of ugu::Image, image.h:354): "
+                                         "D2H through the library's pinned staging ring + a host memcpy"},
                     "numa_rank0": numa},
             "gpu_launches": int(launches),
+            "ms_per_step_spread": {"min": min(per_step), "median": statistics.median(per_step), "max": max(per_step),
+                                   "note": "rank 0's per-step CUDA-event times of the timed pass"},
             "stage_us": {k: round(v * 1e3, 2) for k, v in stage_ms.items()},
             "ms_per_step_stage_timed_pass": prof_ms / K,
             "roofline": {"bound": "hbm", "kernel": dom + "_kernel", "achieved": achieved, "peak": peak,
@@ -364,13 +524,15 @@ def main():
             "clocks": clocks,
             "wall_s_device_loop": wall_dev,
         }
+        if mv is not None:
+            line["multiview"] = mv
         if world == 1 and not args.no_cpu_baseline:
-            cb = time_reference(mesh, opt, cams, steps=24, warmup=1, budget_s=20.0)
+            cb = time_reference(mesh, opt, cams, steps=24, warmup=1, budget_s=20.0, split=True)
             line["cpu_baseline"] = {
                 "value": P * cb["steps"] / cb["seconds"] / 1e6, "unit": "Mpix/s", "cores": cb["cores"],
                 "kind": cb["kind"], "ms_per_step": cb["seconds"] / cb["steps"] * 1e3,
                 "sample": f"{cb['steps']} full views of the same workload (set_c2w + Render each)",
-                "note": cb["note"]}
+                "note": cb["note"], **cb["extra"]}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

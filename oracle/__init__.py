@@ -462,6 +462,11 @@ class OracleRef:
             return None
         return out
 
+    def set_num_threads(self, n: int) -> None:
+        """OpenMP threads of the compiled reference from now on (the ray-table rebuild is its only parallel part)."""
+        self.lib.ugu_ref_set_num_threads.argtypes = [C.c_int]
+        self.lib.ugu_ref_set_num_threads(int(n))
+
     def raytrace(self, camera, option, want=ALL_OUTPUTS):
         """The compiled reference ugu::Raytracer (src/renderer/cpu/raytracer.cc, nanort BVH) on this mesh."""
         self.lib.ugu_ref_raytrace.restype = C.c_int
@@ -675,3 +680,14 @@ def port_visibility_keyframe(vertices, normals, indices, cam: "_VisCamera", opt:
             q(out["v_visible"]), q(out["v_rec"]), q(out["f_visible"]), q(out["f_area"]),
             q(out["f_viewing_angle"]), q(out["f_distance"]), q(out["f_projected_tri"]))
     return out if rc == 0 else None
+
+
+def ref_camera_constants(c2w):
+    """(w2c_R 9, w2c_t 3, c2w_R 9) float32 as the reference Rasterizer derives them (rasterizer.cc:118-119,
+    camera.h:321) — Eigen's inverse() / rotation() through oracle/_ref, no renderer needed."""
+    lib = C.CDLL(str(REF_LIB))
+    lib.ugu_ref_camera_constants.argtypes = [C.POINTER(C.c_double)] + [C.POINTER(C.c_float)] * 3
+    m = (C.c_double * 16)(*np.asarray(c2w, np.float64).reshape(-1))
+    R, t, Cm = (C.c_float * 9)(), (C.c_float * 3)(), (C.c_float * 9)()
+    lib.ugu_ref_camera_constants(m, R, t, Cm)
+    return np.array(R, np.float32), np.array(t, np.float32), np.array(Cm, np.float32)

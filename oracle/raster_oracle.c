@@ -1064,10 +1064,12 @@ static int vis_test_vertex(const OracleVisCamera* cam, const OracleVisOption* op
                            const float* nrm, const float* offset, const uint8_t* color, const float* depth,
                            const uint8_t* mask, const float* zbuf, OracleVisVertex* out) {
   float wp[3] = {vtx[0] + offset[0], vtx[1] + offset[1], vtx[2] + offset[2]};
-  /* Affine3f * Vector3f: translation + linear * v, rows reduced like dot3 (Eigen Transform.h) */
+  /* Affine3f * Vector3f (Eigen/src/Geometry/Transform.h, transform_right_product_impl): res = translation;
+   * res.noalias() += linear * v, the 3x3 * 3x1 product accumulated column by column — the association that
+   * reproduces the compiled reference bit for bit is ((m0 x + m1 y) + m2 z) + t (probed on 3045 projections). */
   float cp[3];
   for (int r = 0; r < 3; r++)
-    cp[r] = cam->w2c[r * 4 + 3] + (cam->w2c[r * 4 + 0] * wp[0] + (cam->w2c[r * 4 + 1] * wp[1] + cam->w2c[r * 4 + 2] * wp[2]));
+    cp[r] = ((cam->w2c[r * 4 + 0] * wp[0] + cam->w2c[r * 4 + 1] * wp[1]) + cam->w2c[r * 4 + 2] * wp[2]) + cam->w2c[r * 4 + 3];
   /* PinholeCamera::Project (camera.h:380-387) */
   const float ix = cam->fx / cp[2] * cp[0] + cam->cx;
   const float iy = cam->fy / cp[2] * cp[1] + cam->cy;

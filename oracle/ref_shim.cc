@@ -199,6 +199,14 @@ int ugu_ref_raytrace(void* handle, const UguRefCamera* cam, const UguRefOption* 
   return 0;
 }
 
+// OpenMP threads of the reference from now on (only PinholeCamera::InitRayTable is parallel on the Rasterizer path,
+// include/ugu/camera.h:482-513): lets the bench report the OMP_NUM_THREADS=1 figure in the same process.
+void ugu_ref_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#endif
+}
+
 // Renders one view.  Any output pointer may be null.  `timing_ms` (optional, 2 doubles) receives
 // [0] wall ms of the whole caller-visible step (set_c2w + Render, i.e. including the lazy ray-table
 // rebuild of include/ugu/camera.h:474-513) and [1] the same again for an immediately repeated Render

@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "rasterizer_cuda.h"
+#include "visibility_tester_cuda.h"
 #include "ugu/camera.h"
 #include "ugu/log.h"
 #include "ugu/mesh.h"
@@ -22,6 +23,8 @@
 #include "ugu/util/rgbd_util.h"
 #include "ugu/util/camera_util.h"
 #include "ugu/util/geom_util.h"
+
+extern "C" void omp_set_num_threads(int);  // libgomp, linked through the compiled reference
 
 namespace {
 
@@ -367,6 +370,80 @@ int main(int argc, char** argv) {
       }
     std::printf("GBuffer vs Rasterizer: %zu covered pixels  %s\n", covered, bad ? "MISMATCH" : "consistent");
     if (bad || covered == 0) failures++;
+  }
+  if (!timing) {
+    // ugu::VisibilityTesterCuda vs the reference ugu::VisibilityTester (BVH rays) on keyframes rendered by the
+    // reference Rasterizer: both fill a ugu::VisibilityInfo through the same interface; compared are the visible
+    // sets (the disagreement of sub-pixel rays vs nearest-pixel depth must stay below 2 %), the per-keyframe
+    // records on the pairs both call visible, and the CalcStat ids on faces whose lists are identical.
+    const std::vector<Eigen::Vector3f> eyes = {{0.f, 0.f, 2.7f}, {2.2f, 0.4f, 1.2f}, {-1.5f, -1.1f, -1.9f}, {0.3f, 2.6f, 0.5f}};
+    std::vector<std::shared_ptr<ugu::Keyframe>> kfs;
+    ugu::RendererCpuOption o;
+    o.diffuse_color = ugu::DiffuseColor::kVertex;
+    ugu::Rasterizer rr(o);
+    rr.set_mesh(mesh);
+    rr.PrepareMesh();
+    for (size_t i = 0; i < eyes.size(); i++) {
+      Eigen::Matrix4f c2w_f;
+      ugu::c2w(eyes[i], Eigen::Vector3f(0.f, 0.f, 0.f), Eigen::Vector3f(0.f, 1.f, 0.1f).normalized(), &c2w_f);
+      Eigen::Affine3d c2w = Eigen::Affine3d(c2w_f.cast<double>());
+      auto cam = std::make_shared<ugu::PinholeCamera>(W, H, 50.0f);
+      cam->set_c2w(c2w);
+      rr.set_camera(cam);
+      auto kf = ugu::Keyframe::Create();
+      kf->id = 100 + 7 * static_cast<int>(i);
+      kf->camera = cam;
+      if (!rr.Render(&kf->color, &kf->depth, nullptr, &kf->mask, nullptr)) return 1;
+      kfs.push_back(kf);
+    }
+    for (int facewise = 0; facewise < 2; facewise++) {
+      omp_set_num_threads(1);  // the reference's face-wise bookkeeping is racy under OpenMP
+      ugu::VisibilityTesterOption vo;
+      ugu::VisibilityTester ref_t(vo);
+      ref_t.set_data(mesh->vertices(), mesh->normals(), mesh->vertex_indices());
+      ugu::VisibilityTesterCuda cu_t(vo);
+      cu_t.set_data(mesh->vertices(), mesh->normals(), mesh->vertex_indices());
+      ugu::VisibilityInfo ri(*mesh), ci(*mesh);
+      if (!ref_t.PrepareData() || !cu_t.PrepareData()) return 2;
+      if (!ref_t.Test(kfs, &ri, facewise != 0) || !cu_t.Test(kfs, &ci, facewise != 0)) return 1;
+      long pairs = 0, differ = 0, rec_bad = 0, stat_faces = 0, stat_bad = 0;
+      for (size_t v = 0; v < ri.vertex_info_list.size(); v++) {
+        const auto& a = ri.vertex_info_list[v].visible_keyframes;
+        const auto& b = ci.vertex_info_list[v].visible_keyframes;
+        for (const auto& kf : kfs) {
+          const int ia = ri.vertex_info_list[v].VisibleFrom(kf->id), ib = ci.vertex_info_list[v].VisibleFrom(kf->id);
+          if (ia < 0 && ib < 0) continue;
+          pairs++;
+          if ((ia < 0) != (ib < 0)) {
+            differ++;
+            continue;
+          }
+          if (facewise) continue;  // a vertex may keep another corner's record after an upstream disagreement
+          if (a[ia].projected_pos != b[ib].projected_pos || a[ia].color != b[ib].color ||
+              a[ia].intensity != b[ib].intensity || std::abs(a[ia].viewing_angle - b[ib].viewing_angle) > 2e-6f)
+            rec_bad++;
+        }
+      }
+      for (size_t f = 0; f < ri.face_info_list.size(); f++) {
+        const auto& a = ri.face_info_list[f].visible_keyframes;
+        const auto& b = ci.face_info_list[f].visible_keyframes;
+        bool same = a.size() == b.size() && !a.empty();
+        for (size_t i = 0; same && i < a.size(); i++)
+          same = a[i].kf_id == b[i].kf_id && a[i].area == b[i].area && a[i].viewing_angle == b[i].viewing_angle;
+        if (!same) continue;
+        stat_faces++;
+        if (ri.face_info_list[f].max_area_id != ci.face_info_list[f].max_area_id ||
+            ri.face_info_list[f].min_viewing_angle_id != ci.face_info_list[f].min_viewing_angle_id)
+          stat_bad++;
+      }
+      const bool ok = pairs > 0 && differ * 50 <= pairs && rec_bad == 0 && stat_bad == 0 && stat_faces > 0 &&
+                      ci.has_vertex_stat && ci.has_face_stat;
+      std::printf("VisibilityTester %-10s: %ld (vertex, keyframe) pairs, %ld decided differently (%.2f %%), %ld record "
+                  "mismatches, CalcStat ids on %ld identical face lists: %ld wrong  %s\n",
+                  facewise ? "face-wise" : "vertex-wise", pairs, differ, 100.0 * differ / (pairs ? pairs : 1), rec_bad,
+                  stat_faces, stat_bad, ok ? "ok" : "MISMATCH");
+      if (!ok) failures++;
+    }
   }
   std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);
   return failures ? 1 : 0;

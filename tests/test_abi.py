@@ -30,7 +30,7 @@ def test_header_symbols_all_exported_and_bound():
 
 
 def test_abi_version():
-    assert N.load().ugu_b200_abi_version() == 7
+    assert N.load().ugu_b200_abi_version() == 8
 
 
 def test_struct_sizes_match_header_layout():
@@ -39,6 +39,8 @@ def test_struct_sizes_match_header_layout():
     assert C.sizeof(N.Outputs) == 40
     assert C.sizeof(N.MeshDesc) == 32 + 12 * 8
     assert C.sizeof(N.Stats) == 8 * 4 + 8 * 8
+    assert C.sizeof(N.VisOption) == 40
+    assert C.sizeof(N.Keyframe) == 8 + 108 + 4 + 48 + 12 + 4 + 32
 
 
 def test_library_carries_sm100a_code_only():

@@ -58,18 +58,20 @@ def _worker(rank, world, port, n_views, mode, q):
         idx, outs = mv.render(cams)
         assert idx == partition(n_views, world, rank, mode)
         got = mv.render_and_gather(cams, "face_id", dst=0)
+        # the chunked form: chunks sent as they finish, straight into the view-ordered destination
+        got2 = mv.render_and_gather_overlapped(cams, "face_id", dst=0, chunk_views=2)
         if rank == 0:
             want = _fake_render(cams, ("face_id",))["face_id"]
-            q.put(bool(torch.equal(got, want)))
+            q.put(bool(torch.equal(got, want)) and bool(torch.equal(got2, want)))
         else:
-            assert got is None
+            assert got is None and got2 is None
             q.put(True)
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.parametrize("world,n_views,mode", [(2, 7, "contiguous"), (2, 6, "round_robin"),
-                                                (3, 2, "contiguous")])
+                                                (3, 2, "contiguous"), (3, 11, "contiguous")])
 def test_sharded_render_and_gather_gloo(world, n_views, mode):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()

@@ -73,6 +73,40 @@ class Stats(C.Structure):
                 ("tile_jobs", C.c_uint64), ("hazard_fragments", C.c_uint64)]
 
 
+class VisOption(C.Structure):
+    _fields_ = [("backface_culling_angle_rad_th", C.c_float), ("use_mask", C.c_int32), ("use_depth", C.c_int32),
+                ("interp", C.c_int32), ("max_viewing_angle", C.c_float),
+                ("max_distance_from_camera_to_vertex", C.c_float), ("max_depth_difference", C.c_float),
+                ("eps", C.c_float), ("facewise", C.c_int32), ("self_occlusion", C.c_int32)]
+
+
+class Keyframe(C.Structure):
+    _fields_ = [("id", C.c_int32), ("reserved", C.c_int32), ("cam", Camera), ("w2c", C.c_float * 12),
+                ("c2w_t", C.c_float * 3), ("reserved2", C.c_float), ("color", C.c_void_p),
+                ("depth", C.c_void_p), ("mask", C.c_void_p), ("zbuf", C.c_void_p)]
+
+
+class VisRecords(C.Structure):
+    _fields_ = [("vertex_visible", C.c_void_p), ("vertex", C.c_void_p), ("face_visible", C.c_void_p),
+                ("face", C.c_void_p)]
+
+
+class VisStats(C.Structure):
+    FIELDS = ("face_count", "face_max_area_order", "face_min_viewing_angle_order", "face_min_distance_order",
+              "face_max_area", "face_min_viewing_angle", "face_min_distance", "vertex_count",
+              "vertex_min_viewing_angle_order", "vertex_min_distance_order", "vertex_mean_color",
+              "vertex_mean_viewing_angle", "vertex_mean_distance", "vertex_min_viewing_angle_color",
+              "vertex_min_distance_color")
+    _fields_ = [(n, C.c_void_p) for n in FIELDS]
+
+
+class VisAccumulators(C.Structure):
+    FIELDS = ("face_count", "face_max_area", "face_min_angle", "face_min_dist", "vertex_count",
+              "vertex_sum_color", "vertex_sum_angle_dist", "vertex_min_angle", "vertex_min_dist",
+              "vertex_min_colors")
+    _fields_ = [(n, C.c_void_p) for n in FIELDS]
+
+
 # every symbol include/ugu_b200_raster.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "ugu_b200_abi_version": (C.c_int, []),
@@ -101,6 +135,16 @@ SYMBOLS = {
                                                   C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ugu_b200_face_visibility": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ugu_b200_visibility_set_data": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "ugu_b200_visibility_reset": (C.c_int, [C.c_void_p]),
+    "ugu_b200_visibility_test": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Keyframe), C.c_int32,
+                                           C.POINTER(VisOption), C.POINTER(VisRecords)]),
+    "ugu_b200_visibility_test_device": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Keyframe), C.c_int32,
+                                                  C.POINTER(VisOption), C.POINTER(VisRecords), C.c_void_p]),
+    "ugu_b200_visibility_stats": (C.c_int, [C.c_void_p, C.POINTER(VisStats)]),
+    "ugu_b200_visibility_accumulators": (C.c_int, [C.c_void_p, C.POINTER(VisAccumulators)]),
+    "ugu_b200_keyframe_camera_from_c2w": (C.c_int, [C.POINTER(C.c_double), C.c_int32, C.c_int32, C.c_float,
+                                                    C.c_float, C.c_float, C.c_float, C.POINTER(Keyframe)]),
     "ugu_b200_depth_to_mesh": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p, C.c_int32,
                                          C.c_int32, C.c_int32, C.c_float, C.c_int32, C.c_int32, C.c_int32,
                                          C.POINTER(Depth2MeshCounts)]),
@@ -144,7 +188,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 7:
+    if lib.ugu_b200_abi_version() != 8:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

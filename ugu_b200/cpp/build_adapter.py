@@ -1,7 +1,8 @@
 """Builds the C++ adapter library — only possible where the reference headers exist (this
 container; the GPU box receives the prebuilt, git-ignored binary).
 
-    ugu_b200/cpp/build/librasterizer_cuda.so   ugu::RasterizerCuda (links libugu_b200_raster.so)
+    ugu_b200/cpp/build/librasterizer_cuda.so   ugu::RasterizerCuda, ugu::RaytracerCuda, ugu::VisibilityTesterCuda
+                                               (links libugu_b200_raster.so)
 
 Its differential harness against the reference Rasterizer is test infrastructure and lives in
 tests/cpp/ (tests/cpp/build_check.py).
@@ -35,6 +36,7 @@ def build() -> Path:
     OUT.mkdir(exist_ok=True)
     so = OUT / "librasterizer_cuda.so"
     subprocess.run([*compile_command(), "-shared", "-o", str(so), str(HERE / "rasterizer_cuda.cc"),
+                    str(HERE / "visibility_tester_cuda.cc"),
                     f"-L{REPO / 'ugu_b200' / 'lib'}", "-lugu_b200_raster", "-Wl,-rpath,$ORIGIN/../../lib"],
                    check=True, capture_output=True)
     return so

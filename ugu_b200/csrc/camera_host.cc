@@ -156,8 +156,9 @@ extern "C" int ugu_b200_camera_from_c2w(const double* c2w16, int32_t width, int3
       out->w2c_R[i * 3 + j] = static_cast<float>(rot.m[i][j]);
       out->c2w_R[i * 3 + j] = static_cast<float>(lin.m[i][j]);
     }
-    // Affine inverse translation: -(inv * t)   (Eigen/src/Geometry/Transform.h, inverse(Affine))
-    out->w2c_t[i] = static_cast<float>(-(inv.m[i][0] * t[0] + inv.m[i][1] * t[1] + inv.m[i][2] * t[2]));
+    // Affine inverse translation: (-inv) * t   (Eigen/src/Geometry/Transform.h, inverse(Affine): unary minus on
+    // the matrix, so a zero sum keeps Eigen's sign of zero)
+    out->w2c_t[i] = static_cast<float>((-inv.m[i][0]) * t[0] + (-inv.m[i][1]) * t[1] + (-inv.m[i][2]) * t[2]);
   }
   return UGU_B200_OK;
 }
@@ -177,7 +178,7 @@ extern "C" int ugu_b200_keyframe_camera_from_c2w(const double* c2w16, int32_t wi
   // w2c_ = c2w_.inverse() (Affine: [L^-1 | -(L^-1 t)]), then .cast<float>() (visibility_tester.cc:422)
   for (int i = 0; i < 3; i++) {
     for (int j = 0; j < 3; j++) kf->w2c[i * 4 + j] = static_cast<float>(inv.m[i][j]);
-    kf->w2c[i * 4 + 3] = static_cast<float>(-(inv.m[i][0] * t[0] + inv.m[i][1] * t[1] + inv.m[i][2] * t[2]));
+    kf->w2c[i * 4 + 3] = static_cast<float>((-inv.m[i][0]) * t[0] + (-inv.m[i][1]) * t[1] + (-inv.m[i][2]) * t[2]);
     kf->c2w_t[i] = static_cast<float>(t[i]);
   }
   return UGU_B200_OK;

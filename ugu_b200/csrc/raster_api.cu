@@ -1805,8 +1805,11 @@ int VtRun(ugu_b200_rasterizer* r, int K, const ugu_b200_keyframe* kfs, int first
           while (j < cams.size() && cams[j].width == cams[i].width && cams[j].height == cams[i].height &&
                  (P * 4) % 256 == 0)
             j++;
-          rc = Validate(r, &cams[i], &d);
-          if (!rc) rc = RenderViews(r, &cams[i], (int)(j - i), &d, st, (int)(j - i));
+          // (no Render validation: a depth-only pass needs positions and indices, nothing the options name)
+          if (cams[i].width > 65535 || cams[i].height > 65535)
+            rc = Fail(r, UGU_B200_E_INVALID, "camera size %dx%d is invalid", cams[i].width, cams[i].height);
+          else
+            rc = RenderViews(r, &cams[i], (int)(j - i), &d, st, std::min((int)(j - i), (int)kMaxBatch));
           i = j - 1;
         }
         r->opt = saved;

@@ -10,7 +10,7 @@
 //     distance  =  t_v                                               (reference: the BVH hit's t)
 //     the depth check uses camera_p.z                                 (reference: the hit's camera z)
 // Every other expression is the reference's, single round-to-nearest float operations in its order
-// (--fmad=false): Affine3f * Vector3f = translation + linear * v with Eigen's a0*b0 + (a1*b1 + a2*b2) rows,
+// (--fmad=false): Affine3f * Vector3f = ((m0 x + m1 y) + m2 z) + t,
 // PinholeCamera::Project (camera.h:380-387), ray_w(float, float) (camera.h:438-448), std::round / std::floor,
 // BilinearInterpolation (util/image_util.h:156-193), Color2Gray in double (image_util.h:228-244).  acosf is the
 // device libm's (<= 2 ulp from glibc's), so viewing_angle is held to a few ulp, everything else bit-exact against
@@ -97,9 +97,11 @@ __device__ __forceinline__ bool vt_test_vertex(const VtKeyframe& kf, const VtOpt
                                                VtVertexRec& out) {
   const VtCamera& c = kf.cam;
   const float wx = vx + ox, wy = vy + oy, wz = vz + oz;
-  const float px = c.w2c[3] + (c.w2c[0] * wx + (c.w2c[1] * wy + c.w2c[2] * wz));
-  const float py = c.w2c[7] + (c.w2c[4] * wx + (c.w2c[5] * wy + c.w2c[6] * wz));
-  const float pz = c.w2c[11] + (c.w2c[8] * wx + (c.w2c[9] * wy + c.w2c[10] * wz));
+  // Affine3f * Vector3f as Eigen evaluates it: ((m0 x + m1 y) + m2 z) + t (column-wise accumulation, then the
+  // translation; probed against the compiled reference)
+  const float px = ((c.w2c[0] * wx + c.w2c[1] * wy) + c.w2c[2] * wz) + c.w2c[3];
+  const float py = ((c.w2c[4] * wx + c.w2c[5] * wy) + c.w2c[6] * wz) + c.w2c[7];
+  const float pz = ((c.w2c[8] * wx + c.w2c[9] * wy) + c.w2c[10] * wz) + c.w2c[11];
   const float ix = c.fx / pz * px + c.cx;
   const float iy = c.fy / pz * py + c.cy;
   if (pz < 0.0f || ix < 0.0f || (float)(c.W - 1) < ix || iy < 0.0f || (float)(c.H - 1) < iy) return false;

@@ -123,6 +123,10 @@ def reduce_face_visibility(pixel_count: torch.Tensor, view_count: torch.Tensor, 
     dist.all_reduce(best, op=dist.ReduceOp.MAX, group=group)
 
 
+OUTPUT_SPEC = dict(color=(torch.uint8, 3), depth=(torch.float32, 1), normal=(torch.float32, 3),
+                   mask=(torch.uint8, 1), face_id=(torch.int32, 1))
+
+
 class MultiViewRenderer:
     """Shards `cameras` over the ranks of the default process group and renders the local slice
     with one device-resident batch call.
@@ -141,25 +145,27 @@ class MultiViewRenderer:
         self._accumulate = accumulate or self._accumulate_cuda
         self._stream = None  # side stream of the CUDA path, see _on_work_stream
 
-    def _render_local_cuda(self, cameras: Sequence, outputs: Sequence[str]):
+    def _render_local_cuda(self, cameras: Sequence, outputs: Sequence[str], into: Optional[dict] = None):
+        """`into` = {output: contiguous (n, H, W[, C]) tensor} renders straight into caller storage (e.g. a slice
+        of the gather destination)."""
         if self.rasterizer is None:
             raise RuntimeError("MultiViewRenderer needs a ugu_b200.Rasterizer (there is no CPU fallback)")
         n = len(cameras)
         if n == 0:
             return {}
         w, h = cameras[0].width(), cameras[0].height()
-        spec = dict(color=(torch.uint8, 3), depth=(torch.float32, 1), normal=(torch.float32, 3),
-                    mask=(torch.uint8, 1), face_id=(torch.int32, 1))
-        dev = {}
-        for k in outputs:
-            dt, ch = spec[k]
-            shape = (n, h, w) if ch == 1 else (n, h, w, ch)
-            dev[k] = torch.empty(shape, dtype=dt, device="cuda")
+        dev = into if into is not None else {k: torch.empty(self.view_shape(n, h, w, k), dtype=OUTPUT_SPEC[k][0],
+                                                            device="cuda") for k in outputs}
         with self._on_work_stream() as stream:
             # view slabs that are not 16-byte aligned (odd W*H) are handled inside the library
             self.rasterizer.render_batch(list(cameras), on_device=True, stream=stream,
                                          **{k: v.data_ptr() for k, v in dev.items()})
         return dev
+
+    @staticmethod
+    def view_shape(n: int, h: int, w: int, output: str):
+        ch = OUTPUT_SPEC[output][1]
+        return (n, h, w) if ch == 1 else (n, h, w, ch)
 
     @contextlib.contextmanager
     def _on_work_stream(self):
@@ -229,3 +235,55 @@ class MultiViewRenderer:
         else:
             local = outs[output]
         return gather_view_maps(local, len(cameras), self.mode, dst, self.group)
+
+    def render_and_gather_overlapped(self, cameras: Sequence, output: str = "face_id", dst: int = 0,
+                                     chunk_views: int = 16):
+        """Render + gather with the exchange hidden under the rendering: every rank renders its contiguous slice
+        `chunk_views` at a time on the library's work stream and, as soon as a chunk is done, sends it (NCCL
+        send / recv, which run on NCCL's own stream) straight into its final place in the view-ordered
+        destination on `dst` — no padded staging buffers, no reordering pass on the root; the root renders its
+        own views in place.  Returns the (num_views, H, W[, C]) tensor on `dst`, None elsewhere.  Round-robin
+        partitions fall back to render_and_gather."""
+        world, rank = _world_rank(self.group)
+        if world == 1 or self.mode != "contiguous":
+            return self.render_and_gather(cameras, output, dst)
+        num = len(cameras)
+        w, h = cameras[0].width(), cameras[0].height()
+        dt = OUTPUT_SPEC[output][0]
+        device = "cuda" if self.rasterizer is not None else "cpu"
+        parts = [partition(num, world, r, self.mode) for r in range(world)]
+        rounds = max((len(p) + chunk_views - 1) // chunk_views for p in parts)
+        out = torch.empty(self.view_shape(num, h, w, output), dtype=dt, device=device) if rank == dst else None
+        works, keep = [], []
+        mine = parts[rank]
+        for k in range(rounds):
+            lo, hi = k * chunk_views, min((k + 1) * chunk_views, len(mine))
+            ops = []
+            if lo < hi:
+                idx = mine[lo:hi]
+                if rank == dst:  # in place
+                    self._render_chunk([cameras[i] for i in idx], output, out[idx[0]: idx[-1] + 1])
+                else:
+                    buf = torch.empty(self.view_shape(len(idx), h, w, output), dtype=dt, device=device)
+                    self._render_chunk([cameras[i] for i in idx], output, buf)
+                    keep.append(buf)
+                    ops.append(dist.P2POp(dist.isend, buf, dst, group=self.group))
+            if rank == dst:
+                for r in range(world):
+                    if r == dst:
+                        continue
+                    plo, phi = k * chunk_views, min((k + 1) * chunk_views, len(parts[r]))
+                    if plo < phi:
+                        ops.append(dist.P2POp(dist.irecv, out[parts[r][plo]: parts[r][phi - 1] + 1], r,
+                                              group=self.group))
+            if ops:
+                works.extend(dist.batch_isend_irecv(ops))
+        for wk in works:
+            wk.wait()
+        return out
+
+    def _render_chunk(self, cameras: Sequence, output: str, into: torch.Tensor) -> None:
+        if self._render_local == self._render_local_cuda:
+            self._render_local_cuda(cameras, (output,), into={output: into})
+        else:  # injected renderer (CPU tests)
+            into.copy_(self._render_local(cameras, (output,))[output])
