@@ -17,6 +17,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
+import copy
 import statistics
 import sys
 import threading
@@ -177,7 +178,7 @@ def run_reference_arm(args):
         return 0
     mesh, opt, cams = make_inputs()
     steps = max(1, args.steps)
-    r = time_reference(mesh, opt, cams, steps, max(0, min(args.warmup, 2)), budget_s=240.0)
+    r = time_reference(mesh, opt, cams, steps, max(0, min(args.warmup, 2)), budget_s=240.0, split=True)
     P = W * H
     F = len(mesh.vertex_indices)
     ms = r["seconds"] / r["steps"] * 1e3
@@ -190,7 +191,7 @@ def run_reference_arm(args):
         "config": {"workload": WORKLOAD, "views_per_step": 1, "culling": True},
         "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": r["cores"], "kind": r["kind"],
                          "sample": f"{r['steps']} full views of the workload (set_c2w + Render each)",
-                         "note": r["note"]},
+                         "note": r["note"], **r["extra"]},
         "e2e": {"value": value, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -238,35 +239,11 @@ def multiview_records(world, rank, r_ico, ico_mesh, barrier):
     # ---- config 5: 1024 random views of the 1.31M-triangle icosphere at 512x512, face_id only -------------------
     n5 = 1024
     cams5 = [PinholeCamera(512, 512, p, fov_y_deg=45.0) for p in meshgen.random_sphere_poses(n5, seed=0)]
-    cams5 = [c.to_native() for c in cams5]
-    for c in cams5:      # MultiViewRenderer reads sizes through the PinholeCamera accessors
-        c.width_ = c.width
-    class _Cam:          # thin accessor shim over the native POD (avoids 1024 host-side matrix inversions per call)
-        def __init__(self, n):
-            self.n = n
-        def width(self):
-            return self.n.width
-        def height(self):
-            return self.n.height
-    saved = r_ico._option
+    wrap5 = [c.to_native() for c in cams5]   # camera blocks built once, as a caller looping over a fixed rig would
+    saved = copy.copy(r_ico._option)
     r_ico.set_option(RendererCpuOption(diffuse_color=DiffuseColor.kNone))
     mv = MultiViewRenderer(r_ico)
     F = len(ico_mesh.vertex_indices)
-    wrap5 = [_Cam(c) for c in cams5]
-    mv._render_local_cuda_orig = mv._render_local_cuda
-
-    def render_native(cameras, outputs, into=None):  # hand the native PODs to render_batch
-        n = len(cameras)
-        w, h = cameras[0].width(), cameras[0].height()
-        from ugu_b200.multiview import OUTPUT_SPEC
-        dev = into if into is not None else {k: torch.empty(mv.view_shape(n, h, w, k), dtype=OUTPUT_SPEC[k][0],
-                                                            device="cuda") for k in outputs}
-        with mv._on_work_stream() as stream:
-            mv.rasterizer.render_batch([c.n for c in cameras], on_device=True, stream=stream,
-                                       **{k: v.data_ptr() for k, v in dev.items()})
-        return dev
-    mv._render_local_cuda = render_native
-    mv._render_local = render_native
     P5 = 512 * 512
     t_render = timed(lambda: mv.render(wrap5, ("face_id",)))
     t_gather = timed(lambda: mv.render_and_gather_overlapped(wrap5, "face_id", dst=0, chunk_views=16))
@@ -295,7 +272,7 @@ def multiview_records(world, rank, r_ico, ico_mesh, barrier):
     r3.set_mesh(spot)
     assert r3.PrepareMesh()
     c, ext = cases.bbox_center_and_extent(spot)
-    cams3 = [PinholeCamera(1024, 1024, p, fov_y_deg=45.0) for p in meshgen.orbit_poses(c, 1.5 * ext, 36)]
+    cams3 = [PinholeCamera(1024, 1024, p, fov_y_deg=45.0).to_native() for p in meshgen.orbit_poses(c, 1.5 * ext, 36)]
     mv3 = MultiViewRenderer(r3)
     outs = ("color", "depth", "normal", "mask", "face_id")
     t3 = timed(lambda: mv3.render(cams3, outs))
@@ -507,7 +484,8 @@ def main():
                     "pageable": {"value": world * P * len(e2e_pg) / (e2e_pg_ms_max * 1e-3) / 1e6, "unit": "Mpix/s",
                                  "ms_per_step": e2e_pg_ms_max / len(e2e_pg), "steps": len(e2e_pg),
                                  "note": "same call, pageable destinations (the layout of ugu::Image, image.h:354): "
-                                         "D2H through the library's pinned staging ring + a host memcpy"},
+                                         "D2H through the library's pinned staging ring, drained by a few host threads "
+                                         "(UGU_B200_COPY_THREADS, default min(6, 3/8 of the host threads))"},
                     "numa_rank0": numa},
             "gpu_launches": int(launches),
             "ms_per_step_spread": {"min": min(per_step), "median": statistics.median(per_step), "max": max(per_step),

@@ -123,6 +123,13 @@ def reduce_face_visibility(pixel_count: torch.Tensor, view_count: torch.Tensor, 
     dist.all_reduce(best, op=dist.ReduceOp.MAX, group=group)
 
 
+def _size(cam):
+    """(width, height) of a PinholeCamera or of a prebuilt native camera block (ugu_b200._native.Camera) — callers
+    that render the same view list repeatedly convert the cameras once (Camera.to_native) and pass the blocks."""
+    w = cam.width
+    return (w(), cam.height()) if callable(w) else (int(w), int(cam.height))
+
+
 OUTPUT_SPEC = dict(color=(torch.uint8, 3), depth=(torch.float32, 1), normal=(torch.float32, 3),
                    mask=(torch.uint8, 1), face_id=(torch.int32, 1))
 
@@ -153,7 +160,7 @@ class MultiViewRenderer:
         n = len(cameras)
         if n == 0:
             return {}
-        w, h = cameras[0].width(), cameras[0].height()
+        w, h = _size(cameras[0])
         dev = into if into is not None else {k: torch.empty(self.view_shape(n, h, w, k), dtype=OUTPUT_SPEC[k][0],
                                                             device="cuda") for k in outputs}
         with self._on_work_stream() as stream:
@@ -229,7 +236,7 @@ class MultiViewRenderer:
         """Render, then gather one output of every view to rank `dst` in global view order."""
         idx, outs = self.render(cameras, (output,))
         if not idx:
-            w, h = cameras[0].width(), cameras[0].height()
+            w, h = _size(cameras[0])
             local = torch.empty((0, h, w), dtype=torch.int32,
                                 device="cuda" if torch.cuda.is_available() else "cpu")
         else:
@@ -248,7 +255,7 @@ class MultiViewRenderer:
         if world == 1 or self.mode != "contiguous":
             return self.render_and_gather(cameras, output, dst)
         num = len(cameras)
-        w, h = cameras[0].width(), cameras[0].height()
+        w, h = _size(cameras[0])
         dt = OUTPUT_SPEC[output][0]
         device = "cuda" if self.rasterizer is not None else "cpu"
         parts = [partition(num, world, r, self.mode) for r in range(world)]
