@@ -354,3 +354,91 @@ def test_full_size_config5_random_views_512_face_id():
         assert np.array_equal(fid[i], single["face_id"])
     # every view sees roughly half of a closed sphere; ids are in range
     assert fid.max() < 1310720 and fid.min() == -1
+
+
+# ---- two-pass occlusion ordering (raster_kernel PASS 1 / PASS 2) forced on meshes of every size ------------------
+@pytest.fixture
+def two_pass(monkeypatch):
+    """Rasterizers created inside the test take the two-pass path whatever the mesh size (the knob is read
+    when the handle is created)."""
+    monkeypatch.setenv("UGU_B200_TWOPASS", "1")
+
+
+@pytest.mark.parametrize("name", util.golden_names())
+def test_two_pass_vs_reference_golden(two_pass, name):
+    mesh, cam, opt, want, _ = util.load_golden(name)
+    run = util.CudaRunner(mesh, opt)
+    got = run.render(cam, opt)
+    assert got is not None
+    util.assert_parity(got, want, strict=True, color_lsb=_lsb(opt), what="two-pass " + name)
+    assert run.r.stats()["hazard_fragments"] == 0
+
+
+@pytest.mark.parametrize("seed", [31, 32])
+def test_two_pass_vs_oracle_random_soup(two_pass, seed):
+    mesh = cases.random_soup(4000, seed=seed, big_fraction=0.1)
+    rng = np.random.RandomState(seed)
+    run = util.CudaRunner(mesh)
+    port = OraclePort(mesh)
+    for tag, opt in cases.ALL_OPTIONS:
+        eye = rng.uniform(-0.3, 0.3, 3)
+        c2w = meshgen.look_at_c2w(eye, eye + np.array([rng.uniform(-0.2, 0.2), rng.uniform(-0.2, 0.2), 1.0]),
+                                  (0.1, -1.0, 0.05))
+        cam = PinholeCamera(int(rng.choice([97, 160, 323])), int(rng.choice([61, 120, 200])), c2w,
+                            fov_y_deg=float(rng.uniform(30, 80)))
+        util.assert_parity(run.render(cam, opt), port.render(cam.to_native(), opt), strict=True,
+                           color_lsb=_lsb(opt), what=f"two-pass seed{seed}/{tag}")
+
+
+def _wall_and_debris(seed, n_debris, sliver):
+    """A camera-facing wall of small triangles (pass 1) in front of a cloud of tiny triangles that face away
+    (pass 2 groups): well-shaped ones, slivers, zero-area and near-degenerate ones, some poking through the
+    wall, some next to its border — what the triangle-level occlusion test of pass 2 has to get right."""
+    from ugu_b200 import Mesh
+    rng = np.random.RandomState(seed)
+    n = 48
+    gx, gy = np.meshgrid(np.linspace(-1, 1, n + 1), np.linspace(-1, 1, n + 1))
+    wall_v = np.stack([gx.ravel(), gy.ravel(), np.full(gx.size, 2.0) + 0.02 * rng.randn(gx.size)], 1)
+    quads = [(j * (n + 1) + i, j * (n + 1) + i + 1, (j + 1) * (n + 1) + i, (j + 1) * (n + 1) + i + 1)
+             for j in range(n) for i in range(n)]
+    # the camera looks down +z; (a, c, b) winds so that the geometric normal points to -z (towards the camera)
+    wall_f = np.array([t for (a, b, c, d) in quads for t in ((a, c, b), (b, c, d))], np.int32)
+    ctr = np.stack([rng.uniform(-1.2, 1.2, n_debris), rng.uniform(-1.2, 1.2, n_debris),
+                    rng.uniform(1.9, 3.0, n_debris)], 1)
+    ext = 0.02 * rng.rand(n_debris, 1, 1) ** 2
+    tri = ctr[:, None, :] + ext * rng.randn(n_debris, 3, 3)
+    if sliver:
+        k = rng.rand(n_debris) < 0.5          # half of them collapse (almost) onto a line
+        t = rng.rand(n_debris, 1)
+        line = tri[:, 0] * (1 - t) + tri[:, 1] * t
+        eps = np.where(rng.rand(n_debris, 1) < 0.3, 0.0, 10.0 ** rng.uniform(-9, -3, (n_debris, 1)))
+        tri[k, 2] = (line + eps * rng.randn(n_debris, 3))[k]
+    # make the debris face away from the camera (normal.z > 0): swap two corners where needed
+    nz = np.cross(tri[:, 1] - tri[:, 0], tri[:, 2] - tri[:, 0])[:, 2]
+    flip = nz < 0
+    tri[flip, 1], tri[flip, 2] = tri[flip, 2].copy(), tri[flip, 1].copy()
+    deb_v = tri.reshape(-1, 3)
+    deb_f = np.arange(n_debris * 3, dtype=np.int32).reshape(-1, 3) + len(wall_v)
+    verts = np.concatenate([wall_v, deb_v]).astype(np.float32)
+    faces = np.concatenate([wall_f, deb_f]).astype(np.int32)
+    fn = np.cross(verts[faces[:, 1]] - verts[faces[:, 0]], verts[faces[:, 2]] - verts[faces[:, 0]])
+    ln = np.linalg.norm(fn, axis=1, keepdims=True)
+    fn = np.where(ln > 0, fn / np.maximum(ln, 1e-30), np.array([[0, 0, 1.0]])).astype(np.float32)
+    cols = rng.uniform(0, 255, verts.shape).astype(np.float32)
+    return Mesh(vertices=verts, vertex_indices=faces, face_normals=fn, vertex_colors=cols)
+
+
+@pytest.mark.parametrize("sliver", [False, True], ids=["shaped", "slivers"])
+@pytest.mark.parametrize("culling", [True, False], ids=["cull", "nocull"])
+def test_two_pass_occluded_debris(two_pass, sliver, culling):
+    mesh = _wall_and_debris(7 + sliver, 20000, sliver)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, shading_normal=ShadingNormal.kFace,
+                            backface_culling=culling)
+    run = util.CudaRunner(mesh, opt)
+    port = OraclePort(mesh)
+    for (w, h, fov) in ((640, 480, 60.0), (203, 117, 75.0)):
+        cam = PinholeCamera(w, h, meshgen.look_at_c2w((0.02, -0.01, 0.0), (0, 0, 2.0), (0, -1, 0)), fov_y_deg=fov)
+        want = port.render(cam.to_native(), opt)
+        got = run.render(cam, opt)
+        util.assert_parity(got, want, strict=True, what=f"debris {w}x{h}")
+    assert (want["face_id"] >= 0).sum() > 1000

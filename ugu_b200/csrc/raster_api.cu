@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cfloat>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -57,7 +58,7 @@ struct ugu_b200_rasterizer {
   std::vector<void*> mesh_allocs;  // everything owned by the current mesh
 
   // per-view scratch
-  DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters;
+  DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters, order;
   size_t vis_pixels = 0;  // pixels per visibility slab
   size_t vis_slabs = 0;   // slabs known to hold EMPTY
   int max_batch = 0;      // views per launch set of render_batch (0 = adaptive, UGU_B200_BATCH overrides)
@@ -68,6 +69,7 @@ struct ugu_b200_rasterizer {
   int coop_max = 0;  // bbox samples up to which a triangle is rasterised inside raster_kernel; larger
                      // ones go to the tile-job queue.  0 = adaptive (see RenderView)
   bool use_pdl = true;  // programmatic dependent launch of the per-view kernels (UGU_B200_PDL=0 disables)
+  int two_pass = -1;    // occlusion ordering of raster_kernel: -1 = by mesh size, 0 / 1 forced (UGU_B200_TWOPASS)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
   DevBuf out_color[2], out_depth[2], out_normal[2], out_mask[2], out_fid[2];
@@ -203,18 +205,90 @@ struct Reorder {
   bool active = false;
 };
 
-void BuildReorder(const int32_t* idx, size_t n_idx, int count, Reorder* out) {
+// `face_order` (optional, slot -> face): the order in which the faces are walked when numbers are handed out
+// (the raster order, see BuildFaceOrder); the remapped index list itself stays in face order.
+void BuildReorder(const int32_t* idx, size_t n_idx, int count, Reorder* out,
+                  const std::vector<int32_t>* face_order = nullptr) {
   out->new_of_old.assign((size_t)count, -1);
   out->idx.resize(n_idx);
   int32_t next = 0;
-  for (size_t i = 0; i < n_idx; i++) {
-    int32_t& slot = out->new_of_old[(size_t)idx[i]];
-    if (slot < 0) slot = next++;
-    out->idx[i] = slot;
+  const size_t nf = n_idx / 3;
+  for (size_t s = 0; s < nf; s++) {
+    const size_t f = face_order ? (size_t)(*face_order)[s] : s;
+    for (int k = 0; k < 3; k++) {
+      int32_t& slot = out->new_of_old[(size_t)idx[3 * f + k]];
+      if (slot < 0) slot = next++;
+    }
   }
+  for (size_t i = 0; i < n_idx; i++) out->idx[i] = out->new_of_old[(size_t)idx[i]];
   for (int v = 0; v < count; v++)
     if (out->new_of_old[(size_t)v] < 0) out->new_of_old[(size_t)v] = next++;
   out->active = true;
+}
+
+// Raster order of the faces (slot -> face).  Face ids are outputs and keep their meaning; the ORDER in which
+// raster_kernel walks the faces is free (the depth test is an order-independent atomicMin), and mesh files
+// come in any order (a subdivided icosphere's consecutive faces lie all over the sphere).  Faces are sorted
+// by (dominant axis and sign of the geometric normal, Morton code of the centroid): a warp's 32 consecutive
+// faces then form a compact patch of similar orientation — its projected vertices, its visibility-buffer
+// pixels and its attribute records are neighbours in memory, and the patch as a whole faces towards or away
+// from the camera, which is what the two-pass occlusion ordering (raster_kernels.cuh) classifies.
+uint32_t MortonSpread10(uint32_t v) {
+  v &= 1023u;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+
+void BuildFaceOrder(const float* vtx, const int32_t* idx, int F, std::vector<int32_t>* slot_face) {
+  float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  std::vector<float> cen((size_t)F * 3);
+  std::vector<uint8_t> bucket((size_t)F);
+  for (int f = 0; f < F; f++) {
+    const float* a = vtx + 3 * (size_t)idx[3 * (size_t)f];
+    const float* b = vtx + 3 * (size_t)idx[3 * (size_t)f + 1];
+    const float* c = vtx + 3 * (size_t)idx[3 * (size_t)f + 2];
+    const float u[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, v[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+    const float n[3] = {u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0]};
+    int ax = 0;
+    if (fabsf(n[1]) > fabsf(n[ax])) ax = 1;
+    if (fabsf(n[2]) > fabsf(n[ax])) ax = 2;
+    bucket[(size_t)f] = (uint8_t)(2 * ax + (n[ax] < 0.f ? 1 : 0));
+    for (int k = 0; k < 3; k++) {
+      const float m = (a[k] + b[k] + c[k]) * (1.0f / 3.0f);
+      cen[3 * (size_t)f + k] = m;
+      if (m == m && fabsf(m) < FLT_MAX) {  // finite
+        lo[k] = std::min(lo[k], m);
+        hi[k] = std::max(hi[k], m);
+      }
+    }
+  }
+  float scale[3];
+  for (int k = 0; k < 3; k++) scale[k] = hi[k] > lo[k] ? 1023.0f / (hi[k] - lo[k]) : 0.f;
+  std::vector<uint64_t> key((size_t)F), tmp((size_t)F);
+  for (int f = 0; f < F; f++) {
+    uint32_t q[3];
+    for (int k = 0; k < 3; k++) {
+      const float t = (cen[3 * (size_t)f + k] - lo[k]) * scale[k];
+      q[k] = (t >= 0.f && t <= 1023.f) ? (uint32_t)t : 0u;  // NaN / inf -> 0
+    }
+    const uint64_t code = ((uint64_t)bucket[(size_t)f] << 30) | (MortonSpread10(q[0]) | (MortonSpread10(q[1]) << 1) |
+                                                                   (MortonSpread10(q[2]) << 2));
+    key[(size_t)f] = (code << 31) | (uint64_t)f;  // F < 2^26 (validated)
+  }
+  // LSD radix sort on the 33 code bits (3 passes of 11 bits): stable, so equal codes keep face order
+  for (int pass = 0; pass < 3; pass++) {
+    const int shift = 31 + 11 * pass;
+    std::vector<size_t> count(2049, 0);
+    for (int f = 0; f < F; f++) count[((key[(size_t)f] >> shift) & 2047u) + 1]++;
+    for (int i = 0; i < 2048; i++) count[i + 1] += count[i];
+    for (int f = 0; f < F; f++) tmp[count[(key[(size_t)f] >> shift) & 2047u]++] = key[(size_t)f];
+    key.swap(tmp);
+  }
+  slot_face->resize((size_t)F);
+  for (int f = 0; f < F; f++) (*slot_face)[(size_t)f] = (int32_t)(key[(size_t)f] & 0x7FFFFFFFu);
 }
 
 void PermuteRows(const float* src, int count, int width, const Reorder& ro, std::vector<float>* dst) {
@@ -307,6 +381,7 @@ int EnsureFrame(ugu_b200_rasterizer* r, int W, int H, int B, cudaStream_t st) {
   if ((rc = Grow(r, &r->proj, (size_t)B * Vpad * sizeof(float4)))) return rc;
   if ((rc = Grow(r, &r->q_face, (size_t)B * Fq * 4))) return rc;
   if ((rc = Grow(r, &r->q_job, (size_t)B * Fq * 8))) return rc;
+  if ((rc = Grow(r, &r->order, (size_t)B * (((size_t)r->mesh.F + 255) / 256 + 1) * 4))) return rc;
   if (P != r->vis_pixels || (size_t)B > r->vis_slabs) {
     // the slabs of one size are contiguous, so a new size or more slabs re-fills the whole area
     if ((rc = Grow(r, &r->vis, (size_t)B * P * 8))) return rc;
@@ -352,10 +427,15 @@ void MakeViewParams(const ugu_b200_camera* cam, ViewParams* vp) {
   memcpy(vp->w2c_R, cam->w2c_R, sizeof(vp->w2c_R));
   memcpy(vp->w2c_t, cam->w2c_t, sizeof(vp->w2c_t));
   memcpy(vp->c2w_R, cam->c2w_R, sizeof(vp->c2w_R));
+  for (int i = 0; i < 3; i++)  // camera centre (ordering heuristic only: exactness is irrelevant)
+    vp->eye[i] = -(cam->c2w_R[3 * i] * cam->w2c_t[0] + cam->c2w_R[3 * i + 1] * cam->w2c_t[1] +
+                   cam->c2w_R[3 * i + 2] * cam->w2c_t[2]);
 }
 
 int g_num_sms = 148;
 int g_binned_ctas_per_sm = 8;
+constexpr int kTwoPassMinFaces = 200000;
+int g_ordered_minb = 5;  // CTAs/SM of the ordered raster kernel (UGU_B200_RASTER_MINB: 5 = 48 registers, 6 = 40 + spills)
 
 // Launch with programmatic stream serialization (PDL): the kernel may be scheduled into the tail of
 // its predecessor on the stream; it synchronises on the predecessor's results itself (pdl_wait()).
@@ -398,6 +478,8 @@ FrameDev MakeFrame(const ugu_b200_rasterizer* r, int W, int H) {
   fr.q_face = (int*)r->q_face.p;
   fr.q_job = (unsigned long long*)r->q_job.p;
   fr.coop_max = 0;
+  fr.order = nullptr;
+  fr.s_order = ((size_t)r->mesh.F + 255) / 256;
   fr.s_proj = std::max<size_t>(((size_t)r->mesh.V + 3) & ~size_t(3), 4);
   fr.s_ray_dx = (size_t)W;
   fr.s_ray_dy = (size_t)H;
@@ -458,6 +540,13 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   // the machine holds (F < ~600k) mid-size triangles are better spread over the whole GPU by the
   // queue (measured: config 4, 10M faces, 1.17 -> 0.93 ms with 32; spot, 5.9k faces, 33 -> 38 us).
   fr.coop_max = r->coop_max > 0 ? r->coop_max : (r->mesh.F >= 4 * 32 * 32 * g_num_sms ? 32 : 16);
+  // Occlusion ordering of raster_kernel (raster_kernels.cuh): camera-facing blocks first, the others after them
+  // with the triangles dropped that are provably behind what is already stored.  Pays once the face warps
+  // outnumber what the machine holds at a time (the ordered kernel cannot prefetch its indices under the
+  // predecessor's tail).
+  const bool two_launch = r->mesh.grp != nullptr && r->two_pass == 2;
+  if (!two_launch && r->mesh.grp != nullptr && (r->two_pass >= 0 ? r->two_pass != 0 : r->mesh.F >= kTwoPassMinFaces))
+    fr.order = (int*)r->order.p;
   const MeshDev& m = r->mesh;
   const size_t P = (size_t)W * H;
   const ShadeParams sp = MakeShade(r, dout, P, first_view);
@@ -465,13 +554,20 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   const unsigned ny = (unsigned)n;
   {
     StageTimer t(r, st, UGU_B200_STAGE_VERTEX);
-    const size_t threads = std::max<size_t>((size_t)m.V, (size_t)W + H);
+    const size_t threads = std::max<size_t>(std::max<size_t>((size_t)m.V, (size_t)W + H), ((size_t)m.F + 255) / 256);
     CU_TRY(r, LaunchView(vertex_kernel_b<NV>, dim3(Blocks(threads, 256)), 256, st, pdl, vb, n, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
     // 6 resident CTAs per SM (40 registers, no spills) measured 2-4 % faster than 4 on every config
-    CU_TRY(r, LaunchView(raster_kernel<1, 6, NV>, dim3(Blocks((size_t)m.F, 8 * 32), ny), 256, st, pdl, vb, m, fr));
+    const dim3 grid(Blocks((size_t)m.F, 8 * 32), ny);
+    if (two_launch) {
+      CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 2>, grid, 256, st, pdl, vb, m, fr));
+      CU_TRY(r, LaunchView(raster_kernel<1, 5, NV, 3>, grid, 256, st, pdl, vb, m, fr));
+      r->stats.kernel_launches++;
+    } else if (fr.order && g_ordered_minb == 6) CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 1>, grid, 256, st, pdl, vb, m, fr));
+    else if (fr.order) CU_TRY(r, LaunchView(raster_kernel<1, 5, NV, 1>, grid, 256, st, pdl, vb, m, fr));
+    else CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 0>, grid, 256, st, pdl, vb, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
@@ -754,6 +850,8 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
     r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
   }
   if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
+  if (const char* e = getenv("UGU_B200_TWOPASS")) r->two_pass = std::max(0, std::min(2, atoi(e)));
+  if (const char* e = getenv("UGU_B200_RASTER_MINB")) g_ordered_minb = atoi(e) == 6 ? 6 : 5;
   if (const char* e = getenv("UGU_B200_COPY_THREADS")) r->copy_threads = std::max(1, std::min(atoi(e), 64));
   if (const char* e = getenv("UGU_B200_BATCH")) r->max_batch = std::max(1, std::min(atoi(e), (int)kMaxBatch));
   auto fail = [&](cudaError_t err, const char* what) {
@@ -794,7 +892,7 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   if (r->stream) cudaStreamSynchronize(r->stream);
   if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
   FreeMesh(r);
-  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters,
+  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters, &r->order,
                     &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask,
                     &r->vis_tmp, &r->vis_in, &r->vis_acc,
                     &r->vt_pos, &r->vt_nrm, &r->vt_idx, &r->vt_acc, &r->vt_owner, &r->vt_vvis, &r->vt_vrec,
@@ -880,8 +978,13 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
   const int32_t* h_vidx = d->vertex_indices;
   const int32_t* h_nidx = d->normal_indices;
   const int32_t* h_uvidx = d->uv_indices;
+  // raster order of the faces (UGU_B200_FACE_ORDER=0: the order of the file)
+  std::vector<int32_t> slot_face;
+  if (F > 0 && V > 0 && !(getenv("UGU_B200_FACE_ORDER") && atoi(getenv("UGU_B200_FACE_ORDER")) == 0))
+    BuildFaceOrder(d->vertices, d->vertex_indices, F, &slot_face);
+  const std::vector<int32_t>* order = slot_face.empty() ? nullptr : &slot_face;
   if (reorder && F > 0 && V > 0) {
-    BuildReorder(d->vertex_indices, (size_t)F * 3, V, &ro_v);
+    BuildReorder(d->vertex_indices, (size_t)F * 3, V, &ro_v, order);
     PermuteRows(d->vertices, V, 3, ro_v, &pos_p);
     h_vertices = pos_p.data();
     h_vidx = ro_v.idx.data();
@@ -890,13 +993,13 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
       h_colors = col_p.data();
     }
     if (d->normal_indices && d->num_normals > 0 && d->normals) {
-      BuildReorder(d->normal_indices, (size_t)F * 3, d->num_normals, &ro_n);
+      BuildReorder(d->normal_indices, (size_t)F * 3, d->num_normals, &ro_n, order);
       PermuteRows(d->normals, d->num_normals, 3, ro_n, &nrm_p);
       h_normals = nrm_p.data();
       h_nidx = ro_n.idx.data();
     }
     if (d->uv_indices && d->num_uv > 0 && d->uv) {
-      BuildReorder(d->uv_indices, (size_t)F * 3, d->num_uv, &ro_uv);
+      BuildReorder(d->uv_indices, (size_t)F * 3, d->num_uv, &ro_uv, order);
       PermuteRows(d->uv, d->num_uv, 2, ro_uv, &uv_p);
       h_uv = uv_p.data();
       h_uvidx = ro_uv.idx.data();
@@ -974,6 +1077,35 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     repack_vec3_to_planes<<<Blocks(F, 256), 256, 0, st>>>((const float*)t, F, fx, fy, fz);
     r->stats.kernel_launches++;
     m.fn_x = fx; m.fn_y = fy; m.fn_z = fz;
+  }
+  // the streams of raster_kernel in raster order, and the group records of its two-pass ordering
+  m.r_idx0 = i0; m.r_idx1 = i1; m.r_idx2 = i2;
+  m.r_fn_x = m.fn_x; m.r_fn_y = m.fn_y; m.r_fn_z = m.fn_z;
+  if (order) {
+    int* planes[4] = {nullptr, nullptr, nullptr, nullptr};
+    for (auto& pl : planes) UP_TRY(MeshAlloc(r, &pl, F));
+    UP_TRY([&]() -> int {
+      CU_TRY(r, cudaMemcpyAsync(planes[3], slot_face.data(), (size_t)F * 4, cudaMemcpyHostToDevice, st));
+      return UGU_B200_OK;
+    }());
+    gather_planes<<<Blocks(F, 256), 256, 0, st>>>(planes[3], F, i0, i1, i2, planes[0], planes[1], planes[2]);
+    r->stats.kernel_launches++;
+    m.r_idx0 = planes[0]; m.r_idx1 = planes[1]; m.r_idx2 = planes[2]; m.r_face = planes[3];
+    if (m.num_face_normals > 0) {
+      float* fp[3] = {nullptr, nullptr, nullptr};
+      for (auto& pl : fp) UP_TRY(MeshAlloc(r, &pl, F));
+      gather_planes<<<Blocks(F, 256), 256, 0, st>>>(planes[3], F, m.fn_x, m.fn_y, m.fn_z, fp[0], fp[1], fp[2]);
+      r->stats.kernel_launches++;
+      m.r_fn_x = fp[0]; m.r_fn_y = fp[1]; m.r_fn_z = fp[2];
+    }
+  }
+  if (F > 0 && V > 0) {
+    float4* grp = nullptr;
+    const size_t blocks = ((size_t)F + 255) / 256;
+    UP_TRY(MeshAlloc(r, &grp, blocks));
+    block_records_kernel<<<(unsigned)blocks, 256, 0, st>>>(m.pos4, m.r_idx0, m.r_idx1, m.r_idx2, F, grp);
+    r->stats.kernel_launches++;
+    m.grp = grp;
   }
   void* nrm_aos = nullptr;
   void* col_aos = nullptr;

@@ -47,6 +47,7 @@ struct ViewParams {
   float w2c_R[9];
   float w2c_t[3];
   float c2w_R[9];
+  float eye[3];  // camera centre in world space (-c2w_R * w2c_t); only the group ordering heuristic reads it
 };
 
 // A batch of views rendered by ONE launch set (blockIdx.y = view of the batch; the vertex kernel loops
@@ -74,6 +75,16 @@ struct MeshDev {
   const float4* nrm4;
   const float4* col4;
   const float4* vattr;  // optional merged per-vertex record {nx ny nz 0, r g b 0} (32 B), see upload
+  // raster order (slot -> face, see BuildFaceOrder in raster_api.cu): the streams raster_kernel reads with
+  // coalesced loads, and the face id of each slot (NULL: slot == face)
+  const int* r_idx0;
+  const int* r_idx1;
+  const int* r_idx2;
+  const float* r_fn_x;
+  const float* r_fn_y;
+  const float* r_fn_z;
+  const int* r_face;
+  const float4* grp;    // per block of 256 consecutive slots: {sum of face normals, their dot with the mean centroid}
   const int4* frec;
   const int4* uvidx;
   const float2* uv2;
@@ -90,12 +101,13 @@ struct FrameDev {
   int* q_face;                   // F
   unsigned long long* q_job;     // F : first tile job of each queued triangle
   int coop_max;                  // bbox sample count up to which a triangle takes the cooperative path
+  int* order;                    // occlusion ordering of raster_kernel: block (256 slots) processed by CTA i; NULL = off
   // element strides between the per-view slabs of a batch (view v uses base + v * stride); the
   // counters slab of a view is 8 words: [0] packed large queue counter, [1] hazard fragments, [2] chunk
-  // cursor, [4] / [5] the view's (queue, hazards) as saved by resolve_kernel for the host.  Word 6 of
-  // slab 0: hazard fragments summed over every view since the handle was created (never reset; the
-  // host reports deltas).
-  unsigned long long s_proj, s_ray_dx, s_ray_dy, s_vis, s_q;
+  // cursor, [3] / [7] camera-facing / deferred blocks of the occlusion ordering (vertex kernel), [4] / [5] the
+  // view's (queue, hazards) as saved by resolve_kernel for the host.  Word 6 of slab 0: hazard fragments
+  // summed over every view since the handle was created (never reset; the host reports deltas).
+  unsigned long long s_proj, s_ray_dx, s_ray_dy, s_vis, s_q, s_order;
 };
 constexpr int kCounterSlab = 8;
 constexpr int kTotalsOffset = 6;
@@ -110,6 +122,7 @@ __device__ __forceinline__ FrameDev frame_view(const FrameDev& b, int view) {
   f.counters = b.counters + v * (unsigned long long)kCounterSlab;
   f.q_face = b.q_face + v * b.s_q;
   f.q_job = b.q_job + v * b.s_q;
+  if (b.order) f.order = b.order + v * b.s_order;
   return f;
 }
 
@@ -241,6 +254,12 @@ __device__ __forceinline__ void vis_update(unsigned long long* __restrict__ vis,
   if (key < seen) atomicMin(vis + pix, key);
 }
 
+// Occlusion ordering (see raster_kernel): does the block face away from the camera?
+__device__ __forceinline__ bool group_deferred(const ViewParams& vp, const float4& g) {
+  // sum_f n_f . (centroid - eye) > 0: the group faces away from the camera (NaN -> not deferred)
+  return g.w - ((g.x * vp.eye[0] + g.y * vp.eye[1]) + g.z * vp.eye[2]) > 0.0f;
+}
+
 // ---------------------------------------------------------------------------------------------
 // K1: vertex transform + projection (rasterizer.cc:125-136, camera.h:380-387) and the per-view ray
 // numerator tables.
@@ -284,6 +303,31 @@ __global__ void __launch_bounds__(256) vertex_kernel_b(const ViewBatch<NV> vb, c
     else if (t < vp.W + vp.H)
       fr.ray_dy[(unsigned long long)v * fr.s_ray_dy + (t - vp.W)] = ((float)(t - vp.W) - vp.cy) / vp.fy;
   }
+  const int nblocks = (m.F + 255) >> 8;
+  if (fr.order == nullptr || (t & ~31) >= nblocks) return;
+  // Occlusion ordering of raster_kernel: camera-facing blocks fill the view's list from the front, the others
+  // from the back (one atomicAdd per warp and list; a warp's 32 consecutive blocks stay neighbours).
+  const bool blk_valid = t < nblocks;
+  const float4 rec = blk_valid ? __ldg(m.grp + t) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int v = 0; v < n; v++) {
+    const bool def = blk_valid && group_deferred(vb.v[v], rec);
+    const unsigned bf = __ballot_sync(0xffffffffu, blk_valid && !def), bd = __ballot_sync(0xffffffffu, def);
+    unsigned long long* cnt = fr.counters + (unsigned long long)v * kCounterSlab;
+    unsigned basef = 0u, based = 0u;
+    if (lane == 0u) {
+      if (bf) basef = (unsigned)atomicAdd(cnt + 3, (unsigned long long)__popc(bf));
+      if (bd) based = (unsigned)atomicAdd(cnt + 7, (unsigned long long)__popc(bd));
+    }
+    basef = __shfl_sync(0xffffffffu, basef, 0);
+    based = __shfl_sync(0xffffffffu, based, 0);
+    int* order = fr.order + (unsigned long long)v * fr.s_order;
+    if (blk_valid) {
+      if (def) order[nblocks - 1 - (int)(based + __popc(bd & lt))] = t;
+      else order[basef + __popc(bf & lt)] = t;
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -310,6 +354,55 @@ __device__ __forceinline__ bool tri_bounds(const Tri& t, const ViewParams& vp, i
   y1 = min(vp.H - 1, sat_int(floorf(ymax)));
   if (fabsf(t.area) < 1.17549435e-38f) return false;
   return x1 >= x0 && y1 >= y0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Occlusion ordering (PASS 1 of raster_kernel).
+//
+// Back faces take part in the reference's depth test (rasterizer.cc:198-200,228-237), so nothing may be
+// culled by orientation.  But ORDER is free — the 64-bit atomicMin is order independent — and a fragment
+// that provably loses against what is already stored need not be produced at all.  The vertex kernel sorts
+// the blocks of 256 faces (= one CTA) into two lists per view: blocks whose summed face normal points
+// towards the camera (on a closed mesh: the visible side) are dispatched first, the others ("deferred")
+// after them, and a deferred block drops a triangle in phase A — before its shared-memory record, its bbox
+// samples and its fragments exist — when
+//   (i)  |area| >= 0.004 * ex * ey   (ex, ey = extents of its image-space bbox), and
+//   (ii) every pixel of its (at most 4 x 4) bbox already stores a depth zs < 0.998 * min(z0, z1, z2).
+// Whatever camera-facing block is still in flight when a deferred block looks only makes (ii) fail more
+// often; which blocks are deferred, and when, affects speed only.
+// Proof that every fragment of such a triangle loses.  Let E = ex * ey, u = 2^-24.  For an integer sample p
+// inside the bbox all coordinate differences are bounded by ex / ey, so each float edge function w_k and
+// `area` carry an absolute error <= 8 u E, and (the three exact edge functions sum to the exact area)
+// the float sum s3 = (w0 + w1) + w2 differs from `area` by <= 44 u E <= 0.001 |area| under (i) (44 u / 0.004
+// = 6.6e-4).  So a covered sample (all w_k >= 0 or all <= 0) cannot have all w_k == 0, `area` has the sign of
+// the w_k, and s3 <= 1.001 |area|: the premises of raster_fragments' early-out, whose bound gives
+// z >= 0.998999 * min z_k > 0.998f * min z_k > zs for the reference's z = 1 / sum_k (w_k / area / z_k).  Stored
+// depths only decrease, so the fragment is strictly behind the final winner whatever its facing (and it is
+// not a hazard fragment: zs >= FLT_MIN).
+// ---------------------------------------------------------------------------------------------
+
+// 0.998 * min z of a triangle that satisfies (i), as float bits (positive floats order like unsigned
+// integers; EMPTY pixels read 0xFFFFFFFF and never pass); 0 when the triangle may not be dropped.
+__device__ __forceinline__ unsigned tri_cull_bits(const Tri& t) {
+  const float ex = fmaxf(fmaxf(t.v0x, t.v1x), t.v2x) - fminf(fminf(t.v0x, t.v1x), t.v2x);
+  const float ey = fmaxf(fmaxf(t.v0y, t.v1y), t.v2y) - fminf(fminf(t.v0y, t.v1y), t.v2y);
+  const float E = ex * ey;
+  const float zmin = fminf(fminf(t.v0z, t.v1z), t.v2z);
+  if (!(E > 1e-25f && E < 1e25f && fabsf(t.area) >= 0.004f * E && zmin > 1e-30f && zmin < 1e30f)) return 0u;
+  return __float_as_uint(0.998f * zmin);
+}
+
+// (ii): is every pixel of [x0, x0 + nx) x [y0, y0 + ny), nx, ny <= 4, nearer than `zbits`?
+__device__ __forceinline__ bool bbox_occluded(const FrameDev& fr, int W, int x0, int y0, int nx, int ny,
+                                              unsigned zbits) {
+  const int xa = x0 + min(1, nx - 1), xb = x0 + min(2, nx - 1), xc = x0 + nx - 1;
+  for (int yy = y0; yy < y0 + ny; yy++) {
+    // high word of the packed key = float bits of the stored depth (plain loads: per-view data)
+    const unsigned* row = reinterpret_cast<const unsigned*>(fr.vis + (size_t)yy * W) + 1;
+    const unsigned m = max(max(row[2 * x0], row[2 * xa]), max(row[2 * xb], row[2 * xc]));
+    if (m >= zbits) return false;
+  }
+  return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -415,9 +508,12 @@ __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const Mes
   }
 }
 
-template <int HALVES, int MINB, int NV>
+// PASS 0: CTA i takes block i.  PASS 1: the occlusion ordering above — CTA i takes block order[i] and applies
+// the occlusion test when i is past the camera-facing blocks (HALVES == 1).
+template <int HALVES, int MINB, int NV, int PASS>
 __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> vb, const MeshDev m,
                                                            const FrameDev fr0) {
+  static_assert(PASS == 0 || HALVES == 1, "block records are per 8 warps x 32 faces");
   const int view = (NV == 1) ? 0 : (int)blockIdx.y;
   const ViewParams& vp = vb.v[view];
   const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
@@ -425,13 +521,29 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
   WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const int base = (int)((blockIdx.x * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
   pdl_launch_dependents();
+  unsigned blk = blockIdx.x;
+  bool deferred = false;
+  if (PASS == 1) {
+    pdl_wait();  // the block order of this view comes from the vertex kernel
+    blk = (unsigned)fr.order[blockIdx.x];
+    deferred = (unsigned long long)blockIdx.x >= fr.counters[3];
+  }
+  if (PASS >= 2) {  // two launches over all blocks: PASS 2 takes the camera-facing ones, PASS 3 the others
+    deferred = group_deferred(vp, __ldg(m.grp + blk));
+    if (deferred != (PASS == 3)) {
+      // not this pass's block.  CTA 0 waits all the same: a grid none of whose threads waited could complete
+      // before its predecessor and break the chain for its successor.
+      if (blockIdx.x == 0) pdl_wait();
+      return;
+    }
+  }
+  const int base = (int)((blk * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
   if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
   const bool has_fn = m.num_face_normals > 0;
 
   // ---- Phase A ---------------------------------------------------------------------------------
-  int fidx[HALVES];
+  int fidx[HALVES], face[HALVES];
   int i0[HALVES], i1[HALVES], i2[HALVES];
   float4 pa[HALVES], pb[HALVES], pc[HALVES];
   float fnx[HALVES], fny[HALVES], fnz[HALVES];
@@ -439,19 +551,22 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
   for (int h = 0; h < HALVES; h++) {
     fnx[h] = fny[h] = fnz[h] = 0.f;
     i0[h] = i1[h] = i2[h] = 0;
-    fidx[h] = base + h * 32 + (int)lane;
+    fidx[h] = base + h * 32 + (int)lane;  // slot in raster order
+    face[h] = fidx[h];
     if (fidx[h] < m.F) {  // immutable mesh data: may be read before the vertex kernel has finished
-      i0[h] = __ldg(m.idx0 + fidx[h]);
-      i1[h] = __ldg(m.idx1 + fidx[h]);
-      i2[h] = __ldg(m.idx2 + fidx[h]);
+      i0[h] = __ldg(m.r_idx0 + fidx[h]);
+      i1[h] = __ldg(m.r_idx1 + fidx[h]);
+      i2[h] = __ldg(m.r_idx2 + fidx[h]);
+      if (PASS != 0 && deferred) continue;  // face id and normal only for the triangles that survive
+      if (m.r_face) face[h] = __ldg(m.r_face + fidx[h]);
       if (has_fn) {  // same round trip as the indices, not a third dependent one
-        fnx[h] = __ldg(m.fn_x + fidx[h]);
-        fny[h] = __ldg(m.fn_y + fidx[h]);
-        fnz[h] = __ldg(m.fn_z + fidx[h]);
+        fnx[h] = __ldg(m.r_fn_x + fidx[h]);
+        fny[h] = __ldg(m.r_fn_y + fidx[h]);
+        fnz[h] = __ldg(m.r_fn_z + fidx[h]);
       }
     }
   }
-  pdl_wait();  // projected vertices of this view; visibility buffer / counters left clean by resolve
+  if (PASS != 1) pdl_wait();  // projected vertices of this view; visibility buffer / counters left clean by resolve
 #pragma unroll
   for (int h = 0; h < HALVES; h++) {
     if (fidx[h] < m.F) {
@@ -479,11 +594,23 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
         const long long ns = (long long)nx * ny;
         if (ns <= (long long)fr.coop_max) {
           cnt = (int)ns;
+          if (PASS != 0 && deferred && nx <= 4 && ny <= 4) {
+            const unsigned zbits = tri_cull_bits(t);
+            if (zbits != 0u && bbox_occluded(fr, vp.W, x0, y0, nx, ny, zbits)) cnt = 0;
+          }
         } else {
           const unsigned long long njobs = (unsigned long long)((nx + kJobW - 1) / kJobW) *
                                            (unsigned long long)((ny + kJobH - 1) / kJobH);
           my[h] = (1ull << kQueueJobBits) | njobs;
         }
+      }
+    }
+    if (PASS != 0 && deferred && (cnt > 0 || my[h] != 0ull)) {
+      if (m.r_face) face[h] = __ldg(m.r_face + f);
+      if (has_fn) {
+        fnx[h] = __ldg(m.r_fn_x + f);
+        fny[h] = __ldg(m.r_fn_y + f);
+        fnz[h] = __ldg(m.r_fn_z + f);
       }
     }
     // slot = rank among the recorded triangles; start = exclusive prefix of the sample counts
@@ -497,7 +624,7 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
     if (cnt > 0) {
       const int slot = nslots + __popc(rec & lt_mask);
       S.a[slot] = make_float4(t.v0x, t.v0y, t.v1x, t.v1y);
-      S.b[slot] = make_float4(t.v2x, t.v2y, __int_as_float(x0 | (y0 << 16)), __int_as_float(f));
+      S.b[slot] = make_float4(t.v2x, t.v2y, __int_as_float(x0 | (y0 << 16)), __int_as_float(face[h]));
       S.c[slot] = make_float4(t.v0z, t.v1z, t.v2z, t.area);
       // g = c2w_R^T * fn and the facing threshold (see facing_backface)
       S.d[slot] = make_float4(
@@ -532,7 +659,7 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
       for (int h = 0; h < HALVES; h++) {
         if (my[h] != 0ull) {
           const unsigned qslot = (unsigned)(excl >> kQueueJobBits);
-          fr.q_face[qslot] = fidx[h];
+          fr.q_face[qslot] = face[h];
           fr.q_job[qslot] = excl & kQueueJobMask;
           excl += my[h];
         }
@@ -987,6 +1114,8 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> 
     fr.counters[0] = 0ull;
     fr.counters[1] = 0ull;
     fr.counters[2] = 0ull;
+    fr.counters[3] = 0ull;
+    fr.counters[7] = 0ull;
   }
   const bool cull = sp.backface_culling != 0;
   using Stage = ResolveStage<COLOR, NMODE>;
@@ -1223,6 +1352,60 @@ __global__ void build_vertex_attr(const float* __restrict__ nrm, const float* __
 __global__ void repack_rgb_to_rgba(const uint8_t* __restrict__ rgb, size_t n, uchar4* __restrict__ out) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = make_uchar4(rgb[i * 3 + 0], rgb[i * 3 + 1], rgb[i * 3 + 2], 255);
+}
+
+// dst plane k [slot] = src plane k [slot_face[slot]]
+template <typename T>
+__global__ void gather_planes(const int* __restrict__ slot_face, int n, const T* __restrict__ a,
+                              const T* __restrict__ b, const T* __restrict__ c, T* __restrict__ oa,
+                              T* __restrict__ ob, T* __restrict__ oc) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const int f = slot_face[i];
+    oa[i] = a[f];
+    ob[i] = b[f];
+    oc[i] = c[f];
+  }
+}
+
+// Block records of the occlusion ordering: a CTA per 256 consecutive slots (= one raster CTA); {sum of the
+// geometric (area-weighted) face normals, its dot product with the mean face centroid}.
+__global__ void __launch_bounds__(256) block_records_kernel(const float4* __restrict__ pos4,
+                                                            const int* __restrict__ i0, const int* __restrict__ i1,
+                                                            const int* __restrict__ i2, int F,
+                                                            float4* __restrict__ grp) {
+  __shared__ float red[8][7];
+  const int f = (int)(blockIdx.x * 256u + threadIdx.x);
+  const int lane = (int)(threadIdx.x & 31u), warp = (int)(threadIdx.x >> 5);
+  float v[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // normal, centroid sum, count
+  if (f < F) {
+    const float4 a = pos4[i0[f]], b = pos4[i1[f]], c = pos4[i2[f]];
+    const float ux = b.x - a.x, uy = b.y - a.y, uz = b.z - a.z;
+    const float wx = c.x - a.x, wy = c.y - a.y, wz = c.z - a.z;
+    v[0] = uy * wz - uz * wy;
+    v[1] = uz * wx - ux * wz;
+    v[2] = ux * wy - uy * wx;
+    v[3] = (a.x + b.x + c.x) * (1.0f / 3.0f);
+    v[4] = (a.y + b.y + c.y) * (1.0f / 3.0f);
+    v[5] = (a.z + b.z + c.z) * (1.0f / 3.0f);
+    v[6] = 1.f;
+  }
+#pragma unroll
+  for (int k = 0; k < 7; k++) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], d);
+    if (lane == 0) red[warp][k] = v[k];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t[7];
+    for (int k = 0; k < 7; k++) {
+      t[k] = 0.f;
+      for (int w = 0; w < 8; w++) t[k] += red[w][k];
+    }
+    const float inv = 1.0f / t[6];
+    grp[blockIdx.x] = make_float4(t[0], t[1], t[2], (t[0] * (t[3] * inv) + t[1] * (t[4] * inv)) + t[2] * (t[5] * inv));
+  }
 }
 
 __global__ void fill_u64(unsigned long long* __restrict__ p, size_t n, unsigned long long v) {
