@@ -442,3 +442,33 @@ def test_two_pass_occluded_debris(two_pass, sliver, culling):
         got = run.render(cam, opt)
         util.assert_parity(got, want, strict=True, what=f"debris {w}x{h}")
     assert (want["face_id"] >= 0).sum() > 1000
+
+
+# ---- per-tile triangle lists (tile_kernel), off by default: forced here so the path stays exact ---------------------
+@pytest.fixture
+def tile_lists(monkeypatch):
+    monkeypatch.setenv("UGU_B200_TILES", "1")
+
+
+@pytest.mark.parametrize("name", [n for n in util.golden_names() if n.startswith(("spot", "soup", "kat"))])
+def test_tile_lists_vs_reference_golden(tile_lists, name):
+    mesh, cam, opt, want, _ = util.load_golden(name)
+    run = util.CudaRunner(mesh, opt)
+    got = run.render(cam, opt)
+    util.assert_parity(got, want, strict=True, color_lsb=_lsb(opt), what="tile lists " + name)
+    # idempotent: the lists are left empty
+    again = run.render(cam, opt)
+    for k in got:
+        assert np.array_equal(util.bits(got[k]), util.bits(again[k])), k
+
+
+def test_tile_lists_overflow_and_huge_triangles(tile_lists):
+    """More than kTileCap triangles on one tile (they fall back to the tile-job queue) next to screen-filling ones
+    (more than 3 x 3 tiles: queue), at a size with ragged border tiles."""
+    mesh = cases.random_soup(6000, seed=41, big_fraction=0.05)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, shading_normal=ShadingNormal.kFace)
+    run = util.CudaRunner(mesh, opt)
+    port = OraclePort(mesh)
+    for (w, h) in ((97, 61), (333, 207)):
+        cam = PinholeCamera(w, h, meshgen.look_at_c2w((0.1, 0.0, 0.0), (0.0, 0.1, 1.0), (0, -1, 0)), fov_y_deg=50.0)
+        util.assert_parity(run.render(cam, opt), port.render(cam.to_native(), opt), strict=True, what=f"tiles {w}x{h}")

@@ -58,7 +58,8 @@ struct ugu_b200_rasterizer {
   std::vector<void*> mesh_allocs;  // everything owned by the current mesh
 
   // per-view scratch
-  DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters, order;
+  DevBuf proj, ray_dx, ray_dy, vis, q_face, q_job, counters, order, tile_cnt, tile_bin;
+  size_t tile_slab = 0, tile_slabs = 0;  // tiles per slab / slabs known to hold zero counts
   size_t vis_pixels = 0;  // pixels per visibility slab
   size_t vis_slabs = 0;   // slabs known to hold EMPTY
   int max_batch = 0;      // views per launch set of render_batch (0 = adaptive, UGU_B200_BATCH overrides)
@@ -69,6 +70,7 @@ struct ugu_b200_rasterizer {
   int coop_max = 0;  // bbox samples up to which a triangle is rasterised inside raster_kernel; larger
                      // ones go to the tile-job queue.  0 = adaptive (see RenderView)
   bool use_pdl = true;  // programmatic dependent launch of the per-view kernels (UGU_B200_PDL=0 disables)
+  int tiles = -1;       // per-tile triangle lists for large triangles (tile_kernel): -1 = by mesh size, 0 / 1 forced (UGU_B200_TILES)
   int two_pass = -1;    // occlusion ordering of raster_kernel: -1 = by mesh size, 0 / 1 forced (UGU_B200_TWOPASS)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
@@ -382,6 +384,16 @@ int EnsureFrame(ugu_b200_rasterizer* r, int W, int H, int B, cudaStream_t st) {
   if ((rc = Grow(r, &r->q_face, (size_t)B * Fq * 4))) return rc;
   if ((rc = Grow(r, &r->q_job, (size_t)B * Fq * 8))) return rc;
   if ((rc = Grow(r, &r->order, (size_t)B * (((size_t)r->mesh.F + 255) / 256 + 1) * 4))) return rc;
+  {
+    const size_t NT = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
+    if (NT != r->tile_slab || (size_t)B > r->tile_slabs) {
+      if ((rc = Grow(r, &r->tile_cnt, (size_t)B * NT * 4))) return rc;
+      if ((rc = Grow(r, &r->tile_bin, (size_t)B * NT * kTileCap * 4))) return rc;
+      CU_TRY(r, cudaMemsetAsync(r->tile_cnt.p, 0, (size_t)B * NT * 4, st));
+      r->tile_slab = NT;
+      r->tile_slabs = (size_t)B;
+    }
+  }
   if (P != r->vis_pixels || (size_t)B > r->vis_slabs) {
     // the slabs of one size are contiguous, so a new size or more slabs re-fills the whole area
     if ((rc = Grow(r, &r->vis, (size_t)B * P * 8))) return rc;
@@ -479,6 +491,10 @@ FrameDev MakeFrame(const ugu_b200_rasterizer* r, int W, int H) {
   fr.q_job = (unsigned long long*)r->q_job.p;
   fr.coop_max = 0;
   fr.order = nullptr;
+  fr.tile_cnt = nullptr;
+  fr.tile_bin = nullptr;
+  fr.tiles_x = (W + kTile - 1) / kTile;
+  fr.s_tiles = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
   fr.s_order = ((size_t)r->mesh.F + 255) / 256;
   fr.s_proj = std::max<size_t>(((size_t)r->mesh.V + 3) & ~size_t(3), 4);
   fr.s_ray_dx = (size_t)W;
@@ -544,6 +560,17 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   // with the triangles dropped that are provably behind what is already stored.  Pays once the face warps
   // outnumber what the machine holds at a time (the ordered kernel cannot prefetch its indices under the
   // predecessor's tail).
+  // Per-tile triangle lists (tile_kernel) for the triangles too large for the cooperative path (the tile-job queue
+  // stays for what overlaps more than 3 x 3 tiles or finds a list full).  OFF unless UGU_B200_TILES=1: measured
+  // against the tile-job queue it loses on the configs it was built for (spot 1024^2, 15.3 M warp
+  // instructions + 2.5 M left in the queue against 11.8 M; 35.7 + 9.9 us against 27.8 us) — a 16 x 16 tile lists ~30
+  // of spot's triangles while ~2 cover any one pixel, so walking every listed triangle at every pixel costs more
+  // than walking each triangle's own bbox.
+  const bool use_tiles = r->tiles > 0;
+  if (use_tiles) {
+    fr.tile_cnt = (int*)r->tile_cnt.p;
+    fr.tile_bin = (int*)r->tile_bin.p;
+  }
   const bool two_launch = r->mesh.grp != nullptr && r->two_pass == 2;
   if (!two_launch && r->mesh.grp != nullptr && (r->two_pass >= 0 ? r->two_pass != 0 : r->mesh.F >= kTwoPassMinFaces))
     fr.order = (int*)r->order.p;
@@ -565,12 +592,18 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
       CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 2>, grid, 256, st, pdl, vb, m, fr));
       CU_TRY(r, LaunchView(raster_kernel<1, 5, NV, 3>, grid, 256, st, pdl, vb, m, fr));
       r->stats.kernel_launches++;
-    } else if (fr.order && g_ordered_minb == 6) CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 1>, grid, 256, st, pdl, vb, m, fr));
+    } else if (fr.order && use_tiles) CU_TRY(r, LaunchView(raster_kernel<1, 4, NV, 1, true>, grid, 256, st, pdl, vb, m, fr));
+    else if (fr.order && g_ordered_minb == 6) CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 1>, grid, 256, st, pdl, vb, m, fr));
     else if (fr.order) CU_TRY(r, LaunchView(raster_kernel<1, 5, NV, 1>, grid, 256, st, pdl, vb, m, fr));
+    else if (use_tiles) CU_TRY(r, LaunchView(raster_kernel<1, 4, NV, 0, true>, grid, 256, st, pdl, vb, m, fr));
     else CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 0>, grid, 256, st, pdl, vb, m, fr));
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
+    if (use_tiles && !two_launch) {
+      CU_TRY(r, LaunchView(tile_kernel<NV>, dim3((unsigned)fr.s_tiles, ny), 256, st, pdl, vb, m, fr));
+      r->stats.kernel_launches++;
+    }
     // persistent: exactly one resident wave, shared by the views of the batch
     const unsigned resident = (unsigned)(g_num_sms * g_binned_ctas_per_sm);
     CU_TRY(r, LaunchView(binned_kernel<NV>, dim3(std::max(1u, (resident + ny - 1) / ny), ny), 128, st, pdl, vb, m, fr));
@@ -851,6 +884,7 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   }
   if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
   if (const char* e = getenv("UGU_B200_TWOPASS")) r->two_pass = std::max(0, std::min(2, atoi(e)));
+  if (const char* e = getenv("UGU_B200_TILES")) r->tiles = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("UGU_B200_RASTER_MINB")) g_ordered_minb = atoi(e) == 6 ? 6 : 5;
   if (const char* e = getenv("UGU_B200_COPY_THREADS")) r->copy_threads = std::max(1, std::min(atoi(e), 64));
   if (const char* e = getenv("UGU_B200_BATCH")) r->max_batch = std::max(1, std::min(atoi(e), (int)kMaxBatch));
@@ -892,7 +926,7 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   if (r->stream) cudaStreamSynchronize(r->stream);
   if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
   FreeMesh(r);
-  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters, &r->order,
+  DevBuf* bufs[] = {&r->proj, &r->ray_dx, &r->ray_dy, &r->vis, &r->q_face, &r->q_job, &r->counters, &r->order, &r->tile_cnt, &r->tile_bin,
                     &r->uv_win, &r->uv_counter, &r->uv_q_face, &r->uv_q_job, &r->uv_rec, &r->uv_in, &r->uv_tex, &r->uv_mask,
                     &r->vis_tmp, &r->vis_in, &r->vis_acc,
                     &r->vt_pos, &r->vt_nrm, &r->vt_idx, &r->vt_acc, &r->vt_owner, &r->vt_vvis, &r->vt_vrec,

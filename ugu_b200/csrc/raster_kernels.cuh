@@ -36,6 +36,10 @@ constexpr int kJobH = 4;
 constexpr int kQueueJobBits = 38;     // packed queue counter: [63:38] entries, [37:0] tile jobs
 constexpr unsigned long long kQueueJobMask = (1ull << kQueueJobBits) - 1ull;
 constexpr int kJobsPerChunk = 16;     // tile jobs a warp claims at a time in the binned kernel
+constexpr int kTile = 16;             // screen tile of the per-tile triangle lists: 16 x 16 pixels = one CTA of tile_kernel
+constexpr int kTileShift = 4;
+constexpr int kTileCap = 64;          // entries per tile list; a triangle that finds a list full takes the tile-job queue
+constexpr int kTileStage = 64;        // triangles staged in shared memory at a time
 
 struct ViewParams {
   int W, H;
@@ -101,13 +105,16 @@ struct FrameDev {
   int* q_face;                   // F
   unsigned long long* q_job;     // F : first tile job of each queued triangle
   int coop_max;                  // bbox sample count up to which a triangle takes the cooperative path
+  int* tile_cnt;                 // per-tile triangle lists (tile_kernel): entries per tile, NULL = off; left 0 by tile_kernel
+  int* tile_bin;                 // kTileCap face ids per tile
+  int tiles_x;                   // tiles per row
   int* order;                    // occlusion ordering of raster_kernel: block (256 slots) processed by CTA i; NULL = off
   // element strides between the per-view slabs of a batch (view v uses base + v * stride); the
   // counters slab of a view is 8 words: [0] packed large queue counter, [1] hazard fragments, [2] chunk
   // cursor, [3] / [7] camera-facing / deferred blocks of the occlusion ordering (vertex kernel), [4] / [5] the
   // view's (queue, hazards) as saved by resolve_kernel for the host.  Word 6 of slab 0: hazard fragments
   // summed over every view since the handle was created (never reset; the host reports deltas).
-  unsigned long long s_proj, s_ray_dx, s_ray_dy, s_vis, s_q, s_order;
+  unsigned long long s_proj, s_ray_dx, s_ray_dy, s_vis, s_q, s_order, s_tiles;
 };
 constexpr int kCounterSlab = 8;
 constexpr int kTotalsOffset = 6;
@@ -123,6 +130,10 @@ __device__ __forceinline__ FrameDev frame_view(const FrameDev& b, int view) {
   f.q_face = b.q_face + v * b.s_q;
   f.q_job = b.q_job + v * b.s_q;
   if (b.order) f.order = b.order + v * b.s_order;
+  if (b.tile_cnt) {
+    f.tile_cnt = b.tile_cnt + v * b.s_tiles;
+    f.tile_bin = b.tile_bin + v * b.s_tiles * (unsigned long long)kTileCap;
+  }
   return f;
 }
 
@@ -510,7 +521,9 @@ __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const Mes
 
 // PASS 0: CTA i takes block i.  PASS 1: the occlusion ordering above — CTA i takes block order[i] and applies
 // the occlusion test when i is past the camera-facing blocks (HALVES == 1).
-template <int HALVES, int MINB, int NV, int PASS>
+// TILES: triangles too large for the cooperative path that overlap at most 3 x 3 screen tiles are appended to the
+// per-tile lists of tile_kernel; the rest (and whatever finds a list full) goes to the tile-job queue.
+template <int HALVES, int MINB, int NV, int PASS, bool TILES = false>
 __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> vb, const MeshDev m,
                                                            const FrameDev fr0) {
   static_assert(PASS == 0 || HALVES == 1, "block records are per 8 warps x 32 faces");
@@ -599,9 +612,36 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
             if (zbits != 0u && bbox_occluded(fr, vp.W, x0, y0, nx, ny, zbits)) cnt = 0;
           }
         } else {
-          const unsigned long long njobs = (unsigned long long)((nx + kJobW - 1) / kJobW) *
-                                           (unsigned long long)((ny + kJobH - 1) / kJobH);
-          my[h] = (1ull << kQueueJobBits) | njobs;
+          bool listed = false;
+          if (TILES) {
+            const int tx0 = x0 >> kTileShift, ty0 = y0 >> kTileShift;
+            const int ntx = (x1 >> kTileShift) - tx0 + 1, nty = (y1 >> kTileShift) - ty0 + 1;
+            if (ntx <= 3 && nty <= 3) {
+              const int fid = (PASS != 0 && deferred && m.r_face) ? __ldg(m.r_face + f) : face[h];
+              int pos[9];  // all the appends in flight together: one round trip, not nine
+#pragma unroll
+              for (int k = 0; k < 9; k++) {
+                const int dx = k % 3, dy = k / 3;
+                pos[k] = (dx < ntx && dy < nty) ? atomicAdd(fr.tile_cnt + (ty0 + dy) * fr.tiles_x + tx0 + dx, 1) : -1;
+              }
+              listed = true;
+#pragma unroll
+              for (int k = 0; k < 9; k++) {
+                const int dx = k % 3, dy = k / 3;
+                if (dx < ntx && dy < nty) {
+                  if (pos[k] < kTileCap)
+                    fr.tile_bin[(size_t)((ty0 + dy) * fr.tiles_x + tx0 + dx) * kTileCap + pos[k]] = fid;
+                  else
+                    listed = false;  // (tiles it did enter may rasterise it twice: the atomicMin is idempotent)
+                }
+              }
+            }
+          }
+          if (!listed) {
+            const unsigned long long njobs = (unsigned long long)((nx + kJobW - 1) / kJobW) *
+                                             (unsigned long long)((ny + kJobH - 1) / kJobH);
+            my[h] = (1ull << kQueueJobBits) | njobs;
+          }
         }
       }
     }
@@ -830,6 +870,117 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, con
       ++e;
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3t: per-tile triangle lists (rasterizer.cc:194-241 for the triangles raster_kernel listed).  One CTA per
+// 16 x 16 pixel screen tile, one thread per pixel.  The tile's list is staged through shared memory 64
+// triangles at a time — thread k < 64 does the dependent loads (face record -> projected vertices) and the
+// setup of one triangle exactly once per (triangle, tile) — then every pixel walks the staged records
+// (broadcast LDS; a warp owns two 16-pixel rows and skips records whose bbox misses them) with the depth test
+// in a register: the same (z, face, backface) key as everywhere else, minimum kept per pixel, and a single
+// atomicMin per covered pixel merges it with what raster_kernel / binned_kernel put into the visibility
+// buffer.  Empty tiles exit on their count; every tile leaves its count 0 for the next view.
+// ---------------------------------------------------------------------------------------------
+struct __align__(16) TileTris {
+  float4 a[kTileStage];  // v0x v0y v1x v1y
+  float4 b[kTileStage];  // v2x v2y (int)(x0 | x1 << 16) (int)(y0 | y1 << 16)   (clamped bbox)
+  float4 c[kTileStage];  // v0z v1z v2z area
+  float4 d[kTileStage];  // g = c2w_R^T * face_normal (3), facing threshold
+  int face[kTileStage];
+};
+
+template <int NV>
+__global__ void __launch_bounds__(256) tile_kernel(const ViewBatch<NV> vb, const MeshDev m, const FrameDev fr0) {
+  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
+  const ViewParams& vp = vb.v[view];
+  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
+  __shared__ TileTris S;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int tile = (int)blockIdx.x;
+  const int total = fr.tile_cnt[tile];
+  if (total == 0) return;  // (CTA-uniform)
+  const int n = min(total, kTileCap);
+  const int ty = tile / fr.tiles_x, tx = tile - ty * fr.tiles_x;
+  const int x = tx * kTile + (int)(threadIdx.x & 15u), y = ty * kTile + (int)(threadIdx.x >> 4);
+  const int wy0 = ty * kTile + (int)(threadIdx.x >> 5) * 2;  // the warp's two rows
+  const bool inside = x < vp.W && y < vp.H;
+  const float px = small_int_to_float(x), py = small_int_to_float(y);
+  const bool has_fn = m.num_face_normals > 0;
+  unsigned long long best = kVisEmpty;
+  unsigned long long hazards = 0ull;
+  for (int c0 = 0; c0 < n; c0 += kTileStage) {
+    const int cn = min(kTileStage, n - c0);
+    if ((int)threadIdx.x < cn) {
+      const int k = (int)threadIdx.x;
+      const int f = fr.tile_bin[(size_t)tile * kTileCap + c0 + k];
+      const int4 vr = __ldg(m.frec + 2 * (size_t)f);
+      float fnx = 0.f, fny = 0.f, fnz = 0.f;
+      if (has_fn) {
+        fnx = __ldg(m.fn_x + f);
+        fny = __ldg(m.fn_y + f);
+        fnz = __ldg(m.fn_z + f);
+      }
+      Tri t;
+      tri_setup(t, fr.proj[vr.x], fr.proj[vr.y], fr.proj[vr.z]);
+      int bx0, by0, bx1, by1;
+      tri_bounds(t, vp, bx0, by0, bx1, by1);  // listed triangles always pass
+      S.a[k] = make_float4(t.v0x, t.v0y, t.v1x, t.v1y);
+      S.b[k] = make_float4(t.v2x, t.v2y, __int_as_float(bx0 | (bx1 << 16)), __int_as_float(by0 | (by1 << 16)));
+      S.c[k] = make_float4(t.v0z, t.v1z, t.v2z, t.area);
+      S.d[k] = make_float4((vp.c2w_R[0] * fnx + vp.c2w_R[3] * fny) + vp.c2w_R[6] * fnz,
+                           (vp.c2w_R[1] * fnx + vp.c2w_R[4] * fny) + vp.c2w_R[7] * fnz,
+                           (vp.c2w_R[2] * fnx + vp.c2w_R[5] * fny) + vp.c2w_R[8] * fnz,
+                           fmaxf(vp.facing_eps * ((fabsf(fnx) + fabsf(fny)) + fabsf(fnz)), 1e-30f));
+      S.face[k] = f;
+    }
+    __syncthreads();
+    for (int k = 0; k < cn; k++) {
+      const float4 rb = S.b[k];
+      const unsigned bx = __float_as_uint(rb.z), by = __float_as_uint(rb.w);
+      const int bx0 = (int)(bx & 0xFFFFu), bx1 = (int)(bx >> 16), by0 = (int)(by & 0xFFFFu), by1 = (int)(by >> 16);
+      if (by1 < wy0 || by0 > wy0 + 1 || bx1 < tx * kTile || bx0 > tx * kTile + (kTile - 1)) continue;  // warp-uniform
+      if (!inside || x < bx0 || x > bx1 || y < by0 || y > by1) continue;
+      const float4 ra = S.a[k];
+      // EdgeFunction(v1,v2,p), (v2,v0,p), (v0,v1,p) — the expressions of tri_setup / tri_edges
+      float w0 = (px - ra.z) * (rb.y - ra.w) - (py - ra.w) * (rb.x - ra.z);
+      float w1 = (px - rb.x) * (ra.y - rb.y) - (py - rb.y) * (ra.x - rb.x);
+      float w2 = (px - ra.x) * (ra.w - ra.y) - (py - ra.y) * (ra.z - ra.x);
+      const bool pos = (w0 >= 0.0f) && (w1 >= 0.0f) && (w2 >= 0.0f);
+      const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
+      if (!(pos || neg)) continue;
+      const float4 rc = S.c[k];
+      {  // conservative early-out against the register winner (the bound of raster_fragments)
+        const float zs = __uint_as_float((unsigned)(best >> 32));  // NaN while there is no winner
+        const float zmin = fminf(fminf(rc.x, rc.y), rc.z);
+        const float s3 = (w0 + w1) + w2;
+        const float sa = pos ? s3 : -s3, aa = pos ? rc.w : -rc.w;
+        if (pos != neg && aa > 0.0f && sa <= 1.001f * aa && zmin < 1e30f && 0.998f * zmin > zs) continue;
+      }
+      const int face = S.face[k];
+      const bool bf = has_fn ? facing_backface(vp, m, fr, S.d[k], face, x, y) : false;
+      if (!(bf ? neg : pos)) continue;
+      w0 = w0 / rc.w;
+      w1 = w1 / rc.w;
+      w2 = w2 / rc.w;
+      w0 = w0 / rc.x;
+      w1 = w1 / rc.y;
+      w2 = w2 / rc.z;
+      const float z = 1.0f / ((w0 + w1) + w2);
+      if (!(z >= 1.17549435e-38f)) {  // see vis_update
+        hazards++;
+        continue;
+      }
+      const unsigned long long key = ((unsigned long long)__float_as_uint(z) << 32) |
+                                     (unsigned long long)(((unsigned)face << 1) | (bf ? 1u : 0u));
+      best = key < best ? key : best;
+    }
+    __syncthreads();  // the staging area is rewritten by the next chunk
+  }
+  if (best != kVisEmpty) atomicMin(fr.vis + (size_t)y * vp.W + x, best);
+  if (hazards) atomicAdd(fr.counters + 1, hazards);
+  if (threadIdx.x == 0) fr.tile_cnt[tile] = 0;
 }
 
 // ---------------------------------------------------------------------------------------------
