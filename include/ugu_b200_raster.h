@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 8
+#define UGU_B200_ABI_VERSION 9
 
 enum {
   UGU_B200_OK = 0,
@@ -498,6 +498,64 @@ void ugu_b200_host_free(void* p);
 
 /* Message of the last error on this rasterizer (or of the last handle-less call when r == NULL). */
 const char* ugu_b200_last_error(const ugu_b200_rasterizer* r);
+
+/* ---- Multi-view dispatch over several GPUs of one box from ONE host process (SURVEY.md 8b last row, 8e) --------
+ * The C++ replacement of the reference's sequential orbit loop (examples/ex09_renderer_realtime.cc:125-182:
+ * set_c2w -> Render per view on one renderer): one rasterizer handle per listed device, the view list sharded
+ * over them (no data-path collective: views are independent given the replicated mesh), each device driven by
+ * its own host thread through the batched launch sets of ugu_b200_rasterizer_render_batch.  The optional exchange
+ * step — gathering the per-view face_id maps on one device for a consumer — sends every chunk of views as soon as it
+ * is rendered, straight to its final place in the view-ordered destination, over NCCL send/recv (libnccl.so.2 is
+ * dlopen-ed at create) or cudaMemcpyPeerAsync; the per-face visibility fold reduces 16 bytes per face instead.
+ * A device may be listed more than once (several handles on one GPU: the sharding logic on a one-GPU box);
+ * NCCL needs distinct devices, the peer transport does not. */
+typedef struct ugu_b200_multiview ugu_b200_multiview;
+enum { UGU_B200_PARTITION_CONTIGUOUS = 0, UGU_B200_PARTITION_ROUND_ROBIN = 1 };
+enum { UGU_B200_TRANSPORT_AUTO = 0, UGU_B200_TRANSPORT_PEER = 1, UGU_B200_TRANSPORT_NCCL = 2 };
+
+/* Global indices of the views slot `rank` of `world` renders.  contiguous: ceil/floor(num_views / world)
+ * consecutive views (the first num_views % world slots get one more); round robin: i % world == rank.
+ * `indices` may be NULL (count only).  Pure host code. */
+int ugu_b200_partition(int32_t num_views, int32_t world, int32_t rank, int32_t mode, int32_t* indices,
+                       int32_t* count);
+
+/* transport AUTO: NCCL when libnccl.so.2 loads and the devices are distinct, else peer copies (the
+ * environment variable UGU_B200_MV_TRANSPORT=peer|nccl overrides the argument). */
+int ugu_b200_multiview_create(const int32_t* devices, int32_t num_devices, int32_t transport,
+                              ugu_b200_multiview** out);
+void ugu_b200_multiview_destroy(ugu_b200_multiview* mv);
+int32_t ugu_b200_multiview_size(const ugu_b200_multiview* mv);
+int32_t ugu_b200_multiview_transport(const ugu_b200_multiview* mv); /* UGU_B200_TRANSPORT_PEER or _NCCL */
+ugu_b200_rasterizer* ugu_b200_multiview_rasterizer(ugu_b200_multiview* mv, int32_t slot);
+const char* ugu_b200_multiview_last_error(const ugu_b200_multiview* mv);
+
+/* set_option / PrepareMesh on every device (the mesh is replicated). */
+int ugu_b200_multiview_set_option(ugu_b200_multiview* mv, const ugu_b200_option* opt);
+int ugu_b200_multiview_upload_mesh(ugu_b200_multiview* mv, const ugu_b200_mesh_desc* mesh);
+
+/* The orbit loop, sharded: view i lands at element offset i * W*H of every non-NULL HOST output, whatever device
+ * rendered it.  All cameras share one image size.  Synchronous. */
+int ugu_b200_multiview_render_batch(ugu_b200_multiview* mv, int32_t num_views, const ugu_b200_camera* cams,
+                                    int32_t partition, const ugu_b200_outputs* host_out);
+
+/* Render the face_id map of every view (sharded, `chunk_views` views per launch set and message; 0 = 16) and
+ * gather the maps in view order on device slot `root`: into `face_id_root_dev` (a 16-byte aligned device pointer
+ * on that device, num_views * W*H int32) or, when it is NULL, into an internal buffer
+ * (ugu_b200_multiview_gathered).  `face_id_host` (optional) additionally receives the gathered maps.  Synchronous. */
+int ugu_b200_multiview_gather_face_ids(ugu_b200_multiview* mv, int32_t num_views, const ugu_b200_camera* cams,
+                                       int32_t partition, int32_t root, int32_t chunk_views,
+                                       int32_t* face_id_root_dev, int32_t* face_id_host);
+const int32_t* ugu_b200_multiview_gathered(const ugu_b200_multiview* mv);
+
+/* Render the face_id maps (sharded), fold them per device into the per-face statistics of
+ * ugu_b200_face_visibility (global view ids) and reduce the accumulators to slot `root` — SUM / SUM / MAX of 16
+ * bytes per face (ncclReduce, or peer copies and a combine kernel) instead of the maps.  Results as in the host
+ * form of ugu_b200_face_visibility; any output may be NULL.  Synchronous. */
+int ugu_b200_multiview_reduce_face_visibility(ugu_b200_multiview* mv, int32_t num_views,
+                                              const ugu_b200_camera* cams, int32_t partition, int32_t root,
+                                              int32_t chunk_views, uint32_t* pixel_count_host,
+                                              uint32_t* view_count_host, int32_t* best_view_host,
+                                              uint32_t* best_count_host);
 
 #ifdef __cplusplus
 }

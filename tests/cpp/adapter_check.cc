@@ -13,6 +13,8 @@
 #include <vector>
 
 #include "rasterizer_cuda.h"
+#include "multiview_cuda.h"
+#include "ugu_b200_raster.h"
 #include "visibility_tester_cuda.h"
 #include "ugu/camera.h"
 #include "ugu/log.h"
@@ -444,6 +446,102 @@ int main(int argc, char** argv) {
                   stat_faces, stat_bad, ok ? "ok" : "MISMATCH");
       if (!ok) failures++;
     }
+  }
+
+  {  // ---- the ex09 orbit loop (examples/ex09_renderer_realtime.cc:125-182) sharded over every visible GPU --------
+    // config-3 shape: 36-view turntable at 1024 x 1024, textured, all five outputs.  N-device result == the
+    // per-view Render of ONE RasterizerCuda, bit for bit, for both partitions; gathered face_id maps == the
+    // rendered ones; the reduced per-face statistics == a histogram of those maps.
+    const int MW = timing ? 1024 : 1024, MH = MW, NVIEWS = 36;
+    ugu::RendererCpuOption option;
+    option.diffuse_color = ugu::DiffuseColor::kTexture;
+    std::vector<std::shared_ptr<const ugu::Camera>> cams;
+    for (int k = 0; k < NVIEWS; k++) {
+      const double a = 2.0 * 3.14159265358979323846 * k / NVIEWS;
+      Eigen::Matrix4d c2w;
+      ugu::c2w(Eigen::Vector3d(2.9 * std::sin(a), 0.0, 2.9 * std::cos(a)), Eigen::Vector3d(0, 0, 0),
+               Eigen::Vector3d(0, -1, 0), &c2w);
+      auto cm = std::make_shared<ugu::PinholeCamera>(MW, MH, 45.0f);
+      cm->set_c2w(Eigen::Affine3d(c2w));
+      cams.push_back(cm);
+    }
+    std::vector<int> devices;
+    for (int i = 0; i < ugu_b200_device_count(); i++) devices.push_back(i);
+    if (devices.size() == 1) devices.push_back(devices[0]);  // one GPU: two handles on it, same sharding logic
+    ugu::MultiViewRasterizerCuda mv(option, devices);
+    auto single = std::make_unique<ugu::RasterizerCuda>(option);
+    bool ok = mv.valid() && single->valid();
+    if (ok) {
+      mv.set_mesh(mesh);
+      single->set_mesh(mesh);
+      ok = mv.PrepareMesh() && single->PrepareMesh();
+    }
+    std::vector<Outs> want(NVIEWS);
+    for (int k = 0; ok && k < NVIEWS; k++) {
+      single->set_camera(cams[k]);
+      ok = single->Render(&want[k].color, &want[k].depth, &want[k].normal, &want[k].mask, &want[k].face_id);
+    }
+    long bad = 0;
+    double ms_batch[2] = {0, 0};
+    for (int rr = 0; ok && rr < 2; rr++) {
+      std::vector<ugu::Image3b> c;
+      std::vector<ugu::Image1f> d;
+      std::vector<ugu::Image3f> n;
+      std::vector<ugu::Image1b> m;
+      std::vector<ugu::Image1i> f;
+      const auto t0 = std::chrono::steady_clock::now();
+      ok = mv.RenderBatch(cams, &c, &d, &n, &m, &f, rr != 0);
+      ms_batch[rr] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      for (int k = 0; ok && k < NVIEWS; k++)
+        bad += CountDiff(want[k].color, c[k], 0) + CountDiff(want[k].depth, d[k], 0) +
+               CountDiff(want[k].normal, n[k], 0) + CountDiff(want[k].mask, m[k], 0) +
+               CountDiff(want[k].face_id, f[k], 0);
+    }
+    long gbad = 0;
+    double ms_gather = 0;
+    for (int rr = 0; ok && rr < 2; rr++) {
+      std::vector<ugu::Image1i> f;
+      const int root = rr == 0 ? 0 : mv.size() - 1;
+      const auto t0 = std::chrono::steady_clock::now();
+      ok = mv.GatherFaceIds(cams, &f, root, rr == 0 ? 4 : 3, rr != 0);
+      if (rr == 0) ms_gather = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      for (int k = 0; ok && k < NVIEWS; k++) gbad += CountDiff(want[k].face_id, f[k], 0);
+    }
+    long vbad = 0;
+    if (ok) {
+      const size_t F = mesh->vertex_indices().size();
+      std::vector<uint32_t> pix(F, 0), views(F, 0), bestc(F, 0);
+      std::vector<int32_t> bestv(F, -1);
+      std::vector<uint32_t> cnt(F);
+      for (int k = 0; k < NVIEWS; k++) {
+        std::fill(cnt.begin(), cnt.end(), 0u);
+        const int32_t* fid = reinterpret_cast<const int32_t*>(want[k].face_id.data);
+        for (size_t i = 0; i < static_cast<size_t>(MW) * MH; i++)
+          if (fid[i] >= 0) cnt[fid[i]]++;
+        for (size_t f = 0; f < F; f++) {
+          if (!cnt[f]) continue;
+          pix[f] += cnt[f];
+          views[f]++;
+          if (cnt[f] > bestc[f]) {  // ties keep the lowest view id
+            bestc[f] = cnt[f];
+            bestv[f] = k;
+          }
+        }
+      }
+      for (int rr = 0; ok && rr < 2; rr++) {
+        std::vector<uint32_t> p2, v2, c2;
+        std::vector<int32_t> b2;
+        ok = mv.FaceVisibility(cams, &p2, &v2, &b2, &c2, rr == 0 ? 0 : mv.size() - 1, 5, rr != 0);
+        for (size_t f = 0; ok && f < F; f++)
+          vbad += (p2[f] != pix[f]) + (v2[f] != views[f]) + (b2[f] != bestv[f]) + (c2[f] != bestc[f]);
+      }
+    }
+    std::printf("MultiViewRasterizerCuda: %d handle(s) on %d device(s), transport %s, %d views %dx%d: batch diff %ld "
+                "(contiguous %.1f ms, round robin %.1f ms incl. host copies), gather diff %ld (%.1f ms), visibility "
+                "diff %ld  %s\n",
+                mv.size(), ugu_b200_device_count(), mv.transport(), NVIEWS, MW, MH, bad, ms_batch[0], ms_batch[1], gbad,
+                ms_gather, vbad, (ok && !bad && !gbad && !vbad) ? "ok" : "MISMATCH");
+    if (!ok || bad || gbad || vbad) failures++;
   }
   std::printf(failures ? "ADAPTER PARITY FAILED (%d)\n" : "ADAPTER PARITY OK\n", failures);
   return failures ? 1 : 0;

@@ -169,6 +169,25 @@ SYMBOLS = {
     "ugu_b200_host_alloc": (C.c_void_p, [C.c_size_t]),
     "ugu_b200_host_free": (None, [C.c_void_p]),
     "ugu_b200_last_error": (C.c_char_p, [C.c_void_p]),
+    # multi-view dispatch over several GPUs from one process
+    "ugu_b200_partition": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32),
+                                     C.POINTER(C.c_int32)]),
+    "ugu_b200_multiview_create": (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "ugu_b200_multiview_destroy": (None, [C.c_void_p]),
+    "ugu_b200_multiview_size": (C.c_int32, [C.c_void_p]),
+    "ugu_b200_multiview_transport": (C.c_int32, [C.c_void_p]),
+    "ugu_b200_multiview_rasterizer": (C.c_void_p, [C.c_void_p, C.c_int32]),
+    "ugu_b200_multiview_last_error": (C.c_char_p, [C.c_void_p]),
+    "ugu_b200_multiview_set_option": (C.c_int, [C.c_void_p, C.POINTER(Option)]),
+    "ugu_b200_multiview_upload_mesh": (C.c_int, [C.c_void_p, C.POINTER(MeshDesc)]),
+    "ugu_b200_multiview_render_batch": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Camera), C.c_int32,
+                                                  C.POINTER(Outputs)]),
+    "ugu_b200_multiview_gather_face_ids": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Camera), C.c_int32, C.c_int32,
+                                                     C.c_int32, C.c_void_p, C.c_void_p]),
+    "ugu_b200_multiview_gathered": (C.c_void_p, [C.c_void_p]),
+    "ugu_b200_multiview_reduce_face_visibility": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Camera), C.c_int32,
+                                                            C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                            C.c_void_p]),
 }
 
 _lib = None
@@ -188,7 +207,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 8:
+    if lib.ugu_b200_abi_version() != 9:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

@@ -1,7 +1,8 @@
 """Builds the C++ adapter library — only possible where the reference headers exist (this
 container; the GPU box receives the prebuilt, git-ignored binary).
 
-    ugu_b200/cpp/build/librasterizer_cuda.so   ugu::RasterizerCuda, ugu::RaytracerCuda, ugu::VisibilityTesterCuda
+    ugu_b200/cpp/build/librasterizer_cuda.so   ugu::RasterizerCuda, ugu::RaytracerCuda, ugu::VisibilityTesterCuda,
+                                               ugu::MultiViewRasterizerCuda
                                                (links libugu_b200_raster.so)
 
 Its differential harness against the reference Rasterizer is test infrastructure and lives in
@@ -36,7 +37,7 @@ def build() -> Path:
     OUT.mkdir(exist_ok=True)
     so = OUT / "librasterizer_cuda.so"
     subprocess.run([*compile_command(), "-shared", "-o", str(so), str(HERE / "rasterizer_cuda.cc"),
-                    str(HERE / "visibility_tester_cuda.cc"),
+                    str(HERE / "visibility_tester_cuda.cc"), str(HERE / "multiview_cuda.cc"),
                     f"-L{REPO / 'ugu_b200' / 'lib'}", "-lugu_b200_raster", "-Wl,-rpath,$ORIGIN/../../lib"],
                    check=True, capture_output=True)
     return so

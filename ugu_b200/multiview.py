@@ -294,3 +294,104 @@ class MultiViewRenderer:
             self._render_local_cuda(cameras, (output,), into={output: into})
         else:  # injected renderer (CPU tests)
             into.copy_(self._render_local(cameras, (output,))[output])
+
+
+class NativeMultiView:
+    """Thin binding of the single-process multi-GPU dispatch behind the C-ABI (ugu_b200_multiview_*,
+    include/ugu_b200_raster.h): one rasterizer handle per listed device, views sharded over them, the optional
+    gather / reduction over NCCL or peer copies inside the library.  This is what a C++ host uses
+    (ugu::MultiViewRasterizerCuda); the torch.distributed classes above are the one-process-per-GPU form."""
+
+    PARTITION = {"contiguous": 0, "round_robin": 1}
+
+    def __init__(self, devices: Sequence[int], option=None, transport: str = "auto"):
+        import ctypes as C
+        from . import _native as N
+        from .renderer import RendererCpuOption
+        self._C, self._N = C, N
+        self._lib = N.load()
+        devs = (C.c_int32 * len(devices))(*devices)
+        h = C.c_void_p()
+        rc = self._lib.ugu_b200_multiview_create(devs, len(devices), {"auto": 0, "peer": 1, "nccl": 2}[transport], C.byref(h))
+        if rc != N.OK:
+            msg = self._lib.ugu_b200_multiview_last_error(None)
+            raise RuntimeError(msg.decode() if msg else "ugu_b200_multiview_create failed")
+        self._h = h
+        self._option = option or RendererCpuOption()
+        self._num_faces = 0
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self._lib.ugu_b200_multiview_destroy(h)
+            self._h = None
+
+    def _check(self, rc):
+        if rc != self._N.OK:
+            msg = self._lib.ugu_b200_multiview_last_error(self._h)
+            raise RuntimeError(msg.decode() if msg else f"status {rc}")
+
+    @property
+    def size(self) -> int:
+        return int(self._lib.ugu_b200_multiview_size(self._h))
+
+    @property
+    def transport(self) -> str:
+        return "nccl" if self._lib.ugu_b200_multiview_transport(self._h) == 2 else "peer"
+
+    def set_option(self, option) -> None:
+        self._option = option
+
+    def prepare_mesh(self, mesh) -> None:
+        from .renderer import mesh_desc
+        d, keep = mesh_desc(mesh)
+        self._check(self._lib.ugu_b200_multiview_upload_mesh(self._h, self._C.byref(d)))
+        self._num_faces = int(d.num_faces)
+        del keep
+
+    def _begin(self, cameras):
+        N, C = self._N, self._C
+        o = self._option
+        opt = N.Option(int(o.diffuse_color), int(o.interp), int(o.shading_normal), int(o.diffuse_shading),
+                       1 if o.backface_culling else 0, float(o.depth_scale), float(o.oren_nayar_sigma))
+        self._check(self._lib.ugu_b200_multiview_set_option(self._h, C.byref(opt)))
+        natives = [c if isinstance(c, N.Camera) else c.to_native() for c in cameras]
+        return (N.Camera * len(natives))(*natives), int(natives[0].width), int(natives[0].height)
+
+    def render_batch(self, cameras, outputs=("color", "depth", "normal", "mask", "face_id"), mode="contiguous"):
+        """-> dict of view-ordered host arrays (n, H, W[, 3])."""
+        import numpy as np
+        from .renderer import pinned_empty
+        cams, w, h = self._begin(cameras)
+        n = len(cameras)
+        spec = dict(color=(np.uint8, (n, h, w, 3)), depth=(np.float32, (n, h, w)), normal=(np.float32, (n, h, w, 3)),
+                    mask=(np.uint8, (n, h, w)), face_id=(np.int32, (n, h, w)))
+        host = {k: pinned_empty(spec[k][1], spec[k][0]) for k in outputs}
+        o = self._N.Outputs(*[host[k].ctypes.data if k in host else None
+                              for k in ("color", "depth", "normal", "mask", "face_id")])
+        self._check(self._lib.ugu_b200_multiview_render_batch(self._h, n, cams, self.PARTITION[mode],
+                                                              self._C.byref(o)))
+        return host
+
+    def gather_face_ids(self, cameras, root=0, chunk_views=0, mode="contiguous", to_host=True):
+        """Render + gather of the face_id maps on device slot `root`; -> (n, H, W) int32 host array, or None with
+        to_host=False (the maps then stay in the library's buffer on the root device: timing runs)."""
+        import numpy as np
+        cams, w, h = self._begin(cameras)
+        n = len(cameras)
+        out = np.empty((n, h, w), np.int32) if to_host else None
+        self._check(self._lib.ugu_b200_multiview_gather_face_ids(
+            self._h, n, cams, self.PARTITION[mode], root, chunk_views, None, out.ctypes.data if to_host else None))
+        return out
+
+    def face_visibility(self, cameras, root=0, chunk_views=0, mode="contiguous"):
+        """-> pixel_count, view_count, best_view, best_count per face over all views (reduced on `root`)."""
+        import numpy as np
+        cams, w, h = self._begin(cameras)
+        F = self._num_faces
+        pc, vc, bc = (np.zeros(F, np.uint32) for _ in range(3))
+        bv = np.full(F, -1, np.int32)
+        self._check(self._lib.ugu_b200_multiview_reduce_face_visibility(
+            self._h, len(cameras), cams, self.PARTITION[mode], root, chunk_views, pc.ctypes.data, vc.ctypes.data,
+            bv.ctypes.data, bc.ctypes.data))
+        return pc, vc, bv, bc

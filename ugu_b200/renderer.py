@@ -268,6 +268,37 @@ def _ptr(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def mesh_desc(m: "Mesh"):
+    """The C-ABI mesh descriptor of a Mesh (AoS host arrays as ugu::Mesh holds them, mesh.h:83-98) and the objects
+    that must stay alive while the descriptor is in use."""
+    f32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1, w))
+    i32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.int32).reshape(-1, w))
+    v, n, c = f32(m.vertices, 3), f32(m.normals, 3), f32(m.vertex_colors, 3)
+    vi, ni, ui = i32(m.vertex_indices, 3), i32(m.normal_indices, 3), i32(m.uv_indices, 3)
+    fn, uv = f32(m.face_normals, 3), f32(m.uv, 2)
+    mid = np.ascontiguousarray(np.asarray(m.material_ids, np.int32).reshape(-1))
+    F = len(vi)
+    texs = [None if (t.diffuse_tex is None or t.diffuse_tex.size == 0)
+            else np.ascontiguousarray(t.diffuse_tex, np.uint8) for t in m.materials]
+    M = len(texs)
+    d = N.MeshDesc()
+    d.num_vertices, d.num_normals, d.num_colors = len(v), len(n), len(c)
+    d.num_faces, d.num_face_normals, d.num_uv, d.num_materials = F, len(fn), len(uv), M
+    d.vertices, d.normals, d.vertex_colors = _ptr(v), _ptr(n), _ptr(c)
+    d.vertex_indices = _ptr(vi)
+    d.normal_indices = _ptr(ni) if len(ni) == F and F > 0 else None
+    d.face_normals, d.uv = _ptr(fn), _ptr(uv)
+    d.uv_indices = _ptr(ui) if len(ui) == F and F > 0 else None
+    d.material_ids = _ptr(mid) if len(mid) == F and F > 0 else None
+    tex_ptrs = (C.c_void_p * max(M, 1))(*[None if t is None else t.ctypes.data for t in texs])
+    tex_w = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[1] for t in texs])
+    tex_h = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[0] for t in texs])
+    d.tex_data = C.cast(tex_ptrs, C.POINTER(C.c_void_p))
+    d.tex_w = C.cast(tex_w, C.POINTER(C.c_int32))
+    d.tex_h = C.cast(tex_h, C.POINTER(C.c_int32))
+    return d, (v, n, c, vi, ni, ui, fn, uv, mid, texs, tex_ptrs, tex_w, tex_h)
+
+
 class Rasterizer:
     """The CUDA-backed drop-in for ugu::Rasterizer (rasterizer.h:14-53)."""
 
@@ -307,32 +338,7 @@ class Rasterizer:
         if self._mesh is None:
             LOGE("mesh has not been set")
             return False
-        m = self._mesh
-        f32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1, w))
-        i32 = lambda a, w: np.ascontiguousarray(np.asarray(a, np.int32).reshape(-1, w))
-        v, n, c = f32(m.vertices, 3), f32(m.normals, 3), f32(m.vertex_colors, 3)
-        vi, ni, ui = i32(m.vertex_indices, 3), i32(m.normal_indices, 3), i32(m.uv_indices, 3)
-        fn, uv = f32(m.face_normals, 3), f32(m.uv, 2)
-        mid = np.ascontiguousarray(np.asarray(m.material_ids, np.int32).reshape(-1))
-        F = len(vi)
-        texs = [None if (t.diffuse_tex is None or t.diffuse_tex.size == 0)
-                else np.ascontiguousarray(t.diffuse_tex, np.uint8) for t in m.materials]
-        M = len(texs)
-        d = N.MeshDesc()
-        d.num_vertices, d.num_normals, d.num_colors = len(v), len(n), len(c)
-        d.num_faces, d.num_face_normals, d.num_uv, d.num_materials = F, len(fn), len(uv), M
-        d.vertices, d.normals, d.vertex_colors = _ptr(v), _ptr(n), _ptr(c)
-        d.vertex_indices = _ptr(vi)
-        d.normal_indices = _ptr(ni) if len(ni) == F and F > 0 else None
-        d.face_normals, d.uv = _ptr(fn), _ptr(uv)
-        d.uv_indices = _ptr(ui) if len(ui) == F and F > 0 else None
-        d.material_ids = _ptr(mid) if len(mid) == F and F > 0 else None
-        tex_ptrs = (C.c_void_p * max(M, 1))(*[None if t is None else t.ctypes.data for t in texs])
-        tex_w = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[1] for t in texs])
-        tex_h = (C.c_int32 * max(M, 1))(*[0 if t is None else t.shape[0] for t in texs])
-        d.tex_data = C.cast(tex_ptrs, C.POINTER(C.c_void_p))
-        d.tex_w = C.cast(tex_w, C.POINTER(C.c_int32))
-        d.tex_h = C.cast(tex_h, C.POINTER(C.c_int32))
+        d, keep = mesh_desc(self._mesh)
         rc = self._lib.ugu_b200_rasterizer_upload_mesh(self._h, C.byref(d))
         if rc != N.OK:
             LOGE(N.last_error(self._h))
