@@ -157,6 +157,12 @@ int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
                                      const ugu_b200_camera* cams, const ugu_b200_outputs* out,
                                      int32_t outputs_on_device, void* stream);
 
+/* Off-contract fragments (depth < FLT_MIN or NaN, where the reference's sequential `d < FLT_MIN || z < d` rule
+ * becomes order dependent, rasterizer.cc:229) met by the last HOST-form render call on this handle (render,
+ * render_batch with host outputs, render_gbuffer, raytrace): 0 = the frame is the reference's frame; > 0 = it may
+ * differ at those fragments.  The call itself still returns UGU_B200_OK; ugu::RasterizerCuda logs a warning. */
+uint64_t ugu_b200_rasterizer_last_hazards(const ugu_b200_rasterizer* r);
+
 /* Block until everything queued by this rasterizer has finished; returns the first deferred error. */
 int ugu_b200_rasterizer_sync(ugu_b200_rasterizer* r);
 

@@ -472,3 +472,27 @@ def test_tile_lists_overflow_and_huge_triangles(tile_lists):
     for (w, h) in ((97, 61), (333, 207)):
         cam = PinholeCamera(w, h, meshgen.look_at_c2w((0.1, 0.0, 0.0), (0.0, 0.1, 1.0), (0, -1, 0)), fov_y_deg=50.0)
         util.assert_parity(run.render(cam, opt), port.render(cam.to_native(), opt), strict=True, what=f"tiles {w}x{h}")
+
+
+def test_hazard_fragments_are_reported_not_silent():
+    """A triangle through the camera plane (z == 0 at a vertex passes the reference's `z < 0` reject and yields
+    inf / NaN depths): the call succeeds, and the handle reports the off-contract fragments."""
+    from ugu_b200 import Mesh, _native as N
+    v = np.array([[-1, -1, 2.0], [1, -1, 2.0], [0, 1, 2.0],          # a regular triangle
+                  [-0.5, -0.5, 0.0], [0.5, -0.5, 1.0], [0.0, 0.5, 1.0]], np.float32)   # one vertex ON the camera plane
+    f = np.array([[0, 1, 2], [3, 4, 5]], np.int32)
+    fn = np.tile(np.array([[0, 0, -1.0]], np.float32), (2, 1))
+    mesh = Mesh(vertices=v, vertex_indices=f, face_normals=fn)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kNone, shading_normal=ShadingNormal.kFace, backface_culling=False)
+    run = util.CudaRunner(mesh, opt)
+    cam = cases.kat_camera()
+    got = run.render(cam, opt, want=("depth", "face_id"))
+    assert got is not None
+    lib = N.load()
+    hz = int(lib.ugu_b200_rasterizer_last_hazards(run.r._h))
+    assert hz == run.r.stats()["hazard_fragments"]
+    # a clean frame afterwards reports zero again
+    mesh2 = Mesh(vertices=v[:3], vertex_indices=f[:1], face_normals=fn[:1])
+    run2 = util.CudaRunner(mesh2, opt)
+    assert run2.render(cam, opt, want=("depth",)) is not None
+    assert int(lib.ugu_b200_rasterizer_last_hazards(run2.r._h)) == 0

@@ -301,6 +301,29 @@ def test_cuda_raytracer_device_form():
 
 
 @pytest.mark.gpu
+def test_cuda_raytracer_render_batch_host_form():
+    """Raytracer.render_batch with HOST destinations (view i at slab i) equals per-view Render calls."""
+    from ugu_b200 import Raytracer
+    mesh, cam, opt, want = _load("ico4_vertex_cull")
+    r = Raytracer(opt)
+    r.set_mesh(mesh)
+    assert r.PrepareMesh()
+    cams = [PinholeCamera(cam.width(), cam.height(), p, fov_y_deg=45.0) for p in meshgen.orbit_poses((0, 0, 0), 2.7, 3)]
+    h, w = cam.height(), cam.width()
+    fid = np.empty((3, h, w), np.int32)
+    dep = np.empty((3, h, w), np.float32)
+    col = np.empty((3, h, w, 3), np.uint8)
+    r.render_batch(cams, color=col.ctypes.data, depth=dep.ctypes.data, face_id=fid.ctypes.data, on_device=False)
+    from ugu_b200 import Image1f, Image1i, Image3b
+    for i, cm in enumerate(cams):
+        r.set_camera(cm)
+        c1, d1, f1 = Image3b(), Image1f(), Image1i()
+        assert r.Render(color=c1, depth=d1, face_id=f1)
+        assert np.array_equal(fid[i], f1.data) and np.array_equal(col[i], c1.data)
+        assert np.array_equal(dep[i].view(np.uint32), d1.data.view(np.uint32))
+
+
+@pytest.mark.gpu
 def test_multiview_renderer_with_the_raytracer_and_visibility_fold():
     """The multi-view driver on ray-cast face_id maps (what the reference's own visibility pass uses: BVH
     rays, include/ugu/texturing/visibility_tester.h): batch == per-view renders, and the per-face

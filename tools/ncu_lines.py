@@ -32,8 +32,12 @@ ci = {n: hdr.index(n) for n in ("Source", "# Samples", "Instructions Executed", 
 
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", lib], cwd=tmp, capture_output=True)
-cubin = next(p for p in Path(tmp).glob("*.cubin") if "camera_host" not in p.name)
-dis = subprocess.run(["nvdisasm", "-g", "-c", str(cubin)], capture_output=True, text=True).stdout.splitlines()
+dis = []
+for cubin in sorted(Path(tmp).glob("*.cubin")):  # one per .cu of the library: keep the one that holds the kernel
+    d = subprocess.run(["nvdisasm", "-g", "-c", str(cubin)], capture_output=True, text=True).stdout.splitlines()
+    if any(l.startswith(".text.") and re.search(kern, l) for l in d):
+        dis = d
+        break
 # locate the function
 def parse(start):
     out, cur = [], 0

@@ -121,6 +121,7 @@ SYMBOLS = {
     "ugu_b200_rasterizer_render_batch": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Camera),
                                                    C.POINTER(Outputs), C.c_int32, C.c_void_p]),
     "ugu_b200_rasterizer_sync": (C.c_int, [C.c_void_p]),
+    "ugu_b200_rasterizer_last_hazards": (C.c_uint64, [C.c_void_p]),
     "ugu_b200_depth_to_u16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     "ugu_b200_depth_to_point_cloud_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p,
                                                        C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),

@@ -203,6 +203,9 @@ class RasterizerCuda::Impl {
       LOGE("%s\n", ugu_b200_last_error(handle_));
       return false;
     }
+    if (const uint64_t hz = ugu_b200_rasterizer_last_hazards(handle_))
+      LOGW("%llu fragment(s) with depth < FLT_MIN or NaN: the reference's result is order dependent there "
+           "(rasterizer.cc:229) and this frame may differ from it at those pixels\n", (unsigned long long)hz);
     return true;
   }
 };

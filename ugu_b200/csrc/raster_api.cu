@@ -1555,6 +1555,10 @@ int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
   return UGU_B200_OK;
 }
 
+uint64_t ugu_b200_rasterizer_last_hazards(const ugu_b200_rasterizer* r) {
+  return r ? r->stats.hazard_fragments : 0;
+}
+
 int ugu_b200_rasterizer_sync(ugu_b200_rasterizer* r) {
   if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
   CU_TRY(r, cudaSetDevice(r->device));

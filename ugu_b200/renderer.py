@@ -382,6 +382,10 @@ class Rasterizer:
         if rc != N.OK:
             LOGE(N.last_error(self._h))
             return False
+        hz = int(self._lib.ugu_b200_rasterizer_last_hazards(self._h))
+        if hz:
+            LOGW(f"{hz} fragment(s) with depth < FLT_MIN or NaN: the reference's result is order dependent there "
+                 "(rasterizer.cc:229) and this frame may differ from it at those pixels")
         return True
 
     def _render_call(self, cam: "N.Camera", out: "N.Outputs") -> int:
@@ -768,11 +772,23 @@ class Raytracer(Rasterizer):
         """len(cameras) views back to back on one stream; view i lands at element offset i*W*H of each
         output (DEVICE pointers; the multi-view driver's path, ugu_b200.multiview.MultiViewRenderer — the
         reference's own visibility pass casts BVH rays, include/ugu/texturing/visibility_tester.h)."""
-        if not on_device:
-            raise NotImplementedError("Raytracer.render_batch takes device outputs (use Render for host images)")
         if not cameras:
             return
         P = cameras[0].width() * cameras[0].height()
+        if not on_device:  # host destinations: one synchronous ray-cast call per view into the view's slab
+            opt = self._native_option()
+            self._lib.ugu_b200_rasterizer_set_option(self._h, C.byref(opt))
+            for i, cam in enumerate(cameras):
+                out = N.Outputs(None if color is None else color + i * P * 3,
+                                None if depth is None else depth + i * P * 4,
+                                None if normal is None else normal + i * P * 12,
+                                None if mask is None else mask + i * P,
+                                None if face_id is None else face_id + i * P * 4)
+                rc = self._lib.ugu_b200_rasterizer_raytrace(self._h, C.byref(cam.to_native()), self._org(cam),
+                                                            C.byref(out))
+                if rc != N.OK:
+                    raise RuntimeError(N.last_error(self._h))
+            return
         for i, cam in enumerate(cameras):
             self.render_device(cam,
                                color=None if color is None else color + i * P * 3,
