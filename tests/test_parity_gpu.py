@@ -496,3 +496,45 @@ def test_hazard_fragments_are_reported_not_silent():
     run2 = util.CudaRunner(mesh2, opt)
     assert run2.render(cam, opt, want=("depth",)) is not None
     assert int(lib.ugu_b200_rasterizer_last_hazards(run2.r._h)) == 0
+
+
+# ---- tile jobs folded into the resolve kernel (no binned_kernel launch), forced on meshes that DO queue triangles -----
+@pytest.fixture
+def folded(monkeypatch):
+    monkeypatch.setenv("UGU_B200_FOLD_BINNED", "1")
+
+
+@pytest.mark.parametrize("name", [n for n in util.golden_names() if n.startswith(("spot", "soup", "kat"))])
+def test_folded_tile_jobs_vs_reference_golden(folded, name):
+    mesh, cam, opt, want, _ = util.load_golden(name)
+    run = util.CudaRunner(mesh, opt)
+    for rep in range(2):  # twice: the grid barrier re-arms itself, the queue is left empty
+        got = run.render(cam, opt)
+        util.assert_parity(got, want, strict=True, color_lsb=_lsb(opt), what=f"folded {name} #{rep}")
+
+
+def test_folded_tile_jobs_close_up_and_batches(folded):
+    """Thousands of tile jobs rasterised by the resolve grid behind its barrier; single views, a 5-view batch
+    (per-view barriers) and a size change."""
+    import torch
+    mesh = meshgen.icosphere(1)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, backface_culling=False)
+    run = util.CudaRunner(mesh, opt)
+    port = OraclePort(mesh)
+    cams = [PinholeCamera(640, 360, meshgen.look_at_c2w((0.0, 0.0, -1.05 - 0.1 * i), (0.05, 0.02, 0), (0, -1, 0)),
+                          fov_y_deg=70.0) for i in range(5)]
+    wants = [port.render(c.to_native(), opt) for c in cams]
+    for c, w in zip(cams, wants):
+        util.assert_parity(run.render(c, opt), w, strict=True, what="folded close-up")
+    assert run.r.stats()["tile_jobs"] > 1000
+    P = 640 * 360
+    fid = torch.empty(5 * P, dtype=torch.int32, device="cuda")
+    dep = torch.empty(5 * P, dtype=torch.float32, device="cuda")
+    run.r.render_batch(cams, face_id=fid.data_ptr(), depth=dep.data_ptr(), on_device=True,
+                       stream=torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for i, w in enumerate(wants):
+        assert np.array_equal(fid[i * P:(i + 1) * P].cpu().numpy().reshape(360, 640), w["face_id"]), i
+        assert np.array_equal(util.bits(dep[i * P:(i + 1) * P].cpu().numpy().reshape(360, 640)), util.bits(w["depth"])), i
+    cam2 = PinholeCamera(97, 61, cams[0].c2w(), fov_y_deg=70.0)
+    util.assert_parity(run.render(cam2, opt), port.render(cam2.to_native(), opt), strict=True, what="folded small")

@@ -71,6 +71,7 @@ struct ugu_b200_rasterizer {
                      // ones go to the tile-job queue.  0 = adaptive (see RenderView)
   bool use_pdl = true;  // programmatic dependent launch of the per-view kernels (UGU_B200_PDL=0 disables)
   int tiles = -1;       // per-tile triangle lists for large triangles (tile_kernel): -1 = by mesh size, 0 / 1 forced (UGU_B200_TILES)
+  int fold_binned = -1; // resolve_kernel owns the tile-job queue, no binned_kernel launch: -1 = by mesh size (UGU_B200_FOLD_BINNED)
   int two_pass = -1;    // occlusion ordering of raster_kernel: -1 = by mesh size, 0 / 1 forced (UGU_B200_TWOPASS)
 
   // internal device outputs for the host-destination paths (two sets for batch overlap)
@@ -525,6 +526,7 @@ ShadeParams MakeShade(const ugu_b200_rasterizer* r, const ugu_b200_outputs* dout
   sp.face_id = dout->face_id;
   sp.view_pixels = view_pixels;
   sp.first_view = first_view;
+  sp.fold_binned = 0;
   return sp;
 }
 
@@ -576,7 +578,15 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
     fr.order = (int*)r->order.p;
   const MeshDev& m = r->mesh;
   const size_t P = (size_t)W * H;
-  const ShadeParams sp = MakeShade(r, dout, P, first_view);
+  ShadeParams sp = MakeShade(r, dout, P, first_view);
+  // Meshes of small triangles rarely queue anything: no binned_kernel launch (it would read one counter and exit,
+  // ~3 us of every view); the resolve kernel rasterises whatever was queued behind a grid barrier (raster_kernels.cuh).
+  // Not with the G-buffer kernel in between, which needs the finished visibility buffer.
+  // Measured (profiles/r03b_fold_binned_ab.jsonl): config 2 74.1 -> 72.9 us, config 5 38.9 -> 37.7 us per single view;
+  // a batch amortises the launch over its views (0.4 us per view) and keeps it.
+  const bool fold_binned = gbuf == nullptr && r->tiles <= 0 &&
+                           (r->fold_binned >= 0 ? r->fold_binned != 0 : (NV == 1 && r->mesh.F >= kTwoPassMinFaces));
+  sp.fold_binned = fold_binned ? 1 : 0;
   const bool pdl = r->use_pdl;
   const unsigned ny = (unsigned)n;
   {
@@ -598,7 +608,7 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
     else if (use_tiles) CU_TRY(r, LaunchView(raster_kernel<1, 4, NV, 0, true>, grid, 256, st, pdl, vb, m, fr));
     else CU_TRY(r, LaunchView(raster_kernel<1, 6, NV, 0>, grid, 256, st, pdl, vb, m, fr));
   }
-  if (m.F > 0) {
+  if (m.F > 0 && !fold_binned) {
     StageTimer t(r, st, UGU_B200_STAGE_BINNED);
     if (use_tiles && !two_launch) {
       CU_TRY(r, LaunchView(tile_kernel<NV>, dim3((unsigned)fr.s_tiles, ny), 256, st, pdl, vb, m, fr));
@@ -628,13 +638,16 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
     const bool need_nrm = sp.normal != nullptr || (need_color && sp.diffuse_shading != 0);
     const int color_mode = need_color ? sp.diffuse_color : 0;
     const int nmode = !need_nrm ? 0 : (sp.shading_normal == 0 ? 1 : (m.vattr ? 3 : 2));
-    const unsigned gx = std::max(1u, std::min(((unsigned)(g_num_sms * 4) + ny - 1) / ny, (chunks + 7) / 8));
+    // (folded tile jobs: the grid barrier needs every CTA resident at once — round down, never up)
+    const unsigned per_view = fold_binned ? (unsigned)(g_num_sms * 4) / ny : ((unsigned)(g_num_sms * 4) + ny - 1) / ny;
+    const unsigned gx = std::max(1u, std::min(per_view, (chunks + 7) / 8));
     const dim3 grid(gx, ny);
     // (the one-chunk-deeper variant <.., true>, which also prefetches the projected vertices, measured
     //  slower on every config: its extra live registers spill at 4 CTAs/SM — see DESIGN.md)
 #define UGU_RESOLVE_CASE(C, N)                                                                      \
   case (C)*4 + (N):                                                                                 \
-    CU_TRY(r, LaunchView(resolve_kernel<C, N, 4, false, NV>, grid, 256, st, pdl, vb, m, fr, sp));   \
+    if (fold_binned) CU_TRY(r, LaunchView(resolve_kernel<C, N, 4, false, NV, true>, grid, 256, st, pdl, vb, m, fr, sp)); \
+    else CU_TRY(r, LaunchView(resolve_kernel<C, N, 4, false, NV, false>, grid, 256, st, pdl, vb, m, fr, sp)); \
     break;
     switch (color_mode * 4 + nmode) {
       UGU_RESOLVE_CASE(0, 0)
@@ -655,7 +668,7 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
 #undef UGU_RESOLVE_CASE
   }
   CU_TRY(r, cudaGetLastError());
-  r->stats.kernel_launches += (m.F > 0) ? 4 : 2;
+  r->stats.kernel_launches += (m.F > 0) ? (fold_binned ? 3 : 4) : 2;
   r->stats.views += (uint64_t)n;
   if (r->profiling) r->stats.timed_views += (uint64_t)n;
   r->stats.h2d_bytes += sizeof(ViewParams) * (size_t)n;
@@ -816,6 +829,8 @@ int SnapshotCounters(ugu_b200_rasterizer* r) {
   const unsigned long long total = r->counters_host[2];
   r->stats.hazard_fragments = total - r->hazard_seen;
   r->hazard_seen = total;
+  if (r->stats.hazard_fragments >= kQueueOverflowFlag)
+    return Fail(r, UGU_B200_E_INVALID, "tile-job queue overflow: more than 2^%d tile jobs in one view", kQueueJobBits);
   return UGU_B200_OK;
 }
 
@@ -884,6 +899,7 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   }
   if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
   if (const char* e = getenv("UGU_B200_TWOPASS")) r->two_pass = std::max(0, std::min(2, atoi(e)));
+  if (const char* e = getenv("UGU_B200_FOLD_BINNED")) r->fold_binned = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("UGU_B200_TILES")) r->tiles = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("UGU_B200_RASTER_MINB")) g_ordered_minb = atoi(e) == 6 ? 6 : 5;
   if (const char* e = getenv("UGU_B200_COPY_THREADS")) r->copy_threads = std::max(1, std::min(atoi(e), 64));
@@ -1301,8 +1317,7 @@ int ugu_b200_rasterizer_render(ugu_b200_rasterizer* r, const ugu_b200_camera* ca
   std::vector<CopySeg> segs;
   CollectSegs(host_out, &dout, P, 0, 1, &segs);
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
-  SnapshotCounters(r);
-  return UGU_B200_OK;
+  return SnapshotCounters(r);
 }
 
 namespace {
@@ -1406,8 +1421,7 @@ int ugu_b200_rasterizer_render_gbuffer(ugu_b200_rasterizer* r, const ugu_b200_ca
   CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
                             r->stream));
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
-  SnapshotCounters(r);
-  return UGU_B200_OK;
+  return SnapshotCounters(r);
 }
 
 namespace {
@@ -1486,8 +1500,7 @@ int ugu_b200_rasterizer_raytrace(ugu_b200_rasterizer* r, const ugu_b200_camera* 
   std::vector<CopySeg> segs;
   CollectSegs(host_out, &dout, P, 0, 1, &segs);
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
-  SnapshotCounters(r);
-  return UGU_B200_OK;
+  return SnapshotCounters(r);
 }
 
 int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
@@ -1551,7 +1564,7 @@ int ugu_b200_rasterizer_render_batch(ugu_b200_rasterizer* r, int32_t num_views,
   CU_TRY(r, cudaStreamSynchronize(r->stream));
   CU_TRY(r, cudaStreamSynchronize(r->copy_stream));
   r->copied_pending[0] = r->copied_pending[1] = false;
-  SnapshotCounters(r);
+  if ((rc = SnapshotCounters(r))) return rc;
   return UGU_B200_OK;
 }
 

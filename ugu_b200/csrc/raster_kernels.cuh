@@ -35,6 +35,7 @@ constexpr int kJobW = 8;              // large-triangle tile job: 8 x 4 pixels =
 constexpr int kJobH = 4;
 constexpr int kQueueJobBits = 38;     // packed queue counter: [63:38] entries, [37:0] tile jobs
 constexpr unsigned long long kQueueJobMask = (1ull << kQueueJobBits) - 1ull;
+constexpr unsigned long long kQueueOverflowFlag = 1ull << 48;  // added to the hazard counter when the job field carries
 constexpr int kJobsPerChunk = 16;     // tile jobs a warp claims at a time in the binned kernel
 constexpr int kTile = 16;             // screen tile of the per-tile triangle lists: 16 x 16 pixels = one CTA of tile_kernel
 constexpr int kTileShift = 4;
@@ -116,7 +117,7 @@ struct FrameDev {
   // summed over every view since the handle was created (never reset; the host reports deltas).
   unsigned long long s_proj, s_ray_dx, s_ray_dy, s_vis, s_q, s_order, s_tiles;
 };
-constexpr int kCounterSlab = 8;
+constexpr int kCounterSlab = 16;  // words [8] / [9]: arrive / leave counters of resolve_kernel's grid barrier
 constexpr int kTotalsOffset = 6;
 
 __device__ __forceinline__ FrameDev frame_view(const FrameDev& b, int view) {
@@ -148,6 +149,7 @@ struct ShadeParams {
   // batch: view v of the launch set writes at element offset (first_view + v) * view_pixels of every output
   unsigned long long view_pixels;
   unsigned first_view;
+  int fold_binned;  // no binned_kernel was launched for this launch set: the resolve kernel owns the tile-job queue
 };
 
 __device__ __forceinline__ ShadeParams shade_view(const ShadeParams& b, int view) {
@@ -692,15 +694,23 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
       }
       const unsigned long long total = __shfl_sync(0xffffffffu, incl, 31);
       unsigned long long qbase = 0ull;
-      if (lane == 31u) qbase = atomicAdd(fr.counters, total);
+      if (lane == 31u) {
+        qbase = atomicAdd(fr.counters, total);
+        // 2^38 tile jobs in one view (hundreds of thousands of screen-filling triangles) would carry into the
+        // entry count: flag the view (the host reports kQueueOverflowFlag in the hazard counter as an error);
+        // the guards below and in binned_kernel keep every access in bounds meanwhile
+        if (((qbase & kQueueJobMask) + (total & kQueueJobMask)) >> kQueueJobBits) atomicAdd(fr.counters + 1, kQueueOverflowFlag);
+      }
       qbase = __shfl_sync(0xffffffffu, qbase, 31);
       unsigned long long excl = qbase + incl - mine;
 #pragma unroll
       for (int h = 0; h < HALVES; h++) {
         if (my[h] != 0ull) {
           const unsigned qslot = (unsigned)(excl >> kQueueJobBits);
-          fr.q_face[qslot] = face[h];
-          fr.q_job[qslot] = excl & kQueueJobMask;
+          if (qslot < (unsigned)m.F) {
+            fr.q_face[qslot] = face[h];
+            fr.q_job[qslot] = excl & kQueueJobMask;
+          }
           excl += my[h];
         }
       }
@@ -776,21 +786,18 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
 // 32-ary search, then walks entries; a job is an 8x4 pixel block of the triangle's bbox, one lane
 // per pixel.  Persistent grid (multiple of the SM count); exits at once when the queue is empty.
 // ---------------------------------------------------------------------------------------------
-template <int NV>
-__global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, const MeshDev m,
-                                                     const FrameDev fr0) {
-  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
-  const ViewParams& vp = vb.v[view];
-  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
-  pdl_launch_dependents();
-  pdl_wait();
-  const unsigned long long packed = fr.counters[0];
+// The tile jobs of one view, shared by `nwarps` warps of which this is warp `gw` (binned_kernel's grid, or the
+// resolve kernel's when the separate launch is folded away).
+// L2ONLY: the early-z read of the visibility buffer bypasses L1 — inside resolve_kernel the same SM reads those
+// lines again after atomics of other SMs have changed them in L2, and must not find a stale copy.
+template <bool L2ONLY>
+__device__ __forceinline__ void tile_jobs(const ViewParams& vp, const MeshDev& m, const FrameDev& fr,
+                                          unsigned long long packed, unsigned long long gw,
+                                          unsigned long long nwarps) {
   const unsigned long long T = packed & kQueueJobMask;
-  const unsigned n = (unsigned)(packed >> kQueueJobBits);
-  if (T == 0ull) return;
+  const unsigned n = min((unsigned)(packed >> kQueueJobBits), (unsigned)m.F);  // (clamped: see the overflow flag)
+  if (T == 0ull || n == 0u) return;
   const unsigned lane = threadIdx.x & 31u;
-  const unsigned long long nwarps = (unsigned long long)gridDim.x * (blockDim.x >> 5);
-  const unsigned long long gw = (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   // Jobs per chunk: every warp makes `rounds` passes over interleaved chunks of at most
   // kJobsPerChunk jobs, sized so that the chunk count is (just under) a multiple of the warp count
   // — with a fixed chunk size a job count slightly above nwarps * kJobsPerChunk would hand a few
@@ -857,7 +864,7 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, con
           const bool neg = (w0 <= 0.0f) && (w1 <= 0.0f) && (w2 <= 0.0f);
           if (pos || neg) {
             const size_t pix = (size_t)y * vp.W + x;
-            const unsigned long long seen = fr.vis[pix];  // consumed after the divisions
+            const unsigned long long seen = L2ONLY ? __ldcg(fr.vis + pix) : fr.vis[pix];  // consumed after the divisions
             const bool bf = has_fn ? facing_backface(vp, m, fr, g, f, x, y) : false;
             if (bf ? neg : pos) {
               const float z = tri_depth(t, w0, w1, w2);
@@ -870,6 +877,18 @@ __global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, con
       ++e;
     }
   }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, const MeshDev m,
+                                                     const FrameDev fr0) {
+  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
+  const ViewParams& vp = vb.v[view];
+  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
+  pdl_launch_dependents();
+  pdl_wait();
+  tile_jobs<false>(vp, m, fr, fr.counters[0], (unsigned long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5),
+            (unsigned long long)gridDim.x * (blockDim.x >> 5));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1236,7 +1255,8 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
 // vertices (and uvs) of chunk i+1, the face record of chunk i+2 and the key of chunk i+3 are in
 // flight, so of the dependent chain key -> face record -> projected vertices / attributes -> texels
 // only the last links are exposed, and those overlap the weight arithmetic of the same chunk.
-template <int COLOR, int NMODE, int MINB, bool DEEP, int NV>
+// FOLD: no binned_kernel ran for this launch set; this kernel owns the tile-job queue (see below).
+template <int COLOR, int NMODE, int MINB, bool DEEP, int NV, bool FOLD = false>
 __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> vb, const MeshDev m,
                                                             const FrameDev fr0, const ShadeParams sp0) {
   const int view = (NV == 1) ? 0 : (int)blockIdx.y;
@@ -1256,6 +1276,43 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> 
   const unsigned nwarps = gridDim.x * 8u;
   pdl_launch_dependents();
   pdl_wait();
+  const bool cull = sp.backface_culling != 0;
+  using Stage = ResolveStage<COLOR, NMODE>;
+  unsigned chunk = blockIdx.x * 8u + warp;
+  Stage a{}, b{}, c{};  // chunk, chunk + nwarps, chunk + 2 nwarps
+  // FOLD: the queue counter travels with the first keys (one round trip, not two); the keys are speculative
+  const unsigned long long packed = FOLD ? fr.counters[0] : 0ull;
+  a.key = resolve_load_key(fr, chunk, nchunks, lane, P);
+  b.key = resolve_load_key(fr, chunk + nwarps, nchunks, lane, P);
+  c.key = resolve_load_key(fr, chunk + 2u * nwarps, nchunks, lane, P);
+  if (FOLD && (packed & kQueueJobMask) != 0ull) {
+    // No binned_kernel ran (meshes of small triangles: the launch would read one counter and exit, ~3 us of every
+    // view), but this view queued triangles after all: this grid rasterises them first — it is persistent and
+    // co-resident (<= 4 CTAs per SM, and its PDL successor cannot start before all of its CTAs have), so a grid
+    // barrier is safe — and only then resolves.  Every thread reads the same counter: the branch is grid-uniform;
+    // the counter is reset after the barrier.
+    tile_jobs<true>(vp, m, fr, packed, (unsigned long long)blockIdx.x * 8u + warp, (unsigned long long)nwarps);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicAdd(fr.counters + 8, 1ull);
+      while (*(volatile unsigned long long*)(fr.counters + 8) < (unsigned long long)gridDim.x) {
+      }
+      __threadfence();
+      // the last CTA to leave re-arms the barrier for the next view
+      if (atomicAdd(fr.counters + 9, 1ull) == (unsigned long long)gridDim.x - 1ull) {
+        fr.counters[8] = 0ull;
+        fr.counters[9] = 0ull;
+      }
+    }
+    __syncthreads();
+    // the speculative keys are stale, and so are their lines in this SM's L1: reload from L2
+    a.key = b.key = c.key = kVisEmpty;
+    const unsigned pa = chunk * 32u + lane, pb = (chunk + nwarps) * 32u + lane, pc = (chunk + 2u * nwarps) * 32u + lane;
+    if (chunk < nchunks && pa < P) a.key = __ldcg(fr.vis + pa);
+    if (chunk + nwarps < nchunks && pb < P) b.key = __ldcg(fr.vis + pb);
+    if (chunk + 2u * nwarps < nchunks && pc < P) c.key = __ldcg(fr.vis + pc);
+  }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     // the queue / hazard counters are consumed: snapshot them for the host (counters[4..5]) and
     // reset them for the next view
@@ -1268,14 +1325,6 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> 
     fr.counters[3] = 0ull;
     fr.counters[7] = 0ull;
   }
-  const bool cull = sp.backface_culling != 0;
-  using Stage = ResolveStage<COLOR, NMODE>;
-
-  unsigned chunk = blockIdx.x * 8u + warp;
-  Stage a{}, b{}, c{};  // chunk, chunk + nwarps, chunk + 2 nwarps
-  a.key = resolve_load_key(fr, chunk, nchunks, lane, P);
-  b.key = resolve_load_key(fr, chunk + nwarps, nchunks, lane, P);
-  c.key = resolve_load_key(fr, chunk + 2u * nwarps, nchunks, lane, P);
   resolve_stage2(m, cull, a);
   resolve_stage2(m, cull, b);
   if (DEEP) resolve_stage3(m, fr, cull, a);

@@ -266,8 +266,16 @@ __global__ void __launch_bounds__(128) uv_tile_kernel(const UvRasterParams p) {
 // (w0*c0 + w1*c1) + w2*c2 (raster_util.h:138-139), convert (saturate_cast, :106-115: std::round for
 // integer texels, then the truncating cast) and store 12 / 48 packed bytes + 4 mask bytes.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned uv_to_u8(float c) {  // (uint8_t)std::round(c) through cvttss2si
-  return (unsigned)cvtt_x86(roundf(c)) & 0xFFu;
+// (uint8_t)std::round(c) through cvttss2si.  std::round = half away from zero: truncate (one FRND), the exact
+// remainder decides the step — the same integer as roundf's generic sequence for every |c| < 2^23, which covers the
+// whole range whose low byte can be non-zero... values beyond are integers already (round is the identity) up to
+// the conversion's range, and out-of-range / NaN inputs give the low byte of INT_MIN = 0.
+__device__ __forceinline__ unsigned uv_to_u8(float c) {
+  if (!(c > -2147483904.0f && c < 2147483648.0f)) return 0u;
+  const float t = truncf(c);
+  const float fr = c - t;  // exact
+  const int step = (fr >= 0.5f) ? 1 : ((fr <= -0.5f) ? -1 : 0);
+  return (unsigned)(__float2int_rz(t) + step) & 0xFFu;
 }
 
 constexpr int kUvGroupsPerThread = 4;  // 4-texel groups per thread: 64 bytes of winners in flight per thread
