@@ -521,76 +521,17 @@ __device__ __forceinline__ void raster_fragments(const ViewParams& vp, const Mes
   }
 }
 
-// PASS 0: CTA i takes block i.  PASS 1: the occlusion ordering above — CTA i takes block order[i] and applies
-// the occlusion test when i is past the camera-facing blocks (HALVES == 1).
-// TILES: triangles too large for the cooperative path that overlap at most 3 x 3 screen tiles are appended to the
-// per-tile lists of tile_kernel; the rest (and whatever finds a list full) goes to the tile-job queue.
-template <int HALVES, int MINB, int NV, int PASS, bool TILES = false>
-__global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> vb, const MeshDev m,
-                                                           const FrameDev fr0) {
-  static_assert(PASS == 0 || HALVES == 1, "block records are per 8 warps x 32 faces");
-  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
-  const ViewParams& vp = vb.v[view];
-  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
-  __shared__ WarpTris<HALVES> sh[8];
-  WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
-  const unsigned lane = threadIdx.x & 31u;
+// Everything a warp does for its 32 * HALVES faces in ONE view once their indices, (optional) normals and projected
+// vertices are in registers: rejects, occlusion test of deferred blocks, queueing of large triangles, the
+// shared-memory table, phase B and the fragment stage.
+template <int HALVES, int PASS, bool TILES>
+__device__ __forceinline__ void raster_warp_view(const ViewParams& vp, const MeshDev& m, const FrameDev& fr,
+                                                 WarpTris<HALVES>& S, const unsigned lane, const bool has_fn,
+                                                 const bool deferred, const int (&fidx)[HALVES], int (&face)[HALVES],
+                                                 float (&fnx)[HALVES], float (&fny)[HALVES], float (&fnz)[HALVES],
+                                                 const float4 (&pa)[HALVES], const float4 (&pb)[HALVES],
+                                                 const float4 (&pc)[HALVES]) {
   const unsigned lt_mask = (1u << lane) - 1u;
-  pdl_launch_dependents();
-  unsigned blk = blockIdx.x;
-  bool deferred = false;
-  if (PASS == 1) {
-    pdl_wait();  // the block order of this view comes from the vertex kernel
-    blk = (unsigned)fr.order[blockIdx.x];
-    deferred = (unsigned long long)blockIdx.x >= fr.counters[3];
-  }
-  if (PASS >= 2) {  // two launches over all blocks: PASS 2 takes the camera-facing ones, PASS 3 the others
-    deferred = group_deferred(vp, __ldg(m.grp + blk));
-    if (deferred != (PASS == 3)) {
-      // not this pass's block.  CTA 0 waits all the same: a grid none of whose threads waited could complete
-      // before its predecessor and break the chain for its successor.
-      if (blockIdx.x == 0) pdl_wait();
-      return;
-    }
-  }
-  const int base = (int)((blk * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
-  if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
-  const bool has_fn = m.num_face_normals > 0;
-
-  // ---- Phase A ---------------------------------------------------------------------------------
-  int fidx[HALVES], face[HALVES];
-  int i0[HALVES], i1[HALVES], i2[HALVES];
-  float4 pa[HALVES], pb[HALVES], pc[HALVES];
-  float fnx[HALVES], fny[HALVES], fnz[HALVES];
-#pragma unroll
-  for (int h = 0; h < HALVES; h++) {
-    fnx[h] = fny[h] = fnz[h] = 0.f;
-    i0[h] = i1[h] = i2[h] = 0;
-    fidx[h] = base + h * 32 + (int)lane;  // slot in raster order
-    face[h] = fidx[h];
-    if (fidx[h] < m.F) {  // immutable mesh data: may be read before the vertex kernel has finished
-      i0[h] = __ldg(m.r_idx0 + fidx[h]);
-      i1[h] = __ldg(m.r_idx1 + fidx[h]);
-      i2[h] = __ldg(m.r_idx2 + fidx[h]);
-      if (PASS != 0 && deferred) continue;  // face id and normal only for the triangles that survive
-      if (m.r_face) face[h] = __ldg(m.r_face + fidx[h]);
-      if (has_fn) {  // same round trip as the indices, not a third dependent one
-        fnx[h] = __ldg(m.r_fn_x + fidx[h]);
-        fny[h] = __ldg(m.r_fn_y + fidx[h]);
-        fnz[h] = __ldg(m.r_fn_z + fidx[h]);
-      }
-    }
-  }
-  if (PASS != 1) pdl_wait();  // projected vertices of this view; visibility buffer / counters left clean by resolve
-#pragma unroll
-  for (int h = 0; h < HALVES; h++) {
-    if (fidx[h] < m.F) {
-      // plain (coherent) loads: proj is rewritten every view by the preceding kernel
-      pa[h] = fr.proj[i0[h]];
-      pb[h] = fr.proj[i1[h]];
-      pc[h] = fr.proj[i2[h]];
-    }
-  }
   int nslots = 0, T = 0;
   unsigned long long my[HALVES];  // packed (1 entry, njobs) when the face is queued
 #pragma unroll
@@ -776,6 +717,79 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
     __syncwarp();
     raster_fragments(vp, m, fr, S, has_fn, qhead, qcount, lane);
   }
+}
+
+// PASS 0: CTA i takes block i.  PASS 1: the occlusion ordering above — CTA i takes block order[i] and applies
+// the occlusion test when i is past the camera-facing blocks (HALVES == 1).
+// TILES: triangles too large for the cooperative path that overlap at most 3 x 3 screen tiles are appended to the
+// per-tile lists of tile_kernel; the rest (and whatever finds a list full) goes to the tile-job queue.
+template <int HALVES, int MINB, int NV, int PASS, bool TILES = false>
+__global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> vb, const MeshDev m,
+                                                           const FrameDev fr0) {
+  static_assert(PASS == 0 || HALVES == 1, "block records are per 8 warps x 32 faces");
+  const int view = (NV == 1) ? 0 : (int)blockIdx.y;
+  const ViewParams& vp = vb.v[view];
+  const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
+  __shared__ WarpTris<HALVES> sh[8];
+  WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  pdl_launch_dependents();
+  unsigned blk = blockIdx.x;
+  bool deferred = false;
+  if (PASS == 1) {
+    pdl_wait();  // the block order of this view comes from the vertex kernel
+    blk = (unsigned)fr.order[blockIdx.x];
+    deferred = (unsigned long long)blockIdx.x >= fr.counters[3];
+  }
+  if (PASS >= 2) {  // two launches over all blocks: PASS 2 takes the camera-facing ones, PASS 3 the others
+    deferred = group_deferred(vp, __ldg(m.grp + blk));
+    if (deferred != (PASS == 3)) {
+      // not this pass's block.  CTA 0 waits all the same: a grid none of whose threads waited could complete
+      // before its predecessor and break the chain for its successor.
+      if (blockIdx.x == 0) pdl_wait();
+      return;
+    }
+  }
+  const int base = (int)((blk * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
+  if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
+  const bool has_fn = m.num_face_normals > 0;
+
+  // ---- Phase A ---------------------------------------------------------------------------------
+  int fidx[HALVES], face[HALVES];
+  int i0[HALVES], i1[HALVES], i2[HALVES];
+  float4 pa[HALVES], pb[HALVES], pc[HALVES];
+  float fnx[HALVES], fny[HALVES], fnz[HALVES];
+#pragma unroll
+  for (int h = 0; h < HALVES; h++) {
+    fnx[h] = fny[h] = fnz[h] = 0.f;
+    i0[h] = i1[h] = i2[h] = 0;
+    fidx[h] = base + h * 32 + (int)lane;  // slot in raster order
+    face[h] = fidx[h];
+    if (fidx[h] < m.F) {  // immutable mesh data: may be read before the vertex kernel has finished
+      i0[h] = __ldg(m.r_idx0 + fidx[h]);
+      i1[h] = __ldg(m.r_idx1 + fidx[h]);
+      i2[h] = __ldg(m.r_idx2 + fidx[h]);
+      if (PASS != 0 && deferred) continue;  // face id and normal only for the triangles that survive
+      if (m.r_face) face[h] = __ldg(m.r_face + fidx[h]);
+      if (has_fn) {  // same round trip as the indices, not a third dependent one
+        fnx[h] = __ldg(m.r_fn_x + fidx[h]);
+        fny[h] = __ldg(m.r_fn_y + fidx[h]);
+        fnz[h] = __ldg(m.r_fn_z + fidx[h]);
+      }
+    }
+  }
+  if (PASS != 1) pdl_wait();  // projected vertices of this view; visibility buffer / counters left clean by resolve
+#pragma unroll
+  for (int h = 0; h < HALVES; h++) {
+    if (fidx[h] < m.F) {
+      // plain (coherent) loads: proj is rewritten every view by the preceding kernel
+      pa[h] = fr.proj[i0[h]];
+      pb[h] = fr.proj[i1[h]];
+      pc[h] = fr.proj[i2[h]];
+    }
+  }
+  raster_warp_view<HALVES, PASS, TILES>(vp, m, fr, S, lane, has_fn, deferred, fidx, face, fnx, fny, fnz, pa, pb, pc);
 }
 
 // ---------------------------------------------------------------------------------------------
