@@ -893,8 +893,10 @@ __device__ __forceinline__ void tile_jobs(const ViewParams& vp, const MeshDev& m
   }
 }
 
+// (8 CTAs of 4 warps per SM = at most 64 registers: the batch instantiation would otherwise take 71 and lose a CTA
+//  per SM — config 3 batched 38.6 -> 35.9 us per view, profiles/r03g_binned_launch_bounds.jsonl)
 template <int NV>
-__global__ void __launch_bounds__(128) binned_kernel(const ViewBatch<NV> vb, const MeshDev m,
+__global__ void __launch_bounds__(128, 8) binned_kernel(const ViewBatch<NV> vb, const MeshDev m,
                                                      const FrameDev fr0) {
   const int view = (NV == 1) ? 0 : (int)blockIdx.y;
   const ViewParams& vp = vb.v[view];
