@@ -191,14 +191,21 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
                                                         const RtParams rp) {
   __shared__ RtWarpFaces sh[8];
   RtWarpFaces& S = sh[threadIdx.x >> 5];
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  // faces are walked in RASTER ORDER (raster_api.cu BuildFaceOrder: a warp's 32 faces are neighbours in space,
+  // so are their positions, projected vertices and nearest-hit pixels); `f` is the face id the outputs carry
+  const int rs = blockIdx.x * blockDim.x + threadIdx.x;
+  int f = rs;
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
   int x0 = 0, y0 = 0, x1 = -1, y1 = -1, kind = 0;
   float A[3], B[3], C[3];
-  if (f < m.F) {
-    int i0, i1, i2;
-    rt_load_face(m, rp, f, i0, i1, i2, A, B, C);
+  if (rs < m.F) {
+    const int i0 = __ldg(m.r_idx0 + rs), i1 = __ldg(m.r_idx1 + rs), i2 = __ldg(m.r_idx2 + rs);
+    if (m.r_face) f = __ldg(m.r_face + rs);
+    const float4 p0 = __ldg(m.pos4 + i0), p1 = __ldg(m.pos4 + i1), p2 = __ldg(m.pos4 + i2);
+    A[0] = p0.x - rp.org[0]; A[1] = p0.y - rp.org[1]; A[2] = p0.z - rp.org[2];
+    B[0] = p1.x - rp.org[0]; B[1] = p1.y - rp.org[1]; B[2] = p1.z - rp.org[2];
+    C[0] = p2.x - rp.org[0]; C[1] = p2.y - rp.org[1]; C[2] = p2.z - rp.org[2];
     kind = rt_bounds(vp, rp, fr.proj[i0], fr.proj[i1], fr.proj[i2], x0, y0, x1, y1);
   }
   const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
