@@ -584,8 +584,12 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   // Not with the G-buffer kernel in between, which needs the finished visibility buffer.
   // Measured (profiles/r03b_fold_binned_ab.jsonl): config 2 74.1 -> 72.9 us, config 5 38.9 -> 37.7 us per single view;
   // a batch amortises the launch over its views (0.4 us per view) and keeps it.
+  // (not the texture instantiations: they sit at the register limit, and carrying the tile-job code costs their hot
+  //  loop more than the launch — config 4 741 -> 756 us per view)
   const bool fold_binned = gbuf == nullptr && r->tiles <= 0 &&
-                           (r->fold_binned >= 0 ? r->fold_binned != 0 : (NV == 1 && r->mesh.F >= kTwoPassMinFaces));
+                           (r->fold_binned >= 0 ? r->fold_binned != 0
+                                                : (NV == 1 && r->mesh.F >= kTwoPassMinFaces &&
+                                                   !(dout->color != nullptr && r->opt.diffuse_color == UGU_B200_COLOR_TEXTURE)));
   sp.fold_binned = fold_binned ? 1 : 0;
   const bool pdl = r->use_pdl;
   const unsigned ny = (unsigned)n;
