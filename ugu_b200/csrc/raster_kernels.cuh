@@ -598,6 +598,7 @@ __device__ __forceinline__ void raster_warp_view(const ViewParams& vp, const Mes
     }
     // slot = rank among the recorded triangles; start = exclusive prefix of the sample counts
     const unsigned rec = __ballot_sync(0xffffffffu, cnt > 0);
+    if (rec == 0u) continue;  // (warp-uniform) nothing to record: sub-pixel, rejected or occluded triangles only
     int incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
