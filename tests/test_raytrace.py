@@ -300,6 +300,37 @@ def test_cuda_raytracer_device_form():
     assert np.array_equal(col.cpu().numpy().reshape(want["color"].shape), want["color"])
 
 
+@pytest.fixture
+def ordered(monkeypatch):
+    """Raytracers created inside the test take the occlusion ordering of rt_raster_kernel whatever the mesh size."""
+    monkeypatch.setenv("UGU_B200_TWOPASS", "1")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NAMES)
+def test_cuda_raytracer_ordered_vs_reference_fixture(ordered, name):
+    mesh, cam, opt, want = _load(name)
+    _, got = _cuda_raytrace(mesh, cam, opt)
+    _assert_same(got, want, "ordered " + name)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sliver", [False, True], ids=["shaped", "slivers"])
+def test_cuda_raytracer_ordered_occluded_debris(ordered, sliver):
+    """The wall-and-debris scene of the rasterizer's occlusion tests (hidden, partly visible and degenerate
+    triangles behind a camera-facing wall) through the ray-cast mode with the ordering forced."""
+    from test_parity_gpu import _wall_and_debris
+    from ugu_b200 import ShadingNormal
+    mesh = _wall_and_debris(17 + sliver, 12000, sliver)
+    port = OraclePort(mesh)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, shading_normal=ShadingNormal.kFace,
+                            backface_culling=False)
+    for (w, h, fov) in ((320, 240, 60.0), (203, 117, 75.0)):
+        cam = PinholeCamera(w, h, meshgen.look_at_c2w((0.02, -0.01, 0.0), (0, 0, 2.0), (0, -1, 0)), fov_y_deg=fov)
+        _, got = _cuda_raytrace(mesh, cam, opt)
+        _assert_same(got, port_raytrace(port, cam.to_native(), _org(cam), opt), f"rt debris {w}x{h}")
+
+
 @pytest.mark.gpu
 def test_cuda_raytracer_render_batch_host_form():
     """Raytracer.render_batch with HOST destinations (view i at slab i) equals per-view Render calls."""

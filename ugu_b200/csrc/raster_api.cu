@@ -1456,7 +1456,9 @@ int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float
   rp.ray_a = (float4*)r->rt_rays.p;
   rp.ray_b = rp.ray_a + P;
   const ShadeParams sp = MakeShade(r, dout, P);
-  const size_t vthreads = std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H);
+  // occlusion ordering of rt_raster_kernel, same policy as the rasterizer's
+  if (m.grp != nullptr && (r->two_pass >= 0 ? r->two_pass != 0 : m.F >= kTwoPassMinFaces)) fr.order = (int*)r->order.p;
+  const size_t vthreads = std::max<size_t>(std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H), ((size_t)m.F + 255) / 256);
   CU_TRY(r, LaunchView(vertex_kernel_b<1>, Blocks(vthreads, 256), 256, st, false, vb, 1, m, fr));
   CU_TRY(r, LaunchView(rt_ray_kernel, Blocks(P, 256), 256, st, false, vp, fr, rp));
   int launches = 3;

@@ -193,7 +193,13 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
   RtWarpFaces& S = sh[threadIdx.x >> 5];
   // faces are walked in RASTER ORDER (raster_api.cu BuildFaceOrder: a warp's 32 faces are neighbours in space,
   // so are their positions, projected vertices and nearest-hit pixels); `f` is the face id the outputs carry
-  const int rs = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned blk = blockIdx.x;
+  bool deferred = false;
+  if (fr.order) {  // occlusion ordering (raster_kernels.cuh): camera-facing blocks of 256 faces first
+    blk = (unsigned)fr.order[blockIdx.x];
+    deferred = (unsigned long long)blockIdx.x >= fr.counters[3];
+  }
+  const int rs = (int)(blk * blockDim.x + threadIdx.x);
   int f = rs;
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -206,7 +212,26 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
     A[0] = p0.x - rp.org[0]; A[1] = p0.y - rp.org[1]; A[2] = p0.z - rp.org[2];
     B[0] = p1.x - rp.org[0]; B[1] = p1.y - rp.org[1]; B[2] = p1.z - rp.org[2];
     C[0] = p2.x - rp.org[0]; C[1] = p2.y - rp.org[1]; C[2] = p2.z - rp.org[2];
-    kind = rt_bounds(vp, rp, fr.proj[i0], fr.proj[i1], fr.proj[i2], x0, y0, x1, y1);
+    const float4 qa = fr.proj[i0], qb = fr.proj[i1], qc = fr.proj[i2];
+    kind = rt_bounds(vp, rp, qa, qb, qc, x0, y0, x1, y1);
+    if (deferred && kind == 1 && x1 - x0 < 4 && y1 - y0 < 4) {
+      // A deferred face whose candidate pixels all hold a nearer hit already cannot win any of them.  nanort's
+      // t = (U Az + V Bz + W Cz) / (U + V + W) with U, V, W of one sign is a convex combination (up to 8 ulp) of
+      // the ray parameters Az.. at which the ray crosses the kz-planes of the vertices, whatever the shape of
+      // the triangle; and for a ray within angle alpha of the direction to a vertex at distance d that parameter
+      // is >= d (cos alpha - sqrt(3) sin alpha) (kz = dominant axis of the unit direction) >= 0.9826 d for
+      // alpha <= 0.01.  alpha <= (largest pixel distance between a candidate pixel and a projected vertex) / f.
+      const float xmin = fminf(fminf(qa.x, qb.x), qc.x), xmax = fmaxf(fmaxf(qa.x, qb.x), qc.x);
+      const float ymin = fminf(fminf(qa.y, qb.y), qc.y), ymax = fmaxf(fmaxf(qa.y, qb.y), qc.y);
+      const float dx = fmaxf((float)x1 - xmin, xmax - (float)x0), dy = fmaxf((float)y1 - ymin, ymax - (float)y0);
+      const float alpha = sqrtf(dx * dx + dy * dy) / fminf(vp.fx, vp.fy);
+      const float d2 = fminf(fminf(A[0] * A[0] + A[1] * A[1] + A[2] * A[2], B[0] * B[0] + B[1] * B[1] + B[2] * B[2]),
+                             C[0] * C[0] + C[1] * C[1] + C[2] * C[2]);
+      if (alpha <= 0.0095f && d2 > 1e-20f && d2 < 1e30f) {
+        const unsigned tbits = __float_as_uint(0.975f * sqrtf(d2));
+        if (bbox_occluded(fr, vp.W, x0, y0, x1 - x0 + 1, y1 - y0 + 1, tbits)) kind = 0;
+      }
+    }
   }
   const int nx = x1 - x0 + 1, ny = y1 - y0 + 1;
   const bool large = kind != 0 && (long long)nx * ny > (long long)rp.inlane_max;
@@ -403,6 +428,8 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
     fr.counters[4] = fr.counters[0];  // host snapshot: packed (queued faces, jobs)
     fr.counters[5] = 0ull;
     fr.counters[0] = 0ull;
+    fr.counters[3] = 0ull;  // block lists of the occlusion ordering (vertex kernel)
+    fr.counters[7] = 0ull;
   }
   const unsigned long long key = p < P ? fr.vis[p] : kVisEmpty;
   unsigned color = 0u;
