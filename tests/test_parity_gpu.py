@@ -538,3 +538,45 @@ def test_folded_tile_jobs_close_up_and_batches(folded):
         assert np.array_equal(util.bits(dep[i * P:(i + 1) * P].cpu().numpy().reshape(360, 640)), util.bits(w["depth"])), i
     cam2 = PinholeCamera(97, 61, cams[0].c2w(), fov_y_deg=70.0)
     util.assert_parity(run.render(cam2, opt), port.render(cam2.to_native(), opt), strict=True, what="folded small")
+
+
+# ---- occlusion ordering: well-shaped camera-averse patches behind an occluder -------------------------------------------
+def test_two_pass_patches_peeking_past_an_occluder(monkeypatch):
+    """Well-shaped, camera-averse patches (whole deferred blocks) behind a wall that covers them fully, partly or not
+    at all, with the ordering forced on this small mesh: against the oracle."""
+    from ugu_b200 import Mesh
+    monkeypatch.setenv("UGU_B200_TWOPASS", "1")
+    rng = np.random.RandomState(3)
+
+    def grid(n, x0, x1, y0, y1, z, flip):
+        gx, gy = np.meshgrid(np.linspace(x0, x1, n + 1), np.linspace(y0, y1, n + 1))
+        v = np.stack([gx.ravel(), gy.ravel(), np.full(gx.size, z) + 0.004 * rng.randn(gx.size)], 1)
+        q = [(j * (n + 1) + i, j * (n + 1) + i + 1, (j + 1) * (n + 1) + i, (j + 1) * (n + 1) + i + 1)
+             for j in range(n) for i in range(n)]
+        f = np.array([t for (a, b, c, d) in q for t in (((a, c, b), (b, c, d)) if not flip else ((a, b, c), (b, d, c)))],
+                     np.int32)
+        return v, f
+    parts = [grid(40, -0.6, 0.5, -0.5, 0.5, 2.0, False)]                       # the wall, facing the camera
+    for k in range(6):                                                            # patches facing away, behind / beside it
+        cx, cy = rng.uniform(-0.9, 0.9, 2)
+        parts.append(grid(16, cx - 0.2, cx + 0.2, cy - 0.2, cy + 0.2, rng.uniform(2.2, 3.0), True))
+    verts, faces, off = [], [], 0
+    for v, f in parts:
+        verts.append(v)
+        faces.append(f + off)
+        off += len(v)
+    verts = np.concatenate(verts).astype(np.float32)
+    faces = np.concatenate(faces).astype(np.int32)
+    fn = np.cross(verts[faces[:, 1]] - verts[faces[:, 0]], verts[faces[:, 2]] - verts[faces[:, 0]])
+    fn = (fn / np.linalg.norm(fn, axis=1, keepdims=True)).astype(np.float32)
+    mesh = Mesh(vertices=verts, vertex_indices=faces, face_normals=fn,
+                vertex_colors=rng.uniform(0, 255, verts.shape).astype(np.float32))
+    for culling in (True, False):
+        opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, shading_normal=ShadingNormal.kFace,
+                                backface_culling=culling)
+        run = util.CudaRunner(mesh, opt)
+        port = OraclePort(mesh)
+        for (w, h, fov, eye) in ((1280, 960, 50.0, (0.0, 0.0, 0.0)), (803, 417, 70.0, (0.15, -0.1, 0.2))):
+            cam = PinholeCamera(w, h, meshgen.look_at_c2w(eye, (0, 0, 2.0), (0, -1, 0)), fov_y_deg=fov)
+            util.assert_parity(run.render(cam, opt), port.render(cam.to_native(), opt), strict=True,
+                               what=f"peeking patches cull={culling} {w}x{h}")
