@@ -148,14 +148,14 @@ int main(int argc, char** argv) {
       if (!r->PrepareMesh()) return 1;
       r->set_camera(camera);
     }
-    const int n_views = timing ? 3 : 5;
+    const int n_views = timing ? 6 : 5;
+    Outs o[2];  // reused across the views like a caller's frame loop (Render re-initialises them, util_private.cc:72-87)
     for (int k = 0; k < n_views; k++) {
       const double a = 2.0 * 3.14159265358979323846 * k / n_views + 0.3;
       Eigen::Matrix4d c2w;
       ugu::c2w(Eigen::Vector3d(2.9 * std::sin(a), 0.4 * std::cos(2 * a), 2.9 * std::cos(a)),
                Eigen::Vector3d(0.02, -0.03, 0.01), Eigen::Vector3d(0, -1, 0), &c2w);
       camera->set_c2w(Eigen::Affine3d(c2w));  // callers mutate the camera the renderers hold
-      Outs o[2];
       double ms[2];
       int idx = 0;
       for (ugu::RendererCpu* r : {ref.get(), cuda.get()}) {
