@@ -1,2 +1,3 @@
 cd $GRAFT_REPO_ROOT
-bash tools/gpu/ncu_full.sh r03m_raster 'raster_kernel' 4 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-multiview
+bash tools/gpu/ncu_full.sh r03u_c3_binned 'binned_kernel' 3 python tools/bench_configs.py c3 --no-cpu
+bash tools/gpu/ncu_full.sh r03u_c3_resolve 'resolve_kernel' 3 python tools/bench_configs.py c3 --no-cpu

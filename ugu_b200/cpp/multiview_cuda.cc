@@ -3,6 +3,7 @@
 #include "multiview_cuda.h"
 
 #include <cstring>
+#include <thread>
 
 #include "ugu/log.h"
 #include "ugu_b200_raster.h"
@@ -11,12 +12,23 @@ namespace ugu {
 
 namespace {
 
-struct PinnedBlock {  // view-ordered landing buffer for the DMA of all devices
+// View-ordered landing buffer for the DMA of all devices.  Kept by the renderer and only ever grown: pinning
+// hundreds of megabytes costs more than rendering them.
+struct PinnedBlock {
   void* p = nullptr;
-  explicit PinnedBlock(size_t bytes) { p = bytes ? ugu_b200_host_alloc(bytes) : nullptr; }
+  size_t bytes = 0;
+  PinnedBlock() = default;
   ~PinnedBlock() { ugu_b200_host_free(p); }
   PinnedBlock(const PinnedBlock&) = delete;
   PinnedBlock& operator=(const PinnedBlock&) = delete;
+  void* Ensure(size_t need) {
+    if (need > bytes) {
+      ugu_b200_host_free(p);
+      p = ugu_b200_host_alloc(need);
+      bytes = p ? need : 0;
+    }
+    return need ? p : nullptr;
+  }
 };
 
 ugu_b200_option ToOption(const RendererCpuOption& option) {
@@ -67,6 +79,7 @@ void Scatter(const void* src, size_t view_bytes, int w, int h, std::vector<Image
 
 class MultiViewRasterizerCuda::Impl {
  public:
+  PinnedBlock land_[5];  // colour, depth, normal, mask, face_id
   ugu_b200_multiview* mv_ = nullptr;
   std::shared_ptr<const Mesh> mesh_;
   RendererCpuOption option_;
@@ -192,26 +205,33 @@ bool MultiViewRasterizerCuda::RenderBatch(const std::vector<std::shared_ptr<cons
   const size_t n = cams.size();
   const int w = cams[0].width, h = cams[0].height;
   const size_t P = static_cast<size_t>(w) * h;
-  PinnedBlock bc(color ? n * P * 3 : 0), bd(depth ? n * P * 4 : 0), bn(normal ? n * P * 12 : 0),
-      bm(mask ? n * P : 0), bf(face_id ? n * P * 4 : 0);
+  PinnedBlock* L = pimpl_->land_;
   ugu_b200_outputs o;
   std::memset(&o, 0, sizeof(o));
-  o.color = static_cast<uint8_t*>(bc.p);
-  o.depth = static_cast<float*>(bd.p);
-  o.normal = static_cast<float*>(bn.p);
-  o.mask = static_cast<uint8_t*>(bm.p);
-  o.face_id = static_cast<int32_t*>(bf.p);
+  o.color = static_cast<uint8_t*>(L[0].Ensure(color ? n * P * 3 : 0));
+  o.depth = static_cast<float*>(L[1].Ensure(depth ? n * P * 4 : 0));
+  o.normal = static_cast<float*>(L[2].Ensure(normal ? n * P * 12 : 0));
+  o.mask = static_cast<uint8_t*>(L[3].Ensure(mask ? n * P : 0));
+  o.face_id = static_cast<int32_t*>(L[4].Ensure(face_id ? n * P * 4 : 0));
+  if ((color && !o.color) || (depth && !o.depth) || (normal && !o.normal) || (mask && !o.mask) ||
+      (face_id && !o.face_id)) {
+    LOGE("MultiViewRasterizerCuda: pinned host allocation failed\n");
+    return false;
+  }
   if (ugu_b200_multiview_render_batch(pimpl_->mv_, static_cast<int32_t>(n), cams.data(),
                                       round_robin ? UGU_B200_PARTITION_ROUND_ROBIN : UGU_B200_PARTITION_CONTIGUOUS,
                                       &o) != UGU_B200_OK) {
     LOGE("%s\n", ugu_b200_multiview_last_error(pimpl_->mv_));
     return false;
   }
-  if (color) { color->resize(n); Scatter(bc.p, P * 3, w, h, color); }
-  if (depth) { depth->resize(n); Scatter(bd.p, P * 4, w, h, depth); }
-  if (normal) { normal->resize(n); Scatter(bn.p, P * 12, w, h, normal); }
-  if (mask) { mask->resize(n); Scatter(bm.p, P, w, h, mask); }
-  if (face_id) { face_id->resize(n); Scatter(bf.p, P * 4, w, h, face_id); }
+  // into the caller's images: one host thread per output
+  std::vector<std::thread> th;
+  if (color) { color->resize(n); th.emplace_back([&] { Scatter(o.color, P * 3, w, h, color); }); }
+  if (depth) { depth->resize(n); th.emplace_back([&] { Scatter(o.depth, P * 4, w, h, depth); }); }
+  if (normal) { normal->resize(n); th.emplace_back([&] { Scatter(o.normal, P * 12, w, h, normal); }); }
+  if (mask) { mask->resize(n); th.emplace_back([&] { Scatter(o.mask, P, w, h, mask); }); }
+  if (face_id) { face_id->resize(n); th.emplace_back([&] { Scatter(o.face_id, P * 4, w, h, face_id); }); }
+  for (auto& t : th) t.join();
   return true;
 }
 
@@ -227,15 +247,19 @@ bool MultiViewRasterizerCuda::GatherFaceIds(const std::vector<std::shared_ptr<co
   const size_t n = cams.size();
   const int w = cams[0].width, h = cams[0].height;
   const size_t P = static_cast<size_t>(w) * h;
-  PinnedBlock bf(n * P * 4);
+  int32_t* land = static_cast<int32_t*>(pimpl_->land_[4].Ensure(n * P * 4));
+  if (land == nullptr) {
+    LOGE("MultiViewRasterizerCuda: pinned host allocation failed\n");
+    return false;
+  }
   if (ugu_b200_multiview_gather_face_ids(pimpl_->mv_, static_cast<int32_t>(n), cams.data(),
                                          round_robin ? UGU_B200_PARTITION_ROUND_ROBIN : UGU_B200_PARTITION_CONTIGUOUS,
-                                         root, chunk_views, nullptr, static_cast<int32_t*>(bf.p)) != UGU_B200_OK) {
+                                         root, chunk_views, nullptr, land) != UGU_B200_OK) {
     LOGE("%s\n", ugu_b200_multiview_last_error(pimpl_->mv_));
     return false;
   }
   face_id->resize(n);
-  Scatter(bf.p, P * 4, w, h, face_id);
+  Scatter(land, P * 4, w, h, face_id);
   return true;
 }
 
