@@ -193,6 +193,21 @@ int main(int argc, char** argv) {
         if (!ugu::Depth2PointCloud(dref, *camera, &p0, gl != 0)) failures++;
         if (!static_cast<ugu::RasterizerCuda*>(cuda.get())->Depth2PointCloud(dref, *camera, &p1, gl != 0)) failures++;
         if (CountDiff(p0, p1, 0)) failures++;
+        {  // the Mesh-output overloads (raster-order compaction, nearest colour)
+          ugu::Mesh m0, m1, m2, m3;
+          ugu::Image3b cref;
+          if (!ref->RenderColor(&cref)) failures++;
+          if (!ugu::Depth2PointCloud(dref, *camera, &m0, gl != 0)) failures++;
+          if (!static_cast<ugu::RasterizerCuda*>(cuda.get())->Depth2PointCloud(dref, *camera, &m1, gl != 0)) failures++;
+          if (!ugu::Depth2PointCloud(dref, cref, *camera, &m2, gl != 0)) failures++;
+          if (!static_cast<ugu::RasterizerCuda*>(cuda.get())->Depth2PointCloud(dref, cref, *camera, &m3, gl != 0)) failures++;
+          auto same = [](const std::vector<Eigen::Vector3f>& a, const std::vector<Eigen::Vector3f>& b) {
+            return a.size() == b.size() && (a.empty() || std::memcmp(a.data(), b.data(), a.size() * sizeof(Eigen::Vector3f)) == 0);
+          };
+          if (m0.vertices().empty() || !same(m0.vertices(), m1.vertices()) || !same(m2.vertices(), m3.vertices()) ||
+              !same(m2.vertex_colors(), m3.vertex_colors()) || m3.vertex_colors().size() != m3.vertices().size())
+            failures++;
+        }
         p0.setTo(ugu::Vec3f({1.f, 2.f, 3.f}));
         p1.setTo(ugu::Vec3f({1.f, 2.f, 3.f}));
         if (!ugu::Depth2PointCloud(dref, *camera, &p0, gl != 0)) failures++;

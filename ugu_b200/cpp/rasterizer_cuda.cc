@@ -3,10 +3,13 @@
 // (src/renderer/cpu/rasterizer.cc:35-103,309-404) and leaves every computation to the CUDA library.
 #include "rasterizer_cuda.h"
 
+#include <cmath>
 #include <cstring>
+#include <limits>
 #include <vector>
 
 #include "ugu/log.h"
+#include "ugu/util/raster_util.h"
 #include "ugu_b200_raster.h"
 
 namespace ugu {
@@ -250,6 +253,58 @@ bool RasterizerCuda::Depth2PointCloud(const Image1f& depth, const Camera& camera
     return false;
   }
   return true;
+}
+
+namespace {
+// Depth2PointCloudImpl (rgbd_util.cc:12-93) on top of the organized device form.
+bool PointCloudMesh(const RasterizerCuda& self, const Image1f& depth, const Image3b* color, const Camera& camera,
+                    Mesh* point_cloud, bool gl_coord) {
+  if (depth.cols != camera.width() || depth.rows != camera.height()) {
+    LOGE("Depth2PointCloud depth size (%d, %d) and camera size (%d, %d) are different\n", depth.cols, depth.rows,
+         camera.width(), camera.height());
+    return false;
+  }
+  if (color != nullptr) {  // rgbd_util.cc:23-39
+    const float depth_aspect_ratio = static_cast<float>(depth.cols) / static_cast<float>(depth.rows);
+    const float color_aspect_ratio = static_cast<float>(color->cols) / static_cast<float>(color->rows);
+    if (std::abs(depth_aspect_ratio - color_aspect_ratio) > 0.01f) {
+      LOGE("Depth2PointCloud depth aspect ratio %f and color aspect ratio %f are very different\n",
+           depth_aspect_ratio, color_aspect_ratio);
+      return false;
+    }
+  }
+  if (point_cloud == nullptr) return false;
+  Image3f organized;
+  if (!self.Depth2PointCloud(depth, camera, &organized, gl_coord)) return false;
+  point_cloud->Clear();
+  std::vector<Eigen::Vector3f> vertices, vertex_colors;
+  for (int y = 0; y < camera.height(); y++) {
+    for (int x = 0; x < camera.width(); x++) {
+      if (depth.at<float>(y, x) < std::numeric_limits<float>::min()) continue;
+      const Vec3f& p = organized.at<Vec3f>(y, x);
+      vertices.emplace_back(p[0], p[1], p[2]);
+      if (color != nullptr) {  // nearest neighbour, rgbd_util.cc:62-78
+        const Eigen::Vector2f uv(X2U(static_cast<float>(x), depth.cols), Y2V(static_cast<float>(y), depth.rows, false));
+        const Eigen::Vector2i pos(static_cast<int>(std::round(U2X(uv.x(), color->cols))),
+                                  static_cast<int>(std::round(V2Y(uv.y(), color->rows, false))));
+        const Vec3b& c = color->at<Vec3b>(pos.y(), pos.x());
+        vertex_colors.emplace_back(static_cast<float>(c[0]), static_cast<float>(c[1]), static_cast<float>(c[2]));
+      }
+    }
+  }
+  point_cloud->set_vertices(vertices);
+  if (color != nullptr) point_cloud->set_vertex_colors(vertex_colors);
+  return true;
+}
+}  // namespace
+
+bool RasterizerCuda::Depth2PointCloud(const Image1f& depth, const Camera& camera, Mesh* point_cloud,
+                                      bool gl_coord) const {
+  return PointCloudMesh(*this, depth, nullptr, camera, point_cloud, gl_coord);
+}
+bool RasterizerCuda::Depth2PointCloud(const Image1f& depth, const Image3b& color, const Camera& camera,
+                                      Mesh* point_cloud, bool gl_coord) const {
+  return PointCloudMesh(*this, depth, &color, camera, point_cloud, gl_coord);
 }
 
 namespace {

@@ -51,6 +51,13 @@ class RasterizerCuda : public RendererCpu {
   // to 0 when its size differs, pixels with depth < FLT_MIN left as they were.  Pinhole cameras only.
   bool Depth2PointCloud(const Image1f& depth, const Camera& camera, Image3f* point_cloud,
                         bool gl_coord = false) const;
+  // The Mesh-output overloads (rgbd_util.h:20-25, Depth2PointCloudImpl rgbd_util.cc:12-93): the valid pixels in
+  // raster order as `vertices` (and, with `color`, their nearest colour texels as `vertex_colors`).  The
+  // unprojection runs on the device (the organized form above); compaction and the colour lookup are host loops
+  // over the reference's own X2U / Y2V / U2X / V2Y expressions.  Same false returns.
+  bool Depth2PointCloud(const Image1f& depth, const Camera& camera, Mesh* point_cloud, bool gl_coord = false) const;
+  bool Depth2PointCloud(const Image1f& depth, const Image3b& color, const Camera& camera, Mesh* point_cloud,
+                        bool gl_coord = false) const;
 
   // ugu::RasterizeVertexAttributeToTexture<T> / RasterizeFaceAttributeToTexture<T> / GenerateUvMask
   // (include/ugu/util/raster_util.h:139-278, src/util/raster_util.cc:9-27) on this renderer's device,
