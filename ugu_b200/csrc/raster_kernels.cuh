@@ -1195,7 +1195,17 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
     Tri t;
     tri_setup(t, s.p0, s.p1, s.p2);
     tri_edges(t, (float)x, (float)y, w0, w1, w2);
-    (void)tri_depth(t, w0, w1, w2);
+    // rasterizer.cc:208-224 without its seventh division: z = 1 / ((w0 + w1) + w2) of exactly these operands is
+    // what the raster kernel stored in the key (o.depth)
+    w0 = w0 / t.area;
+    w1 = w1 / t.area;
+    w2 = w2 / t.area;
+    w0 = w0 / t.v0z;
+    w1 = w1 / t.v1z;
+    w2 = w2 / t.v2z;
+    w0 = w0 * o.depth;
+    w1 = w1 * o.depth;
+    w2 = w2 * o.depth;
   }
   if (NMODE >= 2) {  // rasterizer.cc:271-279
     nwx = (w0 * n0.x + w1 * n1.x) + w2 * n2.x;
