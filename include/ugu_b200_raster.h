@@ -255,6 +255,23 @@ int ugu_b200_face_visibility(ugu_b200_rasterizer* r, const int32_t* face_id_host
                              uint32_t* pixel_count_host, uint32_t* view_count_host,
                              int32_t* best_view_host, uint32_t* best_count_host);
 
+/* Allocation-free variant of ugu_b200_face_visibility_device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same inputs, accumulators and results as the _device
+ * form, but it takes no rasterizer handle and its histogram scratch is a file-scope __device__ array of
+ * UGU_B200_STATIC_VIS_MAX_FACES 32-bit words (16 MiB) that every GPU loading the library holds until the
+ * process exits.  The call performs no cudaMalloc / cudaFree / allocating library routine: it makes `device`
+ * current, clears the part of the array it uses on `stream`, and queues the kernels there (asynchronous;
+ * `stream` NULL = the default stream).  num_faces > UGU_B200_STATIC_VIS_MAX_FACES returns
+ * UGU_B200_E_INVALID.  Views are processed min(8, MAX_FACES / num_faces) at a time.  ALL calls on a device
+ * share the array: calls that overlap on the GPU (different streams, concurrent threads) race — serialise
+ * them.  On failure a message is written to `err` (err_len bytes, may be NULL). */
+#define UGU_B200_STATIC_VIS_MAX_FACES (4 * 1024 * 1024)
+int ugu_b200_face_visibility_static(int32_t device, const int32_t* face_id_dev, int32_t num_views,
+                                    int64_t pixels_per_view, int32_t first_view_id, int32_t num_faces,
+                                    uint32_t* pixel_count_dev, uint32_t* view_count_dev, uint64_t* best_dev,
+                                    void* stream, char* err, size_t err_len);
+
 /* Keyframe visibility pass: replaces ugu::VisibilityTester
  * (include/ugu/texturing/visibility_tester.h:216-265; src/texturing/visibility_tester.cc:416-529 TestVertex,
  * :531-549 TestVertices, :551-604 TestFaces, :606-668 TestFacewiseVertices, :670-733 Test) and the folds of

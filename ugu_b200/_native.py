@@ -136,6 +136,9 @@ SYMBOLS = {
                                                   C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ugu_b200_face_visibility": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ugu_b200_face_visibility_static": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_int32,
+                                                  C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                  C.c_char_p, C.c_size_t]),
     "ugu_b200_visibility_set_data": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "ugu_b200_visibility_reset": (C.c_int, [C.c_void_p]),
     "ugu_b200_visibility_test": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(Keyframe), C.c_int32,

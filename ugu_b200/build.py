@@ -21,7 +21,8 @@ CSRC = ROOT / "csrc"
 LIBDIR = ROOT / "lib"
 LIB = LIBDIR / "libugu_b200_raster.so"
 
-SOURCES = [CSRC / "raster_api.cu", CSRC / "multiview_api.cu", CSRC / "camera_host.cc"]
+SOURCES = [CSRC / "raster_api.cu", CSRC / "multiview_api.cu", CSRC / "static_scratch_api.cu",
+           CSRC / "camera_host.cc"]
 DEPS = SOURCES + sorted(CSRC.glob("*.cuh")) + [REPO / "include" / "ugu_b200_raster.h"]  # every kernel header
 
 NVCC_FLAGS = [
