@@ -186,6 +186,12 @@ int MeshAlloc(ugu_b200_rasterizer* r, T** out, size_t count) {
   return UGU_B200_OK;
 }
 
+inline float __int_as_float_host(int32_t v) {
+  float f;
+  memcpy(&f, &v, 4);
+  return f;
+}
+
 inline unsigned Blocks(size_t n, unsigned threads) { return (unsigned)((n + threads - 1) / threads); }
 
 bool IndicesInRange(const int32_t* idx, size_t count, int32_t limit) {
@@ -593,10 +599,17 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   sp.fold_binned = fold_binned ? 1 : 0;
   const bool pdl = r->use_pdl;
   const unsigned ny = (unsigned)n;
+  // Fused projection (block-local vertex tables, upload_mesh): raster_kernel projects its own vertices, so no vertex
+  // kernel runs — only the block lists of the occlusion ordering are built ahead of it, by classify_kernel.
+  const bool fused = m.lv != nullptr;
   {
     StageTimer t(r, st, UGU_B200_STAGE_VERTEX);
-    const size_t threads = std::max<size_t>(std::max<size_t>((size_t)m.V, (size_t)W + H), ((size_t)m.F + 255) / 256);
-    CU_TRY(r, LaunchView(vertex_kernel_b<NV>, dim3(Blocks(threads, 256)), 256, st, pdl, vb, n, m, fr));
+    if (!fused) {
+      const size_t threads = std::max<size_t>(std::max<size_t>((size_t)m.V, (size_t)W + H), ((size_t)m.F + 255) / 256);
+      CU_TRY(r, LaunchView(vertex_kernel_b<NV>, dim3(Blocks(threads, 256)), 256, st, pdl, vb, n, m, fr));
+    } else if (fr.order) {
+      CU_TRY(r, LaunchView(classify_kernel<NV>, dim3(Blocks(((size_t)m.F + 255) / 256, 256)), 256, st, pdl, vb, n, m, fr));
+    }
   }
   if (m.F > 0) {
     StageTimer t(r, st, UGU_B200_STAGE_RASTER);
@@ -672,7 +685,7 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
 #undef UGU_RESOLVE_CASE
   }
   CU_TRY(r, cudaGetLastError());
-  r->stats.kernel_launches += (m.F > 0) ? (fold_binned ? 3 : 4) : 2;
+  r->stats.kernel_launches += ((m.F > 0) ? (fold_binned ? 3 : 4) : 2) - ((fused && !fr.order) ? 1 : 0);
   r->stats.views += (uint64_t)n;
   if (r->profiling) r->stats.timed_views += (uint64_t)n;
   r->stats.h2d_bytes += sizeof(ViewParams) * (size_t)n;
@@ -1160,6 +1173,55 @@ int ugu_b200_rasterizer_upload_mesh(ugu_b200_rasterizer* r, const ugu_b200_mesh_
     block_records_kernel<<<(unsigned)blocks, 256, 0, st>>>(m.pos4, m.r_idx0, m.r_idx1, m.r_idx2, F, grp);
     r->stats.kernel_launches++;
     m.grp = grp;
+  }
+  // Block-local vertex tables of the fused projection (raster_kernel): per 256-face block of the raster order its
+  // <= 256 distinct vertices {x, y, z, global id} and per face three 8-bit indices into them, so the block projects
+  // its own vertices into shared memory and no vertex kernel runs.  A block with more distinct vertices (a soup of
+  // unshared triangles) gets lidx = 0xFFFFFFFF and its lanes project their own corners.  UGU_B200_FUSED=0: off.
+  std::vector<float4> h_lv;
+  std::vector<uint32_t> h_lidx;
+  if (F > 0 && V > 0 && !(getenv("UGU_B200_FUSED") && atoi(getenv("UGU_B200_FUSED")) == 0)) {
+    const size_t blocks = ((size_t)F + 255) / 256;
+    h_lv.assign(blocks * 256, make_float4(0.f, 0.f, 0.f, __int_as_float_host(-1)));
+    h_lidx.assign((size_t)F, 0xFFFFFFFFu);
+    std::vector<int32_t> stamp((size_t)V, -1);
+    std::vector<uint16_t> local((size_t)V, 0);
+    for (size_t b = 0; b < blocks; b++) {
+      const size_t s0 = b * 256, s1 = std::min(s0 + 256, (size_t)F);
+      int n = 0;
+      for (size_t s = s0; s < s1; s++) {
+        const int32_t* tri = h_vidx + (size_t)(order ? slot_face[s] : (int32_t)s) * 3;
+        for (int k = 0; k < 3; k++)
+          if (stamp[tri[k]] != (int32_t)b) {
+            stamp[tri[k]] = (int32_t)b;
+            local[tri[k]] = (uint16_t)n++;
+          }
+      }
+      if (n > 256) continue;  // lidx stays 0xFFFFFFFF, lv stays empty
+      for (size_t s = s0; s < s1; s++) {
+        const int32_t* tri = h_vidx + (size_t)(order ? slot_face[s] : (int32_t)s) * 3;
+        uint32_t packed = 0;
+        for (int k = 0; k < 3; k++) {
+          const int32_t v = tri[k];
+          const uint32_t l = local[v];
+          packed |= l << (8 * k);
+          h_lv[b * 256 + l] = make_float4(h_vertices[(size_t)v * 3], h_vertices[(size_t)v * 3 + 1],
+                                          h_vertices[(size_t)v * 3 + 2], __int_as_float_host(v));
+        }
+        h_lidx[s] = packed;
+      }
+    }
+    float4* lv = nullptr;
+    unsigned* lidx = nullptr;
+    UP_TRY(MeshAlloc(r, &lv, h_lv.size()));
+    UP_TRY(MeshAlloc(r, &lidx, h_lidx.size()));
+    UP_TRY([&]() -> int {
+      CU_TRY(r, cudaMemcpyAsync(lv, h_lv.data(), h_lv.size() * 16, cudaMemcpyHostToDevice, st));
+      CU_TRY(r, cudaMemcpyAsync(lidx, h_lidx.data(), h_lidx.size() * 4, cudaMemcpyHostToDevice, st));
+      return UGU_B200_OK;
+    }());
+    m.lv = lv;
+    m.lidx = lidx;
   }
   void* nrm_aos = nullptr;
   void* col_aos = nullptr;

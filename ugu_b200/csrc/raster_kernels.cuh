@@ -90,6 +90,10 @@ struct MeshDev {
   const float* r_fn_z;
   const int* r_face;
   const float4* grp;    // per block of 256 consecutive slots: {sum of face normals, their dot with the mean centroid}
+  // fused projection (raster_kernel): per block its <= 256 distinct vertices {x, y, z, global id | -1} and per slot
+  // three 8-bit indices into them (0xFFFFFFFF: the block has more, its lanes project their own corners); NULL = off
+  const float4* lv;
+  const unsigned* lidx;
   const int4* frec;
   const int4* uvidx;
   const float2* uv2;
@@ -292,6 +296,37 @@ __device__ __forceinline__ float4 project_vertex(const ViewParams& vp, float x, 
   return o;
 }
 
+// Occlusion ordering of raster_kernel: camera-facing blocks fill the view's list from the front, the others
+// from the back (one atomicAdd per warp and list; a warp's 32 consecutive blocks stay neighbours).  Thread t
+// classifies block t for each of the n views; whole warps call it.
+template <int NV>
+__device__ __forceinline__ void classify_blocks(const ViewBatch<NV>& vb, const int n, const MeshDev& m,
+                                                const FrameDev& fr, const int t) {
+  const int nblocks = (m.F + 255) >> 8;
+  if (fr.order == nullptr || (t & ~31) >= nblocks) return;
+  const bool blk_valid = t < nblocks;
+  const float4 rec = blk_valid ? __ldg(m.grp + t) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned lt = (1u << lane) - 1u;
+  for (int v = 0; v < n; v++) {
+    const bool def = blk_valid && group_deferred(vb.v[v], rec);
+    const unsigned bf = __ballot_sync(0xffffffffu, blk_valid && !def), bd = __ballot_sync(0xffffffffu, def);
+    unsigned long long* cnt = fr.counters + (unsigned long long)v * kCounterSlab;
+    unsigned basef = 0u, based = 0u;
+    if (lane == 0u) {
+      if (bf) basef = (unsigned)atomicAdd(cnt + 3, (unsigned long long)__popc(bf));
+      if (bd) based = (unsigned)atomicAdd(cnt + 7, (unsigned long long)__popc(bd));
+    }
+    basef = __shfl_sync(0xffffffffu, basef, 0);
+    based = __shfl_sync(0xffffffffu, based, 0);
+    int* order = fr.order + (unsigned long long)v * fr.s_order;
+    if (blk_valid) {
+      if (def) order[nblocks - 1 - (int)(based + __popc(bd & lt))] = t;
+      else order[basef + __popc(bf & lt)] = t;
+    }
+  }
+}
+
 // One vertex per thread (fully coalesced 4-byte loads, 16-byte stores; the kernel is a few
 // microseconds of pure latency at mesh sizes that fit one wave).  A batch loads every position once
 // and projects it through each view of the batch: 12 bytes in, 16 bytes out per (vertex, view).
@@ -316,31 +351,16 @@ __global__ void __launch_bounds__(256) vertex_kernel_b(const ViewBatch<NV> vb, c
     else if (t < vp.W + vp.H)
       fr.ray_dy[(unsigned long long)v * fr.s_ray_dy + (t - vp.W)] = ((float)(t - vp.W) - vp.cy) / vp.fy;
   }
-  const int nblocks = (m.F + 255) >> 8;
-  if (fr.order == nullptr || (t & ~31) >= nblocks) return;
-  // Occlusion ordering of raster_kernel: camera-facing blocks fill the view's list from the front, the others
-  // from the back (one atomicAdd per warp and list; a warp's 32 consecutive blocks stay neighbours).
-  const bool blk_valid = t < nblocks;
-  const float4 rec = blk_valid ? __ldg(m.grp + t) : make_float4(0.f, 0.f, 0.f, 0.f);
-  const unsigned lane = threadIdx.x & 31u;
-  const unsigned lt = (1u << lane) - 1u;
-  for (int v = 0; v < n; v++) {
-    const bool def = blk_valid && group_deferred(vb.v[v], rec);
-    const unsigned bf = __ballot_sync(0xffffffffu, blk_valid && !def), bd = __ballot_sync(0xffffffffu, def);
-    unsigned long long* cnt = fr.counters + (unsigned long long)v * kCounterSlab;
-    unsigned basef = 0u, based = 0u;
-    if (lane == 0u) {
-      if (bf) basef = (unsigned)atomicAdd(cnt + 3, (unsigned long long)__popc(bf));
-      if (bd) based = (unsigned)atomicAdd(cnt + 7, (unsigned long long)__popc(bd));
-    }
-    basef = __shfl_sync(0xffffffffu, basef, 0);
-    based = __shfl_sync(0xffffffffu, based, 0);
-    int* order = fr.order + (unsigned long long)v * fr.s_order;
-    if (blk_valid) {
-      if (def) order[nblocks - 1 - (int)(based + __popc(bd & lt))] = t;
-      else order[basef + __popc(bf & lt)] = t;
-    }
-  }
+  classify_blocks<NV>(vb, n, m, fr, t);
+}
+
+// The block lists alone, for the fused projection (no vertex kernel).
+template <int NV>
+__global__ void __launch_bounds__(256) classify_kernel(const ViewBatch<NV> vb, const int nviews, const MeshDev m,
+                                                       const FrameDev fr) {
+  pdl_launch_dependents();
+  pdl_wait();  // counters [3] / [7] are reset by the previous view's resolve
+  classify_blocks<NV>(vb, (NV == 1) ? 1 : nviews, m, fr, (int)(blockIdx.x * blockDim.x + threadIdx.x));
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -468,7 +488,8 @@ __device__ __forceinline__ bool facing_backface(const ViewParams& vp, const Mesh
   const float dm = fmaxf(fmaxf(fabsf(d0), fabsf(d1)), 1.0f);
   if (fabsf(val) > g.w * dm) return val > 0.0f;
   float r0, r1, r2;
-  ray_world(vp, fr.ray_dx[x], fr.ray_dy[y], r0, r1, r2);
+  // the ray-table expressions of vertex_kernel_b, evaluated here: the fused projection runs no vertex kernel
+  ray_world(vp, (small_int_to_float(x) - vp.cx) / vp.fx, (small_int_to_float(y) - vp.cy) / vp.fy, r0, r1, r2);
   return dot3(__ldg(m.fn_x + face), __ldg(m.fn_y + face), __ldg(m.fn_z + face), r0, r1, r2) > 0.0f;
 }
 
@@ -733,6 +754,10 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
   const FrameDev fr = (NV == 1) ? fr0 : frame_view(fr0, view);
   __shared__ WarpTris<HALVES> sh[8];
   WarpTris<HALVES>& S = sh[threadIdx.x >> 5];
+  // Fused projection: the CTA projects the <= 256 distinct vertices of its block (thread = vertex) into shared
+  // memory and into fr.proj for the later kernels, then its faces pick their corners by 8-bit local index.
+  const bool fused = HALVES == 1 && m.lv != nullptr;
+  __shared__ float4 s_proj[HALVES == 1 ? 256 : 1];
   const unsigned lane = threadIdx.x & 31u;
   const unsigned lt_mask = (1u << lane) - 1u;
   pdl_launch_dependents();
@@ -753,12 +778,15 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
     }
   }
   const int base = (int)((blk * 8u + (threadIdx.x >> 5)) * (unsigned)(32 * HALVES));
-  if (base >= m.F) return;  // whole warp; no block-level barrier is used in this kernel
+  if (!fused && base >= m.F) return;  // whole warp; the fused path has one block-level barrier below
   const bool has_fn = m.num_face_normals > 0;
+  float4 lvx = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+  if (fused) lvx = __ldg(m.lv + (size_t)blk * 256u + threadIdx.x);  // immutable: before the wait
 
   // ---- Phase A ---------------------------------------------------------------------------------
   int fidx[HALVES], face[HALVES];
   int i0[HALVES], i1[HALVES], i2[HALVES];
+  unsigned li[HALVES];
   float4 pa[HALVES], pb[HALVES], pc[HALVES];
   float fnx[HALVES], fny[HALVES], fnz[HALVES];
 #pragma unroll
@@ -767,10 +795,14 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
     i0[h] = i1[h] = i2[h] = 0;
     fidx[h] = base + h * 32 + (int)lane;  // slot in raster order
     face[h] = fidx[h];
+    li[h] = 0xFFFFFFFFu;
     if (fidx[h] < m.F) {  // immutable mesh data: may be read before the vertex kernel has finished
-      i0[h] = __ldg(m.r_idx0 + fidx[h]);
-      i1[h] = __ldg(m.r_idx1 + fidx[h]);
-      i2[h] = __ldg(m.r_idx2 + fidx[h]);
+      if (fused) li[h] = __ldg(m.lidx + fidx[h]);
+      if (li[h] == 0xFFFFFFFFu) {
+        i0[h] = __ldg(m.r_idx0 + fidx[h]);
+        i1[h] = __ldg(m.r_idx1 + fidx[h]);
+        i2[h] = __ldg(m.r_idx2 + fidx[h]);
+      }
       if (PASS != 0 && deferred) continue;  // face id and normal only for the triangles that survive
       if (m.r_face) face[h] = __ldg(m.r_face + fidx[h]);
       if (has_fn) {  // same round trip as the indices, not a third dependent one
@@ -781,13 +813,37 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
     }
   }
   if (PASS != 1) pdl_wait();  // projected vertices of this view; visibility buffer / counters left clean by resolve
+  if (fused) {
+    const int vid = __float_as_int(lvx.w);
+    if (vid >= 0) {
+      const float4 P = project_vertex(vp, lvx.x, lvx.y, lvx.z);
+      s_proj[threadIdx.x] = P;
+      fr.proj[vid] = P;  // binned / resolve gather by global id; blocks sharing a vertex store the same value
+    }
+    __syncthreads();
+    if (base >= m.F) return;
+  }
 #pragma unroll
   for (int h = 0; h < HALVES; h++) {
     if (fidx[h] < m.F) {
-      // plain (coherent) loads: proj is rewritten every view by the preceding kernel
-      pa[h] = fr.proj[i0[h]];
-      pb[h] = fr.proj[i1[h]];
-      pc[h] = fr.proj[i2[h]];
+      if (li[h] != 0xFFFFFFFFu) {
+        pa[h] = s_proj[li[h] & 255u];
+        pb[h] = s_proj[(li[h] >> 8) & 255u];
+        pc[h] = s_proj[(li[h] >> 16) & 255u];
+      } else if (fused) {  // block with more than 256 distinct vertices: every face projects its own corners
+        const float4 A = __ldg(m.pos4 + i0[h]), B = __ldg(m.pos4 + i1[h]), Cc = __ldg(m.pos4 + i2[h]);
+        pa[h] = project_vertex(vp, A.x, A.y, A.z);
+        pb[h] = project_vertex(vp, B.x, B.y, B.z);
+        pc[h] = project_vertex(vp, Cc.x, Cc.y, Cc.z);
+        fr.proj[i0[h]] = pa[h];
+        fr.proj[i1[h]] = pb[h];
+        fr.proj[i2[h]] = pc[h];
+      } else {
+        // plain (coherent) loads: proj is rewritten every view by the preceding kernel
+        pa[h] = fr.proj[i0[h]];
+        pb[h] = fr.proj[i1[h]];
+        pc[h] = fr.proj[i2[h]];
+      }
     }
   }
   raster_warp_view<HALVES, PASS, TILES>(vp, m, fr, S, lane, has_fn, deferred, fidx, face, fnx, fny, fnz, pa, pb, pc);
@@ -1254,7 +1310,7 @@ __device__ __forceinline__ void resolve_pixel(const ViewParams& vp, const MeshDe
   }
   if (NMODE != 0 && shade) {
     float r0, r1, r2;  // light_dir == ray_w (rasterizer.cc:291-298)
-    ray_world(vp, fr.ray_dx[x], fr.ray_dy[y], r0, r1, r2);
+    ray_world(vp, ((float)x - vp.cx) / vp.fx, ((float)y - vp.cy) / vp.fy, r0, r1, r2);  // the ray tables' expressions
     float coeff;
     if (sp.diffuse_shading == 1) {  // DiffuseLambertianShader (pixel_shader.h:367-386)
       coeff = -dot3(r0, r1, r2, nwx, nwy, nwz);
