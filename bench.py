@@ -63,9 +63,12 @@ def algorithmic_bytes(mesh, P):
     Nn = len(mesh.normals)
     out = P * (3 + 4 + 12 + 1 + 4)
     view = 12 * V + 12 * F + 12 * F + (12 * Nn + 12 * F) + 12 * V + out
+    blocks = (F + 255) // 256
     per_kernel = {
-        "vertex": 12 * V + 16 * V,                 # positions in, projected float4 out
-        "raster": 12 * F + 12 * F + 16 * V,        # indices + face normals + projected vertices once
+        # fused projection: the "vertex" stage is classify_kernel (block records in, block lists out) and the raster
+        # kernel takes the positions in and writes the projected vertices out for the later kernels
+        "vertex": 16 * blocks + 4 * blocks,
+        "raster": 12 * V + 12 * F + 12 * F + 16 * V,   # positions + indices + face normals in, projected float4 out
         "binned": 0,                               # empty queue at config 2
         "resolve": 8 * P + 8 * P + out,            # visibility read + clear, outputs written once
     }

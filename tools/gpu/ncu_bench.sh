@@ -11,7 +11,7 @@ $CMD > /dev/null 2>&1 || exit 1
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -c 400 --csv \
   --log-file gpurun_out/${tag}_launches_bench_steps3.csv $CMD > gpurun_out/${tag}_ncu_launches.log 2>&1
 timeout 1200 ncu --set full --clock-control none --import-source on --kernel-name-base demangled \
-  -k "regex:vertex_kernel_b|raster_kernel|binned_kernel|resolve_kernel" -s 12 -c 8 -f -o gpurun_out/${tag}_bench $CMD \
+  -k "regex:vertex_kernel_b|classify_kernel|raster_kernel|binned_kernel|resolve_kernel" -s 12 -c 8 -f -o gpurun_out/${tag}_bench $CMD \
   > gpurun_out/${tag}_ncu_full.log 2>&1
 tail -3 gpurun_out/${tag}_ncu_full.log
 ls -la gpurun_out/
