@@ -43,9 +43,16 @@ struct D2MParams {
   float* face_normals;       // Nf * 3
   float* uv;                 // Nv * 2
   float* colors;             // Nv * 3
-  float* point_cloud;        // W*H*3 (pre-zeroed) or null
-  float* normal_image;       // W*H*3 (pre-zeroed) or null
+  float* point_cloud;        // W*H*3 (pre-zeroed unless zero_fill) or null
+  float* normal_image;       // W*H*3 (pre-zeroed unless zero_fill) or null
+  // single-pass path (d2m_scan_emit_kernel)
+  unsigned long long* state; // per chunk: flag << 62 | faces << 31 | vertices (decoupled look-back), zeroed per call
+  int* ticket;               // chunk ticket counter, zeroed per call
+  int zero_fill;             // steps (1, 1): the kernels write the zeros of the two images themselves (no memsets)
 };
+
+__device__ __forceinline__ void d2m_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void d2m_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ float d2m_depth(const D2MParams& p, int gx, int gy) {
   return __ldg(p.depth + (size_t)((gy + 1) * p.ys) * p.W + (size_t)((gx + 1) * p.xs));
@@ -180,6 +187,63 @@ __global__ void __launch_bounds__(256) d2m_scan_kernel(const D2MParams p, int nb
   if (threadIdx.x == 0) p.totals[0] = carry;
 }
 
+// Everything that belongs to grid point g = (gx, gy) alone, in two parts.
+// d2m_emit_image: what needs no prefix — the point-cloud texel (and, with zero_fill, the zeros of the image),
+// and the "no vertex" marks of an invalid point.
+__device__ __forceinline__ void d2m_zero3(float* q) { q[0] = 0.f; q[1] = 0.f; q[2] = 0.f; }
+__device__ __forceinline__ void d2m_emit_image(const D2MParams& p, int g, int gx, int gy, bool valid, float d) {
+  const int x = (gx + 1) * p.xs, y = (gy + 1) * p.ys;
+  if (p.zero_fill && p.point_cloud) {  // steps (1, 1): pixel row / column 0 belong to the grid points beside them
+    if (gx == 0) d2m_zero3(p.point_cloud + 3 * ((size_t)y * p.W));
+    if (gy == 0) d2m_zero3(p.point_cloud + 3 * (size_t)x);
+    if (g == 0) d2m_zero3(p.point_cloud);
+  }
+  if (!valid) {
+    p.vid[g] = -1;
+    p.fref[g] = 0u;
+    if (p.zero_fill && p.point_cloud) d2m_zero3(p.point_cloud + 3 * ((size_t)y * p.W + x));
+    return;
+  }
+  if (p.point_cloud) {  // rgbd_util.cc:257-266
+    float pos[3];
+    d2m_unproject(p, gx, gy, d, pos);
+    float* q = p.point_cloud + 3 * ((size_t)y * p.W + x);
+    q[0] = pos[0]; q[1] = pos[1]; q[2] = pos[2];
+  }
+}
+// d2m_emit_vertex: vertex id / first face id images, position, uv, nearest colour of a VALID point.
+// `run` = packed (faces << 32 | vertices) exclusive prefix of g.
+__device__ __forceinline__ void d2m_emit_vertex(const D2MParams& p, int g, int gx, int gy, float d,
+                                                unsigned long long run, unsigned tris) {
+  const int x = (gx + 1) * p.xs, y = (gy + 1) * p.ys;
+  const int v = (int)(run & 0xFFFFFFFFull);
+  const unsigned f0 = (unsigned)(run >> 32);
+  p.vid[g] = v;
+  p.fref[g] = f0 | (tris << 30);
+  float pos[3];
+  d2m_unproject(p, gx, gy, d, pos);
+  p.vertices[3 * (size_t)v + 0] = pos[0];
+  p.vertices[3 * (size_t)v + 1] = pos[1];
+  p.vertices[3 * (size_t)v + 2] = pos[2];
+  if (p.with_uv || p.with_color) {
+    const float u = ((float)x + 0.5f) / (float)p.W;   // X2U, raster_util.h:22-24
+    const float w = ((float)y + 0.5f) / (float)p.H;   // Y2V, flip = false
+    if (p.with_color) {  // nearest colour texel, rgbd_util.cc:178-190
+      const int tx = __float2int_rz(roundf(u * (float)p.cw - 0.5f));
+      const int ty = __float2int_rz(roundf(w * (float)p.ch - 0.5f));
+      const int txc = min(max(tx, 0), p.cw - 1), tyc = min(max(ty, 0), p.ch - 1);  // in range on contract
+      const uint8_t* t = p.color + 3 * ((size_t)tyc * p.cw + txc);
+      p.colors[3 * (size_t)v + 0] = (float)t[0];
+      p.colors[3 * (size_t)v + 1] = (float)t[1];
+      p.colors[3 * (size_t)v + 2] = (float)t[2];
+    }
+    if (p.with_uv) {  // rgbd_util.cc:192-195
+      p.uv[2 * (size_t)v + 0] = u;
+      p.uv[2 * (size_t)v + 1] = 1.0f - w;
+    }
+  }
+}
+
 // D2M-K4: vertex ids / first face ids of every grid point (CTA-local scan + the scanned CTA sums),
 // and everything that belongs to the vertex alone: position, uv, nearest colour, point-cloud texel.
 __global__ void __launch_bounds__(256) d2m_emit_vertices_kernel(const D2MParams p) {
@@ -199,42 +263,148 @@ __global__ void __launch_bounds__(256) d2m_emit_vertices_kernel(const D2MParams 
     const unsigned long long run = carry + d2m_block_scan(c, total);
     carry += total;
     if (g >= G) continue;
-    if (c == 0ull) {
-      p.vid[g] = -1;
-      p.fref[g] = 0u;
-      continue;
-    }
-    const int v = (int)(run & 0xFFFFFFFFull);
-    const unsigned f0 = (unsigned)(run >> 32);
-    p.vid[g] = v;
-    p.fref[g] = f0 | (tris << 30);
     const int gy = g / p.GX, gx = g - gy * p.GX;
-    float pos[3];
-    d2m_unproject(p, gx, gy, d2m_depth(p, gx, gy), pos);
-    p.vertices[3 * (size_t)v + 0] = pos[0];
-    p.vertices[3 * (size_t)v + 1] = pos[1];
-    p.vertices[3 * (size_t)v + 2] = pos[2];
-    const int x = (gx + 1) * p.xs, y = (gy + 1) * p.ys;
-    if (p.point_cloud) {  // rgbd_util.cc:257-266
-      float* q = p.point_cloud + 3 * ((size_t)y * p.W + x);
-      q[0] = pos[0]; q[1] = pos[1]; q[2] = pos[2];
+    const float d = d2m_depth(p, gx, gy);
+    d2m_emit_image(p, g, gx, gy, c != 0ull, d);
+    if (c != 0ull) d2m_emit_vertex(p, g, gx, gy, d, run, tris);
+  }
+}
+
+// D2M-K2..4 in ONE pass (decoupled look-back, Merrill & Garland): a CTA takes the next chunk of kD2MBlock grid
+// points by ticket (so every predecessor chunk is already running or done: the spin below cannot deadlock), scans
+// its own contributions, publishes its aggregate, sums the predecessors' aggregates back to the nearest published
+// inclusive prefix (warp 0, 32 chunks per step), publishes its own inclusive prefix and emits.  The depth image
+// is read once instead of twice and the count / scan launches are gone.
+// state word: flag << 62 (0 = nothing yet, 1 = aggregate, 2 = inclusive prefix) | faces << 31 | vertices
+// (both < 2^29: the host bounds W * H below 2^28).  64-bit stores are single-copy atomic, so no fence is needed
+// between value and flag.
+constexpr unsigned long long kD2MAggregate = 1ull << 62, kD2MInclusive = 2ull << 62;
+constexpr unsigned long long kD2MStateValue = (1ull << 62) - 1ull;
+__device__ __forceinline__ unsigned long long d2m_pack31(unsigned long long c) {  // faces << 32 | vertices -> << 31
+  return (c & 0x7FFFFFFFull) | ((c >> 32) << 31);
+}
+__device__ __forceinline__ unsigned long long d2m_unpack31(unsigned long long s) {
+  return (s & 0x7FFFFFFFull) | (((s >> 31) & 0x7FFFFFFFull) << 32);
+}
+__device__ __forceinline__ unsigned long long d2m_ld_state(const unsigned long long* q) {
+  return *(const volatile unsigned long long*)q;
+}
+
+// next slab of the CTA: grid point g + 256 from (gx, gy) without a division (rows of >= 256 points)
+__device__ __forceinline__ void d2m_step256(const D2MParams& p, int g, int& gx, int& gy) {
+  if (p.GX >= 256) {
+    gx += 256;
+    if (gx >= p.GX) {
+      gx -= p.GX;
+      gy++;
     }
-    if (p.with_uv || p.with_color) {
-      const float u = ((float)x + 0.5f) / (float)p.W;   // X2U, raster_util.h:22-24
-      const float w = ((float)y + 0.5f) / (float)p.H;   // Y2V, flip = false
-      if (p.with_color) {  // nearest colour texel, rgbd_util.cc:178-190
-        const int tx = __float2int_rz(roundf(u * (float)p.cw - 0.5f));
-        const int ty = __float2int_rz(roundf(w * (float)p.ch - 0.5f));
-        const int txc = min(max(tx, 0), p.cw - 1), tyc = min(max(ty, 0), p.ch - 1);  // in range on contract
-        const uint8_t* t = p.color + 3 * ((size_t)tyc * p.cw + txc);
-        p.colors[3 * (size_t)v + 0] = (float)t[0];
-        p.colors[3 * (size_t)v + 1] = (float)t[1];
-        p.colors[3 * (size_t)v + 2] = (float)t[2];
+  } else {
+    gy = (g + 256) / p.GX;
+    gx = (g + 256) - gy * p.GX;
+  }
+}
+
+__global__ void __launch_bounds__(256) d2m_scan_emit_kernel(const D2MParams p, int nblocks) {
+  __shared__ int s_chunk;
+  __shared__ unsigned s_part[32];  // [slab * 8 + warp]: vertices | faces << 16 of the warp's 32 points of the slab
+  __shared__ unsigned long long s_prefix;
+  d2m_pdl_launch_dependents();
+  d2m_pdl_wait();  // `first` of d2m_first_kernel
+  if (threadIdx.x == 0) s_chunk = atomicAdd(p.ticket, 1);
+  __syncthreads();
+  const int chunk = s_chunk;
+  const int G = p.GX * p.GY;
+  const int first = *(volatile int*)p.first;
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
+  const int g0 = chunk * kD2MBlock + (int)threadIdx.x;
+  const int gy0 = g0 / p.GX, gx0 = g0 - gy0 * p.GX;
+  // Local scan.  A point contributes 1 vertex and 0..2 faces, so the warp-level prefix is three ballots and the
+  // CTA-level one a 32-entry scan of 16-bit pairs (<= 1024 vertices, <= 2048 faces per chunk).
+  float d[kD2MItems];
+  unsigned tris[kD2MItems], wex[kD2MItems];
+  unsigned valid = 0u;
+  {
+    int gx = gx0, gy = gy0;
+#pragma unroll
+    for (int k = 0; k < kD2MItems; k++) {  // lane = consecutive grid point, as in d2m_emit_vertices_kernel
+      const int g = g0 + k * 256;
+      bool v = false;
+      unsigned t = 0u;
+      float dd = 0.f;
+      if (g < G) {
+        dd = d2m_depth(p, gx, gy);
+        v = d2m_valid(dd);
+        if (v) t = d2m_tris(p, gx, gy, dd, first);
       }
-      if (p.with_uv) {  // rgbd_util.cc:192-195
-        p.uv[2 * (size_t)v + 0] = u;
-        p.uv[2 * (size_t)v + 1] = 1.0f - w;
+      const unsigned bv = __ballot_sync(0xffffffffu, v), b0 = __ballot_sync(0xffffffffu, t & 1u),
+                     b1 = __ballot_sync(0xffffffffu, t & 2u);
+      wex[k] = (unsigned)__popc(bv & lt) | ((unsigned)(__popc(b0 & lt) + __popc(b1 & lt)) << 16);
+      if (lane == 0u) s_part[k * 8 + warp] = (unsigned)__popc(bv) | ((unsigned)(__popc(b0) + __popc(b1)) << 16);
+      d[k] = dd;
+      tris[k] = t;
+      if (v) valid |= 1u << k;
+      d2m_step256(p, g, gx, gy);
+    }
+  }
+  __syncthreads();
+  const unsigned part = s_part[lane];
+  unsigned incl = part;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const unsigned o = __shfl_up_sync(0xffffffffu, incl, s);
+    if (lane >= (unsigned)s) incl += o;
+  }
+  const unsigned tot16 = __shfl_sync(0xffffffffu, incl, 31);
+  const unsigned long long total = (unsigned long long)(tot16 & 0xFFFFu) | ((unsigned long long)(tot16 >> 16) << 32);
+  unsigned long long excl[kD2MItems];
+#pragma unroll
+  for (int k = 0; k < kD2MItems; k++) {
+    const unsigned e = __shfl_sync(0xffffffffu, incl - part, k * 8 + (int)warp) + wex[k];
+    excl[k] = (unsigned long long)(e & 0xFFFFu) | ((unsigned long long)(e >> 16) << 32);
+  }
+  // the aggregate goes out first; the prefix-free part of the emission runs while the predecessors publish theirs
+  if (threadIdx.x == 0 && chunk > 0) *(volatile unsigned long long*)(p.state + chunk) = kD2MAggregate | d2m_pack31(total);
+  {
+    int gx = gx0, gy = gy0;
+#pragma unroll
+    for (int k = 0; k < kD2MItems; k++) {
+      const int g = g0 + k * 256;
+      if (g < G) d2m_emit_image(p, g, gx, gy, (valid >> k) & 1u, d[k]);
+      d2m_step256(p, g, gx, gy);
+    }
+  }
+  if (threadIdx.x < 32u) {
+    unsigned long long prefix = 0ull;  // packed31
+    if (chunk > 0) {
+      for (int base = chunk - 1;; base -= 32) {
+        const int idx = base - (int)lane;
+        unsigned long long st = idx >= 0 ? d2m_ld_state(p.state + idx) : kD2MInclusive;
+        while (__any_sync(0xffffffffu, (st >> 62) == 0ull))
+          if ((st >> 62) == 0ull) st = d2m_ld_state(p.state + idx);
+        const unsigned inc = __ballot_sync(0xffffffffu, (st >> 62) == 2ull);
+        const int stop = inc ? __ffs(inc) - 1 : 32;  // nearest inclusive prefix: lanes past it are not needed
+        unsigned long long v = ((int)lane <= stop) ? (st & kD2MStateValue) : 0ull;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+        prefix += v;
+        if (inc) break;
       }
+    }
+    if (lane == 0u) {
+      *(volatile unsigned long long*)(p.state + chunk) = kD2MInclusive | (prefix + d2m_pack31(total));
+      s_prefix = d2m_unpack31(prefix);
+      if (chunk == nblocks - 1) p.totals[0] = d2m_unpack31(prefix) + total;
+    }
+  }
+  __syncthreads();
+  const unsigned long long prefix = s_prefix;
+  {
+    int gx = gx0, gy = gy0;
+#pragma unroll
+    for (int k = 0; k < kD2MItems; k++) {
+      const int g = g0 + k * 256;
+      if ((valid >> k) & 1u) d2m_emit_vertex(p, g, gx, gy, d[k], prefix + excl[k], tris[k]);
+      d2m_step256(p, g, gx, gy);
     }
   }
 }
@@ -253,6 +423,8 @@ __device__ __forceinline__ void d2m_normalize(float (&v)[3]) {
 // D2M-K5: the (up to two) triangles of every vertex grid point and their face normals
 // (Mesh::CalcFaceNormal, src/mesh.cc:339-349).
 __global__ void __launch_bounds__(256) d2m_emit_faces_kernel(const D2MParams p) {
+  d2m_pdl_launch_dependents();
+  d2m_pdl_wait();
   const int G = p.GX * p.GY;
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= G) return;
@@ -290,12 +462,21 @@ __global__ void __launch_bounds__(256) d2m_emit_faces_kernel(const D2MParams p) 
 // D2M-K6: vertex normals (Mesh::CalcNormal, src/mesh.cc:310-336): sum of the adjacent face normals
 // in face order, divided by their number, normalised; zero for unreferenced vertices.
 __global__ void __launch_bounds__(256) d2m_vertex_normals_kernel(const D2MParams p) {
+  d2m_pdl_launch_dependents();
+  d2m_pdl_wait();
   const int G = p.GX * p.GY;
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= G) return;
   const int v = p.vid[g];
-  if (v < 0) return;
   const int gy = g / p.GX, gx = g - gy * p.GX;
+  if (p.zero_fill && p.normal_image) {  // steps (1, 1): the zeros of Init(normal, .., 0.0f), as in d2m_emit_point
+    const int x = gx + 1, y = gy + 1;
+    if (gx == 0) d2m_zero3(p.normal_image + 3 * ((size_t)y * p.W));
+    if (gy == 0) d2m_zero3(p.normal_image + 3 * (size_t)x);
+    if (g == 0) d2m_zero3(p.normal_image);
+    if (v < 0) d2m_zero3(p.normal_image + 3 * ((size_t)y * p.W + x));
+  }
+  if (v < 0) return;
   float s[3] = {0.f, 0.f, 0.f};
   int cnt = 0;
   auto add = [&](unsigned f) {

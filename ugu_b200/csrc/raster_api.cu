@@ -2378,18 +2378,39 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
   p.colors = (float*)r->d2m_colors.p;
   p.point_cloud = (float*)r->d2m_pc.p;
   p.normal_image = (float*)r->d2m_nimg.p;
+  // Single pass (d2m_scan_emit_kernel: count + scan + vertex emission behind a decoupled look-back) with the three
+  // kernels behind d2m_first_kernel chained by programmatic dependent launch; UGU_B200_D2M_FUSED=0 selects the
+  // three-kernel count / scan / emit form (A/B).  With steps (1, 1) every pixel has a grid point beside it and the
+  // kernels write the zeros of the two organized images themselves instead of two 12 B/pixel memsets.
+  static const bool single_pass = !(getenv("UGU_B200_D2M_FUSED") && atoi(getenv("UGU_B200_D2M_FUSED")) == 0);
+  p.state = p.block_sums;
+  p.ticket = (int*)((char*)r->d2m_small.p + 32);
+  p.zero_fill = (single_pass && x_step == 1 && y_step == 1 && G > 0) ? 1 : 0;
   CU_TRY(r, cudaMemsetAsync(r->d2m_small.p, 0x7f, 4, st));          // first = 0x7f7f7f7f > any grid index
-  CU_TRY(r, cudaMemsetAsync((char*)r->d2m_small.p + 16, 0, 8, st));
-  CU_TRY(r, cudaMemsetAsync(r->d2m_pc.p, 0, P * 12, st));            // ugu::Init(point_cloud, .., 0.0f)
-  CU_TRY(r, cudaMemsetAsync(r->d2m_nimg.p, 0, P * 12, st));
+  CU_TRY(r, cudaMemsetAsync((char*)r->d2m_small.p + 16, 0, 24, st));  // totals, ticket
+  if (!p.zero_fill) {
+    CU_TRY(r, cudaMemsetAsync(r->d2m_pc.p, 0, P * 12, st));            // ugu::Init(point_cloud, .., 0.0f)
+    CU_TRY(r, cudaMemsetAsync(r->d2m_nimg.p, 0, P * 12, st));
+  }
   if (G > 0) {
-    d2m_first_kernel<<<(unsigned)std::min<size_t>((size_t)nblocks, (size_t)g_num_sms * 8), 256, 0, st>>>(p);
-    d2m_count_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
-    d2m_scan_kernel<<<1, 256, 0, st>>>(p, nblocks);
-    d2m_emit_vertices_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
-    d2m_emit_faces_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
-    d2m_vertex_normals_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
-    r->stats.kernel_launches += 6;
+    const unsigned first_grid = (unsigned)std::min<size_t>((size_t)nblocks, (size_t)g_num_sms * 8);
+    if (single_pass) {
+      CU_TRY(r, cudaMemsetAsync(p.state, 0, (size_t)nblocks * 8, st));
+      d2m_first_kernel<<<first_grid, 256, 0, st>>>(p);
+      const bool pdl = r->use_pdl;
+      CU_TRY(r, LaunchView(d2m_scan_emit_kernel, dim3((unsigned)nblocks), 256, st, pdl, p, nblocks));
+      CU_TRY(r, LaunchView(d2m_emit_faces_kernel, dim3(Blocks(G, 256)), 256, st, pdl, p));
+      CU_TRY(r, LaunchView(d2m_vertex_normals_kernel, dim3(Blocks(G, 256)), 256, st, pdl, p));
+      r->stats.kernel_launches += 4;
+    } else {
+      d2m_first_kernel<<<first_grid, 256, 0, st>>>(p);
+      d2m_count_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
+      d2m_scan_kernel<<<1, 256, 0, st>>>(p, nblocks);
+      d2m_emit_vertices_kernel<<<(unsigned)nblocks, 256, 0, st>>>(p);
+      d2m_emit_faces_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
+      d2m_vertex_normals_kernel<<<Blocks(G, 256), 256, 0, st>>>(p);
+      r->stats.kernel_launches += 6;
+    }
   }
   CU_TRY(r, cudaGetLastError());
   CU_TRY(r, cudaMemcpyAsync(r->d2m_totals_host, p.totals, 8, cudaMemcpyDeviceToHost, st));

@@ -759,7 +759,6 @@ __global__ void __launch_bounds__(256, MINB) raster_kernel(const ViewBatch<NV> v
   const bool fused = HALVES == 1 && m.lv != nullptr;
   __shared__ float4 s_proj[HALVES == 1 ? 256 : 1];
   const unsigned lane = threadIdx.x & 31u;
-  const unsigned lt_mask = (1u << lane) - 1u;
   pdl_launch_dependents();
   unsigned blk = blockIdx.x;
   bool deferred = false;
