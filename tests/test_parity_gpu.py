@@ -11,7 +11,7 @@ import pytest
 import cases
 import util
 from oracle import OraclePort, OracleRef, ref_available
-from ugu_b200 import (DiffuseColor, DiffuseShading, PinholeCamera, RendererCpuOption, ShadingNormal)
+from ugu_b200 import (DiffuseColor, DiffuseShading, Image3f, PinholeCamera, RendererCpuOption, ShadingNormal)
 from ugu_b200 import meshgen
 
 pytestmark = pytest.mark.gpu
@@ -538,6 +538,39 @@ def test_folded_tile_jobs_close_up_and_batches(folded):
         assert np.array_equal(util.bits(dep[i * P:(i + 1) * P].cpu().numpy().reshape(360, 640)), util.bits(w["depth"])), i
     cam2 = PinholeCamera(97, 61, cams[0].c2w(), fov_y_deg=70.0)
     util.assert_parity(run.render(cam2, opt), port.render(cam2.to_native(), opt), strict=True, what="folded small")
+
+
+# ---- host-form Render: resolve in two bands, the D2H of band 0 under the resolve of band 1 ------------------------
+@pytest.fixture
+def banded(monkeypatch):
+    monkeypatch.setenv("UGU_B200_BANDS", "2")  # band every image of >= 64 chunks, not only the large ones
+
+
+@pytest.mark.parametrize("name", util.golden_names())
+def test_banded_render_vs_reference_golden(banded, name):
+    mesh, cam, opt, want, _ = util.load_golden(name)
+    run = util.CudaRunner(mesh, opt)  # pinned images: the banded path
+    for rep in range(2):
+        got = run.render(cam, opt)
+        util.assert_parity(got, want, strict=True, color_lsb=_lsb(opt), what=f"banded {name} #{rep}")
+
+
+def test_banded_render_ragged_sizes_and_subsets(banded):
+    """Image sizes whose band boundary / last chunk are ragged, output subsets, large triangles (tile jobs run by
+    binned_kernel ahead of band 0), and a pageable destination among pinned ones (falls back to one launch)."""
+    mesh = meshgen.icosphere(2)
+    opt = RendererCpuOption(diffuse_color=DiffuseColor.kVertex, backface_culling=True)
+    port = OraclePort(mesh)
+    for (w, h) in ((97, 61), (333, 77), (640, 360), (1021, 513)):
+        cam = PinholeCamera(w, h, meshgen.look_at_c2w((0.3, 0.2, -2.2), (0, 0, 0), (0, -1, 0)), fov_y_deg=50.0)
+        want = port.render(cam.to_native(), opt)
+        run = util.CudaRunner(mesh, opt)
+        util.assert_parity(run.render(cam, opt), want, strict=True, what=f"banded {w}x{h}")
+        got = run.render(cam, opt, want=("depth", "face_id"))
+        util.assert_parity(got, {k: want[k] for k in got}, strict=True, what=f"banded subset {w}x{h}")
+        mixed = util.CudaRunner(mesh, opt)
+        mixed.imgs["normal"] = Image3f(pinned=False)
+        util.assert_parity(mixed.render(cam, opt), want, strict=True, what=f"mixed pinned {w}x{h}")
 
 
 # ---- occlusion ordering: well-shaped camera-averse patches behind an occluder -------------------------------------------

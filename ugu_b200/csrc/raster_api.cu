@@ -47,6 +47,8 @@ struct ugu_b200_rasterizer {
   int device = 0;
   cudaStream_t stream = nullptr;       // compute stream (own)
   cudaStream_t copy_stream = nullptr;  // D2H stream for batch overlap
+  cudaEvent_t ev_band[2] = {nullptr, nullptr};  // host-form Render: the resolve bands' completion (BandPlan)
+  int bands = 0;                       // UGU_B200_BANDS: 1 = host-form Render resolves in two bands (off: it loses)
   std::string error;
   int deferred_status = UGU_B200_OK;
 
@@ -121,6 +123,8 @@ struct ugu_b200_rasterizer {
   HostCopyPool* copy_pool = nullptr;  // created by the first pageable destination
   int copy_threads = 0;               // host threads per pageable copy, the caller included (UGU_B200_COPY_THREADS)
   unsigned long long* counters_host = nullptr;  // pinned snapshot of the device counters
+  bool counters_mapped = false;                 // the resolve kernel of a single view writes it directly ...
+  bool host_snapshot = false;                   // ... during the host form of Render (0.7 us per view: not otherwise)
 
   // profiling
   bool profiling = false;
@@ -331,9 +335,11 @@ struct StageTimer {
     r->ev_stage[slot] = stage;
     cudaEventRecord(r->ev_pool[2 * slot], st);
   }
-  ~StageTimer() {
+  void Stop() {
     if (slot >= 0) cudaEventRecord(r->ev_pool[2 * slot + 1], st);
+    slot = -1;
   }
+  ~StageTimer() { Stop(); }
 };
 
 // ---- validation (mirrors ValidateAndInitBeforeRender, util_private.cc:12-67) --------------------
@@ -494,6 +500,7 @@ FrameDev MakeFrame(const ugu_b200_rasterizer* r, int W, int H) {
   fr.ray_dy = (float*)r->ray_dy.p;
   fr.vis = (unsigned long long*)r->vis.p;
   fr.counters = (unsigned long long*)r->counters.p;
+  fr.host_counters = (r->counters_mapped && r->host_snapshot) ? r->counters_host : nullptr;
   fr.q_face = (int*)r->q_face.p;
   fr.q_job = (unsigned long long*)r->q_job.p;
   fr.coop_max = 0;
@@ -514,6 +521,7 @@ FrameDev MakeFrame(const ugu_b200_rasterizer* r, int W, int H) {
 ShadeParams MakeShade(const ugu_b200_rasterizer* r, const ugu_b200_outputs* dout, size_t view_pixels,
                       unsigned first_view = 0) {
   ShadeParams sp;
+  sp.chunk_begin = sp.chunk_end = 0u;
   sp.diffuse_color = r->opt.diffuse_color;
   sp.interp = r->opt.interp;
   sp.shading_normal = r->opt.shading_normal;
@@ -549,9 +557,17 @@ int BatchViews(const ugu_b200_rasterizer* r, int n, int W, int H) {
 
 // One launch set (vertex, raster, tile jobs, resolve) for `n` <= kMaxBatch views of one image size into
 // device outputs on stream `st`; view v writes at element offset v * W*H of every requested output.
+// Resolve of a single view in bands (host-form Render): band b covers the 32-pixel chunks [split[b-1], split[b])
+// (split[-1] = 0, the last band runs to the end of the image) and records ev[b] when its outputs are complete.
+struct BandPlan {
+  int n = 1;
+  unsigned split[3] = {0, 0, 0};
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
 template <int NV>
 int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, const ugu_b200_outputs* dout,
-                  unsigned first_view, cudaStream_t st, const GBufParams* gbuf) {
+                  unsigned first_view, cudaStream_t st, const GBufParams* gbuf, const BandPlan* bands = nullptr) {
   const int W = cams[0].width, H = cams[0].height;
   int rc = EnsureFrame(r, W, H, n, st);
   if (rc) return rc;
@@ -592,7 +608,7 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   // a batch amortises the launch over its views (0.4 us per view) and keeps it.
   // (not the texture instantiations: they sit at the register limit, and carrying the tile-job code costs their hot
   //  loop more than the launch — config 4 741 -> 756 us per view)
-  const bool fold_binned = gbuf == nullptr && r->tiles <= 0 &&
+  const bool fold_binned = gbuf == nullptr && r->tiles <= 0 && bands == nullptr &&
                            (r->fold_binned >= 0 ? r->fold_binned != 0
                                                 : (NV == 1 && r->mesh.F >= kTwoPassMinFaces &&
                                                    !(dout->color != nullptr && r->opt.diffuse_color == UGU_B200_COLOR_TEXTURE)));
@@ -647,10 +663,14 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
     CU_TRY(r, LaunchView(gbuffer_kernel, dim3(grid), 256, st, false, vb.v[0], m, fr, gp));
     r->stats.kernel_launches++;
   }
-  {
-    StageTimer t(r, st, UGU_B200_STAGE_RESOLVE);
+  const int nbands = (NV == 1 && bands) ? bands->n : 1;
+  StageTimer resolve_timer(r, st, UGU_B200_STAGE_RESOLVE);
+  for (int band = 0; band < nbands; band++) {
     // persistent: enough CTAs to fill the machine, never more than there are 32-pixel chunks
-    const unsigned chunks = (unsigned)((P + 31) / 32);
+    const unsigned all_chunks = (unsigned)((P + 31) / 32);
+    sp.chunk_begin = band > 0 ? bands->split[band - 1] : 0u;
+    sp.chunk_end = band + 1 < nbands ? bands->split[band] : 0u;
+    const unsigned chunks = (sp.chunk_end ? sp.chunk_end : all_chunks) - sp.chunk_begin;
     const bool need_color = sp.color != nullptr;
     const bool need_nrm = sp.normal != nullptr || (need_color && sp.diffuse_shading != 0);
     const int color_mode = need_color ? sp.diffuse_color : 0;
@@ -683,9 +703,11 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
         return Fail(r, UGU_B200_E_INVALID, "option enumerator out of range");
     }
 #undef UGU_RESOLVE_CASE
+    if (nbands > 1) CU_TRY(r, cudaEventRecord(bands->ev[band], st));
   }
+  resolve_timer.Stop();
   CU_TRY(r, cudaGetLastError());
-  r->stats.kernel_launches += ((m.F > 0) ? (fold_binned ? 3 : 4) : 2) - ((fused && !fr.order) ? 1 : 0);
+  r->stats.kernel_launches += ((m.F > 0) ? (fold_binned ? 3 : 4) : 2) - ((fused && !fr.order) ? 1 : 0) + (nbands - 1);
   r->stats.views += (uint64_t)n;
   if (r->profiling) r->stats.timed_views += (uint64_t)n;
   r->stats.h2d_bytes += sizeof(ViewParams) * (size_t)n;
@@ -709,10 +731,10 @@ int RenderViews(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, cons
 
 // One view (optionally with the G-buffer kernel between the tile-job and the resolve kernel).
 int RenderView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_outputs* dout,
-               cudaStream_t st, const GBufParams* gbuf = nullptr) {
+               cudaStream_t st, const GBufParams* gbuf = nullptr, const BandPlan* bands = nullptr) {
   int rc = AcquireScratch(r, st);
   if (rc) return rc;
-  if ((rc = LaunchViewSet<1>(r, cam, 1, dout, 0u, st, gbuf))) return rc;
+  if ((rc = LaunchViewSet<1>(r, cam, 1, dout, 0u, st, gbuf, bands))) return rc;
   return ReleaseScratch(r, st);
 }
 
@@ -915,6 +937,7 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
     r->coop_max = std::max(1, std::min(atoi(e), kCoopMaxSamplesLimit));
   }
   if (const char* e = getenv("UGU_B200_PDL")) r->use_pdl = atoi(e) != 0;
+  if (const char* e = getenv("UGU_B200_BANDS")) r->bands = atoi(e);
   if (const char* e = getenv("UGU_B200_TWOPASS")) r->two_pass = std::max(0, std::min(2, atoi(e)));
   if (const char* e = getenv("UGU_B200_FOLD_BINNED")) r->fold_binned = atoi(e) != 0 ? 1 : 0;
   if (const char* e = getenv("UGU_B200_TILES")) r->tiles = atoi(e) != 0 ? 1 : 0;
@@ -949,6 +972,11 @@ int ugu_b200_rasterizer_create(int device, ugu_b200_rasterizer** out) {
   if ((e = cudaHostAlloc((void**)&r->counters_host, 64, cudaHostAllocDefault)) != cudaSuccess)
     return fail(e, "cudaHostAlloc");
   memset(r->counters_host, 0, 64);
+  {  // unified addressing: the pinned block is reachable from the device under the same pointer
+    int uva = 0;
+    cudaDeviceGetAttribute(&uva, cudaDevAttrUnifiedAddressing, device);
+    r->counters_mapped = uva != 0 && !(getenv("UGU_B200_MAPPED_COUNTERS") && atoi(getenv("UGU_B200_MAPPED_COUNTERS")) == 0);
+  }
   *out = r;
   return UGU_B200_OK;
 }
@@ -989,6 +1017,8 @@ void ugu_b200_rasterizer_destroy(ugu_b200_rasterizer* r) {
   if (r->ev_scratch) cudaEventDestroy(r->ev_scratch);
   if (r->stream) cudaStreamDestroy(r->stream);
   if (r->copy_stream) cudaStreamDestroy(r->copy_stream);
+  for (cudaEvent_t& e : r->ev_band)
+    if (e) cudaEventDestroy(e);
   delete r;
 }
 
@@ -1377,11 +1407,51 @@ int ugu_b200_rasterizer_render(ugu_b200_rasterizer* r, const ugu_b200_camera* ca
   const size_t P = (size_t)cam->width * cam->height;
   ugu_b200_outputs dout;
   if ((rc = EnsureInternalOutputs(r, 0, host_out, P, &dout))) return rc;
-  if ((rc = RenderView(r, cam, &dout, r->stream))) return rc;
-  CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
-                            r->stream));
   std::vector<CopySeg> segs;
   CollectSegs(host_out, &dout, P, 0, 1, &segs);
+  // The D2H of a view (24 B per pixel with all five outputs) is 12x its kernels, and nothing can be copied before
+  // the raster kernel is done — but the resolve need not be: it runs in two bands (the first eighth of the image,
+  // then the rest), and the copy stream starts on band 0 while band 1 is resolved.  Pinned destinations only (the
+  // pageable path stages through its own ring).  MEASURED AND OFF BY DEFAULT (UGU_B200_BANDS=1 selects it): ten DMAs
+  // and two cross-stream waits cost more than the 25 us of resolve they hide — config 2 e2e 1.024 vs 1.005 ms
+  // (profiles/r05e_banded_render_ab.jsonl).
+  // (UGU_B200_BANDS=2 bands every image of at least 64 chunks: the tests' small fixtures)
+  bool banded = r->bands != 0 && r->mesh.F > 0 && P >= (r->bands >= 2 ? size_t(2048) : (size_t(1) << 18));
+  for (const CopySeg& s : segs) banded = banded && DestPinned(r, s.dst);
+  if (banded) {
+    BandPlan plan;
+    plan.n = 2;
+    plan.split[0] = (unsigned)(((P + 31) / 32 / 8 + 7) & ~size_t(7));
+    for (int b = 0; b < 2; b++) {
+      if (!r->ev_band[b]) CU_TRY(r, cudaEventCreateWithFlags(&r->ev_band[b], cudaEventDisableTiming));
+      plan.ev[b] = r->ev_band[b];
+    }
+    if ((rc = RenderView(r, cam, &dout, r->stream, nullptr, &plan))) return rc;
+    CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
+                              r->stream));
+    const size_t cut = std::min(P, (size_t)plan.split[0] * 32);  // first pixel of band 1
+    for (int b = 0; b < 2; b++) {
+      CU_TRY(r, cudaStreamWaitEvent(r->copy_stream, plan.ev[b], 0));
+      const size_t p0 = b ? cut : 0, p1 = b ? P : cut;
+      for (const CopySeg& s : segs) {
+        const size_t bpp = s.bytes / P;  // 3, 4, 12, 1, 4
+        if (p1 > p0)
+          CU_TRY(r, cudaMemcpyAsync((char*)s.dst + p0 * bpp, (const char*)s.src + p0 * bpp, (p1 - p0) * bpp,
+                                    cudaMemcpyDeviceToHost, r->copy_stream));
+      }
+    }
+    for (const CopySeg& s : segs) r->stats.d2h_bytes += s.bytes;
+    CU_TRY(r, cudaStreamSynchronize(r->copy_stream));
+    CU_TRY(r, cudaStreamSynchronize(r->stream));
+    return SnapshotCounters(r);
+  }
+  r->host_snapshot = true;
+  rc = RenderView(r, cam, &dout, r->stream);
+  r->host_snapshot = false;
+  if (rc) return rc;
+  if (!r->counters_mapped)
+    CU_TRY(r, cudaMemcpyAsync(r->counters_host, (char*)r->counters.p + 32, 24, cudaMemcpyDeviceToHost,
+                              r->stream));
   if ((rc = CopyOut(r, segs, r->stream))) return rc;
   return SnapshotCounters(r);
 }

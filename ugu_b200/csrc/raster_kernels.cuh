@@ -102,6 +102,7 @@ struct MeshDev {
 };
 
 struct FrameDev {
+  unsigned long long* host_counters;  // mapped pinned host memory (3 words) or null, see resolve_kernel
   float4* proj;                  // V
   float* ray_dx;                 // W: ((float)x - cx) / fx
   float* ray_dy;                 // H: ((float)y - cy) / fy
@@ -154,6 +155,9 @@ struct ShadeParams {
   unsigned long long view_pixels;
   unsigned first_view;
   int fold_binned;  // no binned_kernel was launched for this launch set: the resolve kernel owns the tile-job queue
+  // single view resolved in bands (host-form Render: the D2H of band k runs under the resolve of band k + 1): this
+  // launch covers the 32-pixel chunks [chunk_begin, chunk_end); chunk_end == 0 = to the end of the image
+  unsigned chunk_begin, chunk_end;
 };
 
 __device__ __forceinline__ ShadeParams shade_view(const ShadeParams& b, int view) {
@@ -1354,13 +1358,13 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> 
   __shared__ __align__(16) unsigned char s_c[8][96];
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;  // W*H < 2^31 is validated by the host
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  const unsigned nchunks = (P + 31u) >> 5;
+  const unsigned nchunks = (NV == 1 && sp.chunk_end != 0u) ? sp.chunk_end : ((P + 31u) >> 5);
   const unsigned nwarps = gridDim.x * 8u;
   pdl_launch_dependents();
   pdl_wait();
   const bool cull = sp.backface_culling != 0;
   using Stage = ResolveStage<COLOR, NMODE>;
-  unsigned chunk = blockIdx.x * 8u + warp;
+  unsigned chunk = ((NV == 1) ? sp.chunk_begin : 0u) + blockIdx.x * 8u + warp;
   Stage a{}, b{}, c{};  // chunk, chunk + nwarps, chunk + 2 nwarps
   // FOLD: the queue counter travels with the first keys (one round trip, not two); the keys are speculative
   const unsigned long long packed = FOLD ? fr.counters[0] : 0ull;
@@ -1395,12 +1399,20 @@ __global__ void __launch_bounds__(256, MINB) resolve_kernel(const ViewBatch<NV> 
     if (chunk + nwarps < nchunks && pb < P) b.key = __ldcg(fr.vis + pb);
     if (chunk + 2u * nwarps < nchunks && pc < P) c.key = __ldcg(fr.vis + pc);
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) {
+  if (blockIdx.x == 0 && threadIdx.x == 0 && (NV != 1 || sp.chunk_begin == 0u)) {
     // the queue / hazard counters are consumed: snapshot them for the host (counters[4..5]) and
-    // reset them for the next view
+    // reset them for the next view (by the first band's launch when the view is resolved in bands)
     fr.counters[4] = fr.counters[0];
     fr.counters[5] = fr.counters[1];
     if (fr.counters[1] != 0ull) atomicAdd(fr0.counters + kTotalsOffset, fr.counters[1]);
+    if (NV == 1 && fr0.host_counters != nullptr) {
+      // the same three words straight into the host's (mapped, pinned) snapshot: the host form of a single view
+      // needs no 24-byte DMA between the kernels and the image copies
+      volatile unsigned long long* h = fr0.host_counters;
+      h[0] = fr.counters[0];
+      h[1] = fr.counters[1];
+      h[2] = *(volatile unsigned long long*)(fr0.counters + kTotalsOffset);
+    }
     fr.counters[0] = 0ull;
     fr.counters[1] = 0ull;
     fr.counters[2] = 0ull;
