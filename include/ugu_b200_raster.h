@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define UGU_B200_ABI_VERSION 9
+#define UGU_B200_ABI_VERSION 10
 
 enum {
   UGU_B200_OK = 0,
@@ -439,6 +439,30 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
                                   int32_t color_height, int32_t with_vertex_color,
                                   float max_connect_z_diff, int32_t x_step, int32_t y_step,
                                   int32_t gl_coord, void* stream);
+/* The two-camera overload (rgbd_util.h:39-48; Depth2MeshImpl, src/util/rgbd_util.cc:283-466): the colour image
+ * belongs to a second pinhole camera; uv and nearest-texel vertex colours come from the projection of
+ * depth2color * p (p = the vertex in the depth camera's frame, AFTER the gl_coord flip, as the reference does) into
+ * it (PinholeCamera::Project, camera.h:380-387), then X2U / Y2V over the colour image's size.  depth2color_R is the
+ * row-major 3x3 linear part and depth2color_t the translation of the reference's Eigen::Affine3f.  No aspect-ratio
+ * check in this overload; the colour image is always required; a vertex that projects outside the colour image
+ * reads out of bounds in the reference — here its texel coordinates are clamped.  The reference Init()s the two
+ * organized images only when their size differs from the depth image's; this library always returns what fresh
+ * images would hold.  Results are fetched with ugu_b200_depth_to_mesh_fetch. */
+typedef struct ugu_b200_color_camera {
+  float depth2color_R[9];
+  float depth2color_t[3];
+  float fx, fy, cx, cy;   /* colour camera intrinsics; its size is color_width x color_height */
+} ugu_b200_color_camera;
+int ugu_b200_depth_to_mesh_two_camera(ugu_b200_rasterizer* r, const ugu_b200_camera* depth_cam,
+                                      const ugu_b200_color_camera* color_cam, const float* depth_host,
+                                      const uint8_t* color_host, int32_t color_width, int32_t color_height,
+                                      int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                                      int32_t y_step, int32_t gl_coord, ugu_b200_depth2mesh_counts* counts);
+int ugu_b200_depth_to_mesh_two_camera_device(ugu_b200_rasterizer* r, const ugu_b200_camera* depth_cam,
+                                             const ugu_b200_color_camera* color_cam, const float* depth_dev,
+                                             const uint8_t* color_dev, int32_t color_width, int32_t color_height,
+                                             int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                                             int32_t y_step, int32_t gl_coord, void* stream);
 /* Waits for the last depth_to_mesh call and copies its result to HOST arrays (any may be NULL):
  * vertices / normals / colors num_vertices*3 f32, uv num_vertices*2, faces num_faces*3 i32 (they
  * are the mesh's vertex_indices, normal_indices and uv_indices alike), face_normals num_faces*3,

@@ -344,16 +344,27 @@ def _d2m_bufs(W, H, x_step, y_step):
             np.zeros((H, W, 3), np.float32), np.zeros((H, W, 3), np.float32))
 
 
+def two_camera_constants(depth2color, color_camera):
+    """The 16 floats the two-camera Depth2Mesh needs beside the depth camera: depth2color's rotation (row-major 9)
+    and translation (3), then fx, fy, cx, cy of the colour camera."""
+    m = np.asarray(depth2color, np.float32).reshape(4, 4)
+    f, c = color_camera.focal_length(), color_camera.principal_point()
+    return np.concatenate([m[:3, :3].reshape(-1), m[:3, 3], np.asarray([f[0], f[1], c[0], c[1]], np.float32)]
+                          ).astype(np.float32)
+
+
 def port_depth2mesh(cam_pod, depth, max_connect_z_diff, x_step=1, y_step=1, gl_coord=False, color=None,
-                    with_vertex_color=False):
+                    with_vertex_color=False, two_cam=None):
     """Plain-C restatement of ugu::Depth2Mesh (rgbd_util.cc:94-282 + Mesh::CalcNormal).  color None =
-    the depth-only overload, else the textured one.  Returns a dict of arrays or None (= false)."""
+    the depth-only overload, else the textured one; two_cam (two_camera_constants) = the two-camera overload
+    (rgbd_util.cc:283-466).  Returns a dict of arrays or None (= false)."""
     build_port()
     lib = C.CDLL(str(PORT_LIB))
-    fn = lib.oracle_depth2mesh
+    fn = lib.oracle_depth2mesh if two_cam is None else lib.oracle_depth2mesh2
     fn.restype = C.c_int
-    fn.argtypes = [C.POINTER(_PortCamera), C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float,
-                   C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 9
+    fn.argtypes = ([C.POINTER(_PortCamera)] + ([] if two_cam is None else [C.c_void_p]) +
+                   [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float,
+                    C.c_int32, C.c_int32, C.c_int32] + [C.c_void_p] * 9)
     cam = _PortCamera()
     for name, _ in _PortCamera._fields_:
         setattr(cam, name, getattr(cam_pod, name))
@@ -361,7 +372,9 @@ def port_depth2mesh(cam_pod, depth, max_connect_z_diff, x_step=1, y_step=1, gl_c
     col = None if color is None else np.ascontiguousarray(color, np.uint8)
     bufs = _d2m_bufs(cam.width, cam.height, x_step, y_step)
     counts = np.zeros(3, np.int32)
-    rc = fn(C.byref(cam), d.ctypes.data, None if col is None else col.ctypes.data,
+    tc = None if two_cam is None else np.ascontiguousarray(two_cam, np.float32)
+    rc = fn(C.byref(cam), *([] if tc is None else [tc.ctypes.data]), d.ctypes.data,
+            None if col is None else col.ctypes.data,
             0 if col is None else col.shape[1], 0 if col is None else col.shape[0],
             1 if with_vertex_color else 0, float(max_connect_z_diff), x_step, y_step, 1 if gl_coord else 0,
             *[b.ctypes.data for b in bufs], counts.ctypes.data)
@@ -401,6 +414,49 @@ def ref_depth2mesh(camera, depth, max_connect_z_diff, x_step=1, y_step=1, gl_coo
     if not have_normals:
         ptrs[2] = None
         ptrs[7] = None  # the reference reads normals()[i] of an empty vector here: undefined
+    bad = lib.ugu_ref_depth2mesh_copy(*ptrs)
+    assert bad == 0, "normal_indices / uv_indices differ from vertex_indices"
+    return _d2m_pack(nv, nf, bool(out[2]), bool(out[3]), have_normals, bufs)
+
+
+def _ref_camera(camera):
+    cam = _RefCamera()
+    cam.width, cam.height = camera.width(), camera.height()
+    cam.fx, cam.fy = float(camera.focal_length()[0]), float(camera.focal_length()[1])
+    cam.cx, cam.cy = float(camera.principal_point()[0]), float(camera.principal_point()[1])
+    cam.c2w = (C.c_double * 16)(*np.asarray(camera.c2w(), np.float64).reshape(-1))
+    return cam
+
+
+def ref_depth2mesh2(depth_camera, color_camera, depth2color, depth, color, max_connect_z_diff, x_step=1,
+                    y_step=1, gl_coord=False, with_vertex_color=False):
+    """The compiled reference's two-camera ugu::Depth2Mesh (rgbd_util.h:39-48) through oracle/_ref.
+    depth2color: 4x4 float32 (Eigen::Affine3f); color: (color_camera.height, color_camera.width, 3) u8."""
+    lib = C.CDLL(str(REF_LIB))
+    lib.ugu_ref_depth2mesh2.restype = C.c_int
+    lib.ugu_ref_depth2mesh2.argtypes = [C.POINTER(_RefCamera), C.POINTER(_RefCamera), C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_int32, C.c_float, C.c_int32, C.c_int32, C.c_int32,
+                                        C.c_void_p]
+    lib.ugu_ref_depth2mesh_copy.restype = C.c_int
+    lib.ugu_ref_depth2mesh_copy.argtypes = [C.c_void_p] * 8
+    dcam, ccam = _ref_camera(depth_camera), _ref_camera(color_camera)
+    d = np.ascontiguousarray(depth, np.float32)
+    col = np.ascontiguousarray(color, np.uint8)
+    assert col.shape[:2] == (ccam.height, ccam.width)
+    m = np.ascontiguousarray(depth2color, np.float32).reshape(4, 4)
+    out = np.zeros(6, np.int32)
+    rc = lib.ugu_ref_depth2mesh2(C.byref(dcam), C.byref(ccam), m.ctypes.data, d.ctypes.data, col.ctypes.data,
+                                 1 if with_vertex_color else 0, float(max_connect_z_diff), x_step, y_step,
+                                 1 if gl_coord else 0, out.ctypes.data)
+    if rc != 0:
+        return None
+    nv, nf = int(out[0]), int(out[1])
+    bufs = _d2m_bufs(dcam.width, dcam.height, x_step, y_step)
+    have_normals = nf > 0
+    ptrs = [b.ctypes.data for b in bufs]
+    if not have_normals:
+        ptrs[2] = None
+        ptrs[7] = None
     bad = lib.ugu_ref_depth2mesh_copy(*ptrs)
     assert bad == 0, "normal_indices / uv_indices differ from vertex_indices"
     return _d2m_pack(nv, nf, bool(out[2]), bool(out[3]), have_normals, bufs)

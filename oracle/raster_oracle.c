@@ -571,15 +571,20 @@ static void face_normal3(const float* a, const float* b, const float* c, float* 
  * face_normals 2*G*3 with G = ((W-1)/x_step) * ((H-1)/y_step) grid points; point_cloud and
  * normal_image are W*H*3 (zero-filled here like ugu::Init).  counts[0..1] = Nv, Nf.  Any output
  * except counts may be NULL.  Returns 1 where the reference returns false. */
-int oracle_depth2mesh(const OracleCamera* cam, const float* depth, const uint8_t* color, int32_t cw,
-                      int32_t ch, int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
-                      int32_t y_step, int32_t gl_coord, float* vertices, int32_t* faces, float* normals,
-                      float* face_normals, float* uv, float* colors, float* point_cloud,
-                      float* normal_image, int32_t* counts) {
+/* two_cam != NULL: the two-camera overload (rgbd_util.h:39-48; Depth2MeshImpl, rgbd_util.cc:283-466) — uv and
+ * nearest colour from the projection of depth2color * p into the colour camera (PinholeCamera::Project,
+ * camera.h:380-387).  two_cam = {R row-major 9, t 3, fx, fy, cx, cy} of depth2color / the colour camera; the
+ * Eigen::Affine3f product evaluates ((R_i0 x + R_i1 y) + R_i2 z) + t_i (pinned against the compiled reference).
+ * No aspect-ratio check in that overload; a colour pixel outside the image is undefined there and here. */
+static int depth2mesh_impl(const OracleCamera* cam, const float* two_cam, const float* depth, const uint8_t* color,
+                           int32_t cw, int32_t ch, int32_t with_vertex_color, float max_connect_z_diff,
+                           int32_t x_step, int32_t y_step, int32_t gl_coord, float* vertices, int32_t* faces,
+                           float* normals, float* face_normals, float* uv, float* colors, float* point_cloud,
+                           float* normal_image, int32_t* counts) {
   if (!cam || !depth || !counts) return 1;
   if (max_connect_z_diff < 0 || x_step < 1 || y_step < 1) return 1; /* rgbd_util.cc:100-112 */
   const int W = cam->width, H = cam->height;
-  if (color) { /* rgbd_util.cc:121-136 */
+  if (color && !two_cam) { /* rgbd_util.cc:121-136 */
     const float da = (float)W / (float)H, ca = (float)cw / (float)ch;
     if (fabsf(da - ca) > 0.01f) return 1;
   }
@@ -612,6 +617,17 @@ int oracle_depth2mesh(const OracleCamera* cam, const float* depth, const uint8_t
       vxy[nv * 2 + 1] = y;
       float u = ((float)x + 0.5f) / (float)W;            /* X2U */
       float v = ((float)y + 0.5f) / (float)H;            /* Y2V, flip = false */
+      if (two_cam) { /* rgbd_util.cc:345-350 */
+        const float* R = two_cam;
+        const float* t = two_cam + 9;
+        const float qx = ((R[0] * px + R[1] * py) + R[2] * pz) + t[0];
+        const float qy = ((R[3] * px + R[4] * py) + R[5] * pz) + t[1];
+        const float qz = ((R[6] * px + R[7] * py) + R[8] * pz) + t[2];
+        const float ix = two_cam[12] / qz * qx + two_cam[14];
+        const float iy = two_cam[13] / qz * qy + two_cam[15];
+        u = (ix + 0.5f) / (float)cw;
+        v = (iy + 0.5f) / (float)ch;
+      }
       if (color && with_vertex_color && colors) {
         const int cx_ = (int)roundf(u * (float)cw - 0.5f); /* U2X */
         const int cy_ = (int)roundf(v * (float)ch - 0.5f); /* V2Y, flip = false */
@@ -680,6 +696,27 @@ int oracle_depth2mesh(const OracleCamera* cam, const float* depth, const uint8_t
   counts[2] = have_normals;
   free(added); free(vbuf); free(fbuf); free(vxy); free(nsum); free(ncnt);
   return 0;
+}
+
+int oracle_depth2mesh(const OracleCamera* cam, const float* depth, const uint8_t* color, int32_t cw,
+                      int32_t ch, int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                      int32_t y_step, int32_t gl_coord, float* vertices, int32_t* faces, float* normals,
+                      float* face_normals, float* uv, float* colors, float* point_cloud,
+                      float* normal_image, int32_t* counts) {
+  return depth2mesh_impl(cam, NULL, depth, color, cw, ch, with_vertex_color, max_connect_z_diff, x_step, y_step,
+                         gl_coord, vertices, faces, normals, face_normals, uv, colors, point_cloud, normal_image,
+                         counts);
+}
+
+int oracle_depth2mesh2(const OracleCamera* cam, const float* two_cam16, const float* depth, const uint8_t* color,
+                       int32_t cw, int32_t ch, int32_t with_vertex_color, float max_connect_z_diff,
+                       int32_t x_step, int32_t y_step, int32_t gl_coord, float* vertices, int32_t* faces,
+                       float* normals, float* face_normals, float* uv, float* colors, float* point_cloud,
+                       float* normal_image, int32_t* counts) {
+  if (!two_cam16 || !color) return 1;
+  return depth2mesh_impl(cam, two_cam16, depth, color, cw, ch, with_vertex_color, max_connect_z_diff, x_step,
+                         y_step, gl_coord, vertices, faces, normals, face_normals, uv, colors, point_cloud,
+                         normal_image, counts);
 }
 
 /* ---------------------------------------------------------------------------------------------------

@@ -413,6 +413,42 @@ int ugu_ref_depth2mesh(const UguRefCamera* cam, const float* depth, const uint8_
   return 0;
 }
 
+// The two-camera overload (rgbd_util.h:39-48; Depth2MeshImpl, rgbd_util.cc:283-466): uv / vertex colours from
+// the projection of depth2color * p into the colour camera.  d2c16 = row-major 4x4 float (an Eigen::Affine3f).
+// The organized images are fresh (the overload only Init()s them when the size differs).
+int ugu_ref_depth2mesh2(const UguRefCamera* dcam, const UguRefCamera* ccam, const float* d2c16, const float* depth,
+                        const uint8_t* color, int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                        int32_t y_step, int32_t gl_coord, int32_t* out) {
+  ugu::set_log_level(ugu::LogLevel::kError);
+  ugu::PinholeCamera depth_camera(dcam->width, dcam->height, ToAffine(dcam->c2w),
+                                  Eigen::Vector2f(dcam->cx, dcam->cy), Eigen::Vector2f(dcam->fx, dcam->fy));
+  ugu::PinholeCamera color_camera(ccam->width, ccam->height, ToAffine(ccam->c2w),
+                                  Eigen::Vector2f(ccam->cx, ccam->cy), Eigen::Vector2f(ccam->fx, ccam->fy));
+  Eigen::Affine3f d2c = Eigen::Affine3f::Identity();
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) d2c.matrix()(i, j) = d2c16[i * 4 + j];
+  const size_t P = static_cast<size_t>(dcam->width) * dcam->height;
+  ugu::Image1f d;
+  ugu::Init(&d, dcam->width, dcam->height, 0.0f);
+  std::memcpy(d.data, depth, P * 4);
+  ugu::Image3b c = ugu::Image3b::zeros(ccam->height, ccam->width);
+  std::memcpy(c.data, color, static_cast<size_t>(ccam->width) * ccam->height * 3);
+  g_d2m_mesh.Clear();
+  g_d2m_pc = ugu::Image3f();
+  g_d2m_nrm = ugu::Image3f();
+  const bool ok = ugu::Depth2Mesh(d, c, depth_camera, color_camera, d2c, &g_d2m_mesh, max_connect_z_diff, x_step,
+                                  y_step, gl_coord != 0, "Depth2Mesh_mat", with_vertex_color != 0, &g_d2m_pc,
+                                  &g_d2m_nrm);
+  if (!ok) return 1;
+  out[0] = static_cast<int32_t>(g_d2m_mesh.vertices().size());
+  out[1] = static_cast<int32_t>(g_d2m_mesh.vertex_indices().size());
+  out[2] = g_d2m_mesh.uv().empty() ? 0 : 1;
+  out[3] = g_d2m_mesh.vertex_colors().empty() ? 0 : 1;
+  out[4] = g_d2m_pc.cols;
+  out[5] = g_d2m_pc.rows;
+  return 0;
+}
+
 // Copies the held result (any pointer may be null): vertices / normals Nv*3, faces Nf*3 (== the
 // mesh's normal_indices and uv_indices), face normals Nf*3, uv Nv*2, colours Nv*3, the organized
 // point-cloud and normal images W*H*3.  Returns 1 if an index array differs from vertex_indices.

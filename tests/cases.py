@@ -201,3 +201,28 @@ def ex02_poses(mesh: Mesh, lookat) -> List[np.ndarray]:
         eye[axis] += np.float32(sign) * d
         poses.append(lookat(eye, c, up))
     return poses
+
+
+def procedural_color(cw: int, ch: int) -> np.ndarray:
+    """A deterministic (ch, cw, 3) u8 image whose every texel differs from its neighbours (integer arithmetic only:
+    identical wherever it is generated)."""
+    y, x = np.mgrid[0:ch, 0:cw].astype(np.int64)
+    return np.stack([(x * 7 + y * 13) % 256, (x * 3 + y * 29 + 11) % 256, (x * x + 5 * y) % 256], -1).astype(np.uint8)
+
+
+def two_camera_setup(cw: int, ch: int, fov_y_deg: float, variant: int):
+    """Colour camera (a wider pinhole of its own size), depth2color (4x4 float32: a small rotation + shift, built
+    from exactly representable entries so that it is identical everywhere) and the colour image of the two-camera
+    Depth2Mesh cases."""
+    ccam = PinholeCamera(cw, ch, np.eye(4), fov_y_deg=fov_y_deg)
+    m = np.eye(4, dtype=np.float32)
+    if variant == 0:
+        m[:3, :3] = np.array([[0.99951171875, 0.0, 0.03125], [0.0009765625, 1.0, 0.001953125],
+                              [-0.03125, 0.0029296875, 0.99951171875]], np.float32)
+        m[:3, 3] = np.array([0.015625, -0.0078125, 0.01171875], np.float32)
+    elif variant == 1:
+        m[:3, :3] = np.array([[1.0, -0.015625, 0.0], [0.015625, 1.0, 0.0078125], [0.0, -0.0078125, 1.0]], np.float32)
+        m[:3, 3] = np.array([-0.03125, 0.0, 0.0625], np.float32)
+    else:
+        m[:3, 3] = np.array([0.0, 0.001953125, 0.25], np.float32)
+    return ccam, m, procedural_color(cw, ch)

@@ -298,6 +298,35 @@ int main(int argc, char** argv) {
                   m0.vertex_indices().size(), bad ? "MISMATCH" : "identical");
       if (bad || m0.vertex_indices().empty()) failures++;
     }
+    {  // the two-camera overload (rgbd_util.h:39-48): a wider colour camera, slightly rotated and shifted; the
+       // organized images arrive with the depth image's size and stale contents, which the reference keeps
+      auto color_camera = std::make_shared<ugu::PinholeCamera>(col.cols, col.rows, 60.0f);
+      Eigen::Affine3f d2c = Eigen::Affine3f::Identity();
+      d2c.linear() = (Eigen::AngleAxisf(0.03f, Eigen::Vector3f(0.2f, 1.0f, 0.1f).normalized())).toRotationMatrix();
+      d2c.translation() = Eigen::Vector3f(0.02f, -0.01f, 0.015f);
+      for (int wvc = 0; wvc < 2; wvc++) {
+        ugu::Mesh m0, m1;
+        ugu::Image3f p0, p1, n0, n1;
+        ugu::Init(&p0, dep.cols, dep.rows, 7.0f);
+        ugu::Init(&p1, dep.cols, dep.rows, 7.0f);
+        const int xs = wvc ? 2 : 1;
+        const bool ok0 = ugu::Depth2Mesh(dep, col, *camera, *color_camera, d2c, &m0, 0.05f, xs, 1, false, "mat",
+                                         wvc != 0, &p0, &n0);
+        const bool ok1 = rc.Depth2Mesh(dep, col, *camera, *color_camera, d2c, &m1, 0.05f, xs, 1, false, "mat",
+                                       wvc != 0, &p1, &n1);
+        int bad = 0;
+        if (!ok0 || !ok1) bad++;
+        if (!same3f(m0.vertices(), m1.vertices()) || !same3i(m0.vertex_indices(), m1.vertex_indices())) bad++;
+        if (!same3f(m0.normals(), m1.normals()) || !same3f(m0.face_normals(), m1.face_normals())) bad++;
+        if (!same3i(m0.uv_indices(), m1.uv_indices()) || !same3f(m0.vertex_colors(), m1.vertex_colors())) bad++;
+        if (m0.uv().size() != m1.uv().size() ||
+            (!m0.uv().empty() && std::memcmp(m0.uv()[0].data(), m1.uv()[0].data(), m0.uv().size() * 8) != 0)) bad++;
+        if (CountDiff(p0, p1, 0) || CountDiff(n0, n1, 0)) bad++;
+        std::printf("Depth2Mesh two cameras (vertex colours %d): %zu vertices %zu faces  %s\n", wvc,
+                    m0.vertices().size(), m0.vertex_indices().size(), bad ? "MISMATCH" : "identical");
+        if (bad || m0.vertex_indices().empty() || m0.uv().empty()) failures++;
+      }
+    }
     ugu::Mesh mm;
     if (rc.Depth2Mesh(dep, *camera, &mm, -1.0f)) failures++;  // false like the reference
   }

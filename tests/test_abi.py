@@ -30,7 +30,7 @@ def test_header_symbols_all_exported_and_bound():
 
 
 def test_abi_version():
-    assert N.load().ugu_b200_abi_version() == 9
+    assert N.load().ugu_b200_abi_version() == 10
 
 
 def test_struct_sizes_match_header_layout():

@@ -51,6 +51,11 @@ class UvRasterDesc(C.Structure):
                 ("keep_mask", C.c_int32), ("reserved", C.c_int32)]
 
 
+class ColorCamera(C.Structure):
+    _fields_ = [("depth2color_R", C.c_float * 9), ("depth2color_t", C.c_float * 3), ("fx", C.c_float),
+                ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float)]
+
+
 class Depth2MeshCounts(C.Structure):
     _fields_ = [("num_vertices", C.c_int32), ("num_faces", C.c_int32), ("has_normals", C.c_int32),
                 ("has_uv", C.c_int32), ("has_colors", C.c_int32), ("reserved", C.c_int32)]
@@ -155,6 +160,12 @@ SYMBOLS = {
     "ugu_b200_depth_to_mesh_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.c_void_p, C.c_void_p,
                                                 C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_int32,
                                                 C.c_int32, C.c_int32, C.c_void_p]),
+    "ugu_b200_depth_to_mesh_two_camera": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(ColorCamera), C.c_void_p,
+                                                    C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_float,
+                                                    C.c_int32, C.c_int32, C.c_int32, C.POINTER(Depth2MeshCounts)]),
+    "ugu_b200_depth_to_mesh_two_camera_device": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(ColorCamera),
+                                                           C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                                           C.c_float, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "ugu_b200_depth_to_mesh_fetch": (C.c_int, [C.c_void_p, C.POINTER(Depth2MeshCounts)] + [C.c_void_p] * 8),
     "ugu_b200_rasterizer_render_gbuffer": (C.c_int, [C.c_void_p, C.POINTER(Camera), C.POINTER(GBufferOption),
                                                      C.POINTER(GBuffer)]),
@@ -211,7 +222,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.ugu_b200_abi_version() != 9:
+    if lib.ugu_b200_abi_version() != 10:
         raise ImportError("libugu_b200_raster.so ABI version mismatch")
     _lib = lib
     return lib

@@ -399,10 +399,12 @@ bool RasterizerCuda::GenerateUvMask(const std::vector<Eigen::Vector2f>& uvs,
 }
 
 namespace {
+// `color_camera` / `depth2color` != nullptr: the two-camera overload (rgbd_util.cc:283-466)
 bool Depth2MeshCuda(ugu_b200_rasterizer* h, const Image1f& depth, const Image3b* color, const Camera& camera,
                     Mesh* mesh, float max_connect_z_diff, int x_step, int y_step, bool gl_coord,
                     const std::string& material_name, bool with_vertex_color, Image3f* point_cloud,
-                    Image3f* normal) {
+                    Image3f* normal, const Camera* color_camera = nullptr,
+                    const Eigen::Affine3f* depth2color = nullptr) {
   if (h == nullptr) {
     LOGE("RasterizerCuda: no CUDA rasterizer (no CPU fallback)\n");
     return false;
@@ -427,9 +429,32 @@ bool Depth2MeshCuda(ugu_b200_rasterizer* h, const Image1f& depth, const Image3b*
   c.cx = pin->principal_point().x();
   c.cy = pin->principal_point().y();
   ugu_b200_depth2mesh_counts cnt{};
-  if (ugu_b200_depth_to_mesh(h, &c, reinterpret_cast<const float*>(depth.data), color ? color->data : nullptr,
-                             color ? color->cols : 0, color ? color->rows : 0, with_vertex_color ? 1 : 0,
-                             max_connect_z_diff, x_step, y_step, gl_coord ? 1 : 0, &cnt) != UGU_B200_OK) {
+  int rc;
+  if (color_camera != nullptr) {
+    const auto* cpin = dynamic_cast<const PinholeCamera*>(color_camera);
+    if (cpin == nullptr || dynamic_cast<const OpenCvCamera*>(color_camera) != nullptr || color == nullptr ||
+        depth2color == nullptr) {
+      LOGE("RasterizerCuda::Depth2Mesh supports PinholeCamera only\n");
+      return false;
+    }
+    ugu_b200_color_camera cc{};
+    for (int i = 0; i < 3; i++) {
+      for (int j = 0; j < 3; j++) cc.depth2color_R[i * 3 + j] = depth2color->matrix()(i, j);
+      cc.depth2color_t[i] = depth2color->matrix()(i, 3);
+    }
+    cc.fx = cpin->focal_length().x();
+    cc.fy = cpin->focal_length().y();
+    cc.cx = cpin->principal_point().x();
+    cc.cy = cpin->principal_point().y();
+    rc = ugu_b200_depth_to_mesh_two_camera(h, &c, &cc, reinterpret_cast<const float*>(depth.data), color->data,
+                                           color->cols, color->rows, with_vertex_color ? 1 : 0, max_connect_z_diff,
+                                           x_step, y_step, gl_coord ? 1 : 0, &cnt);
+  } else {
+    rc = ugu_b200_depth_to_mesh(h, &c, reinterpret_cast<const float*>(depth.data), color ? color->data : nullptr,
+                                color ? color->cols : 0, color ? color->rows : 0, with_vertex_color ? 1 : 0,
+                                max_connect_z_diff, x_step, y_step, gl_coord ? 1 : 0, &cnt);
+  }
+  if (rc != UGU_B200_OK) {
     LOGE("%s\n", ugu_b200_last_error(h));
     return false;
   }
@@ -439,16 +464,34 @@ bool Depth2MeshCuda(ugu_b200_rasterizer* h, const Image1f& depth, const Image3b*
       colors(cnt.has_colors ? nv : 0);
   std::vector<Eigen::Vector3i> faces(nf);
   std::vector<Eigen::Vector2f> uvs(cnt.has_uv ? nv : 0);
-  if (point_cloud != nullptr) Init(point_cloud, depth.cols, depth.rows, 0.0f);
-  if (normal != nullptr) Init(normal, depth.cols, depth.rows, 0.0f);
+  // The one-camera overloads Init() the organized images (rgbd_util.cc:258,269); the two-camera one only when
+  // their size differs (:441-443,454-456) and otherwise overwrites the vertices' pixels of what it was given.
+  Image3f pc_fresh, nrm_fresh;
+  Image3f* pc_dst = point_cloud;
+  Image3f* nrm_dst = normal;
+  auto keeps = [&](const Image3f* im) {
+    return color_camera != nullptr && im != nullptr && im->cols == depth.cols && im->rows == depth.rows;
+  };
+  if (keeps(point_cloud)) pc_dst = &pc_fresh;
+  if (keeps(normal)) nrm_dst = &nrm_fresh;
+  if (pc_dst != nullptr) Init(pc_dst, depth.cols, depth.rows, 0.0f);
+  if (nrm_dst != nullptr) Init(nrm_dst, depth.cols, depth.rows, 0.0f);
   if (ugu_b200_depth_to_mesh_fetch(
           h, nullptr, nv ? vertices[0].data() : nullptr, nf ? faces[0].data() : nullptr,
           normals.empty() ? nullptr : normals[0].data(), nf ? face_normals[0].data() : nullptr,
           uvs.empty() ? nullptr : uvs[0].data(), colors.empty() ? nullptr : colors[0].data(),
-          point_cloud ? reinterpret_cast<float*>(point_cloud->data) : nullptr,
-          normal ? reinterpret_cast<float*>(normal->data) : nullptr) != UGU_B200_OK) {
+          pc_dst ? reinterpret_cast<float*>(pc_dst->data) : nullptr,
+          nrm_dst ? reinterpret_cast<float*>(nrm_dst->data) : nullptr) != UGU_B200_OK) {
     LOGE("%s\n", ugu_b200_last_error(h));
     return false;
+  }
+  if (pc_dst == &pc_fresh || nrm_dst == &nrm_fresh) {
+    for (int y = y_step; y < depth.rows; y += y_step)
+      for (int x = x_step; x < depth.cols; x += x_step) {
+        if (depth.at<float>(y, x) < std::numeric_limits<float>::min()) continue;
+        if (pc_dst == &pc_fresh) point_cloud->at<Vec3f>(y, x) = pc_fresh.at<Vec3f>(y, x);
+        if (nrm_dst == &nrm_fresh && cnt.has_normals) normal->at<Vec3f>(y, x) = nrm_fresh.at<Vec3f>(y, x);
+      }
   }
   mesh->set_vertices(vertices);
   mesh->set_vertex_indices(faces);
@@ -483,6 +526,16 @@ bool RasterizerCuda::Depth2Mesh(const Image1f& depth, const Image3b& color, cons
                                 Image3f* normal) const {
   return Depth2MeshCuda(pimpl_->handle_, depth, &color, camera, mesh, max_connect_z_diff, x_step, y_step,
                         gl_coord, material_name, with_vertex_color, point_cloud, normal);
+}
+
+bool RasterizerCuda::Depth2Mesh(const Image1f& depth, const Image3b& color, const Camera& depth_camera,
+                                const Camera& color_camera, const Eigen::Affine3f depth2color, Mesh* mesh,
+                                float max_connect_z_diff, int x_step, int y_step, bool gl_coord,
+                                const std::string& material_name, bool with_vertex_color, Image3f* point_cloud,
+                                Image3f* normal) const {
+  return Depth2MeshCuda(pimpl_->handle_, depth, &color, depth_camera, mesh, max_connect_z_diff, x_step, y_step,
+                        gl_coord, material_name, with_vertex_color, point_cloud, normal, &color_camera,
+                        &depth2color);
 }
 
 void RasterizerCuda::set_option(const RendererCpuOption& option) {

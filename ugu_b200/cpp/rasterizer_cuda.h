@@ -99,6 +99,14 @@ class RasterizerCuda : public RendererCpu {
                   float max_connect_z_diff, int x_step = 1, int y_step = 1, bool gl_coord = false,
                   const std::string& material_name = "Depth2Mesh_mat", bool with_vertex_color = false,
                   Image3f* point_cloud = nullptr, Image3f* normal = nullptr) const;
+  // the two-camera overload (rgbd_util.h:39-48, rgbd_util.cc:283-466): uv / vertex colours from the projection of
+  // depth2color * p into `color_camera`; like the reference it keeps the pixels without a vertex of organized
+  // images that already have the depth image's size
+  bool Depth2Mesh(const Image1f& depth, const Image3b& color, const Camera& depth_camera,
+                  const Camera& color_camera, const Eigen::Affine3f depth2color, Mesh* mesh,
+                  float max_connect_z_diff, int x_step = 1, int y_step = 1, bool gl_coord = false,
+                  const std::string& material_name = "Depth2Mesh_mat", bool with_vertex_color = false,
+                  Image3f* point_cloud = nullptr, Image3f* normal = nullptr) const;
 
   // ugu::GBuffer (include/ugu/renderer/base.h:34-77) as RendererGl::ReadGbuf fills it
   // (src/renderer/gl/renderer.cc:501-650) from the gbuf shaders (src/shader/glsl/{vert/gbuf.vert,

@@ -49,6 +49,11 @@ struct D2MParams {
   unsigned long long* state; // per chunk: flag << 62 | faces << 31 | vertices (decoupled look-back), zeroed per call
   int* ticket;               // chunk ticket counter, zeroed per call
   int zero_fill;             // steps (1, 1): the kernels write the zeros of the two images themselves (no memsets)
+  // two-camera overload (rgbd_util.cc:283-466): uv / colour from the projection of depth2color * p into the colour
+  // camera.  d2c = rotation (row-major 9) + translation (3) of the Eigen::Affine3f
+  int two_cam;
+  float d2c[12];
+  float cfx, cfy, ccx, ccy;
 };
 
 __device__ __forceinline__ void d2m_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -226,8 +231,19 @@ __device__ __forceinline__ void d2m_emit_vertex(const D2MParams& p, int g, int g
   p.vertices[3 * (size_t)v + 1] = pos[1];
   p.vertices[3 * (size_t)v + 2] = pos[2];
   if (p.with_uv || p.with_color) {
-    const float u = ((float)x + 0.5f) / (float)p.W;   // X2U, raster_util.h:22-24
-    const float w = ((float)y + 0.5f) / (float)p.H;   // Y2V, flip = false
+    float u = ((float)x + 0.5f) / (float)p.W;   // X2U, raster_util.h:22-24
+    float w = ((float)y + 0.5f) / (float)p.H;   // Y2V, flip = false
+    if (p.two_cam) {
+      // rgbd_util.cc:345-350: Affine3f * Vector3f evaluates ((R_i0 x + R_i1 y) + R_i2 z) + t_i (pinned against the
+      // compiled reference, tools/probe_d2m2.py), then PinholeCamera::Project (camera.h:380-387), X2U / Y2V
+      const float qx = ((p.d2c[0] * pos[0] + p.d2c[1] * pos[1]) + p.d2c[2] * pos[2]) + p.d2c[9];
+      const float qy = ((p.d2c[3] * pos[0] + p.d2c[4] * pos[1]) + p.d2c[5] * pos[2]) + p.d2c[10];
+      const float qz = ((p.d2c[6] * pos[0] + p.d2c[7] * pos[1]) + p.d2c[8] * pos[2]) + p.d2c[11];
+      const float ix = p.cfx / qz * qx + p.ccx;
+      const float iy = p.cfy / qz * qy + p.ccy;
+      u = (ix + 0.5f) / (float)p.cw;
+      w = (iy + 0.5f) / (float)p.ch;
+    }
     if (p.with_color) {  // nearest colour texel, rgbd_util.cc:178-190
       const int tx = __float2int_rz(roundf(u * (float)p.cw - 0.5f));
       const int ty = __float2int_rz(roundf(w * (float)p.ch - 0.5f));

@@ -2384,13 +2384,15 @@ int ugu_b200_visibility_stats(ugu_b200_rasterizer* r, const ugu_b200_vis_stats* 
   return UGU_B200_OK;
 }
 
-int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
-                                  const float* depth_dev, const uint8_t* color_dev, int32_t color_width,
-                                  int32_t color_height, int32_t with_vertex_color,
-                                  float max_connect_z_diff, int32_t x_step, int32_t y_step,
-                                  int32_t gl_coord, void* stream) {
+namespace {
+// `cc` != NULL: the two-camera overload (rgbd_util.h:39-48; Depth2MeshImpl, rgbd_util.cc:283-466)
+int D2MDevice(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_color_camera* cc,
+              const float* depth_dev, const uint8_t* color_dev, int32_t color_width, int32_t color_height,
+              int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step, int32_t y_step,
+              int32_t gl_coord, void* stream) {
   if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
   if (!cam || !depth_dev) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  if (cc && !color_dev) return Fail(r, UGU_B200_E_INVALID, "the two-camera form needs the colour image");
   r->d2m_valid = false;
   // rgbd_util.cc:100-112 (the reference's messages)
   if (max_connect_z_diff < 0) return Fail(r, UGU_B200_E_INVALID, "Depth2Mesh max_connect_z_diff must be positive %f", max_connect_z_diff);
@@ -2402,7 +2404,7 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
   if (color_dev) {  // rgbd_util.cc:121-136
     if (color_width <= 0 || color_height <= 0) return Fail(r, UGU_B200_E_INVALID, "colour size is invalid");
     const float da = (float)W / (float)H, ca = (float)color_width / (float)color_height;
-    if (std::fabs(da - ca) > 0.01f)
+    if (!cc && std::fabs(da - ca) > 0.01f)  // (the two-camera overload does not check)
       return Fail(r, UGU_B200_E_INVALID, "Depth2Mesh depth aspect ratio %f and color aspect ratio %f are very different", da, ca);
   }
   CU_TRY(r, cudaSetDevice(r->device));
@@ -2417,6 +2419,12 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
   p.with_uv = color_dev ? 1 : 0;
   p.with_color = (color_dev && with_vertex_color) ? 1 : 0;
   p.cw = color_width; p.ch = color_height;
+  p.two_cam = cc ? 1 : 0;
+  if (cc) {
+    for (int i = 0; i < 9; i++) p.d2c[i] = cc->depth2color_R[i];
+    for (int i = 0; i < 3; i++) p.d2c[9 + i] = cc->depth2color_t[i];
+    p.cfx = cc->fx; p.cfy = cc->fy; p.ccx = cc->cx; p.ccy = cc->cy;
+  }
   p.depth = depth_dev;
   p.color = color_dev;
   const size_t G = (size_t)p.GX * (size_t)p.GY, P = (size_t)W * H;
@@ -2492,6 +2500,26 @@ int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera*
   r->d2m_valid = true;
   return UGU_B200_OK;
 }
+}  // namespace
+
+int ugu_b200_depth_to_mesh_device(ugu_b200_rasterizer* r, const ugu_b200_camera* cam,
+                                  const float* depth_dev, const uint8_t* color_dev, int32_t color_width,
+                                  int32_t color_height, int32_t with_vertex_color,
+                                  float max_connect_z_diff, int32_t x_step, int32_t y_step,
+                                  int32_t gl_coord, void* stream) {
+  return D2MDevice(r, cam, nullptr, depth_dev, color_dev, color_width, color_height, with_vertex_color,
+                   max_connect_z_diff, x_step, y_step, gl_coord, stream);
+}
+
+int ugu_b200_depth_to_mesh_two_camera_device(ugu_b200_rasterizer* r, const ugu_b200_camera* depth_cam,
+                                             const ugu_b200_color_camera* color_cam, const float* depth_dev,
+                                             const uint8_t* color_dev, int32_t color_width, int32_t color_height,
+                                             int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                                             int32_t y_step, int32_t gl_coord, void* stream) {
+  if (r && !color_cam) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  return D2MDevice(r, depth_cam, color_cam, depth_dev, color_dev, color_width, color_height, with_vertex_color,
+                   max_connect_z_diff, x_step, y_step, gl_coord, stream);
+}
 
 namespace {
 int D2MCounts(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* c) {
@@ -2509,10 +2537,11 @@ int D2MCounts(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* c) {
 }
 }  // namespace
 
-int ugu_b200_depth_to_mesh(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* depth_host,
-                           const uint8_t* color_host, int32_t color_width, int32_t color_height,
-                           int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
-                           int32_t y_step, int32_t gl_coord, ugu_b200_depth2mesh_counts* counts) {
+namespace {
+int D2MHost(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200_color_camera* cc,
+            const float* depth_host, const uint8_t* color_host, int32_t color_width, int32_t color_height,
+            int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step, int32_t y_step, int32_t gl_coord,
+            ugu_b200_depth2mesh_counts* counts) {
   if (!r) return Fail(nullptr, UGU_B200_E_INVALID, "rasterizer is NULL");
   if (!cam || !depth_host || !counts) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
   if (cam->width <= 0 || cam->height <= 0) return Fail(r, UGU_B200_E_INVALID, "depth size is invalid");
@@ -2531,11 +2560,29 @@ int ugu_b200_depth_to_mesh(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, c
     r->stats.h2d_bytes += cb;
     cdev = (const uint8_t*)r->d2m_in_color.p;
   }
-  if ((rc = ugu_b200_depth_to_mesh_device(r, cam, (const float*)r->d2m_in_depth.p, cdev, color_width,
-                                          color_height, with_vertex_color, max_connect_z_diff, x_step,
-                                          y_step, gl_coord, r->stream)))
+  if ((rc = D2MDevice(r, cam, cc, (const float*)r->d2m_in_depth.p, cdev, color_width, color_height,
+                      with_vertex_color, max_connect_z_diff, x_step, y_step, gl_coord, r->stream)))
     return rc;
   return D2MCounts(r, counts);
+}
+}  // namespace
+
+int ugu_b200_depth_to_mesh(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float* depth_host,
+                           const uint8_t* color_host, int32_t color_width, int32_t color_height,
+                           int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                           int32_t y_step, int32_t gl_coord, ugu_b200_depth2mesh_counts* counts) {
+  return D2MHost(r, cam, nullptr, depth_host, color_host, color_width, color_height, with_vertex_color,
+                 max_connect_z_diff, x_step, y_step, gl_coord, counts);
+}
+
+int ugu_b200_depth_to_mesh_two_camera(ugu_b200_rasterizer* r, const ugu_b200_camera* depth_cam,
+                                      const ugu_b200_color_camera* color_cam, const float* depth_host,
+                                      const uint8_t* color_host, int32_t color_width, int32_t color_height,
+                                      int32_t with_vertex_color, float max_connect_z_diff, int32_t x_step,
+                                      int32_t y_step, int32_t gl_coord, ugu_b200_depth2mesh_counts* counts) {
+  if (r && (!color_cam || !color_host)) return Fail(r, UGU_B200_E_INVALID, "NULL argument");
+  return D2MHost(r, depth_cam, color_cam, depth_host, color_host, color_width, color_height, with_vertex_color,
+                 max_connect_z_diff, x_step, y_step, gl_coord, counts);
 }
 
 int ugu_b200_depth_to_mesh_fetch(ugu_b200_rasterizer* r, ugu_b200_depth2mesh_counts* counts,

@@ -192,6 +192,18 @@ class _PinnedBlock:
                 pass
 
 
+def color_camera_native(color_camera: "PinholeCamera", depth2color) -> "N.ColorCamera":
+    """ugu_b200_color_camera of the two-camera Depth2Mesh: depth2color (4x4, as Eigen::Affine3f) and the colour
+    camera's intrinsics, all rounded to float like the reference's arguments."""
+    m = np.asarray(depth2color, np.float32).reshape(4, 4)
+    cc = N.ColorCamera()
+    cc.depth2color_R = (C.c_float * 9)(*m[:3, :3].reshape(-1))
+    cc.depth2color_t = (C.c_float * 3)(*m[:3, 3])
+    f, c = color_camera.focal_length(), color_camera.principal_point()
+    cc.fx, cc.fy, cc.cx, cc.cy = float(f[0]), float(f[1]), float(c[0]), float(c[1])
+    return cc
+
+
 def pinned_empty(shape, dtype) -> np.ndarray:
     """A numpy array over pinned host memory from the C-ABI (so Render's D2H is one DMA).  The memory
     lives exactly as long as the array and the views taken from it."""
@@ -567,9 +579,12 @@ class Rasterizer:
     def Depth2Mesh(self, depth: "Image1f", camera: "PinholeCamera", mesh: "Mesh", max_connect_z_diff: float,
                    x_step: int = 1, y_step: int = 1, gl_coord: bool = False,
                    point_cloud: Optional["Image3f"] = None, normal: Optional["Image3f"] = None,
-                   color: Optional["Image3b"] = None, with_vertex_color: bool = False) -> bool:
-        """Both overloads of ugu::Depth2Mesh: `color` None = depth only, else the textured one (uv,
-        material = the colour image, vertex colours when asked).  Fills `mesh` like the reference:
+                   color: Optional["Image3b"] = None, with_vertex_color: bool = False,
+                   color_camera: Optional["PinholeCamera"] = None, depth2color=None) -> bool:
+        """The overloads of ugu::Depth2Mesh: `color` None = depth only, else the textured one (uv,
+        material = the colour image, vertex colours when asked); with `color_camera` and `depth2color`
+        (4x4, the reference's Eigen::Affine3f) the two-camera overload (rgbd_util.h:39-48): uv and colours
+        from the projection of depth2color * p into the colour camera.  Fills `mesh` like the reference:
         vertices, vertex_indices, normals + normal_indices + face_normals (Mesh::CalcNormal), uv +
         uv_indices + materials + material_ids, vertex_colors; `point_cloud` / `normal` are the
         organized images.  false + log on the reference's error conditions."""
@@ -580,11 +595,21 @@ class Rasterizer:
         cam = camera.to_native()
         cnt = N.Depth2MeshCounts()
         col = None if color is None else np.ascontiguousarray(color.data, np.uint8)
-        rc = self._lib.ugu_b200_depth_to_mesh(
-            self._h, C.byref(cam), np.ascontiguousarray(depth.data, np.float32).ctypes.data,
-            None if col is None else col.ctypes.data, 0 if col is None else color.cols,
-            0 if col is None else color.rows, 1 if with_vertex_color else 0, float(max_connect_z_diff),
-            int(x_step), int(y_step), 1 if gl_coord else 0, C.byref(cnt))
+        if color_camera is not None:
+            if col is None or depth2color is None:
+                LOGE("Depth2Mesh with a colour camera needs the colour image and depth2color")
+                return False
+            rc = self._lib.ugu_b200_depth_to_mesh_two_camera(
+                self._h, C.byref(cam), C.byref(color_camera_native(color_camera, depth2color)),
+                np.ascontiguousarray(depth.data, np.float32).ctypes.data, col.ctypes.data, color.cols, color.rows,
+                1 if with_vertex_color else 0, float(max_connect_z_diff), int(x_step), int(y_step),
+                1 if gl_coord else 0, C.byref(cnt))
+        else:
+            rc = self._lib.ugu_b200_depth_to_mesh(
+                self._h, C.byref(cam), np.ascontiguousarray(depth.data, np.float32).ctypes.data,
+                None if col is None else col.ctypes.data, 0 if col is None else color.cols,
+                0 if col is None else color.rows, 1 if with_vertex_color else 0, float(max_connect_z_diff),
+                int(x_step), int(y_step), 1 if gl_coord else 0, C.byref(cnt))
         if rc != N.OK:
             LOGE(N.last_error(self._h))
             return False
