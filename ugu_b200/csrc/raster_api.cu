@@ -2419,6 +2419,14 @@ int D2MDevice(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200
   p.with_uv = color_dev ? 1 : 0;
   p.with_color = (color_dev && with_vertex_color) ? 1 : 0;
   p.cw = color_width; p.ch = color_height;
+  p.gx_magic = 0;
+  p.gx_shift = 0;
+  if (p.GX > 1) {  // Granlund-Montgomery, N = 31, as MakeViewParams does for W
+    unsigned l = 0;
+    while ((1ull << l) < (unsigned long long)p.GX) l++;
+    p.gx_magic = (unsigned)(((1ull << (31 + l)) + (unsigned long long)p.GX - 1) / (unsigned long long)p.GX);
+    p.gx_shift = l - 1;
+  }
   p.two_cam = cc ? 1 : 0;
   if (cc) {
     for (int i = 0; i < 9; i++) p.d2c[i] = cc->depth2color_R[i];
