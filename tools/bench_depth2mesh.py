@@ -67,7 +67,7 @@ def main():
     peak = json.loads(peak_file.read_text()).get("hbm_gbs", 6550.0) if peak_file.exists() else 6550.0
     line = {"workload": f"Depth2Mesh (textured + vertex colours, step 1) of config 2's 1920x1080 view: "
                         f"{nv} vertices, {nf} faces", "iters": iters, "ms_per_call": ms,
-            "mpix_per_s": P / ms / 1e3, "mtri_per_s": nf / ms / 1e3, "gpu_launches_per_call": int(os.environ.get("UGU_B200_D2M_FUSED", "1")) and 4 or 6,
+            "mpix_per_s": P / ms / 1e3, "mtri_per_s": nf / ms / 1e3, "gpu_launches_per_call": 6 if os.environ.get("UGU_B200_D2M_FUSED", "1") == "0" else 4,
             "roofline": {"bound": "hbm", "algorithmic_bytes": algo, "achieved": algo / ms / 1e6, "peak": peak,
                          "unit": "GB/s", "frac": algo / ms / 1e6 / peak},
             "l2": "flushed between timed iterations (512 MiB write)"}

@@ -459,21 +459,22 @@ __global__ void __launch_bounds__(256) d2m_emit_faces_kernel(const D2MParams p) 
   const int cur = p.vid[g], ul = p.vid[g - p.GX - 1];
   const float* vc = p.vertices + 3 * (size_t)cur;
   const float* vu = p.vertices + 3 * (size_t)ul;
+  // the diagonal current - upper_left is an edge of both triangles: normalised once
+  float dg[3] = {vc[0] - vu[0], vc[1] - vu[1], vc[2] - vu[2]};
+  d2m_normalize(dg);
 #pragma unroll
   for (int t = 0; t < 2; t++) {
     if (!(tris & (1u << t))) continue;
     // t = 0: (upper_left, current, upper); t = 1: (upper_left, left, current)
     const int other = t == 0 ? p.vid[g - p.GX] : p.vid[g - 1];
-    const int i1 = t == 0 ? cur : other, i2 = t == 0 ? other : cur;
-    const float* v1p = t == 0 ? vc : p.vertices + 3 * (size_t)other;
-    const float* v2p = t == 0 ? p.vertices + 3 * (size_t)other : vc;
+    const float* vo = p.vertices + 3 * (size_t)other;
     p.faces[3 * (size_t)f + 0] = ul;
-    p.faces[3 * (size_t)f + 1] = i1;
-    p.faces[3 * (size_t)f + 2] = i2;
-    float a[3] = {v1p[0] - vu[0], v1p[1] - vu[1], v1p[2] - vu[2]};
-    float b[3] = {v2p[0] - vu[0], v2p[1] - vu[1], v2p[2] - vu[2]};
-    d2m_normalize(a);
-    d2m_normalize(b);
+    p.faces[3 * (size_t)f + 1] = t == 0 ? cur : other;
+    p.faces[3 * (size_t)f + 2] = t == 0 ? other : cur;
+    float e[3] = {vo[0] - vu[0], vo[1] - vu[1], vo[2] - vu[2]};
+    d2m_normalize(e);
+    const float* a = t == 0 ? dg : e;  // (v1 - v0).normalized()
+    const float* b = t == 0 ? e : dg;  // (v2 - v0).normalized()
     float n[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
     d2m_normalize(n);
     p.face_normals[3 * (size_t)f + 0] = n[0];
