@@ -1825,7 +1825,11 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
   p.mask = mask_dev;
   uv_setup_kernel<<<Blocks((size_t)p.F, 256), 256, 0, st>>>(p);
   uv_tile_kernel<<<(unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, 0, st>>>(p);
-  uv_resolve_kernel<<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
+  // long runs of one winner (at least 64 texels per face on average) take the one-live-record instantiation
+  if (P >= (size_t)64 * (size_t)std::max(d->num_faces, 1))
+    uv_resolve_kernel<true><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
+  else
+    uv_resolve_kernel<false><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += 3;
   return UGU_B200_OK;

@@ -281,49 +281,108 @@ __device__ __forceinline__ unsigned uv_to_u8(float c) {
 constexpr int kUvGroupsPerThread = 4;  // 4-texel groups per thread: 64 bytes of winners in flight per thread
 
 // One group of 4 consecutive texels starting at `base` whose winners are f[0..3].
+template <bool RUNS>
 __device__ __forceinline__ void uv_resolve_group(const UvRasterParams& p, size_t P, size_t base, bool full,
                                                  const int (&f)[4]) {
-  // One dependent level after the winners: the 64-byte face records of the (up to 4) distinct
-  // winners are requested together; a texel whose winner equals its left neighbour's reuses the
-  // neighbour's registers.
+  if (full && (f[0] & f[1] & f[2] & f[3]) < 0) {
+    // nothing covers these four texels (most of an atlas's gutters): the cleared values, or nothing at all
+    if (!p.keep_texture) {
+      if (p.texture_f32) {
+        float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.texture) + base * 3);
+        o[0] = o[1] = o[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        unsigned* o = reinterpret_cast<unsigned*>(reinterpret_cast<uint8_t*>(p.texture) + base * 3);
+        o[0] = o[1] = o[2] = 0u;
+      }
+    }
+    if (p.mask && !p.keep_mask) *reinterpret_cast<unsigned*>(p.mask + base) = 0u;
+    return;
+  }
   float c[4][3];
   bool cov[4];
-  float4 r[4][4];
+  if (RUNS) {
+    // Long runs of one winner (few large faces): the (up to 4) distinct records of the group are requested together
+    // as L1 prefetches, which hold no registers, and then ONE record is live at a time — a texel whose winner equals
+    // its left neighbour's keeps the registers, another winner reloads them from the prefetched lines.  64 registers
+    // and three CTAs per SM instead of 123 and two: vc2tex 0.157 -> 0.129 ms.  (Meshes of texel-sized faces change
+    // winner at every texel and want the four loads in flight together: posmap 0.110 -> 0.116 ms with this form;
+    // a two-record pipeline lost on both.)
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    cov[k] = f[k] >= 0;
-    const bool need = cov[k] && (k == 0 || f[k] != f[k - 1]);
-    if (need) {
-      const float4* q = p.rec + 4 * (size_t)f[k];
-      r[k][0] = q[0];  // plain loads: written by uv_setup_kernel of this call
-      r[k][1] = q[1];
-      r[k][2] = q[2];
-      r[k][3] = q[3];
+    for (int k = 0; k < 4; k++) {
+      cov[k] = f[k] >= 0;
+      if (cov[k] && (k == 0 || f[k] != f[k - 1])) {
+        const float4* q = p.rec + 4 * (size_t)f[k];
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
+      }
     }
-  }
-  int y = (int)((unsigned)base / (unsigned)p.W), x = (int)((unsigned)base - (unsigned)y * (unsigned)p.W);
+    int y = (int)((unsigned)base / (unsigned)p.W), x = (int)((unsigned)base - (unsigned)y * (unsigned)p.W);
+    float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0, r3 = r0;
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    if (k > 0 && cov[k] && f[k] == f[k - 1]) {
-      r[k][0] = r[k - 1][0];
-      r[k][1] = r[k - 1][1];
-      r[k][2] = r[k - 1][2];
-      r[k][3] = r[k - 1][3];
+    for (int k = 0; k < 4; k++) {
+      c[k][0] = c[k][1] = c[k][2] = 0.f;
+      if (cov[k]) {
+        if (k == 0 || f[k] != f[k - 1]) {
+          const float4* q = p.rec + 4 * (size_t)f[k];
+          r0 = q[0];  // plain loads: written by uv_setup_kernel of this call
+          r1 = q[1];
+          r2 = q[2];
+          r3 = q[3];
+        }
+        UvTri t;
+        t.x0 = r0.x; t.y0 = r0.y; t.x1 = r0.z; t.y1 = r0.w;
+        t.x2 = r1.x; t.y2 = r1.y; t.inv_area = r1.z;
+        float w0, w1, w2;
+        uv_weights(t, (float)x, (float)y, w0, w1, w2);
+        c[k][0] = (w0 * r1.w + w1 * r2.z) + w2 * r3.y;
+        c[k][1] = (w0 * r2.x + w1 * r2.w) + w2 * r3.z;
+        c[k][2] = (w0 * r2.y + w1 * r3.x) + w2 * r3.w;
+      }
+      if (++x == p.W) {
+        x = 0;
+        ++y;
+      }
     }
-    c[k][0] = c[k][1] = c[k][2] = 0.f;
-    if (cov[k]) {
-      UvTri t;
-      t.x0 = r[k][0].x; t.y0 = r[k][0].y; t.x1 = r[k][0].z; t.y1 = r[k][0].w;
-      t.x2 = r[k][1].x; t.y2 = r[k][1].y; t.inv_area = r[k][1].z;
-      float w0, w1, w2;
-      uv_weights(t, (float)x, (float)y, w0, w1, w2);
-      c[k][0] = (w0 * r[k][1].w + w1 * r[k][2].z) + w2 * r[k][3].y;
-      c[k][1] = (w0 * r[k][2].x + w1 * r[k][2].w) + w2 * r[k][3].z;
-      c[k][2] = (w0 * r[k][2].y + w1 * r[k][3].x) + w2 * r[k][3].w;
+  } else {
+    // One dependent level after the winners: the 64-byte face records of the (up to 4) distinct
+    // winners are requested together; a texel whose winner equals its left neighbour's reuses the
+    // neighbour's registers.
+    float4 r[4][4];
+  #pragma unroll
+    for (int k = 0; k < 4; k++) {
+      cov[k] = f[k] >= 0;
+      const bool need = cov[k] && (k == 0 || f[k] != f[k - 1]);
+      if (need) {
+        const float4* q = p.rec + 4 * (size_t)f[k];
+        r[k][0] = q[0];  // plain loads: written by uv_setup_kernel of this call
+        r[k][1] = q[1];
+        r[k][2] = q[2];
+        r[k][3] = q[3];
+      }
     }
-    if (++x == p.W) {
-      x = 0;
-      ++y;
+    int y = (int)((unsigned)base / (unsigned)p.W), x = (int)((unsigned)base - (unsigned)y * (unsigned)p.W);
+  #pragma unroll
+    for (int k = 0; k < 4; k++) {
+      if (k > 0 && cov[k] && f[k] == f[k - 1]) {
+        r[k][0] = r[k - 1][0];
+        r[k][1] = r[k - 1][1];
+        r[k][2] = r[k - 1][2];
+        r[k][3] = r[k - 1][3];
+      }
+      c[k][0] = c[k][1] = c[k][2] = 0.f;
+      if (cov[k]) {
+        UvTri t;
+        t.x0 = r[k][0].x; t.y0 = r[k][0].y; t.x1 = r[k][0].z; t.y1 = r[k][0].w;
+        t.x2 = r[k][1].x; t.y2 = r[k][1].y; t.inv_area = r[k][1].z;
+        float w0, w1, w2;
+        uv_weights(t, (float)x, (float)y, w0, w1, w2);
+        c[k][0] = (w0 * r[k][1].w + w1 * r[k][2].z) + w2 * r[k][3].y;
+        c[k][1] = (w0 * r[k][2].x + w1 * r[k][2].w) + w2 * r[k][3].z;
+        c[k][2] = (w0 * r[k][2].y + w1 * r[k][3].x) + w2 * r[k][3].w;
+      }
+      if (++x == p.W) {
+        x = 0;
+        ++y;
+      }
     }
   }
   const bool any = cov[0] || cov[1] || cov[2] || cov[3];
@@ -372,7 +431,8 @@ __device__ __forceinline__ void uv_resolve_group(const UvRasterParams& p, size_t
 // cta_base + j * 1024 + 4 t (every load / store instruction of a warp is contiguous).  All winner
 // loads of a thread are issued before the first is consumed: with the L2 cold, a single 16-byte
 // request per thread leaves too few bytes in flight to cover the DRAM latency.
-__global__ void __launch_bounds__(256, 2) uv_resolve_kernel(const UvRasterParams p) {
+template <bool RUNS>
+__global__ void __launch_bounds__(256, RUNS ? 3 : 2) uv_resolve_kernel(const UvRasterParams p) {
   const size_t P = (size_t)p.W * p.H;
   if (blockIdx.x == 0 && threadIdx.x == 0) p.counter[0] = 0ull;  // queue reset for the next call
   const size_t cta_base = (size_t)blockIdx.x * (256u * 4u * kUvGroupsPerThread);
@@ -398,7 +458,7 @@ __global__ void __launch_bounds__(256, 2) uv_resolve_kernel(const UvRasterParams
     } else {
       for (int k = 0; k < 4 && base[j] + k < P; k++) p.win[base[j] + k] = -1;
     }
-    uv_resolve_group(p, P, base[j], full, f[j]);
+    uv_resolve_group<RUNS>(p, P, base[j], full, f[j]);
   }
 }
 
