@@ -1825,11 +1825,23 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
   p.mask = mask_dev;
   uv_setup_kernel<<<Blocks((size_t)p.F, 256), 256, 0, st>>>(p);
   uv_tile_kernel<<<(unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, 0, st>>>(p);
-  // long runs of one winner (at least 64 texels per face on average) take the one-live-record instantiation
-  if (P >= (size_t)64 * (size_t)std::max(d->num_faces, 1))
-    uv_resolve_kernel<true><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
-  else
+  // Long runs of one winner (>= 64 texels per face on average: vc2tex) take the 16-texels-per-thread kernel with one
+  // live record; meshes of texel-sized faces (posmap) the lane-per-texel kernel (one record per thread, 6 CTAs per
+  // SM).  Measured both ways (profiles/r05p_uvraster_bench_lane*.jsonl): posmap 0.108 -> 0.094 ms with the lane
+  // kernel, vc2tex 0.119 -> 0.147 ms.  UGU_B200_UV_RESOLVE=0: the first form (four records per thread) for both.
+  // (1 / 2 force the lane / the one-live-record kernel: the tests run every fixture through each)
+  const int uv_resolve_mode = getenv("UGU_B200_UV_RESOLVE") ? atoi(getenv("UGU_B200_UV_RESOLVE")) : -1;
+  const bool long_runs = uv_resolve_mode == 1 ? false
+                         : (uv_resolve_mode == 2 ? true : P >= (size_t)64 * (size_t)std::max(d->num_faces, 1));
+  if (uv_resolve_mode == 0 && !long_runs) {
     uv_resolve_kernel<false><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
+  } else if (long_runs) {
+    uv_resolve_kernel<true><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
+  } else {
+    const unsigned chunks = (unsigned)((P + 31) / 32);
+    const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 6), (chunks + 7) / 8));
+    uv_resolve_lane_kernel<<<grid, 256, 0, st>>>(p);
+  }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += 3;
   return UGU_B200_OK;

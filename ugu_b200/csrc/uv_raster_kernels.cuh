@@ -462,6 +462,111 @@ __global__ void __launch_bounds__(256, RUNS ? 3 : 2) uv_resolve_kernel(const UvR
   }
 }
 
+// UV-K3, lane-per-texel form: a warp owns 32 consecutive texels (chunk), walks chunks with a grid stride, and has
+// the next chunk's winners in flight while it works.  One face record (16 registers) per thread instead of four, so
+// the kernel runs at 6 CTAs per SM instead of 2 — it is a dependent chain winner -> record -> weights -> store, and
+// occupancy is what hides it.  Texels of a chunk are staged in shared memory and leave as full-width vector stores
+// (96 B of u8 / 384 B of f32 per chunk, 32 mask bytes); chunks nothing covers write their zeros at once.  The
+// in/out forms (keep_texture / keep_mask) and a ragged last chunk store per texel.
+__global__ void __launch_bounds__(256, 6) uv_resolve_lane_kernel(const UvRasterParams p) {
+  __shared__ __align__(16) float s_f[8][96];
+  __shared__ __align__(16) unsigned char s_b[8][96];
+  const unsigned P = (unsigned)p.W * (unsigned)p.H;  // W * H < 2^31 (validated by the host)
+  if (blockIdx.x == 0 && threadIdx.x == 0) p.counter[0] = 0ull;  // queue reset for the next call
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const unsigned nchunks = (P + 31u) >> 5, nwarps = gridDim.x * 8u;
+  unsigned chunk = blockIdx.x * 8u + warp;
+  int f_next = -1;
+  if (chunk < nchunks && chunk * 32u + lane < P) f_next = p.win[chunk * 32u + lane];
+  for (; chunk < nchunks; chunk += nwarps) {
+    const int f = f_next;
+    const unsigned base = chunk * 32u, t = base + lane;
+    f_next = -1;
+    if (chunk + nwarps < nchunks && t + nwarps * 32u < P) f_next = p.win[t + nwarps * 32u];
+    const bool full = base + 32u <= P;
+    const bool cov = f >= 0;
+    const unsigned any = __ballot_sync(0xffffffffu, cov);
+    const bool vec = full && !p.keep_texture;
+    if (any == 0u) {
+      if (vec) {
+        if (p.texture_f32) {
+          if (lane < 24u) reinterpret_cast<float4*>(reinterpret_cast<float*>(p.texture) + (size_t)base * 3)[lane] =
+              make_float4(0.f, 0.f, 0.f, 0.f);
+        } else if (lane < 6u) {
+          reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.texture) + (size_t)base * 3)[lane] = make_uint4(0u, 0u, 0u, 0u);
+        }
+      } else if (!p.keep_texture && t < P) {
+        for (int q = 0; q < 3; q++) {
+          if (p.texture_f32) reinterpret_cast<float*>(p.texture)[(size_t)t * 3 + q] = 0.f;
+          else reinterpret_cast<uint8_t*>(p.texture)[(size_t)t * 3 + q] = 0;
+        }
+      }
+      if (p.mask && !p.keep_mask) {
+        if (full) {
+          if (lane < 8u) reinterpret_cast<unsigned*>(p.mask + base)[lane] = 0u;
+        } else if (t < P) {
+          p.mask[t] = 0;
+        }
+      }
+      continue;
+    }
+    if (cov) p.win[t] = -1;  // leave the winner buffer clear for the next call
+    float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+    if (cov) {
+      const float4* q = p.rec + 4 * (size_t)f;  // plain loads: written by uv_setup_kernel of this call
+      const float4 r0 = q[0], r1 = q[1], r2 = q[2], r3 = q[3];
+      const unsigned y = t / (unsigned)p.W, x = t - y * (unsigned)p.W;
+      UvTri tr;
+      tr.x0 = r0.x; tr.y0 = r0.y; tr.x1 = r0.z; tr.y1 = r0.w;
+      tr.x2 = r1.x; tr.y2 = r1.y; tr.inv_area = r1.z;
+      float w0, w1, w2;
+      uv_weights(tr, (float)x, (float)y, w0, w1, w2);
+      c0 = (w0 * r1.w + w1 * r2.z) + w2 * r3.y;
+      c1 = (w0 * r2.x + w1 * r2.w) + w2 * r3.z;
+      c2 = (w0 * r2.y + w1 * r3.x) + w2 * r3.w;
+    }
+    if (vec) {
+      if (p.texture_f32) {
+        s_f[warp][lane * 3u + 0u] = c0;
+        s_f[warp][lane * 3u + 1u] = c1;
+        s_f[warp][lane * 3u + 2u] = c2;
+        __syncwarp();
+        if (lane < 24u) reinterpret_cast<float4*>(reinterpret_cast<float*>(p.texture) + (size_t)base * 3)[lane] =
+            reinterpret_cast<const float4*>(s_f[warp])[lane];
+      } else {
+        s_b[warp][lane * 3u + 0u] = cov ? (unsigned char)uv_to_u8(c0) : (unsigned char)0;
+        s_b[warp][lane * 3u + 1u] = cov ? (unsigned char)uv_to_u8(c1) : (unsigned char)0;
+        s_b[warp][lane * 3u + 2u] = cov ? (unsigned char)uv_to_u8(c2) : (unsigned char)0;
+        __syncwarp();
+        if (lane < 6u) reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.texture) + (size_t)base * 3)[lane] =
+            reinterpret_cast<const uint4*>(s_b[warp])[lane];
+      }
+      __syncwarp();  // the staging rows are rewritten by the next chunk
+    } else if (t < P && (cov || !p.keep_texture)) {
+      if (p.texture_f32) {
+        float* o = reinterpret_cast<float*>(p.texture) + (size_t)t * 3;
+        o[0] = c0; o[1] = c1; o[2] = c2;
+      } else {
+        uint8_t* o = reinterpret_cast<uint8_t*>(p.texture) + (size_t)t * 3;
+        o[0] = cov ? (uint8_t)uv_to_u8(c0) : 0;
+        o[1] = cov ? (uint8_t)uv_to_u8(c1) : 0;
+        o[2] = cov ? (uint8_t)uv_to_u8(c2) : 0;
+      }
+    }
+    if (p.mask) {
+      if (full && !p.keep_mask) {
+        if (lane < 8u) {
+          const unsigned nb = (any >> (lane * 4u)) & 15u;
+          reinterpret_cast<unsigned*>(p.mask + base)[lane] = ((nb * 0x00204081u) & 0x01010101u) * 0xFFu;
+        }
+      } else if (t < P) {
+        if (cov) p.mask[t] = 255;
+        else if (!p.keep_mask) p.mask[t] = 0;
+      }
+    }
+  }
+}
+
 __global__ void fill_i32(int* __restrict__ p, size_t n, int v) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
