@@ -1588,19 +1588,20 @@ int RaytraceView(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const float
   rp.ray_a = (float4*)r->rt_rays.p;
   rp.ray_b = rp.ray_a + P;
   const ShadeParams sp = MakeShade(r, dout, P);
+  const bool pdl = r->use_pdl;
   // occlusion ordering of rt_raster_kernel, same policy as the rasterizer's
   if (m.grp != nullptr && (r->two_pass >= 0 ? r->two_pass != 0 : m.F >= kTwoPassMinFaces)) fr.order = (int*)r->order.p;
   const size_t vthreads = std::max<size_t>(std::max<size_t>((size_t)m.V, (size_t)vp.W + vp.H), ((size_t)m.F + 255) / 256);
-  CU_TRY(r, LaunchView(vertex_kernel_b<1>, Blocks(vthreads, 256), 256, st, false, vb, 1, m, fr));
-  CU_TRY(r, LaunchView(rt_ray_kernel, Blocks(P, 256), 256, st, false, vp, fr, rp));
+  CU_TRY(r, LaunchView(vertex_kernel_b<1>, Blocks(vthreads, 256), 256, st, pdl, vb, 1, m, fr));
+  CU_TRY(r, LaunchView(rt_ray_kernel, Blocks(P, 256), 256, st, pdl, vp, fr, rp));
   int launches = 3;
   if (m.F > 0) {
-    CU_TRY(r, LaunchView(rt_raster_kernel, Blocks((size_t)m.F, 256), 256, st, false, vp, m, fr, rp));
+    CU_TRY(r, LaunchView(rt_raster_kernel, Blocks((size_t)m.F, 256), 256, st, pdl, vp, m, fr, rp));
     // resident grid: 8 CTAs of 8 warps per SM share the global job space
-    CU_TRY(r, LaunchView(rt_large_kernel, (unsigned)(g_num_sms * 8), 256, st, false, vp, m, fr, rp));
+    CU_TRY(r, LaunchView(rt_large_kernel, (unsigned)(g_num_sms * 8), 256, st, pdl, vp, m, fr, rp));
     launches += 2;
   }
-  CU_TRY(r, LaunchView(rt_resolve_kernel, Blocks(P, 256), 256, st, false, vp, m, fr, rp, sp));
+  CU_TRY(r, LaunchView(rt_resolve_kernel, Blocks(P, 256), 256, st, pdl, vp, m, fr, rp, sp));
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += launches;
   r->stats.views++;

@@ -77,7 +77,11 @@ __device__ __forceinline__ void rt_make_ray(const ViewParams& vp, const FrameDev
 
 // RT-K1: the ray table read by the candidate tests of RT-K2 / RT-K3 (32 bytes per pixel, L2-resident at
 // the BASELINE image sizes).
+// (The five kernels of a ray-cast view form a programmatic-dependent-launch chain like the rasterizer's: each lets its
+//  successor be scheduled as it starts and waits for its predecessor before it touches anything.)
 __global__ void __launch_bounds__(256) rt_ray_kernel(const ViewParams vp, const FrameDev fr, const RtParams rp) {
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
   const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
@@ -191,6 +195,8 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
                                                         const RtParams rp) {
   __shared__ RtWarpFaces sh[8];
   RtWarpFaces& S = sh[threadIdx.x >> 5];
+  pdl_launch_dependents();
+  pdl_wait();
   // faces are walked in RASTER ORDER (raster_api.cu BuildFaceOrder: a warp's 32 faces are neighbours in space,
   // so are their positions, projected vertices and nearest-hit pixels); `f` is the face id the outputs carry
   unsigned blk = blockIdx.x;
@@ -307,6 +313,8 @@ __global__ void __launch_bounds__(256) rt_raster_kernel(const ViewParams vp, con
 // job with one binary search and walks forward from there; lanes stride over a job's pixels.
 __global__ void __launch_bounds__(256) rt_large_kernel(const ViewParams vp, const MeshDev m, const FrameDev fr,
                                                        const RtParams rp) {
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned long long packed = fr.counters[0];
   const unsigned long long T = packed & kQueueJobMask;
   const unsigned n = (unsigned)(packed >> kQueueJobBits);
@@ -422,6 +430,8 @@ __global__ void __launch_bounds__(256) rt_resolve_kernel(const ViewParams vp, co
                                                          const RtParams rp, const ShadeParams sp) {
   __shared__ __align__(16) float s_n[8][96];
   __shared__ __align__(16) unsigned char s_c[8][96];
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
   const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p == 0u) {
