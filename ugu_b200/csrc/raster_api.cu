@@ -1824,8 +1824,9 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
   p.rec = (float4*)r->uv_rec.p;
   p.texture = texture_dev;
   p.mask = mask_dev;
-  uv_setup_kernel<<<Blocks((size_t)p.F, 256), 256, 0, st>>>(p);
-  uv_tile_kernel<<<(unsigned)(g_num_sms * g_binned_ctas_per_sm), 128, 0, st>>>(p);
+  const bool pdl = r->use_pdl;
+  CU_TRY(r, LaunchView(uv_setup_kernel, dim3(Blocks((size_t)p.F, 256)), 256, st, pdl, p));
+  CU_TRY(r, LaunchView(uv_tile_kernel, dim3((unsigned)(g_num_sms * g_binned_ctas_per_sm)), 128, st, pdl, p));
   // Long runs of one winner (>= 64 texels per face on average: vc2tex) take the 16-texels-per-thread kernel with one
   // live record; meshes of texel-sized faces (posmap) the lane-per-texel kernel (one record per thread, 6 CTAs per
   // SM).  Measured both ways (profiles/r05p_uvraster_bench_lane*.jsonl): posmap 0.108 -> 0.094 ms with the lane
@@ -1835,13 +1836,13 @@ int ugu_b200_uv_raster_device(ugu_b200_rasterizer* r, const ugu_b200_uv_raster_d
   const bool long_runs = uv_resolve_mode == 1 ? false
                          : (uv_resolve_mode == 2 ? true : P >= (size_t)64 * (size_t)std::max(d->num_faces, 1));
   if (uv_resolve_mode == 0 && !long_runs) {
-    uv_resolve_kernel<false><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
+    CU_TRY(r, LaunchView(uv_resolve_kernel<false>, dim3(Blocks(P, 256 * 4 * kUvGroupsPerThread)), 256, st, pdl, p));
   } else if (long_runs) {
-    uv_resolve_kernel<true><<<Blocks(P, 256 * 4 * kUvGroupsPerThread), 256, 0, st>>>(p);
+    CU_TRY(r, LaunchView(uv_resolve_kernel<true>, dim3(Blocks(P, 256 * 4 * kUvGroupsPerThread)), 256, st, pdl, p));
   } else {
     const unsigned chunks = (unsigned)((P + 31) / 32);
     const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 6), (chunks + 7) / 8));
-    uv_resolve_lane_kernel<<<grid, 256, 0, st>>>(p);
+    CU_TRY(r, LaunchView(uv_resolve_lane_kernel, dim3(grid), 256, st, pdl, p));
   }
   CU_TRY(r, cudaGetLastError());
   r->stats.kernel_launches += 3;

@@ -102,7 +102,11 @@ __device__ __forceinline__ void uv_weights(const UvTri& t, float px, float py, f
 // here by their own lane; larger ones become tile jobs: the warp's entries are appended to the queue
 // with one atomicAdd on the packed (entries, jobs) counter, so q_job is monotone over queue slots.
 // ---------------------------------------------------------------------------------------------
+// (The three kernels of a call form a programmatic-dependent-launch chain: each lets its successor be scheduled as it
+//  starts and waits for its predecessor before it touches anything.)
 __global__ void __launch_bounds__(256) uv_setup_kernel(const UvRasterParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   const unsigned lane = threadIdx.x & 31u;
   unsigned long long mine = 0ull;
@@ -177,6 +181,8 @@ __global__ void __launch_bounds__(256) uv_setup_kernel(const UvRasterParams p) {
 // the multiplication by inv_area, raster_util.h:127-135) vote with atomicMax(face).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) uv_tile_kernel(const UvRasterParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned long long packed = p.counter[0];
   const unsigned long long T = packed & kQueueJobMask;
   const unsigned n = (unsigned)(packed >> kQueueJobBits);
@@ -433,6 +439,8 @@ __device__ __forceinline__ void uv_resolve_group(const UvRasterParams& p, size_t
 // request per thread leaves too few bytes in flight to cover the DRAM latency.
 template <bool RUNS>
 __global__ void __launch_bounds__(256, RUNS ? 3 : 2) uv_resolve_kernel(const UvRasterParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const size_t P = (size_t)p.W * p.H;
   if (blockIdx.x == 0 && threadIdx.x == 0) p.counter[0] = 0ull;  // queue reset for the next call
   const size_t cta_base = (size_t)blockIdx.x * (256u * 4u * kUvGroupsPerThread);
@@ -471,6 +479,8 @@ __global__ void __launch_bounds__(256, RUNS ? 3 : 2) uv_resolve_kernel(const UvR
 __global__ void __launch_bounds__(256, 6) uv_resolve_lane_kernel(const UvRasterParams p) {
   __shared__ __align__(16) float s_f[8][96];
   __shared__ __align__(16) unsigned char s_b[8][96];
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned P = (unsigned)p.W * (unsigned)p.H;  // W * H < 2^31 (validated by the host)
   if (blockIdx.x == 0 && threadIdx.x == 0) p.counter[0] = 0ull;  // queue reset for the next call
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
