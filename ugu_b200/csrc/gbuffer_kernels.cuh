@@ -169,6 +169,8 @@ __device__ __forceinline__ bool gbuffer_pixel(const ViewParams& vp, const MeshDe
 __global__ void __launch_bounds__(256) gbuffer_kernel(const ViewParams vp, const MeshDev m, const FrameDev fr,
                                                       const GBufParams gp) {
   __shared__ __align__(16) float s_v[8][6][96];
+  pdl_launch_dependents();  // a link of the view's PDL chain: the resolve kernel behind it waits for its completion
+  pdl_wait();
   const unsigned P = (unsigned)vp.W * (unsigned)vp.H;
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const unsigned nchunks = (P + 31u) >> 5;

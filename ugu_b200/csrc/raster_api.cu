@@ -653,14 +653,14 @@ int LaunchViewSet(ugu_b200_rasterizer* r, const ugu_b200_camera* cams, int n, co
   }
   if (gbuf) {
     // G-buffer fields from the finished visibility buffer, before the resolve kernel consumes and
-    // clears it; a plain (fully serialised) launch, so the resolve kernel behind it starts when it ends
+    // clears it (both wait for their predecessor's completion before they touch anything)
     GBufParams gp = *gbuf;
     gp.backface_culling = sp.backface_culling;
     gp.have_normals = (m.num_normals > 0 && r->has_nidx) ? 1 : 0;
     gp.have_uv = (m.num_uv > 0 && r->has_uvidx) ? 1 : 0;
     const unsigned chunks = (unsigned)((P + 31) / 32);
     const unsigned grid = std::max(1u, std::min((unsigned)(g_num_sms * 8), (chunks + 7) / 8));
-    CU_TRY(r, LaunchView(gbuffer_kernel, dim3(grid), 256, st, false, vb.v[0], m, fr, gp));
+    CU_TRY(r, LaunchView(gbuffer_kernel, dim3(grid), 256, st, pdl, vb.v[0], m, fr, gp));
     r->stats.kernel_launches++;
   }
   const int nbands = (NV == 1 && bands) ? bands->n : 1;
