@@ -32,7 +32,7 @@ struct D2MParams {
   int gl, with_uv, with_color, cw, ch;
   const float* depth;
   const uint8_t* color;      // cw * ch * 3 or null
-  int* first;                // [0] = first valid grid point (INT_MAX if none)
+  int* first;                // [0] = INT_MAX - (first valid grid point), 0 if none: see d2m_first()
   unsigned long long* block_sums;  // per CTA packed (faces << 32 | vertices), scanned in place
   unsigned long long* totals;      // [0] packed totals
   int* vid;                  // per grid point: vertex id or -1
@@ -59,6 +59,10 @@ struct D2MParams {
 
 __device__ __forceinline__ void d2m_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void d2m_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// The first valid grid point (INT_MAX if none).  Stored inverted, so that "none" is 0 and one memset of zeros
+// initialises every small word of a call.
+__device__ __forceinline__ int d2m_first(const D2MParams& p) { return 0x7fffffff - *(volatile int*)p.first; }
 
 // row of grid point g (g < 2^31) without an integer division
 __device__ __forceinline__ int d2m_row(const D2MParams& p, int g) {
@@ -143,7 +147,7 @@ __global__ void __launch_bounds__(256) d2m_first_kernel(const D2MParams p) {
   const int nchunks = (G + kD2MBlock - 1) / kD2MBlock;
   for (int chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x) {
     const int base = chunk * kD2MBlock;
-    if (threadIdx.x == 0) s_known = *(volatile int*)p.first;
+    if (threadIdx.x == 0) s_known = d2m_first(p);
     __syncthreads();
     if (base > s_known) break;  // CTA-uniform
     int mine = 0x7fffffff;
@@ -163,7 +167,7 @@ __global__ void __launch_bounds__(256) d2m_first_kernel(const D2MParams p) {
 #pragma unroll
       for (int w = 1; w < 8; w++) m = min(m, s_min[w]);
       // one same-address atomic per CTA at most, and only if it can still lower the (re-read) value
-      if (m < *(volatile int*)p.first) atomicMin(p.first, m);
+      if (m < d2m_first(p)) atomicMax(p.first, 0x7fffffff - m);
     }
   }
 }
@@ -171,7 +175,7 @@ __global__ void __launch_bounds__(256) d2m_first_kernel(const D2MParams p) {
 // D2M-K2: per-CTA sums of the packed contributions
 __global__ void __launch_bounds__(256) d2m_count_kernel(const D2MParams p) {
   const int G = p.GX * p.GY;
-  const int first = p.first[0];
+  const int first = d2m_first(p);
   const int g0 = blockIdx.x * kD2MBlock + threadIdx.x * kD2MItems;
   unsigned long long sum = 0ull;
 #pragma unroll
@@ -270,7 +274,7 @@ __device__ __forceinline__ void d2m_emit_vertex(const D2MParams& p, int g, int g
 // and everything that belongs to the vertex alone: position, uv, nearest colour, point-cloud texel.
 __global__ void __launch_bounds__(256) d2m_emit_vertices_kernel(const D2MParams p) {
   const int G = p.GX * p.GY;
-  const int first = p.first[0];
+  const int first = d2m_first(p);
   // The CTA owns the same kD2MBlock consecutive grid points as in d2m_count_kernel, but walks them as
   // kD2MItems slabs of 256 with lane = consecutive grid point: loads of depth and stores of the per-point
   // images are coalesced, and the compacted vertex ids of a warp are (nearly) consecutive, so the
@@ -336,7 +340,7 @@ __global__ void __launch_bounds__(256) d2m_scan_emit_kernel(const D2MParams p, i
   __syncthreads();
   const int chunk = s_chunk;
   const int G = p.GX * p.GY;
-  const int first = *(volatile int*)p.first;
+  const int first = d2m_first(p);
   const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, lt = (1u << lane) - 1u;
   const int g0 = chunk * kD2MBlock + (int)threadIdx.x;
   const int gy0 = d2m_row(p, g0), gx0 = g0 - gy0 * p.GX;

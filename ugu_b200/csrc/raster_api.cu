@@ -2456,7 +2456,9 @@ int D2MDevice(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200
   const size_t G = (size_t)p.GX * (size_t)p.GY, P = (size_t)W * H;
   const int nblocks = (int)((G + kD2MBlock - 1) / kD2MBlock);
   int rc;
-  if ((rc = Grow(r, &r->d2m_small, 64))) return rc;
+  // one block of small words, zeroed by ONE memset per call: [0] first (inverted), [16] totals, [32] ticket, [64..] the
+  // look-back state of the single-pass kernel
+  if ((rc = Grow(r, &r->d2m_small, 64 + (size_t)std::max(nblocks, 1) * 8))) return rc;
   if ((rc = Grow(r, &r->d2m_block_sums, (size_t)std::max(nblocks, 1) * 8))) return rc;
   if ((rc = Grow(r, &r->d2m_vid, std::max<size_t>(G, 1) * 4))) return rc;
   if ((rc = Grow(r, &r->d2m_fref, std::max<size_t>(G, 1) * 4))) return rc;
@@ -2487,11 +2489,10 @@ int D2MDevice(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200
   // three-kernel count / scan / emit form (A/B).  With steps (1, 1) every pixel has a grid point beside it and the
   // kernels write the zeros of the two organized images themselves instead of two 12 B/pixel memsets.
   static const bool single_pass = !(getenv("UGU_B200_D2M_FUSED") && atoi(getenv("UGU_B200_D2M_FUSED")) == 0);
-  p.state = p.block_sums;
+  p.state = (unsigned long long*)((char*)r->d2m_small.p + 64);
   p.ticket = (int*)((char*)r->d2m_small.p + 32);
   p.zero_fill = (single_pass && x_step == 1 && y_step == 1 && G > 0) ? 1 : 0;
-  CU_TRY(r, cudaMemsetAsync(r->d2m_small.p, 0x7f, 4, st));          // first = 0x7f7f7f7f > any grid index
-  CU_TRY(r, cudaMemsetAsync((char*)r->d2m_small.p + 16, 0, 24, st));  // totals, ticket
+  CU_TRY(r, cudaMemsetAsync(r->d2m_small.p, 0, 64 + (single_pass ? (size_t)std::max(nblocks, 1) * 8 : 0), st));
   if (!p.zero_fill) {
     CU_TRY(r, cudaMemsetAsync(r->d2m_pc.p, 0, P * 12, st));            // ugu::Init(point_cloud, .., 0.0f)
     CU_TRY(r, cudaMemsetAsync(r->d2m_nimg.p, 0, P * 12, st));
@@ -2499,7 +2500,6 @@ int D2MDevice(ugu_b200_rasterizer* r, const ugu_b200_camera* cam, const ugu_b200
   if (G > 0) {
     const unsigned first_grid = (unsigned)std::min<size_t>((size_t)nblocks, (size_t)g_num_sms * 8);
     if (single_pass) {
-      CU_TRY(r, cudaMemsetAsync(p.state, 0, (size_t)nblocks * 8, st));
       d2m_first_kernel<<<first_grid, 256, 0, st>>>(p);
       const bool pdl = r->use_pdl;
       CU_TRY(r, LaunchView(d2m_scan_emit_kernel, dim3((unsigned)nblocks), 256, st, pdl, p, nblocks));
