@@ -396,3 +396,23 @@ def test_config3_turntable_on_the_device():
     assert seen.mean() > 0.8   # a horizontal turntable sees all but the faces turned up or down
     assert (st["face_max_area_id"][seen] >= 0).all() and (st["face_max_area_id"][~seen] == -1).all()
     assert st["face_count"].max() <= K
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("facewise", [False, True], ids=["vertexwise", "facewise"])
+def test_face_fold_inside_the_face_kernels_equals_the_fold_kernel(monkeypatch, name, facewise):
+    """Without dense face records the face kernels fold into the accumulators themselves (packed-key atomics);
+    the statistics must equal, bit for bit, those of the record rows + vt_fold_face_kernel path
+    (UGU_B200_VT_FOLD=0) and those of a call that also returns the records."""
+    d, mesh = load(name)
+    fused, _ = cuda_run(d, mesh, facewise, 1, records=False)
+    monkeypatch.setenv("UGU_B200_VT_FOLD", "0")
+    rows, _ = cuda_run(d, mesh, facewise, 1, records=False)
+    monkeypatch.delenv("UGU_B200_VT_FOLD")
+    full, _ = cuda_run(d, mesh, facewise, 1, records=True)
+    assert int(fused.stats["face_count"].sum()) > 0
+    for k in fused.stats:
+        for other, what in ((rows, "fold kernel"), (full, "with records")):
+            a, b = np.ascontiguousarray(fused.stats[k]), np.ascontiguousarray(other.stats[k])
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), (k, what)

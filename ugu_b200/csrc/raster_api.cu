@@ -2105,7 +2105,7 @@ int VtValidate(ugu_b200_rasterizer* r, int K, const ugu_b200_keyframe* kfs, int 
 
 // Core: keyframes with DEVICE images; `rec` = DEVICE record arrays (any NULL).  Launch sets of kVtMaxKeyframes.
 int VtRun(ugu_b200_rasterizer* r, int K, const ugu_b200_keyframe* kfs, int first_order, const ugu_b200_vis_option* o,
-          const ugu_b200_vis_records* rec, cudaStream_t st) {
+          const ugu_b200_vis_records* rec, cudaStream_t st, bool keep_face_rows = false) {
   const size_t V = (size_t)r->vt_V, F = (size_t)r->vt_F;
   int rc;
   // internal rows for the record arrays the caller does not want
@@ -2211,17 +2211,24 @@ int VtRun(ugu_b200_rasterizer* r, int K, const ugu_b200_keyframe* kfs, int first
     out.f_visible = (rec && rec->face_visible) ? rec->face_visible + (size_t)k0 * F : (uint8_t*)r->vt_fvis.p;
     out.f_rec = (rec && rec->face) ? (VtFaceRec*)rec->face + (size_t)k0 * F : (VtFaceRec*)r->vt_frec.p;
     out.owner = (unsigned*)r->vt_owner.p;
+    // no dense face records asked for: the face kernels fold into the accumulators themselves
+    const bool fold_faces = !keep_face_rows && !(rec && (rec->face || rec->face_visible)) &&
+                            !(getenv("UGU_B200_VT_FOLD") && atoi(getenv("UGU_B200_VT_FOLD")) == 0);
+    out.fold_count = fold_faces ? acc.f_count : nullptr;
+    out.fold_max_area = acc.f_max_area;
+    out.fold_min_angle = acc.f_min_angle;
+    out.fold_min_dist = acc.f_min_dist;
     const dim3 gv(Blocks(V, 256), (unsigned)nk), gf(Blocks(F, 256), (unsigned)nk);
     if (o->facewise) {
       vt_facewise_kernel<<<gf, 256, 0, st>>>(kb, vo, m, out);
       vt_owner_kernel<<<gv, 256, 0, st>>>(kb, vo, m, out);
     } else {
       vt_vertex_kernel<<<gv, 256, 0, st>>>(kb, vo, m, out);
-      vt_face_kernel<<<gf, 256, 0, st>>>(m, out);
+      vt_face_kernel<<<gf, 256, 0, st>>>(kb, m, out);
     }
-    vt_fold_face_kernel<<<Blocks(F, 256), 256, 0, st>>>(kb, nk, m, out, acc);
+    if (!fold_faces) vt_fold_face_kernel<<<Blocks(F, 256), 256, 0, st>>>(kb, nk, m, out, acc);
     vt_fold_vertex_kernel<<<Blocks(V, 256), 256, 0, st>>>(kb, nk, m, out, acc);
-    r->stats.kernel_launches += 4;
+    r->stats.kernel_launches += fold_faces ? 3 : 4;
     CU_TRY(r, cudaGetLastError());
   }
   return UGU_B200_OK;
@@ -2314,7 +2321,9 @@ int ugu_b200_visibility_test(ugu_b200_rasterizer* r, int32_t K, const ugu_b200_k
       dk[k].zbuf = (const float*)up(opt->self_occlusion ? kfs[k0 + k].zbuf : nullptr, P * 4);
     }
     CU_TRY(r, cudaGetLastError());
-    if ((rc = VtRun(r, nk, dk.data(), first_order + k0, opt, nullptr, st))) return rc;
+    // (the rows of the face records are copied out of the internal buffers below: keep them when asked for)
+    if ((rc = VtRun(r, nk, dk.data(), first_order + k0, opt, nullptr, st, want && (rec->face_visible || rec->face))))
+      return rc;
     if (want) {
       std::vector<CopySeg> segs;
       if (rec->vertex_visible) segs.push_back({rec->vertex_visible + (size_t)k0 * V, r->vt_vvis.p, (size_t)nk * V});

@@ -84,6 +84,12 @@ struct VtOut {  // dense per-keyframe records, keyframe kf of the launch set at 
   VtFaceRec* f_rec;     // rows * F
   unsigned* owner;      // kVtMaxKeyframes * V scratch of the face-wise mode, kVtNoOwner between calls
   unsigned row0;
+  // No dense face records wanted: the face kernels fold straight into the accumulators (VtAcc::f_*) with the packed
+  // keys of vt_fold_face_kernel — no rows * F records written and read back, no fold launch.  NULL = write rows.
+  unsigned* fold_count;
+  unsigned long long* fold_max_area;
+  unsigned long long* fold_min_angle;
+  unsigned long long* fold_min_dist;
 };
 
 __device__ __forceinline__ unsigned vt_f2u8(float f) {  // static_cast<unsigned char>(float), x86-64 style
@@ -203,8 +209,17 @@ __global__ void __launch_bounds__(256) vt_vertex_kernel(const VtBatch kb, const 
   vt_store_vertex(out.v_rec + row, r);
 }
 
-__device__ __forceinline__ void vt_store_face(const VtOut& out, size_t row, bool ok, float angle, float dist,
-                                              const float* tri) {
+__device__ __forceinline__ void vt_store_face(const VtOut& out, size_t row, int f, unsigned order, bool ok,
+                                              float angle, float dist, const float* tri) {
+  if (out.fold_count != nullptr) {  // same values, same keys as vt_fold_face_kernel; max / min are order independent
+    if (!ok) return;
+    const float a = 0.5f * fabsf((tri[4] - tri[0]) * (tri[3] - tri[1]) - (tri[5] - tri[1]) * (tri[2] - tri[0]));
+    atomicAdd(out.fold_count + f, 1u);
+    atomicMax(out.fold_max_area + f, ((unsigned long long)__float_as_uint(a) << 32) | (0xFFFFFFFFu - order));
+    atomicMin(out.fold_min_angle + f, ((unsigned long long)__float_as_uint(angle / 3.0f) << 32) | order);
+    atomicMin(out.fold_min_dist + f, ((unsigned long long)__float_as_uint(dist / 3.0f) << 32) | order);
+    return;
+  }
   out.f_visible[row] = ok ? 1 : 0;
   VtFaceRec fr{};
   if (ok) {
@@ -219,7 +234,7 @@ __device__ __forceinline__ void vt_store_face(const VtOut& out, size_t row, bool
 }
 
 // TestFaces (:551-604): a thread per face reads the records of its three vertices.
-__global__ void __launch_bounds__(256) vt_face_kernel(const VtMesh m, const VtOut out) {
+__global__ void __launch_bounds__(256) vt_face_kernel(const VtBatch kb, const VtMesh m, const VtOut out) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= m.F) return;
   const size_t vrow = (size_t)(out.row0 + blockIdx.y) * m.V;
@@ -238,7 +253,7 @@ __global__ void __launch_bounds__(256) vt_face_kernel(const VtMesh m, const VtOu
       ok = false;
     }
   }
-  vt_store_face(out, (size_t)(out.row0 + blockIdx.y) * m.F + f, ok, angle, dist, tri);
+  vt_store_face(out, (size_t)(out.row0 + blockIdx.y) * m.F + f, f, kb.k[blockIdx.y].order, ok, angle, dist, tri);
 }
 
 // TestFacewiseVertices (:606-668): a thread per face tests its corners, each pulled 1e-3 of the way toward the
@@ -284,7 +299,7 @@ __global__ void __launch_bounds__(256) vt_facewise_kernel(const VtBatch kb, cons
       tri[2 * j + 1] = r.projected[1];
     }
   }
-  vt_store_face(out, (size_t)(out.row0 + blockIdx.y) * m.F + f, ok, angle, dist, tri);
+  vt_store_face(out, (size_t)(out.row0 + blockIdx.y) * m.F + f, f, kb.k[blockIdx.y].order, ok, angle, dist, tri);
 }
 
 __global__ void __launch_bounds__(256) vt_owner_kernel(const VtBatch kb, const VtOption opt, const VtMesh m,
